@@ -1,0 +1,341 @@
+// tcgen05 / TMEM / TMA GEMM for sm_100a:  D[M,N] (+)= A[M,K] * B[N,K]^T   (bf16 in, fp32 accumulate)
+//
+// This single kernel family carries every GEMM-shaped op of the framework — Linear and the
+// implicit-GEMM view of Conv2d, forward, data-gradient and weight-gradient — i.e. the work the
+// reference delegates to cuDNN/cuBLAS through nn.Conv2d / nn.Linear
+// (reference example/models.py:8-13,28-43; SURVEY.md §2.5, work-list rows K6-K9).
+//
+// Operand storage ("major"):
+//   K-major  A: row-major [M, K] (lda)      MN-major A: row-major [K, M] (lda)   (i.e. A^T is stored)
+//   K-major  B: row-major [N, K] (ldb)      MN-major B: row-major [K, N] (ldb)
+// so that, with X the activation/column matrix, W the [Cout, K] weight and dY the output gradient:
+//   fprop  Y  = X  * W^T      : A = X  (K-major),   B = W  (K-major)
+//   dgrad  dX = dY * W        : A = dY (K-major),   B = W  (MN-major)     -- no transposed weight copy
+//   wgrad  dW = dY^T * X      : A = dY (MN-major),  B = X  (MN-major)     -- no transposes at all
+//
+// Structure (one CTA per 128 x BN output tile and K-split):
+//   warp 0   : TMA producer  (cp.async.bulk.tensor.2d, 128B swizzle, kStages-deep mbarrier ring)
+//   warp 1   : allocates TMEM, one lane issues tcgen05.mma (M=128, N=BN, K=16) and tcgen05.commit
+//   warps 2-5: epilogue — tcgen05.ld the fp32 accumulator (one TMEM lane = one output row per thread),
+//              fused bias / ReLU / bf16 cast, or vector red.add for split-K and gradient accumulation,
+//              optionally scattering columns (kh,kw,cin)->(cin,kh,kw) so conv weight gradients land
+//              directly in the PyTorch-layout fp32 gradient arena.
+#include "common.cuh"
+
+namespace dmlb {
+
+constexpr int kBM = 128;
+constexpr int kBK = 64;             // 64 bf16 = one 128-byte swizzle row
+constexpr int kUmmaK = 16;
+constexpr int kGemmThreads = 192;   // 6 warps
+
+struct GemmEpilogue {
+    void* out;            // bf16 or fp32
+    const float* bias;    // [N] or nullptr
+    int ldo;              // elements
+    int out_is_f32;
+    int relu;
+    int atomic;           // red.add into fp32 out
+    int perm_cin;         // >0: out column c -> (c % perm_cin) * perm_khw + c / perm_cin
+    int perm_khw;
+};
+
+template <int BN>
+struct GemmSmem {
+    static constexpr int kABytes = kBM * kBK * 2;  // 16 KiB
+    static constexpr int kBBytes = BN * kBK * 2;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kStages = (BN <= 64) ? 6 : (BN <= 128 ? 5 : 4);
+    static constexpr int kBarrierBytes = 256;
+    static constexpr int kTotal = kStages * kStageBytes + kBarrierBytes + 1024;  // +1024: manual 1 KiB alignment
+};
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                         GemmEpilogue ep, int M, int N, int K, int kb_per_split) {
+    using S = GemmSmem<BN>;
+    constexpr int kStages = S::kStages;
+    constexpr int kTmemCols = BN < 32 ? 32 : BN;
+    static_assert(BN % 16 == 0 && BN >= 32 && BN <= 256, "UMMA M=128 needs N%16==0, 16<=N<=256");
+    static_assert(!B_MN || BN % 64 == 0, "MN-major B tiles are built from 64-wide TMA boxes");
+
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_base = smem_base + kStages * S::kStageBytes;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
+    const uint32_t tmem_full_bar = bar_base + 8u * (2 * kStages);
+    const uint32_t tmem_holder = bar_base + 8u * (2 * kStages + 1);
+    uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+    volatile uint32_t* tmem_holder_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + kStages * S::kStageBytes + 8 * (2 * kStages + 1));
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int m0 = blockIdx.x * kBM;
+    const int n0 = blockIdx.y * BN;
+    const int nkb_total = (K + kBK - 1) / kBK;
+    const int kb_begin = blockIdx.z * kb_per_split;
+    const int kb_end = min(nkb_total, kb_begin + kb_per_split);
+    const int nkb = kb_end - kb_begin;  // host guarantees >= 1
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(full_bar(s), 1);
+            mbar_init(empty_bar(s), 1);
+        }
+        mbar_init(tmem_full_bar, 1);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc<kTmemCols>(tmem_holder);
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_d = *tmem_holder_ptr;
+
+    if (warp == 0) {
+        // ------------------------------ TMA producer ------------------------------
+        if (lane == 0) {
+            for (int it = 0; it < nkb; ++it) {
+                const int s = it % kStages;
+                const uint32_t ph = (it / kStages) & 1u;
+                mbar_wait(empty_bar(s), ph ^ 1u);
+                const uint32_t a_dst = smem_base + s * S::kStageBytes;
+                const uint32_t b_dst = a_dst + S::kABytes;
+                const int k0 = (kb_begin + it) * kBK;
+                mbar_arrive_expect_tx(full_bar(s), S::kStageBytes);
+                if constexpr (!A_MN) {
+                    tma_load_2d(a_dst, &tma_a, k0, m0, full_bar(s));
+                } else {
+                    tma_load_2d(a_dst, &tma_a, m0, k0, full_bar(s));
+                    tma_load_2d(a_dst + 8192, &tma_a, m0 + 64, k0, full_bar(s));
+                }
+                if constexpr (!B_MN) {
+                    tma_load_2d(b_dst, &tma_b, k0, n0, full_bar(s));
+                } else {
+#pragma unroll
+                    for (int j = 0; j < BN / 64; ++j) tma_load_2d(b_dst + j * 8192, &tma_b, n0 + 64 * j, k0, full_bar(s));
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------ MMA issuer ------------------------------
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, A_MN, B_MN);
+            for (int it = 0; it < nkb; ++it) {
+                const int s = it % kStages;
+                const uint32_t ph = (it / kStages) & 1u;
+                mbar_wait(full_bar(s), ph);
+                tcgen05_fence_after();
+                const uint32_t a_src = smem_base + s * S::kStageBytes;
+                const uint32_t b_src = a_src + S::kABytes;
+#pragma unroll
+                for (int k = 0; k < kBK / kUmmaK; ++k) {
+                    // K-major: step 16 bf16 = 32 B inside the 128 B swizzle row.
+                    // MN-major: step 16 K-rows = two 8-row groups = 2048 B.
+                    const uint64_t adesc = A_MN ? umma_smem_desc(a_src + k * 2048, 8192, 1024) : umma_smem_desc(a_src + k * 32, 16, 1024);
+                    const uint64_t bdesc = B_MN ? umma_smem_desc(b_src + k * 2048, 8192, 1024) : umma_smem_desc(b_src + k * 32, 16, 1024);
+                    umma_bf16(tmem_d, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                }
+                umma_commit(empty_bar(s));  // smem stage reusable once these MMAs retire
+            }
+            umma_commit(tmem_full_bar);     // accumulator complete
+        }
+    } else {
+        // ------------------------------ epilogue ------------------------------
+        const int q = warp & 3;                 // TMEM lane quadrant this warp may access
+        const int row = m0 + q * 32 + lane;
+        mbar_wait(tmem_full_bar, 0);
+        tcgen05_fence_after();
+        const bool row_ok = row < M;
+        const bool add_bias = ep.bias != nullptr && (!ep.atomic || blockIdx.z == 0);
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+            if (n0 + c0 >= N) break;  // warp-uniform
+            uint32_t v[32];
+            tmem_ld_32x32(tmem_d + (static_cast<uint32_t>(q * 32) << 16) + c0, v);
+            tmem_ld_wait();
+            if (!row_ok) continue;
+            const int col0 = n0 + c0;
+            const int ncols = min(32, N - col0);
+            float f[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                float x = __uint_as_float(v[j]);
+                if (add_bias && j < ncols) x += __ldg(ep.bias + col0 + j);
+                if (ep.relu) x = fmaxf(x, 0.f);
+                f[j] = x;
+            }
+            if (ep.atomic) {
+                float* o = static_cast<float*>(ep.out) + static_cast<size_t>(row) * ep.ldo;
+                if (ep.perm_cin > 0) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const int c = col0 + j;
+                        if (j < ncols) red_add_f32(o + (c % ep.perm_cin) * ep.perm_khw + c / ep.perm_cin, f[j]);
+                    }
+                } else if (ncols == 32 && (ep.ldo & 3) == 0) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) red_add_f32x4(o + col0 + j, f[j], f[j + 1], f[j + 2], f[j + 3]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j < ncols) red_add_f32(o + col0 + j, f[j]);
+                }
+            } else if (ep.out_is_f32) {
+                float* o = static_cast<float*>(ep.out) + static_cast<size_t>(row) * ep.ldo;
+                if (ep.perm_cin > 0) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const int c = col0 + j;
+                        if (j < ncols) o[(c % ep.perm_cin) * ep.perm_khw + c / ep.perm_cin] = f[j];
+                    }
+                } else if (ncols == 32 && (ep.ldo & 3) == 0) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) st_f32x4(o + col0 + j, make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]));
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j < ncols) o[col0 + j] = f[j];
+                }
+            } else {
+                __nv_bfloat16* o = static_cast<__nv_bfloat16*>(ep.out) + static_cast<size_t>(row) * ep.ldo;
+                if (ncols == 32 && (ep.ldo & 7) == 0) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 8) {
+                        uint4 pk;
+                        pk.x = pack_bf16x2(f[j], f[j + 1]);
+                        pk.y = pack_bf16x2(f[j + 2], f[j + 3]);
+                        pk.z = pack_bf16x2(f[j + 4], f[j + 5]);
+                        pk.w = pack_bf16x2(f[j + 6], f[j + 7]);
+                        *reinterpret_cast<uint4*>(o + col0 + j) = pk;
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j < ncols) o[col0 + j] = __float2bfloat16_rn(f[j]);
+                }
+            }
+        }
+    }
+
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc<kTmemCols>(tmem_d);
+    }
+}
+
+// ----------------------------------------------------------------------------------------------
+// host side
+// ----------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// 2-D bf16 tensor map over a row-major [outer, inner] matrix with row pitch ld (elements), 128B swizzle.
+static int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
+                          uint32_t box_outer) {
+    EncodeTiledFn fn = get_encode_fn();
+    DMLB_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point not available");
+    DMLB_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base must be 16-byte aligned");
+    DMLB_REQUIRE((ld * 2) % 16 == 0, "TMA row pitch must be a multiple of 16 bytes (ld % 8 == 0 for bf16)");
+    cuuint64_t dims[2] = {inner, outer};
+    cuuint64_t strides[1] = {ld * 2};
+    cuuint32_t box[2] = {box_inner, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char buf[256];
+        snprintf(buf, sizeof(buf), "cuTensorMapEncodeTiled failed: CUresult %d (inner=%llu outer=%llu ld=%llu box=%ux%u)", (int)r,
+                 (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)ld, box_inner, box_outer);
+        dmlb_set_error(buf);
+        return -3;
+    }
+    return 0;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpilogue& ep, int M, int N, int K, int splits,
+                       cudaStream_t stream) {
+    using S = GemmSmem<BN>;
+    auto kern = gemm_bf16_tcgen05_kernel<BN, A_MN, B_MN>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        DMLB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
+        attr_set = true;
+    }
+    const int nkb = (K + kBK - 1) / kBK;
+    int kb_per = (nkb + splits - 1) / splits;
+    splits = (nkb + kb_per - 1) / kb_per;  // every z-slice owns >= 1 k-block
+    dim3 grid((M + kBM - 1) / kBM, (N + BN - 1) / BN, splits);
+    kern<<<grid, kGemmThreads, S::kTotal, stream>>>(ta, tb, ep, M, N, K, kb_per);
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace dmlb
+
+using namespace dmlb;
+
+// See include/dmlb.h for the contract.
+extern "C" int dmlb_gemm_bf16(const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major, int M, int N, int K,
+                              void* out, int out_is_f32, int ldo, const float* bias, int relu, int split_k, int atomic,
+                              int perm_cin, int perm_khw, int tile_n, void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    DMLB_REQUIRE(M > 0 && N > 0 && K > 0, "empty GEMM");
+    if (split_k < 1) split_k = 1;
+    if (split_k > 1) atomic = 1;
+    DMLB_REQUIRE(!atomic || out_is_f32, "atomic / split-K output must be fp32");
+    DMLB_REQUIRE(!(atomic && relu), "ReLU cannot be fused into an accumulating epilogue");
+    DMLB_REQUIRE(!a_mn_major || b_mn_major, "A MN-major with B K-major is not instantiated");
+
+    int BN = tile_n;
+    if (BN == 0) BN = (N > 64) ? 128 : (N > 32 ? 64 : 32);
+    if (b_mn_major && BN < 64) BN = 64;
+    DMLB_REQUIRE(BN == 32 || BN == 64 || BN == 128 || BN == 256, "tile_n must be 32, 64, 128 or 256");
+
+    CUtensorMap ta, tb;
+    int rc;
+    if (!a_mn_major) rc = make_tmap_bf16(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, kBK, kBM);
+    else             rc = make_tmap_bf16(&ta, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, kBK);
+    if (rc) return rc;
+    if (!b_mn_major) rc = make_tmap_bf16(&tb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, kBK, (uint32_t)BN);
+    else             rc = make_tmap_bf16(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, kBK);
+    if (rc) return rc;
+
+    GemmEpilogue ep;
+    ep.out = out; ep.bias = bias; ep.ldo = ldo; ep.out_is_f32 = out_is_f32; ep.relu = relu; ep.atomic = atomic;
+    ep.perm_cin = perm_cin; ep.perm_khw = perm_khw;
+
+#define DMLB_GEMM_CASE(bn, amn, bmn) \
+    if (BN == bn && (bool)a_mn_major == amn && (bool)b_mn_major == bmn) return launch_gemm<bn, amn, bmn>(ta, tb, ep, M, N, K, split_k, stream);
+    DMLB_GEMM_CASE(32, false, false)
+    DMLB_GEMM_CASE(64, false, false)
+    DMLB_GEMM_CASE(128, false, false)
+    DMLB_GEMM_CASE(256, false, false)
+    DMLB_GEMM_CASE(64, false, true)
+    DMLB_GEMM_CASE(128, false, true)
+    DMLB_GEMM_CASE(64, true, true)
+    DMLB_GEMM_CASE(128, true, true)
+#undef DMLB_GEMM_CASE
+    dmlb_set_error("dmlb_gemm_bf16: no kernel instantiated for this (tile_n, major) combination");
+    return -4;
+}

@@ -1,0 +1,45 @@
+// Host-side runtime glue shared by every kernel launcher: last-error string, kernel-launch
+// accounting (bench.py reports "gpu_launches" from it) and device queries.
+// No counterpart in the reference (it has no native code).
+#include <atomic>
+#include <mutex>
+#include <string>
+
+#include "common.cuh"
+
+namespace {
+std::mutex g_err_mu;
+std::string g_last_error;
+std::atomic<long long> g_launches{0};
+}  // namespace
+
+extern "C" void dmlb_set_error(const char* msg) {
+    std::lock_guard<std::mutex> lk(g_err_mu);
+    g_last_error = msg ? msg : "";
+}
+
+extern "C" const char* dmlb_last_error() {
+    std::lock_guard<std::mutex> lk(g_err_mu);
+    static thread_local std::string copy;
+    copy = g_last_error;
+    return copy.c_str();
+}
+
+extern "C" void dmlb_count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+extern "C" long long dmlb_launch_count() { return g_launches.load(std::memory_order_relaxed); }
+extern "C" void dmlb_reset_launch_count() { g_launches.store(0, std::memory_order_relaxed); }
+
+extern "C" int dmlb_abi_version() { return 1; }
+
+// Number of SMs of the current device (148 on B200); used to size persistent / flat grids.
+extern "C" int dmlb_sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
