@@ -1,0 +1,300 @@
+// Loss, optimizer, dropout and cast kernels (single-GPU part of the training step).
+//
+// Reference call sites replaced:
+//   F.cross_entropy + torch.max(outputs, 1)      example/main.py:71,75,124-125   -> softmax_xent (K11)
+//   per-tensor p.data.add_(-lr, grad) loop       asgd/optim/Asynchronous.py:63-68 -> sgd_flat (K5)
+//   accumulated_gradients.add_(-lr, gradients)   asgd/optim/Asynchronous.py:55    -> folded into sgd_flat
+//   Dropout2d / F.dropout                        example/models.py:10,17,20       -> dropout (K12)
+#include "common.cuh"
+
+namespace dmlb {
+
+// ---------------------------------------------------------------------------------------------
+// softmax cross-entropy, forward + backward in one launch (one CTA, one warp per row at a time).
+//   logits : fp32 or bf16 [B, ldl]
+//   labels : int64 [B]
+//   metrics: fp32 [2] <- { mean loss, number of rows whose arg-max equals the label }
+//   dlogits: same dtype as logits, [B, ldd] <- (softmax - onehot) / B   (may be null: evaluation)
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ float to_f32(T v);
+template <>
+__device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <typename T>
+__device__ __forceinline__ T from_f32(float v);
+template <>
+__device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+template <typename T>
+__global__ void __launch_bounds__(1024) softmax_xent_kernel(const T* __restrict__ logits, const long long* __restrict__ labels,
+                                                            float* __restrict__ metrics, T* __restrict__ dlogits, int B, int C,
+                                                            int ldl, int ldd) {
+    __shared__ float s_loss[32];
+    __shared__ float s_hit[32];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    float loss_acc = 0.f, hit_acc = 0.f;
+    const float inv_b = 1.f / static_cast<float>(B);
+    for (int r = warp; r < B; r += nwarps) {
+        const T* row = logits + static_cast<size_t>(r) * ldl;
+        const int label = static_cast<int>(labels[r]);
+        float mx = -INFINITY;
+        int arg = 0x7fffffff;
+        for (int c = lane; c < C; c += 32) {
+            const float v = to_f32<T>(row[c]);
+            if (v > mx) { mx = v; arg = c; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+            const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+            if (om > mx || (om == mx && oa < arg)) { mx = om; arg = oa; }
+        }
+        float se = 0.f;
+        for (int c = lane; c < C; c += 32) se += __expf(to_f32<T>(row[c]) - mx);
+        se = warp_sum(se);
+        const float lse = mx + __logf(se);
+        if (dlogits != nullptr) {
+            T* drow = dlogits + static_cast<size_t>(r) * ldd;
+            for (int c = lane; c < C; c += 32) {
+                const float p = __expf(to_f32<T>(row[c]) - lse);
+                drow[c] = from_f32<T>((p - (c == label ? 1.f : 0.f)) * inv_b);
+            }
+        }
+        if (lane == 0) {
+            loss_acc += (label >= 0 && label < C) ? (lse - to_f32<T>(row[label])) : 0.f;
+            hit_acc += (arg == label) ? 1.f : 0.f;
+        }
+    }
+    if (lane == 0) { s_loss[warp] = loss_acc; s_hit[warp] = hit_acc; }
+    __syncthreads();
+    if (warp == 0) {
+        float l = lane < nwarps ? s_loss[lane] : 0.f;
+        float h = lane < nwarps ? s_hit[lane] : 0.f;
+        l = warp_sum(l);
+        h = warp_sum(h);
+        if (lane == 0) { metrics[0] = l * inv_b; metrics[1] = h; }
+    }
+}
+
+// x[r, c] *= *scale  (bf16, padded rows) — applies an upstream scalar gradient to the saved dlogits.
+__global__ void __launch_bounds__(256) scale_rows_kernel(__nv_bfloat16* __restrict__ x, const float* __restrict__ scale, long long rows, int C,
+                                                         int ld) {
+    const float s = *scale;
+    const long long total = rows * C;
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
+        const long long r = i / C;
+        const int c = static_cast<int>(i % C);
+        x[r * ld + c] = __float2bfloat16_rn(__bfloat162float(x[r * ld + c]) * s);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Flat SGD over the parameter arena, one launch for the whole model:
+//   g  = grad + wd * theta;   v = mu * v + g (if momentum);   theta -= lr * g;   acc -= lr * g (if acc)
+// lr is read from device memory so a captured CUDA graph follows LR-scheduler changes.
+// n must be a multiple of 4 (the arena pads to that).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ params, const float* __restrict__ grads, float* __restrict__ acc,
+                                                       float* __restrict__ mom, long long n4, const float* __restrict__ lr_ptr, float mu,
+                                                       float wd) {
+    const float lr = *lr_ptr;
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
+        float4 p = reinterpret_cast<float4*>(params)[i];
+        float4 g = ld_stream_f32x4(grads + 4 * i);
+        if (wd != 0.f) { g.x += wd * p.x; g.y += wd * p.y; g.z += wd * p.z; g.w += wd * p.w; }
+        if (mom != nullptr) {
+            float4 v = reinterpret_cast<float4*>(mom)[i];
+            v.x = mu * v.x + g.x; v.y = mu * v.y + g.y; v.z = mu * v.z + g.z; v.w = mu * v.w + g.w;
+            reinterpret_cast<float4*>(mom)[i] = v;
+            g = v;
+        }
+        p.x -= lr * g.x; p.y -= lr * g.y; p.z -= lr * g.z; p.w -= lr * g.w;
+        reinterpret_cast<float4*>(params)[i] = p;
+        if (acc != nullptr) {
+            float4 a = reinterpret_cast<float4*>(acc)[i];
+            a.x -= lr * g.x; a.y -= lr * g.y; a.z -= lr * g.z; a.w -= lr * g.w;
+            reinterpret_cast<float4*>(acc)[i] = a;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// bf16 "shadow" weights for the tensor cores, refreshed from the fp32 master arena in one launch.
+// Each table entry describes one weight tensor [rows, cin, khw] (PyTorch layout, khw = kh*kw, 1 for
+// Linear) and where its GEMM-layout copy [rows, ld] with columns ordered (khw, cin) lives.
+// ---------------------------------------------------------------------------------------------
+struct ShadowEntry {
+    long long src_off;   // elements into the fp32 arena
+    long long dst_off;   // elements into the bf16 shadow arena
+    int rows, cin, khw, ld;
+};
+
+__global__ void __launch_bounds__(256) refresh_shadows_kernel(const float* __restrict__ params, __nv_bfloat16* __restrict__ shadow,
+                                                              const ShadowEntry* __restrict__ table) {
+    const ShadowEntry e = table[blockIdx.y];
+    const int K = e.cin * e.khw;
+    const long long total = 1ll * e.rows * K;
+    const float* src = params + e.src_off;
+    __nv_bfloat16* dst = shadow + e.dst_off;
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
+        // iterate in destination order so the bf16 stores coalesce; sources are gathered (L2-resident)
+        const int r = static_cast<int>(i / K);
+        const int k = static_cast<int>(i % K);
+        const int ci = k % e.cin;
+        const int kk = k / e.cin;
+        dst[1ll * r * e.ld + k] = __float2bfloat16_rn(__ldg(src + (1ll * r * e.cin + ci) * e.khw + kk));
+    }
+}
+
+// Generic 2-D cast fp32 -> bf16 with row pitches (inputs of Linear layers fed with fp32 tensors).
+__global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, long long rows, int C,
+                                                            long long ldx, int ldy) {
+    const long long total = rows * C;
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
+        const long long r = i / C;
+        const int c = static_cast<int>(i % C);
+        y[r * ldy + c] = __float2bfloat16_rn(x[r * ldx + c]);
+    }
+}
+__global__ void __launch_bounds__(256) cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ y, long long rows, int C,
+                                                            int ldx, long long ldy) {
+    const long long total = rows * C;
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
+        const long long r = i / C;
+        const int c = static_cast<int>(i % C);
+        y[r * ldy + c] = __bfloat162float(x[r * ldx + c]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Dropout (element) / Dropout2d (whole channel of one sample), Philox-free counter hash so the mask is
+// a pure function of (seed, *step, unit index): CUDA-graph replays draw fresh masks because *step
+// lives in device memory and is bumped by dmlb_counter_bump after each use.
+//   rows x C elements, pitch ld.  unit = element index (mode 0) or (sample, channel) (mode 1; rows_per_sample = H*W).
+//   mask: uint8 [rows * C] (1 = kept), saved for the backward pass.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t mix32(uint64_t z) {  // splitmix64 finaliser
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return static_cast<uint32_t>(z >> 32);
+}
+
+__global__ void __launch_bounds__(256) dropout_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                                                          uint8_t* __restrict__ mask, long long rows, int C, int ldx, int ldy,
+                                                          int rows_per_sample, int channel_mode, float p, uint64_t seed,
+                                                          const unsigned long long* __restrict__ step) {
+    const uint64_t st = *step;
+    const float scale = 1.f / (1.f - p);
+    const uint32_t thresh = static_cast<uint32_t>(static_cast<double>(p) * 4294967296.0);
+    const long long total = rows * C;
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
+        const long long r = i / C;
+        const int c = static_cast<int>(i % C);
+        const uint64_t unit = channel_mode ? static_cast<uint64_t>((r / rows_per_sample) * C + c) : static_cast<uint64_t>(i);
+        const uint32_t rnd = mix32(seed ^ (st * 0xD1B54A32D192ED03ull) ^ (unit * 0x9E3779B97F4A7C15ull + 0x632BE59BD9B4E019ull));
+        const bool keep = rnd >= thresh;
+        mask[i] = keep ? 1 : 0;
+        y[r * ldy + c] = keep ? __float2bfloat16_rn(__bfloat162float(x[r * ldx + c]) * scale) : __float2bfloat16(0.f);
+    }
+}
+__global__ void __launch_bounds__(256) dropout_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restrict__ mask,
+                                                          __nv_bfloat16* __restrict__ dx, long long rows, int C, int lddy, int lddx, float p) {
+    const float scale = 1.f / (1.f - p);
+    const long long total = rows * C;
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
+        const long long r = i / C;
+        const int c = static_cast<int>(i % C);
+        dx[r * lddx + c] = mask[i] ? __float2bfloat16_rn(__bfloat162float(dy[r * lddy + c]) * scale) : __float2bfloat16(0.f);
+    }
+}
+__global__ void counter_bump_kernel(unsigned long long* c) { *c += 1ull; }
+
+static inline int flat_grid(long long total, int threads = 256) {
+    long long blocks = (total + threads - 1) / threads;
+    const long long cap = 148ll * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return static_cast<int>(blocks);
+}
+
+}  // namespace dmlb
+
+using namespace dmlb;
+
+extern "C" int dmlb_softmax_xent(const void* logits, int logits_is_bf16, const long long* labels, float* metrics, void* dlogits, int B, int C,
+                                 int ldl, int ldd, void* stream) {
+    DMLB_REQUIRE(B > 0 && C > 0, "empty logits");
+    int threads = 32 * ((B < 32) ? B : 32);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (logits_is_bf16)
+        softmax_xent_kernel<__nv_bfloat16><<<1, threads, 0, st>>>(static_cast<const __nv_bfloat16*>(logits), labels, metrics,
+                                                                  static_cast<__nv_bfloat16*>(dlogits), B, C, ldl, ldd);
+    else
+        softmax_xent_kernel<float><<<1, threads, 0, st>>>(static_cast<const float*>(logits), labels, metrics, static_cast<float*>(dlogits), B, C,
+                                                          ldl, ldd);
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int dmlb_scale_rows_bf16(void* x, const float* scale, long long rows, int C, int ld, void* stream) {
+    scale_rows_kernel<<<flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<__nv_bfloat16*>(x), scale, rows, C, ld);
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int dmlb_sgd_flat(float* params, const float* grads, float* acc, float* mom, long long n, const float* lr_ptr, float mu, float wd,
+                             void* stream) {
+    DMLB_REQUIRE(n % 4 == 0, "flat SGD length must be a multiple of 4 (arena padding)");
+    DMLB_REQUIRE(((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads)) & 15) == 0, "arena must be 16-byte aligned");
+    sgd_flat_kernel<<<flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream)>>>(params, grads, acc, mom, n / 4, lr_ptr, mu, wd);
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+// table: device array of n_entries ShadowEntry {int64 src_off, int64 dst_off, int32 rows, cin, khw, ld}.
+extern "C" int dmlb_refresh_shadows(const float* params, void* shadow, const void* table, int n_entries, void* stream) {
+    if (n_entries <= 0) return 0;
+    dim3 grid(96, n_entries);
+    refresh_shadows_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(params, static_cast<__nv_bfloat16*>(shadow),
+                                                                               static_cast<const ShadowEntry*>(table));
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int dmlb_cast_f32_bf16(const float* x, void* y, long long rows, int C, long long ldx, int ldy, void* stream) {
+    cast_f32_bf16_kernel<<<flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, static_cast<__nv_bfloat16*>(y), rows, C, ldx, ldy);
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int dmlb_cast_bf16_f32(const void* x, float* y, long long rows, int C, int ldx, long long ldy, void* stream) {
+    cast_bf16_f32_kernel<<<flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(x), y, rows, C, ldx, ldy);
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int dmlb_dropout_fwd_bf16(const void* x, void* y, void* mask, long long rows, int C, int ldx, int ldy, int rows_per_sample,
+                                     int channel_mode, float p, unsigned long long seed, const void* step, void* stream) {
+    DMLB_REQUIRE(p >= 0.f && p < 1.f, "dropout probability must be in [0, 1)");
+    dropout_fwd_kernel<<<flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), static_cast<uint8_t*>(mask), rows, C, ldx, ldy, rows_per_sample,
+        channel_mode, p, seed, static_cast<const unsigned long long*>(step));
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int dmlb_dropout_bwd_bf16(const void* dy, const void* mask, void* dx, long long rows, int C, int lddy, int lddx, float p, void* stream) {
+    dropout_bwd_kernel<<<flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(dy), static_cast<const uint8_t*>(mask), static_cast<__nv_bfloat16*>(dx), rows, C, lddy, lddx, p);
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int dmlb_counter_bump(void* counter, void* stream) {
+    counter_bump_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<unsigned long long*>(counter));
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}

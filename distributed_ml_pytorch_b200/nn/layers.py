@@ -1,0 +1,251 @@
+"""``torch.nn.Module`` layers backed by the sm_100a kernels.
+
+Parameters keep PyTorch's names, shapes and fp32 dtype (``weight [Cout, Cin, kh, kw]``, ``bias``), so
+``state_dict()`` checkpoints are interchangeable with the reference's ``nn.Conv2d`` / ``nn.Linear`` models
+(reference example/models.py:8-13,28-43).  For the tensor cores each layer additionally
+owns a bf16 *shadow* of its weight in GEMM layout ``[Cout, pad8(K)]`` with K ordered ``(kh, kw, cin)``;
+shadows are refreshed by one table-driven kernel for the whole model (:class:`ShadowSet`) whenever the
+fp32 masters change (optimizer step, parameter pull, ``load_state_dict``).
+"""
+from __future__ import annotations
+
+import math
+import struct
+from typing import List, Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from ..ops import functional as OF
+from ..ops import kernels as K
+
+
+def _pair(v) -> Tuple[int, int]:
+    return (v, v) if isinstance(v, int) else (int(v[0]), int(v[1]))
+
+
+class _ShadowedModule(nn.Module):
+    """Mixin for layers with a ``weight`` that is mirrored into a bf16 GEMM-layout shadow."""
+
+    def _init_shadow_state(self) -> None:
+        self._shadow: Optional[torch.Tensor] = None
+        self._shadow_key = None           # (data_ptr, _version) of the weight the shadow was built from
+        self._shadow_set: Optional["ShadowSet"] = None
+        self._wsink: Optional[torch.Tensor] = None
+        self._bsink: Optional[torch.Tensor] = None
+
+    # (rows, cin, khw) of the weight viewed as [rows, cin, khw]
+    def _shadow_dims(self) -> Tuple[int, int, int]:
+        raise NotImplementedError
+
+    def _shadow_entry(self) -> bytes:
+        rows, cin, khw = self._shadow_dims()
+        ld = K.pad8(cin * khw)
+        return struct.pack("<qqiiii", self.weight.data_ptr() // 4, self._shadow.data_ptr() // 2, rows, cin, khw, ld)
+
+    def _ensure_shadow_storage(self) -> None:
+        rows, cin, khw = self._shadow_dims()
+        ld = K.pad8(cin * khw)
+        w = self.weight
+        if self._shadow is None or self._shadow.device != w.device or tuple(self._shadow.shape) != (rows, ld):
+            self._shadow = torch.zeros((rows, ld), dtype=torch.bfloat16, device=w.device)
+            self._shadow_key = None
+            if self._shadow_set is not None:
+                self._shadow_set.invalidate_table()
+
+    def shadow(self) -> torch.Tensor:
+        """Up-to-date bf16 shadow of ``weight`` (refreshing it, or the whole model's set, when stale)."""
+        w = self.weight
+        key = (w.data_ptr(), w._version)
+        if self._shadow is None or self._shadow_key != key or self._shadow.device != w.device:
+            if self._shadow_set is not None:
+                self._shadow_set.refresh()
+            else:
+                self._ensure_shadow_storage()
+                table = torch.frombuffer(bytearray(self._shadow_entry()), dtype=torch.uint8).to(w.device)
+                K.refresh_shadows(table, 1)
+                self._shadow_key = key
+        return self._shadow
+
+    def _mark_shadow_fresh(self) -> None:
+        self._shadow_key = (self.weight.data_ptr(), self.weight._version)
+
+
+class ShadowSet:
+    """All shadowed layers of one model, refreshed with a single kernel launch.
+
+    ``refresh()`` is called by the framework's optimizers right after they update the fp32 masters (the
+    kernels write through raw pointers, so ``Tensor._version`` does not change) and lazily by
+    :meth:`_ShadowedModule.shadow` when a foreign optimizer or ``load_state_dict`` bumped ``_version``.
+    """
+
+    def __init__(self, model: nn.Module):
+        self.modules: List[_ShadowedModule] = [m for m in model.modules() if isinstance(m, _ShadowedModule)]
+        for m in self.modules:
+            m._shadow_set = self
+        self._table: Optional[torch.Tensor] = None
+        self._ptrs = None
+        model._dmlb_shadows = self
+
+    def invalidate_table(self) -> None:
+        self._table = None
+
+    def _build_table(self) -> None:
+        for m in self.modules:
+            m._ensure_shadow_storage()
+        raw = b"".join(m._shadow_entry() for m in self.modules)
+        dev = self.modules[0].weight.device
+        self._table = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(dev)
+        self._ptrs = [m.weight.data_ptr() for m in self.modules]
+
+    def refresh(self) -> None:
+        if not self.modules or not self.modules[0].weight.is_cuda:
+            return
+        if self._table is None or self._ptrs != [m.weight.data_ptr() for m in self.modules]:
+            self._build_table()
+        K.refresh_shadows(self._table, len(self.modules))
+        for m in self.modules:
+            m._mark_shadow_fresh()
+
+    def prepare(self) -> None:
+        """Allocate storage + table now (call before CUDA-graph capture so capture sees no allocation)."""
+        if self.modules and self.modules[0].weight.is_cuda:
+            self._build_table()
+            self.refresh()
+
+
+def attach_shadows(model: nn.Module) -> ShadowSet:
+    """Create (or return) the model-wide :class:`ShadowSet`."""
+    s = getattr(model, "_dmlb_shadows", None)
+    if s is None:
+        s = ShadowSet(model)
+    return s
+
+
+class Conv2d(_ShadowedModule):
+    """2-D convolution with optional fused ReLU and max-pool (``activation='relu'``, ``pool=(k, s, p)``).
+
+    Same parameters / initialisation as ``torch.nn.Conv2d`` (reference models.py:8-9,29-39).
+    """
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, bias=True, activation=None, pool=None):
+        super().__init__()
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.kernel_size, self.stride, self.padding = _pair(kernel_size), _pair(stride), _pair(padding)
+        self.activation = activation
+        self.pool = None if pool is None else (int(pool[0]), int(pool[1]), int(pool[2]) if len(pool) > 2 else 0)
+        self.weight = nn.Parameter(torch.empty(out_channels, in_channels, *self.kernel_size))
+        self.bias = nn.Parameter(torch.empty(out_channels)) if bias else None
+        self._init_shadow_state()
+        self.reset_parameters()
+
+    def reset_parameters(self) -> None:  # identical to torch.nn.Conv2d
+        nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
+        if self.bias is not None:
+            fan_in = self.in_channels * self.kernel_size[0] * self.kernel_size[1]
+            bound = 1 / math.sqrt(fan_in) if fan_in > 0 else 0
+            nn.init.uniform_(self.bias, -bound, bound)
+
+    def _shadow_dims(self):
+        return self.out_channels, self.in_channels, self.kernel_size[0] * self.kernel_size[1]
+
+    def forward(self, x):
+        relu = self.activation == "relu"
+        if not x.is_cuda:
+            return OF.conv_block(x, self.weight, self.bias, self.stride, self.padding, relu, self.pool)
+        return OF.conv_block(x, self.weight, self.bias, self.stride, self.padding, relu, self.pool, shadow=self.shadow(),
+                             wsink=self._wsink, bsink=self._bsink)
+
+    def extra_repr(self):
+        return (f"{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, stride={self.stride}, padding={self.padding}, "
+                f"activation={self.activation}, pool={self.pool}")
+
+
+class Linear(_ShadowedModule):
+    """Fully connected layer with optional fused ReLU.  ``in_map=(C, H, W)`` marks the input as a flattened
+    channels-last feature map (see :func:`ops.functional.flatten`); the weight keeps PyTorch's column order."""
+
+    def __init__(self, in_features, out_features, bias=True, activation=None, out_fp32=False, in_map=None):
+        super().__init__()
+        self.in_features, self.out_features = in_features, out_features
+        self.activation, self.out_fp32, self.in_map = activation, out_fp32, in_map
+        if in_map is not None and in_map[0] * in_map[1] * in_map[2] != in_features:
+            raise ValueError("in_map does not multiply to in_features")
+        self.weight = nn.Parameter(torch.empty(out_features, in_features))
+        self.bias = nn.Parameter(torch.empty(out_features)) if bias else None
+        self._init_shadow_state()
+        self.reset_parameters()
+
+    def reset_parameters(self) -> None:  # identical to torch.nn.Linear
+        nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
+        if self.bias is not None:
+            bound = 1 / math.sqrt(self.in_features) if self.in_features > 0 else 0
+            nn.init.uniform_(self.bias, -bound, bound)
+
+    def _shadow_dims(self):
+        if self.in_map is not None:
+            c, h, w = self.in_map
+            return self.out_features, c, h * w
+        return self.out_features, self.in_features, 1
+
+    def forward(self, x):
+        relu = self.activation == "relu"
+        if not x.is_cuda:
+            return OF.linear(x, self.weight, self.bias, relu)
+        return OF.linear(x, self.weight, self.bias, relu, self.out_fp32, self.in_map, shadow=self.shadow(), wsink=self._wsink,
+                         bsink=self._bsink)
+
+    def extra_repr(self):
+        return f"in_features={self.in_features}, out_features={self.out_features}, activation={self.activation}"
+
+
+class ReLU(nn.Module):
+    """ReLU.  ``fused=True`` makes it a placeholder (identity) because the preceding layer already applied
+    it in its GEMM epilogue — kept so ``nn.Sequential`` indices match the reference's ``state_dict`` keys."""
+
+    def __init__(self, inplace: bool = False, fused: bool = False):
+        super().__init__()
+        self.fused = fused
+
+    def forward(self, x):
+        return x if self.fused else OF.relu(x)
+
+    def extra_repr(self):
+        return "fused_into_previous" if self.fused else ""
+
+
+class MaxPool2d(nn.Module):
+    """Max pooling; ``fused=True`` = placeholder for a pool already done by the preceding :class:`Conv2d`."""
+
+    def __init__(self, kernel_size, stride=None, padding=0, fused: bool = False):
+        super().__init__()
+        self.kernel_size, self.stride, self.padding, self.fused = kernel_size, stride or kernel_size, padding, fused
+
+    def forward(self, x):
+        return x if self.fused else OF.max_pool2d(x, self.kernel_size, self.stride, self.padding)
+
+    def extra_repr(self):
+        return f"kernel_size={self.kernel_size}, stride={self.stride}, padding={self.padding}" + (", fused_into_previous" if self.fused else "")
+
+
+class Dropout(nn.Module):
+    def __init__(self, p: float = 0.5):
+        super().__init__()
+        self.p = p
+
+    def forward(self, x):
+        return OF.dropout(x, self.p, self.training, channel_mode=False)
+
+
+class Dropout2d(nn.Module):
+    def __init__(self, p: float = 0.5):
+        super().__init__()
+        self.p = p
+
+    def forward(self, x):
+        return OF.dropout(x, self.p, self.training, channel_mode=True)
+
+
+class Flatten(nn.Module):
+    def forward(self, x):
+        return OF.flatten(x)

@@ -1,0 +1,511 @@
+"""Autograd-aware functional ops backed by the sm_100a kernels (CUDA) with plain-PyTorch CPU paths.
+
+On CUDA tensors every op here launches kernels from ``libdmlb.so`` only — tcgen05 GEMMs for
+convolutions and linear layers, hand-written kernels for pooling / activation / loss / dropout —
+so a training step can be captured as one CUDA graph (:mod:`distributed_ml_pytorch_b200.engine`).
+On CPU tensors the same functions fall back to ``torch.nn.functional`` in the input dtype, which is what
+the CPU/gloo configuration (BASELINE.json config 1) and the non-GPU tests use.
+
+Reference call sites covered: ``nn.Conv2d`` / ``nn.Linear`` / ``F.max_pool2d`` / ``F.relu`` / ``Dropout2d`` /
+``F.dropout`` in example/models.py:8-22,28-48 and ``F.cross_entropy`` in example/main.py:71,125.
+
+Layout contract on CUDA (see ``ops/kernels.py``): activations are bf16 and channels-last with a channel
+pitch padded to a multiple of 8; they are ordinary ``torch.Tensor`` views of logical shape ``[B, C, H, W]``
+(or ``[B, F]``), so user code such as ``outputs.max(1)`` keeps working.
+"""
+from __future__ import annotations
+
+from types import SimpleNamespace
+from typing import Optional, Tuple
+
+import torch
+import torch.nn.functional as F
+
+from . import kernels as K
+
+pad8 = K.pad8
+_state = SimpleNamespace(unit_loss_grad=False)
+
+
+def set_unit_loss_grad(flag: bool) -> bool:
+    """Tell :func:`cross_entropy` that ``loss.backward()`` is always seeded with 1 (skips one scale kernel)."""
+    old = _state.unit_loss_grad
+    _state.unit_loss_grad = bool(flag)
+    return old
+
+
+# ------------------------------------------------------------------------------------------------
+# layout helpers
+# ------------------------------------------------------------------------------------------------
+def new_act4(B: int, C: int, H: int, W: int, device) -> torch.Tensor:
+    """Fresh bf16 channels-last activation, logical ``[B, C, H, W]``, channel pitch ``pad8(C)``."""
+    buf = torch.empty((B, H, W, pad8(C)), dtype=torch.bfloat16, device=device)
+    return buf[..., :C].permute(0, 3, 1, 2)
+
+
+def new_act2(B: int, Fdim: int, device, dtype=torch.bfloat16) -> torch.Tensor:
+    if dtype == torch.float32:
+        return torch.empty((B, Fdim), dtype=torch.float32, device=device)
+    buf = torch.empty((B, pad8(Fdim)), dtype=torch.bfloat16, device=device)
+    return buf[:, :Fdim]
+
+
+def act4_pitch(t: torch.Tensor) -> Optional[int]:
+    """Channel pitch of ``t`` if it is a bf16 channels-last activation in our layout, else ``None``."""
+    if t.dtype != torch.bfloat16 or t.dim() != 4:
+        return None
+    B, C, H, W = t.shape
+    s = t.stride()
+    if C > 1 and s[1] != 1:
+        return None
+    if W > 1:
+        ld = s[3]
+    elif H > 1:
+        ld = s[2]
+    elif B > 1:
+        ld = s[0]
+    else:
+        ld = pad8(C)
+    if ld < C or ld % 8 != 0:
+        return None
+    if (W > 1 and s[3] != ld) or (H > 1 and s[2] != W * ld) or (B > 1 and s[0] != H * W * ld):
+        return None
+    if (t.data_ptr() & 15) != 0:
+        return None
+    return ld
+
+
+def as_act4(t: torch.Tensor) -> Tuple[torch.Tensor, int]:
+    """Return ``(tensor, pitch)`` in the kernel layout, converting (one ATen copy) only when needed."""
+    ld = act4_pitch(t)
+    if ld is not None:
+        return t, ld
+    B, C, H, W = t.shape
+    out = new_act4(B, C, H, W, t.device)
+    out.copy_(t)
+    return out, pad8(C)
+
+
+def act2_pitch(t: torch.Tensor) -> Optional[int]:
+    if t.dtype != torch.bfloat16 or t.dim() != 2:
+        return None
+    B, Fd = t.shape
+    s = t.stride()
+    if Fd > 1 and s[1] != 1:
+        return None
+    ld = s[0] if B > 1 else pad8(Fd)
+    if ld < Fd or ld % 8 != 0 or (t.data_ptr() & 15) != 0:
+        return None
+    return ld
+
+
+def as_act2(t: torch.Tensor) -> Tuple[torch.Tensor, int]:
+    ld = act2_pitch(t)
+    if ld is not None:
+        return t, ld
+    B, Fd = t.shape
+    out = new_act2(B, Fd, t.device)
+    if t.dtype == torch.float32 and t.stride(1) == 1:
+        K.cast_f32_bf16(t, out.data_ptr(), B, Fd, t.stride(0), pad8(Fd))
+    else:
+        out.copy_(t)
+    return out, pad8(Fd)
+
+
+def _sink_ok(param: torch.Tensor, sink: Optional[torch.Tensor]) -> bool:
+    return sink is not None and param.grad is not None and param.grad.data_ptr() == sink.data_ptr()
+
+
+# ------------------------------------------------------------------------------------------------
+# conv (+bias +ReLU +max-pool) block
+# ------------------------------------------------------------------------------------------------
+class _ConvBlockFn(torch.autograd.Function):
+    """im2col -> tcgen05 GEMM (bias/ReLU epilogue) -> optional max-pool; backward = fused activation
+    backward + split-K wgrad GEMM (scattered straight into the fp32 gradient arena) + dgrad GEMM + col2im."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, cfg):
+        Cout, Cin, KH, KW = weight.shape
+        B, _, H, W = x.shape
+        SH, SW = cfg.stride
+        PH, PW = cfg.padding
+        Ho = (H + 2 * PH - KH) // SH + 1
+        Wo = (W + 2 * PW - KW) // SW + 1
+        M, Kd = B * Ho * Wo, Cin * KH * KW
+        Kpad = pad8(Kd)
+        dev = x.device
+        from_nchw_f32 = x.dtype == torch.float32 and x.is_contiguous()
+        direct = (not from_nchw_f32) and KH == 1 and KW == 1 and SH == 1 and SW == 1 and PH == 0 and PW == 0
+        ldx = 0
+        if from_nchw_f32:
+            col = torch.empty((M, Kpad), dtype=torch.bfloat16, device=dev)
+            K.im2col_nchw_f32(x, col, B, H, W, Cin, KH, KW, SH, SW, PH, PW, Kpad)
+            a_t, lda = col, Kpad
+        else:
+            x, ldx = as_act4(x)
+            if direct and Cin % 8 == 0:
+                a_t, lda = x, ldx
+            else:
+                direct = False
+                col = torch.empty((M, Kpad), dtype=torch.bfloat16, device=dev)
+                K.im2col_nhwc(x.data_ptr(), col, B, H, W, Cin, ldx, KH, KW, SH, SW, PH, PW, Kpad)
+                a_t, lda = col, Kpad
+        y = new_act4(B, Cout, Ho, Wo, dev)
+        ldy = pad8(Cout)
+        K.gemm(a_t, lda, False, cfg.shadow, Kpad, False, M, Cout, Kd, y, ldy, bias=bias, relu=cfg.relu)
+        out = y
+        if cfg.pool is not None:
+            k, s, p = cfg.pool
+            Hp, Wp = (Ho + 2 * p - k) // s + 1, (Wo + 2 * p - k) // s + 1
+            out = new_act4(B, Cout, Hp, Wp, dev)
+            K.maxpool_fwd(y.data_ptr(), out.data_ptr(), B, Ho, Wo, Cout, ldy, ldy, k, s, p)
+        ctx.cfg = cfg
+        ctx.geom = (B, H, W, Cin, Cout, KH, KW, SH, SW, PH, PW, Ho, Wo, Kd, Kpad, ldx, lda, direct, from_nchw_f32)
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(a_t, y if (cfg.relu or cfg.pool is not None) else None, weight, bias)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        cfg = ctx.cfg
+        a_t, y, weight, bias = ctx.saved_tensors
+        (B, H, W, Cin, Cout, KH, KW, SH, SW, PH, PW, Ho, Wo, Kd, Kpad, ldx, lda, direct, from_nchw_f32) = ctx.geom
+        dev = dout.device
+        M = B * Ho * Wo
+        ldy = pad8(Cout)
+        dout, ldd = as_act4(dout)
+        # ---- activation backward (+ pool backward, + bias gradient) ----
+        gb = None
+        bias_sink = cfg.bsink if (ctx.has_bias and _sink_ok(bias, cfg.bsink)) else None
+        if ctx.has_bias and bias_sink is None and ctx.needs_input_grad[2]:
+            gb = torch.zeros(Cout, dtype=torch.float32, device=dev)
+        db = bias_sink if bias_sink is not None else gb
+        if cfg.relu or cfg.pool is not None or db is not None:
+            dy = new_act4(B, Cout, Ho, Wo, dev)
+            K.act_bwd(y.data_ptr() if y is not None else dy.data_ptr(), dout.data_ptr(), dy.data_ptr(), db, B, Ho, Wo, Cout, ldy, ldd,
+                      cfg.pool, cfg.relu)
+            lddy = ldy
+        else:
+            dy, lddy = dout, ldd
+        # ---- weight gradient: dW[Cout, K] = dY^T[Cout, M] * Xcol[M, K]  (both operands MN-major) ----
+        gw = None
+        if ctx.needs_input_grad[1]:
+            wsink = cfg.wsink if _sink_ok(weight, cfg.wsink) else None
+            if wsink is None:
+                gw = torch.zeros_like(weight, dtype=torch.float32)
+            target = wsink if wsink is not None else gw
+            tiles = ((Cout + 127) // 128) * ((Kd + 127) // 128)
+            split = K.pick_split_k(tiles, M)
+            K.gemm(dy, lddy, True, a_t, lda, True, Cout, Kd, M, target, Kd, split_k=split, atomic=True,
+                   perm_cin=Cin if KH * KW > 1 else 0, perm_khw=KH * KW)
+        # ---- data gradient: dXcol[M, K] = dY[M, Cout] * W[Cout, K]  (B operand MN-major), then col2im ----
+        dx = None
+        if ctx.needs_input_grad[0]:
+            if from_nchw_f32:
+                raise RuntimeError("gradient w.r.t. an fp32 NCHW network input is not implemented on the CUDA path")
+            dx = new_act4(B, Cin, H, W, dev)
+            if direct:
+                K.gemm(dy, lddy, False, cfg.shadow, Kpad, True, M, Kd, Cout, dx, pad8(Cin))
+            else:
+                dcol = torch.empty((M, Kpad), dtype=torch.bfloat16, device=dev)
+                K.gemm(dy, lddy, False, cfg.shadow, Kpad, True, M, Kd, Cout, dcol, Kpad)
+                K.col2im_nhwc(dcol, dx.data_ptr(), B, H, W, Cin, pad8(Cin), KH, KW, SH, SW, PH, PW, Kpad)
+        return dx, gw, gb, None
+
+
+def conv_block(x, weight, bias=None, stride=(1, 1), padding=(0, 0), relu=False, pool=None, shadow=None, wsink=None, bsink=None):
+    """``max_pool(relu(conv2d(x, weight, bias)))`` with the optional parts fused (CUDA) or composed (CPU).
+
+    ``pool`` is ``None`` or ``(kernel, stride, padding)``; ``shadow`` is the bf16 GEMM-layout copy of
+    ``weight`` (see :class:`~distributed_ml_pytorch_b200.nn.layers.Conv2d`); ``wsink`` / ``bsink`` are views
+    of the flat fp32 gradient arena that receive the parameter gradients directly.
+    """
+    if not x.is_cuda:
+        y = F.conv2d(x, weight, bias, stride=stride, padding=padding)
+        if relu:
+            y = F.relu(y)
+        if pool is not None:
+            y = F.max_pool2d(y, pool[0], pool[1], pool[2])
+        return y
+    if shadow is None:
+        raise RuntimeError("conv_block on CUDA needs the bf16 weight shadow (use nn.Conv2d from this package)")
+    cfg = SimpleNamespace(stride=tuple(stride), padding=tuple(padding), relu=bool(relu), pool=pool, shadow=shadow, wsink=wsink, bsink=bsink)
+    return _ConvBlockFn.apply(x, weight, bias, cfg)
+
+
+# ------------------------------------------------------------------------------------------------
+# linear (+bias +ReLU)
+# ------------------------------------------------------------------------------------------------
+class _LinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, cfg):
+        O, I = weight.shape
+        x, ldx = as_act2(x)
+        B = x.shape[0]
+        Kpad = pad8(I)
+        y = new_act2(B, O, x.device, torch.float32 if cfg.out_fp32 else torch.bfloat16)
+        ldo = O if cfg.out_fp32 else pad8(O)
+        K.gemm(x, ldx, False, cfg.shadow, Kpad, False, B, O, I, y, ldo, bias=bias, relu=cfg.relu)
+        ctx.cfg = cfg
+        ctx.ldx = ldx
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(x, y if cfg.relu else None, weight, bias)
+        return y
+
+    @staticmethod
+    def backward(ctx, dout):
+        cfg = ctx.cfg
+        x, y, weight, bias = ctx.saved_tensors
+        O, I = weight.shape
+        B = x.shape[0]
+        dev = dout.device
+        Kpad = pad8(I)
+        dout, ldd = as_act2(dout)
+        gb = None
+        bias_sink = cfg.bsink if (ctx.has_bias and _sink_ok(bias, cfg.bsink)) else None
+        if ctx.has_bias and bias_sink is None and ctx.needs_input_grad[2]:
+            gb = torch.zeros(O, dtype=torch.float32, device=dev)
+        db = bias_sink if bias_sink is not None else gb
+        if cfg.relu or db is not None:
+            dy = new_act2(B, O, dev)
+            lddy = pad8(O)
+            K.act_bwd(y.data_ptr() if y is not None else dy.data_ptr(), dout.data_ptr(), dy.data_ptr(), db, B, 1, 1, O, lddy, ldd, None, cfg.relu)
+        else:
+            dy, lddy = dout, ldd
+        gw = None
+        if ctx.needs_input_grad[1]:
+            wsink = cfg.wsink if _sink_ok(weight, cfg.wsink) else None
+            if wsink is None:
+                gw = torch.zeros_like(weight, dtype=torch.float32)
+            target = wsink if wsink is not None else gw
+            tiles = ((O + 127) // 128) * ((I + 127) // 128)
+            split = K.pick_split_k(tiles, B)
+            pc, pk = (cfg.in_map[0], cfg.in_map[1] * cfg.in_map[2]) if cfg.in_map is not None else (0, 0)
+            K.gemm(dy, lddy, True, x, ctx.ldx, True, O, I, B, target, I, split_k=split, atomic=True, perm_cin=pc if pk > 1 else 0, perm_khw=pk)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = new_act2(B, I, dev)
+            K.gemm(dy, lddy, False, cfg.shadow, Kpad, True, B, I, O, dx, pad8(I))
+        return dx, gw, gb, None
+
+
+def linear(x, weight, bias=None, relu=False, out_fp32=False, in_map=None, shadow=None, wsink=None, bsink=None):
+    """``relu(x @ weight.T + bias)`` (ReLU optional).  ``in_map=(C, H, W)`` declares that ``x`` is a flattened
+    channels-last feature map while ``weight`` columns follow PyTorch's ``(c, h, w)`` order (LeNet's ``fc1``)."""
+    if not x.is_cuda:
+        y = F.linear(x, weight, bias)
+        return F.relu(y) if relu else y
+    if shadow is None:
+        raise RuntimeError("linear on CUDA needs the bf16 weight shadow (use nn.Linear from this package)")
+    cfg = SimpleNamespace(relu=bool(relu), out_fp32=bool(out_fp32), in_map=in_map, shadow=shadow, wsink=wsink, bsink=bsink)
+    return _LinearFn.apply(x, weight, bias, cfg)
+
+
+# ------------------------------------------------------------------------------------------------
+# standalone pool / relu / flatten / dropout
+# ------------------------------------------------------------------------------------------------
+class _MaxPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, k, s, p):
+        x, ldx = as_act4(x)
+        B, C, H, W = x.shape
+        Ho, Wo = (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
+        out = new_act4(B, C, Ho, Wo, x.device)
+        K.maxpool_fwd(x.data_ptr(), out.data_ptr(), B, H, W, C, ldx, pad8(C), k, s, p)
+        ctx.args = (k, s, p, ldx)
+        ctx.save_for_backward(x)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (x,) = ctx.saved_tensors
+        k, s, p, ldx = ctx.args
+        B, C, H, W = x.shape
+        dout, ldd = as_act4(dout)
+        dx = new_act4(B, C, H, W, x.device)
+        if pad8(C) != ldx:
+            x, ldx = as_act4(x.contiguous())
+        K.act_bwd(x.data_ptr(), dout.data_ptr(), dx.data_ptr(), None, B, H, W, C, ldx, ldd, (k, s, p), False)
+        return dx, None, None, None
+
+
+def max_pool2d(x, kernel_size, stride=None, padding=0):
+    stride = kernel_size if stride is None else stride
+    if not x.is_cuda:
+        return F.max_pool2d(x, kernel_size, stride, padding)
+    return _MaxPoolFn.apply(x, int(kernel_size), int(stride), int(padding))
+
+
+class _ReLUFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        if x.dim() == 4:
+            x, ld = as_act4(x)
+            B, C, H, W = x.shape
+            y = new_act4(B, C, H, W, x.device)
+            rows = B * H * W
+        else:
+            x, ld = as_act2(x)
+            rows, C = x.shape
+            y = new_act2(rows, C, x.device)
+        K.relu_fwd(x.data_ptr(), y.data_ptr(), rows, C, ld, pad8(C))
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        if y.dim() == 4:
+            dy, ldd = as_act4(dy)
+            B, C, H, W = y.shape
+            dx = new_act4(B, C, H, W, y.device)
+            rows = B * H * W
+        else:
+            dy, ldd = as_act2(dy)
+            rows, C = y.shape
+            dx = new_act2(rows, C, y.device)
+        K.relu_bwd(y.data_ptr(), dy.data_ptr(), dx.data_ptr(), rows, C, pad8(C), ldd, pad8(C))
+        return dx
+
+
+def relu(x):
+    if not x.is_cuda or x.dtype != torch.bfloat16:
+        return F.relu(x)
+    return _ReLUFn.apply(x)
+
+
+class _FlattenFn(torch.autograd.Function):
+    """[B, C, H, W] channels-last -> [B, H*W*C] (features ordered (h, w, c)); a pure re-view when C % 8 == 0."""
+
+    @staticmethod
+    def forward(ctx, x):
+        x, ld = as_act4(x)
+        B, C, H, W = x.shape
+        ctx.shape = (B, C, H, W)
+        if ld == C:
+            return torch.as_strided(x.detach(), (B, H * W * C), (H * W * C, 1), x.storage_offset())
+        return x.detach().permute(0, 2, 3, 1).reshape(B, H * W * C)
+
+    @staticmethod
+    def backward(ctx, g):
+        B, C, H, W = ctx.shape
+        g, ldg = as_act2(g)
+        if C % 8 == 0 and ldg == H * W * C:
+            return torch.as_strided(g, (B, C, H, W), (H * W * C, 1, W * C, C), g.storage_offset())
+        out = new_act4(B, C, H, W, g.device)
+        out.copy_(g[:, :H * W * C].reshape(B, H, W, C).permute(0, 3, 1, 2))
+        return out
+
+
+def flatten(x):
+    """Flatten a feature map for a following :func:`linear`.
+
+    CPU: PyTorch's ``x.view(B, -1)`` (``(c, h, w)`` order, reference models.py:18,47).  CUDA: channels-last
+    ``(h, w, c)`` order — pair it with ``linear(..., in_map=(C, H, W))`` so the weights keep the reference layout.
+    """
+    if not x.is_cuda:
+        return x.reshape(x.size(0), -1)
+    if x.dim() == 2:
+        return x
+    return _FlattenFn.apply(x)
+
+
+class _DropoutFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, p, channel_mode, seed, counter):
+        if x.dim() == 4:
+            x, ld = as_act4(x)
+            B, C, H, W = x.shape
+            rows, rps = B * H * W, H * W
+            y = new_act4(B, C, H, W, x.device)
+        else:
+            x, ld = as_act2(x)
+            rows, C = x.shape
+            rps = 1
+            y = new_act2(rows, C, x.device)
+        mask = torch.empty(rows * C, dtype=torch.uint8, device=x.device)
+        K.dropout_fwd(x.data_ptr(), y.data_ptr(), mask, rows, C, ld, pad8(C), rps, channel_mode, p, seed, counter)
+        K.counter_bump(counter)
+        ctx.args = (p, rows, C, x.dim() == 4, tuple(x.shape))
+        ctx.save_for_backward(mask)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (mask,) = ctx.saved_tensors
+        p, rows, C, is4, shape = ctx.args
+        if is4:
+            dy, ldd = as_act4(dy)
+            dx = new_act4(*shape, dy.device)
+        else:
+            dy, ldd = as_act2(dy)
+            dx = new_act2(rows, C, dy.device)
+        K.dropout_bwd(dy.data_ptr(), mask, dx.data_ptr(), rows, C, ldd, pad8(C), p)
+        return dx, None, None, None, None
+
+
+_dropout_counters = {}
+
+
+def _counter_for(device) -> torch.Tensor:
+    key = (device.type, device.index)
+    if key not in _dropout_counters:
+        _dropout_counters[key] = torch.zeros(1, dtype=torch.int64, device=device)
+    return _dropout_counters[key]
+
+
+def dropout(x, p=0.5, training=True, channel_mode=False, seed=0x5EED):
+    """Element dropout (``F.dropout``) or, with ``channel_mode``, ``Dropout2d`` (whole channels per sample)."""
+    if not training or p == 0.0:
+        return x
+    if not x.is_cuda or x.dtype != torch.bfloat16:
+        return F.dropout2d(x, p, True) if channel_mode else F.dropout(x, p, True)
+    return _DropoutFn.apply(x, float(p), bool(channel_mode), int(seed), _counter_for(x.device))
+
+
+# ------------------------------------------------------------------------------------------------
+# softmax cross-entropy (forward + backward in one kernel)
+# ------------------------------------------------------------------------------------------------
+class _XentFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, labels, metrics):
+        B, C = logits.shape
+        if logits.dtype == torch.bfloat16:
+            logits, ldl = as_act2(logits)
+            dlogits = new_act2(B, C, logits.device)
+            ldd = pad8(C)
+        else:
+            logits = logits.float().contiguous() if (logits.dtype != torch.float32 or logits.stride(1) != 1) else logits
+            ldl = logits.stride(0) if B > 1 else C
+            dlogits = torch.empty((B, C), dtype=torch.float32, device=logits.device)
+            ldd = C
+        need_grad = ctx.needs_input_grad[0]
+        K.softmax_xent(logits, labels, metrics, dlogits if need_grad else None, B, C, ldl, ldd)
+        ctx.save_for_backward(dlogits if need_grad else None)
+        ctx.dims = (B, C, ldd)
+        return metrics[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        (dlogits,) = ctx.saved_tensors
+        B, C, ldd = ctx.dims
+        if not _state.unit_loss_grad:
+            if dlogits.dtype == torch.bfloat16:
+                K.scale_rows(dlogits, g.reshape(1).float(), B, C, ldd)
+            else:
+                dlogits = dlogits * g
+        return dlogits, None, None
+
+
+def cross_entropy(logits, labels, metrics: Optional[torch.Tensor] = None):
+    """Mean softmax cross-entropy (reference main.py:71).  On CUDA the kernel also writes
+    ``metrics[1]`` = number of correct arg-max predictions (the reference recomputes it with
+    ``torch.max(outputs, 1)``, main.py:75) and the returned loss is a view of ``metrics[0]``."""
+    if not logits.is_cuda:
+        return F.cross_entropy(logits.float(), labels)
+    if metrics is None:
+        metrics = torch.empty(2, dtype=torch.float32, device=logits.device)
+    if labels.dtype != torch.int64:
+        labels = labels.long()
+    loss = _XentFn.apply(logits, labels, metrics)
+    return loss

@@ -1,0 +1,112 @@
+"""Thin, allocation-free Python wrappers over the libdmlb C ABI (``include/dmlb.h``).
+
+Each wrapper takes torch tensors that already have the right dtype/layout, extracts raw pointers and
+pitches and launches on the current CUDA stream.  Layout conventions (see ``csrc/conv_ops.cu``):
+
+* activations: bf16 channels-last, logical ``[B, C, H, W]`` stored ``[B, H, W, ld]`` (``ld >= C``, ``ld % 8 == 0``);
+* 2-D activations: bf16 ``[rows, C]`` with row pitch ``ld``;
+* GEMM weights ("shadows"): bf16 ``[Cout, Kpad]`` with K ordered ``(kh, kw, cin)``.
+"""
+from __future__ import annotations
+
+import torch
+
+from .. import _native
+
+_call = _native.call
+
+
+def stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def pad8(n: int) -> int:
+    return (n + 7) // 8 * 8
+
+
+def gemm(a: torch.Tensor, lda: int, a_mn: bool, b: torch.Tensor, ldb: int, b_mn: bool, M: int, N: int, K: int, out: torch.Tensor,
+         ldo: int, bias=None, relu: bool = False, split_k: int = 1, atomic: bool = False, perm_cin: int = 0, perm_khw: int = 0,
+         tile_n: int = 0) -> None:
+    """``out[M,N] (+)= A[M,K] @ B[N,K]^T`` on the tcgen05 path (see ``dmlb_gemm_bf16``)."""
+    _call("dmlb_gemm_bf16", a.data_ptr(), lda, int(a_mn), b.data_ptr(), ldb, int(b_mn), M, N, K, out.data_ptr(),
+          int(out.dtype == torch.float32), ldo, bias.data_ptr() if bias is not None else None, int(relu), split_k, int(atomic),
+          perm_cin, perm_khw, tile_n, stream_ptr())
+
+
+def pick_split_k(tiles: int, k_total: int, sms: int = 148, min_kblocks: int = 2) -> int:
+    """Split-K factor that fills the SMs when the output has few tiles (weight gradients, tiny-M fprop)."""
+    nkb = (k_total + 63) // 64
+    if tiles >= sms or nkb <= min_kblocks:
+        return 1
+    want = max(1, (sms + tiles - 1) // tiles)
+    return max(1, min(want, nkb // min_kblocks))
+
+
+def im2col_nhwc(x_ptr: int, col: torch.Tensor, B, H, W, C, ldx, KH, KW, SH, SW, PH, PW, Kpad) -> None:
+    _call("dmlb_im2col_nhwc_bf16", x_ptr, col.data_ptr(), B, H, W, C, ldx, KH, KW, SH, SW, PH, PW, Kpad, stream_ptr())
+
+
+def im2col_nchw_f32(x: torch.Tensor, col: torch.Tensor, B, H, W, C, KH, KW, SH, SW, PH, PW, Kpad) -> None:
+    _call("dmlb_im2col_nchw_f32", x.data_ptr(), col.data_ptr(), B, H, W, C, KH, KW, SH, SW, PH, PW, Kpad, stream_ptr())
+
+
+def col2im_nhwc(dcol: torch.Tensor, dx_ptr: int, B, H, W, C, ldx, KH, KW, SH, SW, PH, PW, Kpad) -> None:
+    _call("dmlb_col2im_nhwc_bf16", dcol.data_ptr(), dx_ptr, B, H, W, C, ldx, KH, KW, SH, SW, PH, PW, Kpad, stream_ptr())
+
+
+def maxpool_fwd(x_ptr: int, y_ptr: int, B, H, W, C, ldx, ldo, k, s, p) -> None:
+    _call("dmlb_maxpool_fwd_bf16", x_ptr, y_ptr, B, H, W, C, ldx, ldo, k, s, p, stream_ptr())
+
+
+def act_bwd(y_ptr: int, dout_ptr: int, dy_ptr: int, dbias, B, H, W, C, ldy, ldd, pool, relu: bool) -> None:
+    k, s, p = pool if pool is not None else (1, 1, 0)
+    _call("dmlb_act_bwd_bf16", y_ptr, dout_ptr, dy_ptr, dbias.data_ptr() if dbias is not None else None, B, H, W, C, ldy, ldd,
+          int(pool is not None), k, s, p, int(relu), stream_ptr())
+
+
+def relu_fwd(x_ptr, y_ptr, rows, C, ldx, ldy) -> None:
+    _call("dmlb_relu_fwd_bf16", x_ptr, y_ptr, rows, C, ldx, ldy, stream_ptr())
+
+
+def relu_bwd(y_ptr, dy_ptr, dx_ptr, rows, C, ldy, lddy, lddx) -> None:
+    _call("dmlb_relu_bwd_bf16", y_ptr, dy_ptr, dx_ptr, rows, C, ldy, lddy, lddx, stream_ptr())
+
+
+def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, metrics: torch.Tensor, dlogits, B, C, ldl, ldd) -> None:
+    _call("dmlb_softmax_xent", logits.data_ptr(), int(logits.dtype == torch.bfloat16), labels.data_ptr(), metrics.data_ptr(),
+          dlogits.data_ptr() if dlogits is not None else None, B, C, ldl, ldd, stream_ptr())
+
+
+def scale_rows(x: torch.Tensor, scale: torch.Tensor, rows, C, ld) -> None:
+    _call("dmlb_scale_rows_bf16", x.data_ptr(), scale.data_ptr(), rows, C, ld, stream_ptr())
+
+
+def sgd_flat(params: torch.Tensor, grads: torch.Tensor, acc, mom, n: int, lr_dev: torch.Tensor, mu: float = 0.0, wd: float = 0.0) -> None:
+    _call("dmlb_sgd_flat", params.data_ptr(), grads.data_ptr(), acc.data_ptr() if acc is not None else None,
+          mom.data_ptr() if mom is not None else None, n, lr_dev.data_ptr(), float(mu), float(wd), stream_ptr())
+
+
+def refresh_shadows(table: torch.Tensor, n_entries: int) -> None:
+    """Absolute-address table: base pointers are NULL, offsets are addresses / element size."""
+    _call("dmlb_refresh_shadows", None, None, table.data_ptr(), n_entries, stream_ptr())
+
+
+def cast_f32_bf16(x: torch.Tensor, y_ptr: int, rows, C, ldx, ldy) -> None:
+    _call("dmlb_cast_f32_bf16", x.data_ptr(), y_ptr, rows, C, ldx, ldy, stream_ptr())
+
+
+def cast_bf16_f32(x_ptr: int, y: torch.Tensor, rows, C, ldx, ldy) -> None:
+    _call("dmlb_cast_bf16_f32", x_ptr, y.data_ptr(), rows, C, ldx, ldy, stream_ptr())
+
+
+def dropout_fwd(x_ptr, y_ptr, mask: torch.Tensor, rows, C, ldx, ldy, rows_per_sample, channel_mode, p, seed, step: torch.Tensor) -> None:
+    _call("dmlb_dropout_fwd_bf16", x_ptr, y_ptr, mask.data_ptr(), rows, C, ldx, ldy, rows_per_sample, int(channel_mode), float(p),
+          int(seed) & 0xFFFFFFFFFFFFFFFF, step.data_ptr(), stream_ptr())
+
+
+def dropout_bwd(dy_ptr, mask: torch.Tensor, dx_ptr, rows, C, lddy, lddx, p) -> None:
+    _call("dmlb_dropout_bwd_bf16", dy_ptr, mask.data_ptr(), dx_ptr, rows, C, lddy, lddx, float(p), stream_ptr())
+
+
+def counter_bump(counter: torch.Tensor) -> None:
+    _call("dmlb_counter_bump", counter.data_ptr(), stream_ptr())

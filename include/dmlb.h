@@ -42,6 +42,40 @@ int dmlb_gemm_bf16(const void* A, int lda, int a_mn_major, const void* B, int ld
                    void* out, int out_is_f32, int ldo, const float* bias, int relu, int split_k, int atomic, int perm_cin,
                    int perm_khw, int tile_n, void* stream);
 
+/* ---- conv / pool / activation data movement (reference: example/models.py:16-17,28-41) ----------
+ * Activations are bf16 channels-last [B,H,W,ld] with ld >= C; column matrices are [B*Ho*Wo, Kpad] with K
+ * ordered (kh,kw,cin). */
+int dmlb_im2col_nhwc_bf16(const void* x, void* col, int B, int H, int W, int C, int ldx, int KH, int KW, int SH, int SW, int PH, int PW,
+                          int Kpad, void* stream);
+/* First layer: gathers straight from the user's fp32 NCHW batch (reference main.py:64-70), fusing cast + re-layout. */
+int dmlb_im2col_nchw_f32(const float* x, void* col, int B, int H, int W, int C, int KH, int KW, int SH, int SW, int PH, int PW, int Kpad,
+                         void* stream);
+int dmlb_col2im_nhwc_bf16(const void* dcol, void* dx, int B, int H, int W, int C, int ldx, int KH, int KW, int SH, int SW, int PH, int PW,
+                          int Kpad, void* stream);
+int dmlb_maxpool_fwd_bf16(const void* x, void* y, int B, int H, int W, int C, int ldx, int ldo, int k, int s, int p, void* stream);
+/* Fused (max-pool backward) o (ReLU mask) + bias gradient; see csrc/conv_ops.cu. dbias (fp32 [C], red.add) may be NULL. */
+int dmlb_act_bwd_bf16(const void* y, const void* dout, void* dy, float* dbias, int B, int H, int W, int C, int ldy, int ldd, int has_pool,
+                      int k, int s, int p, int relu, void* stream);
+int dmlb_relu_fwd_bf16(const void* x, void* y, long long rows, int C, int ldx, int ldy, void* stream);
+int dmlb_relu_bwd_bf16(const void* y, const void* dy, void* dx, long long rows, int C, int ldy, int lddy, int lddx, void* stream);
+
+/* ---- loss / optimizer / dropout (reference: example/main.py:71,75; asgd/optim/Asynchronous.py:55,63-68) ---- */
+/* metrics[0] = mean loss, metrics[1] = #rows with argmax == label; dlogits (dtype of logits, [B,ldd], may be NULL) = (softmax-onehot)/B. */
+int dmlb_softmax_xent(const void* logits, int logits_is_bf16, const long long* labels, float* metrics, void* dlogits, int B, int C,
+                      int ldl, int ldd, void* stream);
+int dmlb_scale_rows_bf16(void* x, const float* scale, long long rows, int C, int ld, void* stream);
+/* theta -= lr*g over the flat arena (n % 4 == 0); optional Downpour accumulator acc -= lr*g, momentum buffer, weight decay. */
+int dmlb_sgd_flat(float* params, const float* grads, float* acc, float* mom, long long n, const float* lr_ptr, float mu, float wd,
+                  void* stream);
+/* table: device array of { int64 src_off, int64 dst_off, int32 rows, cin, khw, ld } — see csrc/train_ops.cu. */
+int dmlb_refresh_shadows(const float* params, void* shadow, const void* table, int n_entries, void* stream);
+int dmlb_cast_f32_bf16(const float* x, void* y, long long rows, int C, long long ldx, int ldy, void* stream);
+int dmlb_cast_bf16_f32(const void* x, float* y, long long rows, int C, int ldx, long long ldy, void* stream);
+int dmlb_dropout_fwd_bf16(const void* x, void* y, void* mask, long long rows, int C, int ldx, int ldy, int rows_per_sample, int channel_mode,
+                          float p, unsigned long long seed, const void* step, void* stream);
+int dmlb_dropout_bwd_bf16(const void* dy, const void* mask, void* dx, long long rows, int C, int lddy, int lddx, float p, void* stream);
+int dmlb_counter_bump(void* counter, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
