@@ -1,0 +1,320 @@
+// Fused communication + update kernels over NVLink peer memory (one process per GPU, memory mapped with
+// CUDA IPC by peer.cu).  These replace the reference's message-based parameter-server traffic:
+//
+//   GradientUpdate  send of N floats + server `theta += payload`    asgd/optim/Asynchronous.py:55,58-60  -> push_add (K1)
+//   ParameterRequest (N dummy floats up) + ParameterUpdate reply    asgd/optim/Asynchronous.py:17-18,48-49 -> pull (K3)
+//   NORTH-STAR momentum / staleness-scaled server update                                               -> push_mailbox + owner_apply (K2)
+//   NORTH-STAR synchronous mode (all-reduce + SGD)                                                      -> sync_rs_update_ag (K4)
+//
+// The flat parameter vector [0, n) is cut into `world` contiguous shards of `shard_size` elements; GPU g owns
+// shard g (the "server" for that slice).  No kernel ever spins on, or reads flags from, remote memory in the
+// asynchronous paths: every cross-GPU flag is *written* remotely and *polled* locally.
+#include "common.cuh"
+
+namespace dmlb {
+
+constexpr int kMaxPeers = 16;
+constexpr int kChunk = 4096;  // elements per mailbox chunk (16 KiB)
+
+struct PeerTable {
+    void* ptr[kMaxPeers];
+};
+
+// ---------------------------------------------------------------------------------------------
+// K1  push_add: master[owner(i)][i] += acc[i];  acc[i] = 0          (exact reference semantics)
+// Vector fp32 reductions (red.global.add.v4.f32, .sys scope) travel over NVLink and are applied by the
+// owner's L2; the worker never waits for an acknowledgement.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) push_add_kernel(float* __restrict__ acc, PeerTable masters, long long shard_size, long long n4) {
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
+        const long long e = i * 4;
+        const int owner = static_cast<int>(e / shard_size);
+        float* dst = static_cast<float*>(masters.ptr[owner]) + (e - owner * shard_size);
+        const float4 a = reinterpret_cast<float4*>(acc)[i];
+        if (a.x != 0.f || a.y != 0.f || a.z != 0.f || a.w != 0.f) red_add_f32x4_sys(dst, a.x, a.y, a.z, a.w);
+        reinterpret_cast<float4*>(acc)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K3  pull: params[i] = master[owner(i)][i]  (+ optional version snapshot for staleness accounting)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) pull_kernel(float* __restrict__ params, PeerTable masters, PeerTable versions,
+                                                   uint32_t* __restrict__ pulled_ver, long long shard_size, long long n4, int chunks_per_shard) {
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
+        const long long e = i * 4;
+        const int owner = static_cast<int>(e / shard_size);
+        const long long off = e - owner * shard_size;
+        const float* src = static_cast<const float*>(masters.ptr[owner]) + off;
+        reinterpret_cast<float4*>(params)[i] = ld_volatile_f32x4(src);
+        if (pulled_ver != nullptr && (off % kChunk) == 0) {
+            const int lc = static_cast<int>(off / kChunk);
+            pulled_ver[owner * chunks_per_shard + lc] = ld_relaxed_sys_u32(static_cast<const uint32_t*>(versions.ptr[owner]) + lc);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2a push_mailbox: per 16 KiB chunk, if the worker's slot at the owner is free, store the accumulated
+// update into the owner's mailbox, zero the accumulator and raise the owner's `full` flag carrying
+// (version the worker last pulled + 1).  Busy chunks simply keep accumulating — nothing blocks.
+//   busy   : local  uint32 [world * cps]      (set here, cleared remotely by the owner)
+//   full   : owner's uint32 [world][cps]      (set remotely here, cleared by the owner)
+//   mailbox: owner's float  [world][shard_size]
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) push_mailbox_kernel(float* __restrict__ acc, uint32_t* __restrict__ busy,
+                                                           const uint32_t* __restrict__ pulled_ver, PeerTable mailboxes, PeerTable fulls,
+                                                           int rank, int world, long long shard_size, int cps) {
+    __shared__ uint32_t s_busy;
+    const int total_chunks = world * cps;
+    for (int c = blockIdx.x; c < total_chunks; c += gridDim.x) {
+        if (threadIdx.x == 0) s_busy = busy[c];
+        __syncthreads();
+        const bool is_busy = s_busy != 0;
+        __syncthreads();
+        if (is_busy) continue;
+        const int owner = c / cps, lc = c % cps;
+        float* src = acc + static_cast<long long>(owner) * shard_size + static_cast<long long>(lc) * kChunk;
+        float* dst = static_cast<float*>(mailboxes.ptr[owner]) + static_cast<long long>(rank) * shard_size + static_cast<long long>(lc) * kChunk;
+        for (int j = threadIdx.x; j < kChunk / 4; j += blockDim.x) {
+            reinterpret_cast<float4*>(dst)[j] = reinterpret_cast<float4*>(src)[j];
+            reinterpret_cast<float4*>(src)[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            busy[c] = 1;
+            __threadfence_system();
+            st_release_sys_u32(static_cast<uint32_t*>(fulls.ptr[owner]) + rank * cps + lc, pulled_ver[c] + 1u);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2b owner_apply: the shard owner folds every full mailbox chunk into its master shard:
+//   tau = version[chunk] - version_pulled;  s = staleness scale(tau)
+//   v = mu * v + s * delta;  theta += v;  version[chunk] += 1
+// then frees the slot (local `full` = 0, remote `busy` = 0 at the worker).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float staleness_scale(int mode, float param, uint32_t tau) {
+    if (mode == 1) return 1.f / (1.f + static_cast<float>(tau));           // inverse
+    if (mode == 2) return __powf(param, static_cast<float>(tau));          // exponential decay, param in (0,1]
+    return 1.f;
+}
+
+__global__ void __launch_bounds__(256) owner_apply_kernel(float* __restrict__ master, float* __restrict__ mom, uint32_t* __restrict__ version,
+                                                          uint32_t* __restrict__ full, const float* __restrict__ mailbox, PeerTable busys,
+                                                          uint32_t* __restrict__ stats, int rank, int world, long long shard_size, int cps,
+                                                          float mu, int stale_mode, float stale_param) {
+    __shared__ uint32_t s_flag;
+    for (int lc = blockIdx.x; lc < cps; lc += gridDim.x) {
+        for (int w = 0; w < world; ++w) {
+            if (threadIdx.x == 0) s_flag = ld_acquire_sys_u32(full + w * cps + lc);
+            __syncthreads();
+            const uint32_t flag = s_flag;
+            __syncthreads();
+            if (flag == 0) continue;
+            const uint32_t ver = version[lc];
+            const uint32_t tau = ver - (flag - 1u);
+            const float s = staleness_scale(stale_mode, stale_param, tau);
+            const float* src = mailbox + static_cast<long long>(w) * shard_size + static_cast<long long>(lc) * kChunk;
+            float* th = master + static_cast<long long>(lc) * kChunk;
+            for (int j = threadIdx.x; j < kChunk / 4; j += blockDim.x) {
+                const float4 d = ld_volatile_f32x4(src + 4 * j);
+                float4 t = reinterpret_cast<float4*>(th)[j];
+                if (mom != nullptr) {
+                    float4 v = reinterpret_cast<float4*>(mom + static_cast<long long>(lc) * kChunk)[j];
+                    v.x = mu * v.x + s * d.x; v.y = mu * v.y + s * d.y; v.z = mu * v.z + s * d.z; v.w = mu * v.w + s * d.w;
+                    reinterpret_cast<float4*>(mom + static_cast<long long>(lc) * kChunk)[j] = v;
+                    t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
+                } else {
+                    t.x += s * d.x; t.y += s * d.y; t.z += s * d.z; t.w += s * d.w;
+                }
+                reinterpret_cast<float4*>(th)[j] = t;
+            }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                version[lc] = ver + 1u;
+                full[w * cps + lc] = 0u;
+                if (stats != nullptr) {
+                    atomicAdd(&stats[0], 1u);                              // chunks applied
+                    atomicAdd(&stats[1], tau);                             // sum of staleness
+                    atomicMax(&stats[2], tau);                             // max staleness
+                }
+                __threadfence_system();
+                st_release_sys_u32(static_cast<uint32_t*>(busys.ptr[w]) + rank * cps + lc, 0u);
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K4  sync_rs_update_ag: one kernel per step and GPU does
+//   barrier(all grads ready) -> owner reduces its shard over every replica's gradient arena (peer loads)
+//   -> SGD / momentum on the fp32 shard -> stores the new weights into every replica's parameter arena
+//   (peer stores, the all-gather) -> barrier(all replicas written).
+// flags layout per GPU (uint32): [0, kMaxPeers) start flags, [kMaxPeers, 2*kMaxPeers) done flags,
+// [2*kMaxPeers] epoch, [2*kMaxPeers + 1] local block counter.   Every flag is written remotely and polled locally.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void spin_until_ge(const uint32_t* flag, uint32_t want) {
+    const long long t0 = clock64();
+    while (ld_acquire_sys_u32(flag) < want) {
+        if (clock64() - t0 > DMLB_SPIN_LIMIT_CYCLES) {
+            printf("dmlb: cross-GPU barrier timed out (block %d thread %d want %u have %u)\n", blockIdx.x, threadIdx.x, want, *flag);
+            __trap();
+        }
+    }
+}
+
+__global__ void __launch_bounds__(512) sync_rs_update_ag_kernel(PeerTable grads, PeerTable params, PeerTable flags, float* __restrict__ mom,
+                                                                int rank, int world, long long shard_size, const float* __restrict__ lr_ptr,
+                                                                float mu, float wd, float grad_scale) {
+    uint32_t* my_flags = static_cast<uint32_t*>(flags.ptr[rank]);
+    const uint32_t epoch = my_flags[2 * kMaxPeers] + 1u;   // bumped once per launch by the last block, below
+    // ---- start barrier: tell every peer that my gradients are final, wait for theirs ----
+    if (blockIdx.x == 0 && threadIdx.x < world) {
+        st_release_sys_u32(static_cast<uint32_t*>(flags.ptr[threadIdx.x]) + rank, epoch);
+    }
+    if (threadIdx.x < world) spin_until_ge(my_flags + threadIdx.x, epoch);
+    __syncthreads();
+
+    const float lr = *lr_ptr;
+    const long long base = static_cast<long long>(rank) * shard_size;
+    const long long n4 = shard_size / 4;
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
+        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+        for (int r = 0; r < world; ++r) {
+            const float4 v = ld_volatile_f32x4(static_cast<const float*>(grads.ptr[r]) + base + 4 * i);
+            g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+        }
+        g.x *= grad_scale; g.y *= grad_scale; g.z *= grad_scale; g.w *= grad_scale;
+        float4 p = reinterpret_cast<const float4*>(static_cast<const float*>(params.ptr[rank]) + base)[i];
+        if (wd != 0.f) { g.x += wd * p.x; g.y += wd * p.y; g.z += wd * p.z; g.w += wd * p.w; }
+        if (mom != nullptr) {
+            float4 v = reinterpret_cast<float4*>(mom)[i];
+            v.x = mu * v.x + g.x; v.y = mu * v.y + g.y; v.z = mu * v.z + g.z; v.w = mu * v.w + g.w;
+            reinterpret_cast<float4*>(mom)[i] = v;
+            g = v;
+        }
+        p.x -= lr * g.x; p.y -= lr * g.y; p.z -= lr * g.z; p.w -= lr * g.w;
+#pragma unroll 4
+        for (int r = 0; r < world; ++r) reinterpret_cast<float4*>(static_cast<float*>(params.ptr[r]) + base)[i] = p;
+    }
+
+    // ---- end barrier: my stores to every replica are done; wait until every owner has written into mine ----
+    __syncthreads();
+    __shared__ bool s_last;
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        const uint32_t done = atomicAdd(&my_flags[2 * kMaxPeers + 1], 1u);
+        s_last = (done == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (s_last) {
+        if (threadIdx.x < world) {
+            st_release_sys_u32(static_cast<uint32_t*>(flags.ptr[threadIdx.x]) + kMaxPeers + rank, epoch);
+            spin_until_ge(my_flags + kMaxPeers + threadIdx.x, epoch);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            my_flags[2 * kMaxPeers + 1] = 0u;
+            my_flags[2 * kMaxPeers] = epoch;
+            __threadfence();
+        }
+    }
+}
+
+static inline int comm_grid(long long work_items, int threads) {
+    long long blocks = (work_items + threads - 1) / threads;
+    const long long cap = dmlb_sm_count() * 2ll;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return static_cast<int>(blocks);
+}
+
+static int fill_table(PeerTable* t, void* const* ptrs, int world) {
+    DMLB_REQUIRE(world >= 1 && world <= kMaxPeers, "world size must be in [1, 16]");
+    for (int i = 0; i < kMaxPeers; ++i) t->ptr[i] = i < world ? ptrs[i] : nullptr;
+    return 0;
+}
+
+}  // namespace dmlb
+
+using namespace dmlb;
+
+extern "C" int dmlb_comm_chunk_elems() { return kChunk; }
+extern "C" int dmlb_comm_flag_words() { return 2 * kMaxPeers + 2; }
+
+extern "C" int dmlb_push_add(float* acc, void* const* master_ptrs, int world, long long shard_size, long long n, void* stream) {
+    DMLB_REQUIRE(n % 4 == 0 && shard_size % 4 == 0, "lengths must be multiples of 4");
+    PeerTable t;
+    if (fill_table(&t, master_ptrs, world)) return -2;
+    push_add_kernel<<<comm_grid(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(acc, t, shard_size, n / 4);
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int dmlb_pull(float* params, void* const* master_ptrs, void* const* version_ptrs, void* pulled_ver, int world,
+                         long long shard_size, long long n, void* stream) {
+    DMLB_REQUIRE(n % 4 == 0 && shard_size % kChunk == 0, "shard size must be a multiple of the chunk size");
+    PeerTable t, v;
+    if (fill_table(&t, master_ptrs, world)) return -2;
+    if (version_ptrs != nullptr) {
+        if (fill_table(&v, version_ptrs, world)) return -2;
+    } else {
+        for (int i = 0; i < kMaxPeers; ++i) v.ptr[i] = nullptr;
+        pulled_ver = nullptr;
+    }
+    pull_kernel<<<comm_grid(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(params, t, v, static_cast<uint32_t*>(pulled_ver), shard_size,
+                                                                                     n / 4, static_cast<int>(shard_size / kChunk));
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int dmlb_push_mailbox(float* acc, void* busy, const void* pulled_ver, void* const* mailbox_ptrs, void* const* full_ptrs, int rank,
+                                 int world, long long shard_size, void* stream) {
+    DMLB_REQUIRE(shard_size % kChunk == 0, "shard size must be a multiple of the chunk size");
+    PeerTable m, f;
+    if (fill_table(&m, mailbox_ptrs, world) || fill_table(&f, full_ptrs, world)) return -2;
+    const int cps = static_cast<int>(shard_size / kChunk);
+    int blocks = world * cps;
+    const int cap = dmlb_sm_count() * 4;
+    if (blocks > cap) blocks = cap;
+    push_mailbox_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(acc, static_cast<uint32_t*>(busy),
+                                                                              static_cast<const uint32_t*>(pulled_ver), m, f, rank, world,
+                                                                              shard_size, cps);
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int dmlb_owner_apply(float* master, float* mom, void* version, void* full, const float* mailbox, void* const* busy_ptrs, void* stats,
+                                int rank, int world, long long shard_size, float mu, int stale_mode, float stale_param, void* stream) {
+    DMLB_REQUIRE(shard_size % kChunk == 0, "shard size must be a multiple of the chunk size");
+    PeerTable b;
+    if (fill_table(&b, busy_ptrs, world)) return -2;
+    const int cps = static_cast<int>(shard_size / kChunk);
+    int blocks = cps;
+    const int cap = dmlb_sm_count() * 4;
+    if (blocks > cap) blocks = cap;
+    owner_apply_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(master, mom, static_cast<uint32_t*>(version),
+                                                                             static_cast<uint32_t*>(full), mailbox, b,
+                                                                             static_cast<uint32_t*>(stats), rank, world, shard_size, cps, mu,
+                                                                             stale_mode, stale_param);
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int dmlb_sync_rs_update_ag(void* const* grad_ptrs, void* const* param_ptrs, void* const* flag_ptrs, float* mom, int rank, int world,
+                                      long long shard_size, const float* lr_ptr, float mu, float wd, float grad_scale, void* stream) {
+    DMLB_REQUIRE(shard_size % 4 == 0, "shard size must be a multiple of 4");
+    PeerTable g, p, f;
+    if (fill_table(&g, grad_ptrs, world) || fill_table(&p, param_ptrs, world) || fill_table(&f, flag_ptrs, world)) return -2;
+    // One CTA per SM at most: every CTA polls the start flags, so all of them must be able to become resident.
+    int blocks = comm_grid(shard_size / 4, 512);
+    if (blocks > dmlb_sm_count()) blocks = dmlb_sm_count();
+    sync_rs_update_ag_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(g, p, f, mom, rank, world, shard_size, lr_ptr, mu, wd,
+                                                                                   grad_scale);
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}

@@ -218,6 +218,7 @@ __device__ __forceinline__ void st_f32x4(float* p, float4 v) { *reinterpret_cast
 // ----------------------------------------------------------------------------------------------
 extern "C" void dmlb_set_error(const char* msg);  // defined in runtime.cu
 extern "C" void dmlb_count_launch();              // defined in runtime.cu
+extern "C" int dmlb_sm_count();                   // defined in runtime.cu
 
 #define DMLB_CHECK_CUDA(expr)                                                                      \
     do {                                                                                           \

@@ -1,0 +1,302 @@
+"""Asynchronous (Downpour-style) SGD — the worker-side optimizer of the parameter-server scheme.
+
+API kept from the reference (asgd/optim/Asynchronous.py:20-71): ``Asynchronous(params, lr, n_push, n_pull, model)``
+is a ``torch.optim.Optimizer``; every ``step()`` applies plain SGD locally, accumulates ``-lr * grad`` and, every
+``n_push`` / ``n_pull`` steps, pushes the accumulated update to the server and pulls fresh parameters
+(protocol: SURVEY.md §3.7).  ``DownpourSGD`` is the same class (the name the reference's ``__init__`` exports).
+
+Three transports, chosen from where the model lives:
+
+``peer``  (CUDA model)  — every GPU is a worker *and* owns one shard of the parameter server.  Push =
+          ``red.global.add.v4.f32`` straight into the owners' master shards over NVLink (K1), pull = peer loads into the
+          local arena (K3); with ``momentum`` / ``staleness`` the push goes through per-worker mailboxes and the owner
+          applies ``v = mu v + s(tau) delta; theta += v`` (K2).  No server process, no request messages, no host copies.
+``gloo``  (CPU model, process group initialised) — the reference's topology: rank 0 runs
+          :class:`~distributed_ml_pytorch_b200.parallel.server.ParameterServer`, workers exchange messages
+          (``utils/messaging.py``).  This is BASELINE.json config 1 and the semantic oracle.
+``local`` (no process group) — a loop-back server inside the process; with one worker and ``n_push = n_pull = 1``
+          the trajectory equals plain SGD.
+
+Differences from the reference, all deliberate: ``Optimizer.__init__`` runs first; the push
+precedes the pull inside a step so pulled parameters already contain the worker's own update; pulled
+parameters are applied at a step boundary instead of racing with forward/backward (``torn_pulls=True`` restores
+the reference's behaviour on the gloo transport); a pull request carries no payload; only ``init_rank``
+uploads the initial parameters.
+"""
+from __future__ import annotations
+
+import logging
+import threading
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from ..utils import messaging as msg
+from ..utils.messaging import MessageCode, MessageListener, send_message
+from ..utils.serialization import ravel_model_params, unravel_model_params
+from .arena import FlatArena
+from .fused_sgd import ArenaOptimizer
+
+_LOGGER = logging.getLogger(__name__)
+_STALENESS = {None: 0, "none": 0, "inverse": 1, "exp": 2}
+
+
+class Listener(MessageListener):
+    """Receives ``ParameterUpdate`` replies from the server (reference Asynchronous.py:9-18)."""
+
+    def __init__(self, model, owner: "Asynchronous", src: int = msg.SERVER_RANK):
+        super().__init__(model, src=src)
+        self.owner = owner
+
+    def receive(self, sender, message_code, parameter):
+        _LOGGER.info("Processing message: %s", message_code.name)
+        if message_code == MessageCode.ParameterUpdate:
+            if self.owner.torn_pulls:
+                unravel_model_params(self.model, parameter)       # reference behaviour: overwrite immediately
+            else:
+                with self.owner._lock:
+                    self.owner._pending_params = parameter.clone()
+
+
+class Asynchronous(ArenaOptimizer):
+    def __init__(self, params, lr, n_push: int, n_pull: int, model: torch.nn.Module, momentum: float = 0.0,
+                 staleness: Optional[str] = None, staleness_param: float = 0.9, transport: str = "auto", group=None,
+                 init_rank: Optional[int] = None, torn_pulls: bool = False, server_rank: int = msg.SERVER_RANK):
+        if lr < 0.0:
+            raise ValueError("Invalid learning rate: {}".format(lr))
+        if n_push < 1 or n_pull < 1:
+            raise ValueError("n_push and n_pull must be >= 1")
+        if staleness not in _STALENESS:
+            raise ValueError(f"staleness must be one of {list(_STALENESS)}")
+        device = next(model.parameters()).device
+        if transport == "auto":
+            if device.type == "cuda":
+                transport = "peer"
+            elif dist.is_available() and dist.is_initialized():
+                transport = "gloo"
+            else:
+                transport = "local"
+        self.transport = transport
+        self.n_push, self.n_pull = int(n_push), int(n_pull)
+        self.server_momentum = float(momentum)
+        self.staleness, self.staleness_param = staleness, float(staleness_param)
+        self.torn_pulls = torn_pulls
+        self.server_rank = server_rank
+        self.group = group
+        self.idx = 0
+        self._lock = threading.Lock()
+        self._pending_params: Optional[torch.Tensor] = None
+        self._listener: Optional[Listener] = None
+        self.pushes = self.pulls = 0
+
+        arena = None
+        if transport == "peer":
+            from . import peer
+            self.peer = peer.PeerGroup(group=group, device=device)
+            self._chunk = peer.chunk_elems()
+            arena = FlatArena(model, n_shards=self.peer.world, align=self._chunk)   # shards are whole mailbox chunks
+        super().__init__(params, dict(lr=lr), model, arena=arena)
+        a = self.arena
+        self.accumulated_gradients = torch.zeros(a.padded, dtype=torch.float32, device=a.params.device)
+
+        if transport == "peer":
+            self._init_peer()
+        elif transport == "gloo":
+            self.rank = dist.get_rank()
+            if init_rank is None:
+                init_rank = 1 if self.server_rank == 0 else 0
+            if self.rank == init_rank:
+                # this sets the initial model parameters on the server (reference Asynchronous.py:33-34)
+                send_message(MessageCode.ParameterUpdate, ravel_model_params(model), dst=self.server_rank)
+            self._listener = Listener(model, self, src=self.server_rank)
+            self._listener.start()
+        else:
+            self._master = a.params.clone()
+            self._master_mom = torch.zeros_like(self._master) if self.server_momentum else None
+            self._master_version = 0
+            self._pulled_version = 0
+
+    # ------------------------------------------------------------------------------------------
+    # peer transport set-up
+    # ------------------------------------------------------------------------------------------
+    def _init_peer(self) -> None:
+        from . import peer
+        pg, a = self.peer, self.arena
+        S = a.shards.shard_size
+        cps = S // self._chunk
+        self._cps = cps
+        self._use_mailbox = bool(self.server_momentum) or _STALENESS[self.staleness] != 0
+        self.master_sym = pg.symmetric(S * 4)
+        self.version_sym = pg.symmetric(cps * 4)
+        self.master = self.master_sym.view(torch.float32, S)
+        self.version = self.version_sym.view(torch.int32, cps)
+        b, e = a.shards.bounds(pg.rank)
+        self.master.copy_(a.params[b:e])                       # owner's replica defines its shard
+        self.pulled_ver = torch.zeros(pg.world * cps, dtype=torch.int32, device=a.params.device)
+        self.stats = torch.zeros(4, dtype=torch.int32, device=a.params.device)
+        if self._use_mailbox:
+            self.mailbox_sym = pg.symmetric(pg.world * S * 4)
+            self.full_sym = pg.symmetric(pg.world * cps * 4)
+            self.busy_sym = pg.symmetric(pg.world * cps * 4)
+            self.mailbox = self.mailbox_sym.view(torch.float32, pg.world * S)
+            self.full = self.full_sym.view(torch.int32, pg.world * cps)
+            self.busy = self.busy_sym.view(torch.int32, pg.world * cps)
+            self.master_mom = torch.zeros(S, dtype=torch.float32, device=a.params.device) if self.server_momentum else None
+        pg.barrier()
+        self._pull()                                           # every replica starts from the server's parameters
+        torch.cuda.synchronize(a.params.device)
+        pg.barrier()
+
+    def _push(self) -> None:
+        from . import peer
+        pg, a = self.peer, self.arena
+        if self._use_mailbox:
+            peer.push_mailbox(self.accumulated_gradients, self.busy, self.pulled_ver, self.mailbox_sym.table, self.full_sym.table, pg.rank,
+                              pg.world, a.shards.shard_size)
+        else:
+            peer.push_add(self.accumulated_gradients, self.master_sym.table, pg.world, a.shards.shard_size, a.padded)
+        self.pushes += 1
+
+    def _owner_apply(self) -> None:
+        from . import peer
+        pg, a = self.peer, self.arena
+        peer.owner_apply(self.master, self.master_mom, self.version, self.full, self.mailbox, self.busy_sym.table, self.stats, pg.rank, pg.world,
+                         a.shards.shard_size, self.server_momentum, _STALENESS[self.staleness], self.staleness_param)
+
+    def _pull(self) -> None:
+        from . import peer
+        pg, a = self.peer, self.arena
+        peer.pull(a.params, self.master_sym.table, pg.world, a.shards.shard_size, a.padded, self.version_sym.table, self.pulled_ver)
+        a.mark_params_changed()
+        self.pulls += 1
+
+    # ------------------------------------------------------------------------------------------
+    # the optimizer step
+    # ------------------------------------------------------------------------------------------
+    def capture_state(self):
+        return (self.accumulated_gradients.clone(), self.idx)
+
+    def restore_state(self, st) -> None:
+        self.accumulated_gradients.copy_(st[0])
+        self.idx = st[1]
+
+    @torch.no_grad()
+    def step_local(self) -> None:
+        """Local SGD on the replica + accumulate ``-lr * grad`` (reference Asynchronous.py:52-55,63-68): one kernel."""
+        a = self.arena
+        self._sync_lr()
+        if a.params.is_cuda:
+            from ..ops import kernels as K
+            K.sgd_flat(a.params, a.grads, self.accumulated_gradients, None, a.padded, self.lr_dev, 0.0, 0.0)
+            a.mark_params_changed()
+        else:
+            lr = self.lr
+            self.accumulated_gradients.add_(a.grads, alpha=-lr)
+            a.params.add_(a.grads, alpha=-lr)
+
+    @torch.no_grad()
+    def communicate(self) -> None:
+        """Push every ``n_push`` steps, pull every ``n_pull`` steps (both fire at step 0, like the reference)."""
+        push_now = self.idx % self.n_push == 0
+        pull_now = self.idx % self.n_pull == 0
+        if self.transport == "peer":
+            if push_now:
+                self._push()
+            if self._use_mailbox:
+                self._owner_apply()
+            if pull_now:
+                self._pull()
+        elif self.transport == "gloo":
+            if push_now:
+                send_message(MessageCode.GradientUpdate, self.accumulated_gradients[: self.arena.numel], dst=self.server_rank)
+                self.accumulated_gradients.zero_()
+                self.pushes += 1
+            if pull_now:
+                send_message(MessageCode.ParameterRequest, None, dst=self.server_rank)
+                self.pulls += 1
+        else:
+            if push_now:
+                self._local_server_apply(self.accumulated_gradients)
+                self.accumulated_gradients.zero_()
+                self.pushes += 1
+            if pull_now:
+                self.arena.params.copy_(self._master)
+                self._pulled_version = self._master_version
+                self.arena.mark_params_changed()
+                self.pulls += 1
+        self.idx += 1
+
+    def _local_server_apply(self, delta: torch.Tensor) -> None:
+        tau = self._master_version - self._pulled_version
+        s = staleness_scale(self.staleness, self.staleness_param, tau)
+        if self._master_mom is not None:
+            self._master_mom.mul_(self.server_momentum).add_(delta, alpha=s)
+            self._master.add_(self._master_mom)
+        else:
+            self._master.add_(delta, alpha=s)
+        self._master_version += 1
+
+    def _apply_pending(self) -> None:
+        if self._pending_params is None:
+            return
+        with self._lock:
+            p, self._pending_params = self._pending_params, None
+        unravel_model_params(self.model, p)
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        self._apply_pending()
+        self.step_local()
+        self.communicate()
+        return loss
+
+    # ------------------------------------------------------------------------------------------
+    def finish(self) -> None:
+        """End of training: flush outstanding traffic, tell the server, release peer memory."""
+        if self.transport == "gloo":
+            send_message(MessageCode.WorkerDone, None, dst=self.server_rank)
+            msg.flush_sends()
+            if self._listener is not None:
+                self._listener.join(timeout=30)
+        elif self.transport == "peer":
+            torch.cuda.synchronize(self.arena.params.device)
+            self.peer.barrier()
+            if self._use_mailbox:
+                self._owner_apply()
+                torch.cuda.synchronize(self.arena.params.device)
+                self.peer.barrier()
+
+    def server_parameters(self) -> torch.Tensor:
+        """The server's current flat parameter vector (length N) as seen from this worker."""
+        a = self.arena
+        if self.transport == "peer":
+            out = torch.empty_like(a.params)
+            from . import peer
+            peer.pull(out, self.master_sym.table, self.peer.world, a.shards.shard_size, a.padded)
+            return out[: a.numel]
+        if self.transport == "local":
+            return self._master[: a.numel].clone()
+        raise RuntimeError("on the gloo transport the parameters live on the server rank")
+
+    def staleness_stats(self) -> dict:
+        if self.transport != "peer":
+            return {}
+        s = self.stats.tolist()
+        return {"chunks_applied": s[0], "mean_staleness": (s[1] / s[0] if s[0] else 0.0), "max_staleness": s[2]}
+
+
+def staleness_scale(mode: Optional[str], param: float, tau: int) -> float:
+    """s(tau): 'inverse' -> 1/(1+tau), 'exp' -> param**tau, None/'none' -> 1 (the reference: no scaling)."""
+    if mode == "inverse":
+        return 1.0 / (1.0 + tau)
+    if mode == "exp":
+        return float(param) ** tau
+    return 1.0
+
+
+DownpourSGD = Asynchronous

@@ -1,0 +1,122 @@
+"""Parameter server role.
+
+Re-specifies the reference's ABSENT ``asgd.server.ParameterServer`` from its call sites (example/main.py:21,135-138;
+contract in SURVEY.md §0.2 A3, §3.2): it holds the global flat parameter vector; ``ParameterUpdate`` sets it,
+``GradientUpdate`` adds the (already ``-lr``-scaled) payload, ``ParameterRequest`` is answered with a
+``ParameterUpdate`` to the sender.  ``run()`` is the blocking serve loop of the server rank.
+
+Additions over the reference: a termination path (``WorkerDone`` from every worker ends ``run()`` — the reference's
+server never exits), optional server-side momentum and staleness-scaled updates (NORTH-STAR), and
+``snapshot()`` / ``save()`` to checkpoint the server's parameters as a model ``state_dict``.
+
+On GPUs there is no server *process*: the server is memory — the flat vector is sharded over all GPUs of the box
+and updated in place by NVLink reductions (``parallel/async_optim.py``, transport ``peer``).  A rank started with
+``--server`` in that setting (:meth:`run_peer`) owns its shard and serves it without training.
+"""
+from __future__ import annotations
+
+import logging
+import time
+from typing import Dict, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..utils import messaging as msg
+from ..utils.messaging import MessageCode, recv_message, send_message
+from ..utils.serialization import ravel_model_params, unravel_model_params
+from .async_optim import staleness_scale
+
+_LOGGER = logging.getLogger(__name__)
+
+
+class ParameterServer:
+    def __init__(self, model: torch.nn.Module, n_workers: Optional[int] = None, momentum: float = 0.0, staleness: Optional[str] = None,
+                 staleness_param: float = 0.9, group=None):
+        self.model = model
+        self.parameter_shard = ravel_model_params(model).detach().clone().float().cpu()
+        self.momentum = float(momentum)
+        self.velocity = torch.zeros_like(self.parameter_shard) if self.momentum else None
+        self.staleness, self.staleness_param = staleness, staleness_param
+        self.version = 0
+        self.pulled_version: Dict[int, int] = {}
+        self.group = group
+        if n_workers is None and dist.is_available() and dist.is_initialized():
+            n_workers = dist.get_world_size(group) - 1
+        self.n_workers = n_workers
+        self.done_workers = set()
+        self.running = False
+        self.counters = {"ParameterUpdate": 0, "GradientUpdate": 0, "ParameterRequest": 0}
+        self.staleness_hist: Dict[int, int] = {}
+
+    # ------------------------------------------------------------------------------------------
+    def receive(self, sender: int, message_code: MessageCode, parameter: torch.Tensor) -> None:
+        _LOGGER.info("Processing message: %s from %d", message_code.name, sender)
+        if message_code == MessageCode.ParameterUpdate:
+            self.parameter_shard.copy_(parameter[: self.parameter_shard.numel()])
+            self.counters["ParameterUpdate"] += 1
+        elif message_code == MessageCode.GradientUpdate:
+            tau = self.version - self.pulled_version.get(sender, self.version)
+            self.staleness_hist[tau] = self.staleness_hist.get(tau, 0) + 1
+            s = staleness_scale(self.staleness, self.staleness_param, tau)
+            delta = parameter[: self.parameter_shard.numel()]
+            if self.velocity is not None:
+                self.velocity.mul_(self.momentum).add_(delta, alpha=s)
+                self.parameter_shard.add_(self.velocity)
+            else:
+                self.parameter_shard.add_(delta, alpha=s)
+            self.version += 1
+            self.counters["GradientUpdate"] += 1
+        elif message_code == MessageCode.ParameterRequest:
+            self.pulled_version[sender] = self.version
+            send_message(MessageCode.ParameterUpdate, self.parameter_shard, dst=sender, group=self.group)
+            self.counters["ParameterRequest"] += 1
+        elif message_code == MessageCode.WorkerDone:
+            self.done_workers.add(sender)
+            send_message(MessageCode.WorkerDone, None, dst=sender, group=self.group)   # lets the worker's listener exit
+
+    def run(self) -> None:
+        """Blocking serve loop (reference main.py:138); returns once every worker has sent ``WorkerDone``."""
+        self.running = True
+        while self.running:
+            sender, code, payload = recv_message(src=None, group=self.group)
+            self.receive(sender, code, payload)
+            if self.n_workers is not None and len(self.done_workers) >= self.n_workers:
+                self.running = False
+        msg.flush_sends()
+
+    def stop(self) -> None:
+        self.running = False
+
+    # ------------------------------------------------------------------------------------------
+    def snapshot(self) -> dict:
+        """The server's parameters as a ``state_dict`` of ``model`` (keys identical to the reference's models)."""
+        unravel_model_params(self.model, self.parameter_shard)
+        return {k: v.detach().cpu().clone() for k, v in self.model.state_dict().items()}
+
+    def save(self, path: str) -> None:
+        torch.save(self.snapshot(), path)
+
+    # ------------------------------------------------------------------------------------------
+    @staticmethod
+    def run_peer(model: torch.nn.Module, lr: float = 0.0, momentum: float = 0.0, staleness: Optional[str] = None, group=None,
+                 poll_s: float = 0.0005):
+        """``--server`` rank on the NVLink transport: join the peer group as a shard owner that does not train.
+
+        The rank allocates the same symmetric buffers as the workers (collective), then — for the mailbox protocol —
+        keeps applying incoming updates to its shard until every worker has reached ``finish()``.
+        """
+        from .async_optim import Asynchronous
+        opt = Asynchronous(model.parameters(), lr=lr, n_push=1, n_pull=1, model=model, momentum=momentum, staleness=staleness, group=group)
+        dev = opt.arena.params.device
+        work = dist.barrier(group=group, async_op=True) if opt.peer.world > 1 else None
+        while work is not None and not work.is_completed():
+            if opt._use_mailbox:
+                opt._owner_apply()
+                torch.cuda.synchronize(dev)
+            time.sleep(poll_s)
+        if opt._use_mailbox:
+            opt._owner_apply()
+            torch.cuda.synchronize(dev)
+            opt.peer.barrier()
+        return opt

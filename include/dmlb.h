@@ -10,6 +10,7 @@
 #ifndef DMLB_H_
 #define DMLB_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -75,6 +76,32 @@ int dmlb_dropout_fwd_bf16(const void* x, void* y, void* mask, long long rows, in
                           float p, unsigned long long seed, const void* step, void* stream);
 int dmlb_dropout_bwd_bf16(const void* dy, const void* mask, void* dx, long long rows, int C, int lddy, int lddx, float p, void* stream);
 int dmlb_counter_bump(void* counter, void* stream);
+
+/* ---- peer memory (reference transport: dist.init_process_group('gloo') + isend/recv, example/main.py:165) ---- */
+int dmlb_peer_alloc(size_t bytes, void** out);            /* zeroed cudaMalloc, shareable with CUDA IPC */
+int dmlb_peer_free(void* p);
+int dmlb_ipc_get_handle(void* p, void* handle_out64);     /* 64-byte cudaIpcMemHandle_t */
+int dmlb_ipc_open_handle(const void* handle64, void** out);
+int dmlb_ipc_close(void* p);
+int dmlb_enable_peer_access(int peer_dev);
+
+/* ---- fused communication + update kernels (csrc/comm.cu).  Pointer tables are HOST arrays of `world` device
+ * pointers, index = rank; the flat vector is cut into `world` shards of shard_size elements, GPU g owns shard g. ---- */
+int dmlb_comm_chunk_elems(void);                          /* mailbox chunk (shard sizes must be multiples of it) */
+int dmlb_comm_flag_words(void);                           /* uint32 words of the per-GPU flag block of the sync kernel */
+/* K1 (Asynchronous.py:55,58-60 + server add): master[owner][i] += acc[i]; acc[i] = 0 — vector red.add over NVLink. */
+int dmlb_push_add(float* acc, void* const* master_ptrs, int world, long long shard_size, long long n, void* stream);
+/* K3 (Asynchronous.py:17-18,48-49): params[i] = master[owner][i]; optional per-chunk version snapshot. */
+int dmlb_pull(float* params, void* const* master_ptrs, void* const* version_ptrs, void* pulled_ver, int world, long long shard_size,
+              long long n, void* stream);
+/* K2 (NORTH-STAR momentum / staleness): chunked mailbox push and owner-side apply. */
+int dmlb_push_mailbox(float* acc, void* busy, const void* pulled_ver, void* const* mailbox_ptrs, void* const* full_ptrs, int rank, int world,
+                      long long shard_size, void* stream);
+int dmlb_owner_apply(float* master, float* mom, void* version, void* full, const float* mailbox, void* const* busy_ptrs, void* stats, int rank,
+                     int world, long long shard_size, float mu, int stale_mode, float stale_param, void* stream);
+/* K4 (NORTH-STAR synchronous mode): barrier + reduce-scatter + SGD/momentum + all-gather + barrier in one kernel. */
+int dmlb_sync_rs_update_ag(void* const* grad_ptrs, void* const* param_ptrs, void* const* flag_ptrs, float* mom, int rank, int world,
+                           long long shard_size, const float* lr_ptr, float mu, float wd, float grad_scale, void* stream);
 
 #ifdef __cplusplus
 }
