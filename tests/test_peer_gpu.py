@@ -1,0 +1,203 @@
+"""NVLink peer-memory kernels and the GPU transports of the optimizers.
+
+World-size-1 cases run on a single GPU (the kernels treat the local GPU as its only peer); the multi-GPU cases spawn
+one process per GPU over NCCL + CUDA IPC and are skipped when fewer than two GPUs are visible.
+"""
+import copy
+import os
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300)]
+
+from distributed_ml_pytorch_b200.models import build_model
+from distributed_ml_pytorch_b200.ops import functional as OF
+from distributed_ml_pytorch_b200.parallel import Asynchronous, FusedSGD, Synchronous
+from distributed_ml_pytorch_b200.parallel.launcher import spawn
+from distributed_ml_pytorch_b200.utils.serialization import ravel_model_params
+
+
+def _batch(seed, n=16, dev="cuda"):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randn(n, 3, 32, 32, generator=g).to(dev), torch.randint(0, 10, (n,), generator=g).to(dev)
+
+
+def _steps(net, opt, n, seed0=0):
+    losses = []
+    for i in range(n):
+        x, y = _batch(seed0 + i)
+        opt.zero_grad()
+        loss = OF.cross_entropy(net(x), y)
+        loss.backward()
+        opt.step()
+        losses.append(loss.item())
+    return losses
+
+
+def test_async_peer_world1_equals_fused_sgd():
+    torch.manual_seed(0)
+    a = build_model("lenet").cuda().eval()
+    b = copy.deepcopy(a)
+    oa = Asynchronous(a.parameters(), lr=0.05, n_push=1, n_pull=1, model=a)
+    ob = FusedSGD(b.parameters(), lr=0.05, model=b)
+    la, lb = _steps(a, oa, 5), _steps(b, ob, 5)
+    assert la == pytest.approx(lb, rel=1e-3, abs=1e-3)
+    torch.testing.assert_close(ravel_model_params(a), ravel_model_params(b), rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(oa.server_parameters(), ravel_model_params(a), rtol=1e-5, atol=1e-6)
+    oa.finish()
+
+
+def test_async_peer_accumulates_between_pushes():
+    torch.manual_seed(0)
+    net = build_model("lenet").cuda().eval()
+    opt = Asynchronous(net.parameters(), lr=0.05, n_push=3, n_pull=1000, model=net)
+    theta0 = opt.server_parameters().clone()
+    _steps(net, opt, 4)   # pushes at idx 0 and 3
+    assert opt.pushes == 2
+    torch.testing.assert_close(opt.server_parameters(), ravel_model_params(net), rtol=1e-5, atol=1e-6)
+    assert not torch.equal(theta0, opt.server_parameters())
+    assert opt.accumulated_gradients.abs().sum().item() == 0.0
+
+
+def test_mailbox_momentum_and_staleness_world1():
+    """K2: with one worker pushing every step the owner applies v = mu v + delta; theta += v (tau = 0)."""
+    torch.manual_seed(0)
+    net = build_model("lenet").cuda().eval()
+    opt = Asynchronous(net.parameters(), lr=0.05, n_push=1, n_pull=1000, model=net, momentum=0.5, staleness="inverse")
+    theta = opt.server_parameters().clone()
+    v = torch.zeros_like(theta)
+    prev = ravel_model_params(net).clone()
+    for i in range(4):
+        _steps(net, opt, 1, seed0=i)
+        cur = ravel_model_params(net).clone()
+        delta = cur - prev                   # = -lr * g of this step (pull is far away, replica only does local SGD)
+        prev = cur
+        tau = max(0, i - 1)                  # step 0 pushes then pulls (version 1); afterwards the snapshot ages by one per push
+        v = 0.5 * v + delta / (1.0 + tau)
+        theta = theta + v
+        torch.testing.assert_close(opt.server_parameters(), theta, rtol=1e-4, atol=1e-6)
+    st = opt.staleness_stats()
+    assert st["chunks_applied"] > 0 and st["max_staleness"] == 2
+    opt.finish()
+
+
+def test_sync_peer_world1_equals_fused_sgd_with_momentum():
+    torch.manual_seed(0)
+    a = build_model("lenet").cuda().eval()
+    b = copy.deepcopy(a)
+    oa = Synchronous(a.parameters(), lr=0.05, model=a, momentum=0.9, weight_decay=1e-3)
+    ob = FusedSGD(b.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-3, model=b)
+    la, lb = _steps(a, oa, 5), _steps(b, ob, 5)
+    assert la == pytest.approx(lb, rel=1e-3, abs=1e-3)
+    torch.testing.assert_close(ravel_model_params(a), ravel_model_params(b), rtol=1e-4, atol=1e-5)
+
+
+def test_train_step_graph_matches_eager():
+    from distributed_ml_pytorch_b200.engine import TrainStep
+    torch.manual_seed(0)
+    a = build_model("alexnet").cuda().eval()
+    b = copy.deepcopy(a)
+    oa = Asynchronous(a.parameters(), lr=0.01, n_push=2, n_pull=2, model=a)
+    ob = Asynchronous(b.parameters(), lr=0.01, n_push=2, n_pull=2, model=b)
+    ts = TrainStep(a, oa, 16, (3, 32, 32), use_graph=True)
+    assert ts.graph is not None and ts.kernels_per_step > 10
+    graph_losses = []
+    for i in range(6):
+        x, y = _batch(i)
+        graph_losses.append(ts(x, y, sync=True).loss)
+    eager_losses = _steps(b, ob, 6)
+    assert graph_losses == pytest.approx(eager_losses, rel=2e-3, abs=2e-3)
+    torch.testing.assert_close(ravel_model_params(a), ravel_model_params(b), rtol=1e-3, atol=1e-4)
+    # pipelined (one-step-late) result delivery
+    r0 = ts(*_batch(10))
+    r1 = ts(*_batch(11))
+    assert r1 is not None and r1.step == ts.step_count - 2
+    assert ts.flush().step == ts.step_count - 1
+
+
+# ------------------------------------------------------------------------------------------------
+# multi-GPU
+# ------------------------------------------------------------------------------------------------
+def _need(n):
+    if torch.cuda.device_count() < n:
+        pytest.skip(f"needs {n} GPUs")
+
+
+def _mgpu_sync(rank, size, out_dir, steps):
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(0)
+    net = build_model("lenet").to(dev).eval()
+    opt = Synchronous(net.parameters(), lr=0.05, model=net, momentum=0.9)
+    for i in range(steps):
+        x, y = _batch(10 * i + rank, dev=dev)
+        opt.zero_grad()
+        OF.cross_entropy(net(x), y).backward()
+        opt.step()
+    opt.finish()
+    torch.save(ravel_model_params(net).cpu().clone(), os.path.join(out_dir, f"sync{rank}.pt"))
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_sync_multi_gpu_equals_large_batch_sgd(tmp_path, world):
+    _need(world)
+    steps = 4
+    spawn(_mgpu_sync, world, backend="nccl", args=(str(tmp_path), steps))
+    outs = [torch.load(tmp_path / f"sync{r}.pt") for r in range(world)]
+    for o in outs[1:]:
+        assert torch.equal(o, outs[0])           # every replica holds bit-identical weights
+    torch.manual_seed(0)
+    ref = build_model("lenet").eval()
+    sgd = torch.optim.SGD(ref.parameters(), lr=0.05, momentum=0.9)
+    for i in range(steps):
+        xs, ys = zip(*[_batch(10 * i + r, dev="cpu") for r in range(world)])
+        sgd.zero_grad()
+        F.cross_entropy(ref(torch.cat(xs)), torch.cat(ys)).backward()
+        sgd.step()
+    err = (outs[0] - ravel_model_params(ref)).norm() / ravel_model_params(ref).norm()
+    assert err < 2e-3, err     # bf16 tensor-core forward/backward vs fp32 CPU
+
+
+def _mgpu_async(rank, size, out_dir, steps, momentum):
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(0)
+    net = build_model("lenet").to(dev).eval()
+    opt = Asynchronous(net.parameters(), lr=0.02, n_push=1, n_pull=1, model=net, momentum=momentum,
+                       staleness="inverse" if momentum else None)
+    theta0 = opt.server_parameters().cpu().clone()
+    local_sum = torch.zeros_like(ravel_model_params(net))
+    for i in range(steps):
+        before = ravel_model_params(net).clone()
+        x, y = _batch(100 * rank + i, dev=dev)
+        opt.zero_grad()
+        OF.cross_entropy(net(x), y).backward()
+        opt._apply_pending()
+        opt.step_local()
+        local_sum += ravel_model_params(net) - before      # this worker's -lr*g contribution
+        opt.communicate()
+    opt.finish()
+    final = opt.server_parameters().cpu()
+    torch.save({"theta0": theta0, "sum": local_sum.cpu(), "final": final, "stats": opt.staleness_stats()}, os.path.join(out_dir, f"async{rank}.pt"))
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_async_multi_gpu_server_sums_all_pushes(tmp_path, world):
+    """Plain-add push (reference semantics): server == theta0 + sum over workers and steps of (-lr * g), whatever the interleaving."""
+    _need(world)
+    spawn(_mgpu_async, world, backend="nccl", args=(str(tmp_path), 5, 0.0))
+    outs = [torch.load(tmp_path / f"async{r}.pt", weights_only=False) for r in range(world)]
+    expect = outs[0]["theta0"] + sum(o["sum"] for o in outs)
+    for o in outs:
+        torch.testing.assert_close(o["final"], expect, rtol=1e-4, atol=1e-5)
+
+
+def test_async_multi_gpu_mailbox_runs_and_tracks_staleness(tmp_path):
+    _need(2)
+    spawn(_mgpu_async, 2, backend="nccl", args=(str(tmp_path), 6, 0.5))
+    outs = [torch.load(tmp_path / f"async{r}.pt", weights_only=False) for r in range(2)]
+    assert torch.equal(outs[0]["final"], outs[1]["final"])
+    assert not torch.equal(outs[0]["final"], outs[0]["theta0"])
+    assert torch.isfinite(outs[0]["final"]).all()
+    assert sum(o["stats"]["chunks_applied"] for o in outs) > 0
