@@ -1,0 +1,126 @@
+// Split-K forward GEMM with a fused finishing pass.
+//
+// The reference's conv / linear layers at its default batch of 64 (example/main.py:142) are tiny GEMMs with a
+// long reduction: AlexNet conv3-5 are 256 x {384,256} x {1728,3456,2304}.  A 128 x 128 tile
+// grid has 4-6 CTAs, each limited by what one SM can pull from L2, so the tensor cores idle.  Splitting K over
+// gridDim.z spreads the same work over ~100 SMs; partial tiles are summed with vector fp32 red.add into an fp32
+// workspace (the scratch memory of this path), and one finishing kernel applies bias + ReLU, rounds to bf16,
+// optionally performs the 2x2/2 max-pool that follows the conv in the model, and writes zeros back so the
+// workspace is clean for the next layer (no memset launches in the step).
+#include "common.cuh"
+
+extern "C" int dmlb_gemm_bf16(const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major, int M, int N, int K,
+                              void* out, int out_is_f32, int ldo, const float* bias, int relu, int split_k, int atomic, int perm_cin,
+                              int perm_khw, int tile_n, void* stream);
+
+namespace dmlb {
+
+// ws [M, ldw] fp32 -> y [M, ldy] bf16 = act(ws + bias); ws <- 0.   N % 4 == 0 fast path, scalar otherwise.
+__global__ void __launch_bounds__(256) splitk_finish_kernel(float* __restrict__ ws, int ldw, const float* __restrict__ bias, int relu,
+                                                            __nv_bfloat16* __restrict__ y, int ldy, long long M, int N) {
+    const int n4 = (N + 3) / 4;
+    const long long total = M * n4;
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
+        const long long m = i / n4;
+        const int c = static_cast<int>(i % n4) * 4;
+        float* w = ws + m * ldw + c;
+        float4 v = *reinterpret_cast<float4*>(w);            // ldw % 4 == 0: always in bounds of the padded row
+        *reinterpret_cast<float4*>(w) = make_float4(0.f, 0.f, 0.f, 0.f);
+        float f[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (c + j < N) {
+                float x = f[j] + (bias != nullptr ? __ldg(bias + c + j) : 0.f);
+                if (relu) x = fmaxf(x, 0.f);
+                y[m * ldy + c + j] = __float2bfloat16_rn(x);
+            }
+        }
+    }
+}
+
+// Same, plus the 2x2 stride-2 max-pool of the activation: one thread per pooled pixel and 4 channels.
+//   ws rows are NHWC pixels of a [B, H, W] map (H, W even); pooled is [B, H/2, W/2, ldp].
+__global__ void __launch_bounds__(256) splitk_finish_pool2_kernel(float* __restrict__ ws, int ldw, const float* __restrict__ bias, int relu,
+                                                                  __nv_bfloat16* __restrict__ y, int ldy, __nv_bfloat16* __restrict__ pooled,
+                                                                  int ldp, int B, int H, int W, int N) {
+    const int n4 = (N + 3) / 4;
+    const int Hp = H / 2, Wp = W / 2;
+    const long long total = 1ll * B * Hp * Wp * n4;
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
+        const int c = static_cast<int>(i % n4) * 4;
+        long long t = i / n4;
+        const int wp = static_cast<int>(t % Wp); t /= Wp;
+        const int hp = static_cast<int>(t % Hp);
+        const int b = static_cast<int>(t / Hp);
+        float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        float bb[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) bb[j] = (bias != nullptr && c + j < N) ? __ldg(bias + c + j) : 0.f;
+#pragma unroll
+        for (int dh = 0; dh < 2; ++dh)
+#pragma unroll
+            for (int dw = 0; dw < 2; ++dw) {
+                const long long m = (1ll * b * H + (2 * hp + dh)) * W + (2 * wp + dw);
+                float* w = ws + m * ldw + c;
+                const float4 v = *reinterpret_cast<float4*>(w);
+                *reinterpret_cast<float4*>(w) = make_float4(0.f, 0.f, 0.f, 0.f);
+                const float f[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (c + j < N) {
+                        float x = f[j] + bb[j];
+                        if (relu) x = fmaxf(x, 0.f);
+                        const __nv_bfloat16 h = __float2bfloat16_rn(x);
+                        y[m * ldy + c + j] = h;
+                        mx[j] = fmaxf(mx[j], __bfloat162float(h));
+                    }
+                }
+            }
+        const long long mp = (1ll * b * Hp + hp) * Wp + wp;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (c + j < N) pooled[mp * ldp + c + j] = __float2bfloat16_rn(mx[j]);
+    }
+}
+
+static inline int finish_grid(long long total) {
+    long long blocks = (total + 255) / 256;
+    const long long cap = 148ll * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return static_cast<int>(blocks);
+}
+
+}  // namespace dmlb
+
+using namespace dmlb;
+
+// ws: fp32 [M, ldw], all zeros on entry and again on exit.  pool2 = 1 additionally writes the 2x2/2 max-pool of y
+// (rows of y are the NHWC pixels of a [B, H, W] map with B*H*W == M) into pooled [B, H/2, W/2, ldp].
+extern "C" int dmlb_splitk_finish(float* ws, int ldw, const float* bias, int relu, void* y, int ldy, long long M, int N, int pool2, int B,
+                                  int H, int W, void* pooled, int ldp, void* stream) {
+    DMLB_REQUIRE(ldw % 4 == 0 && ldw >= N, "workspace pitch must be a multiple of 4 and cover N");
+    DMLB_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 15) == 0, "workspace must be 16-byte aligned");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (pool2) {
+        DMLB_REQUIRE(1ll * B * H * W == M && H % 2 == 0 && W % 2 == 0, "pooled finish needs an even [B,H,W] map with B*H*W == M");
+        const long long total = 1ll * B * (H / 2) * (W / 2) * ((N + 3) / 4);
+        splitk_finish_pool2_kernel<<<finish_grid(total), 256, 0, st>>>(ws, ldw, bias, relu, static_cast<__nv_bfloat16*>(y), ldy,
+                                                                       static_cast<__nv_bfloat16*>(pooled), ldp, B, H, W, N);
+    } else {
+        const long long total = M * ((N + 3) / 4);
+        splitk_finish_kernel<<<finish_grid(total), 256, 0, st>>>(ws, ldw, bias, relu, static_cast<__nv_bfloat16*>(y), ldy, M, N);
+    }
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+// y[M,N] (bf16, pitch ldy) = act(A[M,K] * W[N,K]^T + bias) with K split `split_k` ways.
+// Scratch: ws, fp32 [M, round_up(N,4)] — must be all zeros on entry; it is all zeros again when the call's work retires.
+extern "C" int dmlb_gemm_bias_act_splitk(const void* A, int lda, const void* Wt, int ldb, int M, int N, int K, float* ws, const float* bias,
+                                         int relu, void* y, int ldy, int split_k, void* stream) {
+    const int ldw = (N + 3) / 4 * 4;
+    int rc = dmlb_gemm_bf16(A, lda, 0, Wt, ldb, 0, M, N, K, ws, 1, ldw, nullptr, 0, split_k, 1, 0, 0, 0, stream);
+    if (rc) return rc;
+    return dmlb_splitk_finish(ws, ldw, bias, relu, y, ldy, M, N, 0, 0, 0, 0, nullptr, 0, stream);
+}

@@ -152,9 +152,23 @@ class _ConvBlockFn(torch.autograd.Function):
                 a_t, lda = col, Kpad
         y = new_act4(B, Cout, Ho, Wo, dev)
         ldy = pad8(Cout)
-        K.gemm(a_t, lda, False, cfg.shadow, Kpad, False, M, Cout, Kd, y, ldy, bias=bias, relu=cfg.relu)
+        split = K.fprop_split(M, Cout, Kd)
         out = y
-        if cfg.pool is not None:
+        fused_pool = False
+        if split > 1:
+            # tiny-M / long-K layer: spread K over the SMs, reduce in an fp32 workspace, finish (+pool) in one kernel
+            ldw = (Cout + 3) // 4 * 4
+            ws = K.splitk_workspace(dev, M * ldw)
+            K.gemm(a_t, lda, False, cfg.shadow, Kpad, False, M, Cout, Kd, ws, ldw, split_k=split, atomic=True)
+            if cfg.pool == (2, 2, 0) and Ho % 2 == 0 and Wo % 2 == 0:
+                out = new_act4(B, Cout, Ho // 2, Wo // 2, dev)
+                K.splitk_finish(ws, ldw, bias, cfg.relu, y.data_ptr(), ldy, M, Cout, pool2=(B, Ho, Wo), pooled_ptr=out.data_ptr(), ldp=ldy)
+                fused_pool = True
+            else:
+                K.splitk_finish(ws, ldw, bias, cfg.relu, y.data_ptr(), ldy, M, Cout)
+        else:
+            K.gemm(a_t, lda, False, cfg.shadow, Kpad, False, M, Cout, Kd, y, ldy, bias=bias, relu=cfg.relu)
+        if cfg.pool is not None and not fused_pool:
             k, s, p = cfg.pool
             Hp, Wp = (Ho + 2 * p - k) // s + 1, (Wo + 2 * p - k) // s + 1
             out = new_act4(B, Cout, Hp, Wp, dev)

@@ -42,6 +42,38 @@ def pick_split_k(tiles: int, k_total: int, sms: int = 148, min_kblocks: int = 2)
     return max(1, min(want, nkb // min_kblocks))
 
 
+_workspaces = {}
+
+
+def splitk_workspace(device, numel: int) -> torch.Tensor:
+    """Persistent all-zero fp32 scratch for split-K forward GEMMs (one per device; the finishing kernel re-zeroes
+    what the GEMM touched, so every layer can share it).  It only ever grows, and must first be sized outside CUDA
+    graph capture (TrainStep's warm-up iterations do that)."""
+    key = (device.type, device.index)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < numel:
+        ws = torch.zeros(max(numel, 1 << 20), dtype=torch.float32, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def splitk_finish(ws: torch.Tensor, ldw: int, bias, relu: bool, y_ptr: int, ldy: int, M: int, N: int, pool2=None, pooled_ptr: int = 0,
+                  ldp: int = 0) -> None:
+    B, H, W = pool2 if pool2 is not None else (0, 0, 0)
+    _call("dmlb_splitk_finish", ws.data_ptr(), ldw, bias.data_ptr() if bias is not None else None, int(relu), y_ptr, ldy, M, N,
+          int(pool2 is not None), B, H, W, pooled_ptr or None, ldp, stream_ptr())
+
+
+def fprop_split(M: int, N: int, K: int, sms: int = 148) -> int:
+    """Split-K factor for a forward GEMM, 1 when the plain fused-epilogue kernel is the better choice."""
+    bn = 128 if N > 64 else (64 if N > 32 else 32)
+    tiles = ((M + 127) // 128) * ((N + bn - 1) // bn)
+    nkb = (K + 63) // 64
+    if tiles * 3 > sms or nkb < 8:
+        return 1
+    return max(1, min(sms // tiles, nkb // 2))
+
+
 def im2col_nhwc(x_ptr: int, col: torch.Tensor, B, H, W, C, ldx, KH, KW, SH, SW, PH, PW, Kpad) -> None:
     _call("dmlb_im2col_nhwc_bf16", x_ptr, col.data_ptr(), B, H, W, C, ldx, KH, KW, SH, SW, PH, PW, Kpad, stream_ptr())
 

@@ -43,6 +43,13 @@ int dmlb_gemm_bf16(const void* A, int lda, int a_mn_major, const void* B, int ld
                    void* out, int out_is_f32, int ldo, const float* bias, int relu, int split_k, int atomic, int perm_cin,
                    int perm_khw, int tile_n, void* stream);
 
+/* Split-K forward (csrc/splitk.cu): for tiny-M, long-K layers (AlexNet conv3-5 at the reference's batch 64,
+ * example/main.py:142).  ws is fp32 scratch [M, round_up(N,4)], all zeros on entry and zeroed again by the finish. */
+int dmlb_splitk_finish(float* ws, int ldw, const float* bias, int relu, void* y, int ldy, long long M, int N, int pool2, int B, int H, int W,
+                       void* pooled, int ldp, void* stream);
+int dmlb_gemm_bias_act_splitk(const void* A, int lda, const void* Wt, int ldb, int M, int N, int K, float* ws, const float* bias, int relu,
+                              void* y, int ldy, int split_k, void* stream);
+
 /* ---- conv / pool / activation data movement (reference: example/models.py:16-17,28-41) ----------
  * Activations are bf16 channels-last [B,H,W,ld] with ld >= C; column matrices are [B*Ho*Wo, Kpad] with K
  * ordered (kh,kw,cin). */

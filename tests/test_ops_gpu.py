@@ -255,3 +255,25 @@ def test_model_grads_match_fp32_reference(name):
         cos = F.cosine_similarity(p1.grad.cpu().flatten(), g.flatten(), dim=0).item()
         assert cos > 0.97, (n1, cos)
         assert ours < max(2.5 * autocast, 3e-2), (n1, ours, autocast)
+
+
+@pytest.mark.parametrize("M,N,Kd,split", [(256, 384, 1728, 13), (64, 10, 4096, 8), (100, 72, 1000, 4)])
+def test_gemm_bias_act_splitk_c_abi(M, N, Kd, split):
+    """Split-K forward entry point (fp32 workspace scratch + fused finish) against fp32 matmul."""
+    from distributed_ml_pytorch_b200 import _native
+    torch.manual_seed(8)
+    dev = "cuda"
+    A = bf(torch.randn(M, Kd, device=dev))
+    Wt = bf(torch.randn(N, Kd, device=dev) * 0.05)
+    bias = torch.randn(N, device=dev)
+    ref = F.relu(A @ Wt.t() + bias)
+    a, w = A.to(torch.bfloat16).contiguous(), Wt.to(torch.bfloat16).contiguous()
+    ldy = K.pad8(N)
+    y = torch.zeros(M, ldy, device=dev, dtype=torch.bfloat16)
+    ws = torch.zeros(M * ((N + 3) // 4 * 4), device=dev, dtype=torch.float32)
+    for _ in range(2):   # the second call proves the workspace was left clean
+        _native.call("dmlb_gemm_bias_act_splitk", a.data_ptr(), Kd, w.data_ptr(), Kd, M, N, Kd, ws.data_ptr(), bias.data_ptr(), 1,
+                     y.data_ptr(), ldy, split, K.stream_ptr())
+        torch.cuda.synchronize()
+        assert rel_err(y[:, :N], ref) < 1e-2
+        assert ws.abs().max().item() == 0.0
