@@ -50,6 +50,19 @@ int dmlb_splitk_finish(float* ws, int ldw, const float* bias, int relu, void* y,
 int dmlb_gemm_bias_act_splitk(const void* A, int lda, const void* Wt, int ldb, int M, int N, int K, float* ws, const float* bias, int relu,
                               void* y, int ldy, int split_k, void* stream);
 
+/* Same computation as dmlb_gemm_bias_act_splitk, for callers that cannot allocate device memory (a host that links
+ * this library without torch and owns no allocator, a service whose own pool already holds the whole GPU, a loop
+ * that cannot take the device-wide synchronisation of cudaMalloc/cudaFree).  No counterpart in the reference.
+ * The fp32 workspace is a fixed array inside the library: M * round_up(N,4) must not exceed
+ * dmlb_noalloc_scratch_capacity() floats (1 Mi floats = 4 MiB per GPU, held until process exit); larger problems are
+ * rejected with an error.  Calls no cudaMalloc/cudaFree or other allocating routine.  The first call on a device
+ * resolves the array's address — issue it before any stream capture on that device.  All calls on a device share
+ * the array (each call clears the region it uses first), so calls whose GPU work overlaps race: keep them on one
+ * stream or order them yourself.  See csrc/splitk_static.cu. */
+long long dmlb_noalloc_scratch_capacity(void);
+int dmlb_gemm_bias_act_splitk_noalloc(const void* A, int lda, const void* Wt, int ldb, int M, int N, int K, const float* bias, int relu,
+                                      void* y, int ldy, int split_k, void* stream);
+
 /* ---- conv / pool / activation data movement (reference: example/models.py:16-17,28-41) ----------
  * Activations are bf16 channels-last [B,H,W,ld] with ld >= C; column matrices are [B*Ho*Wo, Kpad] with K
  * ordered (kh,kw,cin). */
