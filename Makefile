@@ -1,0 +1,60 @@
+# Same targets as the reference Makefile (run / packaging), plus build / test / bench for the native library.
+PY ?= python
+
+setup:
+	$(PY) -m pip install --no-index --find-links /opt/wheelhouse -r requirements.txt || true
+	$(PY) build_native.py
+
+install:
+	$(PY) -m pip install --no-build-isolation --no-deps .
+
+build:
+	$(PY) build_native.py --harness
+
+graph:
+	$(PY) example/graph.py
+	mkdir -p docs && mv train_time.png test_time.png docs
+
+first:
+	$(PY) example/main.py --rank 1 --world-size 3
+
+second:
+	$(PY) example/main.py --rank 2 --world-size 3
+
+server:
+	$(PY) example/main.py --rank 0 --world-size 3 --server
+
+single:
+	$(PY) example/main.py --no-distributed
+
+gpu:
+	$(PY) example/main.py --no-distributed --cuda
+
+gpu8:
+	$(PY) -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29500 example/main.py --cuda
+
+p2p:
+	$(PY) pytorch_p2p_ex.py
+
+test:
+	$(PY) -m pytest tests -x -q -m "not gpu"
+
+test-gpu:
+	$(PY) -m pytest tests -x -q -m gpu
+
+bench:
+	$(PY) bench.py
+
+dist:
+	$(PY) setup.py sdist bdist_wheel
+
+upload: dist
+	twine upload dist/*
+
+upload-test: dist
+	twine upload --repository-url https://test.pypi.org/legacy/ dist/*
+
+install-test:
+	$(PY) -m pip install --index-url https://test.pypi.org/simple/ pytorch-distbelief
+
+.PHONY: setup install build graph first second server single gpu gpu8 p2p test test-gpu bench dist upload upload-test install-test

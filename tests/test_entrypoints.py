@@ -1,0 +1,66 @@
+"""The reference's entry points keep their names, flags and roles (SURVEY.md §2.1 C4-C12, §5 flag table)."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pytestmark = pytest.mark.timeout(300)
+
+
+def _run(cmd, cwd, timeout=240):
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    return subprocess.run(cmd, cwd=cwd, env=env, capture_output=True, text=True, timeout=timeout)
+
+
+def test_reference_flags_and_defaults_are_kept():
+    sys.path.insert(0, os.path.join(ROOT, "example"))
+    import importlib
+    main = importlib.import_module("main")
+    a = main.build_parser().parse_args([])
+    assert (a.batch_size, a.test_batch_size, a.epochs, a.lr, a.num_pull, a.num_push) == (64, 10000, 20, 0.008, 10, 10)
+    assert (a.cuda, a.log_interval, a.no_distributed, a.rank, a.world_size, a.server, a.master, a.port) == \
+        (False, 100, False, None, 3, False, "localhost", "29500")
+    assert a.model == "alexnet"       # the reference hard-codes AlexNet (main.py:41)
+
+
+def test_single_process_run_writes_reference_csv(tmp_path):
+    r = _run([sys.executable, os.path.join(ROOT, "example", "main.py"), "--no-distributed", "--model", "lenet", "--epochs", "1",
+              "--steps-per-epoch", "12", "--log-interval", "5", "--test-batch-size", "50", "--synthetic"], cwd=tmp_path)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "Finished Training" in r.stdout
+    from distributed_ml_pytorch_b200.utils.csvlog import read_csv
+    rows = read_csv(os.path.join(tmp_path, "log", "single.csv"))
+    assert len(rows) == 12
+    assert set(["index", "timestamp", "iteration", "training_loss", "test_loss", "test_accuracy"]).issubset(rows[0].keys())
+    assert rows[5]["test_loss"] != "" and rows[4]["test_loss"] == ""
+    g = _run([sys.executable, os.path.join(ROOT, "example", "graph.py")], cwd=tmp_path)
+    assert g.returncode == 0, g.stderr
+    assert os.path.getsize(os.path.join(tmp_path, "train_time.png")) > 100
+
+
+def test_server_and_two_workers_via_launcher(tmp_path):
+    """`make server` + `make first` + `make second` (reference Makefile:13-20), started by run-pytorch.py --local."""
+    from distributed_ml_pytorch_b200.parallel.launcher import free_port
+    r = _run([sys.executable, os.path.join(ROOT, "run-pytorch.py"), "--local", "3", "--cpu", "--port", str(free_port()), "--", "--model", "lenet",
+              "--epochs", "1", "--steps-per-epoch", "12", "--log-interval", "1000", "--test-batch-size", "50", "--synthetic", "--num-push", "3",
+              "--num-pull", "3", "--ckpt", str(tmp_path / "ck.pt")], cwd=tmp_path)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    assert os.path.exists(tmp_path / "log" / "node1.csv") and os.path.exists(tmp_path / "log" / "node2.csv")
+    assert "server done" in r.stdout
+    import torch
+    sd = torch.load(tmp_path / "ck.pt", weights_only=False)
+    keys = sd["model"].keys() if "model" in sd else sd.keys()
+    assert "conv1.weight" in keys
+
+
+def test_p2p_example_runs():
+    r = _run([sys.executable, os.path.join(ROOT, "pytorch_p2p_ex.py")], cwd=ROOT, timeout=120)
+    assert r.returncode == 0, r.stderr[-1500:]
+    assert r.stdout.count("tensor(1.)") == 2
+
+
+def test_azure_submit_is_guarded():
+    r = _run([sys.executable, os.path.join(ROOT, "run-pytorch.py")], cwd=ROOT, timeout=60)
+    assert r.returncode != 0 and "azureml-core is not installed" in (r.stderr + r.stdout)
