@@ -94,13 +94,14 @@ __global__ void __launch_bounds__(256) scale_rows_kernel(__nv_bfloat16* __restri
 
 // ---------------------------------------------------------------------------------------------
 // Flat SGD over the parameter arena, one launch for the whole model:
-//   g  = grad + wd * theta;   v = mu * v + g (if momentum);   theta -= lr * g;   acc -= lr * g (if acc)
+//   g  = grad + wd * theta;   v = mu * v + g (if momentum);   theta -= lr * g;   acc -= lr * g (if acc);
+//   shadow = bf16(theta) (if shadow: the flat bf16 mirror the tensor-core GEMMs read)
 // lr is read from device memory so a captured CUDA graph follows LR-scheduler changes.
 // n must be a multiple of 4 (the arena pads to that).
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ params, const float* __restrict__ grads, float* __restrict__ acc,
-                                                       float* __restrict__ mom, long long n4, const float* __restrict__ lr_ptr, float mu,
-                                                       float wd) {
+                                                       float* __restrict__ mom, __nv_bfloat16* __restrict__ shadow, long long n4,
+                                                       const float* __restrict__ lr_ptr, float mu, float wd) {
     const float lr = *lr_ptr;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
         float4 p = reinterpret_cast<float4*>(params)[i];
@@ -114,6 +115,12 @@ __global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ param
         }
         p.x -= lr * g.x; p.y -= lr * g.y; p.z -= lr * g.z; p.w -= lr * g.w;
         reinterpret_cast<float4*>(params)[i] = p;
+        if (shadow != nullptr) {  // bf16 mirror for the tensor cores, same flat offsets
+            uint2 h;
+            h.x = pack_bf16x2(p.x, p.y);
+            h.y = pack_bf16x2(p.z, p.w);
+            reinterpret_cast<uint2*>(shadow)[i] = h;
+        }
         if (acc != nullptr) {
             float4 a = reinterpret_cast<float4*>(acc)[i];
             a.x -= lr * g.x; a.y -= lr * g.y; a.z -= lr * g.z; a.w -= lr * g.w;
@@ -248,11 +255,12 @@ extern "C" int dmlb_scale_rows_bf16(void* x, const float* scale, long long rows,
     return 0;
 }
 
-extern "C" int dmlb_sgd_flat(float* params, const float* grads, float* acc, float* mom, long long n, const float* lr_ptr, float mu, float wd,
-                             void* stream) {
+extern "C" int dmlb_sgd_flat(float* params, const float* grads, float* acc, float* mom, void* shadow, long long n, const float* lr_ptr, float mu,
+                             float wd, void* stream) {
     DMLB_REQUIRE(n % 4 == 0, "flat SGD length must be a multiple of 4 (arena padding)");
     DMLB_REQUIRE(((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads)) & 15) == 0, "arena must be 16-byte aligned");
-    sgd_flat_kernel<<<flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream)>>>(params, grads, acc, mom, n / 4, lr_ptr, mu, wd);
+    sgd_flat_kernel<<<flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream)>>>(params, grads, acc, mom, static_cast<__nv_bfloat16*>(shadow), n / 4, lr_ptr,
+                                                                                     mu, wd);
     DMLB_LAUNCH_CHECK();
     return 0;
 }

@@ -24,8 +24,20 @@ def _pair(v) -> Tuple[int, int]:
     return (v, v) if isinstance(v, int) else (int(v[0]), int(v[1]))
 
 
+def _gemm_order(w: torch.Tensor) -> bool:
+    """True when a 4-D weight is physically stored as [Cout, kh, kw, Cin] (channels-last), i.e. already in GEMM K order."""
+    return w.dim() == 4 and w.permute(0, 2, 3, 1).is_contiguous()
+
+
 class _ShadowedModule(nn.Module):
-    """Mixin for layers with a ``weight`` that is mirrored into a bf16 GEMM-layout shadow."""
+    """Mixin for layers with a ``weight`` that is mirrored into a bf16 GEMM-layout shadow.
+
+    Two kinds of shadow storage:
+    * *flat*  — the weight lives in a CUDA :class:`FlatArena` in GEMM order with ``K % 8 == 0``: the shadow is the slice of the
+      arena's flat bf16 mirror at the same offset, written by the optimizer kernel itself (no extra launch);
+    * *table* — anything else (PyTorch-layout weights, ``K % 8 != 0``, ``in_map`` linears): own storage with padded rows,
+      filled by the table-driven ``refresh_shadows`` kernel.
+    """
 
     def _init_shadow_state(self) -> None:
         self._shadow: Optional[torch.Tensor] = None
@@ -33,23 +45,48 @@ class _ShadowedModule(nn.Module):
         self._shadow_set: Optional["ShadowSet"] = None
         self._wsink: Optional[torch.Tensor] = None
         self._bsink: Optional[torch.Tensor] = None
+        self._arena_slot = None           # (arena, element offset) when the weight is arena-backed on CUDA
+        self._flat = False
 
-    # (rows, cin, khw) of the weight viewed as [rows, cin, khw]
+    # (rows, cin, khw) of the weight viewed as [rows, cin, khw] in PyTorch's logical order
     def _shadow_dims(self) -> Tuple[int, int, int]:
         raise NotImplementedError
+
+    def _needs_permute(self) -> bool:
+        """Does the fp32 weight need a (cin,khw)->(khw,cin) re-order on its way into the shadow?"""
+        rows, cin, khw = self._shadow_dims()
+        if khw == 1 or cin == 1:
+            return False
+        return not _gemm_order(self.weight)
 
     def _shadow_entry(self) -> bytes:
         rows, cin, khw = self._shadow_dims()
         ld = K.pad8(cin * khw)
+        if not self._needs_permute():
+            cin, khw = cin * khw, 1       # source already in GEMM order: plain cast with a row pitch
         return struct.pack("<qqiiii", self.weight.data_ptr() // 4, self._shadow.data_ptr() // 2, rows, cin, khw, ld)
 
     def _ensure_shadow_storage(self) -> None:
         rows, cin, khw = self._shadow_dims()
-        ld = K.pad8(cin * khw)
+        kd = cin * khw
         w = self.weight
-        if self._shadow is None or self._shadow.device != w.device or tuple(self._shadow.shape) != (rows, ld):
+        slot = self._arena_slot
+        flat_ok = False
+        if slot is not None and slot[0].shadow is not None and slot[0].params.device == w.device and not self._needs_permute():
+            arena, off = slot
+            flat_ok = kd % 8 == 0 and off % 8 == 0 and w.data_ptr() == arena.params.data_ptr() + 4 * off
+        if flat_ok:
+            arena, off = slot
+            view = arena.shadow[off:off + rows * kd].view(rows, kd)
+            if self._shadow is None or self._shadow.data_ptr() != view.data_ptr() or not self._flat:
+                self._shadow, self._flat, self._shadow_key = view, True, None
+                if self._shadow_set is not None:
+                    self._shadow_set.invalidate_table()
+            return
+        ld = K.pad8(kd)
+        if self._flat or self._shadow is None or self._shadow.device != w.device or tuple(self._shadow.shape) != (rows, ld):
             self._shadow = torch.zeros((rows, ld), dtype=torch.bfloat16, device=w.device)
-            self._shadow_key = None
+            self._flat, self._shadow_key = False, None
             if self._shadow_set is not None:
                 self._shadow_set.invalidate_table()
 
@@ -62,8 +99,12 @@ class _ShadowedModule(nn.Module):
                 self._shadow_set.refresh()
             else:
                 self._ensure_shadow_storage()
-                table = torch.frombuffer(bytearray(self._shadow_entry()), dtype=torch.uint8).to(w.device)
-                K.refresh_shadows(table, 1)
+                if self._flat:
+                    arena = self._arena_slot[0]
+                    K.cast_f32_bf16(arena.params, arena.shadow.data_ptr(), 1, arena.padded, arena.padded, arena.padded)
+                else:
+                    table = torch.frombuffer(bytearray(self._shadow_entry()), dtype=torch.uint8).to(w.device)
+                    K.refresh_shadows(table, 1)
                 self._shadow_key = key
         return self._shadow
 
@@ -72,38 +113,53 @@ class _ShadowedModule(nn.Module):
 
 
 class ShadowSet:
-    """All shadowed layers of one model, refreshed with a single kernel launch.
+    """All shadowed layers of one model, refreshed with at most two kernel launches.
 
-    ``refresh()`` is called by the framework's optimizers right after they update the fp32 masters (the
-    kernels write through raw pointers, so ``Tensor._version`` does not change) and lazily by
-    :meth:`_ShadowedModule.shadow` when a foreign optimizer or ``load_state_dict`` bumped ``_version``.
+    ``refresh()`` is called by the framework's optimizers right after they update the fp32 masters (the kernels write
+    through raw pointers, so ``Tensor._version`` does not change) and lazily by :meth:`_ShadowedModule.shadow` when a
+    foreign optimizer or ``load_state_dict`` bumped ``_version``.  ``flat_done=True`` means the caller's kernel already
+    wrote the arena's flat bf16 mirror (``sgd_flat`` does), so only table-backed shadows need work.
     """
 
     def __init__(self, model: nn.Module):
+        self.model = model
         self.modules: List[_ShadowedModule] = [m for m in model.modules() if isinstance(m, _ShadowedModule)]
         for m in self.modules:
             m._shadow_set = self
         self._table: Optional[torch.Tensor] = None
+        self._n_table = 0
         self._ptrs = None
+        self._has_flat = False
         model._dmlb_shadows = self
 
     def invalidate_table(self) -> None:
         self._table = None
 
+    def _signature(self):
+        return [(m.weight.data_ptr(), m._arena_slot[1] if m._arena_slot is not None else -1) for m in self.modules]
+
     def _build_table(self) -> None:
         for m in self.modules:
             m._ensure_shadow_storage()
-        raw = b"".join(m._shadow_entry() for m in self.modules)
+        tabled = [m for m in self.modules if not m._flat]
+        self._has_flat = any(m._flat for m in self.modules)
+        self._n_table = len(tabled)
         dev = self.modules[0].weight.device
+        raw = b"".join(m._shadow_entry() for m in tabled) or b"\0" * 32
         self._table = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(dev)
-        self._ptrs = [m.weight.data_ptr() for m in self.modules]
+        self._ptrs = self._signature()
 
-    def refresh(self) -> None:
+    def refresh(self, flat_done: bool = False) -> None:
         if not self.modules or not self.modules[0].weight.is_cuda:
             return
-        if self._table is None or self._ptrs != [m.weight.data_ptr() for m in self.modules]:
+        if self._table is None or self._ptrs != self._signature():
             self._build_table()
-        K.refresh_shadows(self._table, len(self.modules))
+            flat_done = False
+        if self._has_flat and not flat_done:
+            arena = getattr(self.model, "_dmlb_arena", None)
+            K.cast_f32_bf16(arena.params, arena.shadow.data_ptr(), 1, arena.padded, arena.padded, arena.padded)
+        if self._n_table:
+            K.refresh_shadows(self._table, self._n_table)
         for m in self.modules:
             m._mark_shadow_fresh()
 

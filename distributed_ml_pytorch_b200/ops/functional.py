@@ -210,8 +210,11 @@ class _ConvBlockFn(torch.autograd.Function):
             target = wsink if wsink is not None else gw
             tiles = ((Cout + 127) // 128) * ((Kd + 127) // 128)
             split = K.pick_split_k(tiles, M)
+            # a channels-last gradient (arena layout [Cout,kh,kw,Cin]) is exactly the GEMM's column order: contiguous
+            # rows, vector red.add; a PyTorch-layout gradient needs the (kh,kw,cin)->(cin,kh,kw) column scatter
+            gemm_order = KH * KW == 1 or Cin == 1 or target.permute(0, 2, 3, 1).is_contiguous()
             K.gemm(dy, lddy, True, a_t, lda, True, Cout, Kd, M, target, Kd, split_k=split, atomic=True,
-                   perm_cin=Cin if KH * KW > 1 else 0, perm_khw=KH * KW)
+                   perm_cin=0 if gemm_order else Cin, perm_khw=KH * KW)
         # ---- data gradient: dXcol[M, K] = dY[M, Cout] * W[Cout, K]  (B operand MN-major), then col2im ----
         dx = None
         if ctx.needs_input_grad[0]:

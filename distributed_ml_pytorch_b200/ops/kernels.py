@@ -113,9 +113,11 @@ def scale_rows(x: torch.Tensor, scale: torch.Tensor, rows, C, ld) -> None:
     _call("dmlb_scale_rows_bf16", x.data_ptr(), scale.data_ptr(), rows, C, ld, stream_ptr())
 
 
-def sgd_flat(params: torch.Tensor, grads: torch.Tensor, acc, mom, n: int, lr_dev: torch.Tensor, mu: float = 0.0, wd: float = 0.0) -> None:
+def sgd_flat(params: torch.Tensor, grads: torch.Tensor, acc, mom, n: int, lr_dev: torch.Tensor, mu: float = 0.0, wd: float = 0.0,
+             shadow=None) -> None:
     _call("dmlb_sgd_flat", params.data_ptr(), grads.data_ptr(), acc.data_ptr() if acc is not None else None,
-          mom.data_ptr() if mom is not None else None, n, lr_dev.data_ptr(), float(mu), float(wd), stream_ptr())
+          mom.data_ptr() if mom is not None else None, shadow.data_ptr() if shadow is not None else None, n, lr_dev.data_ptr(), float(mu),
+          float(wd), stream_ptr())
 
 
 def refresh_shadows(table: torch.Tensor, n_entries: int) -> None:

@@ -82,52 +82,73 @@ class FlatArena:
             raise ValueError("supplied arena storage is too small")
         self.offsets: Dict[str, Tuple[int, int]] = {}
         self._bound = False
+        self.channels_last = self.params.is_cuda
+        # flat bf16 mirror of the arena (same offsets): the optimizer kernel writes it alongside the fp32 masters
+        self.shadow = torch.zeros(self.padded, dtype=torch.bfloat16, device=self.device) if self.params.is_cuda else None
         self.bind()
 
     def is_bound(self) -> bool:
         return self._bound
+
+    def _view(self, flat: torch.Tensor, off: int, p: torch.Tensor) -> torch.Tensor:
+        """View of ``flat[off:off+numel]`` with ``p``'s logical shape.  On CUDA, conv weights are stored
+        channels-last (physically ``[Cout, kh, kw, Cin]`` — exactly the K order of the implicit GEMM), so their bf16
+        shadows are plain casts and weight-gradient GEMMs write contiguous rows; the tensor the user sees keeps
+        PyTorch's logical ``[Cout, Cin, kh, kw]`` shape, like ``memory_format=torch.channels_last`` weights."""
+        n = p.numel()
+        if self.channels_last and p.dim() == 4:
+            co, ci, kh, kw = p.shape
+            return flat[off:off + n].view(co, kh, kw, ci).permute(0, 3, 1, 2)
+        return flat[off:off + n].view(p.shape)
 
     def bind(self) -> None:
         off = 0
         with torch.no_grad():
             for name, p in self.model.named_parameters():
                 n = p.numel()
-                view = self.params[off:off + n].view(p.shape)
+                view = self._view(self.params, off, p)
                 view.copy_(p.detach().to(self.params.device))
                 p.data = view
-                p.grad = self.grads[off:off + n].view(p.shape)
+                p.grad = self._view(self.grads, off, p)
                 self.offsets[name] = (off, n)
                 off += n
             if off < self.padded:
                 self.params[off:].zero_()
             self.grads.zero_()
-        # hand the gradient views to kernel-backed layers so wgrad GEMMs accumulate in place
+        self._attach_sinks()
+        self.model._dmlb_arena = self
+        self._bound = True
+        shadows = getattr(self.model, "_dmlb_shadows", None)
+        if shadows is not None:
+            shadows.invalidate_table()
+        self.mark_params_changed()
+
+    def _attach_sinks(self) -> None:
+        # hand the gradient views (and flat-shadow slices) to kernel-backed layers so wgrad GEMMs accumulate in place
+        by_param = {id(p): name for name, p in self.model.named_parameters()}
         for mod in self.model.modules():
             if hasattr(mod, "_wsink") and getattr(mod, "weight", None) is not None:
                 mod._wsink = mod.weight.grad
                 mod._bsink = mod.bias.grad if getattr(mod, "bias", None) is not None else None
-        self.model._dmlb_arena = self
-        self._bound = True
-        self.mark_params_changed()
+                name = by_param.get(id(mod.weight))
+                mod._arena_slot = (self, self.offsets[name][0]) if (name is not None and self.shadow is not None) else None
 
     def rebind_grads(self) -> None:
         """Re-attach ``.grad`` views (after a foreign ``zero_grad(set_to_none=True)``)."""
         for name, p in self.model.named_parameters():
             off, n = self.offsets[name]
-            p.grad = self.grads[off:off + n].view(p.shape)
-        for mod in self.model.modules():
-            if hasattr(mod, "_wsink") and getattr(mod, "weight", None) is not None:
-                mod._wsink = mod.weight.grad
-                mod._bsink = mod.bias.grad if getattr(mod, "bias", None) is not None else None
+            p.grad = self._view(self.grads, off, p)
+        self._attach_sinks()
 
     def zero_grads(self) -> None:
         self.grads.zero_()
 
-    def mark_params_changed(self) -> None:
-        """Call after writing ``params`` through raw pointers: refreshes the bf16 weight shadows."""
+    def mark_params_changed(self, flat_done: bool = False) -> None:
+        """Call after writing ``params`` through raw pointers: refreshes the bf16 weight shadows
+        (``flat_done``: the writing kernel already updated the flat bf16 mirror ``self.shadow``)."""
         shadows = getattr(self.model, "_dmlb_shadows", None)
         if shadows is not None and self.params.is_cuda:
-            shadows.refresh()
+            shadows.refresh(flat_done=flat_done)
 
     def flat_params(self) -> torch.Tensor:
         return self.params[: self.numel]

@@ -188,8 +188,8 @@ class Asynchronous(ArenaOptimizer):
         self._sync_lr()
         if a.params.is_cuda:
             from ..ops import kernels as K
-            K.sgd_flat(a.params, a.grads, self.accumulated_gradients, None, a.padded, self.lr_dev, 0.0, 0.0)
-            a.mark_params_changed()
+            K.sgd_flat(a.params, a.grads, self.accumulated_gradients, None, a.padded, self.lr_dev, 0.0, 0.0, shadow=a.shadow)
+            a.mark_params_changed(flat_done=a.shadow is not None)
         else:
             lr = self.lr
             self.accumulated_gradients.add_(a.grads, alpha=-lr)

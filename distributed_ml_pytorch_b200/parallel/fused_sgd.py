@@ -49,8 +49,8 @@ class ArenaOptimizer(Optimizer):
             self.arena.rebind_grads()
         self.arena.zero_grads()
 
-    def refresh_shadows(self) -> None:
-        self.arena.mark_params_changed()
+    def refresh_shadows(self, flat_done: bool = False) -> None:
+        self.arena.mark_params_changed(flat_done=flat_done)
 
 
 class FusedSGD(ArenaOptimizer):
@@ -73,8 +73,8 @@ class FusedSGD(ArenaOptimizer):
         a = self.arena
         if a.params.is_cuda:
             from ..ops import kernels as K
-            K.sgd_flat(a.params, a.grads, None, self.momentum_buf, a.padded, self.lr_dev, g["momentum"], g["weight_decay"])
-            self.refresh_shadows()
+            K.sgd_flat(a.params, a.grads, None, self.momentum_buf, a.padded, self.lr_dev, g["momentum"], g["weight_decay"], shadow=a.shadow)
+            self.refresh_shadows(flat_done=a.shadow is not None)
         else:
             d = a.grads
             if g["weight_decay"]:

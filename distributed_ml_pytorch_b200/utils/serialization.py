@@ -10,7 +10,9 @@ Re-specifies the reference's ABSENT ``asgd.utils.serialization`` from its call s
 B200-first twist: when the model has been placed in a :class:`~distributed_ml_pytorch_b200.parallel.arena.FlatArena`
 every parameter (and gradient) is already a view into one contiguous buffer, so ravel is a zero-copy
 slice and unravel is a single ``copy_`` — the per-step ``cat`` + allocation of the reference design
-(SURVEY.md §2.5 "ravel_model_params ... every step") disappears.
+(SURVEY.md §2.5 "ravel_model_params ... every step") disappears.  (CUDA arenas store conv weights channels-last
+physically; there these two functions keep returning the *logical* ``model.parameters()`` order — which costs a
+gather — while the optimizers and the push / pull / sync kernels work on the arena's own flat order directly.)
 """
 from __future__ import annotations
 
@@ -36,7 +38,7 @@ def ravel_model_params(model, grads: bool = False) -> torch.Tensor:
     Missing gradients are raveled as zeros so the result always has length ``N``.
     """
     arena = getattr(model, "_dmlb_arena", None)
-    if arena is not None and arena.is_bound():
+    if arena is not None and arena.is_bound() and not arena.channels_last:
         flat = arena.grads if grads else arena.params
         return flat[: arena.numel]
     parts = []
@@ -54,7 +56,7 @@ def ravel_model_params(model, grads: bool = False) -> torch.Tensor:
 def unravel_model_params(model, flat: torch.Tensor) -> None:
     """Copy ``flat`` (length >= N) into the model's parameters in place."""
     arena = getattr(model, "_dmlb_arena", None)
-    if arena is not None and arena.is_bound():
+    if arena is not None and arena.is_bound() and not arena.channels_last:
         with torch.no_grad():
             arena.params[: arena.numel].copy_(flat[: arena.numel].to(arena.params.device, non_blocking=True))
         arena.mark_params_changed()
@@ -63,8 +65,10 @@ def unravel_model_params(model, flat: torch.Tensor) -> None:
     with torch.no_grad():
         for p in _params(model):
             n = p.numel()
-            p.copy_(flat[offset:offset + n].view_as(p))
+            p.copy_(flat[offset:offset + n].view(p.shape))
             offset += n
+    if arena is not None and arena.is_bound():
+        arena.mark_params_changed()
 
 
 def unravel_model_grads(model, flat: torch.Tensor) -> None:

@@ -85,9 +85,10 @@ int dmlb_relu_bwd_bf16(const void* y, const void* dy, void* dx, long long rows, 
 int dmlb_softmax_xent(const void* logits, int logits_is_bf16, const long long* labels, float* metrics, void* dlogits, int B, int C,
                       int ldl, int ldd, void* stream);
 int dmlb_scale_rows_bf16(void* x, const float* scale, long long rows, int C, int ld, void* stream);
-/* theta -= lr*g over the flat arena (n % 4 == 0); optional Downpour accumulator acc -= lr*g, momentum buffer, weight decay. */
-int dmlb_sgd_flat(float* params, const float* grads, float* acc, float* mom, long long n, const float* lr_ptr, float mu, float wd,
-                  void* stream);
+/* theta -= lr*g over the flat arena (n % 4 == 0); optional Downpour accumulator acc -= lr*g, momentum buffer,
+ * weight decay, and a flat bf16 mirror of theta (same offsets) for the tensor-core GEMMs. */
+int dmlb_sgd_flat(float* params, const float* grads, float* acc, float* mom, void* shadow_bf16, long long n, const float* lr_ptr, float mu,
+                  float wd, void* stream);
 /* table: device array of { int64 src_off, int64 dst_off, int32 rows, cin, khw, ld } — see csrc/train_ops.cu. */
 int dmlb_refresh_shadows(const float* params, void* shadow, const void* table, int n_entries, void* stream);
 int dmlb_cast_f32_bf16(const float* x, void* y, long long rows, int C, long long ldx, int ldy, void* stream);

@@ -46,7 +46,7 @@ def test_async_peer_world1_equals_fused_sgd():
     la, lb = _steps(a, oa, 5), _steps(b, ob, 5)
     assert la == pytest.approx(lb, rel=1e-3, abs=1e-3)
     torch.testing.assert_close(ravel_model_params(a), ravel_model_params(b), rtol=1e-4, atol=1e-5)
-    torch.testing.assert_close(oa.server_parameters(), ravel_model_params(a), rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(oa.server_parameters(), oa.arena.flat_params(), rtol=1e-5, atol=1e-6)
     oa.finish()
 
 
@@ -57,7 +57,7 @@ def test_async_peer_accumulates_between_pushes():
     theta0 = opt.server_parameters().clone()
     _steps(net, opt, 4)   # pushes at idx 0 and 3
     assert opt.pushes == 2
-    torch.testing.assert_close(opt.server_parameters(), ravel_model_params(net), rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(opt.server_parameters(), opt.arena.flat_params(), rtol=1e-5, atol=1e-6)
     assert not torch.equal(theta0, opt.server_parameters())
     assert opt.accumulated_gradients.abs().sum().item() == 0.0
 
@@ -69,10 +69,10 @@ def test_mailbox_momentum_and_staleness_world1():
     opt = Asynchronous(net.parameters(), lr=0.05, n_push=1, n_pull=1000, model=net, momentum=0.5, staleness="inverse")
     theta = opt.server_parameters().clone()
     v = torch.zeros_like(theta)
-    prev = ravel_model_params(net).clone()
+    prev = opt.arena.flat_params().clone()     # arena order == server order
     for i in range(4):
         _steps(net, opt, 1, seed0=i)
-        cur = ravel_model_params(net).clone()
+        cur = opt.arena.flat_params().clone()
         delta = cur - prev                   # = -lr * g of this step (pull is far away, replica only does local SGD)
         prev = cur
         tau = max(0, i - 1)                  # step 0 pushes then pulls (version 1); afterwards the snapshot ages by one per push
@@ -167,15 +167,15 @@ def _mgpu_async(rank, size, out_dir, steps, momentum):
     opt = Asynchronous(net.parameters(), lr=0.02, n_push=1, n_pull=1, model=net, momentum=momentum,
                        staleness="inverse" if momentum else None)
     theta0 = opt.server_parameters().cpu().clone()
-    local_sum = torch.zeros_like(ravel_model_params(net))
+    local_sum = torch.zeros_like(opt.arena.flat_params())
     for i in range(steps):
-        before = ravel_model_params(net).clone()
+        before = opt.arena.flat_params().clone()
         x, y = _batch(100 * rank + i, dev=dev)
         opt.zero_grad()
         OF.cross_entropy(net(x), y).backward()
         opt._apply_pending()
         opt.step_local()
-        local_sum += ravel_model_params(net) - before      # this worker's -lr*g contribution
+        local_sum += opt.arena.flat_params() - before      # this worker's -lr*g contribution
         opt.communicate()
     opt.finish()
     final = opt.server_parameters().cpu()
