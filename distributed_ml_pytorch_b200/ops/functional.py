@@ -112,6 +112,75 @@ def as_act2(t: torch.Tensor) -> Tuple[torch.Tensor, int]:
     return out, pad8(Fd)
 
 
+# ------------------------------------------------------------------------------------------------
+# side stream for weight-gradient GEMMs
+# ------------------------------------------------------------------------------------------------
+# In the backward pass of a layer the weight-gradient GEMM and the data-gradient chain (dgrad GEMM, col2im, the next
+# layer's activation backward ...) are independent.  At the reference's problem sizes each of them occupies a fraction
+# of the 148 SMs, so the wgrad GEMMs are issued on a second stream and joined once, at the end of the backward pass
+# (autograd end-of-pass callback); inside a CUDA-graph capture this becomes a parallel branch of the graph.
+_side = SimpleNamespace(streams={}, pending={}, enabled=True)
+
+
+def set_wgrad_side_stream(flag: bool) -> bool:
+    old = _side.enabled
+    _side.enabled = bool(flag)
+    return old
+
+
+def _side_stream(dev) -> "torch.cuda.Stream":
+    key = dev.index if dev.index is not None else torch.cuda.current_device()
+    st = _side.streams.get(key)
+    if st is None:
+        st = torch.cuda.Stream(device=dev)
+        _side.streams[key] = st
+    return st
+
+
+def join_side_streams() -> None:
+    """Make the current stream wait for every outstanding side-stream wgrad (idempotent)."""
+    for key, (main, side) in list(_side.pending.items()):
+        main.wait_stream(side)
+        del _side.pending[key]
+
+
+class _WgradFork:
+    """``with _WgradFork(dev, tensors...):`` runs the body on the side stream after the current stream's work."""
+
+    def __init__(self, dev, *tensors):
+        self.dev = dev
+        self.tensors = [t for t in tensors if t is not None]
+        self.active = _side.enabled
+
+    def __enter__(self):
+        if not self.active:
+            return self
+        self.main = torch.cuda.current_stream(self.dev)
+        self.side = _side_stream(self.dev)
+        if self.side.cuda_stream == self.main.cuda_stream:
+            self.active = False
+            return self
+        self.side.wait_stream(self.main)
+        self.ctx = torch.cuda.stream(self.side)
+        self.ctx.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        if not self.active:
+            return False
+        self.ctx.__exit__(*exc)
+        for t in self.tensors:
+            t.record_stream(self.side)
+        key = (self.main.cuda_stream, self.side.cuda_stream)
+        if key not in _side.pending:
+            _side.pending[key] = (self.main, self.side)
+            try:
+                torch.autograd.Variable._execution_engine.queue_callback(join_side_streams)
+            except RuntimeError:      # not inside a backward pass: join right away
+                join_side_streams()
+        return False
+
+
 def _sink_ok(param: torch.Tensor, sink: Optional[torch.Tensor]) -> bool:
     return sink is not None and param.grad is not None and param.grad.data_ptr() == sink.data_ptr()
 
@@ -213,8 +282,11 @@ class _ConvBlockFn(torch.autograd.Function):
             # a channels-last gradient (arena layout [Cout,kh,kw,Cin]) is exactly the GEMM's column order: contiguous
             # rows, vector red.add; a PyTorch-layout gradient needs the (kh,kw,cin)->(cin,kh,kw) column scatter
             gemm_order = KH * KW == 1 or Cin == 1 or target.permute(0, 2, 3, 1).is_contiguous()
-            K.gemm(dy, lddy, True, a_t, lda, True, Cout, Kd, M, target, Kd, split_k=split, atomic=True,
-                   perm_cin=0 if gemm_order else Cin, perm_khw=KH * KW)
+            with _WgradFork(dev, dy, a_t, gw) as fork:
+                K.gemm(dy, lddy, True, a_t, lda, True, Cout, Kd, M, target, Kd, split_k=split, atomic=True,
+                       perm_cin=0 if gemm_order else Cin, perm_khw=KH * KW)
+            if gw is not None and fork.active:
+                join_side_streams()       # autograd consumes a returned gradient immediately
         # ---- data gradient: dXcol[M, K] = dY[M, Cout] * W[Cout, K]  (B operand MN-major), then col2im ----
         dx = None
         if ctx.needs_input_grad[0]:
@@ -298,7 +370,11 @@ class _LinearFn(torch.autograd.Function):
             tiles = ((O + 127) // 128) * ((I + 127) // 128)
             split = K.pick_split_k(tiles, B)
             pc, pk = (cfg.in_map[0], cfg.in_map[1] * cfg.in_map[2]) if cfg.in_map is not None else (0, 0)
-            K.gemm(dy, lddy, True, x, ctx.ldx, True, O, I, B, target, I, split_k=split, atomic=True, perm_cin=pc if pk > 1 else 0, perm_khw=pk)
+            with _WgradFork(dev, dy, x, gw) as fork:
+                K.gemm(dy, lddy, True, x, ctx.ldx, True, O, I, B, target, I, split_k=split, atomic=True, perm_cin=pc if pk > 1 else 0,
+                       perm_khw=pk)
+            if gw is not None and fork.active:
+                join_side_streams()
         dx = None
         if ctx.needs_input_grad[0]:
             dx = new_act2(B, I, dev)
