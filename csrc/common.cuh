@@ -47,6 +47,18 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t v) {
 }
 
 // ----------------------------------------------------------------------------------------------
+// programmatic dependent launch (PDL): a kernel may be launched while its predecessor in the stream is still
+// running; everything before pdl_wait() (barrier init, TMEM allocation, descriptor prefetch, index math) overlaps
+// the predecessor, pdl_wait() blocks until the predecessor has completed and its memory is visible.
+// ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_prologue() {
+    pdl_launch_dependents();
+    pdl_wait();
+}
+
+// ----------------------------------------------------------------------------------------------
 // mbarrier
 // ----------------------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -219,6 +231,25 @@ __device__ __forceinline__ void st_f32x4(float* p, float4 v) { *reinterpret_cast
 extern "C" void dmlb_set_error(const char* msg);  // defined in runtime.cu
 extern "C" void dmlb_count_launch();              // defined in runtime.cu
 extern "C" int dmlb_sm_count();                   // defined in runtime.cu
+extern "C" int dmlb_pdl_enabled();                // defined in runtime.cu
+
+namespace dmlb {
+// Launch with the programmatic-stream-serialization attribute (PDL); kernels call pdl_prologue()/pdl_wait().
+template <typename... P, typename... A>
+inline cudaError_t launch_k(void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, A... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = dmlb_pdl_enabled();
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<P>(args)...);
+}
+}  // namespace dmlb
 
 #define DMLB_CHECK_CUDA(expr)                                                                      \
     do {                                                                                           \

@@ -22,6 +22,7 @@ struct ConvGeom {
 // im2col, bf16 NHWC input, 8 channels (16 B) per thread.  Requires C % 8 == 0.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) im2col_nhwc_vec8_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col, ConvGeom g) {
+    pdl_prologue();
     const int c8n = g.C >> 3;
     const long long total = 1ll * g.B * g.Ho * g.Wo * g.KH * g.KW * c8n;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
@@ -44,6 +45,7 @@ __global__ void __launch_bounds__(256) im2col_nhwc_vec8_kernel(const __nv_bfloat
 
 // im2col, bf16 NHWC input, any C (one element per thread).
 __global__ void __launch_bounds__(256) im2col_nhwc_scalar_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col, ConvGeom g) {
+    pdl_prologue();
     const int K = g.KH * g.KW * g.C;
     const long long total = 1ll * g.B * g.Ho * g.Wo * K;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
@@ -66,6 +68,7 @@ __global__ void __launch_bounds__(256) im2col_nhwc_scalar_kernel(const __nv_bflo
 // im2col straight from the user's fp32 NCHW batch (first layer): fuses the fp32->bf16 cast and the
 // NCHW->NHWC re-layout into the gather (reference main.py:64-70 feeds such a batch to conv1).
 __global__ void __launch_bounds__(256) im2col_nchw_f32_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ col, ConvGeom g) {
+    pdl_prologue();
     const int K = g.KH * g.KW * g.C;
     const long long total = 1ll * g.B * g.Ho * g.Wo * K;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
@@ -90,6 +93,7 @@ __global__ void __launch_bounds__(256) im2col_nchw_f32_kernel(const float* __res
 // ---------------------------------------------------------------------------------------------
 template <int VEC>
 __global__ void __launch_bounds__(256) col2im_nhwc_kernel(const __nv_bfloat16* __restrict__ dcol, __nv_bfloat16* __restrict__ dx, ConvGeom g) {
+    pdl_prologue();
     const int cvn = (g.C + VEC - 1) / VEC;
     const long long total = 1ll * g.B * g.H * g.W * cvn;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
@@ -146,6 +150,7 @@ struct PoolGeom {
 
 template <int VEC>
 __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, PoolGeom g) {
+    pdl_prologue();
     const int cvn = (g.C + VEC - 1) / VEC;
     const long long total = 1ll * g.B * g.Ho * g.Wo * cvn;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
@@ -198,6 +203,7 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* _
 __global__ void __launch_bounds__(256) act_bwd_kernel(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ dout,
                                                       __nv_bfloat16* __restrict__ dy, float* __restrict__ dbias, PoolGeom g, int ldd,
                                                       int has_pool, int relu) {
+    pdl_prologue();
     extern __shared__ float sbias[];  // [C]
     for (int c = threadIdx.x; c < g.C; c += blockDim.x) sbias[c] = 0.f;
     __syncthreads();
@@ -250,6 +256,7 @@ __global__ void __launch_bounds__(256) act_bwd_kernel(const __nv_bfloat16* __res
 // Standalone ReLU (bf16, padded rows): y = max(x, 0); backward dx = dy * (y > 0).
 __global__ void __launch_bounds__(256) relu_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long rows,
                                                        int C, int ldx, int ldy) {
+    pdl_prologue();
     const long long total = rows * C;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
         const long long r = i / C;
@@ -259,6 +266,7 @@ __global__ void __launch_bounds__(256) relu_fwd_kernel(const __nv_bfloat16* __re
 }
 __global__ void __launch_bounds__(256) relu_bwd_kernel(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ dy,
                                                        __nv_bfloat16* __restrict__ dx, long long rows, int C, int ldy, int lddy, int lddx) {
+    pdl_prologue();
     const long long total = rows * C;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
         const long long r = i / C;
@@ -297,10 +305,10 @@ extern "C" int dmlb_im2col_nhwc_bf16(const void* x, void* col, int B, int H, int
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (C % 8 == 0 && ldx % 8 == 0) {
         const long long total = 1ll * B * g.Ho * g.Wo * KH * KW * (C / 8);
-        im2col_nhwc_vec8_kernel<<<grid_for(total), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(col), g);
+        DMLB_CHECK_CUDA(launch_k(im2col_nhwc_vec8_kernel, grid_for(total), 256, 0, s, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(col), g));
     } else {
         const long long total = 1ll * B * g.Ho * g.Wo * KH * KW * C;
-        im2col_nhwc_scalar_kernel<<<grid_for(total), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(col), g);
+        DMLB_CHECK_CUDA(launch_k(im2col_nhwc_scalar_kernel, grid_for(total), 256, 0, s, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(col), g));
     }
     DMLB_LAUNCH_CHECK();
     return 0;
@@ -312,7 +320,7 @@ extern "C" int dmlb_im2col_nchw_f32(const float* x, void* col, int B, int H, int
     DMLB_REQUIRE(g.Ho > 0 && g.Wo > 0, "empty conv output");
     DMLB_REQUIRE(Kpad >= KH * KW * C && Kpad % 8 == 0, "Kpad must cover K and be a multiple of 8");
     const long long total = 1ll * B * g.Ho * g.Wo * KH * KW * C;
-    im2col_nchw_f32_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, static_cast<__nv_bfloat16*>(col), g);
+    DMLB_CHECK_CUDA(launch_k(im2col_nchw_f32_kernel, grid_for(total), 256, 0, static_cast<cudaStream_t>(stream), x, static_cast<__nv_bfloat16*>(col), g));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
@@ -323,10 +331,10 @@ extern "C" int dmlb_col2im_nhwc_bf16(const void* dcol, void* dx, int B, int H, i
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (C % 8 == 0 && ldx % 8 == 0) {
         const long long total = 1ll * B * H * W * (C / 8);
-        col2im_nhwc_kernel<8><<<grid_for(total), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(dcol), static_cast<__nv_bfloat16*>(dx), g);
+        DMLB_CHECK_CUDA(launch_k(col2im_nhwc_kernel<8>, grid_for(total), 256, 0, s, static_cast<const __nv_bfloat16*>(dcol), static_cast<__nv_bfloat16*>(dx), g));
     } else {
         const long long total = 1ll * B * H * W * C;
-        col2im_nhwc_kernel<1><<<grid_for(total), 256, 0, s>>>(static_cast<const __nv_bfloat16*>(dcol), static_cast<__nv_bfloat16*>(dx), g);
+        DMLB_CHECK_CUDA(launch_k(col2im_nhwc_kernel<1>, grid_for(total), 256, 0, s, static_cast<const __nv_bfloat16*>(dcol), static_cast<__nv_bfloat16*>(dx), g));
     }
     DMLB_LAUNCH_CHECK();
     return 0;
@@ -346,10 +354,10 @@ extern "C" int dmlb_maxpool_fwd_bf16(const void* x, void* y, int B, int H, int W
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (C % 8 == 0 && ldx % 8 == 0 && ldo % 8 == 0) {
         const long long total = 1ll * B * g.Ho * g.Wo * (C / 8);
-        maxpool_fwd_kernel<8><<<grid_for(total), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), g);
+        DMLB_CHECK_CUDA(launch_k(maxpool_fwd_kernel<8>, grid_for(total), 256, 0, st, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), g));
     } else {
         const long long total = 1ll * B * g.Ho * g.Wo * C;
-        maxpool_fwd_kernel<1><<<grid_for(total), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), g);
+        DMLB_CHECK_CUDA(launch_k(maxpool_fwd_kernel<1>, grid_for(total), 256, 0, st, static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), g));
     }
     DMLB_LAUNCH_CHECK();
     return 0;
@@ -363,23 +371,23 @@ extern "C" int dmlb_act_bwd_bf16(const void* y, const void* dout, void* dy, floa
     const long long total = 1ll * B * H * W * C;
     int blocks = grid_for(total);
     if (blocks > 148 * 4) blocks = 148 * 4;  // fewer, fatter CTAs: fewer global bias atomics
-    act_bwd_kernel<<<blocks, 256, C * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
+    DMLB_CHECK_CUDA(launch_k(act_bwd_kernel, blocks, 256, C * sizeof(float), static_cast<cudaStream_t>(stream), 
         static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dout), static_cast<__nv_bfloat16*>(dy), dbias, g, ldd, has_pool,
-        relu);
+        relu));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
 
 extern "C" int dmlb_relu_fwd_bf16(const void* x, void* y, long long rows, int C, int ldx, int ldy, void* stream) {
-    relu_fwd_kernel<<<grid_for(rows * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(x),
-                                                                                       static_cast<__nv_bfloat16*>(y), rows, C, ldx, ldy);
+    DMLB_CHECK_CUDA(launch_k(relu_fwd_kernel, grid_for(rows * C), 256, 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(x),
+                                                                                       static_cast<__nv_bfloat16*>(y), rows, C, ldx, ldy));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
 
 extern "C" int dmlb_relu_bwd_bf16(const void* y, const void* dy, void* dx, long long rows, int C, int ldy, int lddy, int lddx, void* stream) {
-    relu_bwd_kernel<<<grid_for(rows * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), rows, C, ldy, lddy, lddx);
+    DMLB_CHECK_CUDA(launch_k(relu_bwd_kernel, grid_for(rows * C), 256, 0, static_cast<cudaStream_t>(stream), 
+        static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dy), static_cast<__nv_bfloat16*>(dx), rows, C, ldy, lddy, lddx));
     DMLB_LAUNCH_CHECK();
     return 0;
 }

@@ -94,6 +94,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_d = *tmem_holder_ptr;
+    // Everything above touched only shared memory / TMEM / kernel parameters: it overlapped the previous kernel.
+    pdl_launch_dependents();
+    pdl_wait();
 
     if (warp == 0) {
         // ------------------------------ TMA producer ------------------------------
@@ -286,7 +289,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmE
     int kb_per = (nkb + splits - 1) / splits;
     splits = (nkb + kb_per - 1) / kb_per;  // every z-slice owns >= 1 k-block
     dim3 grid((M + kBM - 1) / kBM, (N + BN - 1) / BN, splits);
-    kern<<<grid, kGemmThreads, S::kTotal, stream>>>(ta, tb, ep, M, N, K, kb_per);
+    DMLB_CHECK_CUDA(launch_k(kern, grid, kGemmThreads, S::kTotal, stream, ta, tb, ep, M, N, K, kb_per));
     DMLB_LAUNCH_CHECK();
     return 0;
 }

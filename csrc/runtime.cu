@@ -1,6 +1,8 @@
 // Host-side runtime glue shared by every kernel launcher: last-error string, kernel-launch
 // accounting (bench.py reports "gpu_launches" from it) and device queries.
 // No counterpart in the reference (it has no native code).
+#include <stdlib.h>
+
 #include <atomic>
 #include <mutex>
 #include <string>
@@ -30,6 +32,17 @@ extern "C" long long dmlb_launch_count() { return g_launches.load(std::memory_or
 extern "C" void dmlb_reset_launch_count() { g_launches.store(0, std::memory_order_relaxed); }
 
 extern "C" int dmlb_abi_version() { return 1; }
+
+// Programmatic dependent launch switch (default on; DMLB_PDL=0 in the environment or dmlb_set_pdl(0) turns it off).
+static int g_pdl = -1;
+extern "C" int dmlb_pdl_enabled() {
+    if (g_pdl < 0) {
+        const char* e = getenv("DMLB_PDL");
+        g_pdl = (e != nullptr && e[0] == '0') ? 0 : 1;
+    }
+    return g_pdl;
+}
+extern "C" void dmlb_set_pdl(int on) { g_pdl = on ? 1 : 0; }
 
 // Number of SMs of the current device (148 on B200); used to size persistent / flat grids.
 extern "C" int dmlb_sm_count() {

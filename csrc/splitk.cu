@@ -18,6 +18,7 @@ namespace dmlb {
 // ws [M, ldw] fp32 -> y [M, ldy] bf16 = act(ws + bias); ws <- 0.   N % 4 == 0 fast path, scalar otherwise.
 __global__ void __launch_bounds__(256) splitk_finish_kernel(float* __restrict__ ws, int ldw, const float* __restrict__ bias, int relu,
                                                             __nv_bfloat16* __restrict__ y, int ldy, long long M, int N) {
+    pdl_prologue();
     const int n4 = (N + 3) / 4;
     const long long total = M * n4;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
@@ -43,6 +44,7 @@ __global__ void __launch_bounds__(256) splitk_finish_kernel(float* __restrict__ 
 __global__ void __launch_bounds__(256) splitk_finish_pool2_kernel(float* __restrict__ ws, int ldw, const float* __restrict__ bias, int relu,
                                                                   __nv_bfloat16* __restrict__ y, int ldy, __nv_bfloat16* __restrict__ pooled,
                                                                   int ldp, int B, int H, int W, int N) {
+    pdl_prologue();
     const int n4 = (N + 3) / 4;
     const int Hp = H / 2, Wp = W / 2;
     const long long total = 1ll * B * Hp * Wp * n4;
@@ -105,11 +107,11 @@ extern "C" int dmlb_splitk_finish(float* ws, int ldw, const float* bias, int rel
     if (pool2) {
         DMLB_REQUIRE(1ll * B * H * W == M && H % 2 == 0 && W % 2 == 0, "pooled finish needs an even [B,H,W] map with B*H*W == M");
         const long long total = 1ll * B * (H / 2) * (W / 2) * ((N + 3) / 4);
-        splitk_finish_pool2_kernel<<<finish_grid(total), 256, 0, st>>>(ws, ldw, bias, relu, static_cast<__nv_bfloat16*>(y), ldy,
-                                                                       static_cast<__nv_bfloat16*>(pooled), ldp, B, H, W, N);
+        DMLB_CHECK_CUDA(launch_k(splitk_finish_pool2_kernel, finish_grid(total), 256, 0, st, ws, ldw, bias, relu, static_cast<__nv_bfloat16*>(y), ldy,
+                                                                       static_cast<__nv_bfloat16*>(pooled), ldp, B, H, W, N));
     } else {
         const long long total = M * ((N + 3) / 4);
-        splitk_finish_kernel<<<finish_grid(total), 256, 0, st>>>(ws, ldw, bias, relu, static_cast<__nv_bfloat16*>(y), ldy, M, N);
+        DMLB_CHECK_CUDA(launch_k(splitk_finish_kernel, finish_grid(total), 256, 0, st, ws, ldw, bias, relu, static_cast<__nv_bfloat16*>(y), ldy, M, N));
     }
     DMLB_LAUNCH_CHECK();
     return 0;

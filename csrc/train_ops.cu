@@ -33,6 +33,7 @@ template <typename T>
 __global__ void __launch_bounds__(1024) softmax_xent_kernel(const T* __restrict__ logits, const long long* __restrict__ labels,
                                                             float* __restrict__ metrics, T* __restrict__ dlogits, int B, int C,
                                                             int ldl, int ldd) {
+    pdl_prologue();
     __shared__ float s_loss[32];
     __shared__ float s_hit[32];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
@@ -83,6 +84,7 @@ __global__ void __launch_bounds__(1024) softmax_xent_kernel(const T* __restrict_
 // x[r, c] *= *scale  (bf16, padded rows) — applies an upstream scalar gradient to the saved dlogits.
 __global__ void __launch_bounds__(256) scale_rows_kernel(__nv_bfloat16* __restrict__ x, const float* __restrict__ scale, long long rows, int C,
                                                          int ld) {
+    pdl_prologue();
     const float s = *scale;
     const long long total = rows * C;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
@@ -102,6 +104,7 @@ __global__ void __launch_bounds__(256) scale_rows_kernel(__nv_bfloat16* __restri
 __global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ params, const float* __restrict__ grads, float* __restrict__ acc,
                                                        float* __restrict__ mom, __nv_bfloat16* __restrict__ shadow, long long n4,
                                                        const float* __restrict__ lr_ptr, float mu, float wd) {
+    pdl_prologue();
     const float lr = *lr_ptr;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
         float4 p = reinterpret_cast<float4*>(params)[i];
@@ -142,6 +145,7 @@ struct ShadowEntry {
 
 __global__ void __launch_bounds__(256) refresh_shadows_kernel(const float* __restrict__ params, __nv_bfloat16* __restrict__ shadow,
                                                               const ShadowEntry* __restrict__ table) {
+    pdl_prologue();
     const ShadowEntry e = table[blockIdx.y];
     const int K = e.cin * e.khw;
     const long long total = 1ll * e.rows * K;
@@ -160,6 +164,7 @@ __global__ void __launch_bounds__(256) refresh_shadows_kernel(const float* __res
 // Generic 2-D cast fp32 -> bf16 with row pitches (inputs of Linear layers fed with fp32 tensors).
 __global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, long long rows, int C,
                                                             long long ldx, int ldy) {
+    pdl_prologue();
     const long long total = rows * C;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
         const long long r = i / C;
@@ -169,6 +174,7 @@ __global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float* __restr
 }
 __global__ void __launch_bounds__(256) cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ y, long long rows, int C,
                                                             int ldx, long long ldy) {
+    pdl_prologue();
     const long long total = rows * C;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
         const long long r = i / C;
@@ -196,6 +202,7 @@ __global__ void __launch_bounds__(256) dropout_fwd_kernel(const __nv_bfloat16* _
                                                           uint8_t* __restrict__ mask, long long rows, int C, int ldx, int ldy,
                                                           int rows_per_sample, int channel_mode, float p, uint64_t seed,
                                                           const unsigned long long* __restrict__ step) {
+    pdl_prologue();
     const uint64_t st = *step;
     const float scale = 1.f / (1.f - p);
     const uint32_t thresh = static_cast<uint32_t>(static_cast<double>(p) * 4294967296.0);
@@ -212,6 +219,7 @@ __global__ void __launch_bounds__(256) dropout_fwd_kernel(const __nv_bfloat16* _
 }
 __global__ void __launch_bounds__(256) dropout_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restrict__ mask,
                                                           __nv_bfloat16* __restrict__ dx, long long rows, int C, int lddy, int lddx, float p) {
+    pdl_prologue();
     const float scale = 1.f / (1.f - p);
     const long long total = rows * C;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
@@ -240,17 +248,17 @@ extern "C" int dmlb_softmax_xent(const void* logits, int logits_is_bf16, const l
     int threads = 32 * ((B < 32) ? B : 32);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (logits_is_bf16)
-        softmax_xent_kernel<__nv_bfloat16><<<1, threads, 0, st>>>(static_cast<const __nv_bfloat16*>(logits), labels, metrics,
-                                                                  static_cast<__nv_bfloat16*>(dlogits), B, C, ldl, ldd);
+        DMLB_CHECK_CUDA(launch_k(softmax_xent_kernel<__nv_bfloat16>, 1, threads, 0, st, static_cast<const __nv_bfloat16*>(logits), labels, metrics,
+                                                                  static_cast<__nv_bfloat16*>(dlogits), B, C, ldl, ldd));
     else
-        softmax_xent_kernel<float><<<1, threads, 0, st>>>(static_cast<const float*>(logits), labels, metrics, static_cast<float*>(dlogits), B, C,
-                                                          ldl, ldd);
+        DMLB_CHECK_CUDA(launch_k(softmax_xent_kernel<float>, 1, threads, 0, st, static_cast<const float*>(logits), labels, metrics, static_cast<float*>(dlogits), B, C,
+                                                          ldl, ldd));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
 
 extern "C" int dmlb_scale_rows_bf16(void* x, const float* scale, long long rows, int C, int ld, void* stream) {
-    scale_rows_kernel<<<flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<__nv_bfloat16*>(x), scale, rows, C, ld);
+    DMLB_CHECK_CUDA(launch_k(scale_rows_kernel, flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream), static_cast<__nv_bfloat16*>(x), scale, rows, C, ld));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
@@ -259,8 +267,8 @@ extern "C" int dmlb_sgd_flat(float* params, const float* grads, float* acc, floa
                              float wd, void* stream) {
     DMLB_REQUIRE(n % 4 == 0, "flat SGD length must be a multiple of 4 (arena padding)");
     DMLB_REQUIRE(((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads)) & 15) == 0, "arena must be 16-byte aligned");
-    sgd_flat_kernel<<<flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream)>>>(params, grads, acc, mom, static_cast<__nv_bfloat16*>(shadow), n / 4, lr_ptr,
-                                                                                     mu, wd);
+    DMLB_CHECK_CUDA(launch_k(sgd_flat_kernel, flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream), params, grads, acc, mom, static_cast<__nv_bfloat16*>(shadow), n / 4, lr_ptr,
+                                                                                     mu, wd));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
@@ -269,19 +277,19 @@ extern "C" int dmlb_sgd_flat(float* params, const float* grads, float* acc, floa
 extern "C" int dmlb_refresh_shadows(const float* params, void* shadow, const void* table, int n_entries, void* stream) {
     if (n_entries <= 0) return 0;
     dim3 grid(96, n_entries);
-    refresh_shadows_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(params, static_cast<__nv_bfloat16*>(shadow),
-                                                                               static_cast<const ShadowEntry*>(table));
+    DMLB_CHECK_CUDA(launch_k(refresh_shadows_kernel, grid, 256, 0, static_cast<cudaStream_t>(stream), params, static_cast<__nv_bfloat16*>(shadow),
+                                                                               static_cast<const ShadowEntry*>(table)));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
 
 extern "C" int dmlb_cast_f32_bf16(const float* x, void* y, long long rows, int C, long long ldx, int ldy, void* stream) {
-    cast_f32_bf16_kernel<<<flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, static_cast<__nv_bfloat16*>(y), rows, C, ldx, ldy);
+    DMLB_CHECK_CUDA(launch_k(cast_f32_bf16_kernel, flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream), x, static_cast<__nv_bfloat16*>(y), rows, C, ldx, ldy));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
 extern "C" int dmlb_cast_bf16_f32(const void* x, float* y, long long rows, int C, int ldx, long long ldy, void* stream) {
-    cast_bf16_f32_kernel<<<flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(x), y, rows, C, ldx, ldy);
+    DMLB_CHECK_CUDA(launch_k(cast_bf16_f32_kernel, flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(x), y, rows, C, ldx, ldy));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
@@ -289,20 +297,20 @@ extern "C" int dmlb_cast_bf16_f32(const void* x, float* y, long long rows, int C
 extern "C" int dmlb_dropout_fwd_bf16(const void* x, void* y, void* mask, long long rows, int C, int ldx, int ldy, int rows_per_sample,
                                      int channel_mode, float p, unsigned long long seed, const void* step, void* stream) {
     DMLB_REQUIRE(p >= 0.f && p < 1.f, "dropout probability must be in [0, 1)");
-    dropout_fwd_kernel<<<flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    DMLB_CHECK_CUDA(launch_k(dropout_fwd_kernel, flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream), 
         static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), static_cast<uint8_t*>(mask), rows, C, ldx, ldy, rows_per_sample,
-        channel_mode, p, seed, static_cast<const unsigned long long*>(step));
+        channel_mode, p, seed, static_cast<const unsigned long long*>(step)));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
 extern "C" int dmlb_dropout_bwd_bf16(const void* dy, const void* mask, void* dx, long long rows, int C, int lddy, int lddx, float p, void* stream) {
-    dropout_bwd_kernel<<<flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const __nv_bfloat16*>(dy), static_cast<const uint8_t*>(mask), static_cast<__nv_bfloat16*>(dx), rows, C, lddy, lddx, p);
+    DMLB_CHECK_CUDA(launch_k(dropout_bwd_kernel, flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream), 
+        static_cast<const __nv_bfloat16*>(dy), static_cast<const uint8_t*>(mask), static_cast<__nv_bfloat16*>(dx), rows, C, lddy, lddx, p));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
 extern "C" int dmlb_counter_bump(void* counter, void* stream) {
-    counter_bump_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<unsigned long long*>(counter));
+    DMLB_CHECK_CUDA(launch_k(counter_bump_kernel, 1, 1, 0, static_cast<cudaStream_t>(stream), static_cast<unsigned long long*>(counter)));
     DMLB_LAUNCH_CHECK();
     return 0;
 }

@@ -25,6 +25,8 @@ long long dmlb_launch_count(void);       /* kernels launched by this library sin
 void dmlb_reset_launch_count(void);
 void dmlb_count_launch(void);
 int dmlb_sm_count(void);
+int dmlb_pdl_enabled(void);               /* programmatic dependent launch between consecutive kernels (default 1; env DMLB_PDL=0) */
+void dmlb_set_pdl(int on);
 
 /* ---- tcgen05 GEMM (reference: nn.Linear / nn.Conv2d in example/models.py:8-13,28-43) ------------
  * D[M,N] (+)= A[M,K] * B[N,K]^T, bf16 operands, fp32 accumulation in TMEM.
