@@ -69,22 +69,25 @@ __global__ void __launch_bounds__(256) im2col_nhwc_scalar_kernel(const __nv_bflo
 // NCHW->NHWC re-layout into the gather (reference main.py:64-70 feeds such a batch to conv1).
 __global__ void __launch_bounds__(256) im2col_nchw_f32_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ col, ConvGeom g) {
     pdl_prologue();
-    const int K = g.KH * g.KW * g.C;
-    const long long total = 1ll * g.B * g.Ho * g.Wo * K;
+    // one thread per (output pixel, filter tap): the index arithmetic is paid once for all C channels, neighbouring
+    // threads read neighbouring input columns (coalesced) and write neighbouring C-element groups of the same row
+    const int taps = g.KH * g.KW;
+    const long long total = 1ll * g.B * g.Ho * g.Wo * taps;
+    const long long plane = 1ll * g.H * g.W;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
-        const int k = static_cast<int>(i % K);
-        const long long m = i / K;
-        const int c = k % g.C;
-        const int kwi = (k / g.C) % g.KW;
-        const int khi = k / (g.C * g.KW);
+        const int tap = static_cast<int>(i % taps);
+        const long long m = i / taps;
+        const int kwi = tap % g.KW;
+        const int khi = tap / g.KW;
         const int wo = static_cast<int>(m % g.Wo);
         const int ho = static_cast<int>((m / g.Wo) % g.Ho);
         const int b = static_cast<int>(m / (1ll * g.Wo * g.Ho));
         const int hi = ho * g.SH - g.PH + khi;
         const int wi = wo * g.SW - g.PW + kwi;
-        float v = 0.f;
-        if (hi >= 0 && hi < g.H && wi >= 0 && wi < g.W) v = __ldg(x + ((1ll * b * g.C + c) * g.H + hi) * g.W + wi);
-        col[m * g.Kpad + k] = __float2bfloat16_rn(v);
+        const bool ok = hi >= 0 && hi < g.H && wi >= 0 && wi < g.W;
+        const float* src = x + (1ll * b * g.C * g.H + hi) * g.W + wi;
+        __nv_bfloat16* dst = col + m * g.Kpad + tap * g.C;
+        for (int c = 0; c < g.C; ++c) dst[c] = __float2bfloat16_rn(ok ? __ldg(src + c * plane) : 0.f);
     }
 }
 
@@ -253,6 +256,91 @@ __global__ void __launch_bounds__(256) act_bwd_kernel(const __nv_bfloat16* __res
     }
 }
 
+// Vectorised variant (8 channels = 16 bytes per thread) for the common cases: no pooling, or the 2x2 / stride-2 pool of
+// AlexNet and LeNet.  Bias-gradient partial sums stay in registers while a thread keeps visiting the same channel group.
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+    const float2 a = unpack_bf16x2(v.x), b = unpack_bf16x2(v.y), c = unpack_bf16x2(v.z), d = unpack_bf16x2(v.w);
+    f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+
+__global__ void __launch_bounds__(256) act_bwd_vec8_kernel(const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ dout,
+                                                           __nv_bfloat16* __restrict__ dy, float* __restrict__ dbias, PoolGeom g, int ldd,
+                                                           int has_pool, int relu) {
+    pdl_prologue();
+    extern __shared__ float sbias[];  // [C]
+    for (int c = threadIdx.x; c < g.C; c += blockDim.x) sbias[c] = 0.f;
+    __syncthreads();
+    const int c8n = g.C >> 3;
+    const long long total = 1ll * g.B * g.H * g.W * c8n;
+    float bacc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    int cur_c8 = -1;
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
+        const int c8 = static_cast<int>(i % c8n);
+        long long t = i / c8n;
+        const int w = static_cast<int>(t % g.W); t /= g.W;
+        const int h = static_cast<int>(t % g.H);
+        const int b = static_cast<int>(t / g.H);
+        const long long xi = ((1ll * b * g.H + h) * g.W + w) * g.ldx + c8 * 8;
+        float yv[8], gv[8];
+        unpack8(__ldg(reinterpret_cast<const uint4*>(y + xi)), yv);
+        if (!has_pool) {
+            unpack8(__ldg(reinterpret_cast<const uint4*>(dout + ((1ll * b * g.H + h) * g.W + w) * ldd + c8 * 8)), gv);
+        } else {
+            const int hp = h >> 1, wp = w >> 1;
+            if (hp >= g.Ho || wp >= g.Wo) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) gv[j] = 0.f;
+            } else {
+                unpack8(__ldg(reinterpret_cast<const uint4*>(dout + ((1ll * b * g.Ho + hp) * g.Wo + wp) * ldd + c8 * 8)), gv);
+                const int self = ((h & 1) << 1) | (w & 1);   // scan position inside the window
+#pragma unroll
+                for (int o = 0; o < 4; ++o) {
+                    if (o == self) continue;
+                    float ov[8];
+                    const long long oi = ((1ll * b * g.H + (2 * hp + (o >> 1))) * g.W + (2 * wp + (o & 1))) * g.ldx + c8 * 8;
+                    unpack8(__ldg(reinterpret_cast<const uint4*>(y + oi)), ov);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        if (ov[j] > yv[j] || (o < self && ov[j] == yv[j])) gv[j] = 0.f;   // PyTorch: first maximum wins
+                }
+            }
+        }
+        if (relu) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (!(yv[j] > 0.f)) gv[j] = 0.f;
+        }
+        uint4 o;
+        o.x = pack_bf16x2(gv[0], gv[1]); o.y = pack_bf16x2(gv[2], gv[3]);
+        o.z = pack_bf16x2(gv[4], gv[5]); o.w = pack_bf16x2(gv[6], gv[7]);
+        *reinterpret_cast<uint4*>(dy + xi) = o;
+        if (dbias != nullptr) {
+            if (c8 != cur_c8) {
+                if (cur_c8 >= 0) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        if (bacc[j] != 0.f) atomicAdd(&sbias[cur_c8 * 8 + j], bacc[j]);
+                        bacc[j] = 0.f;
+                    }
+                }
+                cur_c8 = c8;
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) bacc[j] += gv[j];
+        }
+    }
+    if (dbias != nullptr) {
+        if (cur_c8 >= 0) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (bacc[j] != 0.f) atomicAdd(&sbias[cur_c8 * 8 + j], bacc[j]);
+        }
+        __syncthreads();
+        for (int c = threadIdx.x; c < g.C; c += blockDim.x)
+            if (sbias[c] != 0.f) red_add_f32(dbias + c, sbias[c]);
+    }
+}
+
 // Standalone ReLU (bf16, padded rows): y = max(x, 0); backward dx = dy * (y > 0).
 __global__ void __launch_bounds__(256) relu_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long rows,
                                                        int C, int ldx, int ldy) {
@@ -319,7 +407,7 @@ extern "C" int dmlb_im2col_nchw_f32(const float* x, void* col, int B, int H, int
     ConvGeom g = make_geom(B, H, W, C, KH, KW, SH, SW, PH, PW, 0, Kpad);
     DMLB_REQUIRE(g.Ho > 0 && g.Wo > 0, "empty conv output");
     DMLB_REQUIRE(Kpad >= KH * KW * C && Kpad % 8 == 0, "Kpad must cover K and be a multiple of 8");
-    const long long total = 1ll * B * g.Ho * g.Wo * KH * KW * C;
+    const long long total = 1ll * B * g.Ho * g.Wo * KH * KW;
     DMLB_CHECK_CUDA(launch_k(im2col_nchw_f32_kernel, grid_for(total), 256, 0, static_cast<cudaStream_t>(stream), x, static_cast<__nv_bfloat16*>(col), g));
     DMLB_LAUNCH_CHECK();
     return 0;
@@ -368,12 +456,28 @@ extern "C" int dmlb_act_bwd_bf16(const void* y, const void* dout, void* dy, floa
                                  int has_pool, int k, int s, int p, int relu, void* stream) {
     PoolGeom g = has_pool ? make_pool(B, H, W, C, ldy, ldd, k, s, p) : make_pool(B, H, W, C, ldy, ldd, 1, 1, 0);
     DMLB_REQUIRE(C * 4 <= 48 * 1024, "channel count too large for the bias-gradient staging buffer");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool pool_ok = !has_pool || (k == 2 && s == 2 && p == 0);
+    if (C % 8 == 0 && ldy % 8 == 0 && ldd % 8 == 0 && pool_ok) {
+        const int c8n = C / 8;
+        const long long total = 1ll * B * H * W * c8n;
+        int blocks = grid_for(total);
+        if (blocks > 148 * 2) blocks = 148 * 2;
+        // keep (threads in the grid) a multiple of the channel-group count so a thread's channel group never changes
+        int a = c8n, bq = 256;
+        while (bq) { const int tmp = a % bq; a = bq; bq = tmp; }
+        const int mult = c8n / a;
+        if (blocks > mult) blocks = blocks / mult * mult;
+        DMLB_CHECK_CUDA(launch_k(act_bwd_vec8_kernel, blocks, 256, C * sizeof(float), st, static_cast<const __nv_bfloat16*>(y),
+                                 static_cast<const __nv_bfloat16*>(dout), static_cast<__nv_bfloat16*>(dy), dbias, g, ldd, has_pool, relu));
+        DMLB_LAUNCH_CHECK();
+        return 0;
+    }
     const long long total = 1ll * B * H * W * C;
     int blocks = grid_for(total);
     if (blocks > 148 * 4) blocks = 148 * 4;  // fewer, fatter CTAs: fewer global bias atomics
-    DMLB_CHECK_CUDA(launch_k(act_bwd_kernel, blocks, 256, C * sizeof(float), static_cast<cudaStream_t>(stream), 
-        static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dout), static_cast<__nv_bfloat16*>(dy), dbias, g, ldd, has_pool,
-        relu));
+    DMLB_CHECK_CUDA(launch_k(act_bwd_kernel, blocks, 256, C * sizeof(float), st, static_cast<const __nv_bfloat16*>(y),
+                             static_cast<const __nv_bfloat16*>(dout), static_cast<__nv_bfloat16*>(dy), dbias, g, ldd, has_pool, relu));
     DMLB_LAUNCH_CHECK();
     return 0;
 }

@@ -101,14 +101,15 @@ __global__ void __launch_bounds__(256) scale_rows_kernel(__nv_bfloat16* __restri
 // lr is read from device memory so a captured CUDA graph follows LR-scheduler changes.
 // n must be a multiple of 4 (the arena pads to that).
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ params, const float* __restrict__ grads, float* __restrict__ acc,
+__global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ params, float* __restrict__ grads, float* __restrict__ acc,
                                                        float* __restrict__ mom, __nv_bfloat16* __restrict__ shadow, long long n4,
-                                                       const float* __restrict__ lr_ptr, float mu, float wd) {
+                                                       const float* __restrict__ lr_ptr, float mu, float wd, int zero_grads) {
     pdl_prologue();
     const float lr = *lr_ptr;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
         float4 p = reinterpret_cast<float4*>(params)[i];
         float4 g = ld_stream_f32x4(grads + 4 * i);
+        if (zero_grads) reinterpret_cast<float4*>(grads)[i] = make_float4(0.f, 0.f, 0.f, 0.f);  // next step starts clean: no memset node
         if (wd != 0.f) { g.x += wd * p.x; g.y += wd * p.y; g.z += wd * p.z; g.w += wd * p.w; }
         if (mom != nullptr) {
             float4 v = reinterpret_cast<float4*>(mom)[i];
@@ -263,12 +264,12 @@ extern "C" int dmlb_scale_rows_bf16(void* x, const float* scale, long long rows,
     return 0;
 }
 
-extern "C" int dmlb_sgd_flat(float* params, const float* grads, float* acc, float* mom, void* shadow, long long n, const float* lr_ptr, float mu,
-                             float wd, void* stream) {
+extern "C" int dmlb_sgd_flat(float* params, float* grads, float* acc, float* mom, void* shadow, long long n, const float* lr_ptr, float mu,
+                             float wd, int zero_grads, void* stream) {
     DMLB_REQUIRE(n % 4 == 0, "flat SGD length must be a multiple of 4 (arena padding)");
     DMLB_REQUIRE(((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads)) & 15) == 0, "arena must be 16-byte aligned");
     DMLB_CHECK_CUDA(launch_k(sgd_flat_kernel, flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream), params, grads, acc, mom, static_cast<__nv_bfloat16*>(shadow), n / 4, lr_ptr,
-                                                                                     mu, wd));
+                             mu, wd, zero_grads));
     DMLB_LAUNCH_CHECK();
     return 0;
 }

@@ -70,6 +70,9 @@ class TrainStep:
             shadows = getattr(model, "_dmlb_shadows", None)
             if shadows is not None:
                 shadows.prepare()
+            if hasattr(optimizer, "fused_zero_grad") and type(optimizer).__name__ != "Synchronous":
+                optimizer.zero_grad()                 # start from clean gradients, then let the update kernel keep them clean
+                optimizer.fused_zero_grad = True
             if use_graph:
                 self._capture(warmup_iters)
 

@@ -114,10 +114,10 @@ def scale_rows(x: torch.Tensor, scale: torch.Tensor, rows, C, ld) -> None:
 
 
 def sgd_flat(params: torch.Tensor, grads: torch.Tensor, acc, mom, n: int, lr_dev: torch.Tensor, mu: float = 0.0, wd: float = 0.0,
-             shadow=None) -> None:
+             shadow=None, zero_grads: bool = False) -> None:
     _call("dmlb_sgd_flat", params.data_ptr(), grads.data_ptr(), acc.data_ptr() if acc is not None else None,
           mom.data_ptr() if mom is not None else None, shadow.data_ptr() if shadow is not None else None, n, lr_dev.data_ptr(), float(mu),
-          float(wd), stream_ptr())
+          float(wd), int(zero_grads), stream_ptr())
 
 
 def refresh_shadows(table: torch.Tensor, n_entries: int) -> None:

@@ -188,7 +188,8 @@ class Asynchronous(ArenaOptimizer):
         self._sync_lr()
         if a.params.is_cuda:
             from ..ops import kernels as K
-            K.sgd_flat(a.params, a.grads, self.accumulated_gradients, None, a.padded, self.lr_dev, 0.0, 0.0, shadow=a.shadow)
+            K.sgd_flat(a.params, a.grads, self.accumulated_gradients, None, a.padded, self.lr_dev, 0.0, 0.0, shadow=a.shadow,
+                       zero_grads=self.fused_zero_grad)
             a.mark_params_changed(flat_done=a.shadow is not None)
         else:
             lr = self.lr

@@ -27,6 +27,9 @@ class ArenaOptimizer(Optimizer):
         self.arena = arena if arena is not None else ensure_arena(model, n_shards=n_shards)
         self.device = self.arena.params.device
         self._lr_cached = None
+        # When True the update kernel clears each gradient as it consumes it, and zero_grad() becomes a no-op
+        # (TrainStep turns this on: one memset node less per step).  After step() the .grad views then read zero.
+        self.fused_zero_grad = False
         self.lr_dev = torch.zeros(1, dtype=torch.float32, device=self.device)
         self._sync_lr()
 
@@ -44,6 +47,8 @@ class ArenaOptimizer(Optimizer):
     # -- gradients -----------------------------------------------------------------------------
     def zero_grad(self, set_to_none: bool = False) -> None:
         """One memset of the gradient arena (gradients stay views, never ``None``)."""
+        if self.fused_zero_grad and self.arena.params.is_cuda:
+            return
         first = next(iter(self.model.parameters()))
         if first.grad is None or first.grad.data_ptr() != self.arena.grads.data_ptr():
             self.arena.rebind_grads()
@@ -73,7 +78,8 @@ class FusedSGD(ArenaOptimizer):
         a = self.arena
         if a.params.is_cuda:
             from ..ops import kernels as K
-            K.sgd_flat(a.params, a.grads, None, self.momentum_buf, a.padded, self.lr_dev, g["momentum"], g["weight_decay"], shadow=a.shadow)
+            K.sgd_flat(a.params, a.grads, None, self.momentum_buf, a.padded, self.lr_dev, g["momentum"], g["weight_decay"], shadow=a.shadow,
+                       zero_grads=self.fused_zero_grad)
             self.refresh_shadows(flat_done=a.shadow is not None)
         else:
             d = a.grads

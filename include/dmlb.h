@@ -88,9 +88,10 @@ int dmlb_softmax_xent(const void* logits, int logits_is_bf16, const long long* l
                       int ldl, int ldd, void* stream);
 int dmlb_scale_rows_bf16(void* x, const float* scale, long long rows, int C, int ld, void* stream);
 /* theta -= lr*g over the flat arena (n % 4 == 0); optional Downpour accumulator acc -= lr*g, momentum buffer,
- * weight decay, and a flat bf16 mirror of theta (same offsets) for the tensor-core GEMMs. */
-int dmlb_sgd_flat(float* params, const float* grads, float* acc, float* mom, void* shadow_bf16, long long n, const float* lr_ptr, float mu,
-                  float wd, void* stream);
+ * weight decay, and a flat bf16 mirror of theta (same offsets) for the tensor-core GEMMs; zero_grads=1 clears the
+ * gradients as they are consumed (replaces the next step's zero_grad memset). */
+int dmlb_sgd_flat(float* params, float* grads, float* acc, float* mom, void* shadow_bf16, long long n, const float* lr_ptr, float mu,
+                  float wd, int zero_grads, void* stream);
 /* table: device array of { int64 src_off, int64 dst_off, int32 rows, cin, khw, ld } — see csrc/train_ops.cu. */
 int dmlb_refresh_shadows(const float* params, void* shadow, const void* table, int n_entries, void* stream);
 int dmlb_cast_f32_bf16(const float* x, void* y, long long rows, int C, long long ldx, int ldy, void* stream);
