@@ -45,6 +45,12 @@ _SIGNATURES = {
     "dmlb_dropout_fwd_bf16": [c_vp, c_vp, c_vp, c_ll, c_int, c_int, c_int, c_int, c_int, c_float, c_ull, c_vp, c_vp],
     "dmlb_dropout_bwd_bf16": [c_vp, c_vp, c_vp, c_ll, c_int, c_int, c_int, c_float, c_vp],
     "dmlb_counter_bump": [c_vp, c_vp],
+    "dmlb_bn_stats": [c_vp, c_int, c_vp, c_ll, c_int, c_vp],
+    "dmlb_bn_apply": [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_ll, c_int, c_float, c_float, c_int, c_vp],
+    "dmlb_bn_bwd_reduce": [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_ll, c_int, c_int, c_vp],
+    "dmlb_bn_bwd_apply": [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_ll, c_int, c_vp],
+    "dmlb_avgpool_fwd_bf16": [c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_vp],
+    "dmlb_avgpool_bwd_bf16": [c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_vp],
 }
 _RESTYPES = {"dmlb_last_error": ctypes.c_char_p, "dmlb_launch_count": c_ll, "dmlb_reset_launch_count": None}
 _OPTIONAL = set()  # entry points that newer libraries add; absent ones are simply not bound

@@ -61,6 +61,7 @@ class TrainStep:
         self.step_count = 0
         self.kernels_per_step = 0       # launches of our kernels inside one captured step
         self._pending: Optional[int] = None
+        self._staging = None
         self._local = getattr(optimizer, "step_local", None) or optimizer.step
         self._communicate = getattr(optimizer, "communicate", None)
         if self.device.type == "cuda":
@@ -135,9 +136,29 @@ class TrainStep:
         if hasattr(self.optimizer, "_sync_lr"):
             self.optimizer._sync_lr()
         slot = self.step_count & 1
+        if not x.is_cuda:
+            # Host batch: the PCIe copy runs on its own stream into a double-buffered staging area, so it overlaps the
+            # previous step's graph replay; the step itself only does a device-to-device move into the static input.
+            if self._staging is None:
+                self._staging = [(torch.empty_like(self.static_x), torch.empty_like(self.static_y)) for _ in range(2)]
+                self._copy_stream = torch.cuda.Stream(device=self.device)
+                self._staged = [torch.cuda.Event() for _ in range(2)]
+                self._consumed = [torch.cuda.Event() for _ in range(2)]
+                for ev in self._consumed:
+                    ev.record(self.stream)
+            sx, sy = self._staging[slot]
+            self._copy_stream.wait_event(self._consumed[slot])     # the step that last read this slot is past its D2D move
+            with torch.cuda.stream(self._copy_stream):
+                sx.copy_(x, non_blocking=True)
+                sy.copy_(y, non_blocking=True)
+                self._staged[slot].record(self._copy_stream)
+            self.stream.wait_event(self._staged[slot])
+            x, y = sx, sy
         with torch.cuda.stream(self.stream):
             self.static_x.copy_(x, non_blocking=True)
             self.static_y.copy_(y, non_blocking=True)
+            if self._staging is not None and x is self._staging[slot][0]:
+                self._consumed[slot].record(self.stream)
             if self.graph is not None:
                 self.graph.replay()
             else:

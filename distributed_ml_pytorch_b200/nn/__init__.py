@@ -1,4 +1,5 @@
 """Kernel-backed ``nn.Module`` layers (see :mod:`.layers`)."""
-from .layers import (Conv2d, Dropout, Dropout2d, Flatten, Linear, MaxPool2d, ReLU, ShadowSet, attach_shadows)
+from .layers import (BatchNorm2d, Conv2d, Dropout, Dropout2d, Flatten, GlobalAvgPool, Linear, MaxPool2d, ReLU, ShadowSet, attach_shadows)
 
-__all__ = ["Conv2d", "Linear", "ReLU", "MaxPool2d", "Dropout", "Dropout2d", "Flatten", "ShadowSet", "attach_shadows"]
+__all__ = ["Conv2d", "Linear", "ReLU", "MaxPool2d", "Dropout", "Dropout2d", "Flatten", "BatchNorm2d", "GlobalAvgPool", "ShadowSet",
+           "attach_shadows"]

@@ -305,3 +305,33 @@ class Dropout2d(nn.Module):
 class Flatten(nn.Module):
     def forward(self, x):
         return OF.flatten(x)
+
+
+class BatchNorm2d(nn.Module):
+    """``torch.nn.BatchNorm2d``-compatible parameters/buffers (``weight``, ``bias``, ``running_mean``, ``running_var``,
+    ``num_batches_tracked``) with optional fused residual add and ReLU: ``forward(x, residual=None)``."""
+
+    def __init__(self, num_features: int, eps: float = 1e-5, momentum: float = 0.1, activation=None):
+        super().__init__()
+        self.num_features, self.eps, self.momentum, self.activation = num_features, eps, momentum, activation
+        self.weight = nn.Parameter(torch.ones(num_features))
+        self.bias = nn.Parameter(torch.zeros(num_features))
+        self.register_buffer("running_mean", torch.zeros(num_features))
+        self.register_buffer("running_var", torch.ones(num_features))
+        self.register_buffer("num_batches_tracked", torch.tensor(0, dtype=torch.long))
+        self._wsink = None
+        self._bsink = None
+        self._arena_slot = None
+
+    def forward(self, x, residual=None):
+        # num_batches_tracked is bookkeeping only (momentum is fixed); it is not bumped on the CUDA-graph path
+        return OF.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var, self.training, self.momentum, self.eps,
+                             residual=residual, relu=self.activation == "relu", wsink=self._wsink, bsink=self._bsink)
+
+    def extra_repr(self):
+        return f"{self.num_features}, eps={self.eps}, momentum={self.momentum}, activation={self.activation}"
+
+
+class GlobalAvgPool(nn.Module):
+    def forward(self, x):
+        return OF.global_avg_pool(x)

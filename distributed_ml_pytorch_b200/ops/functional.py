@@ -557,6 +557,120 @@ def dropout(x, p=0.5, training=True, channel_mode=False, seed=0x5EED):
 
 
 # ------------------------------------------------------------------------------------------------
+# batch norm (+ residual add + ReLU) and global average pooling  (NORTH-STAR ResNets)
+# ------------------------------------------------------------------------------------------------
+class _BatchNormFn(torch.autograd.Function):
+    """Training-mode BatchNorm2d with the residual add and ReLU of a ResNet block folded into the same two passes."""
+
+    @staticmethod
+    def forward(ctx, x, residual, weight, bias, cfg):
+        x, ldx = as_act4(x)
+        B, C, H, W = x.shape
+        M = B * H * W
+        dev = x.device
+        res_ptr, ldr = 0, 0
+        if residual is not None:
+            residual, ldr = as_act4(residual)
+            res_ptr = residual.data_ptr()
+        y = new_act4(B, C, H, W, dev)
+        sums = torch.zeros(2 * C, dtype=torch.float32, device=dev)
+        save = torch.empty(2 * C, dtype=torch.float32, device=dev)
+        K.bn_stats(x.data_ptr(), ldx, sums, M, C)
+        K.bn_apply(x.data_ptr(), ldx, y.data_ptr(), pad8(C), res_ptr, ldr, sums, None, weight, bias, save, cfg.running_mean, cfg.running_var, M, C,
+                   cfg.eps, cfg.momentum, cfg.relu)
+        ctx.cfg = cfg
+        ctx.dims = (B, C, H, W, ldx)
+        ctx.has_res = residual is not None
+        ctx.save_for_backward(x, y if cfg.relu else None, weight, bias, save)
+        return y
+
+    @staticmethod
+    def backward(ctx, dout):
+        cfg = ctx.cfg
+        x, y, weight, bias, save = ctx.saved_tensors
+        B, C, H, W, ldx = ctx.dims
+        M = B * H * W
+        dev = dout.device
+        dout, ldd = as_act4(dout)
+        ldc = pad8(C)
+        dsum = torch.zeros(2 * C, dtype=torch.float32, device=dev)
+        need_g = cfg.relu or ctx.has_res
+        g = new_act4(B, C, H, W, dev) if need_g else dout
+        K.bn_bwd_reduce(x.data_ptr(), ldx, dout.data_ptr(), ldd, y.data_ptr() if y is not None else 0, ldc, g.data_ptr() if need_g else 0, ldc,
+                        save, dsum, M, C, cfg.relu)
+        ldg = ldc if need_g else ldd
+        wsink = cfg.wsink if (weight is not None and _sink_ok(weight, cfg.wsink)) else None
+        bsink = cfg.bsink if (bias is not None and _sink_ok(bias, cfg.bsink)) else None
+        gw = torch.zeros(C, dtype=torch.float32, device=dev) if (weight is not None and wsink is None) else None
+        gb = torch.zeros(C, dtype=torch.float32, device=dev) if (bias is not None and bsink is None) else None
+        dx = new_act4(B, C, H, W, dev)
+        K.bn_bwd_apply(x.data_ptr(), ldx, g.data_ptr(), ldg, dx.data_ptr(), ldc, save, weight, dsum, wsink if wsink is not None else gw,
+                       bsink if bsink is not None else gb, M, C)
+        return dx, (g if ctx.has_res else None), gw, gb, None
+
+
+class _BatchNormEvalFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, residual, weight, bias, cfg):
+        x, ldx = as_act4(x)
+        B, C, H, W = x.shape
+        res_ptr, ldr = 0, 0
+        if residual is not None:
+            residual, ldr = as_act4(residual)
+            res_ptr = residual.data_ptr()
+        y = new_act4(B, C, H, W, x.device)
+        stats = torch.cat([cfg.running_mean, torch.rsqrt(cfg.running_var + cfg.eps)]).float()
+        K.bn_apply(x.data_ptr(), ldx, y.data_ptr(), pad8(C), res_ptr, ldr, None, stats, weight, bias, None, None, None, B * H * W, C, cfg.eps, 0.0,
+                   cfg.relu)
+        return y
+
+    @staticmethod
+    def backward(ctx, dout):
+        raise RuntimeError("backward through inference-mode batch norm is not implemented on the CUDA path")
+
+
+def batch_norm(x, weight, bias, running_mean, running_var, training=True, momentum=0.1, eps=1e-5, residual=None, relu=False, wsink=None,
+               bsink=None):
+    """``relu(batch_norm(x) + residual)`` (residual / ReLU optional) in two kernels forward, two backward."""
+    if not x.is_cuda or x.shape[1] % 8 != 0 or x.shape[1] > 2048:
+        y = F.batch_norm(x.float() if x.is_cuda else x, running_mean, running_var, weight, bias, training, momentum, eps)
+        if residual is not None:
+            y = y + residual
+        y = F.relu(y) if relu else y
+        return y.to(x.dtype) if x.is_cuda else y
+    cfg = SimpleNamespace(running_mean=running_mean, running_var=running_var, eps=eps, momentum=momentum, relu=bool(relu), wsink=wsink, bsink=bsink)
+    if training:
+        return _BatchNormFn.apply(x, residual, weight, bias, cfg)
+    return _BatchNormEvalFn.apply(x, residual, weight, bias, cfg)
+
+
+class _AvgPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x, ldx = as_act4(x)
+        B, C, H, W = x.shape
+        y = new_act2(B, C, x.device)
+        K.avgpool_fwd(x.data_ptr(), ldx, y.data_ptr(), pad8(C), B, H * W, C)
+        ctx.dims = (B, C, H, W)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        B, C, H, W = ctx.dims
+        dy, ldd = as_act2(dy)
+        dx = new_act4(B, C, H, W, dy.device)
+        K.avgpool_bwd(dy.data_ptr(), ldd, dx.data_ptr(), pad8(C), B, H * W, C)
+        return dx
+
+
+def global_avg_pool(x):
+    """``adaptive_avg_pool2d(x, 1).flatten(1)``: [B, C, H, W] -> [B, C]."""
+    if not x.is_cuda or x.shape[1] % 8 != 0:
+        return x.float().mean(dim=(2, 3)).to(x.dtype)
+    return _AvgPoolFn.apply(x)
+
+
+# ------------------------------------------------------------------------------------------------
 # softmax cross-entropy (forward + backward in one kernel)
 # ------------------------------------------------------------------------------------------------
 class _XentFn(torch.autograd.Function):

@@ -144,3 +144,35 @@ def dropout_bwd(dy_ptr, mask: torch.Tensor, dx_ptr, rows, C, lddy, lddx, p) -> N
 
 def counter_bump(counter: torch.Tensor) -> None:
     _call("dmlb_counter_bump", counter.data_ptr(), stream_ptr())
+
+
+def _p(t):
+    return t.data_ptr() if t is not None else None
+
+
+def bn_stats(x_ptr, ldx, sums: torch.Tensor, M, C) -> None:
+    _call("dmlb_bn_stats", x_ptr, ldx, sums.data_ptr(), M, C, stream_ptr())
+
+
+def bn_apply(x_ptr, ldx, y_ptr, ldy, res_ptr, ldr, sums, mean_rstd_in, gamma, beta, save, running_mean, running_var, M, C, eps, momentum,
+             relu) -> None:
+    _call("dmlb_bn_apply", x_ptr, ldx, y_ptr, ldy, res_ptr or None, ldr, _p(sums), _p(mean_rstd_in), _p(gamma), _p(beta), _p(save),
+          _p(running_mean), _p(running_var), M, C, float(eps), float(momentum), int(relu), stream_ptr())
+
+
+def bn_bwd_reduce(x_ptr, ldx, dy_ptr, lddy, yact_ptr, ldya, g_ptr, ldg, mean_rstd, dsum, M, C, relu) -> None:
+    _call("dmlb_bn_bwd_reduce", x_ptr, ldx, dy_ptr, lddy, yact_ptr or None, ldya, g_ptr or None, ldg, mean_rstd.data_ptr(), dsum.data_ptr(), M, C,
+          int(relu), stream_ptr())
+
+
+def bn_bwd_apply(x_ptr, ldx, g_ptr, ldg, dx_ptr, lddx, mean_rstd, gamma, dsum, dgamma, dbeta, M, C) -> None:
+    _call("dmlb_bn_bwd_apply", x_ptr, ldx, g_ptr, ldg, dx_ptr, lddx, mean_rstd.data_ptr(), _p(gamma), dsum.data_ptr(), _p(dgamma), _p(dbeta), M, C,
+          stream_ptr())
+
+
+def avgpool_fwd(x_ptr, ldx, y_ptr, ldy, B, P, C) -> None:
+    _call("dmlb_avgpool_fwd_bf16", x_ptr, ldx, y_ptr, ldy, B, P, C, stream_ptr())
+
+
+def avgpool_bwd(dy_ptr, lddy, dx_ptr, lddx, B, P, C) -> None:
+    _call("dmlb_avgpool_bwd_bf16", dy_ptr, lddy, dx_ptr, lddx, B, P, C, stream_ptr())

@@ -101,6 +101,21 @@ int dmlb_dropout_fwd_bf16(const void* x, void* y, void* mask, long long rows, in
 int dmlb_dropout_bwd_bf16(const void* dy, const void* mask, void* dx, long long rows, int C, int lddy, int lddx, float p, void* stream);
 int dmlb_counter_bump(void* counter, void* stream);
 
+/* ---- batch norm / residual / global average pool (NORTH-STAR ResNets; csrc/norm_ops.cu) ----
+ * bf16 channels-last rows [M, ld]; C % 8 == 0, C <= 2048.  sums / dsum are fp32 [2C] and must be zero on entry. */
+int dmlb_bn_stats(const void* x, int ldx, float* sums, long long M, int C, void* stream);
+/* y = act((x - mean) * rstd * gamma + beta [+ res]); training: statistics from `sums` (saved to save_mean_rstd [2C], folded
+ * into running_mean / running_var); inference: sums = NULL and mean_rstd_in = {running_mean, 1/sqrt(running_var + eps)}. */
+int dmlb_bn_apply(const void* x, int ldx, void* y, int ldy, const void* res, int ldr, const float* sums, const float* mean_rstd_in,
+                  const float* gamma, const float* beta, float* save_mean_rstd, float* running_mean, float* running_var, long long M, int C,
+                  float eps, float momentum, int relu, void* stream);
+int dmlb_bn_bwd_reduce(const void* x, int ldx, const void* dy, int lddy, const void* yact, int ldya, void* g_out, int ldg,
+                       const float* mean_rstd, float* dsum, long long M, int C, int relu, void* stream);
+int dmlb_bn_bwd_apply(const void* x, int ldx, const void* g, int ldg, void* dx, int lddx, const float* mean_rstd, const float* gamma,
+                      const float* dsum, float* dgamma, float* dbeta, long long M, int C, void* stream);
+int dmlb_avgpool_fwd_bf16(const void* x, int ldx, void* y, int ldy, int B, int P, int C, void* stream);
+int dmlb_avgpool_bwd_bf16(const void* dy, int lddy, void* dx, int lddx, int B, int P, int C, void* stream);
+
 /* ---- peer memory (reference transport: dist.init_process_group('gloo') + isend/recv, example/main.py:165) ---- */
 int dmlb_peer_alloc(size_t bytes, void** out);            /* zeroed cudaMalloc, shareable with CUDA IPC */
 int dmlb_peer_free(void* p);
