@@ -1,0 +1,138 @@
+#!/usr/bin/env python
+"""Bandwidth sweep of the fused NVLink kernels against NCCL (BASELINE.json config 5: 1 KB - 1 GB at 2/4/8 GPUs).
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tools/comm_sweep.py [--max-mb 1024]
+
+Per message size (fp32 elements, whole vector = one "model"):
+  push   dmlb_push_add        every GPU adds its N-vector into the sharded masters (red.add.v4 over NVLink)
+  pull   dmlb_pull            every GPU reads the N-vector back from the shard owners (peer loads)
+  sync   dmlb_sync_rs_update_ag   barrier + reduce-scatter + SGD + all-gather + barrier, one kernel
+  nccl   all_reduce + flat axpy   the baseline formulation of the synchronous step
+  p2p    NCCL send/recv rank0 -> rank1 (the reference's pytorch_p2p_ex.py pattern)
+All times are CUDA-event device times, max over ranks.  "wire" = bytes each GPU must move over NVLink in one
+direction: N*4*(W-1)/W for push, pull and each half of sync; roofline = wire / 770 GB/s (measured peer copy).
+Writes one JSON line per size (rank 0) and, with --out, a JSON file.
+"""
+import argparse
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import torch
+import torch.distributed as dist
+
+from distributed_ml_pytorch_b200.parallel import peer
+
+LINK_GBS = 770.0
+
+
+def timed(fn, iters, pre=None):
+    e0 = [torch.cuda.Event(enable_timing=True) for _ in range(iters)]
+    e1 = [torch.cuda.Event(enable_timing=True) for _ in range(iters)]
+    for i in range(iters):
+        if pre is not None:
+            pre()
+        e0[i].record()
+        fn()
+        e1[i].record()
+    torch.cuda.synchronize()
+    ts = sorted(a.elapsed_time(b) for a, b in zip(e0, e1))
+    return ts[len(ts) // 2]
+
+
+def max_ranks(ms, dev):
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--max-mb", type=int, default=1024)
+    ap.add_argument("--out", default=None)
+    a = ap.parse_args()
+    rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    pg = peer.PeerGroup(device=dev)
+    chunk = peer.chunk_elems()
+    lr = torch.tensor([0.01], device=dev)
+    rows = []
+    nbytes = 1 << 10
+    while nbytes <= a.max_mb << 20:
+        n = max(nbytes // 4, 4)
+        shard = ((n + world - 1) // world + chunk - 1) // chunk * chunk
+        padded = shard * world
+        master = pg.symmetric(shard * 4)
+        params_s = pg.symmetric(padded * 4)
+        grads_s = pg.symmetric(padded * 4)
+        flags = pg.symmetric(peer.flag_words() * 4)
+        acc = torch.ones(padded, device=dev)
+        params = params_s.view(torch.float32, padded)
+        grads = grads_s.view(torch.float32, padded)
+        grads.fill_(1.0)
+        nccl_buf = torch.ones(n, device=dev)
+        nccl_p = torch.zeros(n, device=dev)
+        iters = 20 if nbytes <= (64 << 20) else 6
+        pg.barrier()
+        # warm-up
+        for _ in range(3):
+            peer.push_add(acc, master.table, world, shard, padded)
+            peer.pull(params, master.table, world, shard, padded)
+            peer.sync_rs_update_ag(grads_s.table, params_s.table, flags.table, None, rank, world, shard, lr, 0.0, 0.0, 1.0 / world)
+            dist.all_reduce(nccl_buf)
+        pg.barrier()
+        t_push = max_ranks(timed(lambda: peer.push_add(acc, master.table, world, shard, padded), iters, pre=lambda: acc.fill_(1.0)), dev)
+        pg.barrier()
+        t_pull = max_ranks(timed(lambda: peer.pull(params, master.table, world, shard, padded), iters), dev)
+        pg.barrier()
+        t_sync = max_ranks(timed(lambda: peer.sync_rs_update_ag(grads_s.table, params_s.table, flags.table, None, rank, world, shard, lr, 0.0, 0.0,
+                                                                1.0 / world), iters), dev)
+        pg.barrier()
+
+        def nccl_step():
+            dist.all_reduce(nccl_buf)
+            nccl_p.add_(nccl_buf, alpha=-0.01 / world)
+        t_nccl = max_ranks(timed(nccl_step, iters), dev)
+        t_p2p = None
+        if world >= 2:
+            t = torch.empty(max(nbytes, 4), dtype=torch.uint8, device=dev)
+            if rank < 2:
+                def p2p():
+                    dist.send(t, dst=1) if rank == 0 else dist.recv(t, src=0)
+                for _ in range(2):
+                    p2p()
+                ms = timed(p2p, iters)
+            else:
+                ms = 0.0
+            t_p2p = max_ranks(ms, dev)
+        wire = n * 4 * (world - 1) / world
+        row = {"bytes": n * 4, "world": world,
+               "push_us": t_push * 1e3, "pull_us": t_pull * 1e3, "sync_us": t_sync * 1e3, "nccl_allreduce_sgd_us": t_nccl * 1e3,
+               "p2p_us": (t_p2p * 1e3 if t_p2p is not None else None),
+               "push_gbs": wire / (t_push * 1e-3) / 1e9 if world > 1 else n * 4 / (t_push * 1e-3) / 1e9,
+               "pull_gbs": wire / (t_pull * 1e-3) / 1e9 if world > 1 else n * 4 / (t_pull * 1e-3) / 1e9,
+               "sync_gbs_per_dir": wire / (t_sync * 1e-3) / 1e9 if world > 1 else None,
+               "p2p_gbs": (max(nbytes, 4) / (t_p2p * 1e-3) / 1e9 if t_p2p else None),
+               "push_frac_of_link": (wire / (t_push * 1e-3) / 1e9 / LINK_GBS if world > 1 else None),
+               "pull_frac_of_link": (wire / (t_pull * 1e-3) / 1e9 / LINK_GBS if world > 1 else None),
+               "sync_vs_nccl_speedup": t_nccl / t_sync}
+        rows.append(row)
+        if rank == 0:
+            print(json.dumps(row), flush=True)
+        del acc, params, grads, nccl_buf, nccl_p
+        pg.close()
+        pg = peer.PeerGroup(device=dev)
+        nbytes *= 4
+    if rank == 0 and a.out:
+        os.makedirs(os.path.dirname(os.path.abspath(a.out)), exist_ok=True)
+        with open(a.out, "w") as f:
+            json.dump(rows, f, indent=1)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
