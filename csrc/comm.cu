@@ -41,15 +41,35 @@ __global__ void __launch_bounds__(256) push_add_kernel(float* __restrict__ acc, 
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) pull_kernel(float* __restrict__ params, PeerTable masters, PeerTable versions,
                                                    uint32_t* __restrict__ pulled_ver, long long shard_size, long long n4, int chunks_per_shard) {
-    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
-        const long long e = i * 4;
-        const int owner = static_cast<int>(e / shard_size);
-        const long long off = e - owner * shard_size;
-        const float* src = static_cast<const float*>(masters.ptr[owner]) + off;
-        reinterpret_cast<float4*>(params)[i] = ld_volatile_f32x4(src);
-        if (pulled_ver != nullptr && (off % kChunk) == 0) {
-            const int lc = static_cast<int>(off / kChunk);
-            pulled_ver[owner * chunks_per_shard + lc] = ld_relaxed_sys_u32(static_cast<const uint32_t*>(versions.ptr[owner]) + lc);
+    // Peer loads cost an NVLink round trip (~2 us): keep kUnroll independent 16-byte loads in flight per thread.
+    constexpr int kUnroll = 8;
+    const long long stride = 1ll * gridDim.x * blockDim.x;
+    for (long long i0 = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i0 < n4; i0 += stride * kUnroll) {
+        float4 v[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const long long i = i0 + u * stride;
+            if (i < n4) {
+                const long long e = i * 4;
+                const int owner = static_cast<int>(e / shard_size);
+                v[u] = ld_volatile_f32x4(static_cast<const float*>(masters.ptr[owner]) + (e - owner * shard_size));
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const long long i = i0 + u * stride;
+            if (i < n4) {
+                reinterpret_cast<float4*>(params)[i] = v[u];
+                if (pulled_ver != nullptr) {
+                    const long long e = i * 4;
+                    const int owner = static_cast<int>(e / shard_size);
+                    const long long off = e - owner * shard_size;
+                    if ((off % kChunk) == 0) {
+                        const int lc = static_cast<int>(off / kChunk);
+                        pulled_ver[owner * chunks_per_shard + lc] = ld_relaxed_sys_u32(static_cast<const uint32_t*>(versions.ptr[owner]) + lc);
+                    }
+                }
+            }
         }
     }
 }
@@ -183,11 +203,13 @@ __global__ void __launch_bounds__(512) sync_rs_update_ag_kernel(PeerTable grads,
     const long long n4 = shard_size / 4;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
         float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 4
-        for (int r = 0; r < world; ++r) {
-            const float4 v = ld_volatile_f32x4(static_cast<const float*>(grads.ptr[r]) + base + 4 * i);
-            g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
-        }
+        float4 v[kMaxPeers];
+#pragma unroll
+        for (int r = 0; r < kMaxPeers; ++r)   // issue every peer's load before consuming any: one NVLink round trip, not `world`
+            if (r < world) v[r] = ld_volatile_f32x4(static_cast<const float*>(grads.ptr[r]) + base + 4 * i);
+#pragma unroll
+        for (int r = 0; r < kMaxPeers; ++r)
+            if (r < world) { g.x += v[r].x; g.y += v[r].y; g.z += v[r].z; g.w += v[r].w; }
         g.x *= grad_scale; g.y *= grad_scale; g.z *= grad_scale; g.w *= grad_scale;
         float4 p = reinterpret_cast<const float4*>(static_cast<const float*>(params.ptr[rank]) + base)[i];
         if (wd != 0.f) { g.x += wd * p.x; g.y += wd * p.y; g.z += wd * p.z; g.w += wd * p.w; }

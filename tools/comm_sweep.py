@@ -29,17 +29,24 @@ LINK_GBS = 770.0
 
 
 def timed(fn, iters, pre=None):
-    e0 = [torch.cuda.Event(enable_timing=True) for _ in range(iters)]
-    e1 = [torch.cuda.Event(enable_timing=True) for _ in range(iters)]
-    for i in range(iters):
-        if pre is not None:
-            pre()
-        e0[i].record()
+    """Device time per call: `iters` back-to-back launches between one pair of events (so the host's launch latency is
+    hidden behind queued work); `pre` (e.g. refilling the accumulator) is timed separately and subtracted."""
+    def loop(body):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(iters):
+            body()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters
+    if pre is None:
+        return loop(fn)
+
+    def both():
+        pre()
         fn()
-        e1[i].record()
-    torch.cuda.synchronize()
-    ts = sorted(a.elapsed_time(b) for a, b in zip(e0, e1))
-    return ts[len(ts) // 2]
+    return max(loop(both) - loop(pre), 1e-4)
 
 
 def max_ranks(ms, dev):
