@@ -113,7 +113,9 @@ def dump_sass() -> None:
                     compact.append("    " + parts[1].split("/*")[0].strip())
         (out / (obj.stem + ".sass")).write_text("\n".join(compact) + "\n")
         text = res.stdout
-        row = {k: text.count(k) for k in ("UTCHMMA", "UTCBAR", "LDTM", "UTMALDG", "UTMASTG", "UBLKCP", "SYNCS", "REDG", "HMMA", "LDGSTS")}
+        import re
+        row = {k: text.count(k) for k in ("UTCHMMA", "UTCBAR", "LDTM", "UTMALDG", "UTMASTG", "UBLKCP", "SYNCS", "REDG", "LDGSTS")}
+        row["HMMA(legacy mma.sync)"] = len(re.findall(r"(?<![A-Z])HMMA", text))
         census.append(f"{obj.stem:24s} " + " ".join(f"{k}={v}" for k, v in row.items()))
     (out / "CENSUS.txt").write_text("\n".join(census) + "\n")
 

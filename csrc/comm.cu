@@ -37,10 +37,11 @@ __global__ void __launch_bounds__(256) push_add_kernel(float* __restrict__ acc, 
 }
 
 // ---------------------------------------------------------------------------------------------
-// K3  pull: params[i] = master[owner(i)][i]  (+ optional version snapshot for staleness accounting)
+// K3  pull: params[i] = master[owner(i)][i], shadow[i] = bf16(params[i])  (+ optional version snapshot for staleness)
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) pull_kernel(float* __restrict__ params, PeerTable masters, PeerTable versions,
-                                                   uint32_t* __restrict__ pulled_ver, long long shard_size, long long n4, int chunks_per_shard) {
+__global__ void __launch_bounds__(256) pull_kernel(float* __restrict__ params, __nv_bfloat16* __restrict__ shadow, PeerTable masters,
+                                                   PeerTable versions, uint32_t* __restrict__ pulled_ver, long long shard_size, long long n4,
+                                                   int chunks_per_shard) {
     // Peer loads cost an NVLink round trip (~2 us): keep kUnroll independent 16-byte loads in flight per thread.
     constexpr int kUnroll = 8;
     const long long stride = 1ll * gridDim.x * blockDim.x;
@@ -60,6 +61,12 @@ __global__ void __launch_bounds__(256) pull_kernel(float* __restrict__ params, P
             const long long i = i0 + u * stride;
             if (i < n4) {
                 reinterpret_cast<float4*>(params)[i] = v[u];
+                if (shadow != nullptr) {   // fused cast into the worker's bf16 tensor-core weights (same flat offsets)
+                    uint2 h;
+                    h.x = pack_bf16x2(v[u].x, v[u].y);
+                    h.y = pack_bf16x2(v[u].z, v[u].w);
+                    reinterpret_cast<uint2*>(shadow)[i] = h;
+                }
                 if (pulled_ver != nullptr) {
                     const long long e = i * 4;
                     const int owner = static_cast<int>(e / shard_size);
@@ -277,7 +284,7 @@ extern "C" int dmlb_push_add(float* acc, void* const* master_ptrs, int world, lo
     return 0;
 }
 
-extern "C" int dmlb_pull(float* params, void* const* master_ptrs, void* const* version_ptrs, void* pulled_ver, int world,
+extern "C" int dmlb_pull(float* params, void* shadow_bf16, void* const* master_ptrs, void* const* version_ptrs, void* pulled_ver, int world,
                          long long shard_size, long long n, void* stream) {
     DMLB_REQUIRE(n % 4 == 0 && shard_size % kChunk == 0, "shard size must be a multiple of the chunk size");
     PeerTable t, v;
@@ -288,7 +295,8 @@ extern "C" int dmlb_pull(float* params, void* const* master_ptrs, void* const* v
         for (int i = 0; i < kMaxPeers; ++i) v.ptr[i] = nullptr;
         pulled_ver = nullptr;
     }
-    pull_kernel<<<comm_grid(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(params, t, v, static_cast<uint32_t*>(pulled_ver), shard_size,
+    pull_kernel<<<comm_grid(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(params, static_cast<__nv_bfloat16*>(shadow_bf16), t, v,
+                                                                                     static_cast<uint32_t*>(pulled_ver), shard_size,
                                                                                      n / 4, static_cast<int>(shard_size / kChunk));
     DMLB_LAUNCH_CHECK();
     return 0;

@@ -167,8 +167,9 @@ class Asynchronous(ArenaOptimizer):
     def _pull(self) -> None:
         from . import peer
         pg, a = self.peer, self.arena
-        peer.pull(a.params, self.master_sym.table, pg.world, a.shards.shard_size, a.padded, self.version_sym.table, self.pulled_ver)
-        a.mark_params_changed()
+        peer.pull(a.params, self.master_sym.table, pg.world, a.shards.shard_size, a.padded, self.version_sym.table, self.pulled_ver,
+                  shadow=a.shadow)
+        a.mark_params_changed(flat_done=a.shadow is not None)
         self.pulls += 1
 
     # ------------------------------------------------------------------------------------------

@@ -30,7 +30,7 @@ _native.register("dmlb_enable_peer_access", [c_int])
 _native.register("dmlb_comm_chunk_elems", [])
 _native.register("dmlb_comm_flag_words", [])
 _native.register("dmlb_push_add", [c_vp, _PP, c_int, c_ll, c_ll, c_vp])
-_native.register("dmlb_pull", [c_vp, _PP, _PP, c_vp, c_int, c_ll, c_ll, c_vp])
+_native.register("dmlb_pull", [c_vp, c_vp, _PP, _PP, c_vp, c_int, c_ll, c_ll, c_vp])
 _native.register("dmlb_push_mailbox", [c_vp, c_vp, c_vp, _PP, _PP, c_int, c_int, c_ll, c_vp])
 _native.register("dmlb_owner_apply", [c_vp, c_vp, c_vp, c_vp, c_vp, _PP, c_vp, c_int, c_int, c_ll, c_float, c_int, c_float, c_vp])
 _native.register("dmlb_sync_rs_update_ag", [_PP, _PP, _PP, c_vp, c_int, c_int, c_ll, c_vp, c_float, c_float, c_float, c_vp])
@@ -152,8 +152,9 @@ def push_add(acc: torch.Tensor, master_table, world: int, shard_size: int, n: in
     _native.call("dmlb_push_add", acc.data_ptr(), master_table, world, shard_size, n, _stream())
 
 
-def pull(params: torch.Tensor, master_table, world: int, shard_size: int, n: int, version_table=None, pulled_ver: Optional[torch.Tensor] = None) -> None:
-    _native.call("dmlb_pull", params.data_ptr(), master_table, version_table, pulled_ver.data_ptr() if pulled_ver is not None else None, world,
+def pull(params: torch.Tensor, master_table, world: int, shard_size: int, n: int, version_table=None, pulled_ver: Optional[torch.Tensor] = None,
+         shadow: Optional[torch.Tensor] = None) -> None:
+    _native.call("dmlb_pull", params.data_ptr(), shadow.data_ptr() if shadow is not None else None, master_table, version_table, pulled_ver.data_ptr() if pulled_ver is not None else None, world,
                  shard_size, n, _stream())
 
 

@@ -130,9 +130,10 @@ int dmlb_comm_chunk_elems(void);                          /* mailbox chunk (shar
 int dmlb_comm_flag_words(void);                           /* uint32 words of the per-GPU flag block of the sync kernel */
 /* K1 (Asynchronous.py:55,58-60 + server add): master[owner][i] += acc[i]; acc[i] = 0 — vector red.add over NVLink. */
 int dmlb_push_add(float* acc, void* const* master_ptrs, int world, long long shard_size, long long n, void* stream);
-/* K3 (Asynchronous.py:17-18,48-49): params[i] = master[owner][i]; optional per-chunk version snapshot. */
-int dmlb_pull(float* params, void* const* master_ptrs, void* const* version_ptrs, void* pulled_ver, int world, long long shard_size,
-              long long n, void* stream);
+/* K3 (Asynchronous.py:17-18,48-49): params[i] = master[owner][i] by peer loads, fused with the cast into the worker's flat bf16
+ * weight mirror (shadow_bf16, may be NULL); optional per-chunk version snapshot. */
+int dmlb_pull(float* params, void* shadow_bf16, void* const* master_ptrs, void* const* version_ptrs, void* pulled_ver, int world,
+              long long shard_size, long long n, void* stream);
 /* K2 (NORTH-STAR momentum / staleness): chunked mailbox push and owner-side apply. */
 int dmlb_push_mailbox(float* acc, void* busy, const void* pulled_ver, void* const* mailbox_ptrs, void* const* full_ptrs, int rank, int world,
                       long long shard_size, void* stream);
