@@ -46,7 +46,13 @@ def parse():
     ap.add_argument("--batch-size", type=int, default=BATCH, help="per-GPU batch (reference default 64)")
     ap.add_argument("--mode", choices=["async", "sync", "local"], default="async")
     ap.add_argument("--no-graph", action="store_true")
-    return ap.parse_args()
+    ap.add_argument("--input-hw", type=int, default=32, help="image side (32 = CIFAR shape of the headline config; 224 for ResNet-50)")
+    ap.add_argument("--classes", type=int, default=10)
+    ap.add_argument("--momentum", type=float, default=0.0)
+    ap.add_argument("--staleness", default=None)
+    a = ap.parse_args()
+    a.pool_cap_bytes = 2 << 30      # host pool of distinct batches never exceeds 2 GiB
+    return a
 
 
 def dist_env():
@@ -104,17 +110,18 @@ def run_ours(args) -> dict:
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
     torch.manual_seed(1234)  # identical initial replicas on every rank
     B = args.batch_size
-    model = build_model(args.model).to(device)
+    HW, NC = args.input_hw, args.classes
+    model = build_model(args.model, num_classes=NC, input_hw=HW).to(device)
     model.train()
     optimizer, parallelism = make_optimizer(args, model, rank, world, device)
-    ts = TrainStep(model, optimizer, B, (3, 32, 32), device=device, use_graph=not args.no_graph)
+    ts = TrainStep(model, optimizer, B, (3, HW, HW), device=device, use_graph=not args.no_graph)
 
     # rotating input pool larger than L2 (host pinned for e2e, device copy for the device-timed number)
     torch.manual_seed(100 + rank)
-    bytes_per_batch = B * 3 * 32 * 32 * 4 + B * 8
+    bytes_per_batch = B * 3 * HW * HW * 4 + B * 8
     pool = max(8, (L2_BYTES * 5 // 4) // bytes_per_batch + 1)
-    hx = torch.randn(pool, B, 3, 32, 32).pin_memory()
-    hy = torch.randint(0, 10, (pool, B), dtype=torch.int64).pin_memory()
+    hx = torch.randn(pool, B, 3, HW, HW).pin_memory()
+    hy = torch.randint(0, NC, (pool, B), dtype=torch.int64).pin_memory()
     dx, dy = hx.to(device), hy.to(device)
 
     K_, W_ = args.steps, max(args.warmup, 3)
@@ -168,7 +175,7 @@ def run_ours(args) -> dict:
         "ms_per_step": round(dev_ms / K_, 5), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": (round(value / pub, 3) if pub else None), "dtype": "bf16", "data": "synthetic",
         "impl": "ours",
-        "config": {"model": args.model, "global_batch": global_batch, "per_gpu_batch": B, "input": "3x32x32", "seq_len": None,
+        "config": {"model": args.model, "global_batch": global_batch, "per_gpu_batch": B, "input": f"3x{HW}x{HW}", "seq_len": None,
                    "parallelism": parallelism, "lr": LR, "n_push": N_PUSH, "n_pull": N_PULL,
                    "l2_policy": f"inputs rotate through a pool of {pool} distinct batches ({pool * bytes_per_batch >> 20} MiB > 126 MiB L2)",
                    "cuda_graph": ts.graph is not None, "loss_readback": "every step, read one step late (pinned double buffer)"},
@@ -194,8 +201,8 @@ def make_optimizer(args, model, rank, world, device):
     except ImportError:
         return FusedSGD(model.parameters(), lr=LR, model=model), "single-gpu fused SGD"
     if args.mode == "sync":
-        return Synchronous(model.parameters(), lr=LR, model=model), f"sync-dp{world} fused reduce-scatter+update+all-gather"
-    opt = Asynchronous(model.parameters(), lr=LR, n_push=N_PUSH, n_pull=N_PULL, model=model)
+        return Synchronous(model.parameters(), lr=LR, model=model, momentum=args.momentum), f"sync-dp{world} fused reduce-scatter+update+all-gather"
+    opt = Asynchronous(model.parameters(), lr=LR, n_push=N_PUSH, n_pull=N_PULL, model=model, momentum=args.momentum, staleness=args.staleness)
     return opt, f"async-ps dp{world}, parameter server sharded over {world} GPU(s), fused NVLink push/pull"
 
 

@@ -55,25 +55,45 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const __nv_bfloat16* __r
         for (int j = 0; j < 8; ++j) { mu[j] = mean_rstd[tx * 8 + j]; rs[j] = mean_rstd[C + tx * 8 + j]; }
     }
     if (ty < t.lanes) {
-        for (long long r = blockIdx.x * 1ll * t.lanes + ty; r < M; r += 1ll * gridDim.x * t.lanes) {
-            float xv[8];
-            unpack8f(__ldg(reinterpret_cast<const uint4*>(x + r * ldx + tx * 8)), xv);
-            if (mode == 0) {
+        // kU rows per trip, every load issued before the first use: the kernel is a pure stream and lives on loads in flight
+        constexpr int kU = 4;
+        const long long rstride = 1ll * gridDim.x * t.lanes;
+        for (long long r0 = blockIdx.x * 1ll * t.lanes + ty; r0 < M; r0 += rstride * kU) {
+            uint4 rx[kU], rd[kU], ry[kU];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) { s1[j] += xv[j]; s2[j] += xv[j] * xv[j]; }
-            } else {
-                float g[8];
-                unpack8f(__ldg(reinterpret_cast<const uint4*>(dy + r * lddy + tx * 8)), g);
-                if (relu) {
-                    float ya[8];
-                    unpack8f(__ldg(reinterpret_cast<const uint4*>(yact + r * ldya + tx * 8)), ya);
-#pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        if (!(ya[j] > 0.f)) g[j] = 0.f;
+            for (int u = 0; u < kU; ++u) {
+                const long long r = r0 + u * rstride;
+                if (r < M) {
+                    rx[u] = __ldg(reinterpret_cast<const uint4*>(x + r * ldx + tx * 8));
+                    if (mode == 1) {
+                        rd[u] = __ldg(reinterpret_cast<const uint4*>(dy + r * lddy + tx * 8));
+                        if (relu) ry[u] = __ldg(reinterpret_cast<const uint4*>(yact + r * ldya + tx * 8));
+                    }
                 }
-                if (gout != nullptr) *reinterpret_cast<uint4*>(gout + r * ldg + tx * 8) = pack8f(g);
+            }
 #pragma unroll
-                for (int j = 0; j < 8; ++j) { s1[j] += g[j]; s2[j] += g[j] * (xv[j] - mu[j]) * rs[j]; }
+            for (int u = 0; u < kU; ++u) {
+                const long long r = r0 + u * rstride;
+                if (r >= M) continue;
+                float xv[8];
+                unpack8f(rx[u], xv);
+                if (mode == 0) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) { s1[j] += xv[j]; s2[j] += xv[j] * xv[j]; }
+                } else {
+                    float g[8];
+                    unpack8f(rd[u], g);
+                    if (relu) {
+                        float ya[8];
+                        unpack8f(ry[u], ya);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            if (!(ya[j] > 0.f)) g[j] = 0.f;
+                    }
+                    if (gout != nullptr) *reinterpret_cast<uint4*>(gout + r * ldg + tx * 8) = pack8f(g);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) { s1[j] += g[j]; s2[j] += g[j] * (xv[j] - mu[j]) * rs[j]; }
+                }
             }
         }
 #pragma unroll
@@ -126,22 +146,38 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
         sc[j] = g * rstd;
         sh[j] = (beta != nullptr ? beta[c] : 0.f) - mean * g * rstd;
     }
-    for (long long r = blockIdx.x * 1ll * t.lanes + ty; r < M; r += 1ll * gridDim.x * t.lanes) {
-        float v[8];
-        unpack8f(__ldg(reinterpret_cast<const uint4*>(x + r * ldx + tx * 8)), v);
+    constexpr int kU = 4;
+    const long long rstride = 1ll * gridDim.x * t.lanes;
+    for (long long r0 = blockIdx.x * 1ll * t.lanes + ty; r0 < M; r0 += rstride * kU) {
+        uint4 rx[kU], rr[kU];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = v[j] * sc[j] + sh[j];
-        if (res != nullptr) {
-            float q[8];
-            unpack8f(__ldg(reinterpret_cast<const uint4*>(res + r * ldr + tx * 8)), q);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] += q[j];
+        for (int u = 0; u < kU; ++u) {
+            const long long r = r0 + u * rstride;
+            if (r < M) {
+                rx[u] = __ldg(reinterpret_cast<const uint4*>(x + r * ldx + tx * 8));
+                if (res != nullptr) rr[u] = __ldg(reinterpret_cast<const uint4*>(res + r * ldr + tx * 8));
+            }
         }
-        if (relu) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+        for (int u = 0; u < kU; ++u) {
+            const long long r = r0 + u * rstride;
+            if (r >= M) continue;
+            float v[8];
+            unpack8f(rx[u], v);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = v[j] * sc[j] + sh[j];
+            if (res != nullptr) {
+                float q[8];
+                unpack8f(rr[u], q);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] += q[j];
+            }
+            if (relu) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+            }
+            *reinterpret_cast<uint4*>(y + r * ldy + tx * 8) = pack8f(v);
         }
-        *reinterpret_cast<uint4*>(y + r * ldy + tx * 8) = pack8f(v);
     }
 }
 
@@ -169,13 +205,29 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
             if (dbeta != nullptr) dbeta[c] += dsum[c];
         }
     }
-    for (long long r = blockIdx.x * 1ll * t.lanes + ty; r < M; r += 1ll * gridDim.x * t.lanes) {
-        float xv[8], gv[8];
-        unpack8f(__ldg(reinterpret_cast<const uint4*>(x + r * ldx + tx * 8)), xv);
-        unpack8f(__ldg(reinterpret_cast<const uint4*>(g + r * ldg + tx * 8)), gv);
+    constexpr int kU = 4;
+    const long long rstride = 1ll * gridDim.x * t.lanes;
+    for (long long r0 = blockIdx.x * 1ll * t.lanes + ty; r0 < M; r0 += rstride * kU) {
+        uint4 rx[kU], rg[kU];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) gv[j] = k0[j] * (gv[j] - k1[j] - (xv[j] - mu[j]) * rs[j] * k2[j]);
-        *reinterpret_cast<uint4*>(dx + r * lddx + tx * 8) = pack8f(gv);
+        for (int u = 0; u < kU; ++u) {
+            const long long r = r0 + u * rstride;
+            if (r < M) {
+                rx[u] = __ldg(reinterpret_cast<const uint4*>(x + r * ldx + tx * 8));
+                rg[u] = __ldg(reinterpret_cast<const uint4*>(g + r * ldg + tx * 8));
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            const long long r = r0 + u * rstride;
+            if (r >= M) continue;
+            float xv[8], gv[8];
+            unpack8f(rx[u], xv);
+            unpack8f(rg[u], gv);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) gv[j] = k0[j] * (gv[j] - k1[j] - (xv[j] - mu[j]) * rs[j] * k2[j]);
+            *reinterpret_cast<uint4*>(dx + r * lddx + tx * 8) = pack8f(gv);
+        }
     }
 }
 
@@ -221,7 +273,7 @@ __global__ void __launch_bounds__(256) avgpool_bwd_kernel(const __nv_bfloat16* _
 static inline int rows_grid(long long M, int C) {
     const int lanes = 256 / (C / 8);
     long long blocks = (M + lanes - 1) / lanes;
-    const long long cap = 148ll * 4;
+    const long long cap = 148ll * 8;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     return static_cast<int>(blocks);

@@ -33,6 +33,8 @@ _SIGNATURES = {
     "dmlb_im2col_nchw_f32": [c_vp, c_vp] + [c_int] * 11 + [c_vp],
     "dmlb_col2im_nhwc_bf16": [c_vp, c_vp] + [c_int] * 12 + [c_vp],
     "dmlb_maxpool_fwd_bf16": [c_vp, c_vp] + [c_int] * 9 + [c_vp],
+    "dmlb_maxpool_fwd_idx_bf16": [c_vp, c_vp, c_vp] + [c_int] * 9 + [c_vp],
+    "dmlb_maxpool_bwd_idx_bf16": [c_vp, c_vp, c_vp] + [c_int] * 9 + [c_vp],
     "dmlb_act_bwd_bf16": [c_vp, c_vp, c_vp, c_vp] + [c_int] * 11 + [c_vp],
     "dmlb_relu_fwd_bf16": [c_vp, c_vp, c_ll, c_int, c_int, c_int, c_vp],
     "dmlb_relu_bwd_bf16": [c_vp, c_vp, c_vp, c_ll, c_int, c_int, c_int, c_int, c_vp],

@@ -398,27 +398,40 @@ def linear(x, weight, bias=None, relu=False, out_fp32=False, in_map=None, shadow
 # standalone pool / relu / flatten / dropout
 # ------------------------------------------------------------------------------------------------
 class _MaxPoolFn(torch.autograd.Function):
+    """Stand-alone max-pool.  C % 8 == 0: forward stores one arg-max byte per output, backward gathers with it; otherwise the
+    backward recomputes the arg-max from the saved input (generic scalar kernel)."""
+
     @staticmethod
     def forward(ctx, x, k, s, p):
         x, ldx = as_act4(x)
         B, C, H, W = x.shape
         Ho, Wo = (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
         out = new_act4(B, C, Ho, Wo, x.device)
-        K.maxpool_fwd(x.data_ptr(), out.data_ptr(), B, H, W, C, ldx, pad8(C), k, s, p)
-        ctx.args = (k, s, p, ldx)
-        ctx.save_for_backward(x)
+        ctx.args = (k, s, p, ldx, (B, C, H, W))
+        if C % 8 == 0:
+            idx = torch.empty((B, Ho, Wo, C), dtype=torch.uint8, device=x.device)
+            K.maxpool_fwd_idx(x.data_ptr(), out.data_ptr(), idx, B, H, W, C, ldx, pad8(C), k, s, p)
+            ctx.indexed = True
+            ctx.save_for_backward(idx)
+        else:
+            K.maxpool_fwd(x.data_ptr(), out.data_ptr(), B, H, W, C, ldx, pad8(C), k, s, p)
+            ctx.indexed = False
+            ctx.save_for_backward(x)
         return out
 
     @staticmethod
     def backward(ctx, dout):
-        (x,) = ctx.saved_tensors
-        k, s, p, ldx = ctx.args
-        B, C, H, W = x.shape
+        (saved,) = ctx.saved_tensors
+        k, s, p, ldx, (B, C, H, W) = ctx.args
         dout, ldd = as_act4(dout)
-        dx = new_act4(B, C, H, W, x.device)
-        if pad8(C) != ldx:
-            x, ldx = as_act4(x.contiguous())
-        K.act_bwd(x.data_ptr(), dout.data_ptr(), dx.data_ptr(), None, B, H, W, C, ldx, ldd, (k, s, p), False)
+        dx = new_act4(B, C, H, W, dout.device)
+        if ctx.indexed:
+            K.maxpool_bwd_idx(dout.data_ptr(), saved, dx.data_ptr(), B, H, W, C, pad8(C), ldd, k, s, p)
+        else:
+            x = saved
+            if pad8(C) != ldx:
+                x, ldx = as_act4(x.contiguous())
+            K.act_bwd(x.data_ptr(), dout.data_ptr(), dx.data_ptr(), None, B, H, W, C, ldx, ldd, (k, s, p), False)
         return dx, None, None, None
 
 

@@ -90,6 +90,14 @@ def maxpool_fwd(x_ptr: int, y_ptr: int, B, H, W, C, ldx, ldo, k, s, p) -> None:
     _call("dmlb_maxpool_fwd_bf16", x_ptr, y_ptr, B, H, W, C, ldx, ldo, k, s, p, stream_ptr())
 
 
+def maxpool_fwd_idx(x_ptr: int, y_ptr: int, idx: torch.Tensor, B, H, W, C, ldx, ldo, k, s, p) -> None:
+    _call("dmlb_maxpool_fwd_idx_bf16", x_ptr, y_ptr, idx.data_ptr(), B, H, W, C, ldx, ldo, k, s, p, stream_ptr())
+
+
+def maxpool_bwd_idx(dout_ptr: int, idx: torch.Tensor, dx_ptr: int, B, H, W, C, lddx, ldd, k, s, p) -> None:
+    _call("dmlb_maxpool_bwd_idx_bf16", dout_ptr, idx.data_ptr(), dx_ptr, B, H, W, C, lddx, ldd, k, s, p, stream_ptr())
+
+
 def act_bwd(y_ptr: int, dout_ptr: int, dy_ptr: int, dbias, B, H, W, C, ldy, ldd, pool, relu: bool) -> None:
     k, s, p = pool if pool is not None else (1, 1, 0)
     _call("dmlb_act_bwd_bf16", y_ptr, dout_ptr, dy_ptr, dbias.data_ptr() if dbias is not None else None, B, H, W, C, ldy, ldd,

@@ -76,6 +76,10 @@ int dmlb_im2col_nchw_f32(const float* x, void* col, int B, int H, int W, int C, 
 int dmlb_col2im_nhwc_bf16(const void* dcol, void* dx, int B, int H, int W, int C, int ldx, int KH, int KW, int SH, int SW, int PH, int PW,
                           int Kpad, void* stream);
 int dmlb_maxpool_fwd_bf16(const void* x, void* y, int B, int H, int W, int C, int ldx, int ldo, int k, int s, int p, void* stream);
+/* General windows (ResNet stem 3x3/2/1): forward records the arg-max tap per output (uint8 [B,Ho,Wo,C]); backward gathers with it. */
+int dmlb_maxpool_fwd_idx_bf16(const void* x, void* y, void* idx, int B, int H, int W, int C, int ldx, int ldo, int k, int s, int p, void* stream);
+int dmlb_maxpool_bwd_idx_bf16(const void* dout, const void* idx, void* dx, int B, int H, int W, int C, int lddx, int ldd, int k, int s, int p,
+                              void* stream);
 /* Fused (max-pool backward) o (ReLU mask) + bias gradient; see csrc/conv_ops.cu. dbias (fp32 [C], red.add) may be NULL. */
 int dmlb_act_bwd_bf16(const void* y, const void* dout, void* dy, float* dbias, int B, int H, int W, int C, int ldy, int ldd, int has_pool,
                       int k, int s, int p, int relu, void* stream);
