@@ -40,21 +40,26 @@ struct GemmEpilogue {
     int perm_khw;
 };
 
-template <int BN>
+template <int BN, bool kDual>
 struct GemmSmem {
     static constexpr int kABytes = kBM * kBK * 2;  // 16 KiB
     static constexpr int kBBytes = BN * kBK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kStages = (BN <= 64) ? 6 : (BN <= 128 ? 5 : 4);
+    // BN <= 128: stages sized so that two CTAs fit in one SM (~100 KB each): one CTA's epilogue overlaps the other's main loop,
+    // which is what the skinny-N, large-M convolution GEMMs (memory-bound) need.  BN = 256 (large square GEMMs): one CTA, deep ring.
+    // Deep variant (small grids, at most one wave): long ring, one CTA per SM, so every CTA has an SM's L2 port to itself.
+    static constexpr int kStagesDual = (BN <= 32) ? 5 : (BN <= 64 ? 4 : (BN <= 128 ? 3 : 4));
+    static constexpr int kStagesDeep = (BN <= 64) ? 6 : (BN <= 128 ? 5 : 4);
+    static constexpr int kStages = kDual ? kStagesDual : kStagesDeep;
     static constexpr int kBarrierBytes = 256;
     static constexpr int kTotal = kStages * kStageBytes + kBarrierBytes + 1024;  // +1024: manual 1 KiB alignment
 };
 
-template <int BN, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+template <int BN, bool A_MN, bool B_MN, bool kDual>
+__global__ void __launch_bounds__(kGemmThreads, ((kDual && BN <= 128) ? 2 : 1))
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                          GemmEpilogue ep, int M, int N, int K, int kb_per_split) {
-    using S = GemmSmem<BN>;
+    using S = GemmSmem<BN, kDual>;
     constexpr int kStages = S::kStages;
     constexpr int kTmemCols = BN < 32 ? 32 : BN;
     static_assert(BN % 16 == 0 && BN >= 32 && BN <= 256, "UMMA M=128 needs N%16==0, 16<=N<=256");
@@ -275,11 +280,11 @@ static int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t inner, ui
     return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpilogue& ep, int M, int N, int K, int splits,
+template <int BN, bool A_MN, bool B_MN, bool kDual>
+static int launch_gemm_v(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpilogue& ep, int M, int N, int K, int splits,
                        cudaStream_t stream) {
-    using S = GemmSmem<BN>;
-    auto kern = gemm_bf16_tcgen05_kernel<BN, A_MN, B_MN>;
+    using S = GemmSmem<BN, kDual>;
+    auto kern = gemm_bf16_tcgen05_kernel<BN, A_MN, B_MN, kDual>;
     static bool attr_set = false;
     if (!attr_set) {
         DMLB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
@@ -292,6 +297,17 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmE
     DMLB_CHECK_CUDA(launch_k(kern, grid, kGemmThreads, S::kTotal, stream, ta, tb, ep, M, N, K, kb_per));
     DMLB_LAUNCH_CHECK();
     return 0;
+}
+
+// More than one wave of CTAs -> the two-CTAs-per-SM variant (epilogues overlap main loops); otherwise the deep-ring one.
+template <int BN, bool A_MN, bool B_MN>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpilogue& ep, int M, int N, int K, int splits,
+                       cudaStream_t stream) {
+    const int nkb = (K + kBK - 1) / kBK;
+    const int kb_per = (nkb + splits - 1) / splits;
+    const long long ctas = 1ll * ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN) * ((nkb + kb_per - 1) / kb_per);
+    if (BN <= 128 && ctas > dmlb_sm_count()) return launch_gemm_v<BN, A_MN, B_MN, true>(ta, tb, ep, M, N, K, splits, stream);
+    return launch_gemm_v<BN, A_MN, B_MN, false>(ta, tb, ep, M, N, K, splits, stream);
 }
 
 }  // namespace dmlb
