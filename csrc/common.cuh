@@ -113,6 +113,24 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const CUtensorMap
         : "memory");
 }
 
+// TMA im2col mode: `pixels` consecutive output pixels (traversed w -> h -> n inside the descriptor's bounding box) x one
+// box of channels, read at filter-tap offset (off_w, off_h); padding comes back as zeros.  This is the hardware form of
+// the implicit-GEMM A operand of a convolution.
+__device__ __forceinline__ void tma_load_im2col_4d(uint32_t dst_smem, const CUtensorMap* m, int c, int w, int h, int n, uint32_t off_w,
+                                                   uint32_t off_h, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6], {%7, %8};"
+        ::"r"(dst_smem), "l"(reinterpret_cast<uint64_t>(m)), "r"(c), "r"(w), "r"(h), "r"(n), "r"(bar),
+        "h"(static_cast<unsigned short>(off_w)), "h"(static_cast<unsigned short>(off_h))
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst_smem, const CUtensorMap* m, int c0, int c1, int c2, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst_smem),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+        : "memory");
+}
+
 // ----------------------------------------------------------------------------------------------
 // tcgen05 / TMEM
 // ----------------------------------------------------------------------------------------------

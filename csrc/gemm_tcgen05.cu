@@ -40,6 +40,19 @@ struct GemmEpilogue {
     int perm_khw;
 };
 
+// Operand sources.  A: 0 = K-major matrix (2-D TMA), 1 = MN-major matrix, 2 = im2col gather of an NHWC activation
+// (implicit-GEMM convolution: fprop reads x, dgrad reads dY).  B: 0 = K-major matrix, 1 = MN-major matrix,
+// 2 = im2col gather, MN-major (wgrad: the column matrix is never materialised), 3 = conv weight [Cout, kh*kw, Cin] read
+// through a 3-D map as the MN-major operand of dgrad (no transposed / flipped weight copy).
+struct ConvK {
+    int C;            // channels of the gathered activation (Cin for fprop / wgrad, Cout for dgrad)
+    int KH, KW;
+    int P, Q;         // spatial extent of the pixel index space the gather walks (conv output for fprop/wgrad, dX for dgrad)
+    int sh, sw;       // traversal stride
+    int low_h, low_w; // bounding-box lower corner (= -padding for fprop/wgrad, -(k-1-padding) for dgrad)
+    int flip;         // dgrad: weight tap = kh*kw-1 - gather tap
+};
+
 template <int BN, bool kDual>
 struct GemmSmem {
     static constexpr int kABytes = kBM * kBK * 2;  // 16 KiB
@@ -55,10 +68,12 @@ struct GemmSmem {
     static constexpr int kTotal = kStages * kStageBytes + kBarrierBytes + 1024;  // +1024: manual 1 KiB alignment
 };
 
-template <int BN, bool A_MN, bool B_MN, bool kDual>
+template <int BN, int AM, int BMODE, bool kDual>
 __global__ void __launch_bounds__(kGemmThreads, ((kDual && BN <= 128) ? 2 : 1))
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-                         GemmEpilogue ep, int M, int N, int K, int kb_per_split) {
+                         GemmEpilogue ep, ConvK cv, int M, int N, int K, int kb_per_split) {
+    constexpr bool A_MN = AM == 1;
+    constexpr bool B_MN = BMODE >= 1;
     using S = GemmSmem<BN, kDual>;
     constexpr int kStages = S::kStages;
     constexpr int kTmemCols = BN < 32 ? 32 : BN;
@@ -106,6 +121,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     if (warp == 0) {
         // ------------------------------ TMA producer ------------------------------
         if (lane == 0) {
+            // im2col A: the tile's first pixel in (n, p, q) and its input-space coordinates, computed once
+            int a_n = 0, a_h = 0, a_w = 0;
+            if constexpr (AM == 2) {
+                const int pq = cv.P * cv.Q;
+                a_n = m0 / pq;
+                const int rem = m0 - a_n * pq;
+                const int pp = rem / cv.Q;
+                a_h = cv.low_h + pp * cv.sh;
+                a_w = cv.low_w + (rem - pp * cv.Q) * cv.sw;
+            }
             for (int it = 0; it < nkb; ++it) {
                 const int s = it % kStages;
                 const uint32_t ph = (it / kStages) & 1u;
@@ -114,17 +139,48 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
                 const uint32_t b_dst = a_dst + S::kABytes;
                 const int k0 = (kb_begin + it) * kBK;
                 mbar_arrive_expect_tx(full_bar(s), S::kStageBytes);
-                if constexpr (!A_MN) {
+                if constexpr (AM == 0) {
                     tma_load_2d(a_dst, &tma_a, k0, m0, full_bar(s));
-                } else {
+                } else if constexpr (AM == 1) {
                     tma_load_2d(a_dst, &tma_a, m0, k0, full_bar(s));
                     tma_load_2d(a_dst + 8192, &tma_a, m0 + 64, k0, full_bar(s));
-                }
-                if constexpr (!B_MN) {
-                    tma_load_2d(b_dst, &tma_b, k0, n0, full_bar(s));
                 } else {
+                    // k-block = 64 channels of one filter tap (C % 64 == 0): 128 pixels x 128 bytes, one instruction
+                    const int tap = k0 / cv.C;
+                    const int r = tap / cv.KW;
+                    tma_load_im2col_4d(a_dst, &tma_a, k0 - tap * cv.C, a_w, a_h, a_n, tap - r * cv.KW, r, full_bar(s));
+                }
+                if constexpr (BMODE == 0) {
+                    tma_load_2d(b_dst, &tma_b, k0, n0, full_bar(s));
+                } else if constexpr (BMODE == 1) {
 #pragma unroll
                     for (int j = 0; j < BN / 64; ++j) tma_load_2d(b_dst + j * 8192, &tma_b, n0 + 64 * j, k0, full_bar(s));
+                } else if constexpr (BMODE == 2) {
+                    // wgrad: reduction rows = 64 output pixels starting at k0, columns = 64 channels of the tap that owns them
+                    const int pq = cv.P * cv.Q;
+                    const int bn_ = k0 / pq;
+                    const int rem = k0 - bn_ * pq;
+                    const int pp = rem / cv.Q;
+                    const int bh = cv.low_h + pp * cv.sh;
+                    const int bw = cv.low_w + (rem - pp * cv.Q) * cv.sw;
+#pragma unroll
+                    for (int j = 0; j < BN / 64; ++j) {
+                        int kcol = n0 + 64 * j;
+                        if (kcol >= N) kcol = 0;   // tile overhang: any legal box, the epilogue masks those columns
+                        const int tap = kcol / cv.C;
+                        const int r = tap / cv.KW;
+                        tma_load_im2col_4d(b_dst + j * 8192, &tma_b, kcol - tap * cv.C, bw, bh, bn_, tap - r * cv.KW, r, full_bar(s));
+                    }
+                } else {
+                    // dgrad: reduction rows = 64 output channels of one (flipped) tap, columns = 64 input channels
+                    const int tap = k0 / cv.C;
+                    const int wtap = cv.flip ? (cv.KH * cv.KW - 1 - tap) : tap;
+#pragma unroll
+                    for (int j = 0; j < BN / 64; ++j) {
+                        int cin0 = n0 + 64 * j;
+                        if (cin0 >= N) cin0 = 0;
+                        tma_load_3d(b_dst + j * 8192, &tma_b, cin0, wtap, k0 - tap * cv.C, full_bar(s));
+                    }
                 }
             }
         }
@@ -280,11 +336,76 @@ static int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t inner, ui
     return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN, bool kDual>
-static int launch_gemm_v(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpilogue& ep, int M, int N, int K, int splits,
-                       cudaStream_t stream) {
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const int*,
+                                   const int*, cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeIm2colFn get_encode_im2col_fn() {
+    static EncodeIm2colFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeIm2colFn>(p);
+    }
+    return fn;
+}
+
+// im2col tensor map over a bf16 NHWC activation [N, H, W, C] (channel pitch ld): boxes of `pixels` output pixels x 64 channels.
+// Bounding box per spatial dim: [low, dim - 1 + up]; the instruction adds the filter-tap offset to every pixel.
+static int make_tmap_im2col(CUtensorMap* map, const void* base, int C, int W, int H, int N, int ld, int low_w, int low_h, int up_w, int up_h,
+                            int sw, int sh, int pixels) {
+    EncodeIm2colFn fn = get_encode_im2col_fn();
+    DMLB_REQUIRE(fn != nullptr, "cuTensorMapEncodeIm2col entry point not available");
+    DMLB_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0 && ld % 8 == 0, "im2col TMA needs a 16-byte aligned NHWC tensor");
+    cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+    cuuint64_t strides[3] = {(cuuint64_t)ld * 2, (cuuint64_t)W * ld * 2, (cuuint64_t)H * W * ld * 2};
+    int lower[2] = {low_w, low_h};
+    int upper[2] = {up_w, up_h};
+    cuuint32_t trav[4] = {1, (cuuint32_t)sw, (cuuint32_t)sh, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lower, upper, 64, (cuuint32_t)pixels, trav,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char buf[256];
+        snprintf(buf, sizeof(buf), "cuTensorMapEncodeIm2col failed: CUresult %d (C=%d W=%d H=%d N=%d ld=%d low=%d,%d up=%d,%d stride=%d,%d pixels=%d)",
+                 (int)r, C, W, H, N, ld, low_w, low_h, up_w, up_h, sw, sh, pixels);
+        dmlb_set_error(buf);
+        return -3;
+    }
+    // Same adjustment CUTLASS applies (cute/atom/copy_traits_sm90_im2col.hpp) for tensors smaller than 128 KiB on current drivers.
+    int drv = 0;
+    if (cudaDriverGetVersion(&drv) == cudaSuccess && drv <= 13010 && (unsigned long long)N * H * W * ld * 2ull < 131072ull)
+        reinterpret_cast<uint64_t*>(map)[1] &= ~(1ull << 21);
+    return 0;
+}
+
+// 3-D map over a conv weight shadow [Cout][kh*kw][Cin] (row pitch ldrow elements per Cout): box = 64 Cin x 1 tap x 64 Cout.
+static int make_tmap_w3d(CUtensorMap* map, const void* base, int Cin, int KHW, int Cout, int ldrow) {
+    EncodeTiledFn fn = get_encode_fn();
+    DMLB_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t dims[3] = {(cuuint64_t)Cin, (cuuint64_t)KHW, (cuuint64_t)Cout};
+    cuuint64_t strides[2] = {(cuuint64_t)Cin * 2, (cuuint64_t)ldrow * 2};
+    cuuint32_t box[3] = {64, 1, 64};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char buf[200];
+        snprintf(buf, sizeof(buf), "cuTensorMapEncodeTiled (3-D weight map) failed: CUresult %d (Cin=%d taps=%d Cout=%d ld=%d)", (int)r, Cin, KHW, Cout,
+                 ldrow);
+        dmlb_set_error(buf);
+        return -3;
+    }
+    return 0;
+}
+
+template <int BN, int AM, int BMODE, bool kDual>
+static int launch_gemm_v(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpilogue& ep, const ConvK& cv, int M, int N, int K, int splits,
+                         cudaStream_t stream) {
     using S = GemmSmem<BN, kDual>;
-    auto kern = gemm_bf16_tcgen05_kernel<BN, A_MN, B_MN, kDual>;
+    auto kern = gemm_bf16_tcgen05_kernel<BN, AM, BMODE, kDual>;
     static bool attr_set = false;
     if (!attr_set) {
         DMLB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
@@ -294,20 +415,20 @@ static int launch_gemm_v(const CUtensorMap& ta, const CUtensorMap& tb, const Gem
     int kb_per = (nkb + splits - 1) / splits;
     splits = (nkb + kb_per - 1) / kb_per;  // every z-slice owns >= 1 k-block
     dim3 grid((M + kBM - 1) / kBM, (N + BN - 1) / BN, splits);
-    DMLB_CHECK_CUDA(launch_k(kern, grid, kGemmThreads, S::kTotal, stream, ta, tb, ep, M, N, K, kb_per));
+    DMLB_CHECK_CUDA(launch_k(kern, grid, kGemmThreads, S::kTotal, stream, ta, tb, ep, cv, M, N, K, kb_per));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
 
 // More than one wave of CTAs -> the two-CTAs-per-SM variant (epilogues overlap main loops); otherwise the deep-ring one.
-template <int BN, bool A_MN, bool B_MN>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpilogue& ep, int M, int N, int K, int splits,
+template <int BN, int AM, int BMODE>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpilogue& ep, const ConvK& cv, int M, int N, int K, int splits,
                        cudaStream_t stream) {
     const int nkb = (K + kBK - 1) / kBK;
     const int kb_per = (nkb + splits - 1) / splits;
     const long long ctas = 1ll * ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN) * ((nkb + kb_per - 1) / kb_per);
-    if (BN <= 128 && ctas > dmlb_sm_count()) return launch_gemm_v<BN, A_MN, B_MN, true>(ta, tb, ep, M, N, K, splits, stream);
-    return launch_gemm_v<BN, A_MN, B_MN, false>(ta, tb, ep, M, N, K, splits, stream);
+    if (BN <= 128 && ctas > dmlb_sm_count()) return launch_gemm_v<BN, AM, BMODE, true>(ta, tb, ep, cv, M, N, K, splits, stream);
+    return launch_gemm_v<BN, AM, BMODE, false>(ta, tb, ep, cv, M, N, K, splits, stream);
 }
 
 }  // namespace dmlb
@@ -344,8 +465,9 @@ extern "C" int dmlb_gemm_bf16(const void* A, int lda, int a_mn_major, const void
     ep.out = out; ep.bias = bias; ep.ldo = ldo; ep.out_is_f32 = out_is_f32; ep.relu = relu; ep.atomic = atomic;
     ep.perm_cin = perm_cin; ep.perm_khw = perm_khw;
 
+    ConvK cv = {};
 #define DMLB_GEMM_CASE(bn, amn, bmn) \
-    if (BN == bn && (bool)a_mn_major == amn && (bool)b_mn_major == bmn) return launch_gemm<bn, amn, bmn>(ta, tb, ep, M, N, K, split_k, stream);
+    if (BN == bn && (bool)a_mn_major == amn && (bool)b_mn_major == bmn) return launch_gemm<bn, amn ? 1 : 0, bmn ? 1 : 0>(ta, tb, ep, cv, M, N, K, split_k, stream);
     DMLB_GEMM_CASE(32, false, false)
     DMLB_GEMM_CASE(64, false, false)
     DMLB_GEMM_CASE(128, false, false)
@@ -356,5 +478,79 @@ extern "C" int dmlb_gemm_bf16(const void* A, int lda, int a_mn_major, const void
     DMLB_GEMM_CASE(128, true, true)
 #undef DMLB_GEMM_CASE
     dmlb_set_error("dmlb_gemm_bf16: no kernel instantiated for this (tile_n, major) combination");
+    return -4;
+}
+
+
+// Implicit-GEMM convolution (no column matrix in memory): the activation operand is gathered by TMA in im2col mode.
+//   kind 0  fprop : out[B*Ho*Wo, Cout] = conv(x, W)           act = x [B,Ha,Wa,Ca=Cin],   other = W shadow [Cout, kh*kw*Cin]
+//   kind 1  wgrad : out[Cout, kh*kw*Cin] (+)= dY^T * im2col(x) act = x,                     other = dY [B*Ho*Wo, ld_other]
+//   kind 2  dgrad : out[B*Ha'*Wa', Cin]  = conv^T(dY, W)      act = dY [B,Ha,Wa,Ca=Cout],  other = W shadow; stride 1 only;
+//                   n_out = Cin;  (Ha, Wa) are the conv OUTPUT extents, the result has the conv INPUT extents.
+// Needs Ca % 64 == 0 (a 64-wide k-block must stay inside one filter tap); for dgrad also n_out % 8 == 0.
+// Epilogue arguments as in dmlb_gemm_bf16.  Reference: nn.Conv2d forward/backward in example/models.py:29-39 (cuDNN there).
+extern "C" int dmlb_conv_implicit_bf16(int kind, const void* act, int ld_act, int B, int Ha, int Wa, int Ca, const void* other, int ld_other,
+                                       int KH, int KW, int SH, int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo,
+                                       const float* bias, int relu, int split_k, int atomic, int tile_n, void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    DMLB_REQUIRE(kind >= 0 && kind <= 2, "kind must be 0 (fprop), 1 (wgrad) or 2 (dgrad)");
+    DMLB_REQUIRE(Ca % 64 == 0, "implicit-GEMM convolution needs a multiple of 64 channels in the gathered tensor");
+    if (split_k < 1) split_k = 1;
+    if (split_k > 1) atomic = 1;
+    DMLB_REQUIRE(!atomic || out_is_f32, "atomic / split-K output must be fp32");
+    DMLB_REQUIRE(!(atomic && relu), "ReLU cannot be fused into an accumulating epilogue");
+    GemmEpilogue ep;
+    ep.out = out; ep.bias = bias; ep.ldo = ldo; ep.out_is_f32 = out_is_f32; ep.relu = relu; ep.atomic = atomic; ep.perm_cin = 0; ep.perm_khw = 0;
+    ConvK cv = {};
+    cv.C = Ca; cv.KH = KH; cv.KW = KW; cv.sh = SH; cv.sw = SW;
+    CUtensorMap ta, tb;
+    int rc;
+    if (kind == 0 || kind == 1) {
+        const int Ho = (Ha + 2 * PH - KH) / SH + 1, Wo = (Wa + 2 * PW - KW) / SW + 1;
+        DMLB_REQUIRE(Ho > 0 && Wo > 0, "empty conv output");
+        cv.P = Ho; cv.Q = Wo; cv.low_h = -PH; cv.low_w = -PW; cv.flip = 0;
+        const int Kd = KH * KW * Ca;
+        const long long Mpix = 1ll * B * Ho * Wo;
+        DMLB_REQUIRE(Mpix < (1ll << 31), "too many output pixels");
+        if (kind == 0) {
+            const int N = n_out;
+            int BN = tile_n ? tile_n : ((N > 64) ? 128 : (N > 32 ? 64 : 32));
+            rc = make_tmap_im2col(&ta, act, Ca, Wa, Ha, B, ld_act, -PW, -PH, PW - (KW - 1), PH - (KH - 1), SW, SH, kBM);
+            if (rc) return rc;
+            rc = make_tmap_bf16(&tb, other, (uint64_t)Kd, (uint64_t)N, (uint64_t)ld_other, kBK, (uint32_t)BN);
+            if (rc) return rc;
+            if (BN == 32) return launch_gemm<32, 2, 0>(ta, tb, ep, cv, (int)Mpix, N, Kd, split_k, stream);
+            if (BN == 64) return launch_gemm<64, 2, 0>(ta, tb, ep, cv, (int)Mpix, N, Kd, split_k, stream);
+            if (BN == 128) return launch_gemm<128, 2, 0>(ta, tb, ep, cv, (int)Mpix, N, Kd, split_k, stream);
+            if (BN == 256) return launch_gemm<256, 2, 0>(ta, tb, ep, cv, (int)Mpix, N, Kd, split_k, stream);
+        } else {
+            const int Cout = n_out;
+            int BN = tile_n ? tile_n : 128;
+            rc = make_tmap_bf16(&ta, other, (uint64_t)Cout, (uint64_t)Mpix, (uint64_t)ld_other, 64, kBK);   // dY as MN-major A
+            if (rc) return rc;
+            rc = make_tmap_im2col(&tb, act, Ca, Wa, Ha, B, ld_act, -PW, -PH, PW - (KW - 1), PH - (KH - 1), SW, SH, kBK);
+            if (rc) return rc;
+            if (BN == 64) return launch_gemm<64, 1, 2>(ta, tb, ep, cv, Cout, Kd, (int)Mpix, split_k, stream);
+            if (BN == 128) return launch_gemm<128, 1, 2>(ta, tb, ep, cv, Cout, Kd, (int)Mpix, split_k, stream);
+        }
+    } else {
+        DMLB_REQUIRE(SH == 1 && SW == 1, "implicit dgrad supports stride 1 (strided convolutions use the explicit path)");
+        const int Cin = n_out, Cout = Ca;
+        DMLB_REQUIRE(Cin % 8 == 0, "implicit dgrad needs Cin % 8 == 0");
+        const int Hin = Ha + KH - 1 - 2 * PH, Win = Wa + KW - 1 - 2 * PW;     // conv input extents (stride 1)
+        DMLB_REQUIRE(Hin > 0 && Win > 0, "bad dgrad geometry");
+        cv.P = Hin; cv.Q = Win; cv.low_h = -(KH - 1 - PH); cv.low_w = -(KW - 1 - PW); cv.flip = 1;
+        const int Kd = KH * KW * Cout;
+        const long long Mpix = 1ll * B * Hin * Win;
+        DMLB_REQUIRE(Mpix < (1ll << 31), "too many pixels");
+        int BN = tile_n ? tile_n : (Cin > 64 ? 128 : 64);
+        rc = make_tmap_im2col(&ta, act, Cout, Wa, Ha, B, ld_act, cv.low_w, cv.low_h, -PW, -PH, 1, 1, kBM);
+        if (rc) return rc;
+        rc = make_tmap_w3d(&tb, other, Cin, KH * KW, Cout, ld_other);
+        if (rc) return rc;
+        if (BN == 64) return launch_gemm<64, 2, 3>(ta, tb, ep, cv, (int)Mpix, Cin, Kd, split_k, stream);
+        if (BN == 128) return launch_gemm<128, 2, 3>(ta, tb, ep, cv, (int)Mpix, Cin, Kd, split_k, stream);
+    }
+    dmlb_set_error("dmlb_conv_implicit_bf16: unsupported tile_n for this kind");
     return -4;
 }

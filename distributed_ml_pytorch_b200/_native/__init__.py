@@ -27,6 +27,8 @@ _SIGNATURES = {
     "dmlb_reset_launch_count": [],
     "dmlb_gemm_bf16": [c_vp, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_int, c_int, c_vp, c_int, c_int, c_int,
                        c_int, c_int, c_int, c_vp],
+    "dmlb_conv_implicit_bf16": [c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_vp,
+                                c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_vp],
     "dmlb_splitk_finish": [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_ll, c_int, c_int, c_int, c_int, c_int, c_vp, c_int, c_vp],
     "dmlb_gemm_bias_act_splitk": [c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_vp, c_vp, c_int, c_vp, c_int, c_int, c_vp],
     "dmlb_im2col_nhwc_bf16": [c_vp, c_vp] + [c_int] * 12 + [c_vp],

@@ -33,6 +33,14 @@ def gemm(a: torch.Tensor, lda: int, a_mn: bool, b: torch.Tensor, ldb: int, b_mn:
           perm_cin, perm_khw, tile_n, stream_ptr())
 
 
+def conv_implicit(kind: int, act_ptr: int, ld_act: int, B, Ha, Wa, Ca, other_ptr: int, ld_other: int, KH, KW, SH, SW, PH, PW, n_out: int,
+                  out: torch.Tensor, ldo: int, bias=None, relu: bool = False, split_k: int = 1, atomic: bool = False, tile_n: int = 0) -> None:
+    """Implicit-GEMM convolution through TMA im2col (``dmlb_conv_implicit_bf16``): kind 0 fprop, 1 wgrad, 2 dgrad."""
+    _call("dmlb_conv_implicit_bf16", kind, act_ptr, ld_act, B, Ha, Wa, Ca, other_ptr, ld_other, KH, KW, SH, SW, PH, PW, n_out, out.data_ptr(),
+          int(out.dtype == torch.float32), ldo, bias.data_ptr() if bias is not None else None, int(relu), split_k, int(atomic), tile_n,
+          stream_ptr())
+
+
 def pick_split_k(tiles: int, k_total: int, sms: int = 148, min_kblocks: int = 2) -> int:
     """Split-K factor that fills the SMs when the output has few tiles (weight gradients, tiny-M fprop)."""
     nkb = (k_total + 63) // 64

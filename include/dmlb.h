@@ -45,6 +45,14 @@ int dmlb_gemm_bf16(const void* A, int lda, int a_mn_major, const void* B, int ld
                    void* out, int out_is_f32, int ldo, const float* bias, int relu, int split_k, int atomic, int perm_cin,
                    int perm_khw, int tile_n, void* stream);
 
+/* Implicit-GEMM convolution: the activation operand is gathered by TMA in im2col mode, no column matrix exists in memory.
+ * kind 0 fprop (act = x, other = W shadow [n_out=Cout, kh*kw*Cin]), 1 wgrad (act = x, other = dY, out [n_out=Cout, kh*kw*Cin], fp32 accumulate),
+ * 2 dgrad (act = dY with Ca = Cout, other = W shadow, n_out = Cin, stride 1 only).  The gathered tensor needs Ca % 64 == 0.
+ * Reference: nn.Conv2d forward / backward of example/models.py:29-39 (cuDNN there). */
+int dmlb_conv_implicit_bf16(int kind, const void* act, int ld_act, int B, int Ha, int Wa, int Ca, const void* other, int ld_other, int KH, int KW,
+                            int SH, int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo, const float* bias, int relu,
+                            int split_k, int atomic, int tile_n, void* stream);
+
 /* Split-K forward (csrc/splitk.cu): for tiny-M, long-K layers (AlexNet conv3-5 at the reference's batch 64,
  * example/main.py:142).  ws is fp32 scratch [M, round_up(N,4)], all zeros on entry and zeroed again by the finish. */
 int dmlb_splitk_finish(float* ws, int ldw, const float* bias, int relu, void* y, int ldy, long long M, int N, int pool2, int B, int H, int W,
