@@ -188,9 +188,24 @@ def _sink_ok(param: torch.Tensor, sink: Optional[torch.Tensor]) -> bool:
 # ------------------------------------------------------------------------------------------------
 # conv (+bias +ReLU +max-pool) block
 # ------------------------------------------------------------------------------------------------
+_conv_opts = SimpleNamespace(implicit=True)
+
+
+def set_implicit_conv(flag: bool) -> bool:
+    """Toggle the implicit-GEMM (TMA im2col) convolution path; off = explicit im2col / col2im kernels everywhere."""
+    old = _conv_opts.implicit
+    _conv_opts.implicit = bool(flag)
+    return old
+
+
 class _ConvBlockFn(torch.autograd.Function):
-    """im2col -> tcgen05 GEMM (bias/ReLU epilogue) -> optional max-pool; backward = fused activation
-    backward + split-K wgrad GEMM (scattered straight into the fp32 gradient arena) + dgrad GEMM + col2im."""
+    """Convolution (+bias +ReLU +max-pool) on the tcgen05 GEMM.
+
+    Implicit path (bf16 channels-last input with Cin % 64 == 0): the activation operand of fprop, wgrad and dgrad is
+    gathered by TMA in im2col mode — no column matrix is ever written.  Explicit path (first layer from fp32 NCHW, small or
+    odd channel counts, strided dgrad): im2col / col2im kernels around the same GEMM.  Tiny-M layers split K over the SMs
+    and finish (bias, ReLU, 2x2 pool, bf16 cast) in one kernel.  Weight gradients accumulate straight into the fp32 arena
+    on a side stream."""
 
     @staticmethod
     def forward(ctx, x, weight, bias, cfg):
@@ -204,21 +219,28 @@ class _ConvBlockFn(torch.autograd.Function):
         Kpad = pad8(Kd)
         dev = x.device
         from_nchw_f32 = x.dtype == torch.float32 and x.is_contiguous()
-        direct = (not from_nchw_f32) and KH == 1 and KW == 1 and SH == 1 and SW == 1 and PH == 0 and PW == 0
-        ldx = 0
+        direct = (not from_nchw_f32) and KH == 1 and KW == 1 and SH == 1 and SW == 1 and PH == 0 and PW == 0 and Cin % 8 == 0
+        implicit = _conv_opts.implicit and (not from_nchw_f32) and (not direct) and Cin % 64 == 0
+        ldx, a_t, lda = 0, None, 0
         if from_nchw_f32:
-            col = torch.empty((M, Kpad), dtype=torch.bfloat16, device=dev)
-            K.im2col_nchw_f32(x, col, B, H, W, Cin, KH, KW, SH, SW, PH, PW, Kpad)
-            a_t, lda = col, Kpad
+            a_t = torch.empty((M, Kpad), dtype=torch.bfloat16, device=dev)
+            K.im2col_nchw_f32(x, a_t, B, H, W, Cin, KH, KW, SH, SW, PH, PW, Kpad)
+            lda = Kpad
         else:
             x, ldx = as_act4(x)
-            if direct and Cin % 8 == 0:
+            if direct:
                 a_t, lda = x, ldx
+            elif not implicit:
+                a_t = torch.empty((M, Kpad), dtype=torch.bfloat16, device=dev)
+                K.im2col_nhwc(x.data_ptr(), a_t, B, H, W, Cin, ldx, KH, KW, SH, SW, PH, PW, Kpad)
+                lda = Kpad
+
+        def fprop(out_t, ldo, **kw):
+            if implicit:
+                K.conv_implicit(0, x.data_ptr(), ldx, B, H, W, Cin, cfg.shadow.data_ptr(), Kpad, KH, KW, SH, SW, PH, PW, Cout, out_t, ldo, **kw)
             else:
-                direct = False
-                col = torch.empty((M, Kpad), dtype=torch.bfloat16, device=dev)
-                K.im2col_nhwc(x.data_ptr(), col, B, H, W, Cin, ldx, KH, KW, SH, SW, PH, PW, Kpad)
-                a_t, lda = col, Kpad
+                K.gemm(a_t, lda, False, cfg.shadow, Kpad, False, M, Cout, Kd, out_t, ldo, **kw)
+
         y = new_act4(B, Cout, Ho, Wo, dev)
         ldy = pad8(Cout)
         split = K.fprop_split(M, Cout, Kd)
@@ -228,7 +250,7 @@ class _ConvBlockFn(torch.autograd.Function):
             # tiny-M / long-K layer: spread K over the SMs, reduce in an fp32 workspace, finish (+pool) in one kernel
             ldw = (Cout + 3) // 4 * 4
             ws = K.splitk_workspace(dev, M * ldw)
-            K.gemm(a_t, lda, False, cfg.shadow, Kpad, False, M, Cout, Kd, ws, ldw, split_k=split, atomic=True)
+            fprop(ws, ldw, split_k=split, atomic=True)
             if cfg.pool == (2, 2, 0) and Ho % 2 == 0 and Wo % 2 == 0:
                 out = new_act4(B, Cout, Ho // 2, Wo // 2, dev)
                 K.splitk_finish(ws, ldw, bias, cfg.relu, y.data_ptr(), ldy, M, Cout, pool2=(B, Ho, Wo), pooled_ptr=out.data_ptr(), ldp=ldy)
@@ -236,23 +258,23 @@ class _ConvBlockFn(torch.autograd.Function):
             else:
                 K.splitk_finish(ws, ldw, bias, cfg.relu, y.data_ptr(), ldy, M, Cout)
         else:
-            K.gemm(a_t, lda, False, cfg.shadow, Kpad, False, M, Cout, Kd, y, ldy, bias=bias, relu=cfg.relu)
+            fprop(y, ldy, bias=bias, relu=cfg.relu)
         if cfg.pool is not None and not fused_pool:
             k, s, p = cfg.pool
             Hp, Wp = (Ho + 2 * p - k) // s + 1, (Wo + 2 * p - k) // s + 1
             out = new_act4(B, Cout, Hp, Wp, dev)
             K.maxpool_fwd(y.data_ptr(), out.data_ptr(), B, Ho, Wo, Cout, ldy, ldy, k, s, p)
         ctx.cfg = cfg
-        ctx.geom = (B, H, W, Cin, Cout, KH, KW, SH, SW, PH, PW, Ho, Wo, Kd, Kpad, ldx, lda, direct, from_nchw_f32)
+        ctx.geom = (B, H, W, Cin, Cout, KH, KW, SH, SW, PH, PW, Ho, Wo, Kd, Kpad, ldx, lda, direct, from_nchw_f32, implicit)
         ctx.has_bias = bias is not None
-        ctx.save_for_backward(a_t, y if (cfg.relu or cfg.pool is not None) else None, weight, bias)
+        ctx.save_for_backward(x if implicit else a_t, y if (cfg.relu or cfg.pool is not None) else None, weight, bias)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         cfg = ctx.cfg
         a_t, y, weight, bias = ctx.saved_tensors
-        (B, H, W, Cin, Cout, KH, KW, SH, SW, PH, PW, Ho, Wo, Kd, Kpad, ldx, lda, direct, from_nchw_f32) = ctx.geom
+        (B, H, W, Cin, Cout, KH, KW, SH, SW, PH, PW, Ho, Wo, Kd, Kpad, ldx, lda, direct, from_nchw_f32, implicit) = ctx.geom
         dev = dout.device
         M = B * Ho * Wo
         ldy = pad8(Cout)
@@ -270,35 +292,67 @@ class _ConvBlockFn(torch.autograd.Function):
             lddy = ldy
         else:
             dy, lddy = dout, ldd
-        # ---- weight gradient: dW[Cout, K] = dY^T[Cout, M] * Xcol[M, K]  (both operands MN-major) ----
+        # ---- weight gradient: dW[Cout, K] = dY^T[Cout, M] * Xcol[M, K]  (both operands MN-major; Xcol gathered when implicit) ----
         gw = None
         if ctx.needs_input_grad[1]:
             wsink = cfg.wsink if _sink_ok(weight, cfg.wsink) else None
-            if wsink is None:
-                gw = torch.zeros_like(weight, dtype=torch.float32)
-            target = wsink if wsink is not None else gw
             tiles = ((Cout + 127) // 128) * ((Kd + 127) // 128)
             split = K.pick_split_k(tiles, M)
             # a channels-last gradient (arena layout [Cout,kh,kw,Cin]) is exactly the GEMM's column order: contiguous
             # rows, vector red.add; a PyTorch-layout gradient needs the (kh,kw,cin)->(cin,kh,kw) column scatter
-            gemm_order = KH * KW == 1 or Cin == 1 or target.permute(0, 2, 3, 1).is_contiguous()
+            if wsink is not None:
+                target = wsink
+                gemm_order = KH * KW == 1 or Cin == 1 or target.permute(0, 2, 3, 1).is_contiguous()
+            elif implicit:
+                # no arena: accumulate in GEMM order and hand autograd the permuted view (a strided gradient is legal)
+                target = torch.zeros((Cout, KH, KW, Cin), dtype=torch.float32, device=dev)
+                gw = target.permute(0, 3, 1, 2)
+                gemm_order = True
+            else:
+                gw = torch.zeros_like(weight, dtype=torch.float32)
+                target = gw
+                gemm_order = KH * KW == 1 or Cin == 1 or target.permute(0, 2, 3, 1).is_contiguous()
             with _WgradFork(dev, dy, a_t, gw) as fork:
-                K.gemm(dy, lddy, True, a_t, lda, True, Cout, Kd, M, target, Kd, split_k=split, atomic=True,
-                       perm_cin=0 if gemm_order else Cin, perm_khw=KH * KW)
+                if implicit and gemm_order:
+                    K.conv_implicit(1, a_t.data_ptr(), ldx, B, H, W, Cin, dy.data_ptr(), lddy, KH, KW, SH, SW, PH, PW, Cout, target, Kd,
+                                    split_k=split, atomic=True)
+                else:
+                    if implicit:   # PyTorch-layout sink with an implicit forward: rebuild the column matrix once
+                        col = torch.empty((M, Kpad), dtype=torch.bfloat16, device=dev)
+                        K.im2col_nhwc(a_t.data_ptr(), col, B, H, W, Cin, ldx, KH, KW, SH, SW, PH, PW, Kpad)
+                        col.record_stream(torch.cuda.current_stream(dev))
+                        b_t, ldb = col, Kpad
+                    else:
+                        b_t, ldb = a_t, lda
+                    K.gemm(dy, lddy, True, b_t, ldb, True, Cout, Kd, M, target, Kd, split_k=split, atomic=True,
+                           perm_cin=0 if gemm_order else Cin, perm_khw=KH * KW)
             if gw is not None and fork.active:
                 join_side_streams()       # autograd consumes a returned gradient immediately
-        # ---- data gradient: dXcol[M, K] = dY[M, Cout] * W[Cout, K]  (B operand MN-major), then col2im ----
+        # ---- data gradient ----
         dx = None
         if ctx.needs_input_grad[0]:
             if from_nchw_f32:
                 raise RuntimeError("gradient w.r.t. an fp32 NCHW network input is not implemented on the CUDA path")
             dx = new_act4(B, Cin, H, W, dev)
+            ldxo = pad8(Cin)
             if direct:
-                K.gemm(dy, lddy, False, cfg.shadow, Kpad, True, M, Kd, Cout, dx, pad8(Cin))
+                K.gemm(dy, lddy, False, cfg.shadow, Kpad, True, M, Kd, Cout, dx, ldxo)
+            elif implicit and SH == 1 and SW == 1 and Cout % 64 == 0 and Cin % 8 == 0 and Kpad == Kd:
+                # transposed convolution as an implicit GEMM over dY: no dcol matrix, no col2im
+                Min, Kdg = B * H * W, KH * KW * Cout
+                dsplit = K.fprop_split(Min, Cin, Kdg)
+                if dsplit > 1:
+                    ldw = (Cin + 3) // 4 * 4
+                    ws = K.splitk_workspace(dev, Min * ldw)
+                    K.conv_implicit(2, dy.data_ptr(), lddy, B, Ho, Wo, Cout, cfg.shadow.data_ptr(), Kpad, KH, KW, 1, 1, PH, PW, Cin, ws, ldw,
+                                    split_k=dsplit, atomic=True)
+                    K.splitk_finish(ws, ldw, None, False, dx.data_ptr(), ldxo, Min, Cin)
+                else:
+                    K.conv_implicit(2, dy.data_ptr(), lddy, B, Ho, Wo, Cout, cfg.shadow.data_ptr(), Kpad, KH, KW, 1, 1, PH, PW, Cin, dx, ldxo)
             else:
                 dcol = torch.empty((M, Kpad), dtype=torch.bfloat16, device=dev)
                 K.gemm(dy, lddy, False, cfg.shadow, Kpad, True, M, Kd, Cout, dcol, Kpad)
-                K.col2im_nhwc(dcol, dx.data_ptr(), B, H, W, Cin, pad8(Cin), KH, KW, SH, SW, PH, PW, Kpad)
+                K.col2im_nhwc(dcol, dx.data_ptr(), B, H, W, Cin, ldxo, KH, KW, SH, SW, PH, PW, Kpad)
         return dx, gw, gb, None
 
 
