@@ -201,3 +201,74 @@ def test_async_multi_gpu_mailbox_runs_and_tracks_staleness(tmp_path):
     assert not torch.equal(outs[0]["final"], outs[0]["theta0"])
     assert torch.isfinite(outs[0]["final"]).all()
     assert sum(o["stats"]["chunks_applied"] for o in outs) > 0
+
+
+def test_mailbox_protocol_stress_world1():
+    """Flag / version protocol under load (the pool's compute-sanitizer is closed, so the race check is an invariant check):
+    with scale 1 and no momentum the mailbox path must deliver every pushed update exactly once, whatever the interleaving."""
+    torch.manual_seed(0)
+    net = build_model("lenet").cuda().eval()
+    opt = Asynchronous(net.parameters(), lr=0.05, n_push=1, n_pull=7, model=net, staleness="exp", staleness_param=1.0)
+    assert opt._use_mailbox
+    theta0 = opt.server_parameters().clone()
+    total = torch.zeros_like(theta0)
+    g = torch.Generator(device="cuda").manual_seed(1)
+    for i in range(200):
+        delta = torch.randn(opt.arena.padded, device="cuda", generator=g) * 1e-3
+        delta[opt.arena.numel:] = 0
+        opt.accumulated_gradients.add_(delta)
+        total += delta[: opt.arena.numel]
+        opt._push()
+        if i % 3 != 0:                     # the owner does not serve every step: slots stay busy, updates keep accumulating
+            opt._owner_apply()
+        if i % 7 == 0:
+            opt._pull()
+    for _ in range(3):
+        opt._owner_apply()
+        opt._push()
+    opt._owner_apply()
+    torch.cuda.synchronize()
+    assert opt.accumulated_gradients.abs().sum().item() == 0.0
+    torch.testing.assert_close(opt.server_parameters(), theta0 + total, rtol=1e-4, atol=1e-5)
+    assert opt.staleness_stats()["chunks_applied"] > 0
+
+
+def _mgpu_mailbox_stress(rank, size, out_dir, steps):
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(0)
+    net = build_model("lenet").to(dev).eval()
+    opt = Asynchronous(net.parameters(), lr=0.02, n_push=1, n_pull=5, model=net, staleness="exp", staleness_param=1.0)
+    theta0 = opt.server_parameters().cpu().clone()
+    total = torch.zeros(opt.arena.numel, device=dev)
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+    for i in range(steps):
+        delta = torch.randn(opt.arena.padded, device=dev, generator=g) * 1e-3
+        delta[opt.arena.numel:] = 0
+        opt.accumulated_gradients.add_(delta)
+        total += delta[: opt.arena.numel]
+        opt._push()
+        if (i + rank) % 2 == 0:
+            opt._owner_apply()
+        if i % 5 == 0:
+            opt._pull()
+    for _ in range(4):                      # drain: every rank serves, then re-pushes what was still busy
+        opt.peer.barrier()
+        opt._owner_apply()
+        opt.peer.barrier()
+        opt._push()
+    opt.peer.barrier()
+    opt._owner_apply()
+    opt.peer.barrier()
+    left = opt.accumulated_gradients.abs().sum().item()
+    torch.save({"theta0": theta0, "sum": total.cpu(), "final": opt.server_parameters().cpu(), "left": left}, os.path.join(out_dir, f"stress{rank}.pt"))
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_mailbox_protocol_stress_multi_gpu(tmp_path, world):
+    _need(world)
+    spawn(_mgpu_mailbox_stress, world, backend="nccl", args=(str(tmp_path), 60))
+    outs = [torch.load(tmp_path / f"stress{r}.pt", weights_only=False) for r in range(world)]
+    assert all(o["left"] == 0.0 for o in outs)
+    expect = outs[0]["theta0"] + sum(o["sum"] for o in outs)
+    for o in outs:
+        torch.testing.assert_close(o["final"], expect, rtol=1e-4, atol=2e-5)
