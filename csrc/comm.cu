@@ -194,8 +194,8 @@ __device__ __forceinline__ void spin_until_ge(const uint32_t* flag, uint32_t wan
 }
 
 __global__ void __launch_bounds__(512) sync_rs_update_ag_kernel(PeerTable grads, PeerTable params, PeerTable flags, float* __restrict__ mom,
-                                                                int rank, int world, long long shard_size, const float* __restrict__ lr_ptr,
-                                                                float mu, float wd, float grad_scale) {
+                                                                int rank, int world, long long base, long long slice_len,
+                                                                const float* __restrict__ lr_ptr, float mu, float wd, float grad_scale) {
     uint32_t* my_flags = static_cast<uint32_t*>(flags.ptr[rank]);
     const uint32_t epoch = my_flags[2 * kMaxPeers] + 1u;   // bumped once per launch by the last block, below
     // ---- start barrier: tell every peer that my gradients are final, wait for theirs ----
@@ -206,8 +206,9 @@ __global__ void __launch_bounds__(512) sync_rs_update_ag_kernel(PeerTable grads,
     __syncthreads();
 
     const float lr = *lr_ptr;
-    const long long base = static_cast<long long>(rank) * shard_size;
-    const long long n4 = shard_size / 4;
+    // [base, base + slice_len) is the slice of the flat vector this GPU owns in this launch (the whole shard, or this GPU's
+    // part of one gradient bucket when the update is overlapped with the backward pass)
+    const long long n4 = slice_len / 4;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
         float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
         float4 v[kMaxPeers];
@@ -335,16 +336,26 @@ extern "C" int dmlb_owner_apply(float* master, float* mom, void* version, void* 
     return 0;
 }
 
-extern "C" int dmlb_sync_rs_update_ag(void* const* grad_ptrs, void* const* param_ptrs, void* const* flag_ptrs, float* mom, int rank, int world,
-                                      long long shard_size, const float* lr_ptr, float mu, float wd, float grad_scale, void* stream) {
-    DMLB_REQUIRE(shard_size % 4 == 0, "shard size must be a multiple of 4");
+// Range form: this GPU owns [base, base + n) of the flat vector in this launch; mom (may be NULL) is indexed from the start of that
+// slice.  max_blocks > 0 caps the grid (a small grid leaves SMs to the backward kernels it overlaps with).
+extern "C" int dmlb_sync_rs_update_ag_range(void* const* grad_ptrs, void* const* param_ptrs, void* const* flag_ptrs, float* mom, int rank,
+                                            int world, long long base, long long n, const float* lr_ptr, float mu, float wd, float grad_scale,
+                                            int max_blocks, void* stream) {
+    DMLB_REQUIRE(n % 4 == 0 && base % 4 == 0 && n > 0, "slice must be non-empty and 16-byte aligned");
     PeerTable g, p, f;
     if (fill_table(&g, grad_ptrs, world) || fill_table(&p, param_ptrs, world) || fill_table(&f, flag_ptrs, world)) return -2;
     // One CTA per SM at most: every CTA polls the start flags, so all of them must be able to become resident.
-    int blocks = comm_grid(shard_size / 4, 512);
+    int blocks = comm_grid(n / 4, 512);
     if (blocks > dmlb_sm_count()) blocks = dmlb_sm_count();
-    sync_rs_update_ag_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(g, p, f, mom, rank, world, shard_size, lr_ptr, mu, wd,
+    if (max_blocks > 0 && blocks > max_blocks) blocks = max_blocks;
+    sync_rs_update_ag_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(g, p, f, mom, rank, world, base, n, lr_ptr, mu, wd,
                                                                                    grad_scale);
     DMLB_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int dmlb_sync_rs_update_ag(void* const* grad_ptrs, void* const* param_ptrs, void* const* flag_ptrs, float* mom, int rank, int world,
+                                      long long shard_size, const float* lr_ptr, float mu, float wd, float grad_scale, void* stream) {
+    return dmlb_sync_rs_update_ag_range(grad_ptrs, param_ptrs, flag_ptrs, mom, rank, world, static_cast<long long>(rank) * shard_size, shard_size,
+                                        lr_ptr, mu, wd, grad_scale, 0, stream);
 }

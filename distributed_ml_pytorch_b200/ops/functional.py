@@ -181,6 +181,31 @@ class _WgradFork:
         return False
 
 
+# ------------------------------------------------------------------------------------------------
+# gradient-ready notifications (lets the synchronous optimizer start reducing a bucket while backward is still running)
+# ------------------------------------------------------------------------------------------------
+_grad_hooks = []
+
+
+def add_grad_ready_hook(fn) -> None:
+    """``fn(param, stream)`` is called right after the kernel that finalises ``param``'s arena gradient was launched on ``stream``."""
+    if fn not in _grad_hooks:
+        _grad_hooks.append(fn)
+
+
+def remove_grad_ready_hook(fn) -> None:
+    if fn in _grad_hooks:
+        _grad_hooks.remove(fn)
+
+
+def _notify_grad_ready(param, dev, stream=None) -> None:
+    if not _grad_hooks or param is None:
+        return
+    st = stream if stream is not None else torch.cuda.current_stream(dev)
+    for fn in list(_grad_hooks):
+        fn(param, st)
+
+
 def _sink_ok(param: torch.Tensor, sink: Optional[torch.Tensor]) -> bool:
     return sink is not None and param.grad is not None and param.grad.data_ptr() == sink.data_ptr()
 
@@ -290,6 +315,8 @@ class _ConvBlockFn(torch.autograd.Function):
             K.act_bwd(y.data_ptr() if y is not None else dy.data_ptr(), dout.data_ptr(), dy.data_ptr(), db, B, Ho, Wo, Cout, ldy, ldd,
                       cfg.pool, cfg.relu)
             lddy = ldy
+            if bias_sink is not None:
+                _notify_grad_ready(bias, dev)
         else:
             dy, lddy = dout, ldd
         # ---- weight gradient: dW[Cout, K] = dY^T[Cout, M] * Xcol[M, K]  (both operands MN-major; Xcol gathered when implicit) ----
@@ -328,6 +355,8 @@ class _ConvBlockFn(torch.autograd.Function):
                            perm_cin=0 if gemm_order else Cin, perm_khw=KH * KW)
             if gw is not None and fork.active:
                 join_side_streams()       # autograd consumes a returned gradient immediately
+            if wsink is not None:
+                _notify_grad_ready(weight, dev, fork.side if fork.active else None)
         # ---- data gradient ----
         dx = None
         if ctx.needs_input_grad[0]:
@@ -413,6 +442,8 @@ class _LinearFn(torch.autograd.Function):
             dy = new_act2(B, O, dev)
             lddy = pad8(O)
             K.act_bwd(y.data_ptr() if y is not None else dy.data_ptr(), dout.data_ptr(), dy.data_ptr(), db, B, 1, 1, O, lddy, ldd, None, cfg.relu)
+            if bias_sink is not None:
+                _notify_grad_ready(bias, dev)
         else:
             dy, lddy = dout, ldd
         gw = None
@@ -429,6 +460,8 @@ class _LinearFn(torch.autograd.Function):
                        perm_khw=pk)
             if gw is not None and fork.active:
                 join_side_streams()
+            if wsink is not None:
+                _notify_grad_ready(weight, dev, fork.side if fork.active else None)
         dx = None
         if ctx.needs_input_grad[0]:
             dx = new_act2(B, I, dev)
@@ -673,6 +706,10 @@ class _BatchNormFn(torch.autograd.Function):
         dx = new_act4(B, C, H, W, dev)
         K.bn_bwd_apply(x.data_ptr(), ldx, g.data_ptr(), ldg, dx.data_ptr(), ldc, save, weight, dsum, wsink if wsink is not None else gw,
                        bsink if bsink is not None else gb, M, C)
+        if wsink is not None:
+            _notify_grad_ready(weight, dev)
+        if bsink is not None:
+            _notify_grad_ready(bias, dev)
         return dx, (g if ctx.has_res else None), gw, gb, None
 
 

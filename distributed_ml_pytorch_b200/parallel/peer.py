@@ -34,6 +34,7 @@ _native.register("dmlb_pull", [c_vp, c_vp, _PP, _PP, c_vp, c_int, c_ll, c_ll, c_
 _native.register("dmlb_push_mailbox", [c_vp, c_vp, c_vp, _PP, _PP, c_int, c_int, c_ll, c_vp])
 _native.register("dmlb_owner_apply", [c_vp, c_vp, c_vp, c_vp, c_vp, _PP, c_vp, c_int, c_int, c_ll, c_float, c_int, c_float, c_vp])
 _native.register("dmlb_sync_rs_update_ag", [_PP, _PP, _PP, c_vp, c_int, c_int, c_ll, c_vp, c_float, c_float, c_float, c_vp])
+_native.register("dmlb_sync_rs_update_ag_range", [_PP, _PP, _PP, c_vp, c_int, c_int, c_ll, c_ll, c_vp, c_float, c_float, c_float, c_int, c_vp])
 
 
 class _RawCudaBuffer:
@@ -172,3 +173,8 @@ def owner_apply(master, mom, version, full, mailbox, busy_table, stats, rank, wo
 def sync_rs_update_ag(grad_table, param_table, flag_table, mom, rank, world, shard_size, lr_dev, mu, wd, grad_scale) -> None:
     _native.call("dmlb_sync_rs_update_ag", grad_table, param_table, flag_table, mom.data_ptr() if mom is not None else None, rank, world,
                  shard_size, lr_dev.data_ptr(), float(mu), float(wd), float(grad_scale), _stream())
+
+
+def sync_rs_update_ag_range(grad_table, param_table, flag_table, mom_ptr: int, rank, world, base, n, lr_dev, mu, wd, grad_scale, max_blocks=0) -> None:
+    _native.call("dmlb_sync_rs_update_ag_range", grad_table, param_table, flag_table, mom_ptr or None, rank, world, base, n, lr_dev.data_ptr(),
+                 float(mu), float(wd), float(grad_scale), int(max_blocks), _stream())

@@ -155,6 +155,11 @@ int dmlb_owner_apply(float* master, float* mom, void* version, void* full, const
 int dmlb_sync_rs_update_ag(void* const* grad_ptrs, void* const* param_ptrs, void* const* flag_ptrs, float* mom, int rank, int world,
                            long long shard_size, const float* lr_ptr, float mu, float wd, float grad_scale, void* stream);
 
+/* Range form for bucketed overlap with the backward pass: this GPU owns [base, base+n) in this launch. */
+int dmlb_sync_rs_update_ag_range(void* const* grad_ptrs, void* const* param_ptrs, void* const* flag_ptrs, float* mom, int rank, int world,
+                                 long long base, long long n, const float* lr_ptr, float mu, float wd, float grad_scale, int max_blocks,
+                                 void* stream);
+
 #ifdef __cplusplus
 }
 #endif
