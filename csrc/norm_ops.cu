@@ -25,13 +25,20 @@ __device__ __forceinline__ uint4 pack8f(const float (&f)[8]) {
 }
 
 // Block layout shared by the reductions: tx = channel group (8 channels), ty = row lane.
+// blockIdx.y selects a slab of up to 32 channel groups (256 channels), so wide layers keep several row lanes per block and
+// each block ends with at most 512 global reductions.
 struct RowTiling {
-    int c8n, lanes;  // channel groups, row lanes per block (c8n * lanes <= blockDim.x)
+    int c8n;    // channel groups handled by this block (<= 32)
+    int lanes;  // row lanes per block (c8n * lanes <= blockDim.x)
+    int c8_0;   // first channel group of this block's slab
 };
 __device__ __forceinline__ RowTiling row_tiling(int C) {
     RowTiling t;
-    t.c8n = C >> 3;
-    t.lanes = blockDim.x / t.c8n;
+    const int total = C >> 3;
+    const int per = total < 32 ? total : 32;
+    t.c8_0 = blockIdx.y * per;
+    t.c8n = min(per, total - t.c8_0);
+    t.lanes = blockDim.x / per;
     return t;
 }
 
@@ -43,18 +50,21 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const __nv_bfloat16* __r
                                                         const float* __restrict__ mean_rstd, float* __restrict__ sums, long long M, int C, int mode,
                                                         int relu) {
     pdl_prologue();
-    extern __shared__ float ssum[];  // [2C]
-    for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) ssum[i] = 0.f;
+    extern __shared__ float ssum[];  // [2 * 256]: this block's channel slab
+    for (int i = threadIdx.x; i < 512; i += blockDim.x) ssum[i] = 0.f;
     __syncthreads();
     const RowTiling t = row_tiling(C);
-    const int tx = threadIdx.x % t.c8n, ty = threadIdx.x / t.c8n;
+    const int per = (C >> 3) < 32 ? (C >> 3) : 32;
+    const int txl = threadIdx.x % per, ty = threadIdx.x / per;
+    const int tx = t.c8_0 + txl;                       // global channel group
+    const bool live = ty < t.lanes && txl < t.c8n;
     float s1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     float mu[8], rs[8];
-    if (mode == 1 && ty < t.lanes) {
+    if (mode == 1 && live) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) { mu[j] = mean_rstd[tx * 8 + j]; rs[j] = mean_rstd[C + tx * 8 + j]; }
     }
-    if (ty < t.lanes) {
+    if (live) {
         // kU rows per trip, every load issued before the first use: the kernel is a pure stream and lives on loads in flight
         constexpr int kU = 4;
         const long long rstride = 1ll * gridDim.x * t.lanes;
@@ -98,12 +108,15 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const __nv_bfloat16* __r
         }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            atomicAdd(&ssum[tx * 8 + j], s1[j]);
-            atomicAdd(&ssum[C + tx * 8 + j], s2[j]);
+            atomicAdd(&ssum[txl * 8 + j], s1[j]);
+            atomicAdd(&ssum[256 + txl * 8 + j], s2[j]);
         }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) red_add_f32(sums + i, ssum[i]);
+    for (int i = threadIdx.x; i < t.c8n * 8; i += blockDim.x) {
+        red_add_f32(sums + t.c8_0 * 8 + i, ssum[i]);
+        red_add_f32(sums + C + t.c8_0 * 8 + i, ssum[256 + i]);
+    }
 }
 
 // Forward normalisation.  stats: if `sums` != null the batch statistics are derived from it (training) and written to
@@ -117,8 +130,10 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
                                                        float eps, float momentum, int relu) {
     pdl_prologue();
     const RowTiling t = row_tiling(C);
-    const int tx = threadIdx.x % t.c8n, ty = threadIdx.x / t.c8n;
-    if (ty >= t.lanes) return;
+    const int per = (C >> 3) < 32 ? (C >> 3) : 32;
+    const int txl = threadIdx.x % per, ty = threadIdx.x / per;
+    if (ty >= t.lanes || txl >= t.c8n) return;
+    const int tx = t.c8_0 + txl;
     float sc[8], sh[8];
     const float inv_m = 1.f / static_cast<float>(M);
 #pragma unroll
@@ -187,8 +202,10 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
                                                            float* __restrict__ dgamma, float* __restrict__ dbeta, long long M, int C) {
     pdl_prologue();
     const RowTiling t = row_tiling(C);
-    const int tx = threadIdx.x % t.c8n, ty = threadIdx.x / t.c8n;
-    if (ty >= t.lanes) return;
+    const int per = (C >> 3) < 32 ? (C >> 3) : 32;
+    const int txl = threadIdx.x % per, ty = threadIdx.x / per;
+    if (ty >= t.lanes || txl >= t.c8n) return;
+    const int tx = t.c8_0 + txl;
     float mu[8], rs[8], k0[8], k1[8], k2[8];
     const float inv_m = 1.f / static_cast<float>(M);
 #pragma unroll
@@ -270,13 +287,16 @@ __global__ void __launch_bounds__(256) avgpool_bwd_kernel(const __nv_bfloat16* _
     }
 }
 
-static inline int rows_grid(long long M, int C) {
-    const int lanes = 256 / (C / 8);
-    long long blocks = (M + lanes - 1) / lanes;
-    const long long cap = 148ll * 8;
-    if (blocks > cap) blocks = cap;
-    if (blocks < 1) blocks = 1;
-    return static_cast<int>(blocks);
+static inline dim3 rows_grid(long long M, int C) {
+    const int total = C / 8;
+    const int per = total < 32 ? total : 32;
+    const int slabs = (total + per - 1) / per;
+    const int lanes = 256 / per;
+    long long gx = (M + 1ll * lanes * 16 - 1) / (1ll * lanes * 16);     // >= 16 rows per thread before the block reduces
+    const long long cap = (148ll * 8 + slabs - 1) / slabs;
+    if (gx > cap) gx = cap;
+    if (gx < 1) gx = 1;
+    return dim3(static_cast<unsigned>(gx), static_cast<unsigned>(slabs), 1);
 }
 
 }  // namespace dmlb
@@ -288,7 +308,7 @@ using namespace dmlb;
 // sums: fp32 [2C], zero on entry.
 extern "C" int dmlb_bn_stats(const void* x, int ldx, float* sums, long long M, int C, void* stream) {
     DMLB_REQUIRE(BN_SHAPE_OK(C) && ldx % 8 == 0, "batch-norm kernels need C % 8 == 0, C <= 2048 and 16-byte rows");
-    DMLB_CHECK_CUDA(launch_k(bn_reduce_kernel, rows_grid(M, C), 256, 2 * C * sizeof(float), static_cast<cudaStream_t>(stream),
+    DMLB_CHECK_CUDA(launch_k(bn_reduce_kernel, rows_grid(M, C), 256, 512 * sizeof(float), static_cast<cudaStream_t>(stream),
                              static_cast<const __nv_bfloat16*>(x), ldx, static_cast<const __nv_bfloat16*>(nullptr), 0,
                              static_cast<const __nv_bfloat16*>(nullptr), 0, static_cast<__nv_bfloat16*>(nullptr), 0,
                              static_cast<const float*>(nullptr), sums, M, C, 0, 0));
@@ -312,7 +332,7 @@ extern "C" int dmlb_bn_apply(const void* x, int ldx, void* y, int ldy, const voi
 extern "C" int dmlb_bn_bwd_reduce(const void* x, int ldx, const void* dy, int lddy, const void* yact, int ldya, void* g_out, int ldg,
                                   const float* mean_rstd, float* dsum, long long M, int C, int relu, void* stream) {
     DMLB_REQUIRE(BN_SHAPE_OK(C) && ldx % 8 == 0 && lddy % 8 == 0, "batch-norm kernels need C % 8 == 0, C <= 2048 and 16-byte rows");
-    DMLB_CHECK_CUDA(launch_k(bn_reduce_kernel, rows_grid(M, C), 256, 2 * C * sizeof(float), static_cast<cudaStream_t>(stream),
+    DMLB_CHECK_CUDA(launch_k(bn_reduce_kernel, rows_grid(M, C), 256, 512 * sizeof(float), static_cast<cudaStream_t>(stream),
                              static_cast<const __nv_bfloat16*>(x), ldx, static_cast<const __nv_bfloat16*>(dy), lddy,
                              static_cast<const __nv_bfloat16*>(yact), ldya, static_cast<__nv_bfloat16*>(g_out), ldg, mean_rstd, dsum, M, C, 1, relu));
     DMLB_LAUNCH_CHECK();
