@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
                                                        const float* __restrict__ mean_rstd_in, const float* __restrict__ gamma,
                                                        const float* __restrict__ beta, float* __restrict__ save_mean_rstd,
                                                        float* __restrict__ running_mean, float* __restrict__ running_var, long long M, int C,
-                                                       float eps, float momentum, int relu) {
+                                                       float eps, float momentum, int relu, float* __restrict__ zero_2c) {
     pdl_prologue();
     const RowTiling t = row_tiling(C);
     const int per = (C >> 3) < 32 ? (C >> 3) : 32;
@@ -145,6 +145,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
             const float var = fmaxf(sums[C + c] * inv_m - mean * mean, 0.f);
             rstd = rsqrtf(var + eps);
             if (blockIdx.x == 0 && ty == 0) {
+                if (zero_2c != nullptr) { zero_2c[c] = 0.f; zero_2c[C + c] = 0.f; }   // leaves the backward scratch clean (no memset launch)
                 save_mean_rstd[c] = mean;
                 save_mean_rstd[C + c] = rstd;
                 if (running_mean != nullptr) {
@@ -199,7 +200,8 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ x, int ldx, const __nv_bfloat16* __restrict__ g,
                                                            int ldg, __nv_bfloat16* __restrict__ dx, int lddx, const float* __restrict__ mean_rstd,
                                                            const float* __restrict__ gamma, const float* __restrict__ dsum,
-                                                           float* __restrict__ dgamma, float* __restrict__ dbeta, long long M, int C) {
+                                                           float* __restrict__ dgamma, float* __restrict__ dbeta, long long M, int C,
+                                                           float* __restrict__ zero_2c) {
     pdl_prologue();
     const RowTiling t = row_tiling(C);
     const int per = (C >> 3) < 32 ? (C >> 3) : 32;
@@ -218,6 +220,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
         k1[j] = dsum[c] * inv_m;
         k2[j] = dsum[C + c] * inv_m;
         if (blockIdx.x == 0 && ty == 0) {
+            if (zero_2c != nullptr) { zero_2c[c] = 0.f; zero_2c[C + c] = 0.f; }       // leaves the forward statistics scratch clean
             if (dgamma != nullptr) dgamma[c] += dsum[C + c];
             if (dbeta != nullptr) dbeta[c] += dsum[c];
         }
@@ -318,12 +321,12 @@ extern "C" int dmlb_bn_stats(const void* x, int ldx, float* sums, long long M, i
 
 extern "C" int dmlb_bn_apply(const void* x, int ldx, void* y, int ldy, const void* res, int ldr, const float* sums, const float* mean_rstd_in,
                              const float* gamma, const float* beta, float* save_mean_rstd, float* running_mean, float* running_var, long long M,
-                             int C, float eps, float momentum, int relu, void* stream) {
+                             int C, float eps, float momentum, int relu, float* zero_2c, void* stream) {
     DMLB_REQUIRE(BN_SHAPE_OK(C) && ldx % 8 == 0 && ldy % 8 == 0, "batch-norm kernels need C % 8 == 0, C <= 2048 and 16-byte rows");
     DMLB_REQUIRE(sums != nullptr || mean_rstd_in != nullptr, "either batch sums or prepared statistics are required");
     DMLB_CHECK_CUDA(launch_k(bn_apply_kernel, rows_grid(M, C), 256, 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(x), ldx,
                              static_cast<__nv_bfloat16*>(y), ldy, static_cast<const __nv_bfloat16*>(res), ldr, sums, mean_rstd_in, gamma, beta,
-                             save_mean_rstd, running_mean, running_var, M, C, eps, momentum, relu));
+                             save_mean_rstd, running_mean, running_var, M, C, eps, momentum, relu, zero_2c));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
@@ -340,11 +343,11 @@ extern "C" int dmlb_bn_bwd_reduce(const void* x, int ldx, const void* dy, int ld
 }
 
 extern "C" int dmlb_bn_bwd_apply(const void* x, int ldx, const void* g, int ldg, void* dx, int lddx, const float* mean_rstd, const float* gamma,
-                                 const float* dsum, float* dgamma, float* dbeta, long long M, int C, void* stream) {
+                                 const float* dsum, float* dgamma, float* dbeta, long long M, int C, float* zero_2c, void* stream) {
     DMLB_REQUIRE(BN_SHAPE_OK(C) && ldx % 8 == 0 && ldg % 8 == 0 && lddx % 8 == 0, "batch-norm kernels need C % 8 == 0, C <= 2048 and 16-byte rows");
     DMLB_CHECK_CUDA(launch_k(bn_bwd_apply_kernel, rows_grid(M, C), 256, 0, static_cast<cudaStream_t>(stream), static_cast<const __nv_bfloat16*>(x),
                              ldx, static_cast<const __nv_bfloat16*>(g), ldg, static_cast<__nv_bfloat16*>(dx), lddx, mean_rstd, gamma, dsum, dgamma,
-                             dbeta, M, C));
+                             dbeta, M, C, zero_2c));
     DMLB_LAUNCH_CHECK();
     return 0;
 }

@@ -50,9 +50,9 @@ _SIGNATURES = {
     "dmlb_dropout_bwd_bf16": [c_vp, c_vp, c_vp, c_ll, c_int, c_int, c_int, c_float, c_vp],
     "dmlb_counter_bump": [c_vp, c_vp],
     "dmlb_bn_stats": [c_vp, c_int, c_vp, c_ll, c_int, c_vp],
-    "dmlb_bn_apply": [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_ll, c_int, c_float, c_float, c_int, c_vp],
+    "dmlb_bn_apply": [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_ll, c_int, c_float, c_float, c_int, c_vp, c_vp],
     "dmlb_bn_bwd_reduce": [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_ll, c_int, c_int, c_vp],
-    "dmlb_bn_bwd_apply": [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_ll, c_int, c_vp],
+    "dmlb_bn_bwd_apply": [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_ll, c_int, c_vp, c_vp],
     "dmlb_avgpool_fwd_bf16": [c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_vp],
     "dmlb_avgpool_bwd_bf16": [c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_vp],
 }

@@ -322,11 +322,12 @@ class BatchNorm2d(nn.Module):
         self._wsink = None
         self._bsink = None
         self._arena_slot = None
+        self._state = {}                  # persistent statistics scratch of the CUDA kernels
 
     def forward(self, x, residual=None):
         # num_batches_tracked is bookkeeping only (momentum is fixed); it is not bumped on the CUDA-graph path
         return OF.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var, self.training, self.momentum, self.eps,
-                             residual=residual, relu=self.activation == "relu", wsink=self._wsink, bsink=self._bsink)
+                             residual=residual, relu=self.activation == "relu", wsink=self._wsink, bsink=self._bsink, state=self._state)
 
     def extra_repr(self):
         return f"{self.num_features}, eps={self.eps}, momentum={self.momentum}, activation={self.activation}"

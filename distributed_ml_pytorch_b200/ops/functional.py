@@ -673,11 +673,22 @@ class _BatchNormFn(torch.autograd.Function):
             residual, ldr = as_act4(residual)
             res_ptr = residual.data_ptr()
         y = new_act4(B, C, H, W, dev)
-        sums = torch.zeros(2 * C, dtype=torch.float32, device=dev)
+        # Persistent per-layer scratch [sums | dsum]: each half is re-zeroed by the kernel that runs after its consumer
+        # (bn_apply cleans dsum, bn_bwd_apply cleans sums), so a training step launches no memsets for batch norm.
+        scratch = cfg.state.get("scratch")
+        if scratch is None or scratch.device != dev or scratch.numel() != 4 * C:
+            scratch = torch.zeros(4 * C, dtype=torch.float32, device=dev)
+            cfg.state["scratch"] = scratch
+            cfg.state["sums_clean"] = True
+        sums, dsum = scratch[: 2 * C], scratch[2 * C:]
+        if not cfg.state.get("sums_clean", False):
+            sums.zero_()                 # a forward without a backward (e.g. train-mode evaluation) left statistics behind
         save = torch.empty(2 * C, dtype=torch.float32, device=dev)
         K.bn_stats(x.data_ptr(), ldx, sums, M, C)
         K.bn_apply(x.data_ptr(), ldx, y.data_ptr(), pad8(C), res_ptr, ldr, sums, None, weight, bias, save, cfg.running_mean, cfg.running_var, M, C,
-                   cfg.eps, cfg.momentum, cfg.relu)
+                   cfg.eps, cfg.momentum, cfg.relu, zero=dsum)
+        cfg.state["sums_clean"] = False
+        ctx.scratch = scratch
         ctx.cfg = cfg
         ctx.dims = (B, C, H, W, ldx)
         ctx.has_res = residual is not None
@@ -693,7 +704,7 @@ class _BatchNormFn(torch.autograd.Function):
         dev = dout.device
         dout, ldd = as_act4(dout)
         ldc = pad8(C)
-        dsum = torch.zeros(2 * C, dtype=torch.float32, device=dev)
+        sums, dsum = ctx.scratch[: 2 * C], ctx.scratch[2 * C:]
         need_g = cfg.relu or ctx.has_res
         g = new_act4(B, C, H, W, dev) if need_g else dout
         K.bn_bwd_reduce(x.data_ptr(), ldx, dout.data_ptr(), ldd, y.data_ptr() if y is not None else 0, ldc, g.data_ptr() if need_g else 0, ldc,
@@ -705,7 +716,8 @@ class _BatchNormFn(torch.autograd.Function):
         gb = torch.zeros(C, dtype=torch.float32, device=dev) if (bias is not None and bsink is None) else None
         dx = new_act4(B, C, H, W, dev)
         K.bn_bwd_apply(x.data_ptr(), ldx, g.data_ptr(), ldg, dx.data_ptr(), ldc, save, weight, dsum, wsink if wsink is not None else gw,
-                       bsink if bsink is not None else gb, M, C)
+                       bsink if bsink is not None else gb, M, C, zero=sums)
+        cfg.state["sums_clean"] = True
         if wsink is not None:
             _notify_grad_ready(weight, dev)
         if bsink is not None:
@@ -734,7 +746,7 @@ class _BatchNormEvalFn(torch.autograd.Function):
 
 
 def batch_norm(x, weight, bias, running_mean, running_var, training=True, momentum=0.1, eps=1e-5, residual=None, relu=False, wsink=None,
-               bsink=None):
+               bsink=None, state=None):
     """``relu(batch_norm(x) + residual)`` (residual / ReLU optional) in two kernels forward, two backward."""
     if not x.is_cuda or x.shape[1] % 8 != 0 or x.shape[1] > 2048:
         y = F.batch_norm(x.float() if x.is_cuda else x, running_mean, running_var, weight, bias, training, momentum, eps)
@@ -742,7 +754,8 @@ def batch_norm(x, weight, bias, running_mean, running_var, training=True, moment
             y = y + residual
         y = F.relu(y) if relu else y
         return y.to(x.dtype) if x.is_cuda else y
-    cfg = SimpleNamespace(running_mean=running_mean, running_var=running_var, eps=eps, momentum=momentum, relu=bool(relu), wsink=wsink, bsink=bsink)
+    cfg = SimpleNamespace(running_mean=running_mean, running_var=running_var, eps=eps, momentum=momentum, relu=bool(relu), wsink=wsink, bsink=bsink,
+                          state=state if state is not None else {})
     if training:
         return _BatchNormFn.apply(x, residual, weight, bias, cfg)
     return _BatchNormEvalFn.apply(x, residual, weight, bias, cfg)

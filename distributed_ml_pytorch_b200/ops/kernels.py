@@ -171,9 +171,9 @@ def bn_stats(x_ptr, ldx, sums: torch.Tensor, M, C) -> None:
 
 
 def bn_apply(x_ptr, ldx, y_ptr, ldy, res_ptr, ldr, sums, mean_rstd_in, gamma, beta, save, running_mean, running_var, M, C, eps, momentum,
-             relu) -> None:
+             relu, zero=None) -> None:
     _call("dmlb_bn_apply", x_ptr, ldx, y_ptr, ldy, res_ptr or None, ldr, _p(sums), _p(mean_rstd_in), _p(gamma), _p(beta), _p(save),
-          _p(running_mean), _p(running_var), M, C, float(eps), float(momentum), int(relu), stream_ptr())
+          _p(running_mean), _p(running_var), M, C, float(eps), float(momentum), int(relu), _p(zero), stream_ptr())
 
 
 def bn_bwd_reduce(x_ptr, ldx, dy_ptr, lddy, yact_ptr, ldya, g_ptr, ldg, mean_rstd, dsum, M, C, relu) -> None:
@@ -181,9 +181,9 @@ def bn_bwd_reduce(x_ptr, ldx, dy_ptr, lddy, yact_ptr, ldya, g_ptr, ldg, mean_rst
           int(relu), stream_ptr())
 
 
-def bn_bwd_apply(x_ptr, ldx, g_ptr, ldg, dx_ptr, lddx, mean_rstd, gamma, dsum, dgamma, dbeta, M, C) -> None:
+def bn_bwd_apply(x_ptr, ldx, g_ptr, ldg, dx_ptr, lddx, mean_rstd, gamma, dsum, dgamma, dbeta, M, C, zero=None) -> None:
     _call("dmlb_bn_bwd_apply", x_ptr, ldx, g_ptr, ldg, dx_ptr, lddx, mean_rstd.data_ptr(), _p(gamma), dsum.data_ptr(), _p(dgamma), _p(dbeta), M, C,
-          stream_ptr())
+          _p(zero), stream_ptr())
 
 
 def avgpool_fwd(x_ptr, ldx, y_ptr, ldy, B, P, C) -> None:

@@ -117,14 +117,16 @@ int dmlb_counter_bump(void* counter, void* stream);
  * bf16 channels-last rows [M, ld]; C % 8 == 0, C <= 2048.  sums / dsum are fp32 [2C] and must be zero on entry. */
 int dmlb_bn_stats(const void* x, int ldx, float* sums, long long M, int C, void* stream);
 /* y = act((x - mean) * rstd * gamma + beta [+ res]); training: statistics from `sums` (saved to save_mean_rstd [2C], folded
- * into running_mean / running_var); inference: sums = NULL and mean_rstd_in = {running_mean, 1/sqrt(running_var + eps)}. */
+ * into running_mean / running_var); inference: sums = NULL and mean_rstd_in = {running_mean, 1/sqrt(running_var + eps)}.
+ * zero_2c (may be NULL): an fp32 [2C] scratch this launch resets to zero — bn_apply cleans the backward scratch, bn_bwd_apply the
+ * forward one, so a training step needs no memset launches for them. */
 int dmlb_bn_apply(const void* x, int ldx, void* y, int ldy, const void* res, int ldr, const float* sums, const float* mean_rstd_in,
                   const float* gamma, const float* beta, float* save_mean_rstd, float* running_mean, float* running_var, long long M, int C,
-                  float eps, float momentum, int relu, void* stream);
+                  float eps, float momentum, int relu, float* zero_2c, void* stream);
 int dmlb_bn_bwd_reduce(const void* x, int ldx, const void* dy, int lddy, const void* yact, int ldya, void* g_out, int ldg,
                        const float* mean_rstd, float* dsum, long long M, int C, int relu, void* stream);
 int dmlb_bn_bwd_apply(const void* x, int ldx, const void* g, int ldg, void* dx, int lddx, const float* mean_rstd, const float* gamma,
-                      const float* dsum, float* dgamma, float* dbeta, long long M, int C, void* stream);
+                      const float* dsum, float* dgamma, float* dbeta, long long M, int C, float* zero_2c, void* stream);
 int dmlb_avgpool_fwd_bf16(const void* x, int ldx, void* y, int ldy, int B, int P, int C, void* stream);
 int dmlb_avgpool_bwd_bf16(const void* dy, int lddy, void* dx, int lddx, int B, int P, int C, void* stream);
 
