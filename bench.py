@@ -201,7 +201,9 @@ def make_optimizer(args, model, rank, world, device):
     except ImportError:
         return FusedSGD(model.parameters(), lr=LR, model=model), "single-gpu fused SGD"
     if args.mode == "sync":
-        return Synchronous(model.parameters(), lr=LR, model=model, momentum=args.momentum), f"sync-dp{world} fused reduce-scatter+update+all-gather"
+        opt = Synchronous(model.parameters(), lr=LR, model=model, momentum=args.momentum)
+        how = "NVLS multimem.ld_reduce/multimem.st" if getattr(opt, "nvls", False) else "NVLink peer loads/stores"
+        return opt, f"sync-dp{world} fused reduce-scatter+update+all-gather ({how}), 4 buckets overlapped with backward"
     opt = Asynchronous(model.parameters(), lr=LR, n_push=N_PUSH, n_pull=N_PULL, model=model, momentum=args.momentum, staleness=args.staleness)
     return opt, f"async-ps dp{world}, parameter server sharded over {world} GPU(s), fused NVLink push/pull"
 

@@ -255,6 +255,58 @@ __global__ void __launch_bounds__(512) sync_rs_update_ag_kernel(PeerTable grads,
     }
 }
 
+// K4 through NVLS: the reduce-scatter is ONE multimem.ld_reduce per 16 bytes (the NVSwitch adds the replicas) and the all-gather
+// ONE multimem.st (the switch replicates it), so each GPU moves n/world in and n/world out instead of (world-1)/world * n each way.
+//   mc_grads / mc_params: multicast addresses of the gradient / parameter arenas;  params_local: this GPU's own replica.
+__global__ void __launch_bounds__(512) sync_nvls_kernel(const float* __restrict__ mc_grads, float* __restrict__ mc_params,
+                                                        const float* __restrict__ params_local, PeerTable flags, float* __restrict__ mom, int rank,
+                                                        int world, long long base, long long slice_len, const float* __restrict__ lr_ptr, float mu,
+                                                        float wd, float grad_scale) {
+    uint32_t* my_flags = static_cast<uint32_t*>(flags.ptr[rank]);
+    const uint32_t epoch = my_flags[2 * kMaxPeers] + 1u;
+    if (blockIdx.x == 0 && threadIdx.x < world) st_release_sys_u32(static_cast<uint32_t*>(flags.ptr[threadIdx.x]) + rank, epoch);
+    if (threadIdx.x < world) spin_until_ge(my_flags + threadIdx.x, epoch);
+    __syncthreads();
+
+    const float lr = *lr_ptr;
+    const long long n4 = slice_len / 4;
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
+        float4 g = multimem_ld_reduce_add_f32x4(mc_grads + base + 4 * i);
+        g.x *= grad_scale; g.y *= grad_scale; g.z *= grad_scale; g.w *= grad_scale;
+        float4 p = reinterpret_cast<const float4*>(params_local + base)[i];
+        if (wd != 0.f) { g.x += wd * p.x; g.y += wd * p.y; g.z += wd * p.z; g.w += wd * p.w; }
+        if (mom != nullptr) {
+            float4 v = reinterpret_cast<float4*>(mom)[i];
+            v.x = mu * v.x + g.x; v.y = mu * v.y + g.y; v.z = mu * v.z + g.z; v.w = mu * v.w + g.w;
+            reinterpret_cast<float4*>(mom)[i] = v;
+            g = v;
+        }
+        p.x -= lr * g.x; p.y -= lr * g.y; p.z -= lr * g.z; p.w -= lr * g.w;
+        multimem_st_f32x4(mc_params + base + 4 * i, p);
+    }
+
+    __syncthreads();
+    __shared__ bool s_last;
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        const uint32_t done = atomicAdd(&my_flags[2 * kMaxPeers + 1], 1u);
+        s_last = (done == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (s_last) {
+        if (threadIdx.x < world) {
+            st_release_sys_u32(static_cast<uint32_t*>(flags.ptr[threadIdx.x]) + kMaxPeers + rank, epoch);
+            spin_until_ge(my_flags + kMaxPeers + threadIdx.x, epoch);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            my_flags[2 * kMaxPeers + 1] = 0u;
+            my_flags[2 * kMaxPeers] = epoch;
+            __threadfence();
+        }
+    }
+}
+
 static inline int comm_grid(long long work_items, int threads) {
     long long blocks = (work_items + threads - 1) / threads;
     const long long cap = dmlb_sm_count() * 2ll;
@@ -358,4 +410,21 @@ extern "C" int dmlb_sync_rs_update_ag(void* const* grad_ptrs, void* const* param
                                       long long shard_size, const float* lr_ptr, float mu, float wd, float grad_scale, void* stream) {
     return dmlb_sync_rs_update_ag_range(grad_ptrs, param_ptrs, flag_ptrs, mom, rank, world, static_cast<long long>(rank) * shard_size, shard_size,
                                         lr_ptr, mu, wd, grad_scale, 0, stream);
+}
+
+// NVLS form of the range kernel: mc_grads / mc_params are multicast addresses (torch symmetric memory or any cuMulticast mapping).
+extern "C" int dmlb_sync_nvls_range(const float* mc_grads, float* mc_params, const float* params_local, void* const* flag_ptrs, float* mom,
+                                    int rank, int world, long long base, long long n, const float* lr_ptr, float mu, float wd, float grad_scale,
+                                    int max_blocks, void* stream) {
+    DMLB_REQUIRE(n % 4 == 0 && base % 4 == 0 && n > 0, "slice must be non-empty and 16-byte aligned");
+    DMLB_REQUIRE(mc_grads != nullptr && mc_params != nullptr, "multicast addresses are required");
+    PeerTable f;
+    if (fill_table(&f, flag_ptrs, world)) return -2;
+    int blocks = comm_grid(n / 4, 512);
+    if (blocks > dmlb_sm_count()) blocks = dmlb_sm_count();
+    if (max_blocks > 0 && blocks > max_blocks) blocks = max_blocks;
+    sync_nvls_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(mc_grads, mc_params, params_local, f, mom, rank, world, base, n, lr_ptr,
+                                                                           mu, wd, grad_scale);
+    DMLB_LAUNCH_CHECK();
+    return 0;
 }

@@ -227,6 +227,16 @@ __device__ __forceinline__ uint32_t ld_relaxed_sys_u32(const uint32_t* p) {
 __device__ __forceinline__ void red_release_sys_add_u32(uint32_t* p, uint32_t v) {
     asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+// NVLS (NVSwitch multicast): one load returns the sum over every replica mapped behind the multicast address (reduced in the
+// switch), one store lands in every replica.
+__device__ __forceinline__ float4 multimem_ld_reduce_add_f32x4(const float* mc) {
+    float4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(mc) : "memory");
+    return r;
+}
+__device__ __forceinline__ void multimem_st_f32x4(float* mc, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
 // Streaming 16-byte accesses that do not pollute L1 (flat arenas are touched once per step).
 __device__ __forceinline__ float4 ld_stream_f32x4(const float* p) {
     float4 r;

@@ -34,6 +34,7 @@ _native.register("dmlb_pull", [c_vp, c_vp, _PP, _PP, c_vp, c_int, c_ll, c_ll, c_
 _native.register("dmlb_push_mailbox", [c_vp, c_vp, c_vp, _PP, _PP, c_int, c_int, c_ll, c_vp])
 _native.register("dmlb_owner_apply", [c_vp, c_vp, c_vp, c_vp, c_vp, _PP, c_vp, c_int, c_int, c_ll, c_float, c_int, c_float, c_vp])
 _native.register("dmlb_sync_rs_update_ag", [_PP, _PP, _PP, c_vp, c_int, c_int, c_ll, c_vp, c_float, c_float, c_float, c_vp])
+_native.register("dmlb_sync_nvls_range", [c_vp, c_vp, c_vp, _PP, c_vp, c_int, c_int, c_ll, c_ll, c_vp, c_float, c_float, c_float, c_int, c_vp])
 _native.register("dmlb_sync_rs_update_ag_range", [_PP, _PP, _PP, c_vp, c_int, c_int, c_ll, c_ll, c_vp, c_float, c_float, c_float, c_int, c_vp])
 
 
@@ -178,3 +179,28 @@ def sync_rs_update_ag(grad_table, param_table, flag_table, mom, rank, world, sha
 def sync_rs_update_ag_range(grad_table, param_table, flag_table, mom_ptr: int, rank, world, base, n, lr_dev, mu, wd, grad_scale, max_blocks=0) -> None:
     _native.call("dmlb_sync_rs_update_ag_range", grad_table, param_table, flag_table, mom_ptr or None, rank, world, base, n, lr_dev.data_ptr(),
                  float(mu), float(wd), float(grad_scale), int(max_blocks), _stream())
+
+
+def sync_nvls_range(mc_grads: int, mc_params: int, params_local: torch.Tensor, flag_table, mom_ptr: int, rank, world, base, n, lr_dev, mu, wd,
+                    grad_scale, max_blocks=0) -> None:
+    _native.call("dmlb_sync_nvls_range", mc_grads, mc_params, params_local.data_ptr(), flag_table, mom_ptr or None, rank, world, base, n,
+                 lr_dev.data_ptr(), float(mu), float(wd), float(grad_scale), int(max_blocks), _stream())
+
+
+class SymmMemBuffer:
+    """A symmetric buffer obtained from ``torch.distributed._symmetric_memory`` (used for plumbing only): besides the peer
+    pointers it exposes ``mc_ptr``, the NVLS multicast address of the buffer (0 when the fabric offers no multicast)."""
+
+    def __init__(self, nbytes: int, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        group = group if group is not None else dist.group.WORLD
+        self.local = symm_mem.empty((int(nbytes) + 255) // 256 * 256, dtype=torch.uint8, device=device)
+        self.local.zero_()
+        self.handle = symm_mem.rendezvous(self.local, group=group)
+        self.ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        self.mc_ptr = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+        self.table = (ctypes.c_void_p * len(self.ptrs))(*self.ptrs)
+
+    def view(self, dtype: torch.dtype, numel: Optional[int] = None, offset_bytes: int = 0) -> torch.Tensor:
+        t = self.local[offset_bytes:].view(dtype)
+        return t if numel is None else t[:numel]

@@ -13,6 +13,9 @@ travels over NVLink while the earlier layers are still differentiating.  Inside 
 All of this is capturable: in :class:`~distributed_ml_pytorch_b200.engine.TrainStep` the bucket kernels are parallel
 branches of the step's CUDA graph.
 
+NVLS: when the arenas can be mapped behind an NVSwitch multicast address (``nvls=None`` = use it when available), the
+reduce-scatter is one ``multimem.ld_reduce`` per 16 bytes (summed inside the switch) and the all-gather one ``multimem.st``.
+
 On CPU tensors (gloo) the same optimizer falls back to ``dist.all_reduce`` + an in-place update.
 """
 from __future__ import annotations
@@ -39,7 +42,7 @@ class _Bucket:
 
 class Synchronous(ArenaOptimizer):
     def __init__(self, params, lr: float, model: torch.nn.Module, momentum: float = 0.0, weight_decay: float = 0.0, group=None,
-                 overlap: bool = True, n_buckets: int = 4, comm_blocks: int = 48):
+                 overlap: bool = True, n_buckets: int = 4, comm_blocks: int = 48, nvls: Optional[bool] = None):
         if lr < 0.0:
             raise ValueError("Invalid learning rate: {}".format(lr))
         device = next(model.parameters()).device
@@ -55,9 +58,27 @@ class Synchronous(ArenaOptimizer):
             world = self.peer.world
             shard = ((n + world - 1) // world + 255) // 256 * 256
             padded = shard * world
-            self.params_sym = self.peer.symmetric(padded * 4)
-            self.grads_sym = self.peer.symmetric(padded * 4)
-            self.flags_sym = self.peer.symmetric(peer.flag_words() * 4)
+            # Symmetric arenas.  With more than one rank they come from torch's symmetric-memory allocator (plumbing only), which
+            # also maps them behind an NVLS multicast address when the NVSwitch fabric offers one; then the reduce-scatter and
+            # the all-gather run inside the switch (multimem.ld_reduce / multimem.st).  Otherwise: CUDA-IPC buffers, peer loads/stores.
+            self.nvls = False
+            self.params_sym = self.grads_sym = self.flags_sym = None
+            if world > 1 and nvls is not False:
+                try:
+                    self.params_sym = peer.SymmMemBuffer(padded * 4, device, group)
+                    self.grads_sym = peer.SymmMemBuffer(padded * 4, device, group)
+                    self.flags_sym = peer.SymmMemBuffer(peer.flag_words() * 4, device, group)
+                    self.nvls = bool(self.params_sym.mc_ptr and self.grads_sym.mc_ptr)
+                except Exception as exc:          # allocator or fabric without symmetric-memory support
+                    if nvls:
+                        raise
+                    self.params_sym = self.grads_sym = self.flags_sym = None
+            if nvls and not self.nvls:
+                raise RuntimeError("NVLS multicast was requested but is not available on this fabric")
+            if self.params_sym is None:
+                self.params_sym = self.peer.symmetric(padded * 4)
+                self.grads_sym = self.peer.symmetric(padded * 4)
+                self.flags_sym = self.peer.symmetric(peer.flag_words() * 4)
             arena = FlatArena(model, n_shards=world, params_storage=self.params_sym.view(torch.float32, padded),
                               grads_storage=self.grads_sym.view(torch.float32, padded))
             assert arena.shards.shard_size == shard
@@ -128,10 +149,16 @@ class Synchronous(ArenaOptimizer):
         n = (b.end - b.begin) // self.world
         base = b.begin + self.peer.rank * n
         mom_ptr = self.momentum_buf.data_ptr() + 4 * base if self.momentum_buf is not None else 0
+        blocks = self.comm_blocks if self.overlap else 0
         with torch.cuda.stream(self.comm_stream):
-            peer.sync_rs_update_ag_range(self.grads_sym.table, self.params_sym.table, self.flags_sym.table, mom_ptr, self.peer.rank, self.world,
-                                         base, n, self.lr_dev, g["momentum"], g["weight_decay"], 1.0 / self.world,
-                                         max_blocks=self.comm_blocks if self.overlap else 0)
+            if self.nvls:
+                peer.sync_nvls_range(self.grads_sym.mc_ptr, self.params_sym.mc_ptr, self.arena.params, self.flags_sym.table, mom_ptr,
+                                     self.peer.rank, self.world, base, n, self.lr_dev, g["momentum"], g["weight_decay"], 1.0 / self.world,
+                                     max_blocks=blocks)
+            else:
+                peer.sync_rs_update_ag_range(self.grads_sym.table, self.params_sym.table, self.flags_sym.table, mom_ptr, self.peer.rank,
+                                             self.world, base, n, self.lr_dev, g["momentum"], g["weight_decay"], 1.0 / self.world,
+                                             max_blocks=blocks)
         b.launched = True
 
     # ------------------------------------------------------------------------------------------

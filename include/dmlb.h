@@ -162,6 +162,11 @@ int dmlb_sync_rs_update_ag_range(void* const* grad_ptrs, void* const* param_ptrs
                                  long long base, long long n, const float* lr_ptr, float mu, float wd, float grad_scale, int max_blocks,
                                  void* stream);
 
+/* The same step through NVLS: multimem.ld_reduce (reduction inside the NVSwitch) + multimem.st (multicast) on multicast addresses. */
+int dmlb_sync_nvls_range(const float* mc_grads, float* mc_params, const float* params_local, void* const* flag_ptrs, float* mom, int rank,
+                         int world, long long base, long long n, const float* lr_ptr, float mu, float wd, float grad_scale, int max_blocks,
+                         void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -126,11 +126,14 @@ def _need(n):
         pytest.skip(f"needs {n} GPUs")
 
 
-def _mgpu_sync(rank, size, out_dir, steps):
+def _mgpu_sync(rank, size, out_dir, steps, nvls=None):
     dev = torch.device("cuda", rank)
     torch.manual_seed(0)
     net = build_model("lenet").to(dev).eval()
-    opt = Synchronous(net.parameters(), lr=0.05, model=net, momentum=0.9)
+    opt = Synchronous(net.parameters(), lr=0.05, model=net, momentum=0.9, nvls=nvls)
+    if rank == 0:
+        with open(os.path.join(out_dir, "nvls.txt"), "w") as f:
+            f.write(str(opt.nvls))
     for i in range(steps):
         x, y = _batch(10 * i + rank, dev=dev)
         opt.zero_grad()
@@ -140,11 +143,13 @@ def _mgpu_sync(rank, size, out_dir, steps):
     torch.save(ravel_model_params(net).cpu().clone(), os.path.join(out_dir, f"sync{rank}.pt"))
 
 
-@pytest.mark.parametrize("world", [2, 4, 8])
-def test_sync_multi_gpu_equals_large_batch_sgd(tmp_path, world):
+@pytest.mark.parametrize("world,nvls", [(2, None), (2, False), (4, None), (8, None), (8, False)])
+def test_sync_multi_gpu_equals_large_batch_sgd(tmp_path, world, nvls):
+    """nvls=None: NVSwitch multimem path when the fabric offers multicast; nvls=False: peer loads / stores over CUDA IPC."""
     _need(world)
     steps = 4
-    spawn(_mgpu_sync, world, backend="nccl", args=(str(tmp_path), steps))
+    spawn(_mgpu_sync, world, backend="nccl", args=(str(tmp_path), steps, nvls))
+    print("NVLS used:", open(tmp_path / "nvls.txt").read())
     outs = [torch.load(tmp_path / f"sync{r}.pt") for r in range(world)]
     for o in outs[1:]:
         assert torch.equal(o, outs[0])           # every replica holds bit-identical weights

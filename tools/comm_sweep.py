@@ -6,7 +6,8 @@
 Per message size (fp32 elements, whole vector = one "model"):
   push   dmlb_push_add        every GPU adds its N-vector into the sharded masters (red.add.v4 over NVLink)
   pull   dmlb_pull            every GPU reads the N-vector back from the shard owners (peer loads)
-  sync   dmlb_sync_rs_update_ag   barrier + reduce-scatter + SGD + all-gather + barrier, one kernel
+  sync   dmlb_sync_rs_update_ag   barrier + reduce-scatter + SGD + all-gather + barrier, one kernel (peer loads / stores)
+  nvls   dmlb_sync_nvls_range     the same step with multimem.ld_reduce / multimem.st (reduction and multicast inside the NVSwitch)
   nccl   all_reduce + flat axpy   the baseline formulation of the synchronous step
   p2p    NCCL send/recv rank0 -> rank1 (the reference's pytorch_p2p_ex.py pattern)
 All times are CUDA-event device times, max over ranks.  "wire" = bytes each GPU must move over NVLink in one
@@ -99,6 +100,26 @@ def main():
         t_sync = max_ranks(timed(lambda: peer.sync_rs_update_ag(grads_s.table, params_s.table, flags.table, None, rank, world, shard, lr, 0.0, 0.0,
                                                                 1.0 / world), iters), dev)
         pg.barrier()
+        t_nvls = None
+        if world > 1:
+            try:     # the same step through the NVSwitch: multimem.ld_reduce + multimem.st on multicast mappings
+                sg = peer.SymmMemBuffer(padded * 4, dev)
+                sp = peer.SymmMemBuffer(padded * 4, dev)
+                sf = peer.SymmMemBuffer(peer.flag_words() * 4, dev)
+                if sg.mc_ptr and sp.mc_ptr:
+                    pl = sp.view(torch.float32, padded)
+                    sg.view(torch.float32, padded).fill_(1.0)
+                    pg.barrier()
+                    f = lambda: peer.sync_nvls_range(sg.mc_ptr, sp.mc_ptr, pl, sf.table, 0, rank, world, rank * shard, shard, lr, 0.0, 0.0, 1.0 / world)
+                    for _ in range(3):
+                        f()
+                    pg.barrier()
+                    t_nvls = max_ranks(timed(f, iters), dev)
+                    pg.barrier()
+                del sg, sp, sf
+            except Exception as exc:
+                if rank == 0:
+                    print("nvls unavailable:", exc, flush=True)
 
         def nccl_step():
             dist.all_reduce(nccl_buf)
@@ -118,7 +139,8 @@ def main():
             t_p2p = max_ranks(ms, dev)
         wire = n * 4 * (world - 1) / world
         row = {"bytes": n * 4, "world": world,
-               "push_us": t_push * 1e3, "pull_us": t_pull * 1e3, "sync_us": t_sync * 1e3, "nccl_allreduce_sgd_us": t_nccl * 1e3,
+               "push_us": t_push * 1e3, "pull_us": t_pull * 1e3, "sync_us": t_sync * 1e3, "sync_nvls_us": (t_nvls * 1e3 if t_nvls else None),
+               "nccl_allreduce_sgd_us": t_nccl * 1e3,
                "p2p_us": (t_p2p * 1e3 if t_p2p is not None else None),
                "push_gbs": wire / (t_push * 1e-3) / 1e9 if world > 1 else n * 4 / (t_push * 1e-3) / 1e9,
                "pull_gbs": wire / (t_pull * 1e-3) / 1e9 if world > 1 else n * 4 / (t_pull * 1e-3) / 1e9,
@@ -126,7 +148,7 @@ def main():
                "p2p_gbs": (max(nbytes, 4) / (t_p2p * 1e-3) / 1e9 if t_p2p else None),
                "push_frac_of_link": (wire / (t_push * 1e-3) / 1e9 / LINK_GBS if world > 1 else None),
                "pull_frac_of_link": (wire / (t_pull * 1e-3) / 1e9 / LINK_GBS if world > 1 else None),
-               "sync_vs_nccl_speedup": t_nccl / t_sync}
+               "sync_vs_nccl_speedup": t_nccl / t_sync, "nvls_vs_nccl_speedup": (t_nccl / t_nvls if t_nvls else None)}
         rows.append(row)
         if rank == 0:
             print(json.dumps(row), flush=True)
