@@ -270,19 +270,30 @@ __global__ void __launch_bounds__(512) sync_nvls_kernel(const float* __restrict_
 
     const float lr = *lr_ptr;
     const long long n4 = slice_len / 4;
-    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
-        float4 g = multimem_ld_reduce_add_f32x4(mc_grads + base + 4 * i);
-        g.x *= grad_scale; g.y *= grad_scale; g.z *= grad_scale; g.w *= grad_scale;
-        float4 p = reinterpret_cast<const float4*>(params_local + base)[i];
-        if (wd != 0.f) { g.x += wd * p.x; g.y += wd * p.y; g.z += wd * p.z; g.w += wd * p.w; }
-        if (mom != nullptr) {
-            float4 v = reinterpret_cast<float4*>(mom)[i];
-            v.x = mu * v.x + g.x; v.y = mu * v.y + g.y; v.z = mu * v.z + g.z; v.w = mu * v.w + g.w;
-            reinterpret_cast<float4*>(mom)[i] = v;
-            g = v;
+    constexpr int kU = 4;     // switch-reduced loads in flight per thread
+    const long long stride = 1ll * gridDim.x * blockDim.x;
+    for (long long i0 = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i0 < n4; i0 += stride * kU) {
+        float4 gs[kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u)
+            if (i0 + u * stride < n4) gs[u] = multimem_ld_reduce_add_f32x4(mc_grads + base + 4 * (i0 + u * stride));
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            const long long i = i0 + u * stride;
+            if (i >= n4) continue;
+            float4 g = gs[u];
+            g.x *= grad_scale; g.y *= grad_scale; g.z *= grad_scale; g.w *= grad_scale;
+            float4 p = reinterpret_cast<const float4*>(params_local + base)[i];
+            if (wd != 0.f) { g.x += wd * p.x; g.y += wd * p.y; g.z += wd * p.z; g.w += wd * p.w; }
+            if (mom != nullptr) {
+                float4 v = reinterpret_cast<float4*>(mom)[i];
+                v.x = mu * v.x + g.x; v.y = mu * v.y + g.y; v.z = mu * v.z + g.z; v.w = mu * v.w + g.w;
+                reinterpret_cast<float4*>(mom)[i] = v;
+                g = v;
+            }
+            p.x -= lr * g.x; p.y -= lr * g.y; p.z -= lr * g.z; p.w -= lr * g.w;
+            multimem_st_f32x4(mc_params + base + 4 * i, p);
         }
-        p.x -= lr * g.x; p.y -= lr * g.y; p.z -= lr * g.z; p.w -= lr * g.w;
-        multimem_st_f32x4(mc_params + base + 4 * i, p);
     }
 
     __syncthreads();

@@ -277,3 +277,21 @@ def test_mailbox_protocol_stress_multi_gpu(tmp_path, world):
     expect = outs[0]["theta0"] + sum(o["sum"] for o in outs)
     for o in outs:
         torch.testing.assert_close(o["final"], expect, rtol=1e-4, atol=2e-5)
+
+
+def test_train_step_graph_with_dropout_and_lr_schedule():
+    """LeNet in train mode inside the CUDA graph: dropout masks must change from replay to replay (device-side counter) and a
+    learning-rate change between replays must take effect (lr lives in device memory)."""
+    from distributed_ml_pytorch_b200.engine import TrainStep
+    torch.manual_seed(0)
+    net = build_model("lenet").cuda().train()
+    opt = FusedSGD(net.parameters(), lr=0.05, model=net)
+    ts = TrainStep(net, opt, 32, (3, 32, 32))
+    x, y = _batch(0, n=32)
+    l0 = [ts(x, y, sync=True).loss for _ in range(6)]
+    assert len(set(round(v, 6) for v in l0)) > 1 and all(v == v for v in l0)
+    before = opt.arena.flat_params().clone()
+    for g in opt.param_groups:
+        g["lr"] = 0.0                       # a scheduler would do this between steps
+    ts(x, y, sync=True)
+    assert torch.equal(opt.arena.flat_params(), before)

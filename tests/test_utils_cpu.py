@@ -1,0 +1,49 @@
+"""CPU unit tests of the auxiliary subsystems: CSV log schema, plotting, clock sampling, timing helpers, messaging codes."""
+import os
+
+import torch
+
+from distributed_ml_pytorch_b200.utils import csvlog, plot
+from distributed_ml_pytorch_b200.utils.messaging import MessageCode
+from distributed_ml_pytorch_b200.utils.timing import ClockSampler
+
+
+def test_csv_schema_and_paths(tmp_path):
+    assert csvlog.log_path(True, False, None) == os.path.join("log", "single.csv")
+    assert csvlog.log_path(True, True, None) == os.path.join("log", "gpu.csv")
+    assert csvlog.log_path(False, True, 2) == os.path.join("log", "node2.csv")
+    lg = csvlog.CSVLogger(str(tmp_path / "log" / "node1.csv"))       # the directory does not exist yet (reference needs it to)
+    lg.append(0, 2.30)
+    lg.append(100, 2.10, test_loss=2.2, test_accuracy=0.31, images_per_sec=1234.5)
+    rows = csvlog.read_csv(lg.to_csv())
+    assert list(rows[0].keys()) == csvlog.COLUMNS
+    assert rows[0]["test_loss"] == "" and rows[1]["test_accuracy"] == "0.31" and rows[1]["index"] == "1"
+
+
+def test_plot_writes_valid_png_without_matplotlib(tmp_path):
+    out = plot.plot_series(str(tmp_path / "p.png"), {"a": ([0, 1, 2], [3.0, 2.0, 1.0]), "b": ([0, 1, 2], [1.0, 1.5, 2.5])})
+    data = open(out, "rb").read()
+    assert data[:8] == b"\x89PNG\r\n\x1a\n" and len(data) > 200
+    lg = csvlog.CSVLogger(str(tmp_path / "log" / "single.csv"))
+    for i in range(5):
+        lg.append(i, 2.0 - 0.1 * i, test_loss=2.0, test_accuracy=0.1 * i)
+    lg.to_csv()
+    a, b = plot.graph([lg.path], out_dir=str(tmp_path))
+    assert os.path.basename(a) == "train_time.png" and os.path.basename(b) == "test_time.png"      # reference Makefile:9-11
+
+
+def test_clock_sampler_summary_parsing():
+    s = ClockSampler()
+    s.lines = ["0, 1965, 1965, 310.5, 0x0000000000000000, Not Active, Not Active, Not Active, Not Active",
+               "0, 1830, 1965, 990.1, 0x0000000000000004, Not Active, Not Active, Not Active, Active",
+               "0, 1845, 1965, 1001.7, 0x0000000000000004, Not Active, Not Active, Not Active, Active", "garbage"]
+    out = s.summary()
+    assert out["sm_max_mhz"] == 1965.0 and out["reasons"] == ["sw_power_cap"] and out["samples"] == 3
+    assert out["sm_mhz"] in (1830.0, 1837.5, 1845.0)          # median of the samples taken under load
+    assert ClockSampler().summary()["samples"] == 0
+
+
+def test_message_codes_cover_the_reference_protocol():
+    names = {c.name for c in MessageCode}
+    assert {"ParameterRequest", "GradientUpdate", "ParameterUpdate"} <= names       # reference Asynchronous.py:17,34,49,59
+    assert MessageCode(MessageCode.GradientUpdate.value) is MessageCode.GradientUpdate
