@@ -8,7 +8,8 @@ math (AlexNet at batch 64 is ~6 GFLOP per step).  :class:`TrainStep` keeps the s
 * captures ``zero_grad -> forward -> loss -> backward -> local optimizer update -> bf16 shadow refresh`` once
   into a CUDA graph over static buffers and replays it per step (no Python, no allocator, no per-op launch
   overhead on the hot path);
-* feeds it from pinned host memory with asynchronous H2D copies on the same stream;
+* feeds it from pinned host memory through a copy stream and a double-buffered device staging area, so the PCIe
+  transfer of batch i+1 overlaps the replay of step i (set ``DMLB_NVTX=1`` to wrap every step in an NVTX range);
 * returns the loss / accuracy counters through a pinned, double-buffered D2H copy that is read one step
   late, so the host never stalls the GPU (the reference blocks on ``loss.item()`` every step, main.py:79);
 * leaves the communication part of a distributed optimizer (``communicate()``: gradient push / parameter
@@ -17,11 +18,14 @@ math (AlexNet at batch 64 is ~6 GFLOP per step).  :class:`TrainStep` keeps the s
 """
 from __future__ import annotations
 
+import os
 from typing import Callable, Optional, Tuple
 
 import torch
 
 from .ops import functional as OF
+
+_NVTX = os.environ.get("DMLB_NVTX", "0") == "1"
 
 
 class StepResult:
@@ -135,6 +139,8 @@ class TrainStep:
             return StepResult(float(loss), correct, self.step_count - 1)
         if hasattr(self.optimizer, "_sync_lr"):
             self.optimizer._sync_lr()
+        if _NVTX:
+            torch.cuda.nvtx.range_push(f"dmlb.step{self.step_count}")
         slot = self.step_count & 1
         if not x.is_cuda:
             # Host batch: the PCIe copy runs on its own stream into a double-buffered staging area, so it overlaps the
@@ -169,6 +175,8 @@ class TrainStep:
             self._events[slot].record(self.stream)
             if self._communicate is not None:
                 self._communicate()
+        if _NVTX:
+            torch.cuda.nvtx.range_pop()
         prev = self._pending
         self._pending = slot
         self.step_count += 1
