@@ -47,12 +47,23 @@ class ArenaOptimizer(Optimizer):
     # -- gradients -----------------------------------------------------------------------------
     def zero_grad(self, set_to_none: bool = False) -> None:
         """One memset of the gradient arena (gradients stay views, never ``None``)."""
+        first = next(iter(self.model.parameters()))
+        self._check_model_still_bound(first)
         if self.fused_zero_grad and self.arena.params.is_cuda:
             return
-        first = next(iter(self.model.parameters()))
         if first.grad is None or first.grad.data_ptr() != self.arena.grads.data_ptr():
             self.arena.rebind_grads()
         self.arena.zero_grads()
+
+    def _check_model_still_bound(self, first) -> None:
+        """The reference builds its optimizer and only then calls ``net.cuda()`` (example/main.py:46,53-54).  With a flat arena
+        that would silently train a detached copy, so it is reported instead (build the optimizer after the move)."""
+        if first.data_ptr() != self.arena.params.data_ptr():
+            if first.device != self.arena.params.device:
+                raise RuntimeError(
+                    f"the model moved to {first.device} after the optimizer was created on {self.arena.params.device}: "
+                    "construct the optimizer after model.to(device) / model.cuda()")
+            self.arena.bind()          # same device, parameters re-created (e.g. load_state_dict(assign=True)): re-attach them
 
     def refresh_shadows(self, flat_done: bool = False) -> None:
         self.arena.mark_params_changed(flat_done=flat_done)

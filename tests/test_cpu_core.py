@@ -152,3 +152,17 @@ def test_checkpoint_roundtrip_with_reference_layout(tmp_path):
     # a bare reference-style file (torch.save(model.state_dict())) loads too
     torch.save(net.state_dict(), tmp_path / "bare.pt")
     load_checkpoint(str(tmp_path / "bare.pt"), net2)
+
+
+def test_moving_the_model_after_building_the_optimizer_is_reported():
+    """The reference's order (optimizer first, then net.cuda(), main.py:46,53-54) cannot work with a flat arena: say so loudly."""
+    net = LeNet()
+    opt = FusedSGD(net.parameters(), lr=0.1, model=net)
+    opt.zero_grad()                                  # fine while the parameters are still the arena views
+    net.double()                                     # stands in for .cuda() on this CPU box: parameters are re-created
+    net.float()
+    opt.zero_grad()                                  # same device -> silently re-bound
+    assert next(net.parameters()).data_ptr() == opt.arena.params.data_ptr()
+    net.to("meta")
+    with pytest.raises(RuntimeError, match="after the optimizer was created"):
+        opt.zero_grad()
