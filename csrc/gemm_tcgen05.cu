@@ -68,6 +68,82 @@ struct GemmSmem {
     static constexpr int kTotal = kStages * kStageBytes + kBarrierBytes + 1024;  // +1024: manual 1 KiB alignment
 };
 
+// Epilogue of one 128 x BN accumulator tile: every thread owns one TMEM lane = one output row, 32 columns at a time.
+template <int BN>
+__device__ __forceinline__ void gemm_epilogue_tile(uint32_t tmem_d, int q, int lane, int m0, int n0, int M, int N, const GemmEpilogue& ep,
+                                                   bool add_bias) {
+    const int row = m0 + q * 32 + lane;
+    const bool row_ok = row < M;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 32) {
+        if (n0 + c0 >= N) break;  // warp-uniform
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_d + (static_cast<uint32_t>(q * 32) << 16) + c0, v);
+        tmem_ld_wait();
+        if (!row_ok) continue;
+        const int col0 = n0 + c0;
+        const int ncols = min(32, N - col0);
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            float x = __uint_as_float(v[j]);
+            if (add_bias && j < ncols) x += __ldg(ep.bias + col0 + j);
+            if (ep.relu) x = fmaxf(x, 0.f);
+            f[j] = x;
+        }
+        if (ep.atomic) {
+            float* o = static_cast<float*>(ep.out) + static_cast<size_t>(row) * ep.ldo;
+            if (ep.perm_cin > 0) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const int c = col0 + j;
+                    if (j < ncols) red_add_f32(o + (c % ep.perm_cin) * ep.perm_khw + c / ep.perm_cin, f[j]);
+                }
+            } else if (ncols == 32 && (ep.ldo & 3) == 0) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) red_add_f32x4(o + col0 + j, f[j], f[j + 1], f[j + 2], f[j + 3]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (j < ncols) red_add_f32(o + col0 + j, f[j]);
+            }
+        } else if (ep.out_is_f32) {
+            float* o = static_cast<float*>(ep.out) + static_cast<size_t>(row) * ep.ldo;
+            if (ep.perm_cin > 0) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const int c = col0 + j;
+                    if (j < ncols) o[(c % ep.perm_cin) * ep.perm_khw + c / ep.perm_cin] = f[j];
+                }
+            } else if (ncols == 32 && (ep.ldo & 3) == 0) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) st_f32x4(o + col0 + j, make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]));
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (j < ncols) o[col0 + j] = f[j];
+            }
+        } else {
+            __nv_bfloat16* o = static_cast<__nv_bfloat16*>(ep.out) + static_cast<size_t>(row) * ep.ldo;
+            if (ncols == 32 && (ep.ldo & 7) == 0) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) {
+                    uint4 pk;
+                    pk.x = pack_bf16x2(f[j], f[j + 1]);
+                    pk.y = pack_bf16x2(f[j + 2], f[j + 3]);
+                    pk.z = pack_bf16x2(f[j + 4], f[j + 5]);
+                    pk.w = pack_bf16x2(f[j + 6], f[j + 7]);
+                    *reinterpret_cast<uint4*>(o + col0 + j) = pk;
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    if (j < ncols) o[col0 + j] = __float2bfloat16_rn(f[j]);
+            }
+        }
+    }
+}
+
 template <int BN, int AM, int BMODE, bool kDual>
 __global__ void __launch_bounds__(kGemmThreads, ((kDual && BN <= 128) ? 2 : 1))
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
@@ -210,79 +286,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     } else {
         // ------------------------------ epilogue ------------------------------
         const int q = warp & 3;                 // TMEM lane quadrant this warp may access
-        const int row = m0 + q * 32 + lane;
         mbar_wait(tmem_full_bar, 0);
         tcgen05_fence_after();
-        const bool row_ok = row < M;
-        const bool add_bias = ep.bias != nullptr && (!ep.atomic || blockIdx.z == 0);
-#pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 32) {
-            if (n0 + c0 >= N) break;  // warp-uniform
-            uint32_t v[32];
-            tmem_ld_32x32(tmem_d + (static_cast<uint32_t>(q * 32) << 16) + c0, v);
-            tmem_ld_wait();
-            if (!row_ok) continue;
-            const int col0 = n0 + c0;
-            const int ncols = min(32, N - col0);
-            float f[32];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                float x = __uint_as_float(v[j]);
-                if (add_bias && j < ncols) x += __ldg(ep.bias + col0 + j);
-                if (ep.relu) x = fmaxf(x, 0.f);
-                f[j] = x;
-            }
-            if (ep.atomic) {
-                float* o = static_cast<float*>(ep.out) + static_cast<size_t>(row) * ep.ldo;
-                if (ep.perm_cin > 0) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const int c = col0 + j;
-                        if (j < ncols) red_add_f32(o + (c % ep.perm_cin) * ep.perm_khw + c / ep.perm_cin, f[j]);
-                    }
-                } else if (ncols == 32 && (ep.ldo & 3) == 0) {
-#pragma unroll
-                    for (int j = 0; j < 32; j += 4) red_add_f32x4(o + col0 + j, f[j], f[j + 1], f[j + 2], f[j + 3]);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (j < ncols) red_add_f32(o + col0 + j, f[j]);
-                }
-            } else if (ep.out_is_f32) {
-                float* o = static_cast<float*>(ep.out) + static_cast<size_t>(row) * ep.ldo;
-                if (ep.perm_cin > 0) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const int c = col0 + j;
-                        if (j < ncols) o[(c % ep.perm_cin) * ep.perm_khw + c / ep.perm_cin] = f[j];
-                    }
-                } else if (ncols == 32 && (ep.ldo & 3) == 0) {
-#pragma unroll
-                    for (int j = 0; j < 32; j += 4) st_f32x4(o + col0 + j, make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]));
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (j < ncols) o[col0 + j] = f[j];
-                }
-            } else {
-                __nv_bfloat16* o = static_cast<__nv_bfloat16*>(ep.out) + static_cast<size_t>(row) * ep.ldo;
-                if (ncols == 32 && (ep.ldo & 7) == 0) {
-#pragma unroll
-                    for (int j = 0; j < 32; j += 8) {
-                        uint4 pk;
-                        pk.x = pack_bf16x2(f[j], f[j + 1]);
-                        pk.y = pack_bf16x2(f[j + 2], f[j + 3]);
-                        pk.z = pack_bf16x2(f[j + 4], f[j + 5]);
-                        pk.w = pack_bf16x2(f[j + 6], f[j + 7]);
-                        *reinterpret_cast<uint4*>(o + col0 + j) = pk;
-                    }
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (j < ncols) o[col0 + j] = __float2bfloat16_rn(f[j]);
-                }
-            }
-        }
+        gemm_epilogue_tile<BN>(tmem_d, q, lane, m0, n0, M, N, ep, ep.bias != nullptr && (!ep.atomic || blockIdx.z == 0));
     }
 
     tcgen05_fence_before();
@@ -290,6 +296,186 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     if (warp == 1) {
         tcgen05_fence_after();
         tmem_dealloc<kTmemCols>(tmem_d);
+    }
+}
+
+// ----------------------------------------------------------------------------------------------
+// Persistent variant for grids of many tiles (ResNet-sized convolutions): one CTA per SM walks a strided list of output
+// tiles.  Barrier set-up, TMEM allocation and descriptor prefetch are paid once per SM instead of once per tile, the smem
+// ring keeps streaming across tile boundaries, and the accumulator is double-buffered in TMEM (2 x BN columns) so the
+// epilogue of tile t (tcgen05.ld, bias/ReLU, stores) overlaps the TMA + MMA main loop of tile t+1.  No split-K here.
+// ----------------------------------------------------------------------------------------------
+template <int BN>
+struct PersistSmem {
+    static constexpr int kABytes = kBM * kBK * 2;
+    static constexpr int kBBytes = BN * kBK * 2;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kStages = (BN <= 64) ? 7 : (BN <= 128 ? 5 : 4);
+    static constexpr int kTotal = kStages * kStageBytes + 256 + 1024;
+};
+
+template <int BN, int AM, int BMODE>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, GemmEpilogue ep,
+                                    ConvK cv, int M, int N, int K, int tiles_m, int tiles_n) {
+    constexpr bool A_MN = AM == 1;
+    constexpr bool B_MN = BMODE >= 1;
+    using S = PersistSmem<BN>;
+    constexpr int kStages = S::kStages;
+    constexpr int kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
+    static_assert(2 * BN <= 512, "two accumulators must fit in TMEM");
+
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_base = smem_base + kStages * S::kStageBytes;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
+    auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStages + a); };
+    auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStages + 2 + a); };
+    const uint32_t tmem_holder = bar_base + 8u * (2 * kStages + 4);
+    uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+    volatile uint32_t* tmem_holder_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + kStages * S::kStageBytes + 8 * (2 * kStages + 4));
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int nkb = (K + kBK - 1) / kBK;
+    const int num_tiles = tiles_m * tiles_n;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(full_bar(s), 1);
+            mbar_init(empty_bar(s), 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(tfull_bar(a), 1);
+            mbar_init(tempty_bar(a), 4);     // one arrival per epilogue warp
+        }
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc<kTmemCols>(tmem_holder);
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_holder_ptr;
+    pdl_launch_dependents();
+    pdl_wait();
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int it = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int m0 = (tile / tiles_n) * kBM;
+                const int n0 = (tile % tiles_n) * BN;
+                int a_n = 0, a_h = 0, a_w = 0;
+                if constexpr (AM == 2) {
+                    const int pq = cv.P * cv.Q;
+                    a_n = m0 / pq;
+                    const int rem = m0 - a_n * pq;
+                    const int pp = rem / cv.Q;
+                    a_h = cv.low_h + pp * cv.sh;
+                    a_w = cv.low_w + (rem - pp * cv.Q) * cv.sw;
+                }
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int s = it % kStages;
+                    const uint32_t ph = (it / kStages) & 1u;
+                    mbar_wait(empty_bar(s), ph ^ 1u);
+                    const uint32_t a_dst = smem_base + s * S::kStageBytes;
+                    const uint32_t b_dst = a_dst + S::kABytes;
+                    const int k0 = kb * kBK;
+                    mbar_arrive_expect_tx(full_bar(s), S::kStageBytes);
+                    if constexpr (AM == 0) {
+                        tma_load_2d(a_dst, &tma_a, k0, m0, full_bar(s));
+                    } else if constexpr (AM == 1) {
+                        tma_load_2d(a_dst, &tma_a, m0, k0, full_bar(s));
+                        tma_load_2d(a_dst + 8192, &tma_a, m0 + 64, k0, full_bar(s));
+                    } else {
+                        const int tap = k0 / cv.C;
+                        const int r = tap / cv.KW;
+                        tma_load_im2col_4d(a_dst, &tma_a, k0 - tap * cv.C, a_w, a_h, a_n, tap - r * cv.KW, r, full_bar(s));
+                    }
+                    if constexpr (BMODE == 0) {
+                        tma_load_2d(b_dst, &tma_b, k0, n0, full_bar(s));
+                    } else if constexpr (BMODE == 1) {
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j) tma_load_2d(b_dst + j * 8192, &tma_b, n0 + 64 * j, k0, full_bar(s));
+                    } else if constexpr (BMODE == 2) {
+                        const int pq = cv.P * cv.Q;
+                        const int bn_ = k0 / pq;
+                        const int rem = k0 - bn_ * pq;
+                        const int pp = rem / cv.Q;
+                        const int bh = cv.low_h + pp * cv.sh;
+                        const int bw = cv.low_w + (rem - pp * cv.Q) * cv.sw;
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j) {
+                            int kcol = n0 + 64 * j;
+                            if (kcol >= N) kcol = 0;
+                            const int tap = kcol / cv.C;
+                            const int r = tap / cv.KW;
+                            tma_load_im2col_4d(b_dst + j * 8192, &tma_b, kcol - tap * cv.C, bw, bh, bn_, tap - r * cv.KW, r, full_bar(s));
+                        }
+                    } else {
+                        const int tap = k0 / cv.C;
+                        const int wtap = cv.flip ? (cv.KH * cv.KW - 1 - tap) : tap;
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j) {
+                            int cin0 = n0 + 64 * j;
+                            if (cin0 >= N) cin0 = 0;
+                            tma_load_3d(b_dst + j * 8192, &tma_b, cin0, wtap, k0 - tap * cv.C, full_bar(s));
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, A_MN, B_MN);
+            int it = 0, t = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+                const int acc = t & 1;
+                mbar_wait(tempty_bar(acc), ((t >> 1) & 1u) ^ 1u);     // the epilogue has drained this accumulator
+                tcgen05_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int s = it % kStages;
+                    const uint32_t ph = (it / kStages) & 1u;
+                    mbar_wait(full_bar(s), ph);
+                    tcgen05_fence_after();
+                    const uint32_t a_src = smem_base + s * S::kStageBytes;
+                    const uint32_t b_src = a_src + S::kABytes;
+#pragma unroll
+                    for (int k = 0; k < kBK / kUmmaK; ++k) {
+                        const uint64_t adesc = A_MN ? umma_smem_desc(a_src + k * 2048, 8192, 1024) : umma_smem_desc(a_src + k * 32, 16, 1024);
+                        const uint64_t bdesc = B_MN ? umma_smem_desc(b_src + k * 2048, 8192, 1024) : umma_smem_desc(b_src + k * 32, 16, 1024);
+                        umma_bf16(tmem_d, adesc, bdesc, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit(empty_bar(s));
+                }
+                umma_commit(tfull_bar(acc));
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        int t = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+            const int acc = t & 1;
+            const int m0 = (tile / tiles_n) * kBM;
+            const int n0 = (tile % tiles_n) * BN;
+            mbar_wait(tfull_bar(acc), (t >> 1) & 1u);
+            tcgen05_fence_after();
+            gemm_epilogue_tile<BN>(tmem_base + acc * BN, q, lane, m0, n0, M, N, ep, ep.bias != nullptr);
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar(acc));
+        }
+    }
+
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc<kTmemCols>(tmem_base);
     }
 }
 
@@ -420,13 +606,38 @@ static int launch_gemm_v(const CUtensorMap& ta, const CUtensorMap& tb, const Gem
     return 0;
 }
 
-// More than one wave of CTAs -> the two-CTAs-per-SM variant (epilogues overlap main loops); otherwise the deep-ring one.
+template <int BN, int AM, int BMODE>
+static int launch_gemm_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpilogue& ep, const ConvK& cv, int M, int N, int K,
+                                  cudaStream_t stream) {
+    using S = PersistSmem<BN>;
+    auto kern = gemm_bf16_tcgen05_persistent_kernel<BN, AM, BMODE>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        DMLB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
+        attr_set = true;
+    }
+    const int tiles_m = (M + kBM - 1) / kBM, tiles_n = (N + BN - 1) / BN;
+    int grid = tiles_m * tiles_n;
+    if (grid > dmlb_sm_count()) grid = dmlb_sm_count();
+    DMLB_CHECK_CUDA(launch_k(kern, grid, kGemmThreads, S::kTotal, stream, ta, tb, ep, cv, M, N, K, tiles_m, tiles_n));
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int dmlb_gemm_persistent_enabled();
+
+// Several waves of tiles and no split-K -> the persistent kernel; more than one wave -> two CTAs per SM; otherwise the deep ring.
 template <int BN, int AM, int BMODE>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpilogue& ep, const ConvK& cv, int M, int N, int K, int splits,
                        cudaStream_t stream) {
     const int nkb = (K + kBK - 1) / kBK;
     const int kb_per = (nkb + splits - 1) / splits;
     const long long ctas = 1ll * ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN) * ((nkb + kb_per - 1) / kb_per);
+    if constexpr (BN <= 128) {
+        // short reductions only: with a long K loop the per-tile set-up is already amortised and the 2-CTA variant rasterises better
+        if (splits == 1 && nkb <= 24 && ctas >= 3ll * dmlb_sm_count() && dmlb_gemm_persistent_enabled())
+            return launch_gemm_persistent<BN, AM, BMODE>(ta, tb, ep, cv, M, N, K, stream);
+    }
     if (BN <= 128 && ctas > dmlb_sm_count()) return launch_gemm_v<BN, AM, BMODE, true>(ta, tb, ep, cv, M, N, K, splits, stream);
     return launch_gemm_v<BN, AM, BMODE, false>(ta, tb, ep, cv, M, N, K, splits, stream);
 }

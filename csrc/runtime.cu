@@ -44,6 +44,19 @@ extern "C" int dmlb_pdl_enabled() {
 }
 extern "C" void dmlb_set_pdl(int on) { g_pdl = on ? 1 : 0; }
 
+// Persistent GEMM for multi-wave, short-K tile grids.  Opt-in (DMLB_PERSISTENT=1 or dmlb_set_gemm_persistent(1)): measured in
+// isolation it wins (M=200704,N=64,K=576: 61 -> 52 us, 0.76 of HBM peak) but inside a ResNet-50 step it loses (9.6 -> 10.4 ms)
+// because a grid that pins all 148 SMs serialises against the side-stream wgrad GEMMs that otherwise run concurrently.
+static int g_persist = -1;
+extern "C" int dmlb_gemm_persistent_enabled() {
+    if (g_persist < 0) {
+        const char* e = getenv("DMLB_PERSISTENT");
+        g_persist = (e != nullptr && e[0] == '1') ? 1 : 0;
+    }
+    return g_persist;
+}
+extern "C" void dmlb_set_gemm_persistent(int on) { g_persist = on ? 1 : 0; }
+
 // Number of SMs of the current device (148 on B200); used to size persistent / flat grids.
 extern "C" int dmlb_sm_count() {
     static int cached[64] = {0};

@@ -27,6 +27,8 @@ void dmlb_count_launch(void);
 int dmlb_sm_count(void);
 int dmlb_pdl_enabled(void);               /* programmatic dependent launch between consecutive kernels (default 1; env DMLB_PDL=0) */
 void dmlb_set_pdl(int on);
+int dmlb_gemm_persistent_enabled(void);   /* persistent double-buffered GEMM for multi-wave short-K grids (opt-in: default 0; env DMLB_PERSISTENT=1) */
+void dmlb_set_gemm_persistent(int on);
 
 /* ---- tcgen05 GEMM (reference: nn.Linear / nn.Conv2d in example/models.py:8-13,28-43) ------------
  * D[M,N] (+)= A[M,K] * B[N,K]^T, bf16 operands, fp32 accumulation in TMEM.

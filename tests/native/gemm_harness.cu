@@ -189,6 +189,7 @@ int main(int argc, char** argv) {
         }
         return 0;
     }
+    dmlb_set_gemm_persistent(1);   // exercise the opt-in persistent kernel on the multi-wave cases below
     bool quick = argc > 1 && !strcmp(argv[1], "--quick");
     bool big_only = argc > 1 && !strcmp(argv[1], "--big");   // one large GEMM, timing only: the command ncu wraps
     std::vector<Case> cases = {
@@ -210,6 +211,10 @@ int main(int argc, char** argv) {
         {384, 1728, 256, 1, 1, 2, 1, 0, 0, 0, 0, 0},   // conv3 wgrad split-K
         {64, 363, 4096, 1, 1, 16, 1, 0, 0, 0, 3, 121}, // conv1 wgrad, split-K, (kh,kw,cin)->(cin,kh,kw) scatter
         {10, 256, 64, 1, 1, 1, 1, 0, 0, 0, 0, 0},      // classifier wgrad
+        {8192, 1024, 96, 0, 0, 1, 0, 1, 1, 0, 0, 0},   // 512 tiles: persistent kernel, double-buffered TMEM, ragged K
+        {8200, 1000, 200, 0, 1, 1, 0, 0, 0, 0, 0, 0},  // persistent, B MN-major, ragged M and N
+        {2048, 4096, 100, 1, 1, 1, 1, 0, 0, 0, 0, 0},  // persistent, both MN-major, fp32 out
+        {16384, 64, 64, 0, 0, 1, 0, 1, 0, 64, 0, 0},   // persistent, one k-block per tile (ResNet 1x1 conv shape)
     };
     std::vector<Case> perf = {
         {8192, 8192, 8192, 0, 0, 1, 0, 0, 0, 128, 0, 0},
