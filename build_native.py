@@ -93,31 +93,52 @@ def build(verbose: bool = False, harness: bool = False, sass: bool = False) -> P
 
 
 def dump_sass() -> None:
-    """cuobjdump -sass per object -> artifacts/sass/<name>.sass (+ a mnemonic census proving tcgen05/TMA)."""
+    """cuobjdump -sass per object -> artifacts/sass/<name>.sass (compact listings, capped in size), CENSUS.txt (mnemonic counts per
+    object) and FUNCTIONS.txt (mnemonic counts per kernel: the proof of tcgen05 / TMA / TMA-im2col / NVLS multimem use)."""
+    import re
     out = ROOT / "artifacts" / "sass"
     out.mkdir(parents=True, exist_ok=True)
-    census = []
+    keys = ("UTCHMMA", "UTCBAR", "LDTM", "UTMALDG.2D", "UTMALDG.3D", "UTMALDG.4D.IM2COL", "SYNCS", "REDG", "LDGMC", "STG.E.128", "LDGSTS")
+    census, per_fn = [], []
+    cap = 1_200_000
     for obj in sorted(BUILD_DIR.glob("*.o")):
         res = subprocess.run(["cuobjdump", "-sass", str(obj)], capture_output=True, text=True)
         if res.returncode != 0:
             continue
-        lines = [ln for ln in res.stdout.splitlines() if "/*" in ln or "Function" in ln]
-        # keep the listing compact: strip encodings
-        compact = []
-        for ln in lines:
-            if "Function" in ln:
-                compact.append(ln.strip())
+        text = res.stdout
+        compact, size, skipped = [], 0, 0
+        fn_name, fn_lines = None, []
+
+        def flush():
+            nonlocal size, skipped
+            if fn_name is None:
+                return
+            body = "\n".join(fn_lines)
+            per_fn.append(f"{obj.stem:14s} " + " ".join(f"{k}={body.count(k)}" for k in keys if body.count(k)) + f"  {fn_name}")
+            if size + len(body) <= cap:
+                compact.append(fn_name)
+                compact.append(body)
+                size += len(body)
             else:
+                skipped += 1
+
+        for ln in text.splitlines():
+            if "Function :" in ln:
+                flush()
+                fn_name, fn_lines = ln.strip(), []
+            elif "/*" in ln and fn_name is not None:
                 parts = ln.split("*/")
                 if len(parts) >= 2 and parts[1].strip():
-                    compact.append("    " + parts[1].split("/*")[0].strip())
+                    fn_lines.append("    " + parts[1].split("/*")[0].strip())
+        flush()
+        if skipped:
+            compact.append(f"... {skipped} further kernels of this object omitted from the listing (see FUNCTIONS.txt for their mnemonic census)")
         (out / (obj.stem + ".sass")).write_text("\n".join(compact) + "\n")
-        text = res.stdout
-        import re
-        row = {k: text.count(k) for k in ("UTCHMMA", "UTCBAR", "LDTM", "UTMALDG", "UTMASTG", "UBLKCP", "SYNCS", "REDG", "LDGSTS")}
+        row = {k: text.count(k) for k in keys}
         row["HMMA(legacy mma.sync)"] = len(re.findall(r"(?<![A-Z])HMMA", text))
-        census.append(f"{obj.stem:24s} " + " ".join(f"{k}={v}" for k, v in row.items()))
+        census.append(f"{obj.stem:16s} " + " ".join(f"{k}={v}" for k, v in row.items()))
     (out / "CENSUS.txt").write_text("\n".join(census) + "\n")
+    (out / "FUNCTIONS.txt").write_text("\n".join(per_fn) + "\n")
 
 
 if __name__ == "__main__":
