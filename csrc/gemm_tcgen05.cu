@@ -633,8 +633,9 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmE
     const int nkb = (K + kBK - 1) / kBK;
     const int kb_per = (nkb + splits - 1) / splits;
     const long long ctas = 1ll * ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN) * ((nkb + kb_per - 1) / kb_per);
-    if constexpr (BN <= 128) {
-        // short reductions only: with a long K loop the per-tile set-up is already amortised and the 2-CTA variant rasterises better
+    if constexpr (BN <= 128 && BMODE == 0) {
+        // forward form only (both operands K-major): the backward GEMMs share the GPU with the side-stream wgrad branch and a grid
+        // that pins every SM would serialise against it.  Short reductions only: with a long K loop the per-tile set-up is already amortised and the 2-CTA variant rasterises better
         if (splits == 1 && nkb <= 24 && ctas >= 3ll * dmlb_sm_count() && dmlb_gemm_persistent_enabled())
             return launch_gemm_persistent<BN, AM, BMODE>(ta, tb, ep, cv, M, N, K, stream);
     }
