@@ -77,6 +77,9 @@ class Asynchronous(ArenaOptimizer):
                 transport = "gloo"
             else:
                 transport = "local"
+        if transport == "gloo" and device.type == "cuda":
+            # the CUDA arena keeps conv weights channels-last, the message protocol speaks model.parameters() order
+            raise ValueError("a CUDA model uses the NVLink 'peer' transport; the gloo message transport is for CPU models")
         self.transport = transport
         self.n_push, self.n_pull = int(n_push), int(n_pull)
         self.server_momentum = float(momentum)

@@ -132,14 +132,18 @@ def main(args):
             seen += inputs.shape[0]
             test_loss = test_acc = None
             if i % args.log_interval == 0 and i > 0:
+                _sync_step(step_fn, device, before=True)     # the graph step runs on its own stream: let it finish before evaluating
                 test_loss, test_acc = evaluate(net, testloader, args, device=device)
+                _sync_step(step_fn, device, before=False)
                 print("Timestamp: {} | Iteration: {:6} | Loss: {:6.4f} | Test Loss: {:6.4f} | Test Accuracy: {:6.4f}".format(
                     datetime.now(), i, loss_value, test_loss, test_acc))
             logger.append(i, loss_value, test_loss, test_acc, images_per_sec=seen / max(1e-9, time.time() - t_epoch))
         if step_fn is not None:
             step_fn.flush()
+        _sync_step(step_fn, device, before=True)
         print("learning rate is : {}".format(optimizer.param_groups[0]["lr"]))
         evaluate(net, testloader, args, verbose=True, device=device)
+        _sync_step(step_fn, device, before=False)
         if args.step_scheduler:
             scheduler.step()
         if args.ckpt:
@@ -148,6 +152,16 @@ def main(args):
     if hasattr(optimizer, "finish"):
         optimizer.finish()
     print("Finished Training")
+
+
+def _sync_step(step_fn, device, before: bool) -> None:
+    """Order the TrainStep stream against the default stream around an evaluation (both touch the weights and their shadows)."""
+    if step_fn is None or device.type != "cuda":
+        return
+    if before:
+        step_fn.synchronize()
+    else:
+        step_fn.stream.wait_stream(torch.cuda.current_stream(device))
 
 
 def evaluate(net, testloader, args, verbose=False, device=None):
