@@ -45,6 +45,10 @@ class TrainStep:
     ``optimizer`` is any optimizer of this package (``FusedSGD``, ``Asynchronous``, ``Synchronous``); if it
     exposes ``step_local()`` / ``communicate()`` the former is captured and the latter runs eagerly after each
     replay, otherwise ``step()`` is captured whole.
+
+    The step runs on its own stream (``self.stream``).  Anything else that touches the model — an evaluation pass on the
+    default stream, a checkpoint — must be ordered against it: call ``synchronize()`` first and, afterwards,
+    ``self.stream.wait_stream(torch.cuda.current_stream())`` (``example/main.py`` does this around ``evaluate``).
     """
 
     def __init__(self, model: torch.nn.Module, optimizer, batch_size: int, input_shape: Tuple[int, int, int], device=None,
