@@ -243,6 +243,8 @@ def build_parser():
     parser.add_argument("--ckpt", default=None, help="save a state_dict checkpoint here after every epoch")
     parser.add_argument("--resume", default=None)
     parser.add_argument("--no-graph", action="store_true", help="eager kernels instead of the CUDA-graph TrainStep")
+    parser.add_argument("--timeout-s", type=int, default=1800,
+                        help="process-group timeout: a dead peer makes send/recv raise after this long instead of hanging (the reference has none)")
     parser.add_argument("--step-scheduler", action="store_true", help="step the 1/(epoch+1) LambdaLR each epoch (the reference never does)")
     return parser
 
@@ -264,7 +266,8 @@ if __name__ == "__main__":
             os.environ.setdefault("LOCAL_RANK", str(dev.index))
             torch.cuda.set_device(dev)
             kw["device_id"] = dev
-        dist.init_process_group(backend, rank=args.rank, world_size=args.world_size, **kw)
+        from datetime import timedelta
+        dist.init_process_group(backend, rank=args.rank, world_size=args.world_size, timeout=timedelta(seconds=args.timeout_s), **kw)
         if args.server:
             init_server(args)
             dist.destroy_process_group()

@@ -166,3 +166,37 @@ def test_moving_the_model_after_building_the_optimizer_is_reported():
     net.to("meta")
     with pytest.raises(RuntimeError, match="after the optimizer was created"):
         opt.zero_grad()
+
+
+def test_parameter_server_message_semantics_without_a_network(monkeypatch):
+    """Server contract: ParameterUpdate sets, GradientUpdate adds the already -lr-scaled payload,
+    ParameterRequest replies with the current vector; plus the north-star momentum / staleness-scaled update."""
+    from distributed_ml_pytorch_b200.parallel import server as srv
+    from distributed_ml_pytorch_b200.utils.messaging import MessageCode
+    sent = []
+    monkeypatch.setattr(srv, "send_message", lambda code, payload=None, dst=0, group=None: sent.append((code, None if payload is None else payload.clone(), dst)))
+    net = LeNet()
+    n = numel(net)
+    ps = srv.ParameterServer(net, n_workers=2)
+    theta = torch.arange(n, dtype=torch.float32) / n
+    ps.receive(1, MessageCode.ParameterUpdate, theta)
+    ps.receive(1, MessageCode.ParameterRequest, torch.zeros(0))
+    assert sent[-1][0] == MessageCode.ParameterUpdate and sent[-1][2] == 1 and torch.equal(sent[-1][1], theta)
+    delta = torch.full((n,), -0.5)
+    ps.receive(2, MessageCode.GradientUpdate, delta)
+    assert torch.allclose(ps.parameter_shard, theta - 0.5)
+    ps.receive(1, MessageCode.WorkerDone, torch.zeros(0))
+    ps.receive(2, MessageCode.WorkerDone, torch.zeros(0))
+    assert ps.done_workers == {1, 2} and ps.counters == {"ParameterUpdate": 1, "GradientUpdate": 1, "ParameterRequest": 1}
+    # momentum 0.5 + inverse staleness: worker 1 pulled at version 0, two foreign updates later its push is scaled by 1/3
+    ps2 = srv.ParameterServer(net, n_workers=2, momentum=0.5, staleness="inverse")
+    ps2.receive(1, MessageCode.ParameterUpdate, torch.zeros(n))
+    ps2.receive(1, MessageCode.ParameterRequest, torch.zeros(0))
+    one = torch.ones(n)
+    ps2.receive(2, MessageCode.GradientUpdate, one)       # worker 2 never pulled -> tau = 0: v = 1, theta = 1
+    ps2.receive(2, MessageCode.GradientUpdate, one)       # v = 0.5 + 1 = 1.5, theta = 2.5
+    ps2.receive(1, MessageCode.GradientUpdate, one)       # tau = 2: v = 0.75 + 1/3, theta = 2.5 + 0.75 + 1/3
+    assert torch.allclose(ps2.parameter_shard, torch.full((n,), 2.5 + 0.75 + 1 / 3))
+    assert ps2.staleness_hist == {0: 2, 2: 1}
+    snap = ps2.snapshot()
+    assert set(snap.keys()) == set(LeNet().state_dict().keys())
