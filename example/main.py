@@ -62,7 +62,17 @@ class SyntheticLoader:
 
 def get_dataset(args, transform=None):
     """CIFAR-10 through torchvision when it is already on disk (reference main.py:23-29), else synthetic."""
-    if not args.synthetic and os.path.isdir(os.path.join(args.data_root, "cifar-10-batches-py")):
+    on_disk = not args.synthetic and os.path.isdir(os.path.join(args.data_root, "cifar-10-batches-py"))
+    if on_disk and args.cuda and not args.host_data:
+        # B200 path: the 150 MB uint8 image set lives in HBM; shuffling, ToTensor and Normalize are one kernel per batch.
+        from distributed_ml_pytorch_b200.utils.data import GpuResidentLoader, cifar10_arrays
+        device = torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0)))
+        xs, ys = cifar10_arrays(args.data_root, train=True)
+        xt, yt = cifar10_arrays(args.data_root, train=False)
+        train = GpuResidentLoader(xs, ys, args.batch_size, device, shuffle=True, drop_last=True, seed=args.seed + 1000 * (args.rank or 0))
+        test = GpuResidentLoader(xt, yt, args.test_batch_size, device, shuffle=False, drop_last=False)
+        return train, test
+    if on_disk:
         import torchvision
         import torchvision.transforms as transforms
         transform = transform or transforms.Compose([transforms.ToTensor(), transforms.Normalize((0.5, 0.5, 0.5), (0.5, 0.5, 0.5))])
@@ -234,6 +244,8 @@ def build_parser():
     parser.add_argument("--momentum", type=float, default=0.0)
     parser.add_argument("--staleness", default=None, choices=[None, "none", "inverse", "exp"])
     parser.add_argument("--backend", default=None, help="torch.distributed backend (default: nccl with --cuda, gloo otherwise)")
+    parser.add_argument("--host-data", action="store_true", help="keep the torchvision DataLoader on the host even with --cuda "
+                        "(default with --cuda: the dataset is resident on the GPU, utils/data.py)")
     parser.add_argument("--synthetic", action="store_true", help="synthetic CIFAR-shaped data even if ./data holds CIFAR-10")
     parser.add_argument("--data-root", default="./data")
     parser.add_argument("--steps-per-epoch", type=int, default=None)

@@ -132,6 +132,11 @@ int dmlb_bn_bwd_apply(const void* x, int ldx, const void* g, int ldg, void* dx, 
 int dmlb_avgpool_fwd_bf16(const void* x, int ldx, void* y, int ldy, int B, int P, int C, void* stream);
 int dmlb_avgpool_bwd_bf16(const void* dy, int lddy, void* dx, int lddx, int B, int P, int C, void* stream);
 
+/* ---- GPU-resident input pipeline (reference: torchvision ToTensor + Normalize in a host DataLoader, example/main.py:23-40,64-65) ----
+ * images uint8 [N,H,W,C] and labels int64 [N] stay in HBM; one launch gathers index[B], converts to CHW fp32 and normalises. */
+int dmlb_gather_normalize_u8(const void* images, const void* labels, const void* index, float* out_x, void* out_y, int B, int H, int W, int C,
+                             const float* mean3, const float* std3, void* stream);
+
 /* ---- peer memory (reference transport: dist.init_process_group('gloo') + isend/recv, example/main.py:165) ---- */
 int dmlb_peer_alloc(size_t bytes, void** out);            /* zeroed cudaMalloc, shareable with CUDA IPC */
 int dmlb_peer_free(void* p);

@@ -277,3 +277,18 @@ def test_gemm_bias_act_splitk_c_abi(M, N, Kd, split):
         torch.cuda.synchronize()
         assert rel_err(y[:, :N], ref) < 1e-2
         assert ws.abs().max().item() == 0.0
+
+
+@pytest.mark.gpu
+def test_resident_loader_kernel_matches_totensor_normalize():
+    from distributed_ml_pytorch_b200.utils.data import GpuResidentLoader
+    g = torch.Generator().manual_seed(0)
+    imgs = torch.randint(0, 256, (300, 32, 32, 3), generator=g, dtype=torch.uint8)
+    labels = torch.randint(0, 10, (300,), generator=g)
+    ld = GpuResidentLoader(imgs, labels, batch_size=64, device="cuda", shuffle=True, seed=5)
+    idx = torch.randperm(300, device="cuda")[:64]
+    x, y = ld.gather(idx)
+    ref = (imgs[idx.cpu()].permute(0, 3, 1, 2).float() / 255 - 0.5) / 0.5
+    assert torch.allclose(x.cpu(), ref, atol=1e-6) and torch.equal(y.cpu(), labels[idx.cpu()])
+    n = sum(yy.numel() for _, yy in ld)
+    assert n == 4 * 64                                  # drop_last keeps the shape fixed for the captured step

@@ -47,3 +47,38 @@ def test_message_codes_cover_the_reference_protocol():
     names = {c.name for c in MessageCode}
     assert {"ParameterRequest", "GradientUpdate", "ParameterUpdate"} <= names       # reference Asynchronous.py:17,34,49,59
     assert MessageCode(MessageCode.GradientUpdate.value) is MessageCode.GradientUpdate
+
+
+def test_resident_loader_matches_totensor_normalize_on_cpu():
+    from distributed_ml_pytorch_b200.utils.data import GpuResidentLoader
+    g = torch.Generator().manual_seed(0)
+    imgs = torch.randint(0, 256, (50, 32, 32, 3), generator=g, dtype=torch.uint8)
+    labels = torch.randint(0, 10, (50,), generator=g)
+    ld = GpuResidentLoader(imgs.numpy(), labels.numpy(), batch_size=16, device="cpu", shuffle=False)
+    assert len(ld) == 3
+    x, y = next(iter(ld))
+    ref = (imgs[:16].permute(0, 3, 1, 2).float() / 255 - 0.5) / 0.5       # Normalize((.5,.5,.5),(.5,.5,.5))(ToTensor(img))
+    assert torch.allclose(x, ref, atol=1e-6) and torch.equal(y, labels[:16])
+    seen = torch.cat([yy for _, yy in GpuResidentLoader(imgs, labels, 10, "cpu", shuffle=True, seed=3)])
+    assert seen.numel() == 50
+
+
+def _fake_cifar(root, n=40):
+    import os, pickle
+    import numpy as np
+    base = os.path.join(root, "cifar-10-batches-py")
+    os.makedirs(base)
+    rng = np.random.default_rng(0)
+    for name in [f"data_batch_{i}" for i in range(1, 6)] + ["test_batch"]:
+        with open(os.path.join(base, name), "wb") as f:
+            pickle.dump({"data": rng.integers(0, 256, (n, 3072), dtype=np.uint8), "labels": rng.integers(0, 10, n).tolist()}, f)
+    return base
+
+
+def test_cifar10_arrays_reads_torchvision_layout(tmp_path):
+    from distributed_ml_pytorch_b200.utils.data import cifar10_arrays
+    _fake_cifar(str(tmp_path))
+    x, y = cifar10_arrays(str(tmp_path), train=True)
+    assert x.shape == (200, 32, 32, 3) and x.dtype.name == "uint8" and y.shape == (200,)
+    xt, yt = cifar10_arrays(str(tmp_path), train=False)
+    assert xt.shape == (40, 32, 32, 3) and yt.shape == (40,)
