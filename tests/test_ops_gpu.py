@@ -292,3 +292,20 @@ def test_resident_loader_kernel_matches_totensor_normalize():
     assert torch.allclose(x.cpu(), ref, atol=1e-6) and torch.equal(y.cpu(), labels[idx.cpu()])
     n = sum(yy.numel() for _, yy in ld)
     assert n == 4 * 64                                  # drop_last keeps the shape fixed for the captured step
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["alexnet", "lenet"])
+def test_eval_forward_at_reference_test_batch_size(name):
+    """The reference evaluates with one 10000-image batch (main.py:143 --test-batch-size 10000)."""
+    from distributed_ml_pytorch_b200 import models
+    torch.manual_seed(0)
+    net = (models.AlexNet() if name == "alexnet" else models.LeNet()).cuda().eval()
+    ref = (models.AlexNet() if name == "alexnet" else models.LeNet()).eval()
+    ref.load_state_dict({k: v.cpu() for k, v in net.state_dict().items()})
+    x = torch.randn(10000, 3, 32, 32)
+    with torch.no_grad():
+        y = net(x.cuda()).float().cpu()
+        y_ref = ref(x)
+    assert y.shape == (10000, 10)
+    assert ((y - y_ref).norm() / y_ref.norm()).item() < 3e-2
