@@ -120,8 +120,9 @@ def test_conv_module_implicit_vs_explicit_vs_torch(B, Cin, Cout, H, W, k, s, p, 
 
 
 def test_alexnet_graph_step_follows_the_fp32_trajectory():
-    """200 asynchronous-SGD steps on one batch through the CUDA-graph step: the loss must start where torch fp32 SGD on the CPU
-    starts, fall like it does, and end in the same ballpark."""
+    """200 asynchronous-SGD steps on one batch through the CUDA-graph step track torch fp32 SGD on the CPU step by step.
+    (lr 0.05 keeps the run in the regime where the trajectory is well conditioned; measured gap <= 3e-4 over six repeats.  At
+    lr 0.1 the loss takes off after ~100 steps and bf16 / atomic-ordering noise legitimately separates the curves.)"""
     from distributed_ml_pytorch_b200.engine import TrainStep
     from distributed_ml_pytorch_b200.models import build_model
     from distributed_ml_pytorch_b200.parallel import Asynchronous
@@ -132,11 +133,11 @@ def test_alexnet_graph_step_follows_the_fp32_trajectory():
     net = net.cuda().train()
     x = torch.randn(64, 3, 32, 32)
     y = torch.randint(0, 10, (64,))
-    opt = Asynchronous(net.parameters(), lr=0.1, n_push=1, n_pull=1, model=net)
+    opt = Asynchronous(net.parameters(), lr=0.05, n_push=1, n_pull=1, model=net)
     ts = TrainStep(net, opt, 64, (3, 32, 32))
     xg, yg = x.cuda(), y.cuda()
     gpu = [ts(xg, yg, sync=True).loss for _ in range(200)]
-    sgd = torch.optim.SGD(ref.parameters(), lr=0.1)
+    sgd = torch.optim.SGD(ref.parameters(), lr=0.05)
     cpu = []
     for _ in range(200):
         sgd.zero_grad()
@@ -145,8 +146,7 @@ def test_alexnet_graph_step_follows_the_fp32_trajectory():
         sgd.step()
         cpu.append(loss.item())
     assert all(v == v for v in gpu)
-    assert abs(gpu[0] - cpu[0]) < 0.02, (gpu[0], cpu[0])                      # same start (measured: equal to 1e-5)
-    assert gpu[-1] < gpu[0] - 0.3 and cpu[-1] < cpu[0] - 0.3, (gpu[0], gpu[-1], cpu[0], cpu[-1])
-    # once the loss takes off the two runs separate (bf16 vs fp32 noise in a chaotic phase): same ballpark is all that is defined
-    assert 0.5 < gpu[-1] / cpu[-1] < 1.5, (gpu[-1], cpu[-1])
+    gap = max(abs(g - c) for g, c in zip(gpu, cpu))
+    assert gap < 5e-3, gap
+    assert gpu[-1] < gpu[0] - 0.15 and cpu[-1] < cpu[0] - 0.15, (gpu[0], gpu[-1], cpu[0], cpu[-1])
     opt.finish()
