@@ -38,6 +38,16 @@ struct GemmEpilogue {
     int atomic;           // red.add into fp32 out
     int perm_cin;         // >0: out column c -> (c % perm_cin) * perm_khw + c / perm_cin
     int perm_khw;
+    // Split-K with the finishing pass folded in ("last CTA of a tile finishes"): every z-slice red.adds its partial tile into the
+    // fp32 workspace `out`, then bumps the tile's arrival counter; the slice that arrives last reads the summed tile back from L2,
+    // applies bias / ReLU, rounds to bf16 into fin_y (optionally also the 2x2/2 max-pool into fin_pooled), and writes zeros back,
+    // so workspace and counters are clean for the next layer and no separate finishing launch is needed.
+    int* fin_counters;    // nullptr = off; [tiles_n * tiles_m] ints, all zero on entry and on exit
+    void* fin_y;          // bf16 [M, fin_ldy]
+    const float* fin_bias;
+    void* fin_pooled;     // bf16 [M/4, fin_ldp] when fin_pool_w > 0
+    int fin_ldy, fin_ldp, fin_relu;
+    int fin_pool_w;       // W of the [B,H,W] map the rows enumerate (H, W even, 128 % (2W) == 0); 0 = no pooling
 };
 
 // Operand sources.  A: 0 = K-major matrix (2-D TMA), 1 = MN-major matrix, 2 = im2col gather of an NHWC activation
@@ -139,6 +149,107 @@ __device__ __forceinline__ void gemm_epilogue_tile(uint32_t tmem_d, int q, int l
 #pragma unroll
                 for (int j = 0; j < 32; ++j)
                     if (j < ncols) o[col0 + j] = __float2bfloat16_rn(f[j]);
+            }
+        }
+    }
+}
+
+// bf16 store of 4 finished values (bias / ReLU applied by the caller); returns them as rounded floats for the pool.
+__device__ __forceinline__ void fin_store4(__nv_bfloat16* dst, float (&x)[4], int nvalid) {
+    if (nvalid == 4) {
+        uint2 pk;
+        pk.x = pack_bf16x2(x[0], x[1]);
+        pk.y = pack_bf16x2(x[2], x[3]);
+        *reinterpret_cast<uint2*>(dst) = pk;
+    } else {
+        for (int j = 0; j < nvalid; ++j) dst[j] = __float2bfloat16_rn(x[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) x[j] = __bfloat162float(__float2bfloat16_rn(x[j]));
+}
+
+// Finishing pass of one 128 x BN tile by the 128 epilogue threads of the CTA that arrived last (see GemmEpilogue::fin_counters).
+// A warp walks rows, its lanes the columns (4 floats each), so every access is a coalesced 512-byte row segment out of L2.
+template <int BN>
+__device__ __forceinline__ void splitk_finish_tile(const GemmEpilogue& ep, int ew, int lane, int m0, int n0, int M, int N) {
+    float* __restrict__ ws = static_cast<float*>(ep.out);
+    const int ldw = ep.ldo;
+    __nv_bfloat16* __restrict__ y = static_cast<__nv_bfloat16*>(ep.fin_y);
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+    for (int c = lane * 4; c < BN; c += 128) {
+        const int col = n0 + c;
+        if (col >= N) break;
+        const int nvalid = min(4, N - col);
+        float b[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) b[j] = (ep.fin_bias != nullptr && j < nvalid) ? __ldg(ep.fin_bias + col + j) : 0.f;
+        if (ep.fin_pool_w == 0) {
+            constexpr int kU = 16;
+#pragma unroll 1
+            for (int r0 = ew * 32; r0 < ew * 32 + 32; r0 += kU) {
+                float4 v[kU];
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    const int row = m0 + r0 + u;
+                    v[u] = row < M ? __ldcg(reinterpret_cast<const float4*>(ws + static_cast<size_t>(row) * ldw + col)) : zero4;
+                }
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    const int row = m0 + r0 + u;
+                    if (row >= M) continue;
+                    __stcg(reinterpret_cast<float4*>(ws + static_cast<size_t>(row) * ldw + col), zero4);
+                    float x[4] = {v[u].x + b[0], v[u].y + b[1], v[u].z + b[2], v[u].w + b[3]};
+                    if (ep.fin_relu) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) x[j] = fmaxf(x[j], 0.f);
+                    }
+                    fin_store4(y + static_cast<size_t>(row) * ep.fin_ldy + col, x, nvalid);
+                }
+            }
+        } else {
+            // rows of the tile are NHWC pixels; m0 is a multiple of 2W, so the tile holds 128/(2W) row pairs = 32 whole windows
+            __nv_bfloat16* __restrict__ pooled = static_cast<__nv_bfloat16*>(ep.fin_pooled);
+            const int W = ep.fin_pool_w, Wp = W >> 1;
+            const int pair0 = m0 / (2 * W);
+            constexpr int kU = 4;
+#pragma unroll 1
+            for (int j0 = ew * 8; j0 < ew * 8 + 8; j0 += kU) {
+                float4 v[kU][4];
+                int base[kU];
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    const int j = j0 + u;
+                    const int pr = j / Wp, wp = j - pr * Wp;
+                    base[u] = m0 + pr * 2 * W + 2 * wp;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int row = base[u] + (q >> 1) * W + (q & 1);
+                        v[u][q] = base[u] < M ? __ldcg(reinterpret_cast<const float4*>(ws + static_cast<size_t>(row) * ldw + col)) : zero4;
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    if (base[u] >= M) continue;
+                    const int j = j0 + u;
+                    const int pr = j / Wp, wp = j - pr * Wp;
+                    float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int row = base[u] + (q >> 1) * W + (q & 1);
+                        __stcg(reinterpret_cast<float4*>(ws + static_cast<size_t>(row) * ldw + col), zero4);
+                        float x[4] = {v[u][q].x + b[0], v[u][q].y + b[1], v[u][q].z + b[2], v[u][q].w + b[3]};
+                        if (ep.fin_relu) {
+#pragma unroll
+                            for (int jj = 0; jj < 4; ++jj) x[jj] = fmaxf(x[jj], 0.f);
+                        }
+                        fin_store4(y + static_cast<size_t>(row) * ep.fin_ldy + col, x, nvalid);
+#pragma unroll
+                        for (int jj = 0; jj < 4; ++jj) mx[jj] = fmaxf(mx[jj], x[jj]);
+                    }
+                    const size_t mp = static_cast<size_t>(pair0 + pr) * Wp + wp;
+                    fin_store4(pooled + mp * ep.fin_ldp + col, mx, nvalid);
+                }
             }
         }
     }
@@ -289,6 +400,22 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         mbar_wait(tmem_full_bar, 0);
         tcgen05_fence_after();
         gemm_epilogue_tile<BN>(tmem_d, q, lane, m0, n0, M, N, ep, ep.bias != nullptr && (!ep.atomic || blockIdx.z == 0));
+        if (ep.fin_counters != nullptr) {
+            // release: this thread's red.adds are ordered before the counter bump; acquire on the other side before reading back
+            __threadfence();
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (warp == 2 && lane == 0) {
+                int* ctr = ep.fin_counters + blockIdx.y * gridDim.x + blockIdx.x;
+                const bool last = atomicAdd(ctr, 1) == static_cast<int>(gridDim.z) - 1;
+                if (last) *ctr = 0;       // nobody else touches this counter before the next kernel
+                tmem_holder_ptr[1] = last ? 1u : 0u;
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (tmem_holder_ptr[1] != 0u) {
+                __threadfence();
+                splitk_finish_tile<BN>(ep, warp - 2, lane, m0, n0, M, N);
+            }
+        }
     }
 
     tcgen05_fence_before();
@@ -636,19 +763,52 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmE
     if constexpr (BN <= 128 && BMODE == 0) {
         // forward form only (both operands K-major): the backward GEMMs share the GPU with the side-stream wgrad branch and a grid
         // that pins every SM would serialise against it.  Short reductions only: with a long K loop the per-tile set-up is already amortised and the 2-CTA variant rasterises better
-        if (splits == 1 && nkb <= 24 && ctas >= 3ll * dmlb_sm_count() && dmlb_gemm_persistent_enabled())
+        if (splits == 1 && ep.fin_counters == nullptr && nkb <= 24 && ctas >= 3ll * dmlb_sm_count() && dmlb_gemm_persistent_enabled())
             return launch_gemm_persistent<BN, AM, BMODE>(ta, tb, ep, cv, M, N, K, stream);
     }
     if (BN <= 128 && ctas > dmlb_sm_count()) return launch_gemm_v<BN, AM, BMODE, true>(ta, tb, ep, cv, M, N, K, splits, stream);
     return launch_gemm_v<BN, AM, BMODE, false>(ta, tb, ep, cv, M, N, K, splits, stream);
 }
 
+// Arguments of the folded finishing pass (GemmEpilogue::fin_*), validated here.
+struct FinishArgs {
+    int* counters;
+    int n_counters;
+    const float* bias;
+    int relu;
+    void* y;
+    int ldy;
+    int pool_h, pool_w;   // 0, 0 = no pooling
+    void* pooled;
+    int ldp;
+};
+
+static int apply_finish(GemmEpilogue& ep, const FinishArgs& f, int M, int N, int BN) {
+    DMLB_REQUIRE(ep.atomic && ep.out_is_f32 && ep.bias == nullptr && ep.perm_cin == 0, "fused finish needs a plain accumulating fp32 workspace");
+    DMLB_REQUIRE(ep.ldo % 4 == 0 && ep.ldo >= N && (reinterpret_cast<uintptr_t>(ep.out) & 15) == 0, "workspace pitch must be a multiple of 4 covering N, base 16-byte aligned");
+    DMLB_REQUIRE(f.counters != nullptr && f.y != nullptr && f.ldy % 4 == 0 && (reinterpret_cast<uintptr_t>(f.y) & 7) == 0, "fused finish: bad output");
+    const long long tiles = 1ll * ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN);
+    DMLB_REQUIRE(tiles <= f.n_counters, "fused finish: more output tiles than arrival counters");
+    ep.fin_counters = f.counters; ep.fin_y = f.y; ep.fin_bias = f.bias; ep.fin_ldy = f.ldy; ep.fin_relu = f.relu;
+    ep.fin_pooled = nullptr; ep.fin_ldp = 0; ep.fin_pool_w = 0;
+    if (f.pool_w > 0) {
+        DMLB_REQUIRE(f.pool_h % 2 == 0 && f.pool_w % 2 == 0 && kBM % (2 * f.pool_w) == 0 && M % (f.pool_h * f.pool_w) == 0,
+                     "fused 2x2 pool needs an even [H,W] map whose row pairs tile 128 rows (W = 2..64, power of two)");
+        DMLB_REQUIRE(f.pooled != nullptr && f.ldp % 4 == 0 && (reinterpret_cast<uintptr_t>(f.pooled) & 7) == 0, "fused pool: bad pooled output");
+        ep.fin_pooled = f.pooled; ep.fin_ldp = f.ldp; ep.fin_pool_w = f.pool_w;
+    }
+    return 0;
+}
+
+// 1 when dmlb_*_fin can fold the 2x2/2 pool for an [H, W] map (otherwise run the pool as its own kernel).
+extern "C" int dmlb_fin_pool_supported(int H, int W) { return (H > 0 && W > 0 && H % 2 == 0 && W % 2 == 0 && kBM % (2 * W) == 0) ? 1 : 0; }
+
 }  // namespace dmlb
 
 using namespace dmlb;
 
 // See include/dmlb.h for the contract.
-extern "C" int dmlb_gemm_bf16(const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major, int M, int N, int K,
+static int gemm_bf16_impl(const FinishArgs* fin, const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major, int M, int N, int K,
                               void* out, int out_is_f32, int ldo, const float* bias, int relu, int split_k, int atomic,
                               int perm_cin, int perm_khw, int tile_n, void* stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -673,9 +833,13 @@ extern "C" int dmlb_gemm_bf16(const void* A, int lda, int a_mn_major, const void
     else             rc = make_tmap_bf16(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, kBK);
     if (rc) return rc;
 
-    GemmEpilogue ep;
+    GemmEpilogue ep = {};
     ep.out = out; ep.bias = bias; ep.ldo = ldo; ep.out_is_f32 = out_is_f32; ep.relu = relu; ep.atomic = atomic;
     ep.perm_cin = perm_cin; ep.perm_khw = perm_khw;
+    if (fin != nullptr) {
+        rc = apply_finish(ep, *fin, M, N, BN);
+        if (rc) return rc;
+    }
 
     ConvK cv = {};
 #define DMLB_GEMM_CASE(bn, amn, bmn) \
@@ -701,7 +865,7 @@ extern "C" int dmlb_gemm_bf16(const void* A, int lda, int a_mn_major, const void
 //                   n_out = Cin;  (Ha, Wa) are the conv OUTPUT extents, the result has the conv INPUT extents.
 // Needs Ca % 64 == 0 (a 64-wide k-block must stay inside one filter tap); for dgrad also n_out % 8 == 0.
 // Epilogue arguments as in dmlb_gemm_bf16.  Reference: nn.Conv2d forward/backward in example/models.py:29-39 (cuDNN there).
-extern "C" int dmlb_conv_implicit_bf16(int kind, const void* act, int ld_act, int B, int Ha, int Wa, int Ca, const void* other, int ld_other,
+static int conv_implicit_impl(const FinishArgs* fin, int kind, const void* act, int ld_act, int B, int Ha, int Wa, int Ca, const void* other, int ld_other,
                                        int KH, int KW, int SH, int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo,
                                        const float* bias, int relu, int split_k, int atomic, int tile_n, void* stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -711,7 +875,7 @@ extern "C" int dmlb_conv_implicit_bf16(int kind, const void* act, int ld_act, in
     if (split_k > 1) atomic = 1;
     DMLB_REQUIRE(!atomic || out_is_f32, "atomic / split-K output must be fp32");
     DMLB_REQUIRE(!(atomic && relu), "ReLU cannot be fused into an accumulating epilogue");
-    GemmEpilogue ep;
+    GemmEpilogue ep = {};
     ep.out = out; ep.bias = bias; ep.ldo = ldo; ep.out_is_f32 = out_is_f32; ep.relu = relu; ep.atomic = atomic; ep.perm_cin = 0; ep.perm_khw = 0;
     ConvK cv = {};
     cv.C = Ca; cv.KH = KH; cv.KW = KW; cv.sh = SH; cv.sw = SW;
@@ -731,6 +895,7 @@ extern "C" int dmlb_conv_implicit_bf16(int kind, const void* act, int ld_act, in
             if (rc) return rc;
             rc = make_tmap_bf16(&tb, other, (uint64_t)Kd, (uint64_t)N, (uint64_t)ld_other, kBK, (uint32_t)BN);
             if (rc) return rc;
+            if (fin != nullptr && (rc = apply_finish(ep, *fin, (int)Mpix, N, BN)) != 0) return rc;
             if (BN == 32) return launch_gemm<32, 2, 0>(ta, tb, ep, cv, (int)Mpix, N, Kd, split_k, stream);
             if (BN == 64) return launch_gemm<64, 2, 0>(ta, tb, ep, cv, (int)Mpix, N, Kd, split_k, stream);
             if (BN == 128) return launch_gemm<128, 2, 0>(ta, tb, ep, cv, (int)Mpix, N, Kd, split_k, stream);
@@ -738,6 +903,7 @@ extern "C" int dmlb_conv_implicit_bf16(int kind, const void* act, int ld_act, in
         } else {
             const int Cout = n_out;
             int BN = tile_n ? tile_n : 128;
+            DMLB_REQUIRE(fin == nullptr, "weight gradients accumulate into the arena; there is nothing to finish");
             rc = make_tmap_bf16(&ta, other, (uint64_t)Cout, (uint64_t)Mpix, (uint64_t)ld_other, 64, kBK);   // dY as MN-major A
             if (rc) return rc;
             rc = make_tmap_im2col(&tb, act, Ca, Wa, Ha, B, ld_act, -PW, -PH, PW - (KW - 1), PH - (KH - 1), SW, SH, kBK);
@@ -760,9 +926,44 @@ extern "C" int dmlb_conv_implicit_bf16(int kind, const void* act, int ld_act, in
         if (rc) return rc;
         rc = make_tmap_w3d(&tb, other, Cin, KH * KW, Cout, ld_other);
         if (rc) return rc;
+        if (fin != nullptr && (rc = apply_finish(ep, *fin, (int)Mpix, Cin, BN)) != 0) return rc;
         if (BN == 64) return launch_gemm<64, 2, 3>(ta, tb, ep, cv, (int)Mpix, Cin, Kd, split_k, stream);
         if (BN == 128) return launch_gemm<128, 2, 3>(ta, tb, ep, cv, (int)Mpix, Cin, Kd, split_k, stream);
     }
     dmlb_set_error("dmlb_conv_implicit_bf16: unsupported tile_n for this kind");
     return -4;
+}
+
+
+extern "C" int dmlb_gemm_bf16(const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major, int M, int N, int K, void* out,
+                              int out_is_f32, int ldo, const float* bias, int relu, int split_k, int atomic, int perm_cin, int perm_khw,
+                              int tile_n, void* stream) {
+    return gemm_bf16_impl(nullptr, A, lda, a_mn_major, B, ldb, b_mn_major, M, N, K, out, out_is_f32, ldo, bias, relu, split_k, atomic, perm_cin,
+                          perm_khw, tile_n, stream);
+}
+
+extern "C" int dmlb_conv_implicit_bf16(int kind, const void* act, int ld_act, int B, int Ha, int Wa, int Ca, const void* other, int ld_other,
+                                       int KH, int KW, int SH, int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo,
+                                       const float* bias, int relu, int split_k, int atomic, int tile_n, void* stream) {
+    return conv_implicit_impl(nullptr, kind, act, ld_act, B, Ha, Wa, Ca, other, ld_other, KH, KW, SH, SW, PH, PW, n_out, out, out_is_f32, ldo, bias,
+                              relu, split_k, atomic, tile_n, stream);
+}
+
+// Split-K GEMM / implicit convolution with the finishing pass folded into the GEMM kernel (one launch instead of two):
+//   y[M,N] (bf16, pitch ldy) = act(A * B^T + bias), optionally also pooled = maxpool2x2(y) for rows that enumerate a [.., pool_h, pool_w] map.
+//   ws: fp32 [M, ldw] scratch and counters: int [n_counters >= output tiles] — both all zero on entry and all zero again on exit.
+extern "C" int dmlb_gemm_bf16_fin(const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major, int M, int N, int K, float* ws,
+                                  int ldw, int* counters, int n_counters, const float* bias, int relu, void* y, int ldy, int pool_h, int pool_w,
+                                  void* pooled, int ldp, int split_k, int tile_n, void* stream) {
+    const FinishArgs fin = {counters, n_counters, bias, relu, y, ldy, pool_h, pool_w, pooled, ldp};
+    return gemm_bf16_impl(&fin, A, lda, a_mn_major, B, ldb, b_mn_major, M, N, K, ws, 1, ldw, nullptr, 0, split_k, 1, 0, 0, tile_n, stream);
+}
+
+extern "C" int dmlb_conv_implicit_fin(int kind, const void* act, int ld_act, int B, int Ha, int Wa, int Ca, const void* other, int ld_other, int KH,
+                                      int KW, int SH, int SW, int PH, int PW, int n_out, float* ws, int ldw, int* counters, int n_counters,
+                                      const float* bias, int relu, void* y, int ldy, int pool_h, int pool_w, void* pooled, int ldp, int split_k,
+                                      int tile_n, void* stream) {
+    const FinishArgs fin = {counters, n_counters, bias, relu, y, ldy, pool_h, pool_w, pooled, ldp};
+    return conv_implicit_impl(&fin, kind, act, ld_act, B, Ha, Wa, Ca, other, ld_other, KH, KW, SH, SW, PH, PW, n_out, ws, 1, ldw, nullptr, 0, split_k,
+                              1, tile_n, stream);
 }

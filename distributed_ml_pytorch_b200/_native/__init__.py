@@ -29,6 +29,14 @@ _SIGNATURES = {
                        c_int, c_int, c_int, c_vp],
     "dmlb_conv_implicit_bf16": [c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_vp,
                                 c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_vp],
+    # (A, lda, a_mn, B, ldb, b_mn, M, N, K, ws, ldw, counters, n_counters, bias, relu, y, ldy, pool_h, pool_w, pooled, ldp, split_k, tile_n, stream)
+    "dmlb_gemm_bf16_fin": [c_vp, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_int, c_int,
+                           c_int, c_vp, c_int, c_int, c_int, c_vp],
+    # (kind, act, ld_act, B, Ha, Wa, Ca, other, ld_other, KH, KW, SH, SW, PH, PW, n_out, ws, ldw, counters, n_counters, bias, relu, y, ldy,
+    #  pool_h, pool_w, pooled, ldp, split_k, tile_n, stream)
+    "dmlb_conv_implicit_fin": [c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_vp,
+                               c_int, c_vp, c_int, c_vp, c_int, c_vp, c_int, c_int, c_int, c_vp, c_int, c_int, c_int, c_vp],
+    "dmlb_fin_pool_supported": [c_int, c_int],
     "dmlb_splitk_finish": [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_ll, c_int, c_int, c_int, c_int, c_int, c_vp, c_int, c_vp],
     "dmlb_gemm_bias_act_splitk": [c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_vp, c_vp, c_int, c_vp, c_int, c_int, c_vp],
     "dmlb_im2col_nhwc_bf16": [c_vp, c_vp] + [c_int] * 12 + [c_vp],

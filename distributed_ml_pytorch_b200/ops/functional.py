@@ -272,16 +272,29 @@ class _ConvBlockFn(torch.autograd.Function):
         out = y
         fused_pool = False
         if split > 1:
-            # tiny-M / long-K layer: spread K over the SMs, reduce in an fp32 workspace, finish (+pool) in one kernel
+            # tiny-M / long-K layer: spread K over the SMs, reduce in an fp32 workspace, finish (bias, ReLU, bf16, 2x2 pool) in one
+            # more kernel — or, opt-in (K.set_fused_finish(True); measured slower), in the GEMM's last-arriving CTA per tile
             ldw = (Cout + 3) // 4 * 4
             ws = K.splitk_workspace(dev, M * ldw)
-            fprop(ws, ldw, split_k=split, atomic=True)
-            if cfg.pool == (2, 2, 0) and Ho % 2 == 0 and Wo % 2 == 0:
-                out = new_act4(B, Cout, Ho // 2, Wo // 2, dev)
-                K.splitk_finish(ws, ldw, bias, cfg.relu, y.data_ptr(), ldy, M, Cout, pool2=(B, Ho, Wo), pooled_ptr=out.data_ptr(), ldp=ldy)
-                fused_pool = True
+            want_pool = cfg.pool == (2, 2, 0) and Ho % 2 == 0 and Wo % 2 == 0
+            if K.fused_finish() and (not want_pool or K.fin_pool_supported(Ho, Wo)):
+                if want_pool:
+                    out = new_act4(B, Cout, Ho // 2, Wo // 2, dev)
+                    fused_pool = True
+                fin = dict(pool_hw=(Ho, Wo) if want_pool else None, pooled_ptr=out.data_ptr() if want_pool else 0, ldp=ldy if want_pool else 0)
+                if implicit:
+                    K.conv_implicit_fin(0, x.data_ptr(), ldx, B, H, W, Cin, cfg.shadow.data_ptr(), Kpad, KH, KW, SH, SW, PH, PW, Cout, ws, ldw, bias,
+                                        cfg.relu, y.data_ptr(), ldy, split, **fin)
+                else:
+                    K.gemm_fin(a_t, lda, False, cfg.shadow, Kpad, False, M, Cout, Kd, ws, ldw, bias, cfg.relu, y.data_ptr(), ldy, split, **fin)
             else:
-                K.splitk_finish(ws, ldw, bias, cfg.relu, y.data_ptr(), ldy, M, Cout)
+                fprop(ws, ldw, split_k=split, atomic=True)
+                if want_pool:
+                    out = new_act4(B, Cout, Ho // 2, Wo // 2, dev)
+                    K.splitk_finish(ws, ldw, bias, cfg.relu, y.data_ptr(), ldy, M, Cout, pool2=(B, Ho, Wo), pooled_ptr=out.data_ptr(), ldp=ldy)
+                    fused_pool = True
+                else:
+                    K.splitk_finish(ws, ldw, bias, cfg.relu, y.data_ptr(), ldy, M, Cout)
         else:
             fprop(y, ldy, bias=bias, relu=cfg.relu)
         if cfg.pool is not None and not fused_pool:
@@ -373,9 +386,13 @@ class _ConvBlockFn(torch.autograd.Function):
                 if dsplit > 1:
                     ldw = (Cin + 3) // 4 * 4
                     ws = K.splitk_workspace(dev, Min * ldw)
-                    K.conv_implicit(2, dy.data_ptr(), lddy, B, Ho, Wo, Cout, cfg.shadow.data_ptr(), Kpad, KH, KW, 1, 1, PH, PW, Cin, ws, ldw,
-                                    split_k=dsplit, atomic=True)
-                    K.splitk_finish(ws, ldw, None, False, dx.data_ptr(), ldxo, Min, Cin)
+                    if K.fused_finish():
+                        K.conv_implicit_fin(2, dy.data_ptr(), lddy, B, Ho, Wo, Cout, cfg.shadow.data_ptr(), Kpad, KH, KW, 1, 1, PH, PW, Cin, ws, ldw,
+                                            None, False, dx.data_ptr(), ldxo, dsplit)
+                    else:
+                        K.conv_implicit(2, dy.data_ptr(), lddy, B, Ho, Wo, Cout, cfg.shadow.data_ptr(), Kpad, KH, KW, 1, 1, PH, PW, Cin, ws, ldw,
+                                        split_k=dsplit, atomic=True)
+                        K.splitk_finish(ws, ldw, None, False, dx.data_ptr(), ldxo, Min, Cin)
                 else:
                     K.conv_implicit(2, dy.data_ptr(), lddy, B, Ho, Wo, Cout, cfg.shadow.data_ptr(), Kpad, KH, KW, 1, 1, PH, PW, Cin, dx, ldxo)
             else:

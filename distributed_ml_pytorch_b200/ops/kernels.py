@@ -9,6 +9,8 @@ pitches and launches on the current CUDA stream.  Layout conventions (see ``csrc
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from .. import _native
@@ -63,6 +65,60 @@ def splitk_workspace(device, numel: int) -> torch.Tensor:
         ws = torch.zeros(max(numel, 1 << 20), dtype=torch.float32, device=device)
         _workspaces[key] = ws
     return ws
+
+
+_fin_counters = {}
+_FIN_COUNTERS = 4096
+# Measured on B200 (AlexNet step, 8 split-K layers): folded finish 0.2228 ms/step, separate finishing kernel 0.2004 ms/step.  The
+# folded form serialises fence -> counter atomic -> fence -> 64 KB L2 read-back on ONE SM per tile, which costs more than a
+# PDL-overlapped launch that spreads the same read-back over ~100 CTAs.  So it is opt-in (DMLB_FUSED_FINISH=1).
+_fused_finish = [os.environ.get("DMLB_FUSED_FINISH", "0") == "1"]
+
+
+def set_fused_finish(on: bool) -> bool:
+    """Fold the split-K finishing pass into the GEMM kernel, or (default) run it as its own launch; returns the old setting."""
+    old, _fused_finish[0] = _fused_finish[0], bool(on)
+    return old
+
+
+def fused_finish() -> bool:
+    return _fused_finish[0]
+
+
+def fin_counters(device) -> torch.Tensor:
+    """Per-device tile arrival counters of the fused split-K finish (all zero between kernels; shared by every layer because
+    the kernels that use them are ordered on one stream).  First use must happen outside CUDA-graph capture."""
+    key = (device.type, device.index)
+    c = _fin_counters.get(key)
+    if c is None:
+        c = torch.zeros(_FIN_COUNTERS, dtype=torch.int32, device=device)
+        _fin_counters[key] = c
+    return c
+
+
+def fin_pool_supported(H: int, W: int) -> bool:
+    return H > 0 and W > 0 and H % 2 == 0 and W % 2 == 0 and 128 % (2 * W) == 0
+
+
+def gemm_fin(a, lda, a_mn, b, ldb, b_mn, M, N, K, ws: torch.Tensor, ldw: int, bias, relu: bool, y_ptr: int, ldy: int, split_k: int,
+             pool_hw=None, pooled_ptr: int = 0, ldp: int = 0, tile_n: int = 0) -> None:
+    """Split-K GEMM whose last-arriving CTA per tile finishes it (bias, ReLU, bf16, optional 2x2 pool): ``dmlb_gemm_bf16_fin``."""
+    c = fin_counters(ws.device)
+    ph, pw = pool_hw if pool_hw is not None else (0, 0)
+    _call("dmlb_gemm_bf16_fin", a.data_ptr(), lda, int(a_mn), b.data_ptr(), ldb, int(b_mn), M, N, K, ws.data_ptr(), ldw, c.data_ptr(),
+          c.numel(), bias.data_ptr() if bias is not None else None, int(relu), y_ptr, ldy, ph, pw, pooled_ptr or None, ldp, split_k, tile_n,
+          stream_ptr())
+
+
+def conv_implicit_fin(kind: int, act_ptr: int, ld_act: int, B, Ha, Wa, Ca, other_ptr: int, ld_other: int, KH, KW, SH, SW, PH, PW, n_out: int,
+                      ws: torch.Tensor, ldw: int, bias, relu: bool, y_ptr: int, ldy: int, split_k: int, pool_hw=None, pooled_ptr: int = 0,
+                      ldp: int = 0, tile_n: int = 0) -> None:
+    """Implicit-GEMM convolution (fprop / dgrad), split-K, finishing pass folded in: ``dmlb_conv_implicit_fin``."""
+    c = fin_counters(ws.device)
+    ph, pw = pool_hw if pool_hw is not None else (0, 0)
+    _call("dmlb_conv_implicit_fin", kind, act_ptr, ld_act, B, Ha, Wa, Ca, other_ptr, ld_other, KH, KW, SH, SW, PH, PW, n_out, ws.data_ptr(), ldw,
+          c.data_ptr(), c.numel(), bias.data_ptr() if bias is not None else None, int(relu), y_ptr, ldy, ph, pw, pooled_ptr or None, ldp,
+          split_k, tile_n, stream_ptr())
 
 
 def splitk_finish(ws: torch.Tensor, ldw: int, bias, relu: bool, y_ptr: int, ldy: int, M: int, N: int, pool2=None, pooled_ptr: int = 0,

@@ -132,6 +132,18 @@ int dmlb_bn_bwd_apply(const void* x, int ldx, const void* g, int ldg, void* dx, 
 int dmlb_avgpool_fwd_bf16(const void* x, int ldx, void* y, int ldy, int B, int P, int C, void* stream);
 int dmlb_avgpool_bwd_bf16(const void* dy, int lddy, void* dx, int lddx, int B, int P, int C, void* stream);
 
+/* ---- split-K with the finishing pass folded into the GEMM kernel (one launch; measured slower than GEMM + dmlb_splitk_finish on the
+ * AlexNet shapes, see DESIGN.md, hence opt-in).  y[M,N] bf16 = act(A*B^T + bias) and optionally pooled = maxpool2x2(y) when the rows
+ * enumerate a [.., pool_h, pool_w] map (dmlb_fin_pool_supported).  ws (fp32 [M,ldw]) and counters (int [n_counters >= output tiles])
+ * must be all zero on entry and are all zero again on exit.  kind: 0 fprop, 2 dgrad. ---- */
+int dmlb_gemm_bf16_fin(const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major, int M, int N, int K, float* ws, int ldw,
+                       int* counters, int n_counters, const float* bias, int relu, void* y, int ldy, int pool_h, int pool_w, void* pooled,
+                       int ldp, int split_k, int tile_n, void* stream);
+int dmlb_conv_implicit_fin(int kind, const void* act, int ld_act, int B, int Ha, int Wa, int Ca, const void* other, int ld_other, int KH, int KW,
+                           int SH, int SW, int PH, int PW, int n_out, float* ws, int ldw, int* counters, int n_counters, const float* bias,
+                           int relu, void* y, int ldy, int pool_h, int pool_w, void* pooled, int ldp, int split_k, int tile_n, void* stream);
+int dmlb_fin_pool_supported(int H, int W);
+
 /* ---- GPU-resident input pipeline (reference: torchvision ToTensor + Normalize in a host DataLoader, example/main.py:23-40,64-65) ----
  * images uint8 [N,H,W,C] and labels int64 [N] stay in HBM; one launch gathers index[B], converts to CHW fp32 and normalises. */
 int dmlb_gather_normalize_u8(const void* images, const void* labels, const void* index, float* out_x, void* out_y, int B, int H, int W, int C,
