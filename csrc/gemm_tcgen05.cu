@@ -719,10 +719,13 @@ static int launch_gemm_v(const CUtensorMap& ta, const CUtensorMap& tb, const Gem
                          cudaStream_t stream) {
     using S = GemmSmem<BN, kDual>;
     auto kern = gemm_bf16_tcgen05_kernel<BN, AM, BMODE, kDual>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute: remember it per device, not per process
+    static bool attr_set[64] = {};
+    int dev = 0;
+    DMLB_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         DMLB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     const int nkb = (K + kBK - 1) / kBK;
     int kb_per = (nkb + splits - 1) / splits;
@@ -738,10 +741,13 @@ static int launch_gemm_persistent(const CUtensorMap& ta, const CUtensorMap& tb, 
                                   cudaStream_t stream) {
     using S = PersistSmem<BN>;
     auto kern = gemm_bf16_tcgen05_persistent_kernel<BN, AM, BMODE>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute: remember it per device, not per process
+    static bool attr_set[64] = {};
+    int dev = 0;
+    DMLB_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         DMLB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     const int tiles_m = (M + kBM - 1) / kBM, tiles_n = (N + BN - 1) / BN;
     int grid = tiles_m * tiles_n;

@@ -309,3 +309,20 @@ def test_eval_forward_at_reference_test_batch_size(name):
         y_ref = ref(x)
     assert y.shape == (10000, 10)
     assert ((y - y_ref).norm() / y_ref.norm()).item() < 3e-2
+
+
+@pytest.mark.gpu
+def test_gemm_on_every_visible_device_in_one_process():
+    """The > 48 KB shared-memory opt-in is a per-device function attribute; a process that drives several GPUs must get it on each."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    for d in range(min(2, torch.cuda.device_count())):
+        with torch.cuda.device(d):
+            dev = torch.device("cuda", d)
+            torch.manual_seed(d)
+            A = bf(torch.randn(256, 512, device=dev))
+            B = bf(torch.randn(192, 512, device=dev))
+            out = torch.zeros(256, 192, device=dev)
+            K.gemm(A.to(torch.bfloat16), 512, False, B.to(torch.bfloat16), 512, False, 256, 192, 512, out, 192)
+            torch.cuda.synchronize(dev)
+            assert rel_err(out, A @ B.t()) < 1e-5
