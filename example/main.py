@@ -151,6 +151,7 @@ def main(args):
         if step_fn is not None:
             step_fn.flush()
         _sync_step(step_fn, device, before=True)
+        print("epoch {}: {} images in {:.2f} s = {:.0f} images/sec".format(epoch, seen, time.time() - t_epoch, seen / max(1e-9, time.time() - t_epoch)))
         print("learning rate is : {}".format(optimizer.param_groups[0]["lr"]))
         evaluate(net, testloader, args, verbose=True, device=device)
         _sync_step(step_fn, device, before=False)
@@ -161,6 +162,9 @@ def main(args):
     print("wrote", logger.to_csv())
     if hasattr(optimizer, "finish"):
         optimizer.finish()
+    if hasattr(optimizer, "pushes"):
+        stats = optimizer.staleness_stats() if hasattr(optimizer, "staleness_stats") else {}
+        print("pushes: {} | pulls: {}{}".format(optimizer.pushes, optimizer.pulls, " | staleness: {}".format(stats) if stats else ""))
     print("Finished Training")
 
 
