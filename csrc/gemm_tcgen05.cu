@@ -427,6 +427,114 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
 }
 
 // ----------------------------------------------------------------------------------------------
+// CTA-pair variant (tcgen05 cta_group::2) for large GEMMs with both operands K-major: a cluster of two CTAs on the two SMs of a
+// TPC computes one 256 x 256 output tile.  Each CTA stages its own 128 rows of A and only HALF of the B tile (128 of the 256
+// columns); the pair's MMA (M = 256, issued by one thread of the leader CTA) reads both halves, so shared-memory traffic for B is
+// halved per SM and a stage is 32 KB instead of 48 KB (6-deep ring).  Each CTA keeps its 128 x 256 fp32 accumulator in its own
+// TMEM and runs its own epilogue.  Synchronisation: both producers' TMA bytes are counted on the LEADER's full barrier; the
+// leader's tcgen05.commit multicasts the "stage free" / "accumulator ready" arrivals to the barriers of both CTAs.
+// ----------------------------------------------------------------------------------------------
+struct PairSmem {
+    static constexpr int kBN = 256;
+    static constexpr int kABytes = kBM * kBK * 2;          // 128 x 64 bf16 = 16 KiB (this CTA's rows of A)
+    static constexpr int kBBytes = (kBN / 2) * kBK * 2;    // 128 x 64 bf16 = 16 KiB (this CTA's half of the B tile)
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kStages = 6;
+    static constexpr int kTotal = kStages * kStageBytes + 256 + 1024;
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, GemmEpilogue ep, int M,
+                              int N, int K, int kb_per_split) {
+    using S = PairSmem;
+    constexpr int kStages = S::kStages;
+    constexpr int BN = S::kBN;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_base = smem_base + kStages * S::kStageBytes;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
+    const uint32_t tmem_full_bar = bar_base + 8u * (2 * kStages);
+    const uint32_t tmem_holder = bar_base + 8u * (2 * kStages + 1);
+    uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+    volatile uint32_t* tmem_holder_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + kStages * S::kStageBytes + 8 * (2 * kStages + 1));
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();                  // 0 = leader
+    const int m0 = (blockIdx.x >> 1) * (2 * kBM) + static_cast<int>(rank) * kBM;   // this CTA's 128 rows
+    const int n0 = blockIdx.y * BN;
+    const int nkb_total = (K + kBK - 1) / kBK;
+    const int kb_begin = blockIdx.z * kb_per_split;
+    const int kb_end = min(nkb_total, kb_begin + kb_per_split);
+    const int nkb = kb_end - kb_begin;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(full_bar(s), 1);      // leader's: one arrive.expect_tx covering the bytes of both CTAs
+            mbar_init(empty_bar(s), 1);     // one multicast commit per use
+        }
+        mbar_init(tmem_full_bar, 1);
+        fence_mbar_init();
+    }
+    cluster_sync_all();                     // both CTAs' barriers exist before anything can arrive on them remotely
+    if (warp == 1) tmem_alloc_2cta<BN>(tmem_holder);
+    tcgen05_fence_before();
+    __syncthreads();
+    cluster_sync_all();                     // both halves of the pair own their TMEM columns before the leader's first MMA
+    tcgen05_fence_after();
+    const uint32_t tmem_d = *tmem_holder_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int it = 0; it < nkb; ++it) {
+                const int s = it % kStages;
+                const uint32_t ph = (it / kStages) & 1;
+                mbar_wait(empty_bar(s), ph ^ 1);
+                if (rank == 0) mbar_arrive_expect_tx(full_bar(s), 2u * S::kStageBytes);
+                const uint32_t a_dst = smem_base + s * S::kStageBytes;
+                const int kc = (kb_begin + it) * kBK;
+                tma_load_2d_2cta(a_dst, &tma_a, kc, m0, full_bar(s));
+                tma_load_2d_2cta(a_dst + S::kABytes, &tma_b, kc, n0 + static_cast<int>(rank) * (BN / 2), full_bar(s));
+            }
+        }
+    } else if (warp == 1) {
+        if (rank == 0 && lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(2 * kBM, BN, false, false);
+            for (int it = 0; it < nkb; ++it) {
+                const int s = it % kStages;
+                const uint32_t ph = (it / kStages) & 1;
+                mbar_wait(full_bar(s), ph);
+                tcgen05_fence_after();
+                const uint32_t a_src = smem_base + s * S::kStageBytes;
+                const uint32_t b_src = a_src + S::kABytes;
+#pragma unroll
+                for (int k = 0; k < kBK / kUmmaK; ++k)
+                    umma_bf16_2cta(tmem_d, umma_smem_desc(a_src + k * 32, 16, 1024), umma_smem_desc(b_src + k * 32, 16, 1024), idesc,
+                                   (it > 0 || k > 0) ? 1u : 0u);
+                umma_commit_2cta(empty_bar(s));       // frees stage s in both CTAs
+            }
+            umma_commit_2cta(tmem_full_bar);          // both epilogues may start
+        }
+    } else {
+        const int q = warp & 3;
+        mbar_wait(tmem_full_bar, 0);
+        tcgen05_fence_after();
+        gemm_epilogue_tile<BN>(tmem_d, q, lane, m0, n0, M, N, ep, ep.bias != nullptr && (!ep.atomic || blockIdx.z == 0));
+    }
+
+    tcgen05_fence_before();
+    __syncthreads();
+    cluster_sync_all();                     // neither CTA may leave (or free TMEM) while the pair's MMAs / multicast arrivals can still touch it
+    if (warp == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc_2cta<BN>(tmem_d);
+    }
+}
+
+// ----------------------------------------------------------------------------------------------
 // Persistent variant for grids of many tiles (ResNet-sized convolutions): one CTA per SM walks a strided list of output
 // tiles.  Barrier set-up, TMEM allocation and descriptor prefetch are paid once per SM instead of once per tile, the smem
 // ring keeps streaming across tile boundaries, and the accumulator is double-buffered in TMEM (2 x BN columns) so the
@@ -757,6 +865,33 @@ static int launch_gemm_persistent(const CUtensorMap& ta, const CUtensorMap& tb, 
     return 0;
 }
 
+extern "C" int dmlb_gemm_pair_enabled();
+
+// 256 x 256 tiles on CTA pairs (see gemm_bf16_tcgen05_pair_kernel).  B's map has a 128-row box: each CTA loads half of the tile.
+static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb_half, const GemmEpilogue& ep, int M, int N, int K, int splits,
+                            cudaStream_t stream) {
+    using S = PairSmem;
+    auto kern = gemm_bf16_tcgen05_pair_kernel;
+    static bool attr_set[64] = {};
+    int dev = 0;
+    DMLB_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+        DMLB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
+    const int nkb = (K + kBK - 1) / kBK;
+    int kb_per = (nkb + splits - 1) / splits;
+    splits = (nkb + kb_per - 1) / kb_per;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * ((M + 2 * kBM - 1) / (2 * kBM)), (N + S::kBN - 1) / S::kBN, splits);
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = S::kTotal;
+    cfg.stream = stream;
+    DMLB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb_half, ep, M, N, K, kb_per));   // cluster shape comes from __cluster_dims__
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
 extern "C" int dmlb_gemm_persistent_enabled();
 
 // Several waves of tiles and no split-K -> the persistent kernel; more than one wave -> two CTAs per SM; otherwise the deep ring.
@@ -835,7 +970,9 @@ static int gemm_bf16_impl(const FinishArgs* fin, const void* A, int lda, int a_m
     if (!a_mn_major) rc = make_tmap_bf16(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, kBK, kBM);
     else             rc = make_tmap_bf16(&ta, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, kBK);
     if (rc) return rc;
-    if (!b_mn_major) rc = make_tmap_bf16(&tb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, kBK, (uint32_t)BN);
+    // 256-wide tiles of a plain K-major GEMM with at least one full pair of row tiles: CTA pairs (cta_group::2), half a B tile per CTA
+    const bool pair = BN == 256 && !a_mn_major && !b_mn_major && fin == nullptr && M > kBM && dmlb_gemm_pair_enabled();
+    if (!b_mn_major) rc = make_tmap_bf16(&tb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, kBK, (uint32_t)(pair ? BN / 2 : BN));
     else             rc = make_tmap_bf16(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, kBK);
     if (rc) return rc;
 
@@ -847,6 +984,7 @@ static int gemm_bf16_impl(const FinishArgs* fin, const void* A, int lda, int a_m
         if (rc) return rc;
     }
 
+    if (pair) return launch_gemm_pair(ta, tb, ep, M, N, K, split_k, stream);
     ConvK cv = {};
 #define DMLB_GEMM_CASE(bn, amn, bmn) \
     if (BN == bn && (bool)a_mn_major == amn && (bool)b_mn_major == bmn) return launch_gemm<bn, amn ? 1 : 0, bmn ? 1 : 0>(ta, tb, ep, cv, M, N, K, split_k, stream);

@@ -57,6 +57,17 @@ extern "C" int dmlb_gemm_persistent_enabled() {
 }
 extern "C" void dmlb_set_gemm_persistent(int on) { g_persist = on ? 1 : 0; }
 
+// CTA-pair (cta_group::2) GEMM for 256-wide tiles: on unless DMLB_PAIR=0 or dmlb_set_gemm_pair(0).
+static int g_pair = -1;
+extern "C" int dmlb_gemm_pair_enabled() {
+    if (g_pair < 0) {
+        const char* e = getenv("DMLB_PAIR");
+        g_pair = (e != nullptr && e[0] == '0') ? 0 : 1;
+    }
+    return g_pair;
+}
+extern "C" void dmlb_set_gemm_pair(int on) { g_pair = on ? 1 : 0; }
+
 // Number of SMs of the current device (148 on B200); used to size persistent / flat grids.
 extern "C" int dmlb_sm_count() {
     static int cached[64] = {0};

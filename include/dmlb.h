@@ -29,6 +29,9 @@ int dmlb_pdl_enabled(void);               /* programmatic dependent launch betwe
 void dmlb_set_pdl(int on);
 int dmlb_gemm_persistent_enabled(void);   /* persistent double-buffered GEMM for multi-wave short-K grids (opt-in: default 0; env DMLB_PERSISTENT=1) */
 void dmlb_set_gemm_persistent(int on);
+/* 256-wide tiles of plain K-major GEMMs run on CTA pairs (tcgen05 cta_group::2, one 256 x 256 tile per two SMs); 0 switches that off. */
+void dmlb_set_gemm_pair(int on);
+int dmlb_gemm_pair_enabled(void);
 
 /* ---- tcgen05 GEMM (reference: nn.Linear / nn.Conv2d in example/models.py:8-13,28-43) ------------
  * D[M,N] (+)= A[M,K] * B[N,K]^T, bf16 operands, fp32 accumulation in TMEM.

@@ -222,6 +222,26 @@ int main(int argc, char** argv) {
         {200704, 64, 576, 0, 0, 1, 0, 1, 1, 64, 0, 0},
     };
     int fails = 0;
+    if (argc > 1 && !strcmp(argv[1], "--pair")) {
+        // CTA-pair (cta_group::2) kernel: numerics on small / ragged / split-K problems, then 8192^3 with the pair kernel on and off
+        std::vector<Case> pc = {
+            {256, 256, 64, 0, 0, 1, 1, 0, 0, 256, 0, 0},     // one pair, one k-block
+            {512, 512, 512, 0, 0, 1, 1, 0, 0, 256, 0, 0},    // 2 x 2 pairs, ring wraps
+            {300, 700, 200, 0, 0, 1, 0, 1, 1, 256, 0, 0},    // ragged M / N / K, bias + ReLU, bf16 out
+            {256, 256, 3456, 0, 0, 4, 1, 1, 0, 256, 0, 0},   // split-K atomics
+            {1024, 1024, 4096, 0, 0, 1, 0, 0, 0, 256, 0, 0}, // long K: many ring revolutions
+        };
+        for (auto& c : pc) fails += run_case(c, true);
+        Case big = {8192, 8192, 8192, 0, 0, 1, 0, 0, 0, 256, 0, 0};
+        printf("pair kernel on:\n");
+        fails += run_case(big, true, false);
+        dmlb_set_gemm_pair(0);
+        printf("pair kernel off (one CTA per 128 x 256 tile):\n");
+        fails += run_case(big, true, false);
+        dmlb_set_gemm_pair(1);
+        printf(fails ? "HARNESS FAILED (%d)\n" : "HARNESS PASSED\n", fails);
+        return fails ? 1 : 0;
+    }
     if (big_only) {
         Case c = {8192, 8192, 8192, 0, 0, 1, 0, 0, 0, 256, 0, 0};
         fails += run_case(c, true, false);
