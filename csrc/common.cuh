@@ -185,6 +185,10 @@ __device__ __forceinline__ void tma_load_2d_2cta(uint32_t dst_smem, const CUtens
         "l"(reinterpret_cast<uint64_t>(m)), "r"(c_inner), "r"(c_outer), "r"(bar & 0xFEFFFFFFu)
         : "memory");
 }
+// Arrive on the LEADER CTA's mbarrier at this offset (from either CTA of the pair).
+__device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar & 0xFEFFFFFFu) : "memory");
+}
 // One thread of the leader CTA issues the pair's MMA: D[256 x N] (+)= A[256 x 16] * B[N x 16]^T.
 __device__ __forceinline__ void umma_bf16_2cta(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(

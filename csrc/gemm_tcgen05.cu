@@ -534,6 +534,122 @@ gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const _
     }
 }
 
+// Persistent form of the CTA-pair kernel: one cluster per TPC walks a strided list of 256 x 256 tiles.  The accumulator is
+// double-buffered in TMEM (2 x 256 of the 512 columns of each SM), so the epilogue of tile t (tcgen05.ld, bias / ReLU, stores —
+// 128 KB of output per CTA) runs while the pair's tensor cores already work on tile t+1, and the smem ring never drains between
+// tiles.  "Accumulator drained" is signalled by the 4 epilogue warps of BOTH CTAs on the leader's barrier (8 arrivals).
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_tcgen05_pair_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, GemmEpilogue ep,
+                                         int M, int N, int K, int tiles_m2, int tiles_n) {
+    using S = PairSmem;
+    constexpr int kStages = S::kStages;
+    constexpr int BN = S::kBN;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_base = smem_base + kStages * S::kStageBytes;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
+    auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStages + a); };
+    auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStages + 2 + a); };
+    const uint32_t tmem_holder = bar_base + 8u * (2 * kStages + 4);
+    uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+    volatile uint32_t* tmem_holder_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + kStages * S::kStageBytes + 8 * (2 * kStages + 4));
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int nkb = (K + kBK - 1) / kBK;
+    const int num_tiles = tiles_m2 * tiles_n;
+    const int first = blockIdx.x >> 1, stride = gridDim.x >> 1;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(full_bar(s), 1);
+            mbar_init(empty_bar(s), 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(tfull_bar(a), 1);
+            mbar_init(tempty_bar(a), 8);     // 4 epilogue warps x 2 CTAs (only the leader's copy is used)
+        }
+        fence_mbar_init();
+    }
+    cluster_sync_all();
+    if (warp == 1) tmem_alloc_2cta<512>(tmem_holder);
+    tcgen05_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_holder_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int it = 0;
+            for (int tile = first; tile < num_tiles; tile += stride) {
+                const int m0 = (tile % tiles_m2) * (2 * kBM) + static_cast<int>(rank) * kBM;
+                const int nb = (tile / tiles_m2) * BN + static_cast<int>(rank) * (BN / 2);
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int s = it % kStages;
+                    const uint32_t ph = (it / kStages) & 1u;
+                    mbar_wait(empty_bar(s), ph ^ 1u);
+                    if (rank == 0) mbar_arrive_expect_tx(full_bar(s), 2u * S::kStageBytes);
+                    const uint32_t a_dst = smem_base + s * S::kStageBytes;
+                    tma_load_2d_2cta(a_dst, &tma_a, kb * kBK, m0, full_bar(s));
+                    tma_load_2d_2cta(a_dst + S::kABytes, &tma_b, kb * kBK, nb, full_bar(s));
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (rank == 0 && lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(2 * kBM, BN, false, false);
+            int it = 0, t = 0;
+            for (int tile = first; tile < num_tiles; tile += stride, ++t) {
+                const int acc = t & 1;
+                mbar_wait(tempty_bar(acc), ((t >> 1) & 1u) ^ 1u);     // both epilogues have drained this accumulator
+                tcgen05_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (int kb = 0; kb < nkb; ++kb, ++it) {
+                    const int s = it % kStages;
+                    const uint32_t ph = (it / kStages) & 1u;
+                    mbar_wait(full_bar(s), ph);
+                    tcgen05_fence_after();
+                    const uint32_t a_src = smem_base + s * S::kStageBytes;
+                    const uint32_t b_src = a_src + S::kABytes;
+#pragma unroll
+                    for (int k = 0; k < kBK / kUmmaK; ++k)
+                        umma_bf16_2cta(tmem_d, umma_smem_desc(a_src + k * 32, 16, 1024), umma_smem_desc(b_src + k * 32, 16, 1024), idesc,
+                                       (kb > 0 || k > 0) ? 1u : 0u);
+                    umma_commit_2cta(empty_bar(s));
+                }
+                umma_commit_2cta(tfull_bar(acc));
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        int t = 0;
+        for (int tile = first; tile < num_tiles; tile += stride, ++t) {
+            const int acc = t & 1;
+            const int m0 = (tile % tiles_m2) * (2 * kBM) + static_cast<int>(rank) * kBM;
+            const int n0 = (tile / tiles_m2) * BN;
+            mbar_wait(tfull_bar(acc), (t >> 1) & 1u);
+            tcgen05_fence_after();
+            gemm_epilogue_tile<BN>(tmem_base + acc * BN, q, lane, m0, n0, M, N, ep, ep.bias != nullptr);
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(tempty_bar(acc));
+        }
+    }
+
+    tcgen05_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc_2cta<512>(tmem_base);
+    }
+}
+
 // ----------------------------------------------------------------------------------------------
 // Persistent variant for grids of many tiles (ResNet-sized convolutions): one CTA per SM walks a strided list of output
 // tiles.  Barrier set-up, TMEM allocation and descriptor prefetch are paid once per SM instead of once per tile, the smem
@@ -882,8 +998,27 @@ static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb_half, c
     const int nkb = (K + kBK - 1) / kBK;
     int kb_per = (nkb + splits - 1) / splits;
     splits = (nkb + kb_per - 1) / kb_per;
+    const int tiles_m2 = (M + 2 * kBM - 1) / (2 * kBM), tiles_n = (N + S::kBN - 1) / S::kBN;
+    const int clusters = dmlb_sm_count() / 2;
+    if (splits == 1 && tiles_m2 * tiles_n >= 2 * clusters && dmlb_gemm_pair_enabled() != 2) {
+        // at least two tiles per TPC: persistent form, epilogue of tile t overlaps the main loop of tile t+1
+        auto pk = gemm_bf16_tcgen05_pair_persistent_kernel;
+        static bool pattr[64] = {};
+        if (dev < 0 || dev >= 64 || !pattr[dev]) {
+            DMLB_CHECK_CUDA(cudaFuncSetAttribute(pk, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
+            if (dev >= 0 && dev < 64) pattr[dev] = true;
+        }
+        cudaLaunchConfig_t pc = {};
+        pc.gridDim = dim3(2 * clusters);
+        pc.blockDim = dim3(kGemmThreads);
+        pc.dynamicSmemBytes = S::kTotal;
+        pc.stream = stream;
+        DMLB_CHECK_CUDA(cudaLaunchKernelEx(&pc, pk, ta, tb_half, ep, M, N, K, tiles_m2, tiles_n));
+        DMLB_LAUNCH_CHECK();
+        return 0;
+    }
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(2 * ((M + 2 * kBM - 1) / (2 * kBM)), (N + S::kBN - 1) / S::kBN, splits);
+    cfg.gridDim = dim3(2 * tiles_m2, tiles_n, splits);
     cfg.blockDim = dim3(kGemmThreads);
     cfg.dynamicSmemBytes = S::kTotal;
     cfg.stream = stream;

@@ -57,16 +57,17 @@ extern "C" int dmlb_gemm_persistent_enabled() {
 }
 extern "C" void dmlb_set_gemm_persistent(int on) { g_persist = on ? 1 : 0; }
 
-// CTA-pair (cta_group::2) GEMM for 256-wide tiles: on unless DMLB_PAIR=0 or dmlb_set_gemm_pair(0).
+// CTA-pair (cta_group::2) GEMM for 256-wide tiles: 1 = on (default), 0 = off, 2 = on but never the persistent form
+// (env DMLB_PAIR or dmlb_set_gemm_pair).
 static int g_pair = -1;
 extern "C" int dmlb_gemm_pair_enabled() {
     if (g_pair < 0) {
         const char* e = getenv("DMLB_PAIR");
-        g_pair = (e != nullptr && e[0] == '0') ? 0 : 1;
+        g_pair = (e != nullptr && e[0] == '0') ? 0 : ((e != nullptr && e[0] == '2') ? 2 : 1);
     }
     return g_pair;
 }
-extern "C" void dmlb_set_gemm_pair(int on) { g_pair = on ? 1 : 0; }
+extern "C" void dmlb_set_gemm_pair(int on) { g_pair = on < 0 ? 0 : (on > 2 ? 1 : on); }
 
 // Number of SMs of the current device (148 on B200); used to size persistent / flat grids.
 extern "C" int dmlb_sm_count() {

@@ -233,7 +233,14 @@ int main(int argc, char** argv) {
         };
         for (auto& c : pc) fails += run_case(c, true);
         Case big = {8192, 8192, 8192, 0, 0, 1, 0, 0, 0, 256, 0, 0};
-        printf("pair kernel on:\n");
+        Case ragged = {2600, 3600, 100, 0, 0, 1, 1, 1, 0, 256, 0, 0};  // 165 tiles >= 2 per TPC: persistent pair kernel, ragged M / N / K
+        Case deep = {2560, 4096, 192, 0, 0, 1, 0, 1, 1, 256, 0, 0};    // persistent, bf16 out + bias + ReLU, accumulator buffers alternate
+        fails += run_case(ragged, true);
+        fails += run_case(deep, true);
+        printf("pair kernel on (persistent, double-buffered TMEM):\n");
+        fails += run_case(big, true, false);
+        dmlb_set_gemm_pair(2);
+        printf("pair kernel on (one tile per cluster launch):\n");
         fails += run_case(big, true, false);
         dmlb_set_gemm_pair(0);
         printf("pair kernel off (one CTA per 128 x 256 tile):\n");
