@@ -255,7 +255,7 @@ __device__ __forceinline__ void splitk_finish_tile(const GemmEpilogue& ep, int e
     }
 }
 
-template <int BN, int AM, int BMODE, bool kDual>
+template <int BN, int AM, int BMODE, bool kDual, bool kFin = false>
 __global__ void __launch_bounds__(kGemmThreads, ((kDual && BN <= 128) ? 2 : 1))
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                          GemmEpilogue ep, ConvK cv, int M, int N, int K, int kb_per_split) {
@@ -400,7 +400,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         mbar_wait(tmem_full_bar, 0);
         tcgen05_fence_after();
         gemm_epilogue_tile<BN>(tmem_d, q, lane, m0, n0, M, N, ep, ep.bias != nullptr && (!ep.atomic || blockIdx.z == 0));
-        if (ep.fin_counters != nullptr) {
+        if constexpr (kFin) {     // separate instantiation: the finishing code costs ~100 registers the plain kernels should not carry
             // release: this thread's red.adds are ordered before the counter bump; acquire on the other side before reading back
             __threadfence();
             asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -938,11 +938,11 @@ static int make_tmap_w3d(CUtensorMap* map, const void* base, int Cin, int KHW, i
     return 0;
 }
 
-template <int BN, int AM, int BMODE, bool kDual>
+template <int BN, int AM, int BMODE, bool kDual, bool kFin = false>
 static int launch_gemm_v(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpilogue& ep, const ConvK& cv, int M, int N, int K, int splits,
                          cudaStream_t stream) {
     using S = GemmSmem<BN, kDual>;
-    auto kern = gemm_bf16_tcgen05_kernel<BN, AM, BMODE, kDual>;
+    auto kern = gemm_bf16_tcgen05_kernel<BN, AM, BMODE, kDual, kFin>;
     // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute: remember it per device, not per process
     static bool attr_set[64] = {};
     int dev = 0;
@@ -1041,6 +1041,13 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmE
         // that pins every SM would serialise against it.  Short reductions only: with a long K loop the per-tile set-up is already amortised and the 2-CTA variant rasterises better
         if (splits == 1 && ep.fin_counters == nullptr && nkb <= 24 && ctas >= 3ll * dmlb_sm_count() && dmlb_gemm_persistent_enabled())
             return launch_gemm_persistent<BN, AM, BMODE>(ta, tb, ep, cv, M, N, K, stream);
+    }
+    if (ep.fin_counters != nullptr) {
+        // folded split-K finish: forward / dgrad operand forms only, small grids by construction -> deep-ring variant
+        if constexpr ((AM == 0 || AM == 2) && (BMODE == 0 || BMODE == 3) && BN <= 128)
+            return launch_gemm_v<BN, AM, BMODE, false, true>(ta, tb, ep, cv, M, N, K, splits, stream);
+        dmlb_set_error("fused split-K finish is instantiated for K-major / im2col A with K-major / weight-map B and tiles up to 128 wide");
+        return -4;
     }
     if (BN <= 128 && ctas > dmlb_sm_count()) return launch_gemm_v<BN, AM, BMODE, true>(ta, tb, ep, cv, M, N, K, splits, stream);
     return launch_gemm_v<BN, AM, BMODE, false>(ta, tb, ep, cv, M, N, K, splits, stream);

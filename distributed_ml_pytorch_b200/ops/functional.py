@@ -15,6 +15,8 @@ pitch padded to a multiple of 8; they are ordinary ``torch.Tensor`` views of log
 """
 from __future__ import annotations
 
+import os
+
 from types import SimpleNamespace
 from typing import Optional, Tuple
 
@@ -223,6 +225,9 @@ def set_implicit_conv(flag: bool) -> bool:
     return old
 
 
+_PAIR_CONV = os.environ.get("DMLB_PAIR_CONV", "0") == "1"
+
+
 class _ConvBlockFn(torch.autograd.Function):
     """Convolution (+bias +ReLU +max-pool) on the tcgen05 GEMM.
 
@@ -264,6 +269,8 @@ class _ConvBlockFn(torch.autograd.Function):
             if implicit:
                 K.conv_implicit(0, x.data_ptr(), ldx, B, H, W, Cin, cfg.shadow.data_ptr(), Kpad, KH, KW, SH, SW, PH, PW, Cout, out_t, ldo, **kw)
             else:
+                if _PAIR_CONV and direct and Cout >= 256 and M >= 8192 and "tile_n" not in kw and not kw.get("atomic"):
+                    kw["tile_n"] = 256        # wide 1x1 convolutions: 256 x 256 tiles on CTA pairs (persistent, epilogue overlapped)
                 K.gemm(a_t, lda, False, cfg.shadow, Kpad, False, M, Cout, Kd, out_t, ldo, **kw)
 
         y = new_act4(B, Cout, Ho, Wo, dev)
