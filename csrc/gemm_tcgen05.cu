@@ -439,7 +439,7 @@ struct PairSmem {
     static constexpr int kABytes = kBM * kBK * 2;          // 128 x 64 bf16 = 16 KiB (this CTA's rows of A)
     static constexpr int kBBytes = (kBN / 2) * kBK * 2;    // 128 x 64 bf16 = 16 KiB (this CTA's half of the B tile)
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kStages = 6;
+    static constexpr int kStages = 7;             // 7 x 32 KiB + barriers = 225.3 KiB of the 227 KiB a CTA may own
     static constexpr int kTotal = kStages * kStageBytes + 256 + 1024;
 };
 
@@ -540,7 +540,7 @@ gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const _
 // tiles.  "Accumulator drained" is signalled by the 4 epilogue warps of BOTH CTAs on the leader's barrier (8 arrivals).
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_tcgen05_pair_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, GemmEpilogue ep,
-                                         int M, int N, int K, int tiles_m2, int tiles_n) {
+                                         int M, int N, int K, int tiles_m2, int tiles_n, int group_m) {
     using S = PairSmem;
     constexpr int kStages = S::kStages;
     constexpr int BN = S::kBN;
@@ -561,6 +561,15 @@ gemm_bf16_tcgen05_pair_persistent_kernel(const __grid_constant__ CUtensorMap tma
     const int nkb = (K + kBK - 1) / kBK;
     const int num_tiles = tiles_m2 * tiles_n;
     const int first = blockIdx.x >> 1, stride = gridDim.x >> 1;
+    // Tile order: bands of group_m row pairs, column by column inside a band, so the ~74 tiles in flight cover a near-square patch of C
+    // and share A / B panels through L2 (grouped rasterisation).
+    auto tile_mn = [&](int tile, int& mp, int& nt) {
+        const int band = group_m * tiles_n;
+        const int g = tile / band, r = tile - g * band;
+        const int gm = min(group_m, tiles_m2 - g * group_m);
+        nt = r / gm;
+        mp = g * group_m + (r - nt * gm);
+    };
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tma_a);
@@ -587,8 +596,10 @@ gemm_bf16_tcgen05_pair_persistent_kernel(const __grid_constant__ CUtensorMap tma
         if (lane == 0) {
             int it = 0;
             for (int tile = first; tile < num_tiles; tile += stride) {
-                const int m0 = (tile % tiles_m2) * (2 * kBM) + static_cast<int>(rank) * kBM;
-                const int nb = (tile / tiles_m2) * BN + static_cast<int>(rank) * (BN / 2);
+                int mp, nt;
+                tile_mn(tile, mp, nt);
+                const int m0 = mp * (2 * kBM) + static_cast<int>(rank) * kBM;
+                const int nb = nt * BN + static_cast<int>(rank) * (BN / 2);
                 for (int kb = 0; kb < nkb; ++kb, ++it) {
                     const int s = it % kStages;
                     const uint32_t ph = (it / kStages) & 1u;
@@ -630,8 +641,10 @@ gemm_bf16_tcgen05_pair_persistent_kernel(const __grid_constant__ CUtensorMap tma
         int t = 0;
         for (int tile = first; tile < num_tiles; tile += stride, ++t) {
             const int acc = t & 1;
-            const int m0 = (tile % tiles_m2) * (2 * kBM) + static_cast<int>(rank) * kBM;
-            const int n0 = (tile / tiles_m2) * BN;
+            int mp, nt;
+            tile_mn(tile, mp, nt);
+            const int m0 = mp * (2 * kBM) + static_cast<int>(rank) * kBM;
+            const int n0 = nt * BN;
             mbar_wait(tfull_bar(acc), (t >> 1) & 1u);
             tcgen05_fence_after();
             gemm_epilogue_tile<BN>(tmem_base + acc * BN, q, lane, m0, n0, M, N, ep, ep.bias != nullptr);
@@ -1013,7 +1026,13 @@ static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb_half, c
         pc.blockDim = dim3(kGemmThreads);
         pc.dynamicSmemBytes = S::kTotal;
         pc.stream = stream;
-        DMLB_CHECK_CUDA(cudaLaunchKernelEx(&pc, pk, ta, tb_half, ep, M, N, K, tiles_m2, tiles_n));
+        static int group_m = -1;
+        if (group_m < 0) {
+            const char* e = getenv("DMLB_PAIR_GROUP_M");
+            group_m = e != nullptr ? atoi(e) : 8;
+            if (group_m < 1) group_m = 1 << 20;      // 0 = column-major over the whole matrix (no banding)
+        }
+        DMLB_CHECK_CUDA(cudaLaunchKernelEx(&pc, pk, ta, tb_half, ep, M, N, K, tiles_m2, tiles_n, group_m < tiles_m2 ? group_m : tiles_m2));
         DMLB_LAUNCH_CHECK();
         return 0;
     }
