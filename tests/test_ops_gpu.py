@@ -326,3 +326,26 @@ def test_gemm_on_every_visible_device_in_one_process():
             K.gemm(A.to(torch.bfloat16), 512, False, B.to(torch.bfloat16), 512, False, 256, 192, 512, out, 192)
             torch.cuda.synchronize(dev)
             assert rel_err(out, A @ B.t()) < 1e-5
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,N,Kd,bias,relu,out_f32", [
+    (512, 512, 512, False, False, True),       # 2 x 2 CTA pairs, one tile per cluster
+    (300, 700, 200, True, True, False),        # ragged everything, fused bias + ReLU, bf16 out
+    (2600, 3600, 128, True, False, True),      # 165 tiles: persistent pairs, double-buffered TMEM, banded tile order
+    (4096, 2048, 1024, False, False, False),   # persistent, several ring revolutions per tile
+])
+def test_gemm_cta_pair_kernel_matches_fp32(M, N, Kd, bias, relu, out_f32):
+    """256-wide tiles of a K-major GEMM run on CTA pairs (tcgen05 cta_group::2): csrc/gemm_tcgen05.cu pair kernels."""
+    torch.manual_seed(0)
+    dev = "cuda"
+    A = bf(torch.randn(M, Kd, device=dev))
+    B = bf(torch.randn(N, Kd, device=dev) * 0.1)
+    b = torch.randn(N, device=dev) if bias else None
+    ref = A @ B.t() + (b if bias else 0)
+    ref = F.relu(ref) if relu else ref
+    ldo = K.pad8(N)
+    out = torch.zeros(M, ldo, device=dev, dtype=torch.float32 if out_f32 else torch.bfloat16)
+    K.gemm(A.to(torch.bfloat16), Kd, False, B.to(torch.bfloat16), Kd, False, M, N, Kd, out, ldo, bias=b, relu=relu, tile_n=256)
+    torch.cuda.synchronize()
+    assert rel_err(out[:, :N], ref) < (1e-5 if out_f32 else 1e-2)
