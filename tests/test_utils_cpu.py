@@ -82,3 +82,19 @@ def test_cifar10_arrays_reads_torchvision_layout(tmp_path):
     assert x.shape == (200, 32, 32, 3) and x.dtype.name == "uint8" and y.shape == (200,)
     xt, yt = cifar10_arrays(str(tmp_path), train=False)
     assert xt.shape == (40, 32, 32, 3) and yt.shape == (40,)
+
+
+def test_reference_import_paths_resolve():
+    """Every import the reference's own files use (example/main.py:19-21, asgd/optim/__init__.py:1, Asynchronous.py:4-5) works here."""
+    from asgd.optim import Asynchronous, DownpourSGD
+    from asgd.optim.Asynchronous import Asynchronous as A2, Listener
+    from asgd.optim.downpour_sgd import DownpourSGD as D2
+    from asgd.server import ParameterServer
+    from asgd.utils.messaging import MessageCode, MessageListener, send_message
+    from asgd.utils.serialization import ravel_model_params, unravel_model_params
+    import asgd.optim
+    assert A2 is Asynchronous and D2 is DownpourSGD is Asynchronous
+    assert asgd.optim.Asynchronous is Asynchronous            # the class, not a shadowing submodule
+    assert issubclass(Listener, MessageListener)
+    assert {c.name for c in MessageCode} >= {"ParameterRequest", "GradientUpdate", "ParameterUpdate"}
+    assert callable(send_message) and callable(ravel_model_params) and callable(unravel_model_params) and ParameterServer is not None
