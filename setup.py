@@ -19,10 +19,12 @@ class BuildWithNative(build_py):
 setup(
     name="pytorch-distbelief",
     version="0.1.0",
+    license="MIT",
     description="Blackwell-native asynchronous/synchronous SGD (parameter server over NVLink) with the API of distributed_ML_pytorch",
     packages=find_packages(include=["distributed_ml_pytorch_b200*", "asgd*"]),
     package_data={"distributed_ml_pytorch_b200._native": ["libdmlb.so"]},
     include_package_data=True,
+    data_files=[("include", ["include/dmlb.h"])],       # the C ABI of libdmlb.so
     python_requires=">=3.10",
     install_requires=["torch>=2.4", "numpy"],
     cmdclass={"build_py": BuildWithNative},
