@@ -64,3 +64,20 @@ def test_p2p_example_runs():
 def test_azure_submit_is_guarded():
     r = _run([sys.executable, os.path.join(ROOT, "run-pytorch.py")], cwd=ROOT, timeout=60)
     assert r.returncode != 0 and "azureml-core is not installed" in (r.stderr + r.stdout)
+
+
+def test_checkpoint_then_resume_continues_from_the_next_epoch(tmp_path):
+    """--ckpt after every epoch, --resume picks up at epoch+1 with the saved weights (SURVEY.md §5 checkpoint / resume)."""
+    common = [sys.executable, os.path.join(ROOT, "example", "main.py"), "--no-distributed", "--model", "lenet", "--steps-per-epoch", "6",
+              "--log-interval", "1000", "--test-batch-size", "50", "--synthetic", "--ckpt", str(tmp_path / "ck.pt")]
+    r = _run(common + ["--epochs", "1"], cwd=tmp_path)
+    assert r.returncode == 0, r.stderr[-2000:]
+    import torch
+    first = torch.load(tmp_path / "ck.pt", weights_only=False)
+    assert first["meta"]["epoch"] == 0
+    r = _run(common + ["--epochs", "3", "--resume", str(tmp_path / "ck.pt")], cwd=tmp_path)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "Training for epoch 0" not in r.stdout and "Training for epoch 1" in r.stdout and "Training for epoch 2" in r.stdout
+    last = torch.load(tmp_path / "ck.pt", weights_only=False)
+    assert last["meta"]["epoch"] == 2
+    assert not torch.equal(first["model"]["conv1.weight"], last["model"]["conv1.weight"])
