@@ -13,7 +13,6 @@ from __future__ import annotations
 import torch.nn as nn
 
 from .. import nn as dnn
-from ..ops import functional as OF
 
 
 def _conv(cin, cout, k, stride=1):

@@ -57,12 +57,14 @@ class Listener(MessageListener):
             else:
                 with self.owner._lock:
                     self.owner._pending_params = parameter.clone()
+            self.owner._reply_event.set()
 
 
 class Asynchronous(ArenaOptimizer):
     def __init__(self, params, lr, n_push: int, n_pull: int, model: torch.nn.Module, momentum: float = 0.0,
                  staleness: Optional[str] = None, staleness_param: float = 0.9, transport: str = "auto", group=None,
-                 init_rank: Optional[int] = None, torn_pulls: bool = False, server_rank: int = msg.SERVER_RANK):
+                 init_rank: Optional[int] = None, torn_pulls: bool = False, server_rank: int = msg.SERVER_RANK,
+                 blocking_pull: bool = False, pull_timeout_s: float = 60.0):
         if lr < 0.0:
             raise ValueError("Invalid learning rate: {}".format(lr))
         if n_push < 1 or n_pull < 1:
@@ -85,6 +87,10 @@ class Asynchronous(ArenaOptimizer):
         self.server_momentum = float(momentum)
         self.staleness, self.staleness_param = staleness, float(staleness_param)
         self.torn_pulls = torn_pulls
+        # gloo transport only: wait for the server's reply to every pull request and apply it before the next step.  The reference
+        # never waits (replies land whenever the listener thread gets them); this switch makes a run reproducible for debugging.
+        self.blocking_pull, self.pull_timeout_s = bool(blocking_pull), float(pull_timeout_s)
+        self._reply_event = threading.Event()
         self.server_rank = server_rank
         self.group = group
         self.idx = 0
@@ -218,8 +224,13 @@ class Asynchronous(ArenaOptimizer):
                 self.accumulated_gradients.zero_()
                 self.pushes += 1
             if pull_now:
+                self._reply_event.clear()
                 send_message(MessageCode.ParameterRequest, None, dst=self.server_rank)
                 self.pulls += 1
+                if self.blocking_pull:
+                    if not self._reply_event.wait(self.pull_timeout_s):
+                        raise TimeoutError(f"no ParameterUpdate from the server within {self.pull_timeout_s} s")
+                    self._apply_pending()
         else:
             if push_now:
                 self._local_server_apply(self.accumulated_gradients)
@@ -268,6 +279,7 @@ class Asynchronous(ArenaOptimizer):
             msg.flush_sends()
             if self._listener is not None:
                 self._listener.join(timeout=30)
+            self._apply_pending()        # the server answers every request before it echoes WorkerDone: end on its latest parameters
         elif self.transport == "peer":
             torch.cuda.synchronize(self.arena.params.device)
             self.peer.barrier()

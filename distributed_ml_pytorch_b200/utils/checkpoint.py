@@ -9,7 +9,7 @@ momentum, learning rate.
 """
 from __future__ import annotations
 
-from typing import Any, Dict, Optional
+from typing import Any, Dict
 
 import torch
 

@@ -16,7 +16,7 @@ gather — while the optimizers and the push / pull / sync kernels work on the a
 """
 from __future__ import annotations
 
-from typing import Iterable, List
+from typing import List
 
 import torch
 

@@ -43,7 +43,9 @@ def _one_worker(rank, size, out_dir, steps):
         server.run()
         torch.save({"theta": server.parameter_shard, "counters": server.counters}, os.path.join(out_dir, "server.pt"))
         return
-    opt = Asynchronous(net.parameters(), lr=0.05, n_push=1, n_pull=1, model=net)
+    # blocking_pull: every pull reply is applied before the next step, so the run is reproducible (replies otherwise land whenever
+    # the listener thread receives them, and a late one legitimately rewinds the replica by a step)
+    opt = Asynchronous(net.parameters(), lr=0.05, n_push=1, n_pull=1, model=net, blocking_pull=True)
     for i in range(steps):
         x, y = _batch(i)
         opt.zero_grad()

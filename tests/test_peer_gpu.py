@@ -8,7 +8,6 @@ import os
 
 import pytest
 import torch
-import torch.distributed as dist
 import torch.nn.functional as F
 
 pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300)]

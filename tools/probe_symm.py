@@ -17,7 +17,6 @@ try:
     dist.barrier()
     torch.cuda.synchronize()
     if mc:
-        import ctypes
         print(f"rank {rank}: multicast supported", flush=True)
 except Exception as e:
     print(f"rank {rank}: symmetric memory failed: {type(e).__name__}: {e}", flush=True)
