@@ -45,26 +45,31 @@ _STALENESS = {None: 0, "none": 0, "inverse": 1, "exp": 2}
 class Listener(MessageListener):
     """Receives ``ParameterUpdate`` replies from the server (reference Asynchronous.py:9-18)."""
 
-    def __init__(self, model, owner: "Asynchronous", src: int = msg.SERVER_RANK):
-        super().__init__(model, src=src)
+    def __init__(self, model, owner: "Asynchronous", src: Optional[int] = msg.SERVER_RANK, done_expected: int = 1):
+        super().__init__(model, src=src, done_expected=done_expected)
         self.owner = owner
 
     def receive(self, sender, message_code, parameter):
         _LOGGER.info("Processing message: %s", message_code.name)
         if message_code == MessageCode.ParameterUpdate:
-            if self.owner.torn_pulls:
-                unravel_model_params(self.model, parameter)       # reference behaviour: overwrite immediately
-            else:
-                with self.owner._lock:
-                    self.owner._pending_params = parameter.clone()
-            self.owner._reply_event.set()
+            o = self.owner
+            shard = o.server_ranks.index(sender) if sender in o.server_ranks else 0
+            if o.torn_pulls:
+                o._write_shard(shard, parameter)                  # reference behaviour: overwrite immediately
+            with o._lock:
+                if not o.torn_pulls:
+                    o._pending_slices[shard] = parameter.clone()
+                o._replies += 1
+                complete = o._replies >= len(o.server_ranks)
+            if complete:
+                o._reply_event.set()
 
 
 class Asynchronous(ArenaOptimizer):
     def __init__(self, params, lr, n_push: int, n_pull: int, model: torch.nn.Module, momentum: float = 0.0,
                  staleness: Optional[str] = None, staleness_param: float = 0.9, transport: str = "auto", group=None,
                  init_rank: Optional[int] = None, torn_pulls: bool = False, server_rank: int = msg.SERVER_RANK,
-                 blocking_pull: bool = False, pull_timeout_s: float = 60.0):
+                 blocking_pull: bool = False, pull_timeout_s: float = 60.0, server_ranks=None):
         if lr < 0.0:
             raise ValueError("Invalid learning rate: {}".format(lr))
         if n_push < 1 or n_pull < 1:
@@ -92,10 +97,13 @@ class Asynchronous(ArenaOptimizer):
         self.blocking_pull, self.pull_timeout_s = bool(blocking_pull), float(pull_timeout_s)
         self._reply_event = threading.Event()
         self.server_rank = server_rank
+        # gloo transport, NORTH-STAR sharded server: several server ranks, each owning one contiguous slice of the flat vector
+        self.server_ranks = [int(r) for r in server_ranks] if server_ranks else [int(server_rank)]
+        self._pending_slices = {}
+        self._replies = 0
         self.group = group
         self.idx = 0
         self._lock = threading.Lock()
-        self._pending_params: Optional[torch.Tensor] = None
         self._listener: Optional[Listener] = None
         self.pushes = self.pulls = 0
 
@@ -113,12 +121,18 @@ class Asynchronous(ArenaOptimizer):
             self._init_peer()
         elif transport == "gloo":
             self.rank = dist.get_rank()
+            from .arena import ShardMap
+            self._srv_shards = ShardMap(a.numel, len(self.server_ranks), align=1)
             if init_rank is None:
-                init_rank = 1 if self.server_rank == 0 else 0
+                init_rank = min(r for r in range(dist.get_world_size(group)) if r not in self.server_ranks)
             if self.rank == init_rank:
                 # this sets the initial model parameters on the server (reference Asynchronous.py:33-34)
-                send_message(MessageCode.ParameterUpdate, ravel_model_params(model), dst=self.server_rank)
-            self._listener = Listener(model, self, src=self.server_rank)
+                flat = ravel_model_params(model)
+                for k, r in enumerate(self.server_ranks):
+                    b, e = self._srv_shards.valid_bounds(k)
+                    send_message(MessageCode.ParameterUpdate, flat[b:e], dst=r)
+            single = len(self.server_ranks) == 1
+            self._listener = Listener(model, self, src=self.server_ranks[0] if single else None, done_expected=len(self.server_ranks))
             self._listener.start()
         else:
             self._master = a.params.clone()
@@ -220,12 +234,17 @@ class Asynchronous(ArenaOptimizer):
                 self._pull()
         elif self.transport == "gloo":
             if push_now:
-                send_message(MessageCode.GradientUpdate, self.accumulated_gradients[: self.arena.numel], dst=self.server_rank)
+                for k, r in enumerate(self.server_ranks):
+                    b, e = self._srv_shards.valid_bounds(k)
+                    send_message(MessageCode.GradientUpdate, self.accumulated_gradients[b:e], dst=r)
                 self.accumulated_gradients.zero_()
                 self.pushes += 1
             if pull_now:
+                with self._lock:
+                    self._replies = 0
                 self._reply_event.clear()
-                send_message(MessageCode.ParameterRequest, None, dst=self.server_rank)
+                for r in self.server_ranks:
+                    send_message(MessageCode.ParameterRequest, None, dst=r)
                 self.pulls += 1
                 if self.blocking_pull:
                     if not self._reply_event.wait(self.pull_timeout_s):
@@ -253,12 +272,23 @@ class Asynchronous(ArenaOptimizer):
             self._master.add_(delta, alpha=s)
         self._master_version += 1
 
+    def _write_shard(self, shard: int, values: torch.Tensor) -> None:
+        """Overwrite the slice of the model owned by server ``shard`` with ``values`` (one server: the whole model)."""
+        if len(self.server_ranks) == 1:
+            unravel_model_params(self.model, values)
+            return
+        b, e = self._srv_shards.valid_bounds(shard)
+        flat = ravel_model_params(self.model).detach().clone()
+        flat[b:e] = values[: e - b]
+        unravel_model_params(self.model, flat)
+
     def _apply_pending(self) -> None:
-        if self._pending_params is None:
+        if not self._pending_slices:
             return
         with self._lock:
-            p, self._pending_params = self._pending_params, None
-        unravel_model_params(self.model, p)
+            slices, self._pending_slices = self._pending_slices, {}
+        for shard, p in sorted(slices.items()):
+            self._write_shard(shard, p)
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -275,7 +305,8 @@ class Asynchronous(ArenaOptimizer):
     def finish(self) -> None:
         """End of training: flush outstanding traffic, tell the server, release peer memory."""
         if self.transport == "gloo":
-            send_message(MessageCode.WorkerDone, None, dst=self.server_rank)
+            for r in self.server_ranks:
+                send_message(MessageCode.WorkerDone, None, dst=r)
             msg.flush_sends()
             if self._listener is not None:
                 self._listener.join(timeout=30)

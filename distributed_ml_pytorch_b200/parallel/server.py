@@ -25,6 +25,7 @@ import torch.distributed as dist
 from ..utils import messaging as msg
 from ..utils.messaging import MessageCode, recv_message, send_message
 from ..utils.serialization import ravel_model_params, unravel_model_params
+from .arena import ShardMap
 from .async_optim import staleness_scale
 
 _LOGGER = logging.getLogger(__name__)
@@ -32,9 +33,16 @@ _LOGGER = logging.getLogger(__name__)
 
 class ParameterServer:
     def __init__(self, model: torch.nn.Module, n_workers: Optional[int] = None, momentum: float = 0.0, staleness: Optional[str] = None,
-                 staleness_param: float = 0.9, group=None):
+                 staleness_param: float = 0.9, group=None, shard_index: int = 0, n_shards: int = 1):
+        """``n_shards > 1``: the flat parameter vector is cut into ``n_shards`` contiguous pieces (``ShardMap``, the same cut the
+        workers use) and this server owns piece ``shard_index``; every message payload is then that slice (NORTH-STAR sharded
+        server, SURVEY.md §2.4 — the reference has exactly one server rank)."""
         self.model = model
-        self.parameter_shard = ravel_model_params(model).detach().clone().float().cpu()
+        full = ravel_model_params(model).detach().clone().float().cpu()
+        self.shards = ShardMap(full.numel(), n_shards, align=1)
+        self.shard_index, self.n_shards = int(shard_index), int(n_shards)
+        self.bounds = self.shards.valid_bounds(self.shard_index)
+        self.parameter_shard = full[self.bounds[0]:self.bounds[1]].clone()
         self.momentum = float(momentum)
         self.velocity = torch.zeros_like(self.parameter_shard) if self.momentum else None
         self.staleness, self.staleness_param = staleness, staleness_param
@@ -42,7 +50,7 @@ class ParameterServer:
         self.pulled_version: Dict[int, int] = {}
         self.group = group
         if n_workers is None and dist.is_available() and dist.is_initialized():
-            n_workers = dist.get_world_size(group) - 1
+            n_workers = dist.get_world_size(group) - self.n_shards
         self.n_workers = n_workers
         self.done_workers = set()
         self.running = False
@@ -90,12 +98,36 @@ class ParameterServer:
 
     # ------------------------------------------------------------------------------------------
     def snapshot(self) -> dict:
-        """The server's parameters as a ``state_dict`` of ``model`` (keys identical to the reference's models)."""
-        unravel_model_params(self.model, self.parameter_shard)
+        """The server's parameters as a ``state_dict`` of ``model`` (keys identical to the reference's models).  A sharded server
+        only knows its own slice: the rest of the vector keeps the values ``model`` was built with (see :meth:`merge_shards`)."""
+        flat = ravel_model_params(self.model).detach().clone().float().cpu()
+        flat[self.bounds[0]:self.bounds[1]] = self.parameter_shard
+        unravel_model_params(self.model, flat)
         return {k: v.detach().cpu().clone() for k, v in self.model.state_dict().items()}
 
     def save(self, path: str) -> None:
-        torch.save(self.snapshot(), path)
+        """One server: a plain ``state_dict``.  Sharded: this rank's slice, to ``<path>.shard<i>`` (combine with :meth:`merge_shards`)."""
+        if self.n_shards == 1:
+            torch.save(self.snapshot(), path)
+        else:
+            torch.save({"format": "dmlb-server-shard-v1", "shard_index": self.shard_index, "n_shards": self.n_shards, "bounds": self.bounds,
+                        "parameter_shard": self.parameter_shard.clone(), "version": self.version}, f"{path}.shard{self.shard_index}")
+
+    @staticmethod
+    def merge_shards(paths, model: torch.nn.Module) -> dict:
+        """Combine the ``.shard<i>`` files written by every server rank into one ``state_dict`` of ``model``."""
+        flat = ravel_model_params(model).detach().clone().float().cpu()
+        seen = set()
+        for p in paths:
+            part = torch.load(p, weights_only=False)
+            b, e = part["bounds"]
+            flat[b:e] = part["parameter_shard"]
+            seen.add(int(part["shard_index"]))
+            n = int(part["n_shards"])
+        if seen != set(range(n)):
+            raise ValueError(f"need the shards 0..{n - 1}, got {sorted(seen)}")
+        unravel_model_params(model, flat)
+        return {k: v.detach().cpu().clone() for k, v in model.state_dict().items()}
 
     # ------------------------------------------------------------------------------------------
     @staticmethod

@@ -105,12 +105,14 @@ class MessageListener(threading.Thread):
     ``stop()`` ends the loop once the peer sends ``WorkerDone`` (or any message after the flag is set).
     """
 
-    def __init__(self, model, src: Optional[int] = SERVER_RANK, group=None):
+    def __init__(self, model, src: Optional[int] = SERVER_RANK, group=None, done_expected: int = 1):
         super().__init__(daemon=True)
         self.model = model
-        self.src = src
+        self.src = src                        # None = any source (several server ranks)
         self.group = group
         self.running = True
+        self.done_expected = int(done_expected)   # WorkerDone echoes to see before the loop ends (one per server rank)
+        self._done_seen = 0
 
     def receive(self, sender: int, message_code: MessageCode, parameter: torch.Tensor) -> None:
         raise NotImplementedError
@@ -127,6 +129,9 @@ class MessageListener(threading.Thread):
                     _LOGGER.debug("listener exiting: %s", exc)
                 return
             if code == MessageCode.WorkerDone:
-                self.running = False
-                return
+                self._done_seen += 1
+                if self._done_seen >= self.done_expected:
+                    self.running = False
+                    return
+                continue
             self.receive(sender, code, payload)

@@ -97,8 +97,9 @@ def make_optimizer(args, net):
         return optim.SGD(net.parameters(), lr=args.lr, momentum=args.momentum)     # reference main.py:44
     if args.mode == "sync":
         return Synchronous(net.parameters(), lr=args.lr, model=net, momentum=args.momentum)
+    servers = list(range(args.num_servers)) if (args.num_servers > 1 and not args.cuda) else None
     return Asynchronous(net.parameters(), lr=args.lr, n_push=args.num_push, n_pull=args.num_pull, model=net, momentum=args.momentum,
-                        staleness=args.staleness)
+                        staleness=args.staleness, server_ranks=servers)
 
 
 def main(args):
@@ -219,7 +220,8 @@ def init_server(args):
         torch.manual_seed(args.seed)
         ParameterServer.run_peer(model.to(device), momentum=args.momentum, staleness=args.staleness)
         return
-    server = ParameterServer(model=model, momentum=args.momentum, staleness=args.staleness)
+    server = ParameterServer(model=model, momentum=args.momentum, staleness=args.staleness, shard_index=args.rank if args.num_servers > 1 else 0,
+                             n_shards=args.num_servers)
     server.run()
     if args.ckpt:
         server.save(args.ckpt)
@@ -248,6 +250,8 @@ def build_parser():
     parser.add_argument("--momentum", type=float, default=0.0)
     parser.add_argument("--staleness", default=None, choices=[None, "none", "inverse", "exp"])
     parser.add_argument("--backend", default=None, help="torch.distributed backend (default: nccl with --cuda, gloo otherwise)")
+    parser.add_argument("--num-servers", type=int, default=1, help="CPU/gloo: shard the parameter server over ranks 0..K-1 (each started "
+                        "with --server); on GPUs the server is always sharded over all ranks")
     parser.add_argument("--host-data", action="store_true", help="keep the torchvision DataLoader on the host even with --cuda "
                         "(default with --cuda: the dataset is resident on the GPU, utils/data.py)")
     parser.add_argument("--synthetic", action="store_true", help="synthetic CIFAR-shaped data even if ./data holds CIFAR-10")

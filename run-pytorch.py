@@ -28,14 +28,16 @@ def submit_azureml(extra):
     print(aml_url)
 
 
-def launch_local(n, cpu, extra, port):
+def launch_local(n, cpu, extra, port, servers=1):
     procs = []
     for rank in range(n):
         env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(n), LOCAL_RANK=str(rank))
         cmd = [sys.executable, os.path.join(HERE, "example", "main.py"), "--rank", str(rank), "--world-size", str(n), "--master", "127.0.0.1",
                "--port", str(port)] + list(extra)
-        if cpu and rank == 0:
-            cmd.append("--server")            # reference topology: rank 0 is the parameter server (main.py:151,153)
+        if cpu and rank < servers:
+            cmd.append("--server")            # reference topology: rank 0 is the parameter server (main.py:151,153); --servers K: ranks 0..K-1
+        if servers > 1:
+            cmd += ["--num-servers", str(servers)]
         procs.append(subprocess.Popen(cmd, env=env))
     rc = 0
     for p in procs:
@@ -48,9 +50,10 @@ if __name__ == "__main__":
     ap.add_argument("--local", type=int, default=0, help="launch N local processes instead of submitting to AzureML")
     ap.add_argument("--cpu", action="store_true", help="CPU/gloo topology: rank 0 serves, ranks 1.. train")
     ap.add_argument("--port", type=int, default=29500)
+    ap.add_argument("--servers", type=int, default=1, help="with --cpu: shard the parameter server over ranks 0..K-1")
     ap.add_argument("extra", nargs=argparse.REMAINDER)
     a = ap.parse_args()
     extra = [e for e in a.extra if e != "--"]
     if a.local:
-        sys.exit(launch_local(a.local, a.cpu, extra, a.port))
+        sys.exit(launch_local(a.local, a.cpu, extra, a.port, a.servers))
     submit_azureml(extra)

@@ -81,3 +81,18 @@ def test_checkpoint_then_resume_continues_from_the_next_epoch(tmp_path):
     last = torch.load(tmp_path / "ck.pt", weights_only=False)
     assert last["meta"]["epoch"] == 2
     assert not torch.equal(first["model"]["conv1.weight"], last["model"]["conv1.weight"])
+
+
+def test_two_sharded_servers_and_two_workers_via_launcher(tmp_path):
+    """NORTH-STAR sharded server on CPU: run-pytorch.py --local 4 --cpu --servers 2 (ranks 0-1 serve one slice each, 2-3 train)."""
+    from distributed_ml_pytorch_b200.parallel.launcher import free_port
+    r = _run([sys.executable, os.path.join(ROOT, "run-pytorch.py"), "--local", "4", "--cpu", "--servers", "2", "--port", str(free_port()), "--",
+              "--model", "lenet", "--epochs", "1", "--steps-per-epoch", "10", "--log-interval", "1000", "--test-batch-size", "50", "--synthetic",
+              "--num-push", "2", "--num-pull", "2", "--ckpt", str(tmp_path / "ck.pt")], cwd=tmp_path)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    assert os.path.exists(tmp_path / "log" / "node2.csv") and os.path.exists(tmp_path / "log" / "node3.csv")
+    assert r.stdout.count("server done") == 2
+    from distributed_ml_pytorch_b200.models import build_model
+    from distributed_ml_pytorch_b200.parallel import ParameterServer
+    sd = ParameterServer.merge_shards([str(tmp_path / "ck.pt") + f".shard{i}" for i in range(2)], build_model("lenet"))
+    assert "conv1.weight" in sd and "fc3.bias" in sd

@@ -139,3 +139,50 @@ def test_synchronous_mode_equals_large_batch_sgd(tmp_path):
         F.cross_entropy(ref(torch.cat([x0, x1])), torch.cat([y0, y1])).backward()
         sgd.step()
     torch.testing.assert_close(a, ravel_model_params(ref), rtol=1e-4, atol=1e-5)
+
+
+def _sharded_servers(rank, size, out_dir, steps, n_servers):
+    """NORTH-STAR sharded parameter server on the gloo transport: ranks 0..n_servers-1 each own one slice of the flat vector."""
+    torch.manual_seed(0)
+    net = build_model("lenet", in_channels=1, input_hw=28).eval()
+    if rank < n_servers:
+        server = ParameterServer(model=net, shard_index=rank, n_shards=n_servers)
+        server.run()
+        server.save(os.path.join(out_dir, "server.pt"))                     # -> server.pt.shard<rank>
+        torch.save({"bounds": server.bounds, "counters": server.counters}, os.path.join(out_dir, f"srv{rank}.pt"))
+        return
+    opt = Asynchronous(net.parameters(), lr=0.05, n_push=1, n_pull=1, model=net, server_ranks=list(range(n_servers)), blocking_pull=True)
+    for i in range(steps):
+        x, y = _batch(i)
+        opt.zero_grad()
+        F.cross_entropy(net(x), y).backward()
+        opt.step()
+    opt.finish()
+    torch.save(ravel_model_params(net).clone(), os.path.join(out_dir, "worker.pt"))
+
+
+def test_two_server_shards_one_worker_equals_sgd(tmp_path):
+    steps, n_servers = 5, 2
+    spawn(_sharded_servers, n_servers + 1, args=(str(tmp_path), steps, n_servers))
+    torch.manual_seed(0)
+    ref = build_model("lenet", in_channels=1, input_hw=28).eval()
+    sgd = torch.optim.SGD(ref.parameters(), lr=0.05)
+    for i in range(steps):
+        x, y = _batch(i)
+        sgd.zero_grad()
+        F.cross_entropy(ref(x), y).backward()
+        sgd.step()
+    expect = ravel_model_params(ref)
+    torch.testing.assert_close(torch.load(tmp_path / "worker.pt"), expect, rtol=1e-4, atol=1e-5)
+    covered = 0
+    for r in range(n_servers):
+        info = torch.load(tmp_path / f"srv{r}.pt", weights_only=False)
+        part = torch.load(tmp_path / f"server.pt.shard{r}", weights_only=False)
+        b, e = info["bounds"]
+        covered += e - b
+        torch.testing.assert_close(part["parameter_shard"], expect[b:e], rtol=1e-4, atol=1e-5)
+        assert info["counters"]["GradientUpdate"] == steps and info["counters"]["ParameterRequest"] == steps
+    assert covered == expect.numel()
+    merged = ParameterServer.merge_shards([tmp_path / f"server.pt.shard{r}" for r in range(n_servers)],
+                                          build_model("lenet", in_channels=1, input_hw=28))
+    torch.testing.assert_close(merged["fc3.bias"], dict(ref.named_parameters())["fc3.bias"].detach(), rtol=1e-4, atol=1e-5)
