@@ -288,6 +288,8 @@ if __name__ == "__main__":
             kw["device_id"] = dev
         from datetime import timedelta
         dist.init_process_group(backend, rank=args.rank, world_size=args.world_size, timeout=timedelta(seconds=args.timeout_s), **kw)
+        if args.server and args.mode == "sync":
+            raise SystemExit("--mode sync has no server rank (every rank trains and the update is an all-reduce): drop --server")
         if args.server:
             init_server(args)
             dist.destroy_process_group()

@@ -29,6 +29,10 @@ def submit_azureml(extra):
 
 
 def launch_local(n, cpu, extra, port, servers=1):
+    extra = list(extra)
+    sync = any(a == "--mode" and b == "sync" for a, b in zip(extra, extra[1:])) or "--mode=sync" in extra
+    if sync:
+        servers = 0                            # synchronous data parallelism: every rank trains, nobody serves
     procs = []
     for rank in range(n):
         env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(n), LOCAL_RANK=str(rank))

@@ -96,3 +96,14 @@ def test_two_sharded_servers_and_two_workers_via_launcher(tmp_path):
     from distributed_ml_pytorch_b200.parallel import ParameterServer
     sd = ParameterServer.merge_shards([str(tmp_path / "ck.pt") + f".shard{i}" for i in range(2)], build_model("lenet"))
     assert "conv1.weight" in sd and "fc3.bias" in sd
+
+
+def test_sync_mode_two_cpu_ranks_via_launcher(tmp_path):
+    """--mode sync on CPU/gloo (NORTH-STAR synchronous data parallelism): no server rank, both ranks train, gradients are all-reduced."""
+    from distributed_ml_pytorch_b200.parallel.launcher import free_port
+    r = _run([sys.executable, os.path.join(ROOT, "run-pytorch.py"), "--local", "2", "--cpu", "--port", str(free_port()), "--", "--mode", "sync",
+              "--model", "lenet", "--epochs", "1", "--steps-per-epoch", "8", "--log-interval", "1000", "--test-batch-size", "50", "--synthetic"],
+             cwd=tmp_path)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    assert os.path.exists(tmp_path / "log" / "node0.csv") and os.path.exists(tmp_path / "log" / "node1.csv")
+    assert r.stdout.count("Finished Training") == 2
