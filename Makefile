@@ -33,6 +33,19 @@ gpu:
 gpu8:
 	$(PY) -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29500 example/main.py --cuda
 
+gpu8-sync:
+	$(PY) -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29500 example/main.py --cuda --mode sync
+
+# one machine, CPU / gloo: the reference's 1 server + 2 workers, a server sharded over 2 ranks + 2 workers, synchronous data parallelism
+local3:
+	$(PY) run-pytorch.py --local 3 --cpu
+
+local-sharded:
+	$(PY) run-pytorch.py --local 4 --cpu --servers 2
+
+local-sync:
+	$(PY) run-pytorch.py --local 2 --cpu -- --mode sync
+
 p2p:
 	$(PY) pytorch_p2p_ex.py
 
@@ -57,4 +70,4 @@ upload-test: dist
 install-test:
 	$(PY) -m pip install --index-url https://test.pypi.org/simple/ pytorch-distbelief
 
-.PHONY: setup install build graph first second server single gpu gpu8 p2p test test-gpu bench dist upload upload-test install-test
+.PHONY: setup install build graph first second server single gpu gpu8 gpu8-sync local3 local-sharded local-sync p2p test test-gpu bench dist upload upload-test install-test
