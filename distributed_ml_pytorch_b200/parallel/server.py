@@ -31,13 +31,18 @@ from .async_optim import staleness_scale
 _LOGGER = logging.getLogger(__name__)
 
 
+class WorkerLost(RuntimeError):
+    """The server's idle timeout expired before every worker reported ``WorkerDone``."""
+
+
 class ParameterServer:
     def __init__(self, model: torch.nn.Module, n_workers: Optional[int] = None, momentum: float = 0.0, staleness: Optional[str] = None,
-                 staleness_param: float = 0.9, group=None, shard_index: int = 0, n_shards: int = 1):
+                 staleness_param: float = 0.9, group=None, shard_index: int = 0, n_shards: int = 1, idle_timeout_s: Optional[float] = None):
         """``n_shards > 1``: the flat parameter vector is cut into ``n_shards`` contiguous pieces (``ShardMap``, the same cut the
         workers use) and this server owns piece ``shard_index``; every message payload is then that slice (NORTH-STAR sharded
         server, SURVEY.md §2.4 — the reference has exactly one server rank)."""
         self.model = model
+        self.idle_timeout_s = idle_timeout_s       # run() raises WorkerLost when no message arrives for this long (None: wait forever)
         full = ravel_model_params(model).detach().clone().float().cpu()
         self.shards = ShardMap(full.numel(), n_shards, align=1)
         self.shard_index, self.n_shards = int(shard_index), int(n_shards)
@@ -86,8 +91,16 @@ class ParameterServer:
     def run(self) -> None:
         """Blocking serve loop (reference main.py:138); returns once every worker has sent ``WorkerDone``."""
         self.running = True
+        seen = 0
         while self.running:
-            sender, code, payload = recv_message(src=None, group=self.group)
+            try:
+                # the idle clock starts with the first message: workers may need long to start (imports, data, CUDA context)
+                sender, code, payload = recv_message(src=None, group=self.group, timeout_s=self.idle_timeout_s if seen else None)
+                seen += 1
+            except TimeoutError:
+                self.running = False
+                raise WorkerLost(f"parameter server: no message for {self.idle_timeout_s} s; {len(self.done_workers)} of {self.n_workers} "
+                                 f"workers had finished (done: {sorted(self.done_workers)})") from None
             self.receive(sender, code, payload)
             if self.n_workers is not None and len(self.done_workers) >= self.n_workers:
                 self.running = False

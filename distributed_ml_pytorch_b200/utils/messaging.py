@@ -21,6 +21,8 @@ from __future__ import annotations
 import enum
 import logging
 import threading
+import time
+from datetime import timedelta
 from typing import Optional
 
 import torch
@@ -44,12 +46,16 @@ class MessageCode(enum.Enum):
     EvaluateParams = 4      # kept for wire compatibility with the upstream lineage (unused)
 
 
+_MAX_INFLIGHT = 16     # outstanding isend work items (header + payload per message) before the sender waits for the oldest
+
+
 def _reap_pending() -> None:
-    alive = []
-    for work, keep in _pending:
-        if not work.is_completed():
-            alive.append((work, keep))
-    _pending[:] = alive
+    """Bound the send queue.  gloo only marks a send ``is_completed()`` once somebody has waited on it, so polling the flag never
+    frees anything; waiting on the oldest entries (delivered long ago, the peer receives in order) returns at once and releases
+    their payload snapshots, and acts as back-pressure if the peer has really fallen behind."""
+    while len(_pending) >= _MAX_INFLIGHT:
+        work, _ = _pending.pop(0)
+        work.wait()
 
 
 def send_message(message_code: MessageCode, payload: Optional[torch.Tensor] = None, dst: int = SERVER_RANK,
@@ -86,10 +92,23 @@ def flush_sends() -> None:
         _pending.clear()
 
 
-def recv_message(src: Optional[int] = None, group=None):
-    """Blocking receive of one message. Returns ``(sender, MessageCode, payload)``."""
+def recv_message(src: Optional[int] = None, group=None, timeout_s: Optional[float] = None):
+    """Blocking receive of one message. Returns ``(sender, MessageCode, payload)``.
+
+    ``timeout_s``: give up with ``TimeoutError`` when no message header arrives in that time (failure detection: the
+    reference's server blocks forever when its workers die)."""
     header = torch.zeros(3, dtype=torch.int64)
-    dist.recv(header, src=src, group=group, tag=_HEADER_TAG)
+    if timeout_s is None:
+        dist.recv(header, src=src, group=group, tag=_HEADER_TAG)
+    else:
+        # gloo closes the pair when a timed wait expires, so after the TimeoutError the group is only good for shutting down
+        work = dist.irecv(header, src=src, group=group, tag=_HEADER_TAG)
+        try:
+            work.wait(timedelta(seconds=float(timeout_s)))
+        except RuntimeError as exc:
+            if "Timed out" in str(exc) or "timeout" in str(exc).lower():
+                raise TimeoutError(f"no message within {timeout_s} s") from None
+            raise
     sender, code, n = int(header[0]), int(header[1]), int(header[2])
     payload = torch.zeros(n, dtype=torch.float32)
     if n:

@@ -221,7 +221,7 @@ def init_server(args):
         ParameterServer.run_peer(model.to(device), momentum=args.momentum, staleness=args.staleness)
         return
     server = ParameterServer(model=model, momentum=args.momentum, staleness=args.staleness, shard_index=args.rank if args.num_servers > 1 else 0,
-                             n_shards=args.num_servers)
+                             n_shards=args.num_servers, idle_timeout_s=args.server_idle_timeout_s)
     server.run()
     if args.ckpt:
         server.save(args.ckpt)
@@ -250,6 +250,8 @@ def build_parser():
     parser.add_argument("--momentum", type=float, default=0.0)
     parser.add_argument("--staleness", default=None, choices=[None, "none", "inverse", "exp"])
     parser.add_argument("--backend", default=None, help="torch.distributed backend (default: nccl with --cuda, gloo otherwise)")
+    parser.add_argument("--server-idle-timeout-s", type=float, default=None, help="CPU/gloo server: exit with an error when no worker "
+                        "message arrives for this long (default: wait forever, like the reference)")
     parser.add_argument("--num-servers", type=int, default=1, help="CPU/gloo: shard the parameter server over ranks 0..K-1 (each started "
                         "with --server); on GPUs the server is always sharded over all ranks")
     parser.add_argument("--host-data", action="store_true", help="keep the torchvision DataLoader on the host even with --cuda "

@@ -51,6 +51,8 @@ def _one_worker(rank, size, out_dir, steps):
         opt.zero_grad()
         F.cross_entropy(net(x), y).backward()
         opt.step()
+    from distributed_ml_pytorch_b200.utils import messaging
+    assert len(messaging._pending) <= messaging._MAX_INFLIGHT      # 20 work items were queued: the send queue stays bounded
     opt.finish()
     torch.save(ravel_model_params(net).clone(), os.path.join(out_dir, "worker.pt"))
 
@@ -186,3 +188,30 @@ def test_two_server_shards_one_worker_equals_sgd(tmp_path):
     merged = ParameterServer.merge_shards([tmp_path / f"server.pt.shard{r}" for r in range(n_servers)],
                                           build_model("lenet", in_channels=1, input_hw=28))
     torch.testing.assert_close(merged["fc3.bias"], dict(ref.named_parameters())["fc3.bias"].detach(), rtol=1e-4, atol=1e-5)
+
+
+def _dying_worker(rank, size, out_dir):
+    torch.manual_seed(0)
+    net = build_model("lenet", in_channels=1, input_hw=28)
+    if rank == 0:
+        server = ParameterServer(model=net, idle_timeout_s=3.0)
+        try:
+            server.run()
+        except Exception as exc:
+            torch.save({"type": type(exc).__name__, "msg": str(exc), "counters": server.counters}, os.path.join(out_dir, "server_exc.pt"))
+        return
+    opt = Asynchronous(net.parameters(), lr=0.05, n_push=1, n_pull=1, model=net)
+    x, y = _batch(0)
+    opt.zero_grad()
+    F.cross_entropy(net(x), y).backward()
+    opt.step()
+    from distributed_ml_pytorch_b200.utils import messaging
+    messaging.flush_sends()
+    # the worker "crashes" here: no WorkerDone is ever sent (the reference's server would block forever)
+
+
+def test_server_reports_lost_workers_instead_of_hanging(tmp_path):
+    spawn(_dying_worker, 2, args=(str(tmp_path),))
+    exc = torch.load(tmp_path / "server_exc.pt", weights_only=False)
+    assert exc["type"] == "WorkerLost" and "0 of 1 workers had finished" in exc["msg"]
+    assert exc["counters"]["GradientUpdate"] == 1
