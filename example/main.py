@@ -225,7 +225,7 @@ def init_server(args):
     server.run()
     if args.ckpt:
         server.save(args.ckpt)
-    print("server done:", server.counters)
+    print("server done:", server.counters, "| staleness histogram (updates applied at version lag tau):", dict(sorted(server.staleness_hist.items())))
 
 
 def build_parser():
