@@ -52,7 +52,7 @@ def _ours(rank, size, steps, channels, hw, out):
     dt = time.perf_counter() - t0
     opt.finish()
     with open(os.path.join(out, f"ours{rank}.json"), "w") as f:
-        json.dump({"s": dt, "loss": float(loss)}, f)
+        json.dump({"s": dt, "loss": float(loss.detach())}, f)
 
 
 def _ref(rank, size, steps, out):
@@ -102,9 +102,14 @@ def _ref(rank, size, steps, out):
     from asgd.utils import messaging as m
     for wk, _ in m._keep:
         wk.wait()
-    time.sleep(0.5)
+    # The reference keeps its listener in a local variable (Asynchronous.py:37-38).  It must have consumed the server's Shutdown
+    # (sent once EVERY worker is done) before this process tears the group down, or the thread dies inside dist.recv and aborts.
+    import threading
+    for th in threading.enumerate():
+        if th is not threading.current_thread() and type(th).__name__ == "Listener":
+            th.join(timeout=120)
     with open(os.path.join(out, f"ref{rank}.json"), "w") as f:
-        json.dump({"s": dt, "loss": float(loss)}, f)
+        json.dump({"s": dt, "loss": float(loss.detach())}, f)
 
 
 def main():
