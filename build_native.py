@@ -28,7 +28,9 @@ LIB = OUT_DIR / "libdmlb.so"
 NVCC = os.environ.get("NVCC") or shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
 ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "--use_fast_math", "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall",
-          "-Xcompiler", "-Wno-unused-function", "-I", str(ROOT / "include"), "-I", str(CSRC)]
+          "-Xcompiler", "-Wno-unused-function", "-I", str(ROOT / "include"), "-I", str(CSRC),
+          # every translation unit sees the public header first: a definition that drifts from include/dmlb.h is a build error
+          "--pre-include", str(ROOT / "include" / "dmlb.h")]
 
 
 def _sources():

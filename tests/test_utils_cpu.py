@@ -98,3 +98,44 @@ def test_reference_import_paths_resolve():
     assert issubclass(Listener, MessageListener)
     assert {c.name for c in MessageCode} >= {"ParameterRequest", "GradientUpdate", "ParameterUpdate"}
     assert callable(send_message) and callable(ravel_model_params) and callable(unravel_model_params) and ParameterServer is not None
+
+
+def test_c_abi_header_matches_the_built_library():
+    """include/dmlb.h declares exactly the dmlb_* functions libdmlb.so exports, and every entry point named in INTEGRATION.md exists."""
+    import os
+    import re
+    import shutil
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib = os.path.join(root, "distributed_ml_pytorch_b200", "_native", "libdmlb.so")
+    if not os.path.exists(lib) or shutil.which("nm") is None:
+        import pytest
+        pytest.skip("library not built here")
+    out = subprocess.run(["nm", "-D", "--defined-only", lib], capture_output=True, text=True, check=True).stdout
+    exported = {ln.split()[-1] for ln in out.splitlines() if " T dmlb_" in ln}
+    header = open(os.path.join(root, "include", "dmlb.h")).read()
+    declared = set(re.findall(r"\b(dmlb_[a-z0-9_]+)\s*\(", header))
+    assert exported == declared, (sorted(exported - declared), sorted(declared - exported))
+    doc = open(os.path.join(root, "INTEGRATION.md")).read()
+    named = set(re.findall(r"`(dmlb_[a-z0-9_]+)`", doc))             # plain names only; brace patterns like dmlb_relu_{fwd,bwd} are skipped
+    assert named <= exported, sorted(named - exported)
+
+
+def test_ctypes_signatures_have_the_arity_of_the_header():
+    """Every ctypes prototype in _native._SIGNATURES has as many arguments as the declaration in include/dmlb.h."""
+    import os
+    import re
+    from distributed_ml_pytorch_b200 import _native
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = re.sub(r"/\*.*?\*/", "", open(os.path.join(root, "include", "dmlb.h")).read(), flags=re.S)
+    arity = {}
+    for name, args in re.findall(r"\b(dmlb_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", header, flags=re.S):
+        args = args.strip()
+        arity[name] = 0 if args in ("", "void") else args.count(",") + 1
+    checked = 0
+    for name, proto in _native._SIGNATURES.items():
+        argtypes = proto[0] if (isinstance(proto, tuple) and len(proto) == 2 and isinstance(proto[0], (list, tuple))) else proto
+        assert name in arity, f"{name} is not declared in include/dmlb.h"
+        assert len(argtypes) == arity[name], (name, len(argtypes), arity[name])
+        checked += 1
+    assert checked >= 30
