@@ -121,21 +121,37 @@ def test_c_abi_header_matches_the_built_library():
     assert named <= exported, sorted(named - exported)
 
 
-def test_ctypes_signatures_have_the_arity_of_the_header():
-    """Every ctypes prototype in _native._SIGNATURES has as many arguments as the declaration in include/dmlb.h."""
+def test_ctypes_signatures_match_the_header():
+    """Every ctypes prototype in _native._SIGNATURES has the arity and the argument classes (pointer / int / long long / float) of the
+    declaration in include/dmlb.h — a c_int where the C side reads a long long would silently corrupt the call."""
+    import ctypes
     import os
     import re
     from distributed_ml_pytorch_b200 import _native
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     header = re.sub(r"/\*.*?\*/", "", open(os.path.join(root, "include", "dmlb.h")).read(), flags=re.S)
-    arity = {}
+
+    def c_class(text):
+        if "*" in text:
+            return "ptr"
+        for key, name in (("long long", "i64"), ("float", "float"), ("double", "double"), ("size_t", "size_t"), ("int", "int")):
+            if key in text:
+                return name
+        return text
+
+    def ctypes_class(c):
+        if c in (ctypes.c_void_p, ctypes.c_char_p):
+            return "ptr"
+        return {ctypes.c_int: "int", ctypes.c_uint: "int", ctypes.c_longlong: "i64", ctypes.c_ulonglong: "i64", ctypes.c_float: "float",
+                ctypes.c_double: "double", ctypes.c_size_t: "size_t"}.get(c, str(c))
+
+    declared = {}
     for name, args in re.findall(r"\b(dmlb_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", header, flags=re.S):
-        args = args.strip()
-        arity[name] = 0 if args in ("", "void") else args.count(",") + 1
+        params = [a for a in (x.strip() for x in args.split(",")) if a and a != "void"]
+        declared[name] = [c_class(p) for p in params]
     checked = 0
     for name, proto in _native._SIGNATURES.items():
-        argtypes = proto[0] if (isinstance(proto, tuple) and len(proto) == 2 and isinstance(proto[0], (list, tuple))) else proto
-        assert name in arity, f"{name} is not declared in include/dmlb.h"
-        assert len(argtypes) == arity[name], (name, len(argtypes), arity[name])
+        assert name in declared, f"{name} is not declared in include/dmlb.h"
+        assert [ctypes_class(c) for c in proto] == declared[name], name
         checked += 1
     assert checked >= 30
