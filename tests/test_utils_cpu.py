@@ -134,7 +134,7 @@ def test_ctypes_signatures_match_the_header():
     def c_class(text):
         if "*" in text:
             return "ptr"
-        for key, name in (("long long", "i64"), ("float", "float"), ("double", "double"), ("size_t", "size_t"), ("int", "int")):
+        for key, name in (("long long", "i64"), ("float", "float"), ("double", "double"), ("size_t", "i64"), ("int", "int")):
             if key in text:
                 return name
         return text
@@ -142,8 +142,9 @@ def test_ctypes_signatures_match_the_header():
     def ctypes_class(c):
         if c in (ctypes.c_void_p, ctypes.c_char_p):
             return "ptr"
-        return {ctypes.c_int: "int", ctypes.c_uint: "int", ctypes.c_longlong: "i64", ctypes.c_ulonglong: "i64", ctypes.c_float: "float",
-                ctypes.c_double: "double", ctypes.c_size_t: "size_t"}.get(c, str(c))
+        if c in (ctypes.c_float, ctypes.c_double):
+            return "float" if c is ctypes.c_float else "double"
+        return {4: "int", 8: "i64"}.get(ctypes.sizeof(c), str(c))      # integer classes by width (c_size_t aliases c_ulong here)
 
     declared = {}
     for name, args in re.findall(r"\b(dmlb_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", header, flags=re.S):
