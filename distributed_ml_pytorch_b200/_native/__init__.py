@@ -37,6 +37,8 @@ _SIGNATURES = {
     "dmlb_conv_implicit_fin": [c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_vp,
                                c_int, c_vp, c_int, c_vp, c_int, c_vp, c_int, c_int, c_int, c_vp, c_int, c_int, c_int, c_vp],
     "dmlb_fin_pool_supported": [c_int, c_int],
+    # (images, labels, index, out_x, out_y, B, H, W, C, mean3, std3, stream)
+    "dmlb_gather_normalize_u8": [c_vp] * 5 + [c_int] * 4 + [c_vp] * 3,
     "dmlb_splitk_finish": [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_ll, c_int, c_int, c_int, c_int, c_int, c_vp, c_int, c_vp],
     "dmlb_gemm_bias_act_splitk": [c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_vp, c_vp, c_int, c_vp, c_int, c_int, c_vp],
     "dmlb_im2col_nhwc_bf16": [c_vp, c_vp] + [c_int] * 12 + [c_vp],

@@ -54,7 +54,6 @@ class GpuResidentLoader:
             out_y = torch.empty((B,), dtype=torch.int64, device=self.device)
         if self.device.type == "cuda":
             from .. import _native
-            _native.register("dmlb_gather_normalize_u8", [_native.c_vp] * 5 + [_native.c_int] * 4 + [_native.c_vp] * 3)
             _native.call("dmlb_gather_normalize_u8", self.images.data_ptr(), self.labels.data_ptr(), index.data_ptr(), out_x.data_ptr(),
                          out_y.data_ptr(), B, H, W, C, self._mean_c, self._std_c, torch.cuda.current_stream(self.device).cuda_stream)
         else:

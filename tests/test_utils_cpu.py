@@ -128,6 +128,7 @@ def test_ctypes_signatures_match_the_header():
     import os
     import re
     from distributed_ml_pytorch_b200 import _native
+    from distributed_ml_pytorch_b200.parallel import peer  # noqa: F401  (registers the peer-memory / collective entry points)
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     header = re.sub(r"/\*.*?\*/", "", open(os.path.join(root, "include", "dmlb.h")).read(), flags=re.S)
 
@@ -140,7 +141,7 @@ def test_ctypes_signatures_match_the_header():
         return text
 
     def ctypes_class(c):
-        if c in (ctypes.c_void_p, ctypes.c_char_p):
+        if c in (ctypes.c_void_p, ctypes.c_char_p) or (isinstance(c, type) and issubclass(c, ctypes._Pointer)):
             return "ptr"
         if c in (ctypes.c_float, ctypes.c_double):
             return "float" if c is ctypes.c_float else "double"
@@ -155,4 +156,4 @@ def test_ctypes_signatures_match_the_header():
         assert name in declared, f"{name} is not declared in include/dmlb.h"
         assert [ctypes_class(c) for c in proto] == declared[name], name
         checked += 1
-    assert checked >= 30
+    assert checked >= 45 and "dmlb_sync_nvls_range" in _native._SIGNATURES
