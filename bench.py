@@ -367,6 +367,12 @@ def _relaunch_under_torchrun(args) -> None:
 
 def main():
     args = parse()
+    import torch
+    if not torch.cuda.is_available():
+        # nothing is measured without a B200: say so in the output contract instead of dying inside CUDA initialisation
+        print(json.dumps({"impl": args.impl, "unavailable": "no CUDA device visible; bench.py measures on B200 GPUs (CPU numbers: tools/bench_b1_cpu.py)"}),
+              flush=True)
+        sys.exit(0 if args.impl == "reference" else 1)
     if args.gpus > 1 and "RANK" not in os.environ and "WORLD_SIZE" not in os.environ:
         _relaunch_under_torchrun(args)
     if args.impl == "reference":

@@ -107,3 +107,16 @@ def test_sync_mode_two_cpu_ranks_via_launcher(tmp_path):
     assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
     assert os.path.exists(tmp_path / "log" / "node0.csv") and os.path.exists(tmp_path / "log" / "node1.csv")
     assert r.stdout.count("Finished Training") == 2
+
+
+def test_bench_reports_unavailable_without_a_gpu():
+    """bench.py keeps its one-JSON-line contract on a machine without CUDA (the reference arm exits 0, as the driver expects)."""
+    import json
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("this check is for CPU-only machines")
+    for impl, rc in (("ours", 1), ("reference", 0)):
+        r = _run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", impl], cwd=ROOT, timeout=120)
+        assert r.returncode == rc, r.stderr[-800:]
+        line = json.loads(r.stdout.strip().splitlines()[-1])
+        assert line["impl"] == impl and "unavailable" in line
