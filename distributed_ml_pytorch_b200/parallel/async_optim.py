@@ -33,6 +33,7 @@ import torch
 import torch.distributed as dist
 
 from ..utils import messaging as msg
+from ..utils import trace
 from ..utils.messaging import MessageCode, MessageListener, send_message
 from ..utils.serialization import ravel_model_params, unravel_model_params
 from .arena import FlatArena
@@ -51,6 +52,7 @@ class Listener(MessageListener):
 
     def receive(self, sender, message_code, parameter):
         _LOGGER.info("Processing message: %s", message_code.name)
+        trace.instant("reply " + message_code.name, "comm", sender=sender)
         if message_code == MessageCode.ParameterUpdate:
             o = self.owner
             shard = o.server_ranks.index(sender) if sender in o.server_ranks else 0
@@ -234,22 +236,24 @@ class Asynchronous(ArenaOptimizer):
                 self._pull()
         elif self.transport == "gloo":
             if push_now:
-                for k, r in enumerate(self.server_ranks):
-                    b, e = self._srv_shards.valid_bounds(k)
-                    send_message(MessageCode.GradientUpdate, self.accumulated_gradients[b:e], dst=r)
-                self.accumulated_gradients.zero_()
+                with trace.span("push", "comm", step=self.idx, floats=self.arena.numel):
+                    for k, r in enumerate(self.server_ranks):
+                        b, e = self._srv_shards.valid_bounds(k)
+                        send_message(MessageCode.GradientUpdate, self.accumulated_gradients[b:e], dst=r)
+                    self.accumulated_gradients.zero_()
                 self.pushes += 1
             if pull_now:
-                with self._lock:
-                    self._replies = 0
-                self._reply_event.clear()
-                for r in self.server_ranks:
-                    send_message(MessageCode.ParameterRequest, None, dst=r)
-                self.pulls += 1
-                if self.blocking_pull:
-                    if not self._reply_event.wait(self.pull_timeout_s):
-                        raise TimeoutError(f"no ParameterUpdate from the server within {self.pull_timeout_s} s")
-                    self._apply_pending()
+                with trace.span("pull request", "comm", step=self.idx, blocking=self.blocking_pull):
+                    with self._lock:
+                        self._replies = 0
+                    self._reply_event.clear()
+                    for r in self.server_ranks:
+                        send_message(MessageCode.ParameterRequest, None, dst=r)
+                    self.pulls += 1
+                    if self.blocking_pull:
+                        if not self._reply_event.wait(self.pull_timeout_s):
+                            raise TimeoutError(f"no ParameterUpdate from the server within {self.pull_timeout_s} s")
+                        self._apply_pending()
         else:
             if push_now:
                 self._local_server_apply(self.accumulated_gradients)

@@ -23,6 +23,7 @@ import torch
 import torch.distributed as dist
 
 from ..utils import messaging as msg
+from ..utils import trace
 from ..utils.messaging import MessageCode, recv_message, send_message
 from ..utils.serialization import ravel_model_params, unravel_model_params
 from .arena import ShardMap
@@ -97,11 +98,14 @@ class ParameterServer:
                 # the idle clock starts with the first message: workers may need long to start (imports, data, CUDA context)
                 sender, code, payload = recv_message(src=None, group=self.group, timeout_s=self.idle_timeout_s if seen else None)
                 seen += 1
-            except TimeoutError:
+            except (TimeoutError, RuntimeError) as exc:
+                # idle timeout, or the transport reported that a worker's connection went away
                 self.running = False
-                raise WorkerLost(f"parameter server: no message for {self.idle_timeout_s} s; {len(self.done_workers)} of {self.n_workers} "
+                why = f"no message for {self.idle_timeout_s} s" if isinstance(exc, TimeoutError) else f"transport error: {str(exc)[:120]}"
+                raise WorkerLost(f"parameter server: {why}; {len(self.done_workers)} of {self.n_workers} "
                                  f"workers had finished (done: {sorted(self.done_workers)})") from None
-            self.receive(sender, code, payload)
+            with trace.span(code.name, "server", sender=sender, floats=int(payload.numel())):
+                self.receive(sender, code, payload)
             if self.n_workers is not None and len(self.done_workers) >= self.n_workers:
                 self.running = False
         msg.flush_sends()

@@ -35,6 +35,7 @@ from asgd.server import ParameterServer
 from distributed_ml_pytorch_b200.models import MODEL_NAMES, build_model
 from distributed_ml_pytorch_b200.ops import cross_entropy
 from distributed_ml_pytorch_b200.utils.checkpoint import load_checkpoint, save_checkpoint
+from distributed_ml_pytorch_b200.utils import trace
 from distributed_ml_pytorch_b200.utils.csvlog import CSVLogger, log_path
 
 CLASSES = ("plane", "car", "bird", "cat", "deer", "dog", "frog", "horse", "ship", "truck")
@@ -130,21 +131,27 @@ def main(args):
         seen = 0
         for i, (inputs, labels) in enumerate(trainloader, 0):
             if step_fn is not None:
-                res = step_fn(inputs, labels)                # H2D copy + graph replay; result of the previous step
+                with trace.span("step (enqueue)", "train", epoch=epoch, iteration=i):
+                    res = step_fn(inputs, labels)            # H2D copy + graph replay; result of the previous step
                 loss_value = res.loss if res is not None else float("nan")
             else:
-                inputs, labels = inputs.to(device, non_blocking=True), labels.to(device, non_blocking=True)
-                optimizer.zero_grad()
-                outputs = net(inputs)
-                loss = cross_entropy(outputs, labels)
-                loss.backward()
-                optimizer.step()
-                loss_value = loss.item()
+                with trace.span("step", "train", epoch=epoch, iteration=i):
+                    inputs, labels = inputs.to(device, non_blocking=True), labels.to(device, non_blocking=True)
+                    optimizer.zero_grad()
+                    with trace.span("forward+loss", "train"):
+                        outputs = net(inputs)
+                        loss = cross_entropy(outputs, labels)
+                    with trace.span("backward", "train"):
+                        loss.backward()
+                    with trace.span("optimizer.step", "train"):
+                        optimizer.step()
+                    loss_value = loss.item()
             seen += inputs.shape[0]
             test_loss = test_acc = None
             if i % args.log_interval == 0 and i > 0:
                 _sync_step(step_fn, device, before=True)     # the graph step runs on its own stream: let it finish before evaluating
-                test_loss, test_acc = evaluate(net, testloader, args, device=device)
+                with trace.span("evaluate", "eval", iteration=i):
+                    test_loss, test_acc = evaluate(net, testloader, args, device=device)
                 _sync_step(step_fn, device, before=False)
                 print("Timestamp: {} | Iteration: {:6} | Loss: {:6.4f} | Test Loss: {:6.4f} | Test Accuracy: {:6.4f}".format(
                     datetime.now(), i, loss_value, test_loss, test_acc))
@@ -163,10 +170,20 @@ def main(args):
     print("wrote", logger.to_csv())
     if hasattr(optimizer, "finish"):
         optimizer.finish()
+    if args.trace:
+        print("wrote", trace.save(_trace_path(args.trace, rank)))
     if hasattr(optimizer, "pushes"):
         stats = optimizer.staleness_stats() if hasattr(optimizer, "staleness_stats") else {}
         print("pushes: {} | pulls: {}{}".format(optimizer.pushes, optimizer.pulls, " | staleness: {}".format(stats) if stats else ""))
     print("Finished Training")
+
+
+def _trace_path(path, rank):
+    """One trace file per process: out.json -> out.rank3.json in a distributed run."""
+    if rank is None:
+        return path
+    root, ext = os.path.splitext(path)
+    return f"{root}.rank{rank}{ext or '.json'}"
 
 
 def _sync_step(step_fn, device, before: bool) -> None:
@@ -223,6 +240,8 @@ def init_server(args):
     server = ParameterServer(model=model, momentum=args.momentum, staleness=args.staleness, shard_index=args.rank if args.num_servers > 1 else 0,
                              n_shards=args.num_servers, idle_timeout_s=args.server_idle_timeout_s)
     server.run()
+    if args.trace:
+        print("wrote", trace.save(_trace_path(args.trace, args.rank)))
     if args.ckpt:
         server.save(args.ckpt)
     print("server done:", server.counters, "| staleness histogram (updates applied at version lag tau):", dict(sorted(server.staleness_hist.items())))
@@ -250,6 +269,8 @@ def build_parser():
     parser.add_argument("--momentum", type=float, default=0.0)
     parser.add_argument("--staleness", default=None, choices=[None, "none", "inverse", "exp"])
     parser.add_argument("--backend", default=None, help="torch.distributed backend (default: nccl with --cuda, gloo otherwise)")
+    parser.add_argument("--trace", default=None, help="write a Chrome / Perfetto trace of this process (steps, push / pull, server "
+                        "messages) to this path; distributed runs add .rank<N>")
     parser.add_argument("--server-idle-timeout-s", type=float, default=None, help="CPU/gloo server: exit with an error when no worker "
                         "message arrives for this long (default: wait forever, like the reference)")
     parser.add_argument("--num-servers", type=int, default=1, help="CPU/gloo: shard the parameter server over ranks 0..K-1 (each started "
@@ -274,6 +295,8 @@ def build_parser():
 if __name__ == "__main__":
     args = build_parser().parse_args()
     print(args)
+    if args.trace:
+        trace.start(process_name=("server" if args.server else "worker") + ("" if args.rank is None else f" rank {args.rank}"))
     if not args.no_distributed:
         # Initialise the distributed environment; server and clients call this as an entry point (reference main.py:159-167).
         if args.rank is None:

@@ -120,3 +120,20 @@ def test_bench_reports_unavailable_without_a_gpu():
         assert r.returncode == rc, r.stderr[-800:]
         line = json.loads(r.stdout.strip().splitlines()[-1])
         assert line["impl"] == impl and "unavailable" in line
+
+
+def test_trace_flag_writes_chrome_traces_for_server_and_workers(tmp_path):
+    """--trace: one Chrome / Perfetto trace per process with steps, push / pull and the server's message handling."""
+    import json
+    from distributed_ml_pytorch_b200.parallel.launcher import free_port
+    r = _run([sys.executable, os.path.join(ROOT, "run-pytorch.py"), "--local", "2", "--cpu", "--port", str(free_port()), "--", "--model", "lenet",
+              "--epochs", "1", "--steps-per-epoch", "6", "--log-interval", "1000", "--test-batch-size", "50", "--synthetic", "--num-push", "2",
+              "--num-pull", "3", "--trace", str(tmp_path / "t.json")], cwd=tmp_path)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    worker = json.load(open(tmp_path / "t.rank1.json"))["traceEvents"]
+    server = json.load(open(tmp_path / "t.rank0.json"))["traceEvents"]
+    names = [e["name"] for e in worker]
+    assert names.count("step") == 6 and names.count("push") == 3 and names.count("pull request") == 2
+    assert {"forward+loss", "backward", "optimizer.step"} <= set(names)
+    assert all(e["dur"] >= 0 for e in worker if e["ph"] == "X")
+    assert sum(e["name"] == "GradientUpdate" for e in server) == 3 and any(e["name"] == "ParameterRequest" for e in server)

@@ -207,11 +207,15 @@ def _dying_worker(rank, size, out_dir):
     opt.step()
     from distributed_ml_pytorch_b200.utils import messaging
     messaging.flush_sends()
-    # the worker "crashes" here: no WorkerDone is ever sent (the reference's server would block forever)
+    import time
+    time.sleep(1.0)
+    # the worker "crashes" here: no WorkerDone is ever sent (the reference's server would block forever) and the
+    # process ends without tearing the process group down
+    os._exit(0)
 
 
 def test_server_reports_lost_workers_instead_of_hanging(tmp_path):
     spawn(_dying_worker, 2, args=(str(tmp_path),))
     exc = torch.load(tmp_path / "server_exc.pt", weights_only=False)
-    assert exc["type"] == "WorkerLost" and "0 of 1 workers had finished" in exc["msg"]
+    assert exc["type"] == "WorkerLost" and "0 of 1 workers had finished" in exc["msg"]       # idle timeout or closed connection
     assert exc["counters"]["GradientUpdate"] == 1
