@@ -125,6 +125,7 @@ def main(args):
         from distributed_ml_pytorch_b200.engine import TrainStep
         step_fn = TrainStep(net, optimizer, args.batch_size, (args.in_channels, args.input_hw, args.input_hw), device=device)
 
+    t_train = time.time()
     for epoch in range(start_epoch, args.epochs):
         print("Training for epoch {}".format(epoch))
         t_epoch = time.time()
@@ -174,7 +175,11 @@ def main(args):
         print("wrote", trace.save(_trace_path(args.trace, rank)))
     if hasattr(optimizer, "pushes"):
         stats = optimizer.staleness_stats() if hasattr(optimizer, "staleness_stats") else {}
-        print("pushes: {} | pulls: {}{}".format(optimizer.pushes, optimizer.pulls, " | staleness: {}".format(stats) if stats else ""))
+        n_bytes = 4 * sum(p.numel() for p in net.parameters())
+        wall = max(1e-9, time.time() - t_train)
+        print("pushes: {} | pulls: {} | {:.1f} MB pushed, {:.1f} MB pulled ({:.1f} MB/s of parameter traffic over {:.1f} s){}".format(
+            optimizer.pushes, optimizer.pulls, optimizer.pushes * n_bytes / 1e6, optimizer.pulls * n_bytes / 1e6,
+            (optimizer.pushes + optimizer.pulls) * n_bytes / 1e6 / wall, wall, " | staleness: {}".format(stats) if stats else ""))
     print("Finished Training")
 
 
