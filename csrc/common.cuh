@@ -155,6 +155,15 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
         "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// D[tmem] (+)= A * B with fp32 words read as tf32 (K = 8 per instruction), fp32 accumulate.
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 // Arrive on an mbarrier once every previously issued tcgen05.mma of this thread has retired.
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
@@ -232,6 +241,25 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t 
     d |= static_cast<uint64_t>(1) << 46;  // descriptor version (Blackwell)
     d |= static_cast<uint64_t>(2) << 61;  // SWIZZLE_128B
     return d;
+}
+// Same with an explicit layout type: 2 = SWIZZLE_128B (16-byte granules), 1 = SWIZZLE_128B with 32-byte granules — the one layout an
+// MN-major 32-bit (tf32) operand may have: rows of 128 B of MN, 4-row swizzle atoms (512 B, SBO), LBO to the next 128 B of MN.
+__device__ __forceinline__ uint64_t umma_smem_desc_l(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+    d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFFu) << 16;
+    d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFFu) << 32;
+    d |= static_cast<uint64_t>(1) << 46;
+    d |= static_cast<uint64_t>(layout & 7u) << 61;
+    return d;
+}
+// Instruction descriptor, kind::tf32: tf32 x tf32 -> fp32 (operands are fp32 words in shared memory; the low 13 mantissa bits are ignored).
+__host__ __device__ constexpr uint32_t umma_idesc_tf32(int m, int n, bool a_mn_major, bool b_mn_major) {
+    return (1u << 4)                                   // D format: fp32
+           | (2u << 7)                                 // A format: tf32
+           | (2u << 10)                                // B format: tf32
+           | (static_cast<uint32_t>(a_mn_major) << 15) | (static_cast<uint32_t>(b_mn_major) << 16)
+           | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
 }
 // Instruction descriptor, kind::f16: bf16 x bf16 -> fp32.
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int m, int n, bool a_mn_major, bool b_mn_major) {

@@ -1,1257 +1,24 @@
-// tcgen05 / TMEM / TMA GEMM for sm_100a:  D[M,N] (+)= A[M,K] * B[N,K]^T   (bf16 in, fp32 accumulate)
-//
-// This single kernel family carries every GEMM-shaped op of the framework — Linear and the
-// implicit-GEMM view of Conv2d, forward, data-gradient and weight-gradient — i.e. the work the
-// reference delegates to cuDNN/cuBLAS through nn.Conv2d / nn.Linear
-// (reference example/models.py:8-13,28-43; SURVEY.md §2.5, work-list rows K6-K9).
-//
-// Operand storage ("major"):
-//   K-major  A: row-major [M, K] (lda)      MN-major A: row-major [K, M] (lda)   (i.e. A^T is stored)
-//   K-major  B: row-major [N, K] (ldb)      MN-major B: row-major [K, N] (ldb)
-// so that, with X the activation/column matrix, W the [Cout, K] weight and dY the output gradient:
-//   fprop  Y  = X  * W^T      : A = X  (K-major),   B = W  (K-major)
-//   dgrad  dX = dY * W        : A = dY (K-major),   B = W  (MN-major)     -- no transposed weight copy
-//   wgrad  dW = dY^T * X      : A = dY (MN-major),  B = X  (MN-major)     -- no transposes at all
-//
-// Structure (one CTA per 128 x BN output tile and K-split):
-//   warp 0   : TMA producer  (cp.async.bulk.tensor.2d, 128B swizzle, kStages-deep mbarrier ring)
-//   warp 1   : allocates TMEM, one lane issues tcgen05.mma (M=128, N=BN, K=16) and tcgen05.commit
-//   warps 2-5: epilogue — tcgen05.ld the fp32 accumulator (one TMEM lane = one output row per thread),
-//              fused bias / ReLU / bf16 cast, or vector red.add for split-K and gradient accumulation,
-//              optionally scattering columns (kh,kw,cin)->(cin,kh,kw) so conv weight gradients land
-//              directly in the PyTorch-layout fp32 gradient arena.
-#include "common.cuh"
+// bf16 entry points of the tcgen05 GEMM family (kind::f16): see gemm_tcgen05.cuh for the kernels and include/dmlb.h for the contracts.
+// Reference work taken over: nn.Conv2d / nn.Linear forward and backward, example/models.py:8-13,28-43 (cuDNN / cuBLAS there).
+#include "gemm_tcgen05.cuh"
 
-namespace dmlb {
-
-constexpr int kBM = 128;
-constexpr int kBK = 64;             // 64 bf16 = one 128-byte swizzle row
-constexpr int kUmmaK = 16;
-constexpr int kGemmThreads = 192;   // 6 warps
-
-struct GemmEpilogue {
-    void* out;            // bf16 or fp32
-    const float* bias;    // [N] or nullptr
-    int ldo;              // elements
-    int out_is_f32;
-    int relu;
-    int atomic;           // red.add into fp32 out
-    int perm_cin;         // >0: out column c -> (c % perm_cin) * perm_khw + c / perm_cin
-    int perm_khw;
-    // Split-K with the finishing pass folded in ("last CTA of a tile finishes"): every z-slice red.adds its partial tile into the
-    // fp32 workspace `out`, then bumps the tile's arrival counter; the slice that arrives last reads the summed tile back from L2,
-    // applies bias / ReLU, rounds to bf16 into fin_y (optionally also the 2x2/2 max-pool into fin_pooled), and writes zeros back,
-    // so workspace and counters are clean for the next layer and no separate finishing launch is needed.
-    int* fin_counters;    // nullptr = off; [tiles_n * tiles_m] ints, all zero on entry and on exit
-    void* fin_y;          // bf16 [M, fin_ldy]
-    const float* fin_bias;
-    void* fin_pooled;     // bf16 [M/4, fin_ldp] when fin_pool_w > 0
-    int fin_ldy, fin_ldp, fin_relu;
-    int fin_pool_w;       // W of the [B,H,W] map the rows enumerate (H, W even, 128 % (2W) == 0); 0 = no pooling
-};
-
-// Operand sources.  A: 0 = K-major matrix (2-D TMA), 1 = MN-major matrix, 2 = im2col gather of an NHWC activation
-// (implicit-GEMM convolution: fprop reads x, dgrad reads dY).  B: 0 = K-major matrix, 1 = MN-major matrix,
-// 2 = im2col gather, MN-major (wgrad: the column matrix is never materialised), 3 = conv weight [Cout, kh*kw, Cin] read
-// through a 3-D map as the MN-major operand of dgrad (no transposed / flipped weight copy).
-struct ConvK {
-    int C;            // channels of the gathered activation (Cin for fprop / wgrad, Cout for dgrad)
-    int KH, KW;
-    int P, Q;         // spatial extent of the pixel index space the gather walks (conv output for fprop/wgrad, dX for dgrad)
-    int sh, sw;       // traversal stride
-    int low_h, low_w; // bounding-box lower corner (= -padding for fprop/wgrad, -(k-1-padding) for dgrad)
-    int flip;         // dgrad: weight tap = kh*kw-1 - gather tap
-};
-
-template <int BN, bool kDual>
-struct GemmSmem {
-    static constexpr int kABytes = kBM * kBK * 2;  // 16 KiB
-    static constexpr int kBBytes = BN * kBK * 2;
-    static constexpr int kStageBytes = kABytes + kBBytes;
-    // BN <= 128: stages sized so that two CTAs fit in one SM (~100 KB each): one CTA's epilogue overlaps the other's main loop,
-    // which is what the skinny-N, large-M convolution GEMMs (memory-bound) need.  BN = 256 (large square GEMMs): one CTA, deep ring.
-    // Deep variant (small grids, at most one wave): long ring, one CTA per SM, so every CTA has an SM's L2 port to itself.
-    static constexpr int kStagesDual = (BN <= 32) ? 5 : (BN <= 64 ? 4 : (BN <= 128 ? 3 : 4));
-    static constexpr int kStagesDeep = (BN <= 64) ? 6 : (BN <= 128 ? 5 : 4);
-    static constexpr int kStages = kDual ? kStagesDual : kStagesDeep;
-    static constexpr int kBarrierBytes = 256;
-    static constexpr int kTotal = kStages * kStageBytes + kBarrierBytes + 1024;  // +1024: manual 1 KiB alignment
-};
-
-// Epilogue of one 128 x BN accumulator tile: every thread owns one TMEM lane = one output row, 32 columns at a time.
-template <int BN>
-__device__ __forceinline__ void gemm_epilogue_tile(uint32_t tmem_d, int q, int lane, int m0, int n0, int M, int N, const GemmEpilogue& ep,
-                                                   bool add_bias) {
-    const int row = m0 + q * 32 + lane;
-    const bool row_ok = row < M;
-#pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += 32) {
-        if (n0 + c0 >= N) break;  // warp-uniform
-        uint32_t v[32];
-        tmem_ld_32x32(tmem_d + (static_cast<uint32_t>(q * 32) << 16) + c0, v);
-        tmem_ld_wait();
-        if (!row_ok) continue;
-        const int col0 = n0 + c0;
-        const int ncols = min(32, N - col0);
-        float f[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            float x = __uint_as_float(v[j]);
-            if (add_bias && j < ncols) x += __ldg(ep.bias + col0 + j);
-            if (ep.relu) x = fmaxf(x, 0.f);
-            f[j] = x;
-        }
-        if (ep.atomic) {
-            float* o = static_cast<float*>(ep.out) + static_cast<size_t>(row) * ep.ldo;
-            if (ep.perm_cin > 0) {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const int c = col0 + j;
-                    if (j < ncols) red_add_f32(o + (c % ep.perm_cin) * ep.perm_khw + c / ep.perm_cin, f[j]);
-                }
-            } else if (ncols == 32 && (ep.ldo & 3) == 0) {
-#pragma unroll
-                for (int j = 0; j < 32; j += 4) red_add_f32x4(o + col0 + j, f[j], f[j + 1], f[j + 2], f[j + 3]);
-            } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (j < ncols) red_add_f32(o + col0 + j, f[j]);
-            }
-        } else if (ep.out_is_f32) {
-            float* o = static_cast<float*>(ep.out) + static_cast<size_t>(row) * ep.ldo;
-            if (ep.perm_cin > 0) {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const int c = col0 + j;
-                    if (j < ncols) o[(c % ep.perm_cin) * ep.perm_khw + c / ep.perm_cin] = f[j];
-                }
-            } else if (ncols == 32 && (ep.ldo & 3) == 0) {
-#pragma unroll
-                for (int j = 0; j < 32; j += 4) st_f32x4(o + col0 + j, make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]));
-            } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (j < ncols) o[col0 + j] = f[j];
-            }
-        } else {
-            __nv_bfloat16* o = static_cast<__nv_bfloat16*>(ep.out) + static_cast<size_t>(row) * ep.ldo;
-            if (ncols == 32 && (ep.ldo & 7) == 0) {
-#pragma unroll
-                for (int j = 0; j < 32; j += 8) {
-                    uint4 pk;
-                    pk.x = pack_bf16x2(f[j], f[j + 1]);
-                    pk.y = pack_bf16x2(f[j + 2], f[j + 3]);
-                    pk.z = pack_bf16x2(f[j + 4], f[j + 5]);
-                    pk.w = pack_bf16x2(f[j + 6], f[j + 7]);
-                    *reinterpret_cast<uint4*>(o + col0 + j) = pk;
-                }
-            } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (j < ncols) o[col0 + j] = __float2bfloat16_rn(f[j]);
-            }
-        }
-    }
-}
-
-// bf16 store of 4 finished values (bias / ReLU applied by the caller); returns them as rounded floats for the pool.
-__device__ __forceinline__ void fin_store4(__nv_bfloat16* dst, float (&x)[4], int nvalid) {
-    if (nvalid == 4) {
-        uint2 pk;
-        pk.x = pack_bf16x2(x[0], x[1]);
-        pk.y = pack_bf16x2(x[2], x[3]);
-        *reinterpret_cast<uint2*>(dst) = pk;
-    } else {
-        for (int j = 0; j < nvalid; ++j) dst[j] = __float2bfloat16_rn(x[j]);
-    }
-#pragma unroll
-    for (int j = 0; j < 4; ++j) x[j] = __bfloat162float(__float2bfloat16_rn(x[j]));
-}
-
-// Finishing pass of one 128 x BN tile by the 128 epilogue threads of the CTA that arrived last (see GemmEpilogue::fin_counters).
-// A warp walks rows, its lanes the columns (4 floats each), so every access is a coalesced 512-byte row segment out of L2.
-template <int BN>
-__device__ __forceinline__ void splitk_finish_tile(const GemmEpilogue& ep, int ew, int lane, int m0, int n0, int M, int N) {
-    float* __restrict__ ws = static_cast<float*>(ep.out);
-    const int ldw = ep.ldo;
-    __nv_bfloat16* __restrict__ y = static_cast<__nv_bfloat16*>(ep.fin_y);
-    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 1
-    for (int c = lane * 4; c < BN; c += 128) {
-        const int col = n0 + c;
-        if (col >= N) break;
-        const int nvalid = min(4, N - col);
-        float b[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) b[j] = (ep.fin_bias != nullptr && j < nvalid) ? __ldg(ep.fin_bias + col + j) : 0.f;
-        if (ep.fin_pool_w == 0) {
-            constexpr int kU = 16;
-#pragma unroll 1
-            for (int r0 = ew * 32; r0 < ew * 32 + 32; r0 += kU) {
-                float4 v[kU];
-#pragma unroll
-                for (int u = 0; u < kU; ++u) {
-                    const int row = m0 + r0 + u;
-                    v[u] = row < M ? __ldcg(reinterpret_cast<const float4*>(ws + static_cast<size_t>(row) * ldw + col)) : zero4;
-                }
-#pragma unroll
-                for (int u = 0; u < kU; ++u) {
-                    const int row = m0 + r0 + u;
-                    if (row >= M) continue;
-                    __stcg(reinterpret_cast<float4*>(ws + static_cast<size_t>(row) * ldw + col), zero4);
-                    float x[4] = {v[u].x + b[0], v[u].y + b[1], v[u].z + b[2], v[u].w + b[3]};
-                    if (ep.fin_relu) {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) x[j] = fmaxf(x[j], 0.f);
-                    }
-                    fin_store4(y + static_cast<size_t>(row) * ep.fin_ldy + col, x, nvalid);
-                }
-            }
-        } else {
-            // rows of the tile are NHWC pixels; m0 is a multiple of 2W, so the tile holds 128/(2W) row pairs = 32 whole windows
-            __nv_bfloat16* __restrict__ pooled = static_cast<__nv_bfloat16*>(ep.fin_pooled);
-            const int W = ep.fin_pool_w, Wp = W >> 1;
-            const int pair0 = m0 / (2 * W);
-            constexpr int kU = 4;
-#pragma unroll 1
-            for (int j0 = ew * 8; j0 < ew * 8 + 8; j0 += kU) {
-                float4 v[kU][4];
-                int base[kU];
-#pragma unroll
-                for (int u = 0; u < kU; ++u) {
-                    const int j = j0 + u;
-                    const int pr = j / Wp, wp = j - pr * Wp;
-                    base[u] = m0 + pr * 2 * W + 2 * wp;
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const int row = base[u] + (q >> 1) * W + (q & 1);
-                        v[u][q] = base[u] < M ? __ldcg(reinterpret_cast<const float4*>(ws + static_cast<size_t>(row) * ldw + col)) : zero4;
-                    }
-                }
-#pragma unroll
-                for (int u = 0; u < kU; ++u) {
-                    if (base[u] >= M) continue;
-                    const int j = j0 + u;
-                    const int pr = j / Wp, wp = j - pr * Wp;
-                    float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const int row = base[u] + (q >> 1) * W + (q & 1);
-                        __stcg(reinterpret_cast<float4*>(ws + static_cast<size_t>(row) * ldw + col), zero4);
-                        float x[4] = {v[u][q].x + b[0], v[u][q].y + b[1], v[u][q].z + b[2], v[u][q].w + b[3]};
-                        if (ep.fin_relu) {
-#pragma unroll
-                            for (int jj = 0; jj < 4; ++jj) x[jj] = fmaxf(x[jj], 0.f);
-                        }
-                        fin_store4(y + static_cast<size_t>(row) * ep.fin_ldy + col, x, nvalid);
-#pragma unroll
-                        for (int jj = 0; jj < 4; ++jj) mx[jj] = fmaxf(mx[jj], x[jj]);
-                    }
-                    const size_t mp = static_cast<size_t>(pair0 + pr) * Wp + wp;
-                    fin_store4(pooled + mp * ep.fin_ldp + col, mx, nvalid);
-                }
-            }
-        }
-    }
-}
-
-template <int BN, int AM, int BMODE, bool kDual, bool kFin = false>
-__global__ void __launch_bounds__(kGemmThreads, ((kDual && BN <= 128) ? 2 : 1))
-gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-                         GemmEpilogue ep, ConvK cv, int M, int N, int K, int kb_per_split) {
-    constexpr bool A_MN = AM == 1;
-    constexpr bool B_MN = BMODE >= 1;
-    using S = GemmSmem<BN, kDual>;
-    constexpr int kStages = S::kStages;
-    constexpr int kTmemCols = BN < 32 ? 32 : BN;
-    static_assert(BN % 16 == 0 && BN >= 32 && BN <= 256, "UMMA M=128 needs N%16==0, 16<=N<=256");
-    static_assert(!B_MN || BN % 64 == 0, "MN-major B tiles are built from 64-wide TMA boxes");
-
-    extern __shared__ uint8_t smem_raw[];
-    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t bar_base = smem_base + kStages * S::kStageBytes;
-    auto full_bar = [&](int s) { return bar_base + 8u * s; };
-    auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
-    const uint32_t tmem_full_bar = bar_base + 8u * (2 * kStages);
-    const uint32_t tmem_holder = bar_base + 8u * (2 * kStages + 1);
-    uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
-    volatile uint32_t* tmem_holder_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + kStages * S::kStageBytes + 8 * (2 * kStages + 1));
-
-    const int warp = threadIdx.x >> 5;
-    const int lane = threadIdx.x & 31;
-    const int m0 = blockIdx.x * kBM;
-    const int n0 = blockIdx.y * BN;
-    const int nkb_total = (K + kBK - 1) / kBK;
-    const int kb_begin = blockIdx.z * kb_per_split;
-    const int kb_end = min(nkb_total, kb_begin + kb_per_split);
-    const int nkb = kb_end - kb_begin;  // host guarantees >= 1
-
-    if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&tma_a);
-        tma_prefetch_desc(&tma_b);
-        for (int s = 0; s < kStages; ++s) {
-            mbar_init(full_bar(s), 1);
-            mbar_init(empty_bar(s), 1);
-        }
-        mbar_init(tmem_full_bar, 1);
-        fence_mbar_init();
-    }
-    if (warp == 1) tmem_alloc<kTmemCols>(tmem_holder);
-    tcgen05_fence_before();
-    __syncthreads();
-    tcgen05_fence_after();
-    const uint32_t tmem_d = *tmem_holder_ptr;
-    // Everything above touched only shared memory / TMEM / kernel parameters: it overlapped the previous kernel.
-    pdl_launch_dependents();
-    pdl_wait();
-
-    if (warp == 0) {
-        // ------------------------------ TMA producer ------------------------------
-        if (lane == 0) {
-            // im2col A: the tile's first pixel in (n, p, q) and its input-space coordinates, computed once
-            int a_n = 0, a_h = 0, a_w = 0;
-            if constexpr (AM == 2) {
-                const int pq = cv.P * cv.Q;
-                a_n = m0 / pq;
-                const int rem = m0 - a_n * pq;
-                const int pp = rem / cv.Q;
-                a_h = cv.low_h + pp * cv.sh;
-                a_w = cv.low_w + (rem - pp * cv.Q) * cv.sw;
-            }
-            for (int it = 0; it < nkb; ++it) {
-                const int s = it % kStages;
-                const uint32_t ph = (it / kStages) & 1u;
-                mbar_wait(empty_bar(s), ph ^ 1u);
-                const uint32_t a_dst = smem_base + s * S::kStageBytes;
-                const uint32_t b_dst = a_dst + S::kABytes;
-                const int k0 = (kb_begin + it) * kBK;
-                mbar_arrive_expect_tx(full_bar(s), S::kStageBytes);
-                if constexpr (AM == 0) {
-                    tma_load_2d(a_dst, &tma_a, k0, m0, full_bar(s));
-                } else if constexpr (AM == 1) {
-                    tma_load_2d(a_dst, &tma_a, m0, k0, full_bar(s));
-                    tma_load_2d(a_dst + 8192, &tma_a, m0 + 64, k0, full_bar(s));
-                } else {
-                    // k-block = 64 channels of one filter tap (C % 64 == 0): 128 pixels x 128 bytes, one instruction
-                    const int tap = k0 / cv.C;
-                    const int r = tap / cv.KW;
-                    tma_load_im2col_4d(a_dst, &tma_a, k0 - tap * cv.C, a_w, a_h, a_n, tap - r * cv.KW, r, full_bar(s));
-                }
-                if constexpr (BMODE == 0) {
-                    tma_load_2d(b_dst, &tma_b, k0, n0, full_bar(s));
-                } else if constexpr (BMODE == 1) {
-#pragma unroll
-                    for (int j = 0; j < BN / 64; ++j) tma_load_2d(b_dst + j * 8192, &tma_b, n0 + 64 * j, k0, full_bar(s));
-                } else if constexpr (BMODE == 2) {
-                    // wgrad: reduction rows = 64 output pixels starting at k0, columns = 64 channels of the tap that owns them
-                    const int pq = cv.P * cv.Q;
-                    const int bn_ = k0 / pq;
-                    const int rem = k0 - bn_ * pq;
-                    const int pp = rem / cv.Q;
-                    const int bh = cv.low_h + pp * cv.sh;
-                    const int bw = cv.low_w + (rem - pp * cv.Q) * cv.sw;
-#pragma unroll
-                    for (int j = 0; j < BN / 64; ++j) {
-                        int kcol = n0 + 64 * j;
-                        if (kcol >= N) kcol = 0;   // tile overhang: any legal box, the epilogue masks those columns
-                        const int tap = kcol / cv.C;
-                        const int r = tap / cv.KW;
-                        tma_load_im2col_4d(b_dst + j * 8192, &tma_b, kcol - tap * cv.C, bw, bh, bn_, tap - r * cv.KW, r, full_bar(s));
-                    }
-                } else {
-                    // dgrad: reduction rows = 64 output channels of one (flipped) tap, columns = 64 input channels
-                    const int tap = k0 / cv.C;
-                    const int wtap = cv.flip ? (cv.KH * cv.KW - 1 - tap) : tap;
-#pragma unroll
-                    for (int j = 0; j < BN / 64; ++j) {
-                        int cin0 = n0 + 64 * j;
-                        if (cin0 >= N) cin0 = 0;
-                        tma_load_3d(b_dst + j * 8192, &tma_b, cin0, wtap, k0 - tap * cv.C, full_bar(s));
-                    }
-                }
-            }
-        }
-    } else if (warp == 1) {
-        // ------------------------------ MMA issuer ------------------------------
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, A_MN, B_MN);
-            for (int it = 0; it < nkb; ++it) {
-                const int s = it % kStages;
-                const uint32_t ph = (it / kStages) & 1u;
-                mbar_wait(full_bar(s), ph);
-                tcgen05_fence_after();
-                const uint32_t a_src = smem_base + s * S::kStageBytes;
-                const uint32_t b_src = a_src + S::kABytes;
-#pragma unroll
-                for (int k = 0; k < kBK / kUmmaK; ++k) {
-                    // K-major: step 16 bf16 = 32 B inside the 128 B swizzle row.
-                    // MN-major: step 16 K-rows = two 8-row groups = 2048 B.
-                    const uint64_t adesc = A_MN ? umma_smem_desc(a_src + k * 2048, 8192, 1024) : umma_smem_desc(a_src + k * 32, 16, 1024);
-                    const uint64_t bdesc = B_MN ? umma_smem_desc(b_src + k * 2048, 8192, 1024) : umma_smem_desc(b_src + k * 32, 16, 1024);
-                    umma_bf16(tmem_d, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
-                }
-                umma_commit(empty_bar(s));  // smem stage reusable once these MMAs retire
-            }
-            umma_commit(tmem_full_bar);     // accumulator complete
-        }
-    } else {
-        // ------------------------------ epilogue ------------------------------
-        const int q = warp & 3;                 // TMEM lane quadrant this warp may access
-        mbar_wait(tmem_full_bar, 0);
-        tcgen05_fence_after();
-        gemm_epilogue_tile<BN>(tmem_d, q, lane, m0, n0, M, N, ep, ep.bias != nullptr && (!ep.atomic || blockIdx.z == 0));
-        if constexpr (kFin) {     // separate instantiation: the finishing code costs ~100 registers the plain kernels should not carry
-            // release: this thread's red.adds are ordered before the counter bump; acquire on the other side before reading back
-            __threadfence();
-            asm volatile("bar.sync 1, 128;" ::: "memory");
-            if (warp == 2 && lane == 0) {
-                int* ctr = ep.fin_counters + blockIdx.y * gridDim.x + blockIdx.x;
-                const bool last = atomicAdd(ctr, 1) == static_cast<int>(gridDim.z) - 1;
-                if (last) *ctr = 0;       // nobody else touches this counter before the next kernel
-                tmem_holder_ptr[1] = last ? 1u : 0u;
-            }
-            asm volatile("bar.sync 1, 128;" ::: "memory");
-            if (tmem_holder_ptr[1] != 0u) {
-                __threadfence();
-                splitk_finish_tile<BN>(ep, warp - 2, lane, m0, n0, M, N);
-            }
-        }
-    }
-
-    tcgen05_fence_before();
-    __syncthreads();
-    if (warp == 1) {
-        tcgen05_fence_after();
-        tmem_dealloc<kTmemCols>(tmem_d);
-    }
-}
-
-// ----------------------------------------------------------------------------------------------
-// CTA-pair variant (tcgen05 cta_group::2) for large GEMMs with both operands K-major: a cluster of two CTAs on the two SMs of a
-// TPC computes one 256 x 256 output tile.  Each CTA stages its own 128 rows of A and only HALF of the B tile (128 of the 256
-// columns); the pair's MMA (M = 256, issued by one thread of the leader CTA) reads both halves, so shared-memory traffic for B is
-// halved per SM and a stage is 32 KB instead of 48 KB (6-deep ring).  Each CTA keeps its 128 x 256 fp32 accumulator in its own
-// TMEM and runs its own epilogue.  Synchronisation: both producers' TMA bytes are counted on the LEADER's full barrier; the
-// leader's tcgen05.commit multicasts the "stage free" / "accumulator ready" arrivals to the barriers of both CTAs.
-// ----------------------------------------------------------------------------------------------
-struct PairSmem {
-    static constexpr int kBN = 256;
-    static constexpr int kABytes = kBM * kBK * 2;          // 128 x 64 bf16 = 16 KiB (this CTA's rows of A)
-    static constexpr int kBBytes = (kBN / 2) * kBK * 2;    // 128 x 64 bf16 = 16 KiB (this CTA's half of the B tile)
-    static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kStages = 7;             // 7 x 32 KiB + barriers = 225.3 KiB of the 227 KiB a CTA may own
-    static constexpr int kTotal = kStages * kStageBytes + 256 + 1024;
-};
-
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
-gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, GemmEpilogue ep, int M,
-                              int N, int K, int kb_per_split) {
-    using S = PairSmem;
-    constexpr int kStages = S::kStages;
-    constexpr int BN = S::kBN;
-    extern __shared__ uint8_t smem_raw[];
-    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t bar_base = smem_base + kStages * S::kStageBytes;
-    auto full_bar = [&](int s) { return bar_base + 8u * s; };
-    auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
-    const uint32_t tmem_full_bar = bar_base + 8u * (2 * kStages);
-    const uint32_t tmem_holder = bar_base + 8u * (2 * kStages + 1);
-    uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
-    volatile uint32_t* tmem_holder_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + kStages * S::kStageBytes + 8 * (2 * kStages + 1));
-
-    const int warp = threadIdx.x >> 5;
-    const int lane = threadIdx.x & 31;
-    const uint32_t rank = cluster_ctarank();                  // 0 = leader
-    const int m0 = (blockIdx.x >> 1) * (2 * kBM) + static_cast<int>(rank) * kBM;   // this CTA's 128 rows
-    const int n0 = blockIdx.y * BN;
-    const int nkb_total = (K + kBK - 1) / kBK;
-    const int kb_begin = blockIdx.z * kb_per_split;
-    const int kb_end = min(nkb_total, kb_begin + kb_per_split);
-    const int nkb = kb_end - kb_begin;
-
-    if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&tma_a);
-        tma_prefetch_desc(&tma_b);
-        for (int s = 0; s < kStages; ++s) {
-            mbar_init(full_bar(s), 1);      // leader's: one arrive.expect_tx covering the bytes of both CTAs
-            mbar_init(empty_bar(s), 1);     // one multicast commit per use
-        }
-        mbar_init(tmem_full_bar, 1);
-        fence_mbar_init();
-    }
-    cluster_sync_all();                     // both CTAs' barriers exist before anything can arrive on them remotely
-    if (warp == 1) tmem_alloc_2cta<BN>(tmem_holder);
-    tcgen05_fence_before();
-    __syncthreads();
-    cluster_sync_all();                     // both halves of the pair own their TMEM columns before the leader's first MMA
-    tcgen05_fence_after();
-    const uint32_t tmem_d = *tmem_holder_ptr;
-
-    if (warp == 0) {
-        if (lane == 0) {
-            for (int it = 0; it < nkb; ++it) {
-                const int s = it % kStages;
-                const uint32_t ph = (it / kStages) & 1;
-                mbar_wait(empty_bar(s), ph ^ 1);
-                if (rank == 0) mbar_arrive_expect_tx(full_bar(s), 2u * S::kStageBytes);
-                const uint32_t a_dst = smem_base + s * S::kStageBytes;
-                const int kc = (kb_begin + it) * kBK;
-                tma_load_2d_2cta(a_dst, &tma_a, kc, m0, full_bar(s));
-                tma_load_2d_2cta(a_dst + S::kABytes, &tma_b, kc, n0 + static_cast<int>(rank) * (BN / 2), full_bar(s));
-            }
-        }
-    } else if (warp == 1) {
-        if (rank == 0 && lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(2 * kBM, BN, false, false);
-            for (int it = 0; it < nkb; ++it) {
-                const int s = it % kStages;
-                const uint32_t ph = (it / kStages) & 1;
-                mbar_wait(full_bar(s), ph);
-                tcgen05_fence_after();
-                const uint32_t a_src = smem_base + s * S::kStageBytes;
-                const uint32_t b_src = a_src + S::kABytes;
-#pragma unroll
-                for (int k = 0; k < kBK / kUmmaK; ++k)
-                    umma_bf16_2cta(tmem_d, umma_smem_desc(a_src + k * 32, 16, 1024), umma_smem_desc(b_src + k * 32, 16, 1024), idesc,
-                                   (it > 0 || k > 0) ? 1u : 0u);
-                umma_commit_2cta(empty_bar(s));       // frees stage s in both CTAs
-            }
-            umma_commit_2cta(tmem_full_bar);          // both epilogues may start
-        }
-    } else {
-        const int q = warp & 3;
-        mbar_wait(tmem_full_bar, 0);
-        tcgen05_fence_after();
-        gemm_epilogue_tile<BN>(tmem_d, q, lane, m0, n0, M, N, ep, ep.bias != nullptr && (!ep.atomic || blockIdx.z == 0));
-    }
-
-    tcgen05_fence_before();
-    __syncthreads();
-    cluster_sync_all();                     // neither CTA may leave (or free TMEM) while the pair's MMAs / multicast arrivals can still touch it
-    if (warp == 1) {
-        tcgen05_fence_after();
-        tmem_dealloc_2cta<BN>(tmem_d);
-    }
-}
-
-// Persistent form of the CTA-pair kernel: one cluster per TPC walks a strided list of 256 x 256 tiles.  The accumulator is
-// double-buffered in TMEM (2 x 256 of the 512 columns of each SM), so the epilogue of tile t (tcgen05.ld, bias / ReLU, stores —
-// 128 KB of output per CTA) runs while the pair's tensor cores already work on tile t+1, and the smem ring never drains between
-// tiles.  "Accumulator drained" is signalled by the 4 epilogue warps of BOTH CTAs on the leader's barrier (8 arrivals).
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
-gemm_bf16_tcgen05_pair_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, GemmEpilogue ep,
-                                         int M, int N, int K, int tiles_m2, int tiles_n, int group_m) {
-    using S = PairSmem;
-    constexpr int kStages = S::kStages;
-    constexpr int BN = S::kBN;
-    extern __shared__ uint8_t smem_raw[];
-    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t bar_base = smem_base + kStages * S::kStageBytes;
-    auto full_bar = [&](int s) { return bar_base + 8u * s; };
-    auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
-    auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStages + a); };
-    auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStages + 2 + a); };
-    const uint32_t tmem_holder = bar_base + 8u * (2 * kStages + 4);
-    uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
-    volatile uint32_t* tmem_holder_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + kStages * S::kStageBytes + 8 * (2 * kStages + 4));
-
-    const int warp = threadIdx.x >> 5;
-    const int lane = threadIdx.x & 31;
-    const uint32_t rank = cluster_ctarank();
-    const int nkb = (K + kBK - 1) / kBK;
-    const int num_tiles = tiles_m2 * tiles_n;
-    const int first = blockIdx.x >> 1, stride = gridDim.x >> 1;
-    // Tile order: bands of group_m row pairs, column by column inside a band, so the ~74 tiles in flight cover a near-square patch of C
-    // and share A / B panels through L2 (grouped rasterisation).
-    auto tile_mn = [&](int tile, int& mp, int& nt) {
-        const int band = group_m * tiles_n;
-        const int g = tile / band, r = tile - g * band;
-        const int gm = min(group_m, tiles_m2 - g * group_m);
-        nt = r / gm;
-        mp = g * group_m + (r - nt * gm);
-    };
-
-    if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&tma_a);
-        tma_prefetch_desc(&tma_b);
-        for (int s = 0; s < kStages; ++s) {
-            mbar_init(full_bar(s), 1);
-            mbar_init(empty_bar(s), 1);
-        }
-        for (int a = 0; a < 2; ++a) {
-            mbar_init(tfull_bar(a), 1);
-            mbar_init(tempty_bar(a), 8);     // 4 epilogue warps x 2 CTAs (only the leader's copy is used)
-        }
-        fence_mbar_init();
-    }
-    cluster_sync_all();
-    if (warp == 1) tmem_alloc_2cta<512>(tmem_holder);
-    tcgen05_fence_before();
-    __syncthreads();
-    cluster_sync_all();
-    tcgen05_fence_after();
-    const uint32_t tmem_base = *tmem_holder_ptr;
-
-    if (warp == 0) {
-        if (lane == 0) {
-            int it = 0;
-            for (int tile = first; tile < num_tiles; tile += stride) {
-                int mp, nt;
-                tile_mn(tile, mp, nt);
-                const int m0 = mp * (2 * kBM) + static_cast<int>(rank) * kBM;
-                const int nb = nt * BN + static_cast<int>(rank) * (BN / 2);
-                for (int kb = 0; kb < nkb; ++kb, ++it) {
-                    const int s = it % kStages;
-                    const uint32_t ph = (it / kStages) & 1u;
-                    mbar_wait(empty_bar(s), ph ^ 1u);
-                    if (rank == 0) mbar_arrive_expect_tx(full_bar(s), 2u * S::kStageBytes);
-                    const uint32_t a_dst = smem_base + s * S::kStageBytes;
-                    tma_load_2d_2cta(a_dst, &tma_a, kb * kBK, m0, full_bar(s));
-                    tma_load_2d_2cta(a_dst + S::kABytes, &tma_b, kb * kBK, nb, full_bar(s));
-                }
-            }
-        }
-    } else if (warp == 1) {
-        if (rank == 0 && lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(2 * kBM, BN, false, false);
-            int it = 0, t = 0;
-            for (int tile = first; tile < num_tiles; tile += stride, ++t) {
-                const int acc = t & 1;
-                mbar_wait(tempty_bar(acc), ((t >> 1) & 1u) ^ 1u);     // both epilogues have drained this accumulator
-                tcgen05_fence_after();
-                const uint32_t tmem_d = tmem_base + acc * BN;
-                for (int kb = 0; kb < nkb; ++kb, ++it) {
-                    const int s = it % kStages;
-                    const uint32_t ph = (it / kStages) & 1u;
-                    mbar_wait(full_bar(s), ph);
-                    tcgen05_fence_after();
-                    const uint32_t a_src = smem_base + s * S::kStageBytes;
-                    const uint32_t b_src = a_src + S::kABytes;
-#pragma unroll
-                    for (int k = 0; k < kBK / kUmmaK; ++k)
-                        umma_bf16_2cta(tmem_d, umma_smem_desc(a_src + k * 32, 16, 1024), umma_smem_desc(b_src + k * 32, 16, 1024), idesc,
-                                       (kb > 0 || k > 0) ? 1u : 0u);
-                    umma_commit_2cta(empty_bar(s));
-                }
-                umma_commit_2cta(tfull_bar(acc));
-            }
-        }
-    } else {
-        const int q = warp & 3;
-        int t = 0;
-        for (int tile = first; tile < num_tiles; tile += stride, ++t) {
-            const int acc = t & 1;
-            int mp, nt;
-            tile_mn(tile, mp, nt);
-            const int m0 = mp * (2 * kBM) + static_cast<int>(rank) * kBM;
-            const int n0 = nt * BN;
-            mbar_wait(tfull_bar(acc), (t >> 1) & 1u);
-            tcgen05_fence_after();
-            gemm_epilogue_tile<BN>(tmem_base + acc * BN, q, lane, m0, n0, M, N, ep, ep.bias != nullptr);
-            tcgen05_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive_leader(tempty_bar(acc));
-        }
-    }
-
-    tcgen05_fence_before();
-    __syncthreads();
-    cluster_sync_all();
-    if (warp == 1) {
-        tcgen05_fence_after();
-        tmem_dealloc_2cta<512>(tmem_base);
-    }
-}
-
-// ----------------------------------------------------------------------------------------------
-// Persistent variant for grids of many tiles (ResNet-sized convolutions): one CTA per SM walks a strided list of output
-// tiles.  Barrier set-up, TMEM allocation and descriptor prefetch are paid once per SM instead of once per tile, the smem
-// ring keeps streaming across tile boundaries, and the accumulator is double-buffered in TMEM (2 x BN columns) so the
-// epilogue of tile t (tcgen05.ld, bias/ReLU, stores) overlaps the TMA + MMA main loop of tile t+1.  No split-K here.
-// ----------------------------------------------------------------------------------------------
-template <int BN>
-struct PersistSmem {
-    static constexpr int kABytes = kBM * kBK * 2;
-    static constexpr int kBBytes = BN * kBK * 2;
-    static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kStages = (BN <= 64) ? 7 : (BN <= 128 ? 5 : 4);
-    static constexpr int kTotal = kStages * kStageBytes + 256 + 1024;
-};
-
-template <int BN, int AM, int BMODE>
-__global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_bf16_tcgen05_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, GemmEpilogue ep,
-                                    ConvK cv, int M, int N, int K, int tiles_m, int tiles_n) {
-    constexpr bool A_MN = AM == 1;
-    constexpr bool B_MN = BMODE >= 1;
-    using S = PersistSmem<BN>;
-    constexpr int kStages = S::kStages;
-    constexpr int kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
-    static_assert(2 * BN <= 512, "two accumulators must fit in TMEM");
-
-    extern __shared__ uint8_t smem_raw[];
-    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t bar_base = smem_base + kStages * S::kStageBytes;
-    auto full_bar = [&](int s) { return bar_base + 8u * s; };
-    auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
-    auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStages + a); };
-    auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStages + 2 + a); };
-    const uint32_t tmem_holder = bar_base + 8u * (2 * kStages + 4);
-    uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
-    volatile uint32_t* tmem_holder_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + kStages * S::kStageBytes + 8 * (2 * kStages + 4));
-
-    const int warp = threadIdx.x >> 5;
-    const int lane = threadIdx.x & 31;
-    const int nkb = (K + kBK - 1) / kBK;
-    const int num_tiles = tiles_m * tiles_n;
-
-    if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&tma_a);
-        tma_prefetch_desc(&tma_b);
-        for (int s = 0; s < kStages; ++s) {
-            mbar_init(full_bar(s), 1);
-            mbar_init(empty_bar(s), 1);
-        }
-        for (int a = 0; a < 2; ++a) {
-            mbar_init(tfull_bar(a), 1);
-            mbar_init(tempty_bar(a), 4);     // one arrival per epilogue warp
-        }
-        fence_mbar_init();
-    }
-    if (warp == 1) tmem_alloc<kTmemCols>(tmem_holder);
-    tcgen05_fence_before();
-    __syncthreads();
-    tcgen05_fence_after();
-    const uint32_t tmem_base = *tmem_holder_ptr;
-    pdl_launch_dependents();
-    pdl_wait();
-
-    if (warp == 0) {
-        if (lane == 0) {
-            int it = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int m0 = (tile / tiles_n) * kBM;
-                const int n0 = (tile % tiles_n) * BN;
-                int a_n = 0, a_h = 0, a_w = 0;
-                if constexpr (AM == 2) {
-                    const int pq = cv.P * cv.Q;
-                    a_n = m0 / pq;
-                    const int rem = m0 - a_n * pq;
-                    const int pp = rem / cv.Q;
-                    a_h = cv.low_h + pp * cv.sh;
-                    a_w = cv.low_w + (rem - pp * cv.Q) * cv.sw;
-                }
-                for (int kb = 0; kb < nkb; ++kb, ++it) {
-                    const int s = it % kStages;
-                    const uint32_t ph = (it / kStages) & 1u;
-                    mbar_wait(empty_bar(s), ph ^ 1u);
-                    const uint32_t a_dst = smem_base + s * S::kStageBytes;
-                    const uint32_t b_dst = a_dst + S::kABytes;
-                    const int k0 = kb * kBK;
-                    mbar_arrive_expect_tx(full_bar(s), S::kStageBytes);
-                    if constexpr (AM == 0) {
-                        tma_load_2d(a_dst, &tma_a, k0, m0, full_bar(s));
-                    } else if constexpr (AM == 1) {
-                        tma_load_2d(a_dst, &tma_a, m0, k0, full_bar(s));
-                        tma_load_2d(a_dst + 8192, &tma_a, m0 + 64, k0, full_bar(s));
-                    } else {
-                        const int tap = k0 / cv.C;
-                        const int r = tap / cv.KW;
-                        tma_load_im2col_4d(a_dst, &tma_a, k0 - tap * cv.C, a_w, a_h, a_n, tap - r * cv.KW, r, full_bar(s));
-                    }
-                    if constexpr (BMODE == 0) {
-                        tma_load_2d(b_dst, &tma_b, k0, n0, full_bar(s));
-                    } else if constexpr (BMODE == 1) {
-#pragma unroll
-                        for (int j = 0; j < BN / 64; ++j) tma_load_2d(b_dst + j * 8192, &tma_b, n0 + 64 * j, k0, full_bar(s));
-                    } else if constexpr (BMODE == 2) {
-                        const int pq = cv.P * cv.Q;
-                        const int bn_ = k0 / pq;
-                        const int rem = k0 - bn_ * pq;
-                        const int pp = rem / cv.Q;
-                        const int bh = cv.low_h + pp * cv.sh;
-                        const int bw = cv.low_w + (rem - pp * cv.Q) * cv.sw;
-#pragma unroll
-                        for (int j = 0; j < BN / 64; ++j) {
-                            int kcol = n0 + 64 * j;
-                            if (kcol >= N) kcol = 0;
-                            const int tap = kcol / cv.C;
-                            const int r = tap / cv.KW;
-                            tma_load_im2col_4d(b_dst + j * 8192, &tma_b, kcol - tap * cv.C, bw, bh, bn_, tap - r * cv.KW, r, full_bar(s));
-                        }
-                    } else {
-                        const int tap = k0 / cv.C;
-                        const int wtap = cv.flip ? (cv.KH * cv.KW - 1 - tap) : tap;
-#pragma unroll
-                        for (int j = 0; j < BN / 64; ++j) {
-                            int cin0 = n0 + 64 * j;
-                            if (cin0 >= N) cin0 = 0;
-                            tma_load_3d(b_dst + j * 8192, &tma_b, cin0, wtap, k0 - tap * cv.C, full_bar(s));
-                        }
-                    }
-                }
-            }
-        }
-    } else if (warp == 1) {
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, A_MN, B_MN);
-            int it = 0, t = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
-                const int acc = t & 1;
-                mbar_wait(tempty_bar(acc), ((t >> 1) & 1u) ^ 1u);     // the epilogue has drained this accumulator
-                tcgen05_fence_after();
-                const uint32_t tmem_d = tmem_base + acc * BN;
-                for (int kb = 0; kb < nkb; ++kb, ++it) {
-                    const int s = it % kStages;
-                    const uint32_t ph = (it / kStages) & 1u;
-                    mbar_wait(full_bar(s), ph);
-                    tcgen05_fence_after();
-                    const uint32_t a_src = smem_base + s * S::kStageBytes;
-                    const uint32_t b_src = a_src + S::kABytes;
-#pragma unroll
-                    for (int k = 0; k < kBK / kUmmaK; ++k) {
-                        const uint64_t adesc = A_MN ? umma_smem_desc(a_src + k * 2048, 8192, 1024) : umma_smem_desc(a_src + k * 32, 16, 1024);
-                        const uint64_t bdesc = B_MN ? umma_smem_desc(b_src + k * 2048, 8192, 1024) : umma_smem_desc(b_src + k * 32, 16, 1024);
-                        umma_bf16(tmem_d, adesc, bdesc, idesc, (kb > 0 || k > 0) ? 1u : 0u);
-                    }
-                    umma_commit(empty_bar(s));
-                }
-                umma_commit(tfull_bar(acc));
-            }
-        }
-    } else {
-        const int q = warp & 3;
-        int t = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
-            const int acc = t & 1;
-            const int m0 = (tile / tiles_n) * kBM;
-            const int n0 = (tile % tiles_n) * BN;
-            mbar_wait(tfull_bar(acc), (t >> 1) & 1u);
-            tcgen05_fence_after();
-            gemm_epilogue_tile<BN>(tmem_base + acc * BN, q, lane, m0, n0, M, N, ep, ep.bias != nullptr);
-            tcgen05_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(tempty_bar(acc));
-        }
-    }
-
-    tcgen05_fence_before();
-    __syncthreads();
-    if (warp == 1) {
-        tcgen05_fence_after();
-        tmem_dealloc<kTmemCols>(tmem_base);
-    }
-}
-
-// ----------------------------------------------------------------------------------------------
-// host side
-// ----------------------------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode_fn() {
-    static EncodeTiledFn fn = nullptr;
-    if (!fn) {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult qres;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
-            qres == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<EncodeTiledFn>(p);
-    }
-    return fn;
-}
-
-// 2-D bf16 tensor map over a row-major [outer, inner] matrix with row pitch ld (elements), 128B swizzle.
-static int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
-                          uint32_t box_outer) {
-    EncodeTiledFn fn = get_encode_fn();
-    DMLB_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point not available");
-    DMLB_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base must be 16-byte aligned");
-    DMLB_REQUIRE((ld * 2) % 16 == 0, "TMA row pitch must be a multiple of 16 bytes (ld % 8 == 0 for bf16)");
-    cuuint64_t dims[2] = {inner, outer};
-    cuuint64_t strides[1] = {ld * 2};
-    cuuint32_t box[2] = {box_inner, box_outer};
-    cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) {
-        char buf[256];
-        snprintf(buf, sizeof(buf), "cuTensorMapEncodeTiled failed: CUresult %d (inner=%llu outer=%llu ld=%llu box=%ux%u)", (int)r,
-                 (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)ld, box_inner, box_outer);
-        dmlb_set_error(buf);
-        return -3;
-    }
-    return 0;
-}
-
-typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const int*,
-                                   const int*, cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeIm2colFn get_encode_im2col_fn() {
-    static EncodeIm2colFn fn = nullptr;
-    if (!fn) {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult qres;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &qres) == cudaSuccess &&
-            qres == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<EncodeIm2colFn>(p);
-    }
-    return fn;
-}
-
-// im2col tensor map over a bf16 NHWC activation [N, H, W, C] (channel pitch ld): boxes of `pixels` output pixels x 64 channels.
-// Bounding box per spatial dim: [low, dim - 1 + up]; the instruction adds the filter-tap offset to every pixel.
-static int make_tmap_im2col(CUtensorMap* map, const void* base, int C, int W, int H, int N, int ld, int low_w, int low_h, int up_w, int up_h,
-                            int sw, int sh, int pixels) {
-    EncodeIm2colFn fn = get_encode_im2col_fn();
-    DMLB_REQUIRE(fn != nullptr, "cuTensorMapEncodeIm2col entry point not available");
-    DMLB_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0 && ld % 8 == 0, "im2col TMA needs a 16-byte aligned NHWC tensor");
-    cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-    cuuint64_t strides[3] = {(cuuint64_t)ld * 2, (cuuint64_t)W * ld * 2, (cuuint64_t)H * W * ld * 2};
-    int lower[2] = {low_w, low_h};
-    int upper[2] = {up_w, up_h};
-    cuuint32_t trav[4] = {1, (cuuint32_t)sw, (cuuint32_t)sh, 1};
-    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lower, upper, 64, (cuuint32_t)pixels, trav,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) {
-        char buf[256];
-        snprintf(buf, sizeof(buf), "cuTensorMapEncodeIm2col failed: CUresult %d (C=%d W=%d H=%d N=%d ld=%d low=%d,%d up=%d,%d stride=%d,%d pixels=%d)",
-                 (int)r, C, W, H, N, ld, low_w, low_h, up_w, up_h, sw, sh, pixels);
-        dmlb_set_error(buf);
-        return -3;
-    }
-    // Same adjustment CUTLASS applies (cute/atom/copy_traits_sm90_im2col.hpp) for tensors smaller than 128 KiB on current drivers.
-    int drv = 0;
-    if (cudaDriverGetVersion(&drv) == cudaSuccess && drv <= 13010 && (unsigned long long)N * H * W * ld * 2ull < 131072ull)
-        reinterpret_cast<uint64_t*>(map)[1] &= ~(1ull << 21);
-    return 0;
-}
-
-// 3-D map over a conv weight shadow [Cout][kh*kw][Cin] (row pitch ldrow elements per Cout): box = 64 Cin x 1 tap x 64 Cout.
-static int make_tmap_w3d(CUtensorMap* map, const void* base, int Cin, int KHW, int Cout, int ldrow) {
-    EncodeTiledFn fn = get_encode_fn();
-    DMLB_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point not available");
-    cuuint64_t dims[3] = {(cuuint64_t)Cin, (cuuint64_t)KHW, (cuuint64_t)Cout};
-    cuuint64_t strides[2] = {(cuuint64_t)Cin * 2, (cuuint64_t)ldrow * 2};
-    cuuint32_t box[3] = {64, 1, 64};
-    cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) {
-        char buf[200];
-        snprintf(buf, sizeof(buf), "cuTensorMapEncodeTiled (3-D weight map) failed: CUresult %d (Cin=%d taps=%d Cout=%d ld=%d)", (int)r, Cin, KHW, Cout,
-                 ldrow);
-        dmlb_set_error(buf);
-        return -3;
-    }
-    return 0;
-}
-
-template <int BN, int AM, int BMODE, bool kDual, bool kFin = false>
-static int launch_gemm_v(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpilogue& ep, const ConvK& cv, int M, int N, int K, int splits,
-                         cudaStream_t stream) {
-    using S = GemmSmem<BN, kDual>;
-    auto kern = gemm_bf16_tcgen05_kernel<BN, AM, BMODE, kDual, kFin>;
-    // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute: remember it per device, not per process
-    static bool attr_set[64] = {};
-    int dev = 0;
-    DMLB_CHECK_CUDA(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        DMLB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
-        if (dev >= 0 && dev < 64) attr_set[dev] = true;
-    }
-    const int nkb = (K + kBK - 1) / kBK;
-    int kb_per = (nkb + splits - 1) / splits;
-    splits = (nkb + kb_per - 1) / kb_per;  // every z-slice owns >= 1 k-block
-    dim3 grid((M + kBM - 1) / kBM, (N + BN - 1) / BN, splits);
-    DMLB_CHECK_CUDA(launch_k(kern, grid, kGemmThreads, S::kTotal, stream, ta, tb, ep, cv, M, N, K, kb_per));
-    DMLB_LAUNCH_CHECK();
-    return 0;
-}
-
-template <int BN, int AM, int BMODE>
-static int launch_gemm_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpilogue& ep, const ConvK& cv, int M, int N, int K,
-                                  cudaStream_t stream) {
-    using S = PersistSmem<BN>;
-    auto kern = gemm_bf16_tcgen05_persistent_kernel<BN, AM, BMODE>;
-    // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute: remember it per device, not per process
-    static bool attr_set[64] = {};
-    int dev = 0;
-    DMLB_CHECK_CUDA(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        DMLB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
-        if (dev >= 0 && dev < 64) attr_set[dev] = true;
-    }
-    const int tiles_m = (M + kBM - 1) / kBM, tiles_n = (N + BN - 1) / BN;
-    int grid = tiles_m * tiles_n;
-    if (grid > dmlb_sm_count()) grid = dmlb_sm_count();
-    DMLB_CHECK_CUDA(launch_k(kern, grid, kGemmThreads, S::kTotal, stream, ta, tb, ep, cv, M, N, K, tiles_m, tiles_n));
-    DMLB_LAUNCH_CHECK();
-    return 0;
-}
-
-extern "C" int dmlb_gemm_pair_enabled();
-
-// 256 x 256 tiles on CTA pairs (see gemm_bf16_tcgen05_pair_kernel).  B's map has a 128-row box: each CTA loads half of the tile.
-static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb_half, const GemmEpilogue& ep, int M, int N, int K, int splits,
-                            cudaStream_t stream) {
-    using S = PairSmem;
-    auto kern = gemm_bf16_tcgen05_pair_kernel;
-    static bool attr_set[64] = {};
-    int dev = 0;
-    DMLB_CHECK_CUDA(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        DMLB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
-        if (dev >= 0 && dev < 64) attr_set[dev] = true;
-    }
-    const int nkb = (K + kBK - 1) / kBK;
-    int kb_per = (nkb + splits - 1) / splits;
-    splits = (nkb + kb_per - 1) / kb_per;
-    const int tiles_m2 = (M + 2 * kBM - 1) / (2 * kBM), tiles_n = (N + S::kBN - 1) / S::kBN;
-    const int clusters = dmlb_sm_count() / 2;
-    if (splits == 1 && tiles_m2 * tiles_n >= 2 * clusters && dmlb_gemm_pair_enabled() != 2) {
-        // at least two tiles per TPC: persistent form, epilogue of tile t overlaps the main loop of tile t+1
-        auto pk = gemm_bf16_tcgen05_pair_persistent_kernel;
-        static bool pattr[64] = {};
-        if (dev < 0 || dev >= 64 || !pattr[dev]) {
-            DMLB_CHECK_CUDA(cudaFuncSetAttribute(pk, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
-            if (dev >= 0 && dev < 64) pattr[dev] = true;
-        }
-        cudaLaunchConfig_t pc = {};
-        pc.gridDim = dim3(2 * clusters);
-        pc.blockDim = dim3(kGemmThreads);
-        pc.dynamicSmemBytes = S::kTotal;
-        pc.stream = stream;
-        static int group_m = -1;
-        if (group_m < 0) {
-            const char* e = getenv("DMLB_PAIR_GROUP_M");
-            group_m = e != nullptr ? atoi(e) : 8;
-            if (group_m < 1) group_m = 1 << 20;      // 0 = column-major over the whole matrix (no banding)
-        }
-        DMLB_CHECK_CUDA(cudaLaunchKernelEx(&pc, pk, ta, tb_half, ep, M, N, K, tiles_m2, tiles_n, group_m < tiles_m2 ? group_m : tiles_m2));
-        DMLB_LAUNCH_CHECK();
-        return 0;
-    }
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(2 * tiles_m2, tiles_n, splits);
-    cfg.blockDim = dim3(kGemmThreads);
-    cfg.dynamicSmemBytes = S::kTotal;
-    cfg.stream = stream;
-    DMLB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb_half, ep, M, N, K, kb_per));   // cluster shape comes from __cluster_dims__
-    DMLB_LAUNCH_CHECK();
-    return 0;
-}
-
-extern "C" int dmlb_gemm_persistent_enabled();
-
-// Several waves of tiles and no split-K -> the persistent kernel; more than one wave -> two CTAs per SM; otherwise the deep ring.
-template <int BN, int AM, int BMODE>
-static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpilogue& ep, const ConvK& cv, int M, int N, int K, int splits,
-                       cudaStream_t stream) {
-    const int nkb = (K + kBK - 1) / kBK;
-    const int kb_per = (nkb + splits - 1) / splits;
-    const long long ctas = 1ll * ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN) * ((nkb + kb_per - 1) / kb_per);
-    if constexpr (BN <= 128 && BMODE == 0) {
-        // forward form only (both operands K-major): the backward GEMMs share the GPU with the side-stream wgrad branch and a grid
-        // that pins every SM would serialise against it.  Short reductions only: with a long K loop the per-tile set-up is already amortised and the 2-CTA variant rasterises better
-        if (splits == 1 && ep.fin_counters == nullptr && nkb <= 24 && ctas >= 3ll * dmlb_sm_count() && dmlb_gemm_persistent_enabled())
-            return launch_gemm_persistent<BN, AM, BMODE>(ta, tb, ep, cv, M, N, K, stream);
-    }
-    if (ep.fin_counters != nullptr) {
-        // folded split-K finish: forward / dgrad operand forms only, small grids by construction -> deep-ring variant
-        if constexpr ((AM == 0 || AM == 2) && (BMODE == 0 || BMODE == 3) && BN <= 128)
-            return launch_gemm_v<BN, AM, BMODE, false, true>(ta, tb, ep, cv, M, N, K, splits, stream);
-        dmlb_set_error("fused split-K finish is instantiated for K-major / im2col A with K-major / weight-map B and tiles up to 128 wide");
-        return -4;
-    }
-    if (BN <= 128 && ctas > dmlb_sm_count()) return launch_gemm_v<BN, AM, BMODE, true>(ta, tb, ep, cv, M, N, K, splits, stream);
-    return launch_gemm_v<BN, AM, BMODE, false>(ta, tb, ep, cv, M, N, K, splits, stream);
-}
-
-// Arguments of the folded finishing pass (GemmEpilogue::fin_*), validated here.
-struct FinishArgs {
-    int* counters;
-    int n_counters;
-    const float* bias;
-    int relu;
-    void* y;
-    int ldy;
-    int pool_h, pool_w;   // 0, 0 = no pooling
-    void* pooled;
-    int ldp;
-};
-
-static int apply_finish(GemmEpilogue& ep, const FinishArgs& f, int M, int N, int BN) {
-    DMLB_REQUIRE(ep.atomic && ep.out_is_f32 && ep.bias == nullptr && ep.perm_cin == 0, "fused finish needs a plain accumulating fp32 workspace");
-    DMLB_REQUIRE(ep.ldo % 4 == 0 && ep.ldo >= N && (reinterpret_cast<uintptr_t>(ep.out) & 15) == 0, "workspace pitch must be a multiple of 4 covering N, base 16-byte aligned");
-    DMLB_REQUIRE(f.counters != nullptr && f.y != nullptr && f.ldy % 4 == 0 && (reinterpret_cast<uintptr_t>(f.y) & 7) == 0, "fused finish: bad output");
-    const long long tiles = 1ll * ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN);
-    DMLB_REQUIRE(tiles <= f.n_counters, "fused finish: more output tiles than arrival counters");
-    ep.fin_counters = f.counters; ep.fin_y = f.y; ep.fin_bias = f.bias; ep.fin_ldy = f.ldy; ep.fin_relu = f.relu;
-    ep.fin_pooled = nullptr; ep.fin_ldp = 0; ep.fin_pool_w = 0;
-    if (f.pool_w > 0) {
-        DMLB_REQUIRE(f.pool_h % 2 == 0 && f.pool_w % 2 == 0 && kBM % (2 * f.pool_w) == 0 && M % (f.pool_h * f.pool_w) == 0,
-                     "fused 2x2 pool needs an even [H,W] map whose row pairs tile 128 rows (W = 2..64, power of two)");
-        DMLB_REQUIRE(f.pooled != nullptr && f.ldp % 4 == 0 && (reinterpret_cast<uintptr_t>(f.pooled) & 7) == 0, "fused pool: bad pooled output");
-        ep.fin_pooled = f.pooled; ep.fin_ldp = f.ldp; ep.fin_pool_w = f.pool_w;
-    }
-    return 0;
-}
+using namespace dmlb;
 
 // 1 when dmlb_*_fin can fold the 2x2/2 pool for an [H, W] map (otherwise run the pool as its own kernel).
 extern "C" int dmlb_fin_pool_supported(int H, int W) { return (H > 0 && W > 0 && H % 2 == 0 && W % 2 == 0 && kBM % (2 * W) == 0) ? 1 : 0; }
 
-}  // namespace dmlb
-
-using namespace dmlb;
-
-// See include/dmlb.h for the contract.
-static int gemm_bf16_impl(const FinishArgs* fin, const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major, int M, int N, int K,
-                              void* out, int out_is_f32, int ldo, const float* bias, int relu, int split_k, int atomic,
-                              int perm_cin, int perm_khw, int tile_n, void* stream_) {
-    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    DMLB_REQUIRE(M > 0 && N > 0 && K > 0, "empty GEMM");
-    if (split_k < 1) split_k = 1;
-    if (split_k > 1) atomic = 1;
-    DMLB_REQUIRE(!atomic || out_is_f32, "atomic / split-K output must be fp32");
-    DMLB_REQUIRE(!(atomic && relu), "ReLU cannot be fused into an accumulating epilogue");
-    DMLB_REQUIRE(!a_mn_major || b_mn_major, "A MN-major with B K-major is not instantiated");
-
-    int BN = tile_n;
-    if (BN == 0) BN = (N > 64) ? 128 : (N > 32 ? 64 : 32);
-    if (b_mn_major && BN < 64) BN = 64;
-    DMLB_REQUIRE(BN == 32 || BN == 64 || BN == 128 || BN == 256, "tile_n must be 32, 64, 128 or 256");
-
-    CUtensorMap ta, tb;
-    int rc;
-    if (!a_mn_major) rc = make_tmap_bf16(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, kBK, kBM);
-    else             rc = make_tmap_bf16(&ta, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, kBK);
-    if (rc) return rc;
-    // 256-wide tiles of a plain K-major GEMM with at least one full pair of row tiles: CTA pairs (cta_group::2), half a B tile per CTA
-    const bool pair = BN == 256 && !a_mn_major && !b_mn_major && fin == nullptr && M > kBM && dmlb_gemm_pair_enabled();
-    if (!b_mn_major) rc = make_tmap_bf16(&tb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, kBK, (uint32_t)(pair ? BN / 2 : BN));
-    else             rc = make_tmap_bf16(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, kBK);
-    if (rc) return rc;
-
-    GemmEpilogue ep = {};
-    ep.out = out; ep.bias = bias; ep.ldo = ldo; ep.out_is_f32 = out_is_f32; ep.relu = relu; ep.atomic = atomic;
-    ep.perm_cin = perm_cin; ep.perm_khw = perm_khw;
-    if (fin != nullptr) {
-        rc = apply_finish(ep, *fin, M, N, BN);
-        if (rc) return rc;
-    }
-
-    if (pair) return launch_gemm_pair(ta, tb, ep, M, N, K, split_k, stream);
-    ConvK cv = {};
-#define DMLB_GEMM_CASE(bn, amn, bmn) \
-    if (BN == bn && (bool)a_mn_major == amn && (bool)b_mn_major == bmn) return launch_gemm<bn, amn ? 1 : 0, bmn ? 1 : 0>(ta, tb, ep, cv, M, N, K, split_k, stream);
-    DMLB_GEMM_CASE(32, false, false)
-    DMLB_GEMM_CASE(64, false, false)
-    DMLB_GEMM_CASE(128, false, false)
-    DMLB_GEMM_CASE(256, false, false)
-    DMLB_GEMM_CASE(64, false, true)
-    DMLB_GEMM_CASE(128, false, true)
-    DMLB_GEMM_CASE(64, true, true)
-    DMLB_GEMM_CASE(128, true, true)
-#undef DMLB_GEMM_CASE
-    dmlb_set_error("dmlb_gemm_bf16: no kernel instantiated for this (tile_n, major) combination");
-    return -4;
-}
-
-
-// Implicit-GEMM convolution (no column matrix in memory): the activation operand is gathered by TMA in im2col mode.
-//   kind 0  fprop : out[B*Ho*Wo, Cout] = conv(x, W)           act = x [B,Ha,Wa,Ca=Cin],   other = W shadow [Cout, kh*kw*Cin]
-//   kind 1  wgrad : out[Cout, kh*kw*Cin] (+)= dY^T * im2col(x) act = x,                     other = dY [B*Ho*Wo, ld_other]
-//   kind 2  dgrad : out[B*Ha'*Wa', Cin]  = conv^T(dY, W)      act = dY [B,Ha,Wa,Ca=Cout],  other = W shadow; stride 1 only;
-//                   n_out = Cin;  (Ha, Wa) are the conv OUTPUT extents, the result has the conv INPUT extents.
-// Needs Ca % 64 == 0 (a 64-wide k-block must stay inside one filter tap); for dgrad also n_out % 8 == 0.
-// Epilogue arguments as in dmlb_gemm_bf16.  Reference: nn.Conv2d forward/backward in example/models.py:29-39 (cuDNN there).
-static int conv_implicit_impl(const FinishArgs* fin, int kind, const void* act, int ld_act, int B, int Ha, int Wa, int Ca, const void* other, int ld_other,
-                                       int KH, int KW, int SH, int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo,
-                                       const float* bias, int relu, int split_k, int atomic, int tile_n, void* stream_) {
-    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    DMLB_REQUIRE(kind >= 0 && kind <= 2, "kind must be 0 (fprop), 1 (wgrad) or 2 (dgrad)");
-    DMLB_REQUIRE(Ca % 64 == 0, "implicit-GEMM convolution needs a multiple of 64 channels in the gathered tensor");
-    if (split_k < 1) split_k = 1;
-    if (split_k > 1) atomic = 1;
-    DMLB_REQUIRE(!atomic || out_is_f32, "atomic / split-K output must be fp32");
-    DMLB_REQUIRE(!(atomic && relu), "ReLU cannot be fused into an accumulating epilogue");
-    GemmEpilogue ep = {};
-    ep.out = out; ep.bias = bias; ep.ldo = ldo; ep.out_is_f32 = out_is_f32; ep.relu = relu; ep.atomic = atomic; ep.perm_cin = 0; ep.perm_khw = 0;
-    ConvK cv = {};
-    cv.C = Ca; cv.KH = KH; cv.KW = KW; cv.sh = SH; cv.sw = SW;
-    CUtensorMap ta, tb;
-    int rc;
-    if (kind == 0 || kind == 1) {
-        const int Ho = (Ha + 2 * PH - KH) / SH + 1, Wo = (Wa + 2 * PW - KW) / SW + 1;
-        DMLB_REQUIRE(Ho > 0 && Wo > 0, "empty conv output");
-        cv.P = Ho; cv.Q = Wo; cv.low_h = -PH; cv.low_w = -PW; cv.flip = 0;
-        const int Kd = KH * KW * Ca;
-        const long long Mpix = 1ll * B * Ho * Wo;
-        DMLB_REQUIRE(Mpix < (1ll << 31), "too many output pixels");
-        if (kind == 0) {
-            const int N = n_out;
-            int BN = tile_n ? tile_n : ((N > 64) ? 128 : (N > 32 ? 64 : 32));
-            rc = make_tmap_im2col(&ta, act, Ca, Wa, Ha, B, ld_act, -PW, -PH, PW - (KW - 1), PH - (KH - 1), SW, SH, kBM);
-            if (rc) return rc;
-            rc = make_tmap_bf16(&tb, other, (uint64_t)Kd, (uint64_t)N, (uint64_t)ld_other, kBK, (uint32_t)BN);
-            if (rc) return rc;
-            if (fin != nullptr && (rc = apply_finish(ep, *fin, (int)Mpix, N, BN)) != 0) return rc;
-            if (BN == 32) return launch_gemm<32, 2, 0>(ta, tb, ep, cv, (int)Mpix, N, Kd, split_k, stream);
-            if (BN == 64) return launch_gemm<64, 2, 0>(ta, tb, ep, cv, (int)Mpix, N, Kd, split_k, stream);
-            if (BN == 128) return launch_gemm<128, 2, 0>(ta, tb, ep, cv, (int)Mpix, N, Kd, split_k, stream);
-            if (BN == 256) return launch_gemm<256, 2, 0>(ta, tb, ep, cv, (int)Mpix, N, Kd, split_k, stream);
-        } else {
-            const int Cout = n_out;
-            int BN = tile_n ? tile_n : 128;
-            DMLB_REQUIRE(fin == nullptr, "weight gradients accumulate into the arena; there is nothing to finish");
-            rc = make_tmap_bf16(&ta, other, (uint64_t)Cout, (uint64_t)Mpix, (uint64_t)ld_other, 64, kBK);   // dY as MN-major A
-            if (rc) return rc;
-            rc = make_tmap_im2col(&tb, act, Ca, Wa, Ha, B, ld_act, -PW, -PH, PW - (KW - 1), PH - (KH - 1), SW, SH, kBK);
-            if (rc) return rc;
-            if (BN == 64) return launch_gemm<64, 1, 2>(ta, tb, ep, cv, Cout, Kd, (int)Mpix, split_k, stream);
-            if (BN == 128) return launch_gemm<128, 1, 2>(ta, tb, ep, cv, Cout, Kd, (int)Mpix, split_k, stream);
-        }
-    } else {
-        DMLB_REQUIRE(SH == 1 && SW == 1, "implicit dgrad supports stride 1 (strided convolutions use the explicit path)");
-        const int Cin = n_out, Cout = Ca;
-        DMLB_REQUIRE(Cin % 8 == 0, "implicit dgrad needs Cin % 8 == 0");
-        const int Hin = Ha + KH - 1 - 2 * PH, Win = Wa + KW - 1 - 2 * PW;     // conv input extents (stride 1)
-        DMLB_REQUIRE(Hin > 0 && Win > 0, "bad dgrad geometry");
-        cv.P = Hin; cv.Q = Win; cv.low_h = -(KH - 1 - PH); cv.low_w = -(KW - 1 - PW); cv.flip = 1;
-        const int Kd = KH * KW * Cout;
-        const long long Mpix = 1ll * B * Hin * Win;
-        DMLB_REQUIRE(Mpix < (1ll << 31), "too many pixels");
-        int BN = tile_n ? tile_n : (Cin > 64 ? 128 : 64);
-        rc = make_tmap_im2col(&ta, act, Cout, Wa, Ha, B, ld_act, cv.low_w, cv.low_h, -PW, -PH, 1, 1, kBM);
-        if (rc) return rc;
-        rc = make_tmap_w3d(&tb, other, Cin, KH * KW, Cout, ld_other);
-        if (rc) return rc;
-        if (fin != nullptr && (rc = apply_finish(ep, *fin, (int)Mpix, Cin, BN)) != 0) return rc;
-        if (BN == 64) return launch_gemm<64, 2, 3>(ta, tb, ep, cv, (int)Mpix, Cin, Kd, split_k, stream);
-        if (BN == 128) return launch_gemm<128, 2, 3>(ta, tb, ep, cv, (int)Mpix, Cin, Kd, split_k, stream);
-    }
-    dmlb_set_error("dmlb_conv_implicit_bf16: unsupported tile_n for this kind");
-    return -4;
-}
-
-
 extern "C" int dmlb_gemm_bf16(const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major, int M, int N, int K, void* out,
                               int out_is_f32, int ldo, const float* bias, int relu, int split_k, int atomic, int perm_cin, int perm_khw,
                               int tile_n, void* stream) {
-    return gemm_bf16_impl(nullptr, A, lda, a_mn_major, B, ldb, b_mn_major, M, N, K, out, out_is_f32, ldo, bias, relu, split_k, atomic, perm_cin,
-                          perm_khw, tile_n, stream);
+    return gemm_impl<ElemBF16>(nullptr, A, lda, a_mn_major, B, ldb, b_mn_major, M, N, K, out, out_is_f32, ldo, bias, relu, split_k, atomic,
+                               perm_cin, perm_khw, tile_n, stream);
 }
 
 extern "C" int dmlb_conv_implicit_bf16(int kind, const void* act, int ld_act, int B, int Ha, int Wa, int Ca, const void* other, int ld_other,
                                        int KH, int KW, int SH, int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo,
                                        const float* bias, int relu, int split_k, int atomic, int tile_n, void* stream) {
-    return conv_implicit_impl(nullptr, kind, act, ld_act, B, Ha, Wa, Ca, other, ld_other, KH, KW, SH, SW, PH, PW, n_out, out, out_is_f32, ldo, bias,
-                              relu, split_k, atomic, tile_n, stream);
+    return conv_implicit_impl<ElemBF16>(nullptr, kind, act, ld_act, B, Ha, Wa, Ca, other, ld_other, KH, KW, SH, SW, PH, PW, n_out, out, out_is_f32,
+                                        ldo, bias, relu, split_k, atomic, tile_n, stream);
 }
 
 // Split-K GEMM / implicit convolution with the finishing pass folded into the GEMM kernel (one launch instead of two):
@@ -1261,7 +28,7 @@ extern "C" int dmlb_gemm_bf16_fin(const void* A, int lda, int a_mn_major, const 
                                   int ldw, int* counters, int n_counters, const float* bias, int relu, void* y, int ldy, int pool_h, int pool_w,
                                   void* pooled, int ldp, int split_k, int tile_n, void* stream) {
     const FinishArgs fin = {counters, n_counters, bias, relu, y, ldy, pool_h, pool_w, pooled, ldp};
-    return gemm_bf16_impl(&fin, A, lda, a_mn_major, B, ldb, b_mn_major, M, N, K, ws, 1, ldw, nullptr, 0, split_k, 1, 0, 0, tile_n, stream);
+    return gemm_impl<ElemBF16>(&fin, A, lda, a_mn_major, B, ldb, b_mn_major, M, N, K, ws, 1, ldw, nullptr, 0, split_k, 1, 0, 0, tile_n, stream);
 }
 
 extern "C" int dmlb_conv_implicit_fin(int kind, const void* act, int ld_act, int B, int Ha, int Wa, int Ca, const void* other, int ld_other, int KH,
@@ -1269,6 +36,6 @@ extern "C" int dmlb_conv_implicit_fin(int kind, const void* act, int ld_act, int
                                       const float* bias, int relu, void* y, int ldy, int pool_h, int pool_w, void* pooled, int ldp, int split_k,
                                       int tile_n, void* stream) {
     const FinishArgs fin = {counters, n_counters, bias, relu, y, ldy, pool_h, pool_w, pooled, ldp};
-    return conv_implicit_impl(&fin, kind, act, ld_act, B, Ha, Wa, Ca, other, ld_other, KH, KW, SH, SW, PH, PW, n_out, ws, 1, ldw, nullptr, 0, split_k,
-                              1, tile_n, stream);
+    return conv_implicit_impl<ElemBF16>(&fin, kind, act, ld_act, B, Ha, Wa, Ca, other, ld_other, KH, KW, SH, SW, PH, PW, n_out, ws, 1, ldw, nullptr,
+                                        0, split_k, 1, tile_n, stream);
 }

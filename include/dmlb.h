@@ -50,6 +50,16 @@ int dmlb_gemm_bf16(const void* A, int lda, int a_mn_major, const void* B, int ld
                    void* out, int out_is_f32, int ldo, const float* bias, int relu, int split_k, int atomic, int perm_cin,
                    int perm_khw, int tile_n, void* stream);
 
+/* The same GEMM on fp32 tensors read by the tensor cores as tf32 (tcgen05 kind::tf32), fp32 accumulation, fp32 output: the precision
+ * the reference trains at (fp32 tensors, cuDNN TF32 convolutions — example/main.py:41,53-54,70-73).  Pitches in elements, multiples of 4.
+ * tile_n: 0 = auto, else 32 / 64 / 128. */
+int dmlb_gemm_tf32(const void* A, int lda, int a_mn_major, const void* B, int ldb, int b_mn_major, int M, int N, int K, void* out, int ldo,
+                   const float* bias, int relu, int split_k, int atomic, int perm_cin, int perm_khw, int tile_n, void* stream);
+/* dmlb_conv_implicit_bf16 on fp32 channels-last tensors (tf32 math): the gathered tensor needs Ca % 32 == 0. */
+int dmlb_conv_implicit_tf32(int kind, const void* act, int ld_act, int B, int Ha, int Wa, int Ca, const void* other, int ld_other, int KH, int KW,
+                            int SH, int SW, int PH, int PW, int n_out, void* out, int ldo, const float* bias, int relu, int split_k,
+                            int atomic, int tile_n, void* stream);
+
 /* Implicit-GEMM convolution: the activation operand is gathered by TMA in im2col mode, no column matrix exists in memory.
  * kind 0 fprop (act = x, other = W shadow [n_out=Cout, kh*kw*Cin]), 1 wgrad (act = x, other = dY, out [n_out=Cout, kh*kw*Cin], fp32 accumulate),
  * 2 dgrad (act = dY with Ca = Cout, other = W shadow, n_out = Cin, stride 1 only).  The gathered tensor needs Ca % 64 == 0.
