@@ -46,6 +46,49 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t v) {
     return __bfloat1622float2(h);
 }
 
+// Element-type helpers of the activation kernels: T = __nv_bfloat16 (bf16 path) or float (tf32 path, fp32 activations).
+template <typename T>
+__device__ __forceinline__ float to_f32(T v);
+template <>
+__device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <typename T>
+__device__ __forceinline__ T from_f32(float v);
+template <>
+__device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+// One 16-byte vector of T as floats: 8 bf16 or 4 fp32 (the channel granule of every vectorised activation kernel).
+template <typename T>
+struct Vec16;
+template <>
+struct Vec16<__nv_bfloat16> {
+    static constexpr int N = 8;
+    static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&f)[8]) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+        const float2 a = unpack_bf16x2(v.x), b = unpack_bf16x2(v.y), c = unpack_bf16x2(v.z), d = unpack_bf16x2(v.w);
+        f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+    }
+    static __device__ __forceinline__ void store(__nv_bfloat16* p, const float (&f)[8]) {
+        uint4 o;
+        o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]); o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+        *reinterpret_cast<uint4*>(p) = o;
+    }
+};
+template <>
+struct Vec16<float> {
+    static constexpr int N = 4;
+    static __device__ __forceinline__ void load(const float* p, float (&f)[4]) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(p));
+        f[0] = v.x; f[1] = v.y; f[2] = v.z; f[3] = v.w;
+    }
+    static __device__ __forceinline__ void store(float* p, const float (&f)[4]) {
+        *reinterpret_cast<float4*>(p) = make_float4(f[0], f[1], f[2], f[3]);
+    }
+};
+
 // ----------------------------------------------------------------------------------------------
 // programmatic dependent launch (PDL): a kernel may be launched while its predecessor in the stream is still
 // running; everything before pdl_wait() (barrier init, TMEM allocation, descriptor prefetch, index math) overlaps

@@ -15,9 +15,10 @@ extern "C" int dmlb_gemm_bf16(const void* A, int lda, int a_mn_major, const void
 
 namespace dmlb {
 
-// ws [M, ldw] fp32 -> y [M, ldy] bf16 = act(ws + bias); ws <- 0.   N % 4 == 0 fast path, scalar otherwise.
+// ws [M, ldw] fp32 -> y [M, ldy] (bf16 or fp32) = act(ws + bias); ws <- 0.   N % 4 == 0 fast path, scalar otherwise.
+template <typename T>
 __global__ void __launch_bounds__(256) splitk_finish_kernel(float* __restrict__ ws, int ldw, const float* __restrict__ bias, int relu,
-                                                            __nv_bfloat16* __restrict__ y, int ldy, long long M, int N) {
+                                                            T* __restrict__ y, int ldy, long long M, int N) {
     pdl_prologue();
     const int n4 = (N + 3) / 4;
     const long long total = M * n4;
@@ -33,7 +34,7 @@ __global__ void __launch_bounds__(256) splitk_finish_kernel(float* __restrict__ 
             if (c + j < N) {
                 float x = f[j] + (bias != nullptr ? __ldg(bias + c + j) : 0.f);
                 if (relu) x = fmaxf(x, 0.f);
-                y[m * ldy + c + j] = __float2bfloat16_rn(x);
+                y[m * ldy + c + j] = from_f32<T>(x);
             }
         }
     }
@@ -41,9 +42,10 @@ __global__ void __launch_bounds__(256) splitk_finish_kernel(float* __restrict__ 
 
 // Same, plus the 2x2 stride-2 max-pool of the activation: one thread per pooled pixel and 4 channels.
 //   ws rows are NHWC pixels of a [B, H, W] map (H, W even); pooled is [B, H/2, W/2, ldp].
+template <typename T>
 __global__ void __launch_bounds__(256) splitk_finish_pool2_kernel(float* __restrict__ ws, int ldw, const float* __restrict__ bias, int relu,
-                                                                  __nv_bfloat16* __restrict__ y, int ldy, __nv_bfloat16* __restrict__ pooled,
-                                                                  int ldp, int B, int H, int W, int N) {
+                                                                  T* __restrict__ y, int ldy, T* __restrict__ pooled, int ldp, int B, int H,
+                                                                  int W, int N) {
     pdl_prologue();
     const int n4 = (N + 3) / 4;
     const int Hp = H / 2, Wp = W / 2;
@@ -72,16 +74,16 @@ __global__ void __launch_bounds__(256) splitk_finish_pool2_kernel(float* __restr
                     if (c + j < N) {
                         float x = f[j] + bb[j];
                         if (relu) x = fmaxf(x, 0.f);
-                        const __nv_bfloat16 h = __float2bfloat16_rn(x);
+                        const T h = from_f32<T>(x);
                         y[m * ldy + c + j] = h;
-                        mx[j] = fmaxf(mx[j], __bfloat162float(h));
+                        mx[j] = fmaxf(mx[j], to_f32<T>(h));
                     }
                 }
             }
         const long long mp = (1ll * b * Hp + hp) * Wp + wp;
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-            if (c + j < N) pooled[mp * ldp + c + j] = __float2bfloat16_rn(mx[j]);
+            if (c + j < N) pooled[mp * ldp + c + j] = from_f32<T>(mx[j]);
     }
 }
 
@@ -99,22 +101,33 @@ using namespace dmlb;
 
 // ws: fp32 [M, ldw], all zeros on entry and again on exit.  pool2 = 1 additionally writes the 2x2/2 max-pool of y
 // (rows of y are the NHWC pixels of a [B, H, W] map with B*H*W == M) into pooled [B, H/2, W/2, ldp].
-extern "C" int dmlb_splitk_finish(float* ws, int ldw, const float* bias, int relu, void* y, int ldy, long long M, int N, int pool2, int B,
-                                  int H, int W, void* pooled, int ldp, void* stream) {
+template <typename T>
+static int splitk_finish_t(float* ws, int ldw, const float* bias, int relu, void* y, int ldy, long long M, int N, int pool2, int B, int H, int W,
+                           void* pooled, int ldp, void* stream) {
     DMLB_REQUIRE(ldw % 4 == 0 && ldw >= N, "workspace pitch must be a multiple of 4 and cover N");
     DMLB_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 15) == 0, "workspace must be 16-byte aligned");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (pool2) {
         DMLB_REQUIRE(1ll * B * H * W == M && H % 2 == 0 && W % 2 == 0, "pooled finish needs an even [B,H,W] map with B*H*W == M");
         const long long total = 1ll * B * (H / 2) * (W / 2) * ((N + 3) / 4);
-        DMLB_CHECK_CUDA(launch_k(splitk_finish_pool2_kernel, finish_grid(total), 256, 0, st, ws, ldw, bias, relu, static_cast<__nv_bfloat16*>(y), ldy,
-                                                                       static_cast<__nv_bfloat16*>(pooled), ldp, B, H, W, N));
+        DMLB_CHECK_CUDA(launch_k(splitk_finish_pool2_kernel<T>, finish_grid(total), 256, 0, st, ws, ldw, bias, relu, static_cast<T*>(y), ldy,
+                                 static_cast<T*>(pooled), ldp, B, H, W, N));
     } else {
         const long long total = M * ((N + 3) / 4);
-        DMLB_CHECK_CUDA(launch_k(splitk_finish_kernel, finish_grid(total), 256, 0, st, ws, ldw, bias, relu, static_cast<__nv_bfloat16*>(y), ldy, M, N));
+        DMLB_CHECK_CUDA(launch_k(splitk_finish_kernel<T>, finish_grid(total), 256, 0, st, ws, ldw, bias, relu, static_cast<T*>(y), ldy, M, N));
     }
     DMLB_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int dmlb_splitk_finish(float* ws, int ldw, const float* bias, int relu, void* y, int ldy, long long M, int N, int pool2, int B,
+                                  int H, int W, void* pooled, int ldp, void* stream) {
+    return splitk_finish_t<__nv_bfloat16>(ws, ldw, bias, relu, y, ldy, M, N, pool2, B, H, W, pooled, ldp, stream);
+}
+// fp32 outputs (tf32 path)
+extern "C" int dmlb_splitk_finish_f32(float* ws, int ldw, const float* bias, int relu, void* y, int ldy, long long M, int N, int pool2, int B,
+                                      int H, int W, void* pooled, int ldp, void* stream) {
+    return splitk_finish_t<float>(ws, ldw, bias, relu, y, ldy, M, N, pool2, B, H, W, pooled, ldp, stream);
 }
 
 // y[M,N] (bf16, pitch ldy) = act(A[M,K] * W[N,K]^T + bias) with K split `split_k` ways.

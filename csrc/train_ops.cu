@@ -17,19 +17,6 @@ namespace dmlb {
 //   dlogits: same dtype as logits, [B, ldd] <- (softmax - onehot) / B   (may be null: evaluation)
 // ---------------------------------------------------------------------------------------------
 template <typename T>
-__device__ __forceinline__ float to_f32(T v);
-template <>
-__device__ __forceinline__ float to_f32<float>(float v) { return v; }
-template <>
-__device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
-template <typename T>
-__device__ __forceinline__ T from_f32(float v);
-template <>
-__device__ __forceinline__ float from_f32<float>(float v) { return v; }
-template <>
-__device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
-
-template <typename T>
 __global__ void __launch_bounds__(1024) softmax_xent_kernel(const T* __restrict__ logits, const long long* __restrict__ labels,
                                                             float* __restrict__ metrics, T* __restrict__ dlogits, int B, int C,
                                                             int ldl, int ldd) {
@@ -82,15 +69,15 @@ __global__ void __launch_bounds__(1024) softmax_xent_kernel(const T* __restrict_
 }
 
 // x[r, c] *= *scale  (bf16, padded rows) — applies an upstream scalar gradient to the saved dlogits.
-__global__ void __launch_bounds__(256) scale_rows_kernel(__nv_bfloat16* __restrict__ x, const float* __restrict__ scale, long long rows, int C,
-                                                         int ld) {
+template <typename T>
+__global__ void __launch_bounds__(256) scale_rows_kernel(T* __restrict__ x, const float* __restrict__ scale, long long rows, int C, int ld) {
     pdl_prologue();
     const float s = *scale;
     const long long total = rows * C;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
         const long long r = i / C;
         const int c = static_cast<int>(i % C);
-        x[r * ld + c] = __float2bfloat16_rn(__bfloat162float(x[r * ld + c]) * s);
+        x[r * ld + c] = from_f32<T>(to_f32<T>(x[r * ld + c]) * s);
     }
 }
 
@@ -144,21 +131,22 @@ struct ShadowEntry {
     int rows, cin, khw, ld;
 };
 
-__global__ void __launch_bounds__(256) refresh_shadows_kernel(const float* __restrict__ params, __nv_bfloat16* __restrict__ shadow,
+template <typename T>
+__global__ void __launch_bounds__(256) refresh_shadows_kernel(const float* __restrict__ params, T* __restrict__ shadow,
                                                               const ShadowEntry* __restrict__ table) {
     pdl_prologue();
     const ShadowEntry e = table[blockIdx.y];
     const int K = e.cin * e.khw;
     const long long total = 1ll * e.rows * K;
     const float* src = params + e.src_off;
-    __nv_bfloat16* dst = shadow + e.dst_off;
+    T* dst = shadow + e.dst_off;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
         // iterate in destination order so the bf16 stores coalesce; sources are gathered (L2-resident)
         const int r = static_cast<int>(i / K);
         const int k = static_cast<int>(i % K);
         const int ci = k % e.cin;
         const int kk = k / e.cin;
-        dst[1ll * r * e.ld + k] = __float2bfloat16_rn(__ldg(src + (1ll * r * e.cin + ci) * e.khw + kk));
+        dst[1ll * r * e.ld + k] = from_f32<T>(__ldg(src + (1ll * r * e.cin + ci) * e.khw + kk));
     }
 }
 
@@ -199,7 +187,8 @@ __device__ __forceinline__ uint32_t mix32(uint64_t z) {  // splitmix64 finaliser
     return static_cast<uint32_t>(z >> 32);
 }
 
-__global__ void __launch_bounds__(256) dropout_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+template <typename T>
+__global__ void __launch_bounds__(256) dropout_fwd_kernel(const T* __restrict__ x, T* __restrict__ y,
                                                           uint8_t* __restrict__ mask, long long rows, int C, int ldx, int ldy,
                                                           int rows_per_sample, int channel_mode, float p, uint64_t seed,
                                                           const unsigned long long* __restrict__ step) {
@@ -215,18 +204,19 @@ __global__ void __launch_bounds__(256) dropout_fwd_kernel(const __nv_bfloat16* _
         const uint32_t rnd = mix32(seed ^ (st * 0xD1B54A32D192ED03ull) ^ (unit * 0x9E3779B97F4A7C15ull + 0x632BE59BD9B4E019ull));
         const bool keep = rnd >= thresh;
         mask[i] = keep ? 1 : 0;
-        y[r * ldy + c] = keep ? __float2bfloat16_rn(__bfloat162float(x[r * ldx + c]) * scale) : __float2bfloat16(0.f);
+        y[r * ldy + c] = keep ? from_f32<T>(to_f32<T>(x[r * ldx + c]) * scale) : from_f32<T>(0.f);
     }
 }
-__global__ void __launch_bounds__(256) dropout_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restrict__ mask,
-                                                          __nv_bfloat16* __restrict__ dx, long long rows, int C, int lddy, int lddx, float p) {
+template <typename T>
+__global__ void __launch_bounds__(256) dropout_bwd_kernel(const T* __restrict__ dy, const uint8_t* __restrict__ mask,
+                                                          T* __restrict__ dx, long long rows, int C, int lddy, int lddx, float p) {
     pdl_prologue();
     const float scale = 1.f / (1.f - p);
     const long long total = rows * C;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
         const long long r = i / C;
         const int c = static_cast<int>(i % C);
-        dx[r * lddx + c] = mask[i] ? __float2bfloat16_rn(__bfloat162float(dy[r * lddy + c]) * scale) : __float2bfloat16(0.f);
+        dx[r * lddx + c] = mask[i] ? from_f32<T>(to_f32<T>(dy[r * lddy + c]) * scale) : from_f32<T>(0.f);
     }
 }
 __global__ void counter_bump_kernel(unsigned long long* c) { *c += 1ull; }
@@ -259,7 +249,12 @@ extern "C" int dmlb_softmax_xent(const void* logits, int logits_is_bf16, const l
 }
 
 extern "C" int dmlb_scale_rows_bf16(void* x, const float* scale, long long rows, int C, int ld, void* stream) {
-    DMLB_CHECK_CUDA(launch_k(scale_rows_kernel, flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream), static_cast<__nv_bfloat16*>(x), scale, rows, C, ld));
+    DMLB_CHECK_CUDA(launch_k(scale_rows_kernel<__nv_bfloat16>, flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream), static_cast<__nv_bfloat16*>(x), scale, rows, C, ld));
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int dmlb_scale_rows_f32(void* x, const float* scale, long long rows, int C, int ld, void* stream) {
+    DMLB_CHECK_CUDA(launch_k(scale_rows_kernel<float>, flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream), static_cast<float*>(x), scale, rows, C, ld));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
@@ -278,8 +273,18 @@ extern "C" int dmlb_sgd_flat(float* params, float* grads, float* acc, float* mom
 extern "C" int dmlb_refresh_shadows(const float* params, void* shadow, const void* table, int n_entries, void* stream) {
     if (n_entries <= 0) return 0;
     dim3 grid(96, n_entries);
-    DMLB_CHECK_CUDA(launch_k(refresh_shadows_kernel, grid, 256, 0, static_cast<cudaStream_t>(stream), params, static_cast<__nv_bfloat16*>(shadow),
+    DMLB_CHECK_CUDA(launch_k(refresh_shadows_kernel<__nv_bfloat16>, grid, 256, 0, static_cast<cudaStream_t>(stream), params, static_cast<__nv_bfloat16*>(shadow),
                                                                                static_cast<const ShadowEntry*>(table)));
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+// fp32 GEMM-layout copies (tf32 path): only weights whose arena storage is not already a legal TMA operand need one
+// (row length not a multiple of 4, PyTorch (cin,kh,kw) order, in_map linears); dst_off counts fp32 elements.
+extern "C" int dmlb_refresh_shadows_f32(const float* params, void* shadow, const void* table, int n_entries, void* stream) {
+    if (n_entries <= 0) return 0;
+    dim3 grid(96, n_entries);
+    DMLB_CHECK_CUDA(launch_k(refresh_shadows_kernel<float>, grid, 256, 0, static_cast<cudaStream_t>(stream), params, static_cast<float*>(shadow),
+                             static_cast<const ShadowEntry*>(table)));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
@@ -295,20 +300,36 @@ extern "C" int dmlb_cast_bf16_f32(const void* x, float* y, long long rows, int C
     return 0;
 }
 
-extern "C" int dmlb_dropout_fwd_bf16(const void* x, void* y, void* mask, long long rows, int C, int ldx, int ldy, int rows_per_sample,
-                                     int channel_mode, float p, unsigned long long seed, const void* step, void* stream) {
+template <typename T>
+static int dropout_fwd_t(const void* x, void* y, void* mask, long long rows, int C, int ldx, int ldy, int rows_per_sample, int channel_mode, float p,
+                         unsigned long long seed, const void* step, void* stream) {
     DMLB_REQUIRE(p >= 0.f && p < 1.f, "dropout probability must be in [0, 1)");
-    DMLB_CHECK_CUDA(launch_k(dropout_fwd_kernel, flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream), 
-        static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), static_cast<uint8_t*>(mask), rows, C, ldx, ldy, rows_per_sample,
-        channel_mode, p, seed, static_cast<const unsigned long long*>(step)));
+    DMLB_CHECK_CUDA(launch_k(dropout_fwd_kernel<T>, flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream), static_cast<const T*>(x),
+                             static_cast<T*>(y), static_cast<uint8_t*>(mask), rows, C, ldx, ldy, rows_per_sample, channel_mode, p, seed,
+                             static_cast<const unsigned long long*>(step)));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
-extern "C" int dmlb_dropout_bwd_bf16(const void* dy, const void* mask, void* dx, long long rows, int C, int lddy, int lddx, float p, void* stream) {
-    DMLB_CHECK_CUDA(launch_k(dropout_bwd_kernel, flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream), 
-        static_cast<const __nv_bfloat16*>(dy), static_cast<const uint8_t*>(mask), static_cast<__nv_bfloat16*>(dx), rows, C, lddy, lddx, p));
+template <typename T>
+static int dropout_bwd_t(const void* dy, const void* mask, void* dx, long long rows, int C, int lddy, int lddx, float p, void* stream) {
+    DMLB_CHECK_CUDA(launch_k(dropout_bwd_kernel<T>, flat_grid(rows * C), 256, 0, static_cast<cudaStream_t>(stream), static_cast<const T*>(dy),
+                             static_cast<const uint8_t*>(mask), static_cast<T*>(dx), rows, C, lddy, lddx, p));
     DMLB_LAUNCH_CHECK();
     return 0;
+}
+extern "C" int dmlb_dropout_fwd_bf16(const void* x, void* y, void* mask, long long rows, int C, int ldx, int ldy, int rows_per_sample,
+                                     int channel_mode, float p, unsigned long long seed, const void* step, void* stream) {
+    return dropout_fwd_t<__nv_bfloat16>(x, y, mask, rows, C, ldx, ldy, rows_per_sample, channel_mode, p, seed, step, stream);
+}
+extern "C" int dmlb_dropout_fwd_f32(const void* x, void* y, void* mask, long long rows, int C, int ldx, int ldy, int rows_per_sample,
+                                    int channel_mode, float p, unsigned long long seed, const void* step, void* stream) {
+    return dropout_fwd_t<float>(x, y, mask, rows, C, ldx, ldy, rows_per_sample, channel_mode, p, seed, step, stream);
+}
+extern "C" int dmlb_dropout_bwd_bf16(const void* dy, const void* mask, void* dx, long long rows, int C, int lddy, int lddx, float p, void* stream) {
+    return dropout_bwd_t<__nv_bfloat16>(dy, mask, dx, rows, C, lddy, lddx, p, stream);
+}
+extern "C" int dmlb_dropout_bwd_f32(const void* dy, const void* mask, void* dx, long long rows, int C, int lddy, int lddx, float p, void* stream) {
+    return dropout_bwd_t<float>(dy, mask, dx, rows, C, lddy, lddx, p, stream);
 }
 extern "C" int dmlb_counter_bump(void* counter, void* stream) {
     DMLB_CHECK_CUDA(launch_k(counter_bump_kernel, 1, 1, 0, static_cast<cudaStream_t>(stream), static_cast<unsigned long long*>(counter)));

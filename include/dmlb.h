@@ -72,6 +72,8 @@ int dmlb_conv_implicit_bf16(int kind, const void* act, int ld_act, int B, int Ha
  * example/main.py:142).  ws is fp32 scratch [M, round_up(N,4)], all zeros on entry and zeroed again by the finish. */
 int dmlb_splitk_finish(float* ws, int ldw, const float* bias, int relu, void* y, int ldy, long long M, int N, int pool2, int B, int H, int W,
                        void* pooled, int ldp, void* stream);
+int dmlb_splitk_finish_f32(float* ws, int ldw, const float* bias, int relu, void* y, int ldy, long long M, int N, int pool2, int B, int H, int W,
+                           void* pooled, int ldp, void* stream);   /* fp32 y / pooled (tf32 path) */
 int dmlb_gemm_bias_act_splitk(const void* A, int lda, const void* Wt, int ldb, int M, int N, int K, float* ws, const float* bias, int relu,
                               void* y, int ldy, int split_k, void* stream);
 
@@ -108,12 +110,26 @@ int dmlb_act_bwd_bf16(const void* y, const void* dout, void* dy, float* dbias, i
                       int k, int s, int p, int relu, void* stream);
 int dmlb_relu_fwd_bf16(const void* x, void* y, long long rows, int C, int ldx, int ldy, void* stream);
 int dmlb_relu_bwd_bf16(const void* y, const void* dy, void* dx, long long rows, int C, int ldy, int lddy, int lddx, void* stream);
+/* The same kernels on fp32 channels-last activations [B,H,W,ld] (ld % 4 == 0) for the tf32 path — the reference keeps fp32 activations
+ * (example/main.py:64-73).  dmlb_im2col_nchw_f32_f32 writes an fp32 column matrix. */
+int dmlb_im2col_nhwc_f32(const void* x, void* col, int B, int H, int W, int C, int ldx, int KH, int KW, int SH, int SW, int PH, int PW, int Kpad,
+                         void* stream);
+int dmlb_im2col_nchw_f32_f32(const float* x, void* col, int B, int H, int W, int C, int KH, int KW, int SH, int SW, int PH, int PW, int Kpad,
+                             void* stream);
+int dmlb_col2im_nhwc_f32(const void* dcol, void* dx, int B, int H, int W, int C, int ldx, int KH, int KW, int SH, int SW, int PH, int PW, int Kpad,
+                         void* stream);
+int dmlb_maxpool_fwd_f32(const void* x, void* y, int B, int H, int W, int C, int ldx, int ldo, int k, int s, int p, void* stream);
+int dmlb_act_bwd_f32(const void* y, const void* dout, void* dy, float* dbias, int B, int H, int W, int C, int ldy, int ldd, int has_pool, int k,
+                     int s, int p, int relu, void* stream);
+int dmlb_relu_fwd_f32(const void* x, void* y, long long rows, int C, int ldx, int ldy, void* stream);
+int dmlb_relu_bwd_f32(const void* y, const void* dy, void* dx, long long rows, int C, int ldy, int lddy, int lddx, void* stream);
 
 /* ---- loss / optimizer / dropout (reference: example/main.py:71,75; asgd/optim/Asynchronous.py:55,63-68) ---- */
 /* metrics[0] = mean loss, metrics[1] = #rows with argmax == label; dlogits (dtype of logits, [B,ldd], may be NULL) = (softmax-onehot)/B. */
 int dmlb_softmax_xent(const void* logits, int logits_is_bf16, const long long* labels, float* metrics, void* dlogits, int B, int C,
                       int ldl, int ldd, void* stream);
 int dmlb_scale_rows_bf16(void* x, const float* scale, long long rows, int C, int ld, void* stream);
+int dmlb_scale_rows_f32(void* x, const float* scale, long long rows, int C, int ld, void* stream);
 /* theta -= lr*g over the flat arena (n % 4 == 0); optional Downpour accumulator acc -= lr*g, momentum buffer,
  * weight decay, and a flat bf16 mirror of theta (same offsets) for the tensor-core GEMMs; zero_grads=1 clears the
  * gradients as they are consumed (replaces the next step's zero_grad memset). */
@@ -121,11 +137,15 @@ int dmlb_sgd_flat(float* params, float* grads, float* acc, float* mom, void* sha
                   float wd, int zero_grads, void* stream);
 /* table: device array of { int64 src_off, int64 dst_off, int32 rows, cin, khw, ld } — see csrc/train_ops.cu. */
 int dmlb_refresh_shadows(const float* params, void* shadow, const void* table, int n_entries, void* stream);
+int dmlb_refresh_shadows_f32(const float* params, void* shadow, const void* table, int n_entries, void* stream);   /* fp32 copies (tf32 path) */
 int dmlb_cast_f32_bf16(const float* x, void* y, long long rows, int C, long long ldx, int ldy, void* stream);
 int dmlb_cast_bf16_f32(const void* x, float* y, long long rows, int C, int ldx, long long ldy, void* stream);
 int dmlb_dropout_fwd_bf16(const void* x, void* y, void* mask, long long rows, int C, int ldx, int ldy, int rows_per_sample, int channel_mode,
                           float p, unsigned long long seed, const void* step, void* stream);
 int dmlb_dropout_bwd_bf16(const void* dy, const void* mask, void* dx, long long rows, int C, int lddy, int lddx, float p, void* stream);
+int dmlb_dropout_fwd_f32(const void* x, void* y, void* mask, long long rows, int C, int ldx, int ldy, int rows_per_sample, int channel_mode,
+                         float p, unsigned long long seed, const void* step, void* stream);
+int dmlb_dropout_bwd_f32(const void* dy, const void* mask, void* dx, long long rows, int C, int lddy, int lddx, float p, void* stream);
 int dmlb_counter_bump(void* counter, void* stream);
 
 /* ---- batch norm / residual / global average pool (NORTH-STAR ResNets; csrc/norm_ops.cu) ----
