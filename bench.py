@@ -50,6 +50,9 @@ def parse():
     ap.add_argument("--classes", type=int, default=10)
     ap.add_argument("--momentum", type=float, default=0.0)
     ap.add_argument("--staleness", default=None)
+    ap.add_argument("--dtype", choices=["tf32", "bf16"], default=None,
+                    help="CUDA compute dtype (default: tf32 for the reference's LeNet / AlexNet = the reference's own precision, bf16 for the ResNets)")
+    ap.add_argument("--no-second-dtype", action="store_true", help="skip the short extra measurement in the other compute dtype (1 GPU only)")
     a = ap.parse_args()
     a.pool_cap_bytes = 2 << 30      # host pool of distinct batches never exceeds 2 GiB
     return a
@@ -90,28 +93,19 @@ def barrier(world: int):
 # ------------------------------------------------------------------------------------------------
 # own arm
 # ------------------------------------------------------------------------------------------------
-def run_ours(args) -> dict:
+def _measure(args, dtype, rank, local_rank, world, device, steps, warmup, with_e2e=True) -> dict:
+    """Build model + optimizer + TrainStep in compute dtype ``dtype`` and time ``steps`` steps (device-timed, then end to end)."""
     import torch
-    import torch.distributed as dist
 
     from distributed_ml_pytorch_b200 import _native
     from distributed_ml_pytorch_b200.engine import TrainStep
     from distributed_ml_pytorch_b200.models import build_model
     from distributed_ml_pytorch_b200.utils.timing import ClockSampler
 
-    rank, local_rank, world = dist_env()
-    if world != args.gpus:
-        if args.gpus > 1 and world == 1:
-            raise SystemExit("launch multi-GPU runs with torch.distributed.run (see module docstring)")
-    torch.cuda.set_device(local_rank)
-    device = torch.device("cuda", local_rank)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
     torch.manual_seed(1234)  # identical initial replicas on every rank
     B = args.batch_size
     HW, NC = args.input_hw, args.classes
-    model = build_model(args.model, num_classes=NC, input_hw=HW).to(device)
+    model = build_model(args.model, num_classes=NC, input_hw=HW, dtype=dtype).to(device)
     model.train()
     optimizer, parallelism = make_optimizer(args, model, rank, world, device)
     ts = TrainStep(model, optimizer, B, (3, HW, HW), device=device, use_graph=not args.no_graph)
@@ -124,7 +118,7 @@ def run_ours(args) -> dict:
     hy = torch.randint(0, NC, (pool, B), dtype=torch.int64).pin_memory()
     dx, dy = hx.to(device), hy.to(device)
 
-    K_, W_ = args.steps, max(args.warmup, 3)
+    K_, W_ = steps, max(warmup, 3)
     for i in range(W_):
         ts(hx[i % pool], hy[i % pool])
     ts.flush()
@@ -133,6 +127,7 @@ def run_ours(args) -> dict:
     # ---- device-timed, device-resident inputs ----
     barrier(world)
     launches0 = _native.launch_count()
+    pushes0 = getattr(optimizer, "pushes", 0)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(ts.stream)
     for i in range(K_):
@@ -142,50 +137,99 @@ def run_ours(args) -> dict:
     barrier(world)
     dev_ms = max_over_ranks(e0.elapsed_time(e1), world, device)
     eager_launches = _native.launch_count() - launches0
-    # ---- end to end: pinned host -> H2D each step, loss read back each step ----
-    barrier(world)
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    f0.record(ts.stream)
-    seen = 0
-    loss_sum = 0.0
-    for i in range(K_):
-        r = ts(hx[i % pool], hy[i % pool])
+    timed_pushes = getattr(optimizer, "pushes", 0) - pushes0
+    res = {"dev_ms": dev_ms, "kernels_per_step": int(ts.kernels_per_step), "gpu_launches": int(ts.kernels_per_step * K_ + eager_launches),
+           "final_loss": (last.loss if last is not None else None), "parallelism": parallelism, "pool": pool, "bytes_per_batch": bytes_per_batch,
+           "cuda_graph": ts.graph is not None, "timed_push_intervals": int(timed_pushes), "steps": K_, "warmup": W_}
+    if with_e2e:
+        # ---- end to end: pinned host -> H2D each step, loss read back each step ----
+        barrier(world)
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record(ts.stream)
+        seen = 0
+        loss_sum = 0.0
+        for i in range(K_):
+            r = ts(hx[i % pool], hy[i % pool])
+            if r is not None:
+                loss_sum += r.loss
+                seen += 1
+        r = ts.flush()
         if r is not None:
             loss_sum += r.loss
             seen += 1
-    r = ts.flush()
-    if r is not None:
-        loss_sum += r.loss
-        seen += 1
-    f1.record(ts.stream)
-    f1.synchronize()
-    barrier(world)
-    e2e_ms = max_over_ranks(f0.elapsed_time(f1), world, device)
-    clocks = sampler.stop()
-
+        f1.record(ts.stream)
+        f1.synchronize()
+        barrier(world)
+        res["e2e_ms"] = max_over_ranks(f0.elapsed_time(f1), world, device)
+        res["mean_loss"] = loss_sum / seen if seen else None
+    res["clocks"] = sampler.stop()
     if hasattr(optimizer, "finish"):
         optimizer.finish()
+    del ts, optimizer, model, dx, dy, hx, hy
+    torch.cuda.empty_cache()
+    return res
+
+
+def run_ours(args) -> dict:
+    import torch
+    import torch.distributed as dist
+
+    from distributed_ml_pytorch_b200.models import default_dtype
+
+    rank, local_rank, world = dist_env()
+    if world != args.gpus:
+        if args.gpus > 1 and world == 1:
+            raise SystemExit("launch multi-GPU runs with torch.distributed.run (see module docstring)")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=device)
+    dtype = args.dtype or default_dtype(args.model)
+    B = args.batch_size
+    HW = args.input_hw
+    m = _measure(args, dtype, rank, local_rank, world, device, args.steps, args.warmup)
+    K_, W_ = m["steps"], m["warmup"]
+    dev_ms, e2e_ms, clocks = m["dev_ms"], m["e2e_ms"], m["clocks"]
     global_batch = B * world
     value = global_batch * K_ / (dev_ms / 1e3)
     e2e = global_batch * K_ / (e2e_ms / 1e3)
     pub = published_baseline()
+    async_mode = "async" in m["parallelism"]
     out = {
         "metric": "images/sec (device-timed, max over ranks)",
         "value": round(value, 1), "unit": "images/sec", "n_gpus": world, "steps": K_, "warmup": W_,
         "ms_per_step": round(dev_ms / K_, 5), "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": (round(value / pub, 3) if pub else None), "dtype": "bf16", "data": "synthetic",
+        "vs_baseline": (round(value / pub, 3) if pub else None), "dtype": dtype, "data": "synthetic",
         "impl": "ours",
         "config": {"model": args.model, "global_batch": global_batch, "per_gpu_batch": B, "input": f"3x{HW}x{HW}", "seq_len": None,
-                   "parallelism": parallelism, "lr": LR, "n_push": N_PUSH, "n_pull": N_PULL,
-                   "l2_policy": f"inputs rotate through a pool of {pool} distinct batches ({pool * bytes_per_batch >> 20} MiB > 126 MiB L2)",
-                   "cuda_graph": ts.graph is not None, "loss_readback": "every step, read one step late (pinned double buffer)"},
+                   "parallelism": m["parallelism"], "lr": LR, "n_push": N_PUSH, "n_pull": N_PULL,
+                   "precision": ("fp32 parameters / activations / gradients, tensor-core products in tf32 with fp32 accumulation "
+                                 "(the reference: fp32 tensors, cuDNN TF32 convolutions)" if dtype == "tf32" else
+                                 "fp32 master parameters and gradients, bf16 GEMM operands and activations, fp32 accumulation"),
+                   "l2_policy": f"inputs rotate through a pool of {m['pool']} distinct batches ({m['pool'] * m['bytes_per_batch'] >> 20} MiB > 126 MiB L2)",
+                   "cuda_graph": m["cuda_graph"], "loss_readback": "every step, read one step late (pinned double buffer)"},
         "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"), "reasons": clocks.get("reasons", [])},
-        "e2e": {"value": round(e2e, 1), "unit": "images/sec", "h2d_bytes_per_step": bytes_per_batch, "d2h_bytes_per_step": 8,
-                "ms_per_step": round(e2e_ms / K_, 5), "mean_loss": (loss_sum / seen if seen else None)},
-        "gpu_launches": int(ts.kernels_per_step * K_ + eager_launches),
-        "kernels_per_step": int(ts.kernels_per_step),
-        "final_loss": (last.loss if last is not None else None),
+        "e2e": {"value": round(e2e, 1), "unit": "images/sec", "h2d_bytes_per_step": m["bytes_per_batch"], "d2h_bytes_per_step": 8,
+                "ms_per_step": round(e2e_ms / K_, 5), "mean_loss": m["mean_loss"]},
+        "gpu_launches": m["gpu_launches"],
+        "kernels_per_step": m["kernels_per_step"],
+        "final_loss": m["final_loss"],
     }
+    if async_mode:
+        out["timed_push_intervals"] = m["timed_push_intervals"]
+        if m["timed_push_intervals"] < 3:
+            out["note"] = (f"the device-timed region of {K_} steps holds only {m['timed_push_intervals']} push/pull interval(s) (n_push = {N_PUSH}); "
+                           "run with --steps >= 30 for a value that averages over the communication cadence")
+    if world == 1 and not args.no_second_dtype and args.model in ("alexnet", "lenet"):
+        # context, not the headline: the same step in the other compute dtype (short, device-timed only)
+        other = "bf16" if dtype == "tf32" else "tf32"
+        try:
+            o = _measure(args, other, rank, local_rank, world, device, min(args.steps, 100), args.warmup, with_e2e=False)
+            out["other_dtype"] = {"dtype": other, "value": round(global_batch * o["steps"] / (o["dev_ms"] / 1e3), 1), "unit": "images/sec",
+                                  "ms_per_step": round(o["dev_ms"] / o["steps"], 5), "steps": o["steps"], "kernels_per_step": o["kernels_per_step"]}
+        except Exception as exc:  # the headline number must not depend on the context measurement
+            out["other_dtype"] = {"dtype": other, "error": f"{type(exc).__name__}: {exc}"[:200]}
     if world > 1:
         dist.destroy_process_group()
     return out if rank == 0 else {}

@@ -65,6 +65,25 @@ _SIGNATURES = {
     "dmlb_bn_bwd_apply": [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_ll, c_int, c_vp, c_vp],
     "dmlb_avgpool_fwd_bf16": [c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_vp],
     "dmlb_avgpool_bwd_bf16": [c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_vp],
+    # ---- tf32 path: fp32 tensors, tcgen05 kind::tf32 ----
+    # (A, lda, a_mn, B, ldb, b_mn, M, N, K, out, ldo, bias, relu, split_k, atomic, perm_cin, perm_khw, tile_n, stream)
+    "dmlb_gemm_tf32": [c_vp, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int,
+                       c_vp],
+    # (kind, act, ld_act, B, Ha, Wa, Ca, other, ld_other, KH, KW, SH, SW, PH, PW, n_out, out, ldo, bias, relu, split_k, atomic, tile_n, stream)
+    "dmlb_conv_implicit_tf32": [c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_vp,
+                                c_int, c_vp, c_int, c_int, c_int, c_int, c_vp],
+    "dmlb_splitk_finish_f32": [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_ll, c_int, c_int, c_int, c_int, c_int, c_vp, c_int, c_vp],
+    "dmlb_im2col_nhwc_f32": [c_vp, c_vp] + [c_int] * 12 + [c_vp],
+    "dmlb_im2col_nchw_f32_f32": [c_vp, c_vp] + [c_int] * 11 + [c_vp],
+    "dmlb_col2im_nhwc_f32": [c_vp, c_vp] + [c_int] * 12 + [c_vp],
+    "dmlb_maxpool_fwd_f32": [c_vp, c_vp] + [c_int] * 9 + [c_vp],
+    "dmlb_act_bwd_f32": [c_vp, c_vp, c_vp, c_vp] + [c_int] * 11 + [c_vp],
+    "dmlb_relu_fwd_f32": [c_vp, c_vp, c_ll, c_int, c_int, c_int, c_vp],
+    "dmlb_relu_bwd_f32": [c_vp, c_vp, c_vp, c_ll, c_int, c_int, c_int, c_int, c_vp],
+    "dmlb_scale_rows_f32": [c_vp, c_vp, c_ll, c_int, c_int, c_vp],
+    "dmlb_refresh_shadows_f32": [c_vp, c_vp, c_vp, c_int, c_vp],
+    "dmlb_dropout_fwd_f32": [c_vp, c_vp, c_vp, c_ll, c_int, c_int, c_int, c_int, c_int, c_float, c_ull, c_vp, c_vp],
+    "dmlb_dropout_bwd_f32": [c_vp, c_vp, c_vp, c_ll, c_int, c_int, c_int, c_float, c_vp],
 }
 _RESTYPES = {"dmlb_last_error": ctypes.c_char_p, "dmlb_launch_count": c_ll, "dmlb_reset_launch_count": None}
 _OPTIONAL = set()  # entry points that newer libraries add; absent ones are simply not bound

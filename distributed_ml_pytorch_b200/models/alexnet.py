@@ -14,7 +14,7 @@ from ..ops import functional as OF
 
 
 class AlexNet(nn.Module):
-    def __init__(self, num_classes: int = 10, in_channels: int = 3):
+    def __init__(self, num_classes: int = 10, in_channels: int = 3, dtype="tf32"):
         super().__init__()
         P = (2, 2, 0)
         self.features = nn.Sequential(
@@ -34,6 +34,8 @@ class AlexNet(nn.Module):
         )
         self.classifier = dnn.Linear(256, num_classes)
         dnn.attach_shadows(self)
+        # CUDA compute dtype: "tf32" = the reference's precision (fp32 tensors, TF32 tensor-core math), "bf16" = bf16 operands / activations
+        dnn.set_compute_dtype(self, dtype)
 
     def forward(self, x):
         x = self.features(x)

@@ -17,7 +17,7 @@ from ..ops import functional as OF
 
 
 class LeNet(nn.Module):
-    def __init__(self, in_channels: int = 3, input_hw: int = 32, num_classes: int = 10):
+    def __init__(self, in_channels: int = 3, input_hw: int = 32, num_classes: int = 10, dtype="tf32"):
         super().__init__()
         s1 = (input_hw - 4) // 2
         s2 = (s1 - 4) // 2
@@ -30,6 +30,8 @@ class LeNet(nn.Module):
         self.fc3 = dnn.Linear(84, num_classes)
         self.fc_drop = dnn.Dropout()  # stateless (F.dropout in the reference, models.py:20)
         dnn.attach_shadows(self)
+        # CUDA compute dtype: "tf32" = the reference's precision (fp32 tensors, TF32 tensor-core math), "bf16" = bf16 operands / activations
+        dnn.set_compute_dtype(self, dtype)
 
     def forward(self, x):
         x = self.conv1(x)

@@ -3,9 +3,14 @@
 Parameters keep PyTorch's names, shapes and fp32 dtype (``weight [Cout, Cin, kh, kw]``, ``bias``), so
 ``state_dict()`` checkpoints are interchangeable with the reference's ``nn.Conv2d`` / ``nn.Linear`` models
 (reference example/models.py:8-13,28-43).  For the tensor cores each layer additionally
-owns a bf16 *shadow* of its weight in GEMM layout ``[Cout, pad8(K)]`` with K ordered ``(kh, kw, cin)``;
+owns a *shadow* of its weight in GEMM layout ``[Cout, Kpad]`` with K ordered ``(kh, kw, cin)``;
 shadows are refreshed by one table-driven kernel for the whole model (:class:`ShadowSet`) whenever the
 fp32 masters change (optimizer step, parameter pull, ``load_state_dict``).
+
+The shadow's dtype is the layer's *compute dtype* (:func:`set_compute_dtype`): bf16 (default — bf16 operands and
+activations), or fp32 for the tf32 path, where the tensor cores read fp32 words as tf32 and activations stay fp32
+like the reference's (example/main.py:41,53-54,70-73).  In tf32 mode a weight that already sits in GEMM order with
+16-byte rows (every arena-backed AlexNet layer but conv1) needs no copy at all: its shadow *is* its master storage.
 """
 from __future__ import annotations
 
@@ -24,22 +29,61 @@ def _pair(v) -> Tuple[int, int]:
     return (v, v) if isinstance(v, int) else (int(v[0]), int(v[1]))
 
 
+_DTYPES = {"bf16": torch.bfloat16, "bfloat16": torch.bfloat16, "tf32": torch.float32, "fp32": torch.float32, "float32": torch.float32}
+
+
+def resolve_dtype(dtype) -> torch.dtype:
+    """'bf16' | 'tf32' (or a torch dtype) -> the storage dtype of activations / GEMM operands."""
+    if isinstance(dtype, torch.dtype):
+        if dtype not in (torch.bfloat16, torch.float32):
+            raise ValueError("compute dtype must be bf16 or tf32 (fp32 storage)")
+        return dtype
+    try:
+        return _DTYPES[str(dtype).lower()]
+    except KeyError:
+        raise ValueError(f"unknown compute dtype {dtype!r}: choose 'bf16' or 'tf32'") from None
+
+
+def set_compute_dtype(model: nn.Module, dtype) -> nn.Module:
+    """Select the CUDA compute dtype of every kernel-backed layer of ``model``: ``'bf16'`` or ``'tf32'``.
+    Call it before the optimizer (the flat arena keeps a bf16 mirror only for bf16 models)."""
+    dt = resolve_dtype(dtype)
+    if dt == torch.float32 and any(isinstance(m, BatchNorm2d) for m in model.modules()):
+        raise NotImplementedError("the tf32 compute dtype covers the reference's models (LeNet, AlexNet); batch-norm models run in bf16")
+    for m in model.modules():
+        if isinstance(m, _ShadowedModule):
+            if m.compute_dtype != dt:
+                m.compute_dtype = dt
+                m._shadow, m._shadow_key, m._flat = None, None, False
+    model._dmlb_compute_dtype = dt
+    ss = getattr(model, "_dmlb_shadows", None)
+    if ss is not None:
+        ss.invalidate_table()
+    return model
+
+
+def compute_dtype_name(model: nn.Module) -> str:
+    return "tf32" if getattr(model, "_dmlb_compute_dtype", torch.bfloat16) == torch.float32 else "bf16"
+
+
 def _gemm_order(w: torch.Tensor) -> bool:
     """True when a 4-D weight is physically stored as [Cout, kh, kw, Cin] (channels-last), i.e. already in GEMM K order."""
     return w.dim() == 4 and w.permute(0, 2, 3, 1).is_contiguous()
 
 
 class _ShadowedModule(nn.Module):
-    """Mixin for layers with a ``weight`` that is mirrored into a bf16 GEMM-layout shadow.
+    """Mixin for layers with a ``weight`` that is mirrored into a GEMM-layout shadow of the compute dtype.
 
     Two kinds of shadow storage:
-    * *flat*  — the weight lives in a CUDA :class:`FlatArena` in GEMM order with ``K % 8 == 0``: the shadow is the slice of the
+    * *flat*  — bf16: the weight lives in a CUDA :class:`FlatArena` in GEMM order with ``K % 8 == 0``: the shadow is the slice of the
       arena's flat bf16 mirror at the same offset, written by the optimizer kernel itself (no extra launch);
-    * *table* — anything else (PyTorch-layout weights, ``K % 8 != 0``, ``in_map`` linears): own storage with padded rows,
+      tf32: the weight's own fp32 storage is in GEMM order with 16-byte rows: the shadow aliases it, nothing is ever copied;
+    * *table* — anything else (PyTorch-layout weights, unaligned ``K``, ``in_map`` linears): own storage with padded rows,
       filled by the table-driven ``refresh_shadows`` kernel.
     """
 
     def _init_shadow_state(self) -> None:
+        self.compute_dtype = torch.bfloat16
         self._shadow: Optional[torch.Tensor] = None
         self._shadow_key = None           # (data_ptr, _version) of the weight the shadow was built from
         self._shadow_set: Optional["ShadowSet"] = None
@@ -61,10 +105,10 @@ class _ShadowedModule(nn.Module):
 
     def _shadow_entry(self) -> bytes:
         rows, cin, khw = self._shadow_dims()
-        ld = K.pad8(cin * khw)
+        ld = K.pad_for(self.compute_dtype, cin * khw)
         if not self._needs_permute():
             cin, khw = cin * khw, 1       # source already in GEMM order: plain cast with a row pitch
-        return struct.pack("<qqiiii", self.weight.data_ptr() // 4, self._shadow.data_ptr() // 2, rows, cin, khw, ld)
+        return struct.pack("<qqiiii", self.weight.data_ptr() // 4, self._shadow.data_ptr() // self._shadow.element_size(), rows, cin, khw, ld)
 
     def _ensure_shadow_storage(self) -> None:
         rows, cin, khw = self._shadow_dims()
@@ -72,6 +116,27 @@ class _ShadowedModule(nn.Module):
         w = self.weight
         slot = self._arena_slot
         flat_ok = False
+        if self.compute_dtype == torch.float32:
+            # tf32: fp32 storage already in GEMM order with 16-byte rows is read by TMA as it is
+            if w.dim() == 4:
+                in_order = khw == 1 and w.is_contiguous() or cin == 1 and w.is_contiguous() or _gemm_order(w)
+            else:
+                in_order = w.is_contiguous() and khw == 1
+            if in_order and kd % 4 == 0 and (w.data_ptr() & 15) == 0 and not self._needs_permute():
+                view = torch.as_strided(w.detach(), (rows, kd), (kd, 1), w.storage_offset())
+                if self._shadow is None or self._shadow.data_ptr() != view.data_ptr() or not self._flat or self._shadow.dtype != torch.float32:
+                    self._shadow, self._flat, self._shadow_key = view, True, None
+                    if self._shadow_set is not None:
+                        self._shadow_set.invalidate_table()
+                return
+            ld = K.pad_for(torch.float32, kd)
+            if self._flat or self._shadow is None or self._shadow.device != w.device or tuple(self._shadow.shape) != (rows, ld) \
+                    or self._shadow.dtype != torch.float32:
+                self._shadow = torch.zeros((rows, ld), dtype=torch.float32, device=w.device)
+                self._flat, self._shadow_key = False, None
+                if self._shadow_set is not None:
+                    self._shadow_set.invalidate_table()
+            return
         if slot is not None and slot[0].shadow is not None and slot[0].params.device == w.device and not self._needs_permute():
             arena, off = slot
             flat_ok = kd % 8 == 0 and off % 8 == 0 and w.data_ptr() == arena.params.data_ptr() + 4 * off
@@ -84,7 +149,8 @@ class _ShadowedModule(nn.Module):
                     self._shadow_set.invalidate_table()
             return
         ld = K.pad8(kd)
-        if self._flat or self._shadow is None or self._shadow.device != w.device or tuple(self._shadow.shape) != (rows, ld):
+        if self._flat or self._shadow is None or self._shadow.device != w.device or tuple(self._shadow.shape) != (rows, ld) \
+                or self._shadow.dtype != torch.bfloat16:
             self._shadow = torch.zeros((rows, ld), dtype=torch.bfloat16, device=w.device)
             self._flat, self._shadow_key = False, None
             if self._shadow_set is not None:
@@ -100,11 +166,12 @@ class _ShadowedModule(nn.Module):
             else:
                 self._ensure_shadow_storage()
                 if self._flat:
-                    arena = self._arena_slot[0]
-                    K.cast_f32_bf16(arena.params, arena.shadow.data_ptr(), 1, arena.padded, arena.padded, arena.padded)
+                    if self.compute_dtype == torch.bfloat16:
+                        arena = self._arena_slot[0]
+                        K.cast_f32_bf16(arena.params, arena.shadow.data_ptr(), 1, arena.padded, arena.padded, arena.padded)
                 else:
                     table = torch.frombuffer(bytearray(self._shadow_entry()), dtype=torch.uint8).to(w.device)
-                    K.refresh_shadows(table, 1)
+                    K.refresh_shadows(table, 1, dt=self.compute_dtype)
                 self._shadow_key = key
         return self._shadow
 
@@ -155,11 +222,12 @@ class ShadowSet:
         if self._table is None or self._ptrs != self._signature():
             self._build_table()
             flat_done = False
-        if self._has_flat and not flat_done:
+        dt = self.modules[0].compute_dtype
+        if self._has_flat and not flat_done and dt == torch.bfloat16:
             arena = getattr(self.model, "_dmlb_arena", None)
             K.cast_f32_bf16(arena.params, arena.shadow.data_ptr(), 1, arena.padded, arena.padded, arena.padded)
         if self._n_table:
-            K.refresh_shadows(self._table, self._n_table)
+            K.refresh_shadows(self._table, self._n_table, dt=dt)
         for m in self.modules:
             m._mark_shadow_fresh()
 

@@ -9,13 +9,16 @@ the CPU/gloo configuration (BASELINE.json config 1) and the non-GPU tests use.
 Reference call sites covered: ``nn.Conv2d`` / ``nn.Linear`` / ``F.max_pool2d`` / ``F.relu`` / ``Dropout2d`` /
 ``F.dropout`` in example/models.py:8-22,28-48 and ``F.cross_entropy`` in example/main.py:71,125.
 
-Layout contract on CUDA (see ``ops/kernels.py``): activations are bf16 and channels-last with a channel
-pitch padded to a multiple of 8; they are ordinary ``torch.Tensor`` views of logical shape ``[B, C, H, W]``
-(or ``[B, F]``), so user code such as ``outputs.max(1)`` keeps working.
+Layout contract on CUDA (see ``ops/kernels.py``): activations are channels-last with a channel pitch padded
+to 16 bytes; they are ordinary ``torch.Tensor`` views of logical shape ``[B, C, H, W]`` (or ``[B, F]``), so user
+code such as ``outputs.max(1)`` keeps working.  Their dtype is the layer's *compute dtype*: ``torch.bfloat16``
+(bf16 operands, the default) or ``torch.float32`` (the tf32 path: fp32 activations and weights that the tensor
+cores read as tf32 — the reference's own precision, example/main.py:41,53-54,70-73).
 """
 from __future__ import annotations
 
 import os
+import warnings
 
 from types import SimpleNamespace
 from typing import Optional, Tuple
@@ -26,7 +29,21 @@ import torch.nn.functional as F
 from . import kernels as K
 
 pad8 = K.pad8
+pad_for = K.pad_for
+BF16, F32 = torch.bfloat16, torch.float32
 _state = SimpleNamespace(unit_loss_grad=False)
+_warned = set()
+
+
+def _warn_once(key: str, msg: str) -> None:
+    """Say (once per process and call site) that an op left the hand-written sm_100a path for an ATen kernel."""
+    if key not in _warned:
+        _warned.add(key)
+        warnings.warn(f"distributed_ml_pytorch_b200: {msg}", RuntimeWarning, stacklevel=3)
+
+
+def _vec(dt) -> int:
+    return 4 if dt == F32 else 8
 
 
 def set_unit_loss_grad(flag: bool) -> bool:
@@ -39,23 +56,22 @@ def set_unit_loss_grad(flag: bool) -> bool:
 # ------------------------------------------------------------------------------------------------
 # layout helpers
 # ------------------------------------------------------------------------------------------------
-def new_act4(B: int, C: int, H: int, W: int, device) -> torch.Tensor:
-    """Fresh bf16 channels-last activation, logical ``[B, C, H, W]``, channel pitch ``pad8(C)``."""
-    buf = torch.empty((B, H, W, pad8(C)), dtype=torch.bfloat16, device=device)
+def new_act4(B: int, C: int, H: int, W: int, device, dt=BF16) -> torch.Tensor:
+    """Fresh channels-last activation of dtype ``dt``, logical ``[B, C, H, W]``, channel pitch ``pad_for(dt, C)``."""
+    buf = torch.empty((B, H, W, pad_for(dt, C)), dtype=dt, device=device)
     return buf[..., :C].permute(0, 3, 1, 2)
 
 
-def new_act2(B: int, Fdim: int, device, dtype=torch.bfloat16) -> torch.Tensor:
-    if dtype == torch.float32:
-        return torch.empty((B, Fdim), dtype=torch.float32, device=device)
-    buf = torch.empty((B, pad8(Fdim)), dtype=torch.bfloat16, device=device)
+def new_act2(B: int, Fdim: int, device, dtype=BF16) -> torch.Tensor:
+    buf = torch.empty((B, pad_for(dtype, Fdim)), dtype=dtype, device=device)
     return buf[:, :Fdim]
 
 
-def act4_pitch(t: torch.Tensor) -> Optional[int]:
-    """Channel pitch of ``t`` if it is a bf16 channels-last activation in our layout, else ``None``."""
-    if t.dtype != torch.bfloat16 or t.dim() != 4:
+def act4_pitch(t: torch.Tensor, dt=BF16) -> Optional[int]:
+    """Channel pitch of ``t`` if it is a channels-last activation of dtype ``dt`` in our layout, else ``None``."""
+    if t.dtype != dt or t.dim() != 4:
         return None
+    v = _vec(dt)
     B, C, H, W = t.shape
     s = t.stride()
     if C > 1 and s[1] != 1:
@@ -67,8 +83,8 @@ def act4_pitch(t: torch.Tensor) -> Optional[int]:
     elif B > 1:
         ld = s[0]
     else:
-        ld = pad8(C)
-    if ld < C or ld % 8 != 0:
+        ld = pad_for(dt, C)
+    if ld < C or ld % v != 0:
         return None
     if (W > 1 and s[3] != ld) or (H > 1 and s[2] != W * ld) or (B > 1 and s[0] != H * W * ld):
         return None
@@ -77,41 +93,49 @@ def act4_pitch(t: torch.Tensor) -> Optional[int]:
     return ld
 
 
-def as_act4(t: torch.Tensor) -> Tuple[torch.Tensor, int]:
-    """Return ``(tensor, pitch)`` in the kernel layout, converting (one ATen copy) only when needed."""
-    ld = act4_pitch(t)
+def as_act4(t: torch.Tensor, dt=None) -> Tuple[torch.Tensor, int]:
+    """Return ``(tensor, pitch)`` in the kernel layout of dtype ``dt`` (default: ``t``'s own dtype when it is a compute
+    dtype, else bf16), converting with one ATen copy only when needed."""
+    if dt is None:
+        dt = t.dtype if t.dtype in (BF16, F32) else BF16
+    ld = act4_pitch(t, dt)
     if ld is not None:
         return t, ld
     B, C, H, W = t.shape
-    out = new_act4(B, C, H, W, t.device)
+    out = new_act4(B, C, H, W, t.device, dt)
+    _warn_once("as_act4", f"a {tuple(t.shape)} {t.dtype} tensor with strides {t.stride()} is not in the channels-last kernel layout; "
+                          "converting it with an ATen copy")
     out.copy_(t)
-    return out, pad8(C)
+    return out, pad_for(dt, C)
 
 
-def act2_pitch(t: torch.Tensor) -> Optional[int]:
-    if t.dtype != torch.bfloat16 or t.dim() != 2:
+def act2_pitch(t: torch.Tensor, dt=BF16) -> Optional[int]:
+    if t.dtype != dt or t.dim() != 2:
         return None
     B, Fd = t.shape
     s = t.stride()
     if Fd > 1 and s[1] != 1:
         return None
-    ld = s[0] if B > 1 else pad8(Fd)
-    if ld < Fd or ld % 8 != 0 or (t.data_ptr() & 15) != 0:
+    ld = s[0] if B > 1 else pad_for(dt, Fd)
+    if ld < Fd or ld % _vec(dt) != 0 or (t.data_ptr() & 15) != 0:
         return None
     return ld
 
 
-def as_act2(t: torch.Tensor) -> Tuple[torch.Tensor, int]:
-    ld = act2_pitch(t)
+def as_act2(t: torch.Tensor, dt=None) -> Tuple[torch.Tensor, int]:
+    if dt is None:
+        dt = t.dtype if t.dtype in (BF16, F32) else BF16
+    ld = act2_pitch(t, dt)
     if ld is not None:
         return t, ld
     B, Fd = t.shape
-    out = new_act2(B, Fd, t.device)
-    if t.dtype == torch.float32 and t.stride(1) == 1:
+    out = new_act2(B, Fd, t.device, dt)
+    if dt == BF16 and t.dtype == F32 and t.stride(1) == 1:
         K.cast_f32_bf16(t, out.data_ptr(), B, Fd, t.stride(0), pad8(Fd))
     else:
+        _warn_once("as_act2", f"a {tuple(t.shape)} {t.dtype} tensor with strides {t.stride()} is converted to the kernel layout with an ATen copy")
         out.copy_(t)
-    return out, pad8(Fd)
+    return out, pad_for(dt, Fd)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -231,8 +255,8 @@ _PAIR_CONV = os.environ.get("DMLB_PAIR_CONV", "0") == "1"
 class _ConvBlockFn(torch.autograd.Function):
     """Convolution (+bias +ReLU +max-pool) on the tcgen05 GEMM.
 
-    Implicit path (bf16 channels-last input with Cin % 64 == 0): the activation operand of fprop, wgrad and dgrad is
-    gathered by TMA in im2col mode — no column matrix is ever written.  Explicit path (first layer from fp32 NCHW, small or
+    Implicit path (channels-last input whose channels fill whole 128-byte k-blocks: Cin % 64 == 0 in bf16, % 32 in tf32): the
+    activation operand of fprop, wgrad and dgrad is gathered by TMA in im2col mode — no column matrix is ever written.  Explicit path (first layer from fp32 NCHW, small or
     odd channel counts, strided dgrad): im2col / col2im kernels around the same GEMM.  Tiny-M layers split K over the SMs
     and finish (bias, ReLU, 2x2 pool, bf16 cast) in one kernel.  Weight gradients accumulate straight into the fp32 arena
     on a side stream."""
@@ -246,36 +270,38 @@ class _ConvBlockFn(torch.autograd.Function):
         Ho = (H + 2 * PH - KH) // SH + 1
         Wo = (W + 2 * PW - KW) // SW + 1
         M, Kd = B * Ho * Wo, Cin * KH * KW
-        Kpad = pad8(Kd)
+        dt = cfg.dt
+        bk = K.kblock(dt)
+        Kpad = pad_for(dt, Kd)
         dev = x.device
-        from_nchw_f32 = x.dtype == torch.float32 and x.is_contiguous()
-        direct = (not from_nchw_f32) and KH == 1 and KW == 1 and SH == 1 and SW == 1 and PH == 0 and PW == 0 and Cin % 8 == 0
-        implicit = _conv_opts.implicit and (not from_nchw_f32) and (not direct) and Cin % 64 == 0
+        from_nchw_f32 = act4_pitch(x, dt) is None and x.dtype == torch.float32 and x.is_contiguous()
+        direct = (not from_nchw_f32) and KH == 1 and KW == 1 and SH == 1 and SW == 1 and PH == 0 and PW == 0 and Cin % _vec(dt) == 0
+        implicit = _conv_opts.implicit and (not from_nchw_f32) and (not direct) and Cin % bk == 0
         ldx, a_t, lda = 0, None, 0
         if from_nchw_f32:
-            a_t = torch.empty((M, Kpad), dtype=torch.bfloat16, device=dev)
+            a_t = torch.empty((M, Kpad), dtype=dt, device=dev)
             K.im2col_nchw_f32(x, a_t, B, H, W, Cin, KH, KW, SH, SW, PH, PW, Kpad)
             lda = Kpad
         else:
-            x, ldx = as_act4(x)
+            x, ldx = as_act4(x, dt)
             if direct:
                 a_t, lda = x, ldx
             elif not implicit:
-                a_t = torch.empty((M, Kpad), dtype=torch.bfloat16, device=dev)
+                a_t = torch.empty((M, Kpad), dtype=dt, device=dev)
                 K.im2col_nhwc(x.data_ptr(), a_t, B, H, W, Cin, ldx, KH, KW, SH, SW, PH, PW, Kpad)
                 lda = Kpad
 
         def fprop(out_t, ldo, **kw):
             if implicit:
-                K.conv_implicit(0, x.data_ptr(), ldx, B, H, W, Cin, cfg.shadow.data_ptr(), Kpad, KH, KW, SH, SW, PH, PW, Cout, out_t, ldo, **kw)
+                K.conv_implicit(0, x.data_ptr(), ldx, B, H, W, Cin, cfg.shadow.data_ptr(), Kpad, KH, KW, SH, SW, PH, PW, Cout, out_t, ldo, dt=dt, **kw)
             else:
-                if _PAIR_CONV and direct and Cout >= 256 and M >= 8192 and "tile_n" not in kw and not kw.get("atomic"):
+                if _PAIR_CONV and dt == BF16 and direct and Cout >= 256 and M >= 8192 and "tile_n" not in kw and not kw.get("atomic"):
                     kw["tile_n"] = 256        # wide 1x1 convolutions: 256 x 256 tiles on CTA pairs (persistent, epilogue overlapped)
                 K.gemm(a_t, lda, False, cfg.shadow, Kpad, False, M, Cout, Kd, out_t, ldo, **kw)
 
-        y = new_act4(B, Cout, Ho, Wo, dev)
-        ldy = pad8(Cout)
-        split = K.fprop_split(M, Cout, Kd)
+        y = new_act4(B, Cout, Ho, Wo, dev, dt)
+        ldy = pad_for(dt, Cout)
+        split = K.fprop_split(M, Cout, Kd, bk=bk)
         out = y
         fused_pool = False
         if split > 1:
@@ -284,7 +310,7 @@ class _ConvBlockFn(torch.autograd.Function):
             ldw = (Cout + 3) // 4 * 4
             ws = K.splitk_workspace(dev, M * ldw)
             want_pool = cfg.pool == (2, 2, 0) and Ho % 2 == 0 and Wo % 2 == 0
-            if K.fused_finish() and (not want_pool or K.fin_pool_supported(Ho, Wo)):
+            if dt == BF16 and K.fused_finish() and (not want_pool or K.fin_pool_supported(Ho, Wo)):
                 if want_pool:
                     out = new_act4(B, Cout, Ho // 2, Wo // 2, dev)
                     fused_pool = True
@@ -297,18 +323,19 @@ class _ConvBlockFn(torch.autograd.Function):
             else:
                 fprop(ws, ldw, split_k=split, atomic=True)
                 if want_pool:
-                    out = new_act4(B, Cout, Ho // 2, Wo // 2, dev)
-                    K.splitk_finish(ws, ldw, bias, cfg.relu, y.data_ptr(), ldy, M, Cout, pool2=(B, Ho, Wo), pooled_ptr=out.data_ptr(), ldp=ldy)
+                    out = new_act4(B, Cout, Ho // 2, Wo // 2, dev, dt)
+                    K.splitk_finish(ws, ldw, bias, cfg.relu, y.data_ptr(), ldy, M, Cout, pool2=(B, Ho, Wo), pooled_ptr=out.data_ptr(), ldp=ldy,
+                                    dt=dt)
                     fused_pool = True
                 else:
-                    K.splitk_finish(ws, ldw, bias, cfg.relu, y.data_ptr(), ldy, M, Cout)
+                    K.splitk_finish(ws, ldw, bias, cfg.relu, y.data_ptr(), ldy, M, Cout, dt=dt)
         else:
             fprop(y, ldy, bias=bias, relu=cfg.relu)
         if cfg.pool is not None and not fused_pool:
             k, s, p = cfg.pool
             Hp, Wp = (Ho + 2 * p - k) // s + 1, (Wo + 2 * p - k) // s + 1
-            out = new_act4(B, Cout, Hp, Wp, dev)
-            K.maxpool_fwd(y.data_ptr(), out.data_ptr(), B, Ho, Wo, Cout, ldy, ldy, k, s, p)
+            out = new_act4(B, Cout, Hp, Wp, dev, dt)
+            K.maxpool_fwd(y.data_ptr(), out.data_ptr(), B, Ho, Wo, Cout, ldy, ldy, k, s, p, dt=dt)
         ctx.cfg = cfg
         ctx.geom = (B, H, W, Cin, Cout, KH, KW, SH, SW, PH, PW, Ho, Wo, Kd, Kpad, ldx, lda, direct, from_nchw_f32, implicit)
         ctx.has_bias = bias is not None
@@ -321,9 +348,11 @@ class _ConvBlockFn(torch.autograd.Function):
         a_t, y, weight, bias = ctx.saved_tensors
         (B, H, W, Cin, Cout, KH, KW, SH, SW, PH, PW, Ho, Wo, Kd, Kpad, ldx, lda, direct, from_nchw_f32, implicit) = ctx.geom
         dev = dout.device
+        dt = cfg.dt
+        bk = K.kblock(dt)
         M = B * Ho * Wo
-        ldy = pad8(Cout)
-        dout, ldd = as_act4(dout)
+        ldy = pad_for(dt, Cout)
+        dout, ldd = as_act4(dout, dt)
         # ---- activation backward (+ pool backward, + bias gradient) ----
         gb = None
         bias_sink = cfg.bsink if (ctx.has_bias and _sink_ok(bias, cfg.bsink)) else None
@@ -331,9 +360,9 @@ class _ConvBlockFn(torch.autograd.Function):
             gb = torch.zeros(Cout, dtype=torch.float32, device=dev)
         db = bias_sink if bias_sink is not None else gb
         if cfg.relu or cfg.pool is not None or db is not None:
-            dy = new_act4(B, Cout, Ho, Wo, dev)
+            dy = new_act4(B, Cout, Ho, Wo, dev, dt)
             K.act_bwd(y.data_ptr() if y is not None else dy.data_ptr(), dout.data_ptr(), dy.data_ptr(), db, B, Ho, Wo, Cout, ldy, ldd,
-                      cfg.pool, cfg.relu)
+                      cfg.pool, cfg.relu, dt=dt)
             lddy = ldy
             if bias_sink is not None:
                 _notify_grad_ready(bias, dev)
@@ -344,7 +373,7 @@ class _ConvBlockFn(torch.autograd.Function):
         if ctx.needs_input_grad[1]:
             wsink = cfg.wsink if _sink_ok(weight, cfg.wsink) else None
             tiles = ((Cout + 127) // 128) * ((Kd + 127) // 128)
-            split = K.pick_split_k(tiles, M)
+            split = K.pick_split_k(tiles, M, bk=bk)
             # a channels-last gradient (arena layout [Cout,kh,kw,Cin]) is exactly the GEMM's column order: contiguous
             # rows, vector red.add; a PyTorch-layout gradient needs the (kh,kw,cin)->(cin,kh,kw) column scatter
             if wsink is not None:
@@ -362,10 +391,10 @@ class _ConvBlockFn(torch.autograd.Function):
             with _WgradFork(dev, dy, a_t, gw) as fork:
                 if implicit and gemm_order:
                     K.conv_implicit(1, a_t.data_ptr(), ldx, B, H, W, Cin, dy.data_ptr(), lddy, KH, KW, SH, SW, PH, PW, Cout, target, Kd,
-                                    split_k=split, atomic=True)
+                                    split_k=split, atomic=True, dt=dt)
                 else:
                     if implicit:   # PyTorch-layout sink with an implicit forward: rebuild the column matrix once
-                        col = torch.empty((M, Kpad), dtype=torch.bfloat16, device=dev)
+                        col = torch.empty((M, Kpad), dtype=dt, device=dev)
                         K.im2col_nhwc(a_t.data_ptr(), col, B, H, W, Cin, ldx, KH, KW, SH, SW, PH, PW, Kpad)
                         col.record_stream(torch.cuda.current_stream(dev))
                         b_t, ldb = col, Kpad
@@ -382,28 +411,29 @@ class _ConvBlockFn(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             if from_nchw_f32:
                 raise RuntimeError("gradient w.r.t. an fp32 NCHW network input is not implemented on the CUDA path")
-            dx = new_act4(B, Cin, H, W, dev)
-            ldxo = pad8(Cin)
+            dx = new_act4(B, Cin, H, W, dev, dt)
+            ldxo = pad_for(dt, Cin)
             if direct:
                 K.gemm(dy, lddy, False, cfg.shadow, Kpad, True, M, Kd, Cout, dx, ldxo)
-            elif implicit and SH == 1 and SW == 1 and Cout % 64 == 0 and Cin % 8 == 0 and Kpad == Kd:
+            elif implicit and SH == 1 and SW == 1 and Cout % bk == 0 and Cin % _vec(dt) == 0 and Kpad == Kd:
                 # transposed convolution as an implicit GEMM over dY: no dcol matrix, no col2im
                 Min, Kdg = B * H * W, KH * KW * Cout
-                dsplit = K.fprop_split(Min, Cin, Kdg)
+                dsplit = K.fprop_split(Min, Cin, Kdg, bk=bk)
                 if dsplit > 1:
                     ldw = (Cin + 3) // 4 * 4
                     ws = K.splitk_workspace(dev, Min * ldw)
-                    if K.fused_finish():
+                    if dt == BF16 and K.fused_finish():
                         K.conv_implicit_fin(2, dy.data_ptr(), lddy, B, Ho, Wo, Cout, cfg.shadow.data_ptr(), Kpad, KH, KW, 1, 1, PH, PW, Cin, ws, ldw,
                                             None, False, dx.data_ptr(), ldxo, dsplit)
                     else:
                         K.conv_implicit(2, dy.data_ptr(), lddy, B, Ho, Wo, Cout, cfg.shadow.data_ptr(), Kpad, KH, KW, 1, 1, PH, PW, Cin, ws, ldw,
-                                        split_k=dsplit, atomic=True)
-                        K.splitk_finish(ws, ldw, None, False, dx.data_ptr(), ldxo, Min, Cin)
+                                        split_k=dsplit, atomic=True, dt=dt)
+                        K.splitk_finish(ws, ldw, None, False, dx.data_ptr(), ldxo, Min, Cin, dt=dt)
                 else:
-                    K.conv_implicit(2, dy.data_ptr(), lddy, B, Ho, Wo, Cout, cfg.shadow.data_ptr(), Kpad, KH, KW, 1, 1, PH, PW, Cin, dx, ldxo)
+                    K.conv_implicit(2, dy.data_ptr(), lddy, B, Ho, Wo, Cout, cfg.shadow.data_ptr(), Kpad, KH, KW, 1, 1, PH, PW, Cin, dx, ldxo,
+                                    dt=dt)
             else:
-                dcol = torch.empty((M, Kpad), dtype=torch.bfloat16, device=dev)
+                dcol = torch.empty((M, Kpad), dtype=dt, device=dev)
                 K.gemm(dy, lddy, False, cfg.shadow, Kpad, True, M, Kd, Cout, dcol, Kpad)
                 K.col2im_nhwc(dcol, dx.data_ptr(), B, H, W, Cin, ldxo, KH, KW, SH, SW, PH, PW, Kpad)
         return dx, gw, gb, None
@@ -412,9 +442,10 @@ class _ConvBlockFn(torch.autograd.Function):
 def conv_block(x, weight, bias=None, stride=(1, 1), padding=(0, 0), relu=False, pool=None, shadow=None, wsink=None, bsink=None):
     """``max_pool(relu(conv2d(x, weight, bias)))`` with the optional parts fused (CUDA) or composed (CPU).
 
-    ``pool`` is ``None`` or ``(kernel, stride, padding)``; ``shadow`` is the bf16 GEMM-layout copy of
-    ``weight`` (see :class:`~distributed_ml_pytorch_b200.nn.layers.Conv2d`); ``wsink`` / ``bsink`` are views
-    of the flat fp32 gradient arena that receive the parameter gradients directly.
+    ``pool`` is ``None`` or ``(kernel, stride, padding)``; ``shadow`` is the GEMM-layout form of ``weight``
+    (see :class:`~distributed_ml_pytorch_b200.nn.layers.Conv2d`) whose dtype selects the compute dtype: bf16, or
+    fp32 for the tf32 path; ``wsink`` / ``bsink`` are views of the flat fp32 gradient arena that receive the
+    parameter gradients directly.
     """
     if not x.is_cuda:
         y = F.conv2d(x, weight, bias, stride=stride, padding=padding)
@@ -424,8 +455,9 @@ def conv_block(x, weight, bias=None, stride=(1, 1), padding=(0, 0), relu=False, 
             y = F.max_pool2d(y, pool[0], pool[1], pool[2])
         return y
     if shadow is None:
-        raise RuntimeError("conv_block on CUDA needs the bf16 weight shadow (use nn.Conv2d from this package)")
-    cfg = SimpleNamespace(stride=tuple(stride), padding=tuple(padding), relu=bool(relu), pool=pool, shadow=shadow, wsink=wsink, bsink=bsink)
+        raise RuntimeError("conv_block on CUDA needs the GEMM-layout weight shadow (use nn.Conv2d from this package)")
+    cfg = SimpleNamespace(stride=tuple(stride), padding=tuple(padding), relu=bool(relu), pool=pool, shadow=shadow, wsink=wsink, bsink=bsink,
+                          dt=shadow.dtype)
     return _ConvBlockFn.apply(x, weight, bias, cfg)
 
 
@@ -436,11 +468,13 @@ class _LinearFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias, cfg):
         O, I = weight.shape
-        x, ldx = as_act2(x)
+        dt = cfg.dt
+        x, ldx = as_act2(x, dt)
         B = x.shape[0]
-        Kpad = pad8(I)
-        y = new_act2(B, O, x.device, torch.float32 if cfg.out_fp32 else torch.bfloat16)
-        ldo = O if cfg.out_fp32 else pad8(O)
+        Kpad = pad_for(dt, I)
+        odt = torch.float32 if cfg.out_fp32 else dt
+        y = new_act2(B, O, x.device, odt)
+        ldo = pad_for(odt, O)
         K.gemm(x, ldx, False, cfg.shadow, Kpad, False, B, O, I, y, ldo, bias=bias, relu=cfg.relu)
         ctx.cfg = cfg
         ctx.ldx = ldx
@@ -455,17 +489,22 @@ class _LinearFn(torch.autograd.Function):
         O, I = weight.shape
         B = x.shape[0]
         dev = dout.device
-        Kpad = pad8(I)
-        dout, ldd = as_act2(dout)
+        dt = cfg.dt
+        Kpad = pad_for(dt, I)
+        dout, ldd = as_act2(dout, dt)
         gb = None
         bias_sink = cfg.bsink if (ctx.has_bias and _sink_ok(bias, cfg.bsink)) else None
         if ctx.has_bias and bias_sink is None and ctx.needs_input_grad[2]:
             gb = torch.zeros(O, dtype=torch.float32, device=dev)
         db = bias_sink if bias_sink is not None else gb
         if cfg.relu or db is not None:
-            dy = new_act2(B, O, dev)
-            lddy = pad8(O)
-            K.act_bwd(y.data_ptr() if y is not None else dy.data_ptr(), dout.data_ptr(), dy.data_ptr(), db, B, 1, 1, O, lddy, ldd, None, cfg.relu)
+            dy = new_act2(B, O, dev, dt)
+            lddy = pad_for(dt, O)
+            ldyv = y.stride(0) if (y is not None and B > 1) else lddy
+            if ldyv != lddy:          # fp32 logits of a bf16 layer never carry a ReLU, so y and dy share a pitch whenever y is read
+                raise RuntimeError("linear backward: saved output and gradient pitches differ")
+            K.act_bwd(y.data_ptr() if y is not None else dy.data_ptr(), dout.data_ptr(), dy.data_ptr(), db, B, 1, 1, O, lddy, ldd, None, cfg.relu,
+                      dt=dt)
             if bias_sink is not None:
                 _notify_grad_ready(bias, dev)
         else:
@@ -477,7 +516,7 @@ class _LinearFn(torch.autograd.Function):
                 gw = torch.zeros_like(weight, dtype=torch.float32)
             target = wsink if wsink is not None else gw
             tiles = ((O + 127) // 128) * ((I + 127) // 128)
-            split = K.pick_split_k(tiles, B)
+            split = K.pick_split_k(tiles, B, bk=K.kblock(dt))
             pc, pk = (cfg.in_map[0], cfg.in_map[1] * cfg.in_map[2]) if cfg.in_map is not None else (0, 0)
             with _WgradFork(dev, dy, x, gw) as fork:
                 K.gemm(dy, lddy, True, x, ctx.ldx, True, O, I, B, target, I, split_k=split, atomic=True, perm_cin=pc if pk > 1 else 0,
@@ -488,8 +527,8 @@ class _LinearFn(torch.autograd.Function):
                 _notify_grad_ready(weight, dev, fork.side if fork.active else None)
         dx = None
         if ctx.needs_input_grad[0]:
-            dx = new_act2(B, I, dev)
-            K.gemm(dy, lddy, False, cfg.shadow, Kpad, True, B, I, O, dx, pad8(I))
+            dx = new_act2(B, I, dev, dt)
+            K.gemm(dy, lddy, False, cfg.shadow, Kpad, True, B, I, O, dx, pad_for(dt, I))
         return dx, gw, gb, None
 
 
@@ -500,8 +539,8 @@ def linear(x, weight, bias=None, relu=False, out_fp32=False, in_map=None, shadow
         y = F.linear(x, weight, bias)
         return F.relu(y) if relu else y
     if shadow is None:
-        raise RuntimeError("linear on CUDA needs the bf16 weight shadow (use nn.Linear from this package)")
-    cfg = SimpleNamespace(relu=bool(relu), out_fp32=bool(out_fp32), in_map=in_map, shadow=shadow, wsink=wsink, bsink=bsink)
+        raise RuntimeError("linear on CUDA needs the GEMM-layout weight shadow (use nn.Linear from this package)")
+    cfg = SimpleNamespace(relu=bool(relu), out_fp32=bool(out_fp32), in_map=in_map, shadow=shadow, wsink=wsink, bsink=bsink, dt=shadow.dtype)
     return _LinearFn.apply(x, weight, bias, cfg)
 
 
@@ -515,17 +554,18 @@ class _MaxPoolFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, k, s, p):
         x, ldx = as_act4(x)
+        dt = x.dtype
         B, C, H, W = x.shape
         Ho, Wo = (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
-        out = new_act4(B, C, Ho, Wo, x.device)
+        out = new_act4(B, C, Ho, Wo, x.device, dt)
         ctx.args = (k, s, p, ldx, (B, C, H, W))
-        if C % 8 == 0:
+        if C % 8 == 0 and dt == BF16:
             idx = torch.empty((B, Ho, Wo, C), dtype=torch.uint8, device=x.device)
             K.maxpool_fwd_idx(x.data_ptr(), out.data_ptr(), idx, B, H, W, C, ldx, pad8(C), k, s, p)
             ctx.indexed = True
             ctx.save_for_backward(idx)
         else:
-            K.maxpool_fwd(x.data_ptr(), out.data_ptr(), B, H, W, C, ldx, pad8(C), k, s, p)
+            K.maxpool_fwd(x.data_ptr(), out.data_ptr(), B, H, W, C, ldx, pad_for(dt, C), k, s, p, dt=dt)
             ctx.indexed = False
             ctx.save_for_backward(x)
         return out
@@ -534,15 +574,16 @@ class _MaxPoolFn(torch.autograd.Function):
     def backward(ctx, dout):
         (saved,) = ctx.saved_tensors
         k, s, p, ldx, (B, C, H, W) = ctx.args
-        dout, ldd = as_act4(dout)
-        dx = new_act4(B, C, H, W, dout.device)
+        dt = BF16 if ctx.indexed else saved.dtype
+        dout, ldd = as_act4(dout, dt)
+        dx = new_act4(B, C, H, W, dout.device, dt)
         if ctx.indexed:
             K.maxpool_bwd_idx(dout.data_ptr(), saved, dx.data_ptr(), B, H, W, C, pad8(C), ldd, k, s, p)
         else:
             x = saved
-            if pad8(C) != ldx:
-                x, ldx = as_act4(x.contiguous())
-            K.act_bwd(x.data_ptr(), dout.data_ptr(), dx.data_ptr(), None, B, H, W, C, ldx, ldd, (k, s, p), False)
+            if pad_for(dt, C) != ldx:
+                x, ldx = as_act4(x.contiguous(), dt)
+            K.act_bwd(x.data_ptr(), dout.data_ptr(), dx.data_ptr(), None, B, H, W, C, ldx, ldd, (k, s, p), False, dt=dt)
         return dx, None, None, None
 
 
@@ -556,43 +597,48 @@ def max_pool2d(x, kernel_size, stride=None, padding=0):
 class _ReLUFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x):
+        dt = x.dtype
         if x.dim() == 4:
-            x, ld = as_act4(x)
+            x, ld = as_act4(x, dt)
             B, C, H, W = x.shape
-            y = new_act4(B, C, H, W, x.device)
+            y = new_act4(B, C, H, W, x.device, dt)
             rows = B * H * W
         else:
-            x, ld = as_act2(x)
+            x, ld = as_act2(x, dt)
             rows, C = x.shape
-            y = new_act2(rows, C, x.device)
-        K.relu_fwd(x.data_ptr(), y.data_ptr(), rows, C, ld, pad8(C))
+            y = new_act2(rows, C, x.device, dt)
+        K.relu_fwd(x.data_ptr(), y.data_ptr(), rows, C, ld, pad_for(dt, C), dt=dt)
         ctx.save_for_backward(y)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         (y,) = ctx.saved_tensors
+        dt = y.dtype
         if y.dim() == 4:
-            dy, ldd = as_act4(dy)
+            dy, ldd = as_act4(dy, dt)
             B, C, H, W = y.shape
-            dx = new_act4(B, C, H, W, y.device)
+            dx = new_act4(B, C, H, W, y.device, dt)
             rows = B * H * W
         else:
-            dy, ldd = as_act2(dy)
+            dy, ldd = as_act2(dy, dt)
             rows, C = y.shape
-            dx = new_act2(rows, C, y.device)
-        K.relu_bwd(y.data_ptr(), dy.data_ptr(), dx.data_ptr(), rows, C, pad8(C), ldd, pad8(C))
+            dx = new_act2(rows, C, y.device, dt)
+        K.relu_bwd(y.data_ptr(), dy.data_ptr(), dx.data_ptr(), rows, C, pad_for(dt, C), ldd, pad_for(dt, C), dt=dt)
         return dx
 
 
 def relu(x):
-    if not x.is_cuda or x.dtype != torch.bfloat16:
+    if not x.is_cuda:
+        return F.relu(x)
+    if x.dtype not in (BF16, F32) or x.dim() not in (2, 4):
+        _warn_once("relu", f"relu on a {x.dtype} {x.dim()}-D CUDA tensor runs the ATen kernel (the sm_100a kernels take bf16 / fp32, 2-D or 4-D)")
         return F.relu(x)
     return _ReLUFn.apply(x)
 
 
 class _FlattenFn(torch.autograd.Function):
-    """[B, C, H, W] channels-last -> [B, H*W*C] (features ordered (h, w, c)); a pure re-view when C % 8 == 0."""
+    """[B, C, H, W] channels-last -> [B, H*W*C] (features ordered (h, w, c)); a pure re-view when the channel rows carry no padding."""
 
     @staticmethod
     def forward(ctx, x):
@@ -607,9 +653,9 @@ class _FlattenFn(torch.autograd.Function):
     def backward(ctx, g):
         B, C, H, W = ctx.shape
         g, ldg = as_act2(g)
-        if C % 8 == 0 and ldg == H * W * C:
+        if C % _vec(g.dtype) == 0 and ldg == H * W * C:
             return torch.as_strided(g, (B, C, H, W), (H * W * C, 1, W * C, C), g.storage_offset())
-        out = new_act4(B, C, H, W, g.device)
+        out = new_act4(B, C, H, W, g.device, g.dtype)
         out.copy_(g[:, :H * W * C].reshape(B, H, W, C).permute(0, 3, 1, 2))
         return out
 
@@ -630,34 +676,35 @@ def flatten(x):
 class _DropoutFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, p, channel_mode, seed, counter):
+        dt = x.dtype
         if x.dim() == 4:
-            x, ld = as_act4(x)
+            x, ld = as_act4(x, dt)
             B, C, H, W = x.shape
             rows, rps = B * H * W, H * W
-            y = new_act4(B, C, H, W, x.device)
+            y = new_act4(B, C, H, W, x.device, dt)
         else:
-            x, ld = as_act2(x)
+            x, ld = as_act2(x, dt)
             rows, C = x.shape
             rps = 1
-            y = new_act2(rows, C, x.device)
+            y = new_act2(rows, C, x.device, dt)
         mask = torch.empty(rows * C, dtype=torch.uint8, device=x.device)
-        K.dropout_fwd(x.data_ptr(), y.data_ptr(), mask, rows, C, ld, pad8(C), rps, channel_mode, p, seed, counter)
+        K.dropout_fwd(x.data_ptr(), y.data_ptr(), mask, rows, C, ld, pad_for(dt, C), rps, channel_mode, p, seed, counter, dt=dt)
         K.counter_bump(counter)
-        ctx.args = (p, rows, C, x.dim() == 4, tuple(x.shape))
+        ctx.args = (p, rows, C, x.dim() == 4, tuple(x.shape), dt)
         ctx.save_for_backward(mask)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         (mask,) = ctx.saved_tensors
-        p, rows, C, is4, shape = ctx.args
+        p, rows, C, is4, shape, dt = ctx.args
         if is4:
-            dy, ldd = as_act4(dy)
-            dx = new_act4(*shape, dy.device)
+            dy, ldd = as_act4(dy, dt)
+            dx = new_act4(*shape, dy.device, dt)
         else:
-            dy, ldd = as_act2(dy)
-            dx = new_act2(rows, C, dy.device)
-        K.dropout_bwd(dy.data_ptr(), mask, dx.data_ptr(), rows, C, ldd, pad8(C), p)
+            dy, ldd = as_act2(dy, dt)
+            dx = new_act2(rows, C, dy.device, dt)
+        K.dropout_bwd(dy.data_ptr(), mask, dx.data_ptr(), rows, C, ldd, pad_for(dt, C), p, dt=dt)
         return dx, None, None, None, None
 
 
@@ -675,7 +722,10 @@ def dropout(x, p=0.5, training=True, channel_mode=False, seed=0x5EED):
     """Element dropout (``F.dropout``) or, with ``channel_mode``, ``Dropout2d`` (whole channels per sample)."""
     if not training or p == 0.0:
         return x
-    if not x.is_cuda or x.dtype != torch.bfloat16:
+    if not x.is_cuda:
+        return F.dropout2d(x, p, True) if channel_mode else F.dropout(x, p, True)
+    if x.dtype not in (BF16, F32) or x.dim() not in (2, 4):
+        _warn_once("dropout", f"dropout on a {x.dtype} {x.dim()}-D CUDA tensor runs the ATen kernel")
         return F.dropout2d(x, p, True) if channel_mode else F.dropout(x, p, True)
     return _DropoutFn.apply(x, float(p), bool(channel_mode), int(seed), _counter_for(x.device))
 
@@ -688,13 +738,13 @@ class _BatchNormFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, residual, weight, bias, cfg):
-        x, ldx = as_act4(x)
+        x, ldx = as_act4(x, BF16)
         B, C, H, W = x.shape
         M = B * H * W
         dev = x.device
         res_ptr, ldr = 0, 0
         if residual is not None:
-            residual, ldr = as_act4(residual)
+            residual, ldr = as_act4(residual, BF16)
             res_ptr = residual.data_ptr()
         y = new_act4(B, C, H, W, dev)
         # Persistent per-layer scratch [sums | dsum]: each half is re-zeroed by the kernel that runs after its consumer
@@ -726,7 +776,7 @@ class _BatchNormFn(torch.autograd.Function):
         B, C, H, W, ldx = ctx.dims
         M = B * H * W
         dev = dout.device
-        dout, ldd = as_act4(dout)
+        dout, ldd = as_act4(dout, BF16)
         ldc = pad8(C)
         sums, dsum = ctx.scratch[: 2 * C], ctx.scratch[2 * C:]
         need_g = cfg.relu or ctx.has_res
@@ -752,11 +802,11 @@ class _BatchNormFn(torch.autograd.Function):
 class _BatchNormEvalFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, residual, weight, bias, cfg):
-        x, ldx = as_act4(x)
+        x, ldx = as_act4(x, BF16)
         B, C, H, W = x.shape
         res_ptr, ldr = 0, 0
         if residual is not None:
-            residual, ldr = as_act4(residual)
+            residual, ldr = as_act4(residual, BF16)
             res_ptr = residual.data_ptr()
         y = new_act4(B, C, H, W, x.device)
         stats = torch.cat([cfg.running_mean, torch.rsqrt(cfg.running_var + cfg.eps)]).float()
@@ -772,6 +822,11 @@ class _BatchNormEvalFn(torch.autograd.Function):
 def batch_norm(x, weight, bias, running_mean, running_var, training=True, momentum=0.1, eps=1e-5, residual=None, relu=False, wsink=None,
                bsink=None, state=None):
     """``relu(batch_norm(x) + residual)`` (residual / ReLU optional) in two kernels forward, two backward."""
+    if x.is_cuda and x.dtype == F32 and act4_pitch(x, F32) is not None:
+        raise NotImplementedError("batch norm has no fp32-activation (tf32) kernels: the tf32 compute dtype covers the reference's models "
+                                  "(LeNet, AlexNet); the ResNets run in bf16")
+    if x.is_cuda and (x.shape[1] % 8 != 0 or x.shape[1] > 2048):
+        _warn_once("batch_norm", f"batch_norm with C={x.shape[1]} (needs C % 8 == 0 and C <= 2048) runs the ATen kernel in fp32")
     if not x.is_cuda or x.shape[1] % 8 != 0 or x.shape[1] > 2048:
         y = F.batch_norm(x.float() if x.is_cuda else x, running_mean, running_var, weight, bias, training, momentum, eps)
         if residual is not None:
@@ -788,7 +843,7 @@ def batch_norm(x, weight, bias, running_mean, running_var, training=True, moment
 class _AvgPoolFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x):
-        x, ldx = as_act4(x)
+        x, ldx = as_act4(x, BF16)
         B, C, H, W = x.shape
         y = new_act2(B, C, x.device)
         K.avgpool_fwd(x.data_ptr(), ldx, y.data_ptr(), pad8(C), B, H * W, C)
@@ -798,7 +853,7 @@ class _AvgPoolFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         B, C, H, W = ctx.dims
-        dy, ldd = as_act2(dy)
+        dy, ldd = as_act2(dy, BF16)
         dx = new_act4(B, C, H, W, dy.device)
         K.avgpool_bwd(dy.data_ptr(), ldd, dx.data_ptr(), pad8(C), B, H * W, C)
         return dx
@@ -806,7 +861,9 @@ class _AvgPoolFn(torch.autograd.Function):
 
 def global_avg_pool(x):
     """``adaptive_avg_pool2d(x, 1).flatten(1)``: [B, C, H, W] -> [B, C]."""
-    if not x.is_cuda or x.shape[1] % 8 != 0:
+    if x.is_cuda and (x.shape[1] % 8 != 0 or x.dtype != BF16):
+        _warn_once("global_avg_pool", f"global_avg_pool on a {x.dtype} tensor with C={x.shape[1]} (needs bf16, C % 8 == 0) runs the ATen kernel")
+    if not x.is_cuda or x.shape[1] % 8 != 0 or x.dtype != BF16:
         return x.float().mean(dim=(2, 3)).to(x.dtype)
     return _AvgPoolFn.apply(x)
 
@@ -825,8 +882,8 @@ class _XentFn(torch.autograd.Function):
         else:
             logits = logits.float().contiguous() if (logits.dtype != torch.float32 or logits.stride(1) != 1) else logits
             ldl = logits.stride(0) if B > 1 else C
-            dlogits = torch.empty((B, C), dtype=torch.float32, device=logits.device)
-            ldd = C
+            dlogits = new_act2(B, C, logits.device, F32)       # padded rows: the gradient is a legal GEMM operand of the tf32 path as is
+            ldd = pad_for(F32, C)
         need_grad = ctx.needs_input_grad[0]
         K.softmax_xent(logits, labels, metrics, dlogits if need_grad else None, B, C, ldl, ldd)
         ctx.save_for_backward(dlogits if need_grad else None)
@@ -838,10 +895,7 @@ class _XentFn(torch.autograd.Function):
         (dlogits,) = ctx.saved_tensors
         B, C, ldd = ctx.dims
         if not _state.unit_loss_grad:
-            if dlogits.dtype == torch.bfloat16:
-                K.scale_rows(dlogits, g.reshape(1).float(), B, C, ldd)
-            else:
-                dlogits = dlogits * g
+            K.scale_rows(dlogits, g.reshape(1).float(), B, C, ldd)
         return dlogits, None, None
 
 

@@ -3,9 +3,13 @@
 Each wrapper takes torch tensors that already have the right dtype/layout, extracts raw pointers and
 pitches and launches on the current CUDA stream.  Layout conventions (see ``csrc/conv_ops.cu``):
 
-* activations: bf16 channels-last, logical ``[B, C, H, W]`` stored ``[B, H, W, ld]`` (``ld >= C``, ``ld % 8 == 0``);
-* 2-D activations: bf16 ``[rows, C]`` with row pitch ``ld``;
-* GEMM weights ("shadows"): bf16 ``[Cout, Kpad]`` with K ordered ``(kh, kw, cin)``.
+* activations: channels-last, logical ``[B, C, H, W]`` stored ``[B, H, W, ld]`` (``ld >= C``, rows padded to 16 bytes);
+* 2-D activations: ``[rows, C]`` with row pitch ``ld``;
+* GEMM weights ("shadows"): ``[Cout, Kpad]`` with K ordered ``(kh, kw, cin)``.
+
+Two compute dtypes share every wrapper through the ``dt`` argument: ``torch.bfloat16`` (bf16 operands and activations,
+``ld % 8 == 0``) and ``torch.float32`` (the tf32 path: fp32 activations and weights read by the tensor cores as tf32,
+``ld % 4 == 0`` — the precision of the reference, example/main.py:41,53-54,70-73).
 """
 from __future__ import annotations
 
@@ -26,26 +30,55 @@ def pad8(n: int) -> int:
     return (n + 7) // 8 * 8
 
 
+BF16, F32 = torch.bfloat16, torch.float32
+
+
+def pad_for(dt, n: int) -> int:
+    """Row length padded to a whole number of 16-byte granules of ``dt`` (8 bf16 / 4 fp32)."""
+    return (n + 3) // 4 * 4 if dt == torch.float32 else (n + 7) // 8 * 8
+
+
+def kblock(dt) -> int:
+    """Elements of one 128-byte GEMM k-block: 64 bf16 or 32 fp32 (tf32)."""
+    return 32 if dt == torch.float32 else 64
+
+
+def _sfx(dt) -> str:
+    return "f32" if dt == torch.float32 else "bf16"
+
+
 def gemm(a: torch.Tensor, lda: int, a_mn: bool, b: torch.Tensor, ldb: int, b_mn: bool, M: int, N: int, K: int, out: torch.Tensor,
          ldo: int, bias=None, relu: bool = False, split_k: int = 1, atomic: bool = False, perm_cin: int = 0, perm_khw: int = 0,
          tile_n: int = 0) -> None:
-    """``out[M,N] (+)= A[M,K] @ B[N,K]^T`` on the tcgen05 path (see ``dmlb_gemm_bf16``)."""
+    """``out[M,N] (+)= A[M,K] @ B[N,K]^T`` on the tcgen05 path (``dmlb_gemm_bf16``; fp32 operands: ``dmlb_gemm_tf32``)."""
+    if a.dtype == torch.float32:
+        if b.dtype != torch.float32 or out.dtype != torch.float32:
+            raise TypeError("tf32 GEMM: A, B and out must all be fp32")
+        _call("dmlb_gemm_tf32", a.data_ptr(), lda, int(a_mn), b.data_ptr(), ldb, int(b_mn), M, N, K, out.data_ptr(), ldo,
+              bias.data_ptr() if bias is not None else None, int(relu), split_k, int(atomic), perm_cin, perm_khw, tile_n, stream_ptr())
+        return
     _call("dmlb_gemm_bf16", a.data_ptr(), lda, int(a_mn), b.data_ptr(), ldb, int(b_mn), M, N, K, out.data_ptr(),
           int(out.dtype == torch.float32), ldo, bias.data_ptr() if bias is not None else None, int(relu), split_k, int(atomic),
           perm_cin, perm_khw, tile_n, stream_ptr())
 
 
 def conv_implicit(kind: int, act_ptr: int, ld_act: int, B, Ha, Wa, Ca, other_ptr: int, ld_other: int, KH, KW, SH, SW, PH, PW, n_out: int,
-                  out: torch.Tensor, ldo: int, bias=None, relu: bool = False, split_k: int = 1, atomic: bool = False, tile_n: int = 0) -> None:
-    """Implicit-GEMM convolution through TMA im2col (``dmlb_conv_implicit_bf16``): kind 0 fprop, 1 wgrad, 2 dgrad."""
+                  out: torch.Tensor, ldo: int, bias=None, relu: bool = False, split_k: int = 1, atomic: bool = False, tile_n: int = 0,
+                  dt=torch.bfloat16) -> None:
+    """Implicit-GEMM convolution through TMA im2col (``dmlb_conv_implicit_bf16`` / ``_tf32``): kind 0 fprop, 1 wgrad, 2 dgrad."""
+    if dt == torch.float32:
+        _call("dmlb_conv_implicit_tf32", kind, act_ptr, ld_act, B, Ha, Wa, Ca, other_ptr, ld_other, KH, KW, SH, SW, PH, PW, n_out, out.data_ptr(),
+              ldo, bias.data_ptr() if bias is not None else None, int(relu), split_k, int(atomic), tile_n, stream_ptr())
+        return
     _call("dmlb_conv_implicit_bf16", kind, act_ptr, ld_act, B, Ha, Wa, Ca, other_ptr, ld_other, KH, KW, SH, SW, PH, PW, n_out, out.data_ptr(),
           int(out.dtype == torch.float32), ldo, bias.data_ptr() if bias is not None else None, int(relu), split_k, int(atomic), tile_n,
           stream_ptr())
 
 
-def pick_split_k(tiles: int, k_total: int, sms: int = 148, min_kblocks: int = 2) -> int:
+def pick_split_k(tiles: int, k_total: int, sms: int = 148, min_kblocks: int = 2, bk: int = 64) -> int:
     """Split-K factor that fills the SMs when the output has few tiles (weight gradients, tiny-M fprop)."""
-    nkb = (k_total + 63) // 64
+    nkb = (k_total + bk - 1) // bk
+    min_kblocks = min_kblocks * (64 // bk)
     if tiles >= sms or nkb <= min_kblocks:
         return 1
     want = max(1, (sms + tiles - 1) // tiles)
@@ -122,36 +155,37 @@ def conv_implicit_fin(kind: int, act_ptr: int, ld_act: int, B, Ha, Wa, Ca, other
 
 
 def splitk_finish(ws: torch.Tensor, ldw: int, bias, relu: bool, y_ptr: int, ldy: int, M: int, N: int, pool2=None, pooled_ptr: int = 0,
-                  ldp: int = 0) -> None:
+                  ldp: int = 0, dt=torch.bfloat16) -> None:
     B, H, W = pool2 if pool2 is not None else (0, 0, 0)
-    _call("dmlb_splitk_finish", ws.data_ptr(), ldw, bias.data_ptr() if bias is not None else None, int(relu), y_ptr, ldy, M, N,
+    _call("dmlb_splitk_finish_f32" if dt == torch.float32 else "dmlb_splitk_finish", ws.data_ptr(), ldw, bias.data_ptr() if bias is not None else None, int(relu), y_ptr, ldy, M, N,
           int(pool2 is not None), B, H, W, pooled_ptr or None, ldp, stream_ptr())
 
 
-def fprop_split(M: int, N: int, K: int, sms: int = 148) -> int:
+def fprop_split(M: int, N: int, K: int, sms: int = 148, bk: int = 64) -> int:
     """Split-K factor for a forward GEMM, 1 when the plain fused-epilogue kernel is the better choice."""
     bn = 128 if N > 64 else (64 if N > 32 else 32)
     tiles = ((M + 127) // 128) * ((N + bn - 1) // bn)
-    nkb = (K + 63) // 64
-    if tiles * 3 > sms or nkb < 8:
+    nkb = (K + bk - 1) // bk
+    r = 64 // bk                      # same byte thresholds for both element sizes
+    if tiles * 3 > sms or nkb < 8 * r:
         return 1
-    return max(1, min(sms // tiles, nkb // 2))
+    return max(1, min(sms // tiles, nkb // (2 * r)))
 
 
 def im2col_nhwc(x_ptr: int, col: torch.Tensor, B, H, W, C, ldx, KH, KW, SH, SW, PH, PW, Kpad) -> None:
-    _call("dmlb_im2col_nhwc_bf16", x_ptr, col.data_ptr(), B, H, W, C, ldx, KH, KW, SH, SW, PH, PW, Kpad, stream_ptr())
+    _call("dmlb_im2col_nhwc_" + _sfx(col.dtype), x_ptr, col.data_ptr(), B, H, W, C, ldx, KH, KW, SH, SW, PH, PW, Kpad, stream_ptr())
 
 
 def im2col_nchw_f32(x: torch.Tensor, col: torch.Tensor, B, H, W, C, KH, KW, SH, SW, PH, PW, Kpad) -> None:
-    _call("dmlb_im2col_nchw_f32", x.data_ptr(), col.data_ptr(), B, H, W, C, KH, KW, SH, SW, PH, PW, Kpad, stream_ptr())
+    _call("dmlb_im2col_nchw_f32_f32" if col.dtype == torch.float32 else "dmlb_im2col_nchw_f32", x.data_ptr(), col.data_ptr(), B, H, W, C, KH, KW, SH, SW, PH, PW, Kpad, stream_ptr())
 
 
 def col2im_nhwc(dcol: torch.Tensor, dx_ptr: int, B, H, W, C, ldx, KH, KW, SH, SW, PH, PW, Kpad) -> None:
-    _call("dmlb_col2im_nhwc_bf16", dcol.data_ptr(), dx_ptr, B, H, W, C, ldx, KH, KW, SH, SW, PH, PW, Kpad, stream_ptr())
+    _call("dmlb_col2im_nhwc_" + _sfx(dcol.dtype), dcol.data_ptr(), dx_ptr, B, H, W, C, ldx, KH, KW, SH, SW, PH, PW, Kpad, stream_ptr())
 
 
-def maxpool_fwd(x_ptr: int, y_ptr: int, B, H, W, C, ldx, ldo, k, s, p) -> None:
-    _call("dmlb_maxpool_fwd_bf16", x_ptr, y_ptr, B, H, W, C, ldx, ldo, k, s, p, stream_ptr())
+def maxpool_fwd(x_ptr: int, y_ptr: int, B, H, W, C, ldx, ldo, k, s, p, dt=torch.bfloat16) -> None:
+    _call("dmlb_maxpool_fwd_" + _sfx(dt), x_ptr, y_ptr, B, H, W, C, ldx, ldo, k, s, p, stream_ptr())
 
 
 def maxpool_fwd_idx(x_ptr: int, y_ptr: int, idx: torch.Tensor, B, H, W, C, ldx, ldo, k, s, p) -> None:
@@ -162,18 +196,18 @@ def maxpool_bwd_idx(dout_ptr: int, idx: torch.Tensor, dx_ptr: int, B, H, W, C, l
     _call("dmlb_maxpool_bwd_idx_bf16", dout_ptr, idx.data_ptr(), dx_ptr, B, H, W, C, lddx, ldd, k, s, p, stream_ptr())
 
 
-def act_bwd(y_ptr: int, dout_ptr: int, dy_ptr: int, dbias, B, H, W, C, ldy, ldd, pool, relu: bool) -> None:
+def act_bwd(y_ptr: int, dout_ptr: int, dy_ptr: int, dbias, B, H, W, C, ldy, ldd, pool, relu: bool, dt=torch.bfloat16) -> None:
     k, s, p = pool if pool is not None else (1, 1, 0)
-    _call("dmlb_act_bwd_bf16", y_ptr, dout_ptr, dy_ptr, dbias.data_ptr() if dbias is not None else None, B, H, W, C, ldy, ldd,
+    _call("dmlb_act_bwd_" + _sfx(dt), y_ptr, dout_ptr, dy_ptr, dbias.data_ptr() if dbias is not None else None, B, H, W, C, ldy, ldd,
           int(pool is not None), k, s, p, int(relu), stream_ptr())
 
 
-def relu_fwd(x_ptr, y_ptr, rows, C, ldx, ldy) -> None:
-    _call("dmlb_relu_fwd_bf16", x_ptr, y_ptr, rows, C, ldx, ldy, stream_ptr())
+def relu_fwd(x_ptr, y_ptr, rows, C, ldx, ldy, dt=torch.bfloat16) -> None:
+    _call("dmlb_relu_fwd_" + _sfx(dt), x_ptr, y_ptr, rows, C, ldx, ldy, stream_ptr())
 
 
-def relu_bwd(y_ptr, dy_ptr, dx_ptr, rows, C, ldy, lddy, lddx) -> None:
-    _call("dmlb_relu_bwd_bf16", y_ptr, dy_ptr, dx_ptr, rows, C, ldy, lddy, lddx, stream_ptr())
+def relu_bwd(y_ptr, dy_ptr, dx_ptr, rows, C, ldy, lddy, lddx, dt=torch.bfloat16) -> None:
+    _call("dmlb_relu_bwd_" + _sfx(dt), y_ptr, dy_ptr, dx_ptr, rows, C, ldy, lddy, lddx, stream_ptr())
 
 
 def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, metrics: torch.Tensor, dlogits, B, C, ldl, ldd) -> None:
@@ -182,7 +216,7 @@ def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, metrics: torch.Tens
 
 
 def scale_rows(x: torch.Tensor, scale: torch.Tensor, rows, C, ld) -> None:
-    _call("dmlb_scale_rows_bf16", x.data_ptr(), scale.data_ptr(), rows, C, ld, stream_ptr())
+    _call("dmlb_scale_rows_" + _sfx(x.dtype), x.data_ptr(), scale.data_ptr(), rows, C, ld, stream_ptr())
 
 
 def sgd_flat(params: torch.Tensor, grads: torch.Tensor, acc, mom, n: int, lr_dev: torch.Tensor, mu: float = 0.0, wd: float = 0.0,
@@ -192,9 +226,9 @@ def sgd_flat(params: torch.Tensor, grads: torch.Tensor, acc, mom, n: int, lr_dev
           float(wd), int(zero_grads), stream_ptr())
 
 
-def refresh_shadows(table: torch.Tensor, n_entries: int) -> None:
+def refresh_shadows(table: torch.Tensor, n_entries: int, dt=torch.bfloat16) -> None:
     """Absolute-address table: base pointers are NULL, offsets are addresses / element size."""
-    _call("dmlb_refresh_shadows", None, None, table.data_ptr(), n_entries, stream_ptr())
+    _call("dmlb_refresh_shadows_f32" if dt == torch.float32 else "dmlb_refresh_shadows", None, None, table.data_ptr(), n_entries, stream_ptr())
 
 
 def cast_f32_bf16(x: torch.Tensor, y_ptr: int, rows, C, ldx, ldy) -> None:
@@ -205,13 +239,14 @@ def cast_bf16_f32(x_ptr: int, y: torch.Tensor, rows, C, ldx, ldy) -> None:
     _call("dmlb_cast_bf16_f32", x_ptr, y.data_ptr(), rows, C, ldx, ldy, stream_ptr())
 
 
-def dropout_fwd(x_ptr, y_ptr, mask: torch.Tensor, rows, C, ldx, ldy, rows_per_sample, channel_mode, p, seed, step: torch.Tensor) -> None:
-    _call("dmlb_dropout_fwd_bf16", x_ptr, y_ptr, mask.data_ptr(), rows, C, ldx, ldy, rows_per_sample, int(channel_mode), float(p),
+def dropout_fwd(x_ptr, y_ptr, mask: torch.Tensor, rows, C, ldx, ldy, rows_per_sample, channel_mode, p, seed, step: torch.Tensor,
+                dt=torch.bfloat16) -> None:
+    _call("dmlb_dropout_fwd_" + _sfx(dt), x_ptr, y_ptr, mask.data_ptr(), rows, C, ldx, ldy, rows_per_sample, int(channel_mode), float(p),
           int(seed) & 0xFFFFFFFFFFFFFFFF, step.data_ptr(), stream_ptr())
 
 
-def dropout_bwd(dy_ptr, mask: torch.Tensor, dx_ptr, rows, C, lddy, lddx, p) -> None:
-    _call("dmlb_dropout_bwd_bf16", dy_ptr, mask.data_ptr(), dx_ptr, rows, C, lddy, lddx, float(p), stream_ptr())
+def dropout_bwd(dy_ptr, mask: torch.Tensor, dx_ptr, rows, C, lddy, lddx, p, dt=torch.bfloat16) -> None:
+    _call("dmlb_dropout_bwd_" + _sfx(dt), dy_ptr, mask.data_ptr(), dx_ptr, rows, C, lddy, lddx, float(p), stream_ptr())
 
 
 def counter_bump(counter: torch.Tensor) -> None:

@@ -83,8 +83,11 @@ class FlatArena:
         self.offsets: Dict[str, Tuple[int, int]] = {}
         self._bound = False
         self.channels_last = self.params.is_cuda
-        # flat bf16 mirror of the arena (same offsets): the optimizer kernel writes it alongside the fp32 masters
-        self.shadow = torch.zeros(self.padded, dtype=torch.bfloat16, device=self.device) if self.params.is_cuda else None
+        # flat bf16 mirror of the arena (same offsets): the optimizer kernel writes it alongside the fp32 masters.  A tf32 model reads
+        # the fp32 masters themselves and keeps no mirror.
+        self.compute_dtype = getattr(model, "_dmlb_compute_dtype", torch.bfloat16)
+        want_mirror = self.params.is_cuda and self.compute_dtype == torch.bfloat16
+        self.shadow = torch.zeros(self.padded, dtype=torch.bfloat16, device=self.device) if want_mirror else None
         self.bind()
 
     def is_bound(self) -> bool:
@@ -131,7 +134,7 @@ class FlatArena:
                 mod._wsink = mod.weight.grad
                 mod._bsink = mod.bias.grad if getattr(mod, "bias", None) is not None else None
                 name = by_param.get(id(mod.weight))
-                mod._arena_slot = (self, self.offsets[name][0]) if (name is not None and self.shadow is not None) else None
+                mod._arena_slot = (self, self.offsets[name][0]) if (name is not None and self.params.is_cuda) else None
 
     def rebind_grads(self) -> None:
         """Re-attach ``.grad`` views (after a foreign ``zero_grad(set_to_none=True)``)."""

@@ -109,7 +109,7 @@ def main(args):
         torch.cuda.set_device(device)
     trainloader, testloader = get_dataset(args)
     torch.manual_seed(args.seed)
-    net = build_model(args.model, in_channels=args.in_channels, input_hw=args.input_hw).to(device)
+    net = build_model(args.model, in_channels=args.in_channels, input_hw=args.input_hw, dtype=args.dtype).to(device)
     net.train()
     optimizer = make_optimizer(args, net)
     start_epoch = 0
@@ -271,6 +271,9 @@ def build_parser():
     # additive flags
     parser.add_argument("--model", default="alexnet", choices=MODEL_NAMES)
     parser.add_argument("--mode", default="async", choices=["async", "sync"])
+    parser.add_argument("--dtype", default=None, choices=["tf32", "bf16"],
+                        help="CUDA compute dtype: tf32 = fp32 tensors with TF32 tensor-core products, the reference's own precision (default for "
+                        "lenet / alexnet); bf16 = bf16 operands and activations over fp32 masters (default for the resnets)")
     parser.add_argument("--momentum", type=float, default=0.0)
     parser.add_argument("--staleness", default=None, choices=[None, "none", "inverse", "exp"])
     parser.add_argument("--backend", default=None, help="torch.distributed backend (default: nccl with --cuda, gloo otherwise)")
