@@ -164,6 +164,14 @@ class TrainStep:
                 self._staged[slot].record(self._copy_stream)
             self.stream.wait_event(self._staged[slot])
             x, y = sx, sy
+        else:
+            # Device batch (e.g. utils.data.GpuResidentLoader): it was produced on the caller's current stream.  Order the step's
+            # D2D move behind that work, and keep the caching allocator from recycling the batch while this stream still reads it.
+            cur = torch.cuda.current_stream(self.device)
+            if cur.cuda_stream != self.stream.cuda_stream:
+                self.stream.wait_stream(cur)
+                x.record_stream(self.stream)
+                y.record_stream(self.stream)
         with torch.cuda.stream(self.stream):
             self.static_x.copy_(x, non_blocking=True)
             self.static_y.copy_(y, non_blocking=True)

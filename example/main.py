@@ -34,7 +34,7 @@ from asgd.optim import Asynchronous, FusedSGD, Synchronous
 from asgd.server import ParameterServer
 from distributed_ml_pytorch_b200.models import MODEL_NAMES, build_model
 from distributed_ml_pytorch_b200.ops import cross_entropy
-from distributed_ml_pytorch_b200.utils.checkpoint import load_checkpoint, save_checkpoint
+from distributed_ml_pytorch_b200.utils.checkpoint import load_model_state, load_optimizer_state, read_checkpoint, save_checkpoint
 from distributed_ml_pytorch_b200.utils import trace
 from distributed_ml_pytorch_b200.utils.csvlog import CSVLogger, log_path
 
@@ -111,11 +111,15 @@ def main(args):
     torch.manual_seed(args.seed)
     net = build_model(args.model, in_channels=args.in_channels, input_hw=args.input_hw, dtype=args.dtype).to(device)
     net.train()
-    optimizer = make_optimizer(args, net)
-    start_epoch = 0
+    start_epoch, resumed_opt = 0, None
     if args.resume:
-        meta = load_checkpoint(args.resume, net, optimizer)
+        # The model is restored BEFORE the optimizer exists: a distributed optimizer seeds the parameter server (the sharded masters
+        # on NVLink, the server rank's vector on gloo) from the model it is constructed with.
+        sd, meta, resumed_opt = read_checkpoint(args.resume)
+        load_model_state(net, sd)
         start_epoch = int(meta.get("epoch", -1)) + 1
+    optimizer = make_optimizer(args, net)
+    load_optimizer_state(optimizer, resumed_opt)
     scheduler = optim.lr_scheduler.LambdaLR(optimizer, lr_lambda=lambda epoch: 1 / (epoch + 1))   # reference main.py:47-48
 
     rank = dist.get_rank() if (dist.is_available() and dist.is_initialized()) else None
@@ -166,8 +170,9 @@ def main(args):
         _sync_step(step_fn, device, before=False)
         if args.step_scheduler:
             scheduler.step()
-        if args.ckpt:
-            save_checkpoint(args.ckpt, net, optimizer, epoch=epoch)
+        ck = _ckpt_path(args, rank, optimizer)
+        if ck:
+            save_checkpoint(ck, net, optimizer, epoch=epoch)
     print("wrote", logger.to_csv())
     if hasattr(optimizer, "finish"):
         optimizer.finish()
@@ -181,6 +186,19 @@ def main(args):
             optimizer.pushes, optimizer.pulls, optimizer.pushes * n_bytes / 1e6, optimizer.pulls * n_bytes / 1e6,
             (optimizer.pushes + optimizer.pulls) * n_bytes / 1e6 / wall, wall, " | staleness: {}".format(stats) if stats else ""))
     print("Finished Training")
+
+
+def _ckpt_path(args, rank, optimizer):
+    """Who writes --ckpt.  One process: the path itself.  NVLink transport / synchronous mode: rank 0 alone (it writes the server's
+    parameters, every replica of a synchronous run is identical).  CPU/gloo asynchronous: the server rank owns ``<path>`` (its final
+    parameters), every worker writes its replica + optimizer state to ``<path>.rank<r>`` — no two processes share a file."""
+    if not args.ckpt:
+        return None
+    if rank is None:
+        return args.ckpt
+    if getattr(optimizer, "transport", None) == "gloo":
+        return f"{args.ckpt}.rank{rank}"
+    return args.ckpt if rank == 0 else None
 
 
 def _trace_path(path, rank):

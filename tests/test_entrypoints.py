@@ -137,3 +137,26 @@ def test_trace_flag_writes_chrome_traces_for_server_and_workers(tmp_path):
     assert {"forward+loss", "backward", "optimizer.step"} <= set(names)
     assert all(e["dur"] >= 0 for e in worker if e["ph"] == "X")
     assert sum(e["name"] == "GradientUpdate" for e in server) == 3 and any(e["name"] == "ParameterRequest" for e in server)
+
+
+def test_async_gloo_resume_reseeds_the_server(tmp_path):
+    """--resume in asynchronous distributed mode (1 gloo server + 1 worker): the worker loads the checkpoint before it builds the optimizer,
+    so the server starts from the resumed parameters and the first pull does not throw them away.  Each process writes its own file."""
+    import torch
+    from distributed_ml_pytorch_b200.parallel.launcher import free_port
+    base = ["--model", "lenet", "--steps-per-epoch", "6", "--log-interval", "1000", "--test-batch-size", "50", "--synthetic", "--num-push", "2",
+            "--num-pull", "2", "--lr", "0.05", "--ckpt", str(tmp_path / "ck.pt")]
+    r = _run([sys.executable, os.path.join(ROOT, "run-pytorch.py"), "--local", "2", "--cpu", "--port", str(free_port()), "--", "--epochs", "1"] + base,
+             cwd=tmp_path)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    server1 = torch.load(tmp_path / "ck.pt", weights_only=False)               # the server rank's final parameters (plain state_dict)
+    worker1 = torch.load(tmp_path / "ck.pt.rank1", weights_only=False)         # the worker's replica + optimizer state
+    assert worker1["format"] == "dmlb-checkpoint-v2" and worker1["meta"]["epoch"] == 0 and worker1["optimizer"]["layout"] == "logical"
+    assert worker1["optimizer"]["accumulated_gradients"].numel() == 62006
+    # resume from the server's parameters, zero further steps of learning rate: whatever the server holds at the end must be them
+    r = _run([sys.executable, os.path.join(ROOT, "run-pytorch.py"), "--local", "2", "--cpu", "--port", str(free_port()), "--", "--epochs", "1",
+              "--resume", str(tmp_path / "ck.pt")] + [a if a != "0.05" else "0.0" for a in base], cwd=tmp_path)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    server2 = torch.load(tmp_path / "ck.pt", weights_only=False)
+    for k in server1:
+        assert torch.equal(server1[k], server2[k]), k
