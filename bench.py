@@ -165,6 +165,8 @@ def _measure(args, dtype, rank, local_rank, world, device, steps, warmup, with_e
     res["clocks"] = sampler.stop()
     if hasattr(optimizer, "finish"):
         optimizer.finish()
+    if hasattr(optimizer, "close"):
+        optimizer.close()
     del ts, optimizer, model, dx, dy, hx, hy
     torch.cuda.empty_cache()
     return res

@@ -183,10 +183,13 @@ __global__ void __launch_bounds__(256) owner_apply_kernel(float* __restrict__ ma
 // flags layout per GPU (uint32): [0, kMaxPeers) start flags, [kMaxPeers, 2*kMaxPeers) done flags,
 // [2*kMaxPeers] epoch, [2*kMaxPeers + 1] local block counter.   Every flag is written remotely and polled locally.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void spin_until_ge(const uint32_t* flag, uint32_t want) {
+// Every rank must reach the same bucket launch within `limit` cycles of the first one (host: DMLB_BARRIER_TIMEOUT_S, default 1800 s —
+// the process-group timeout of example/main.py): a peer that stalls in its data loader or a checkpoint write only delays the others;
+// a peer that died turns into a CUDA error on the survivors after the limit instead of a hang.
+__device__ __forceinline__ void spin_until_ge(const uint32_t* flag, uint32_t want, long long limit) {
     const long long t0 = clock64();
     while (ld_acquire_sys_u32(flag) < want) {
-        if (clock64() - t0 > DMLB_SPIN_LIMIT_CYCLES) {
+        if (clock64() - t0 > limit) {
             printf("dmlb: cross-GPU barrier timed out (block %d thread %d want %u have %u)\n", blockIdx.x, threadIdx.x, want, *flag);
             __trap();
         }
@@ -195,14 +198,15 @@ __device__ __forceinline__ void spin_until_ge(const uint32_t* flag, uint32_t wan
 
 __global__ void __launch_bounds__(512) sync_rs_update_ag_kernel(PeerTable grads, PeerTable params, PeerTable flags, float* __restrict__ mom,
                                                                 int rank, int world, long long base, long long slice_len,
-                                                                const float* __restrict__ lr_ptr, float mu, float wd, float grad_scale) {
+                                                                const float* __restrict__ lr_ptr, float mu, float wd, float grad_scale,
+                                                                long long spin_limit) {
     uint32_t* my_flags = static_cast<uint32_t*>(flags.ptr[rank]);
     const uint32_t epoch = my_flags[2 * kMaxPeers] + 1u;   // bumped once per launch by the last block, below
     // ---- start barrier: tell every peer that my gradients are final, wait for theirs ----
     if (blockIdx.x == 0 && threadIdx.x < world) {
         st_release_sys_u32(static_cast<uint32_t*>(flags.ptr[threadIdx.x]) + rank, epoch);
     }
-    if (threadIdx.x < world) spin_until_ge(my_flags + threadIdx.x, epoch);
+    if (threadIdx.x < world) spin_until_ge(my_flags + threadIdx.x, epoch, spin_limit);
     __syncthreads();
 
     const float lr = *lr_ptr;
@@ -244,7 +248,7 @@ __global__ void __launch_bounds__(512) sync_rs_update_ag_kernel(PeerTable grads,
     if (s_last) {
         if (threadIdx.x < world) {
             st_release_sys_u32(static_cast<uint32_t*>(flags.ptr[threadIdx.x]) + kMaxPeers + rank, epoch);
-            spin_until_ge(my_flags + kMaxPeers + threadIdx.x, epoch);
+            spin_until_ge(my_flags + kMaxPeers + threadIdx.x, epoch, spin_limit);
         }
         __syncthreads();
         if (threadIdx.x == 0) {
@@ -261,11 +265,11 @@ __global__ void __launch_bounds__(512) sync_rs_update_ag_kernel(PeerTable grads,
 __global__ void __launch_bounds__(512) sync_nvls_kernel(const float* __restrict__ mc_grads, float* __restrict__ mc_params,
                                                         const float* __restrict__ params_local, PeerTable flags, float* __restrict__ mom, int rank,
                                                         int world, long long base, long long slice_len, const float* __restrict__ lr_ptr, float mu,
-                                                        float wd, float grad_scale) {
+                                                        float wd, float grad_scale, long long spin_limit) {
     uint32_t* my_flags = static_cast<uint32_t*>(flags.ptr[rank]);
     const uint32_t epoch = my_flags[2 * kMaxPeers] + 1u;
     if (blockIdx.x == 0 && threadIdx.x < world) st_release_sys_u32(static_cast<uint32_t*>(flags.ptr[threadIdx.x]) + rank, epoch);
-    if (threadIdx.x < world) spin_until_ge(my_flags + threadIdx.x, epoch);
+    if (threadIdx.x < world) spin_until_ge(my_flags + threadIdx.x, epoch, spin_limit);
     __syncthreads();
 
     const float lr = *lr_ptr;
@@ -307,7 +311,7 @@ __global__ void __launch_bounds__(512) sync_nvls_kernel(const float* __restrict_
     if (s_last) {
         if (threadIdx.x < world) {
             st_release_sys_u32(static_cast<uint32_t*>(flags.ptr[threadIdx.x]) + kMaxPeers + rank, epoch);
-            spin_until_ge(my_flags + kMaxPeers + threadIdx.x, epoch);
+            spin_until_ge(my_flags + kMaxPeers + threadIdx.x, epoch, spin_limit);
         }
         __syncthreads();
         if (threadIdx.x == 0) {
@@ -324,6 +328,20 @@ static inline int comm_grid(long long work_items, int threads) {
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     return static_cast<int>(blocks);
+}
+
+// Cross-GPU barrier time-out in SM clock cycles: DMLB_BARRIER_TIMEOUT_S seconds (default 1800) at the device's peak clock.
+static long long barrier_spin_limit() {
+    static long long limit = 0;
+    if (limit == 0) {
+        double secs = 1800.0;
+        const char* e = getenv("DMLB_BARRIER_TIMEOUT_S");
+        if (e != nullptr && atof(e) > 0.0) secs = atof(e);
+        int dev = 0, khz = 2000000;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev);
+        limit = static_cast<long long>(secs * 1e3 * static_cast<double>(khz));
+    }
+    return limit;
 }
 
 static int fill_table(PeerTable* t, void* const* ptrs, int world) {
@@ -412,7 +430,7 @@ extern "C" int dmlb_sync_rs_update_ag_range(void* const* grad_ptrs, void* const*
     if (blocks > dmlb_sm_count()) blocks = dmlb_sm_count();
     if (max_blocks > 0 && blocks > max_blocks) blocks = max_blocks;
     sync_rs_update_ag_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(g, p, f, mom, rank, world, base, n, lr_ptr, mu, wd,
-                                                                                   grad_scale);
+                                                                                   grad_scale, barrier_spin_limit());
     DMLB_LAUNCH_CHECK();
     return 0;
 }
@@ -435,7 +453,7 @@ extern "C" int dmlb_sync_nvls_range(const float* mc_grads, float* mc_params, con
     if (blocks > dmlb_sm_count()) blocks = dmlb_sm_count();
     if (max_blocks > 0 && blocks > max_blocks) blocks = max_blocks;
     sync_nvls_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(mc_grads, mc_params, params_local, f, mom, rank, world, base, n, lr_ptr,
-                                                                           mu, wd, grad_scale);
+                                                                           mu, wd, grad_scale, barrier_spin_limit());
     DMLB_LAUNCH_CHECK();
     return 0;
 }

@@ -157,7 +157,10 @@ class Asynchronous(ArenaOptimizer):
         self.master = self.master_sym.view(torch.float32, S)
         self.version = self.version_sym.view(torch.int32, cps)
         b, e = a.shards.bounds(pg.rank)
-        self.master.copy_(a.params[b:e])                       # owner's replica defines its shard
+        # One initial model for everybody (the reference: one worker's vector sets the server, Asynchronous.py:33-34): rank 0's
+        # replica is broadcast before the owners seed their shards, so differently seeded ranks do not start from a patchwork.
+        _broadcast_flat(a.params, pg.group, pg.world)
+        self.master.copy_(a.params[b:e])                       # owner's (now common) replica defines its shard
         self.pulled_ver = torch.zeros(pg.world * cps, dtype=torch.int32, device=a.params.device)
         self.stats = torch.zeros(4, dtype=torch.int32, device=a.params.device)
         if self._use_mailbox:
@@ -323,6 +326,20 @@ class Asynchronous(ArenaOptimizer):
                 torch.cuda.synchronize(self.arena.params.device)
                 self.peer.barrier()
 
+    def close(self) -> None:
+        """Release the NVLink-shared buffers (masters, mailboxes, flags) and their CUDA-IPC mappings.  Collective: every rank of the
+        group must call it, after :meth:`finish`.  The model and its arena stay usable; this optimizer does not."""
+        if self.transport != "peer" or self.peer is None:
+            return
+        for name in ("master", "version", "mailbox", "full", "busy"):
+            if hasattr(self, name):
+                setattr(self, name, None)
+        for name in ("master_sym", "version_sym", "mailbox_sym", "full_sym", "busy_sym"):
+            if hasattr(self, name):
+                setattr(self, name, None)
+        self.peer.close()
+        self.peer = None
+
     def server_parameters(self) -> torch.Tensor:
         """The server's current flat parameter vector (length N) as seen from this worker."""
         a = self.arena
@@ -340,6 +357,20 @@ class Asynchronous(ArenaOptimizer):
             return {}
         s = self.stats.tolist()
         return {"chunks_applied": s[0], "mean_staleness": (s[1] / s[0] if s[0] else 0.0), "max_staleness": s[2]}
+
+
+def _broadcast_flat(t: torch.Tensor, group, world: int, src: int = 0) -> None:
+    """Broadcast a flat device tensor from group rank ``src`` over the control-plane process group (one-off, at set-up)."""
+    if world <= 1 or not (dist.is_available() and dist.is_initialized()):
+        return
+    gsrc = dist.get_global_rank(group, src) if group is not None else src
+    try:
+        dist.broadcast(t, src=gsrc, group=group)
+    except RuntimeError:                      # a control plane without CUDA support (gloo): stage through the host
+        h = t.detach().cpu()
+        dist.broadcast(h, src=gsrc, group=group)
+        t.copy_(h)
+    torch.cuda.synchronize(t.device)
 
 
 def staleness_scale(mode: Optional[str], param: float, tau: int) -> float:

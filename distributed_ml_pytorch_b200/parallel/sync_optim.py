@@ -231,8 +231,19 @@ class Synchronous(ArenaOptimizer):
         return loss
 
     def finish(self) -> None:
-        if self.is_peer:
+        if self.is_peer and self.peer is not None:
             if self.overlap:
                 from ..ops import functional as OF
                 OF.remove_grad_ready_hook(self._on_grad_ready)
             self.peer.barrier()
+
+    def close(self) -> None:
+        """Release the shared arenas.  The model's parameters live IN them, so they are first moved to a private arena (values kept);
+        then the CUDA-IPC / symmetric-memory buffers are unmapped and freed.  Collective, call after :meth:`finish`."""
+        if not self.is_peer or self.peer is None:
+            return
+        torch.cuda.synchronize(self.arena.params.device)
+        self.arena = FlatArena(self.model, n_shards=1)          # copies the parameters out and re-points them
+        self.params_sym = self.grads_sym = self.flags_sym = None
+        self.peer.close()
+        self.peer = None

@@ -185,6 +185,8 @@ def main(args):
         print("pushes: {} | pulls: {} | {:.1f} MB pushed, {:.1f} MB pulled ({:.1f} MB/s of parameter traffic over {:.1f} s){}".format(
             optimizer.pushes, optimizer.pulls, optimizer.pushes * n_bytes / 1e6, optimizer.pulls * n_bytes / 1e6,
             (optimizer.pushes + optimizer.pulls) * n_bytes / 1e6 / wall, wall, " | staleness: {}".format(stats) if stats else ""))
+    if hasattr(optimizer, "close"):
+        optimizer.close()                 # NVLink-shared buffers and their IPC mappings
     print("Finished Training")
 
 

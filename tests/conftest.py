@@ -8,6 +8,10 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
+# cross-GPU barriers of the synchronous kernels: fail fast in tests (production default: 30 min, csrc/comm.cu)
+os.environ.setdefault("DMLB_BARRIER_TIMEOUT_S", "10")
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: test needs a CUDA device (run on the B200 box with -m gpu)")
 
