@@ -88,11 +88,16 @@ __global__ void __launch_bounds__(256) scale_rows_kernel(T* __restrict__ x, cons
 // lr is read from device memory so a captured CUDA graph follows LR-scheduler changes.
 // n must be a multiple of 4 (the arena pads to that).
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ params, float* __restrict__ grads, float* __restrict__ acc,
-                                                       float* __restrict__ mom, __nv_bfloat16* __restrict__ shadow, long long n4,
-                                                       const float* __restrict__ lr_ptr, float mu, float wd, int zero_grads) {
+// acc_slot (may be null): device location holding the address of the CURRENT accumulator.  The asynchronous optimizer double-buffers
+// its accumulator so a gradient push can drain the retired buffer on a communication stream while the next steps already
+// accumulate into the other one; reading the address from memory lets a captured CUDA graph follow the swap.
+__global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ params, float* __restrict__ grads, float* __restrict__ acc_direct,
+                                                       float* const* __restrict__ acc_slot, float* __restrict__ mom,
+                                                       __nv_bfloat16* __restrict__ shadow, long long n4, const float* __restrict__ lr_ptr,
+                                                       float mu, float wd, int zero_grads) {
     pdl_prologue();
     const float lr = *lr_ptr;
+    float* __restrict__ acc = acc_slot != nullptr ? *acc_slot : acc_direct;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
         float4 p = reinterpret_cast<float4*>(params)[i];
         float4 g = ld_stream_f32x4(grads + 4 * i);
@@ -263,8 +268,63 @@ extern "C" int dmlb_sgd_flat(float* params, float* grads, float* acc, float* mom
                              float wd, int zero_grads, void* stream) {
     DMLB_REQUIRE(n % 4 == 0, "flat SGD length must be a multiple of 4 (arena padding)");
     DMLB_REQUIRE(((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads)) & 15) == 0, "arena must be 16-byte aligned");
-    DMLB_CHECK_CUDA(launch_k(sgd_flat_kernel, flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream), params, grads, acc, mom, static_cast<__nv_bfloat16*>(shadow), n / 4, lr_ptr,
-                             mu, wd, zero_grads));
+    DMLB_CHECK_CUDA(launch_k(sgd_flat_kernel, flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream), params, grads, acc,
+                             static_cast<float* const*>(nullptr), mom, static_cast<__nv_bfloat16*>(shadow), n / 4, lr_ptr, mu, wd, zero_grads));
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+// dmlb_sgd_flat with the accumulator named indirectly: *acc_slot (device memory) is the buffer to accumulate -lr*g into.
+extern "C" int dmlb_sgd_flat_slot(float* params, float* grads, void* acc_slot, float* mom, void* shadow, long long n, const float* lr_ptr, float mu,
+                                  float wd, int zero_grads, void* stream) {
+    DMLB_REQUIRE(n % 4 == 0, "flat SGD length must be a multiple of 4 (arena padding)");
+    DMLB_REQUIRE(((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads)) & 15) == 0, "arena must be 16-byte aligned");
+    DMLB_REQUIRE(acc_slot != nullptr, "acc_slot is required (use dmlb_sgd_flat for a direct accumulator)");
+    DMLB_CHECK_CUDA(launch_k(sgd_flat_kernel, flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream), params, grads, static_cast<float*>(nullptr),
+                             static_cast<float* const*>(acc_slot), mom, static_cast<__nv_bfloat16*>(shadow), n / 4, lr_ptr, mu, wd, zero_grads));
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+namespace dmlb {
+__global__ void store_u64_kernel(unsigned long long* slot, unsigned long long value) { *slot = value; }
+
+// params = pulled + unpushed;  shadow = bf16(params)   (n4 float4 groups; unpushed / shadow may be null)
+__global__ void __launch_bounds__(256) apply_pull_kernel(float* __restrict__ params, const float* __restrict__ pulled,
+                                                         float* const* __restrict__ unpushed_slot, __nv_bfloat16* __restrict__ shadow, long long n4) {
+    pdl_prologue();
+    const float* __restrict__ unpushed = unpushed_slot != nullptr ? *unpushed_slot : nullptr;
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
+        float4 p = ld_stream_f32x4(pulled + 4 * i);
+        if (unpushed != nullptr) {
+            const float4 a = reinterpret_cast<const float4*>(unpushed)[i];
+            p.x += a.x; p.y += a.y; p.z += a.z; p.w += a.w;
+        }
+        reinterpret_cast<float4*>(params)[i] = p;
+        if (shadow != nullptr) {
+            uint2 h;
+            h.x = pack_bf16x2(p.x, p.y);
+            h.y = pack_bf16x2(p.z, p.w);
+            reinterpret_cast<uint2*>(shadow)[i] = h;
+        }
+    }
+}
+}  // namespace dmlb
+
+// *slot = value on the stream (8 bytes of device memory): how the host retargets dmlb_sgd_flat_slot / dmlb_apply_pull between replays.
+extern "C" int dmlb_store_u64(void* slot, unsigned long long value, void* stream) {
+    DMLB_REQUIRE(slot != nullptr && (reinterpret_cast<uintptr_t>(slot) & 7) == 0, "slot must be an 8-byte aligned device address");
+    DMLB_CHECK_CUDA(launch_k(store_u64_kernel, 1, 1, 0, static_cast<cudaStream_t>(stream), static_cast<unsigned long long*>(slot), value));
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+// Landing of an overlapped parameter pull (reference Asynchronous.py:17-18: the listener overwrites the model with the server's reply):
+// params = pulled (+ *unpushed_slot, the worker's updates the server has not seen yet), fused with the cast into the bf16 mirror.
+extern "C" int dmlb_apply_pull(float* params, const float* pulled, void* unpushed_slot, void* shadow_bf16, long long n, void* stream) {
+    DMLB_REQUIRE(n % 4 == 0, "length must be a multiple of 4");
+    DMLB_CHECK_CUDA(launch_k(apply_pull_kernel, flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream), params, pulled,
+                             static_cast<float* const*>(unpushed_slot), static_cast<__nv_bfloat16*>(shadow_bf16), n / 4));
     DMLB_LAUNCH_CHECK();
     return 0;
 }

@@ -135,6 +135,13 @@ int dmlb_scale_rows_f32(void* x, const float* scale, long long rows, int C, int 
  * gradients as they are consumed (replaces the next step's zero_grad memset). */
 int dmlb_sgd_flat(float* params, float* grads, float* acc, float* mom, void* shadow_bf16, long long n, const float* lr_ptr, float mu,
                   float wd, int zero_grads, void* stream);
+/* dmlb_sgd_flat whose accumulator is named indirectly (*acc_slot, a device location holding the buffer's address): the asynchronous
+ * optimizer swaps two accumulators so a push can drain one on a communication stream while training fills the other. */
+int dmlb_sgd_flat_slot(float* params, float* grads, void* acc_slot, float* mom, void* shadow_bf16, long long n, const float* lr_ptr, float mu,
+                       float wd, int zero_grads, void* stream);
+int dmlb_store_u64(void* slot, unsigned long long value, void* stream);   /* *slot = value, stream ordered */
+/* Landing of an overlapped pull (Asynchronous.py:17-18): params = pulled (+ *unpushed_slot), bf16 mirror refreshed in the same pass. */
+int dmlb_apply_pull(float* params, const float* pulled, void* unpushed_slot, void* shadow_bf16, long long n, void* stream);
 /* table: device array of { int64 src_off, int64 dst_off, int32 rows, cin, khw, ld } — see csrc/train_ops.cu. */
 int dmlb_refresh_shadows(const float* params, void* shadow, const void* table, int n_entries, void* stream);
 int dmlb_refresh_shadows_f32(const float* params, void* shadow, const void* table, int n_entries, void* stream);   /* fp32 copies (tf32 path) */

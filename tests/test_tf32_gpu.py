@@ -82,11 +82,16 @@ def test_gemm_tf32_bias_relu_epilogue():
     (8, 16, 3, 1, 1, 8, True, (3, 2, 1)),
 ])
 def test_conv_block_tf32_fwd_bwd(cin, cout, k, s, p, hw, relu, pool):
+    """Operands are tf32-exact (inputs, weights, incoming gradient), so kernel and fp32 oracle compute the same products and differ only in
+    accumulation order: ReLU masks and pool arg-maxes agree, and the gradients can be held to a tight tolerance.  (With unrounded operands
+    the forward agrees to 1e-3 but ~0.1 % of the ReLU decisions flip, which alone moves a weight gradient by ~sqrt(1e-3) = 3 %.)"""
     torch.manual_seed(1)
     dev = "cuda"
     B = 8
     conv = dnn.set_compute_dtype(dnn.Conv2d(cin, cout, k, stride=s, padding=p, activation="relu" if relu else None, pool=pool), "tf32").to(dev)
-    x32 = torch.randn(B, cin, hw, hw, device=dev)
+    with torch.no_grad():
+        conv.weight.copy_(tf32_round(conv.weight))
+    x32 = tf32_round(torch.randn(B, cin, hw, hw, device=dev))
     x = act4(x32).requires_grad_(True)
     y = conv(x)
     assert y.dtype == torch.float32
@@ -99,31 +104,46 @@ def test_conv_block_tf32_fwd_bwd(cin, cout, k, s, p, hw, relu, pool):
             z = F.relu(z)
         yr = z if pool is None else F.max_pool2d(z, pool[0], pool[1], pool[2])
         assert y.shape == yr.shape
-        assert rel_err(y, yr) < TOL
-        g = torch.randn_like(yr)
+        assert rel_err(y, yr) < 1e-5
+        g = tf32_round(torch.randn_like(yr))
         y.backward(act4(g))
         yr.backward(g)
     torch.cuda.synchronize()
-    # ReLU / arg-max decisions on values that differ by tf32 rounding can flip for a handful of elements: 2x the forward tolerance
-    assert rel_err(conv.weight.grad, w.grad) < 2 * TOL
-    assert rel_err(conv.bias.grad, b.grad) < 2 * TOL
-    assert rel_err(x.grad, xr.grad) < 2 * TOL
+    # dY is tf32-exact only before the ReLU / pool routing, which keeps values as they are: still exact.  What remains: the rare
+    # sign flip of a pre-activation that is zero to within accumulation order.
+    assert rel_err(conv.weight.grad, w.grad) < TOL
+    assert rel_err(conv.bias.grad, b.grad) < TOL
+    assert rel_err(x.grad, xr.grad) < TOL
+
+
+def test_conv_tf32_unrounded_operands_forward():
+    """Plain fp32 tensors (what training feeds): the copy engine / tensor core reduce the operands to tf32, error ~2^-11 per product."""
+    torch.manual_seed(11)
+    dev = "cuda"
+    conv = dnn.set_compute_dtype(dnn.Conv2d(64, 192, 5, padding=2, activation="relu", pool=(2, 2, 0)), "tf32").to(dev)
+    x32 = torch.randn(16, 64, 4, 4, device=dev)
+    y = conv(act4(x32))
+    with torch.backends.cudnn.flags(allow_tf32=False):
+        yr = F.max_pool2d(F.relu(F.conv2d(x32, conv.weight, conv.bias, padding=2)), 2, 2)
+    assert rel_err(y, yr) < TOL
 
 
 def test_conv_first_layer_tf32_from_fp32_nchw():
     torch.manual_seed(2)
     dev = "cuda"
     conv = dnn.set_compute_dtype(dnn.Conv2d(3, 64, 11, stride=4, padding=5, activation="relu", pool=(2, 2, 0)), "tf32").to(dev)
-    x = torch.randn(16, 3, 32, 32, device=dev)
+    with torch.no_grad():
+        conv.weight.copy_(tf32_round(conv.weight))
+    x = tf32_round(torch.randn(16, 3, 32, 32, device=dev))
     y = conv(x)
     w = conv.weight.detach().clone().requires_grad_(True)
     with torch.backends.cudnn.flags(allow_tf32=False):
         yr = F.max_pool2d(F.relu(F.conv2d(x, w, conv.bias.detach(), stride=4, padding=5)), 2, 2)
-        assert rel_err(y, yr) < TOL
-        g = torch.randn_like(yr)
+        assert rel_err(y, yr) < 1e-5
+        g = tf32_round(torch.randn_like(yr))
         y.backward(act4(g))
         yr.backward(g)
-    assert rel_err(conv.weight.grad, w.grad) < 2 * TOL
+    assert rel_err(conv.weight.grad, w.grad) < TOL
 
 
 @pytest.mark.parametrize("i,o,relu,in_map", [(256, 10, False, None), (400, 120, True, (16, 5, 5)), (120, 84, True, None), (84, 10, False, None)])
