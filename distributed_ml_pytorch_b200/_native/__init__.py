@@ -65,6 +65,9 @@ _SIGNATURES = {
     "dmlb_bn_bwd_apply": [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_ll, c_int, c_vp, c_vp],
     "dmlb_avgpool_fwd_bf16": [c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_vp],
     "dmlb_avgpool_bwd_bf16": [c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_vp],
+    "dmlb_sgd_flat_slot": [c_vp, c_vp, c_vp, c_vp, c_vp, c_ll, c_vp, c_float, c_float, c_int, c_vp],
+    "dmlb_store_u64": [c_vp, c_ull, c_vp],
+    "dmlb_apply_pull": [c_vp, c_vp, c_vp, c_vp, c_ll, c_vp],
     # ---- tf32 path: fp32 tensors, tcgen05 kind::tf32 ----
     # (A, lda, a_mn, B, ldb, b_mn, M, N, K, out, ldo, bias, relu, split_k, atomic, perm_cin, perm_khw, tile_n, stream)
     "dmlb_gemm_tf32": [c_vp, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int,

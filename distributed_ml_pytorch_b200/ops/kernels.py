@@ -226,6 +226,23 @@ def sgd_flat(params: torch.Tensor, grads: torch.Tensor, acc, mom, n: int, lr_dev
           float(wd), int(zero_grads), stream_ptr())
 
 
+def sgd_flat_slot(params: torch.Tensor, grads: torch.Tensor, acc_slot: torch.Tensor, mom, n: int, lr_dev: torch.Tensor, mu: float = 0.0,
+                  wd: float = 0.0, shadow=None, zero_grads: bool = False) -> None:
+    """:func:`sgd_flat` accumulating into the buffer whose address is stored in ``acc_slot`` (int64 device tensor)."""
+    _call("dmlb_sgd_flat_slot", params.data_ptr(), grads.data_ptr(), acc_slot.data_ptr(), mom.data_ptr() if mom is not None else None,
+          shadow.data_ptr() if shadow is not None else None, n, lr_dev.data_ptr(), float(mu), float(wd), int(zero_grads), stream_ptr())
+
+
+def store_u64(slot: torch.Tensor, value: int) -> None:
+    _call("dmlb_store_u64", slot.data_ptr(), int(value), stream_ptr())
+
+
+def apply_pull(params: torch.Tensor, pulled: torch.Tensor, unpushed_slot, shadow, n: int) -> None:
+    """``params = pulled (+ *unpushed_slot)``, bf16 mirror refreshed in the same pass (``dmlb_apply_pull``)."""
+    _call("dmlb_apply_pull", params.data_ptr(), pulled.data_ptr(), unpushed_slot.data_ptr() if unpushed_slot is not None else None,
+          shadow.data_ptr() if shadow is not None else None, n, stream_ptr())
+
+
 def refresh_shadows(table: torch.Tensor, n_entries: int, dt=torch.bfloat16) -> None:
     """Absolute-address table: base pointers are NULL, offsets are addresses / element size."""
     _call("dmlb_refresh_shadows_f32" if dt == torch.float32 else "dmlb_refresh_shadows", None, None, table.data_ptr(), n_entries, stream_ptr())

@@ -22,6 +22,13 @@ precedes the pull inside a step so pulled parameters already contain the worker'
 parameters are applied at a step boundary instead of racing with forward/backward (``torn_pulls=True`` restores
 the reference's behaviour on the gloo transport); a pull request carries no payload; only ``init_rank``
 uploads the initial parameters.
+
+Overlap on the peer transport (``overlap=True``, the default): pushes, owner-side applies and pulls run on a communication stream
+while the worker keeps training.  The accumulator is double-buffered — at a push the training step switches to the other buffer (its
+address is read from device memory, so a captured CUDA graph follows the switch) and the push drains the retired one over NVLink — and a
+pull is fetched into a staging buffer that *lands* one step later, at a step boundary, as ``params = pulled + unpushed local updates``
+(one local pass over HBM).  The step stream therefore never waits for NVLink: per communication round it runs one 8-byte store and
+one landing kernel.
 """
 from __future__ import annotations
 
@@ -71,7 +78,7 @@ class Asynchronous(ArenaOptimizer):
     def __init__(self, params, lr, n_push: int, n_pull: int, model: torch.nn.Module, momentum: float = 0.0,
                  staleness: Optional[str] = None, staleness_param: float = 0.9, transport: str = "auto", group=None,
                  init_rank: Optional[int] = None, torn_pulls: bool = False, server_rank: int = msg.SERVER_RANK,
-                 blocking_pull: bool = False, pull_timeout_s: float = 60.0, server_ranks=None):
+                 blocking_pull: bool = False, pull_timeout_s: float = 60.0, server_ranks=None, overlap: bool = True, pull_lag: int = 1):
         if lr < 0.0:
             raise ValueError("Invalid learning rate: {}".format(lr))
         if n_push < 1 or n_pull < 1:
@@ -108,6 +115,8 @@ class Asynchronous(ArenaOptimizer):
         self._lock = threading.Lock()
         self._listener: Optional[Listener] = None
         self.pushes = self.pulls = 0
+        self.overlap = bool(overlap) and transport == "peer"
+        self.pull_lag = max(0, int(pull_lag))
 
         arena = None
         if transport == "peer":
@@ -171,19 +180,28 @@ class Asynchronous(ArenaOptimizer):
             self.full = self.full_sym.view(torch.int32, pg.world * cps)
             self.busy = self.busy_sym.view(torch.int32, pg.world * cps)
             self.master_mom = torch.zeros(S, dtype=torch.float32, device=a.params.device) if self.server_momentum else None
+        if self.overlap:
+            dev = a.params.device
+            self._acc = [self.accumulated_gradients, torch.zeros_like(self.accumulated_gradients)]
+            self._acc_cur = 0
+            self._acc_slot = torch.tensor([self._acc[0].data_ptr()], dtype=torch.int64, device=dev)
+            self._pulled = torch.empty_like(a.params)
+            self.comm_stream = torch.cuda.Stream(device=dev)
+            self._push_done = [None, None]
+            self._pending_pull = None        # (step index it was issued at, completion event)
         pg.barrier()
         self._pull()                                           # every replica starts from the server's parameters
         torch.cuda.synchronize(a.params.device)
         pg.barrier()
 
-    def _push(self) -> None:
+    def _push(self, acc: Optional[torch.Tensor] = None) -> None:
         from . import peer
         pg, a = self.peer, self.arena
+        acc = acc if acc is not None else self.accumulated_gradients
         if self._use_mailbox:
-            peer.push_mailbox(self.accumulated_gradients, self.busy, self.pulled_ver, self.mailbox_sym.table, self.full_sym.table, pg.rank,
-                              pg.world, a.shards.shard_size)
+            peer.push_mailbox(acc, self.busy, self.pulled_ver, self.mailbox_sym.table, self.full_sym.table, pg.rank, pg.world, a.shards.shard_size)
         else:
-            peer.push_add(self.accumulated_gradients, self.master_sym.table, pg.world, a.shards.shard_size, a.padded)
+            peer.push_add(acc, self.master_sym.table, pg.world, a.shards.shard_size, a.padded)
         self.pushes += 1
 
     def _owner_apply(self) -> None:
@@ -200,6 +218,58 @@ class Asynchronous(ArenaOptimizer):
         a.mark_params_changed(flat_done=a.shadow is not None)
         self.pulls += 1
 
+    def _land_pull(self, force: bool = False) -> None:
+        """Overlap mode: make a fetched pull the model's parameters (on the current stream, at a step boundary)."""
+        pp = self._pending_pull
+        if pp is None or (not force and self.idx - pp[0] < self.pull_lag):
+            return
+        from ..ops import kernels as K
+        a = self.arena
+        cur = torch.cuda.current_stream(a.params.device)
+        cur.wait_event(pp[1])
+        # pulled + the local updates the server has not seen yet (they sit in the current accumulator): exactly what a pull that
+        # had landed the moment it was issued, followed by the local steps since, would have produced
+        K.apply_pull(a.params, self._pulled, self._acc_slot, a.shadow, a.padded)
+        a.mark_params_changed(flat_done=a.shadow is not None)
+        self._pending_pull = None
+
+    def _communicate_overlapped(self, push_now: bool, pull_now: bool) -> None:
+        from . import peer
+        from ..ops import kernels as K
+        pg, a = self.peer, self.arena
+        dev = a.params.device
+        cur = torch.cuda.current_stream(dev)
+        self._land_pull()
+        if not (push_now or pull_now or self._use_mailbox):
+            return
+        retired = None
+        if push_now:
+            retired, nxt = self._acc_cur, self._acc_cur ^ 1
+            if self._push_done[nxt] is not None:
+                cur.wait_event(self._push_done[nxt])       # drained n_push steps ago: no wait in practice
+            K.store_u64(self._acc_slot, self._acc[nxt].data_ptr())
+            self._acc_cur = nxt
+            self.accumulated_gradients = self._acc[nxt]
+        ready = torch.cuda.Event()
+        ready.record(cur)
+        self.comm_stream.wait_event(ready)
+        with torch.cuda.stream(self.comm_stream):
+            if push_now:
+                self._push(self._acc[retired])
+                done = torch.cuda.Event()
+                done.record(self.comm_stream)
+                self._push_done[retired] = done
+            if self._use_mailbox:
+                self._owner_apply()
+            if pull_now:
+                peer.pull(self._pulled, self.master_sym.table, pg.world, a.shards.shard_size, a.padded, self.version_sym.table, self.pulled_ver)
+                fetched = torch.cuda.Event()
+                fetched.record(self.comm_stream)
+                self._pending_pull = (self.idx, fetched)
+                self.pulls += 1
+        if pull_now and self.pull_lag == 0:
+            self._land_pull(force=True)
+
     # ------------------------------------------------------------------------------------------
     # the optimizer step
     # ------------------------------------------------------------------------------------------
@@ -210,6 +280,13 @@ class Asynchronous(ArenaOptimizer):
         self.accumulated_gradients.copy_(st[0])
         self.idx = st[1]
 
+    def drain(self) -> None:
+        """Overlap mode: wait (stream-wise) for outstanding pushes and land a fetched pull, e.g. before evaluating or checkpointing."""
+        if not self.overlap:
+            return
+        torch.cuda.current_stream(self.arena.params.device).wait_stream(self.comm_stream)
+        self._land_pull(force=True)
+
     @torch.no_grad()
     def step_local(self) -> None:
         """Local SGD on the replica + accumulate ``-lr * grad`` (reference Asynchronous.py:52-55,63-68): one kernel."""
@@ -217,8 +294,12 @@ class Asynchronous(ArenaOptimizer):
         self._sync_lr()
         if a.params.is_cuda:
             from ..ops import kernels as K
-            K.sgd_flat(a.params, a.grads, self.accumulated_gradients, None, a.padded, self.lr_dev, 0.0, 0.0, shadow=a.shadow,
-                       zero_grads=self.fused_zero_grad)
+            if self.overlap:
+                K.sgd_flat_slot(a.params, a.grads, self._acc_slot, None, a.padded, self.lr_dev, 0.0, 0.0, shadow=a.shadow,
+                                zero_grads=self.fused_zero_grad)
+            else:
+                K.sgd_flat(a.params, a.grads, self.accumulated_gradients, None, a.padded, self.lr_dev, 0.0, 0.0, shadow=a.shadow,
+                           zero_grads=self.fused_zero_grad)
             a.mark_params_changed(flat_done=a.shadow is not None)
         else:
             lr = self.lr
@@ -230,7 +311,9 @@ class Asynchronous(ArenaOptimizer):
         """Push every ``n_push`` steps, pull every ``n_pull`` steps (both fire at step 0, like the reference)."""
         push_now = self.idx % self.n_push == 0
         pull_now = self.idx % self.n_pull == 0
-        if self.transport == "peer":
+        if self.transport == "peer" and self.overlap:
+            self._communicate_overlapped(push_now, pull_now)
+        elif self.transport == "peer":
             if push_now:
                 self._push()
             if self._use_mailbox:
@@ -319,6 +402,9 @@ class Asynchronous(ArenaOptimizer):
                 self._listener.join(timeout=30)
             self._apply_pending()        # the server answers every request before it echoes WorkerDone: end on its latest parameters
         elif self.transport == "peer":
+            if self.peer is None:
+                return
+            self.drain()
             torch.cuda.synchronize(self.arena.params.device)
             self.peer.barrier()
             if self._use_mailbox:
@@ -344,6 +430,8 @@ class Asynchronous(ArenaOptimizer):
         """The server's current flat parameter vector (length N) as seen from this worker."""
         a = self.arena
         if self.transport == "peer":
+            if self.overlap:      # pushes still in flight on the communication stream belong to the answer
+                torch.cuda.current_stream(a.params.device).wait_stream(self.comm_stream)
             out = torch.empty_like(a.params)
             from . import peer
             peer.pull(out, self.master_sym.table, self.peer.world, a.shards.shard_size, a.padded)
