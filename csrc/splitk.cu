@@ -87,6 +87,133 @@ __global__ void __launch_bounds__(256) splitk_finish_pool2_kernel(float* __restr
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Finish of a split-K *data-gradient* GEMM fused with the activation backward of the layer that produced the GEMM's input
+// ("conv_dgrad fused with the ReLU-mask of the previous layer").
+//   ws   : fp32 [Mx, ldw], the summed dgrad = gradient w.r.t. the producer block's OUTPUT (pooled when the producer pools); zeroed here
+//   y    : the producer's post-activation conv output [B, H, W, ldy]       (H = Hx, or 2*Hx with the 2x2/2 pool)
+//   dy   : gradient w.r.t. the producer's pre-activation output [B, H, W, ldy] — the operand of its wgrad / dgrad GEMMs
+//   dbias: fp32 [C] += column sums of dy (may be null)
+// One thread handles one ws pixel x 4 channels: with pooling it routes the value to the first maximum of the 2x2 window of y
+// (PyTorch's rule) and writes all four dy pixels.  Replaces splitk_finish + act_bwd (two launches, one extra round trip of dx).
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ void load4(const T* p, float (&f)[4]);
+template <>
+__device__ __forceinline__ void load4<float>(const float* p, float (&f)[4]) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(p));
+    f[0] = v.x; f[1] = v.y; f[2] = v.z; f[3] = v.w;
+}
+template <>
+__device__ __forceinline__ void load4<__nv_bfloat16>(const __nv_bfloat16* p, float (&f)[4]) {
+    const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
+    const float2 a = unpack_bf16x2(v.x), b = unpack_bf16x2(v.y);
+    f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
+}
+template <typename T>
+__device__ __forceinline__ void store4(T* p, const float (&f)[4]);
+template <>
+__device__ __forceinline__ void store4<float>(float* p, const float (&f)[4]) {
+    *reinterpret_cast<float4*>(p) = make_float4(f[0], f[1], f[2], f[3]);
+}
+template <>
+__device__ __forceinline__ void store4<__nv_bfloat16>(__nv_bfloat16* p, const float (&f)[4]) {
+    uint2 o;
+    o.x = pack_bf16x2(f[0], f[1]);
+    o.y = pack_bf16x2(f[2], f[3]);
+    *reinterpret_cast<uint2*>(p) = o;
+}
+
+template <typename T, bool POOL>
+__global__ void __launch_bounds__(256) splitk_finish_actbwd_kernel(float* __restrict__ ws, int ldw, const T* __restrict__ y, T* __restrict__ dy,
+                                                                   int ldy, float* __restrict__ dbias, int B, int Hx, int Wx, int C, int relu) {
+    pdl_prologue();
+    extern __shared__ float sbias[];  // [C]
+    if (dbias != nullptr) {
+        for (int c = threadIdx.x; c < C; c += blockDim.x) sbias[c] = 0.f;
+        __syncthreads();
+    }
+    const int c4n = C >> 2;                       // C % 4 == 0 (host checks)
+    const long long total = 1ll * B * Hx * Wx * c4n;
+    const int H = POOL ? 2 * Hx : Hx, W = POOL ? 2 * Wx : Wx;
+    float bacc[4] = {0.f, 0.f, 0.f, 0.f};
+    int cur_c4 = -1;
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
+        const int c4 = static_cast<int>(i % c4n);
+        long long t = i / c4n;
+        const int wx = static_cast<int>(t % Wx); t /= Wx;
+        const int hx = static_cast<int>(t % Hx);
+        const int b = static_cast<int>(t / Hx);
+        float* wp = ws + ((1ll * b * Hx + hx) * Wx + wx) * ldw + c4 * 4;
+        const float4 gq = *reinterpret_cast<const float4*>(wp);
+        *reinterpret_cast<float4*>(wp) = make_float4(0.f, 0.f, 0.f, 0.f);
+        const float g[4] = {gq.x, gq.y, gq.z, gq.w};
+        float sum[4] = {0.f, 0.f, 0.f, 0.f};
+        if constexpr (!POOL) {
+            const long long yi = ((1ll * b * H + hx) * W + wx) * ldy + c4 * 4;
+            float yv[4], o[4];
+            load4<T>(y + yi, yv);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                o[j] = (relu && !(yv[j] > 0.f)) ? 0.f : g[j];
+                sum[j] = o[j];
+            }
+            store4<T>(dy + yi, o);
+        } else {
+            float yv[4][4];
+            long long yi[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                yi[q] = ((1ll * b * H + (2 * hx + (q >> 1))) * W + (2 * wx + (q & 1))) * ldy + c4 * 4;
+                load4<T>(y + yi[q], yv[q]);
+            }
+            int win[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                int best = 0;
+#pragma unroll
+                for (int q = 1; q < 4; ++q)
+                    if (yv[q][j] > yv[best][j]) best = q;          // strict: the first maximum wins
+                win[j] = best;
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                float o[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    o[j] = (win[j] == q && !(relu && !(yv[q][j] > 0.f))) ? g[j] : 0.f;
+                    sum[j] += o[j];
+                }
+                store4<T>(dy + yi[q], o);
+            }
+        }
+        if (dbias != nullptr) {
+            if (c4 != cur_c4) {
+                if (cur_c4 >= 0) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        if (bacc[j] != 0.f) atomicAdd(&sbias[cur_c4 * 4 + j], bacc[j]);
+                        bacc[j] = 0.f;
+                    }
+                }
+                cur_c4 = c4;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) bacc[j] += sum[j];
+        }
+    }
+    if (dbias != nullptr) {
+        if (cur_c4 >= 0) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (bacc[j] != 0.f) atomicAdd(&sbias[cur_c4 * 4 + j], bacc[j]);
+        }
+        __syncthreads();
+        for (int c = threadIdx.x; c < C; c += blockDim.x)
+            if (sbias[c] != 0.f) red_add_f32(dbias + c, sbias[c]);
+    }
+}
+
 static inline int finish_grid(long long total) {
     long long blocks = (total + 255) / 256;
     const long long cap = 148ll * 8;
@@ -128,6 +255,42 @@ extern "C" int dmlb_splitk_finish(float* ws, int ldw, const float* bias, int rel
 extern "C" int dmlb_splitk_finish_f32(float* ws, int ldw, const float* bias, int relu, void* y, int ldy, long long M, int N, int pool2, int B,
                                       int H, int W, void* pooled, int ldp, void* stream) {
     return splitk_finish_t<float>(ws, ldw, bias, relu, y, ldy, M, N, pool2, B, H, W, pooled, ldp, stream);
+}
+
+template <typename T>
+static int splitk_finish_actbwd_t(float* ws, int ldw, const void* y, void* dy, int ldy, float* dbias, int B, int Hx, int Wx, int C, int pool2,
+                                  int relu, void* stream) {
+    DMLB_REQUIRE(ldw % 4 == 0 && ldw >= C && C % 4 == 0 && ldy % 4 == 0, "channels and pitches must be multiples of 4");
+    DMLB_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 7) == 0 && (reinterpret_cast<uintptr_t>(dy) & 7) == 0,
+                 "workspace / activation alignment");
+    DMLB_REQUIRE(C * 4 <= 48 * 1024, "channel count too large for the bias-gradient staging buffer");
+    const int c4n = C / 4;
+    const long long total = 1ll * B * Hx * Wx * c4n;
+    int blocks = finish_grid(total);
+    if (blocks > 148 * 2) blocks = 148 * 2;
+    // keep (threads in the grid) a multiple of the channel-group count so a thread's channel group never changes
+    int a = c4n, bq = 256;
+    while (bq) { const int tmp = a % bq; a = bq; bq = tmp; }
+    const int mult = c4n / a;
+    if (blocks > mult) blocks = blocks / mult * mult;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t smem = dbias != nullptr ? C * sizeof(float) : 0;
+    if (pool2)
+        DMLB_CHECK_CUDA(launch_k(splitk_finish_actbwd_kernel<T, true>, blocks, 256, smem, st, ws, ldw, static_cast<const T*>(y), static_cast<T*>(dy), ldy,
+                                 dbias, B, Hx, Wx, C, relu));
+    else
+        DMLB_CHECK_CUDA(launch_k(splitk_finish_actbwd_kernel<T, false>, blocks, 256, smem, st, ws, ldw, static_cast<const T*>(y), static_cast<T*>(dy), ldy,
+                                 dbias, B, Hx, Wx, C, relu));
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+// ws: fp32 [B*Hx*Wx, ldw] summed split-K dgrad (zeroed again here); y / dy: [B, H, W, ldy] with (H, W) = (Hx, Wx), or (2Hx, 2Wx) when
+// pool2 = 1 (the producer block ends in a 2x2/2 max-pool).  is_f32 selects fp32 (tf32 path) or bf16 activations.
+extern "C" int dmlb_splitk_finish_actbwd(float* ws, int ldw, const void* y, void* dy, int ldy, float* dbias, int B, int Hx, int Wx, int C,
+                                         int pool2, int relu, int is_f32, void* stream) {
+    if (is_f32) return splitk_finish_actbwd_t<float>(ws, ldw, y, dy, ldy, dbias, B, Hx, Wx, C, pool2, relu, stream);
+    return splitk_finish_actbwd_t<__nv_bfloat16>(ws, ldw, y, dy, ldy, dbias, B, Hx, Wx, C, pool2, relu, stream);
 }
 
 // y[M,N] (bf16, pitch ldy) = act(A[M,K] * W[N,K]^T + bias) with K split `split_k` ways.

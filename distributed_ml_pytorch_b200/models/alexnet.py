@@ -18,15 +18,15 @@ class AlexNet(nn.Module):
         super().__init__()
         P = (2, 2, 0)
         self.features = nn.Sequential(
-            dnn.Conv2d(in_channels, 64, kernel_size=11, stride=4, padding=5, activation="relu", pool=P),
+            dnn.Conv2d(in_channels, 64, kernel_size=11, stride=4, padding=5, activation="relu", pool=P, sole_consumer_is_conv=True),
             dnn.ReLU(fused=True),
             dnn.MaxPool2d(2, 2, fused=True),
-            dnn.Conv2d(64, 192, kernel_size=5, padding=2, activation="relu", pool=P),
+            dnn.Conv2d(64, 192, kernel_size=5, padding=2, activation="relu", pool=P, sole_consumer_is_conv=True),
             dnn.ReLU(fused=True),
             dnn.MaxPool2d(2, 2, fused=True),
-            dnn.Conv2d(192, 384, kernel_size=3, padding=1, activation="relu"),
+            dnn.Conv2d(192, 384, kernel_size=3, padding=1, activation="relu", sole_consumer_is_conv=True),
             dnn.ReLU(fused=True),
-            dnn.Conv2d(384, 256, kernel_size=3, padding=1, activation="relu"),
+            dnn.Conv2d(384, 256, kernel_size=3, padding=1, activation="relu", sole_consumer_is_conv=True),
             dnn.ReLU(fused=True),
             dnn.Conv2d(256, 256, kernel_size=3, padding=1, activation="relu", pool=P),
             dnn.ReLU(fused=True),

@@ -252,8 +252,12 @@ class Conv2d(_ShadowedModule):
     Same parameters / initialisation as ``torch.nn.Conv2d`` (reference models.py:8-9,29-39).
     """
 
-    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, bias=True, activation=None, pool=None):
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, bias=True, activation=None, pool=None,
+                 sole_consumer_is_conv=False):
         super().__init__()
+        # the model author's promise that this layer's output is read by exactly one op, another Conv2d of this package: that layer's
+        # backward may then run this layer's pool / ReLU backward inside its own split-K dgrad finish (ops/functional.py, K8)
+        self.sole_consumer_is_conv = bool(sole_consumer_is_conv)
         self.in_channels, self.out_channels = in_channels, out_channels
         self.kernel_size, self.stride, self.padding = _pair(kernel_size), _pair(stride), _pair(padding)
         self.activation = activation
@@ -278,7 +282,7 @@ class Conv2d(_ShadowedModule):
         if not x.is_cuda:
             return OF.conv_block(x, self.weight, self.bias, self.stride, self.padding, relu, self.pool)
         return OF.conv_block(x, self.weight, self.bias, self.stride, self.padding, relu, self.pool, shadow=self.shadow(),
-                             wsink=self._wsink, bsink=self._bsink)
+                             wsink=self._wsink, bsink=self._bsink, sole_consumer=self.sole_consumer_is_conv)
 
     def extra_repr(self):
         return (f"{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, stride={self.stride}, padding={self.padding}, "

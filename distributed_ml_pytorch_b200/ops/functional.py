@@ -251,6 +251,18 @@ def set_implicit_conv(flag: bool) -> bool:
 
 _PAIR_CONV = os.environ.get("DMLB_PAIR_CONV", "0") == "1"
 
+# Backward fusion across two conv blocks (K8).  When block P declares that its output feeds exactly one consumer and that consumer is a
+# conv block C (``conv_block(..., sole_consumer=True)``; the model author's promise), C's backward finishes its split-K data-gradient
+# GEMM with ONE kernel that also runs P's pool / ReLU backward and bias gradient (`dmlb_splitk_finish_actbwd`).  C then hands autograd a
+# zero-stride token of the right shape instead of dx, and P's backward, recognising the token, picks up its ready-made dy.
+_fuse = SimpleNamespace(enabled=os.environ.get("DMLB_FUSE_ACT_BWD", "1") == "1", pending={})
+
+
+def set_fused_act_bwd(flag: bool) -> bool:
+    old = _fuse.enabled
+    _fuse.enabled = bool(flag)
+    return old
+
 
 class _ConvBlockFn(torch.autograd.Function):
     """Convolution (+bias +ReLU +max-pool) on the tcgen05 GEMM.
@@ -337,6 +349,14 @@ class _ConvBlockFn(torch.autograd.Function):
             out = new_act4(B, Cout, Hp, Wp, dev, dt)
             K.maxpool_fwd(y.data_ptr(), out.data_ptr(), B, Ho, Wo, Cout, ldy, ldy, k, s, p, dt=dt)
         ctx.cfg = cfg
+        cfg.fwd = None
+        if cfg.sole_consumer and _fuse.enabled:
+            pool2 = cfg.pool == (2, 2, 0)
+            if (cfg.pool is None or (pool2 and Ho % 2 == 0 and Wo % 2 == 0)) and Cout % 4 == 0:
+                cfg.fwd = SimpleNamespace(y=y, B=B, Ho=Ho, Wo=Wo, C=Cout, ldy=ldy, dt=dt, pool2=pool2, relu=cfg.relu, out_ptr=out.data_ptr(),
+                                          bias=bias, bsink=cfg.bsink if (bias is not None and _sink_ok(bias, cfg.bsink)) else None,
+                                          needs_bias_grad=bias is not None and bias.requires_grad)
+        ctx.x_ptr = x.data_ptr()
         ctx.geom = (B, H, W, Cin, Cout, KH, KW, SH, SW, PH, PW, Ho, Wo, Kd, Kpad, ldx, lda, direct, from_nchw_f32, implicit)
         ctx.has_bias = bias is not None
         ctx.save_for_backward(x if implicit else a_t, y if (cfg.relu or cfg.pool is not None) else None, weight, bias)
@@ -352,14 +372,21 @@ class _ConvBlockFn(torch.autograd.Function):
         bk = K.kblock(dt)
         M = B * Ho * Wo
         ldy = pad_for(dt, Cout)
-        dout, ldd = as_act4(dout, dt)
+        entry = _fuse.pending.pop(dout.data_ptr(), None) if (_fuse.pending and dout.dim() == 4 and dout.stride() == (0, 0, 0, 0)) else None
+        if entry is None:
+            dout, ldd = as_act4(dout, dt)
         # ---- activation backward (+ pool backward, + bias gradient) ----
         gb = None
         bias_sink = cfg.bsink if (ctx.has_bias and _sink_ok(bias, cfg.bsink)) else None
-        if ctx.has_bias and bias_sink is None and ctx.needs_input_grad[2]:
+        if entry is not None:
+            # the consumer block already ran this block's activation backward inside its dgrad finish
+            dy, lddy, gb = entry.dy, ldy, entry.gb
+        elif ctx.has_bias and bias_sink is None and ctx.needs_input_grad[2]:
             gb = torch.zeros(Cout, dtype=torch.float32, device=dev)
         db = bias_sink if bias_sink is not None else gb
-        if cfg.relu or cfg.pool is not None or db is not None:
+        if entry is not None:
+            pass
+        elif cfg.relu or cfg.pool is not None or db is not None:
             dy = new_act4(B, Cout, Ho, Wo, dev, dt)
             K.act_bwd(y.data_ptr() if y is not None else dy.data_ptr(), dout.data_ptr(), dy.data_ptr(), db, B, Ho, Wo, Cout, ldy, ldd,
                       cfg.pool, cfg.relu, dt=dt)
@@ -428,7 +455,25 @@ class _ConvBlockFn(torch.autograd.Function):
                     else:
                         K.conv_implicit(2, dy.data_ptr(), lddy, B, Ho, Wo, Cout, cfg.shadow.data_ptr(), Kpad, KH, KW, 1, 1, PH, PW, Cin, ws, ldw,
                                         split_k=dsplit, atomic=True, dt=dt)
-                        K.splitk_finish(ws, ldw, None, False, dx.data_ptr(), ldxo, Min, Cin, dt=dt)
+                        pf = cfg.prod.fwd if (cfg.prod is not None and _fuse.enabled) else None
+                        if pf is not None and pf.out_ptr == ctx.x_ptr and pf.dt == dt and pf.C == Cin and pf.B == B and \
+                                (pf.Ho, pf.Wo) == ((2 * H, 2 * W) if pf.pool2 else (H, W)):
+                            # one kernel: sum of the K-splits -> producer's pool / ReLU backward + bias gradient -> producer's dy
+                            dyp = new_act4(B, Cin, pf.Ho, pf.Wo, dev, dt)
+                            pgb = None
+                            if pf.bsink is None and pf.needs_bias_grad:
+                                pgb = torch.zeros(Cin, dtype=torch.float32, device=dev)
+                            K.splitk_finish_actbwd(ws, ldw, pf.y.data_ptr(), dyp.data_ptr(), pf.ldy, pf.bsink if pf.bsink is not None else pgb, B, H, W,
+                                                   Cin, pf.pool2, pf.relu, dt=dt)
+                            if pf.bsink is not None:
+                                _notify_grad_ready(pf.bias, dev)
+                            token = torch.empty(1, dtype=dt, device=dev)
+                            if len(_fuse.pending) > 256:
+                                _fuse.pending.clear()
+                            _fuse.pending[token.data_ptr()] = SimpleNamespace(dy=dyp, gb=pgb, token=token)
+                            dx = token.expand(B, Cin, H, W)
+                        else:
+                            K.splitk_finish(ws, ldw, None, False, dx.data_ptr(), ldxo, Min, Cin, dt=dt)
                 else:
                     K.conv_implicit(2, dy.data_ptr(), lddy, B, Ho, Wo, Cout, cfg.shadow.data_ptr(), Kpad, KH, KW, 1, 1, PH, PW, Cin, dx, ldxo,
                                     dt=dt)
@@ -439,9 +484,12 @@ class _ConvBlockFn(torch.autograd.Function):
         return dx, gw, gb, None
 
 
-def conv_block(x, weight, bias=None, stride=(1, 1), padding=(0, 0), relu=False, pool=None, shadow=None, wsink=None, bsink=None):
+def conv_block(x, weight, bias=None, stride=(1, 1), padding=(0, 0), relu=False, pool=None, shadow=None, wsink=None, bsink=None,
+               sole_consumer=False):
     """``max_pool(relu(conv2d(x, weight, bias)))`` with the optional parts fused (CUDA) or composed (CPU).
 
+    ``sole_consumer=True`` promises that the result is read by exactly one op and that op is another ``conv_block``: its backward may
+    then fold this block's pool / ReLU backward and bias gradient into its split-K dgrad finish (one launch instead of two).
     ``pool`` is ``None`` or ``(kernel, stride, padding)``; ``shadow`` is the GEMM-layout form of ``weight``
     (see :class:`~distributed_ml_pytorch_b200.nn.layers.Conv2d`) whose dtype selects the compute dtype: bf16, or
     fp32 for the tf32 path; ``wsink`` / ``bsink`` are views of the flat fp32 gradient arena that receive the
@@ -457,8 +505,11 @@ def conv_block(x, weight, bias=None, stride=(1, 1), padding=(0, 0), relu=False, 
     if shadow is None:
         raise RuntimeError("conv_block on CUDA needs the GEMM-layout weight shadow (use nn.Conv2d from this package)")
     cfg = SimpleNamespace(stride=tuple(stride), padding=tuple(padding), relu=bool(relu), pool=pool, shadow=shadow, wsink=wsink, bsink=bsink,
-                          dt=shadow.dtype)
-    return _ConvBlockFn.apply(x, weight, bias, cfg)
+                          dt=shadow.dtype, sole_consumer=bool(sole_consumer), prod=getattr(x, "_dmlb_prod", None), fwd=None)
+    out = _ConvBlockFn.apply(x, weight, bias, cfg)
+    if cfg.fwd is not None:
+        out._dmlb_prod = cfg          # "this activation's only reader is a conv block": lets that block fuse our activation backward
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -497,7 +548,12 @@ class _LinearFn(torch.autograd.Function):
         if ctx.has_bias and bias_sink is None and ctx.needs_input_grad[2]:
             gb = torch.zeros(O, dtype=torch.float32, device=dev)
         db = bias_sink if bias_sink is not None else gb
-        if cfg.relu or db is not None:
+        side_bias = None
+        if not cfg.relu and bias_sink is not None and _side.enabled and ctx.needs_input_grad[1]:
+            # no mask to apply: dy IS dout; the bias gradient (column sums) joins the weight gradient on the side stream
+            dy, lddy = dout, ldd
+            side_bias = db
+        elif cfg.relu or db is not None:
             dy = new_act2(B, O, dev, dt)
             lddy = pad_for(dt, O)
             ldyv = y.stride(0) if (y is not None and B > 1) else lddy
@@ -519,6 +575,10 @@ class _LinearFn(torch.autograd.Function):
             split = K.pick_split_k(tiles, B, bk=K.kblock(dt))
             pc, pk = (cfg.in_map[0], cfg.in_map[1] * cfg.in_map[2]) if cfg.in_map is not None else (0, 0)
             with _WgradFork(dev, dy, x, gw) as fork:
+                if side_bias is not None:
+                    scratch = new_act2(B, O, dev, dt)
+                    K.act_bwd(scratch.data_ptr(), dy.data_ptr(), scratch.data_ptr(), side_bias, B, 1, 1, O, pad_for(dt, O), lddy, None, False, dt=dt)
+                    _notify_grad_ready(bias, dev, fork.side if fork.active else None)
                 K.gemm(dy, lddy, True, x, ctx.ldx, True, O, I, B, target, I, split_k=split, atomic=True, perm_cin=pc if pk > 1 else 0,
                        perm_khw=pk)
             if gw is not None and fork.active:

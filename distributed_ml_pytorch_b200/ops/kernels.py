@@ -161,6 +161,13 @@ def splitk_finish(ws: torch.Tensor, ldw: int, bias, relu: bool, y_ptr: int, ldy:
           int(pool2 is not None), B, H, W, pooled_ptr or None, ldp, stream_ptr())
 
 
+def splitk_finish_actbwd(ws: torch.Tensor, ldw: int, y_ptr: int, dy_ptr: int, ldy: int, dbias, B, Hx, Wx, C, pool2: bool, relu: bool,
+                         dt=torch.bfloat16) -> None:
+    """Split-K dgrad finish fused with the producer block's pool / ReLU backward and bias gradient (``dmlb_splitk_finish_actbwd``)."""
+    _call("dmlb_splitk_finish_actbwd", ws.data_ptr(), ldw, y_ptr, dy_ptr, ldy, dbias.data_ptr() if dbias is not None else None, B, Hx, Wx, C,
+          int(pool2), int(relu), int(dt == torch.float32), stream_ptr())
+
+
 def fprop_split(M: int, N: int, K: int, sms: int = 148, bk: int = 64) -> int:
     """Split-K factor for a forward GEMM, 1 when the plain fused-epilogue kernel is the better choice."""
     bn = 128 if N > 64 else (64 if N > 32 else 32)

@@ -74,6 +74,11 @@ int dmlb_splitk_finish(float* ws, int ldw, const float* bias, int relu, void* y,
                        void* pooled, int ldp, void* stream);
 int dmlb_splitk_finish_f32(float* ws, int ldw, const float* bias, int relu, void* y, int ldy, long long M, int N, int pool2, int B, int H, int W,
                            void* pooled, int ldp, void* stream);   /* fp32 y / pooled (tf32 path) */
+/* Finish of a split-K data-gradient GEMM fused with the activation backward of the block that produced the GEMM's input (K8): reads the
+ * summed dgrad from ws (and zeroes it), applies that block's 2x2 max-pool backward (pool2) and ReLU mask using its saved activation y,
+ * writes dy (the operand of the block's own wgrad / dgrad) and accumulates its bias gradient.  Replaces dmlb_splitk_finish + dmlb_act_bwd_*. */
+int dmlb_splitk_finish_actbwd(float* ws, int ldw, const void* y, void* dy, int ldy, float* dbias, int B, int Hx, int Wx, int C, int pool2,
+                              int relu, int is_f32, void* stream);
 int dmlb_gemm_bias_act_splitk(const void* A, int lda, const void* Wt, int ldb, int M, int N, int K, float* ws, const float* bias, int relu,
                               void* y, int ldy, int split_k, void* stream);
 

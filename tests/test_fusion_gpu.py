@@ -1,0 +1,48 @@
+"""Launch-count reductions of the training step must not change its numbers.
+
+K8: the split-K data-gradient finish of a conv block also runs the previous block's pool / ReLU backward and bias gradient
+(`dmlb_splitk_finish_actbwd`), replacing a finish kernel + an activation-backward kernel per layer boundary.
+"""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from distributed_ml_pytorch_b200 import _native
+from distributed_ml_pytorch_b200.models import build_model
+from distributed_ml_pytorch_b200.ops import functional as OF
+from distributed_ml_pytorch_b200.parallel.fused_sgd import FusedSGD
+
+
+def _grads(dtype, fused, seed=0):
+    torch.manual_seed(seed)
+    net = build_model("alexnet", dtype=dtype).cuda()
+    opt = FusedSGD(net.parameters(), lr=0.0, model=net)
+    torch.manual_seed(seed + 1)
+    x = torch.randn(64, 3, 32, 32, device="cuda")
+    y = torch.randint(0, 10, (64,), device="cuda")
+    old = OF.set_fused_act_bwd(fused)
+    try:
+        net(x)                                     # warm-up: shadows, workspaces
+        opt.zero_grad()
+        torch.cuda.synchronize()
+        n0 = _native.launch_count()
+        loss = OF.cross_entropy(net(x), y)
+        loss.backward()
+        torch.cuda.synchronize()
+        launches = _native.launch_count() - n0
+    finally:
+        OF.set_fused_act_bwd(old)
+    return net._dmlb_arena.grads.clone(), float(loss), launches
+
+
+@pytest.mark.parametrize("dtype", ["tf32", "bf16"])
+def test_fused_dgrad_finish_matches_two_kernel_form(dtype):
+    g0, l0, n0 = _grads(dtype, fused=False)
+    g1, l1, n1 = _grads(dtype, fused=True)
+    assert l0 == l1
+    assert n1 == n0 - 4, (n0, n1)                  # four layer boundaries of AlexNet: (finish + act_bwd) -> one kernel each
+    err = ((g0 - g1).norm() / g0.norm()).item()
+    # identical products; only the bias gradients' summation differs (fp32 values before vs after the bf16 rounding of dy)
+    assert err < (1e-6 if dtype == "tf32" else 2e-3), err
+    assert torch.isfinite(g1).all() and g1.abs().sum() > 0
