@@ -67,6 +67,14 @@ struct GemmEpilogue {
     int atomic;           // red.add into fp32 out
     int perm_cin;         // >0: out column c -> (c % perm_cin) * perm_khw + c / perm_cin
     int perm_khw;
+    // Small-channel convolutions (first layers): the GEMM's columns are (tap, padded channel) with `cpad` channels per tap of which only
+    // `cin` are real.  cpad > 0 (accumulating epilogue only): column c = tap * cpad + ch is dropped when ch >= cin, else lands at
+    // tap * cin + ch (GEMM order) or, with perm_khw > 0, at ch * perm_khw + tap (PyTorch's [Cout, Cin, kh, kw]).
+    int cpad, cin;
+    // 2x2 / stride-2 max-pool of the stored activation computed in the same epilogue (warp shuffles across the rows = pixels of the
+    // tile): pool_w = W of the [B, H, W] map the rows enumerate (power of two <= 16, H even), 0 = off; pooled is [M/4, ldp].
+    void* pooled;
+    int ldp, pool_w;
     // Split-K with the finishing pass folded in ("last CTA of a tile finishes"): every z-slice red.adds its partial tile into the
     // fp32 workspace `out`, then bumps the tile's arrival counter; the slice that arrives last reads the summed tile back from L2,
     // applies bias / ReLU, rounds to bf16 into fin_y (optionally also the 2x2/2 max-pool into fin_pooled), and writes zeros back,
@@ -83,6 +91,10 @@ struct GemmEpilogue {
 // (implicit-GEMM convolution: fprop reads x, dgrad reads dY).  B: 0 = K-major matrix, 1 = MN-major matrix,
 // 2 = im2col gather, MN-major (wgrad: the column matrix is never materialised), 3 = conv weight [Cout, kh*kw, Cin] read
 // through a 3-D map as the MN-major operand of dgrad (no transposed / flipped weight copy).
+// Small-channel convolutions (first layers: Cin <= one 16-byte granule, i.e. 4 fp32 / 8 bf16 channels after padding): A = 3 gathers
+// EIGHT filter taps per 128-byte k-block, each tap one TMA im2col box of 128 pixels x 16 bytes written unswizzled (the K-major
+// no-swizzle core-matrix layout: 8 pixels x 16 B = 128 B, next 8 pixels +128 B, next tap +2048 B); B = 4 is the same gather as the
+// MN-major operand of wgrad (one box of kBK pixels x 16 B per tap).  K order = (tap, padded channel).
 struct ConvK {
     int C;            // channels of the gathered activation (Cin for fprop / wgrad, Cout for dgrad)
     int KH, KW;
@@ -107,6 +119,38 @@ struct GemmSmem {
     static constexpr int kTotal = kStages * kStageBytes + kBarrierBytes + 1024;  // +1024: manual 1 KiB alignment
 };
 
+// Store 32 consecutive output columns of one row: vector stores when the row segment is aligned, scalar otherwise.
+__device__ __forceinline__ void store_row32(void* out, int out_is_f32, size_t row, int ldo, int col0, int ncols, const float (&f)[32]) {
+    if (out_is_f32) {
+        float* o = static_cast<float*>(out) + row * ldo;
+        if (ncols == 32 && (ldo & 3) == 0) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) st_f32x4(o + col0 + j, make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]));
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (j < ncols) o[col0 + j] = f[j];
+        }
+    } else {
+        __nv_bfloat16* o = static_cast<__nv_bfloat16*>(out) + row * ldo;
+        if (ncols == 32 && (ldo & 7) == 0) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+                uint4 pk;
+                pk.x = pack_bf16x2(f[j], f[j + 1]);
+                pk.y = pack_bf16x2(f[j + 2], f[j + 3]);
+                pk.z = pack_bf16x2(f[j + 4], f[j + 5]);
+                pk.w = pack_bf16x2(f[j + 6], f[j + 7]);
+                *reinterpret_cast<uint4*>(o + col0 + j) = pk;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (j < ncols) o[col0 + j] = __float2bfloat16_rn(f[j]);
+        }
+    }
+}
+
 // Epilogue of one 128 x BN accumulator tile: every thread owns one TMEM lane = one output row, 32 columns at a time.
 template <int BN>
 __device__ __forceinline__ void gemm_epilogue_tile(uint32_t tmem_d, int q, int lane, int m0, int n0, int M, int N, const GemmEpilogue& ep,
@@ -119,7 +163,7 @@ __device__ __forceinline__ void gemm_epilogue_tile(uint32_t tmem_d, int q, int l
         uint32_t v[32];
         tmem_ld_32x32(tmem_d + (static_cast<uint32_t>(q * 32) << 16) + c0, v);
         tmem_ld_wait();
-        if (!row_ok) continue;
+        if (!row_ok && ep.pool_w == 0) continue;     // (with the fused pool every lane takes part in the shuffles)
         const int col0 = n0 + c0;
         const int ncols = min(32, N - col0);
         float f[32];
@@ -132,7 +176,14 @@ __device__ __forceinline__ void gemm_epilogue_tile(uint32_t tmem_d, int q, int l
         }
         if (ep.atomic) {
             float* o = static_cast<float*>(ep.out) + static_cast<size_t>(row) * ep.ldo;
-            if (ep.perm_cin > 0) {
+            if (ep.cpad > 0) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const int c = col0 + j;
+                    const int tap = c / ep.cpad, ch = c - tap * ep.cpad;
+                    if (j < ncols && ch < ep.cin) red_add_f32(o + (ep.perm_khw > 0 ? ch * ep.perm_khw + tap : tap * ep.cin + ch), f[j]);
+                }
+            } else if (ep.perm_cin > 0) {
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                     const int c = col0 + j;
@@ -146,38 +197,34 @@ __device__ __forceinline__ void gemm_epilogue_tile(uint32_t tmem_d, int q, int l
                 for (int j = 0; j < 32; ++j)
                     if (j < ncols) red_add_f32(o + col0 + j, f[j]);
             }
-        } else if (ep.out_is_f32) {
+        } else if (ep.out_is_f32 && ep.perm_cin > 0) {
             float* o = static_cast<float*>(ep.out) + static_cast<size_t>(row) * ep.ldo;
-            if (ep.perm_cin > 0) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const int c = col0 + j;
-                    if (j < ncols) o[(c % ep.perm_cin) * ep.perm_khw + c / ep.perm_cin] = f[j];
-                }
-            } else if (ncols == 32 && (ep.ldo & 3) == 0) {
-#pragma unroll
-                for (int j = 0; j < 32; j += 4) st_f32x4(o + col0 + j, make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]));
-            } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (j < ncols) o[col0 + j] = f[j];
+            for (int j = 0; j < 32; ++j) {
+                const int c = col0 + j;
+                if (j < ncols) o[(c % ep.perm_cin) * ep.perm_khw + c / ep.perm_cin] = f[j];
             }
         } else {
-            __nv_bfloat16* o = static_cast<__nv_bfloat16*>(ep.out) + static_cast<size_t>(row) * ep.ldo;
-            if (ncols == 32 && (ep.ldo & 7) == 0) {
+            if (!ep.out_is_f32) {
+                // the stored activation is bf16: pool (and everything downstream) must see the rounded values
 #pragma unroll
-                for (int j = 0; j < 32; j += 8) {
-                    uint4 pk;
-                    pk.x = pack_bf16x2(f[j], f[j + 1]);
-                    pk.y = pack_bf16x2(f[j + 2], f[j + 3]);
-                    pk.z = pack_bf16x2(f[j + 4], f[j + 5]);
-                    pk.w = pack_bf16x2(f[j + 6], f[j + 7]);
-                    *reinterpret_cast<uint4*>(o + col0 + j) = pk;
+                for (int j = 0; j < 32; ++j) f[j] = __bfloat162float(__float2bfloat16_rn(f[j]));
+            }
+            if (row_ok) store_row32(ep.out, ep.out_is_f32, static_cast<size_t>(row), ep.ldo, col0, ncols, f);
+            if (ep.pool_w > 0) {
+                // rows of a warp are 32 consecutive pixels of a [.., H, W] map with W | 16: lane bit 0 is the column parity and lane bit
+                // log2(W) the row parity, so the 2x2 window lives in lanes {l, l^1, l^W, l^W^1} of this warp
+                const int W = ep.pool_w;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    float m = fmaxf(f[j], __shfl_xor_sync(0xffffffffu, f[j], 1));
+                    f[j] = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, W));
                 }
-            } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (j < ncols) o[col0 + j] = __float2bfloat16_rn(f[j]);
+                if (row_ok && (lane & 1) == 0 && (lane & W) == 0) {
+                    const int irow = row / W;                                     // image row index over the whole batch (H is even)
+                    const size_t mp = static_cast<size_t>(irow >> 1) * (W >> 1) + ((row - irow * W) >> 1);
+                    store_row32(ep.pooled, ep.out_is_f32, mp, ep.ldp, col0, ncols, f);
+                }
             }
         }
     }
@@ -294,7 +341,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     constexpr int kStages = S::kStages;
     constexpr int kTmemCols = BN < 32 ? 32 : BN;
     static_assert(BN % 16 == 0 && BN >= 32 && BN <= 256, "UMMA M=128 needs N%16==0, 16<=N<=256");
-    static_assert(!B_MN || BN % E::kBK == 0, "MN-major B tiles are built from kBK-wide TMA boxes");
+    static_assert(!B_MN || BMODE == 4 || BN % E::kBK == 0, "MN-major B tiles are built from kBK-wide TMA boxes");
     constexpr int kBK = E::kBK;        // shadows the bf16-only namespace constant inside this kernel
 
     extern __shared__ uint8_t smem_raw[];
@@ -340,7 +387,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
         if (lane == 0) {
             // im2col A: the tile's first pixel in (n, p, q) and its input-space coordinates, computed once
             int a_n = 0, a_h = 0, a_w = 0;
-            if constexpr (AM == 2) {
+            if constexpr (AM >= 2) {
                 const int pq = cv.P * cv.Q;
                 a_n = m0 / pq;
                 const int rem = m0 - a_n * pq;
@@ -361,11 +408,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
                 } else if constexpr (AM == 1) {
 #pragma unroll
                     for (int j = 0; j < kBM / kBK; ++j) tma_load_2d(a_dst + j * E::kBoxBytes, &tma_a, m0 + kBK * j, k0, full_bar(s));
-                } else {
+                } else if constexpr (AM == 2) {
                     // k-block = kBK channels of one filter tap (C % kBK == 0): 128 pixels x 128 bytes, one instruction
                     const int tap = k0 / cv.C;
                     const int r = tap / cv.KW;
                     tma_load_im2col_4d(a_dst, &tma_a, k0 - tap * cv.C, a_w, a_h, a_n, tap - r * cv.KW, r, full_bar(s));
+                } else {
+                    // small-channel conv: k-block = 8 taps x one 16-byte channel granule; taps past the filter repeat the last one
+                    // (their weights are zero-filled by B's map, the products vanish, the byte count stays that of a full stage)
+                    const int ntaps = cv.KH * cv.KW;
+                    const int tap0 = (kb_begin + it) * 8;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int tap = min(tap0 + j, ntaps - 1);
+                        const int r = tap / cv.KW;
+                        tma_load_im2col_4d(a_dst + j * 2048, &tma_a, 0, a_w, a_h, a_n, tap - r * cv.KW, r, full_bar(s));
+                    }
                 }
                 if constexpr (BMODE == 0) {
                     tma_load_2d(b_dst, &tma_b, k0, n0, full_bar(s));
@@ -388,7 +446,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
                         const int r = tap / cv.KW;
                         tma_load_im2col_4d(b_dst + j * E::kBoxBytes, &tma_b, kcol - tap * cv.C, bw, bh, bn_, tap - r * cv.KW, r, full_bar(s));
                     }
-                } else {
+                } else if constexpr (BMODE == 3) {
                     // dgrad: reduction rows = kBK output channels of one (flipped) tap, columns = kBK input channels
                     const int tap = k0 / cv.C;
                     const int wtap = cv.flip ? (cv.KH * cv.KW - 1 - tap) : tap;
@@ -397,6 +455,24 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
                         int cin0 = n0 + kBK * j;
                         if (cin0 >= N) cin0 = 0;
                         tma_load_3d(b_dst + j * E::kBoxBytes, &tma_b, cin0, wtap, k0 - tap * cv.C, full_bar(s));
+                    }
+                } else {
+                    // small-channel wgrad: reduction rows = kBK output pixels starting at k0, columns = (tap, padded channel):
+                    // one box of kBK pixels x 16 B per tap, unswizzled (MN-major core matrices: 8 pixels x 16 B)
+                    constexpr int kGran = 16 / E::kBytes;                  // channels per 16-byte granule
+                    const int ntaps = cv.KH * cv.KW;
+                    const int pq = cv.P * cv.Q;
+                    const int bn_ = k0 / pq;
+                    const int rem = k0 - bn_ * pq;
+                    const int pp = rem / cv.Q;
+                    const int bh = cv.low_h + pp * cv.sh;
+                    const int bw = cv.low_w + (rem - pp * cv.Q) * cv.sw;
+                    const int tapb = n0 / kGran;
+#pragma unroll 4
+                    for (int j = 0; j < BN / kGran; ++j) {
+                        const int tap = min(tapb + j, ntaps - 1);
+                        const int r = tap / cv.KW;
+                        tma_load_im2col_4d(b_dst + j * (kBK * 16), &tma_b, 0, bw, bh, bn_, tap - r * cv.KW, r, full_bar(s));
                     }
                 }
             }
@@ -416,10 +492,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
                 for (int k = 0; k < kBK / E::kUmmaK; ++k) {
                     // K-major: one UMMA_K = 32 B inside the 128 B swizzle row (16 bf16 / 8 tf32).
                     // MN-major: one UMMA_K = UMMA_K K-rows of 128 B; the next 128 B of MN start one TMA box (kBoxBytes) further.
-                    const uint64_t adesc = A_MN ? umma_smem_desc_l(a_src + k * E::kMnStep, E::kBoxBytes, E::kMnSbo, E::kMnLayout)
-                                                : umma_smem_desc(a_src + k * 32, 16, 1024);
-                    const uint64_t bdesc = B_MN ? umma_smem_desc_l(b_src + k * E::kMnStep, E::kBoxBytes, E::kMnSbo, E::kMnLayout)
-                                                : umma_smem_desc(b_src + k * 32, 16, 1024);
+                    // small-channel forms (unswizzled): A — one UMMA_K = 2 taps = 2 x 2048 B, taps 2048 B apart (LBO), 8-pixel groups
+                    // 128 B apart (SBO); B — one UMMA_K = UMMA_K pixel rows of 16 B, 8-row groups 128 B apart (LBO), taps kBK*16 B apart (SBO)
+                    const uint64_t adesc = AM == 3 ? umma_smem_desc_l(a_src + k * 4096, 2048, 128, 0)
+                                           : A_MN  ? umma_smem_desc_l(a_src + k * E::kMnStep, E::kBoxBytes, E::kMnSbo, E::kMnLayout)
+                                                   : umma_smem_desc(a_src + k * 32, 16, 1024);
+                    const uint64_t bdesc = BMODE == 4 ? umma_smem_desc_l(b_src + k * (E::kUmmaK * 16), 128, kBK * 16, 0)
+                                           : B_MN     ? umma_smem_desc_l(b_src + k * E::kMnStep, E::kBoxBytes, E::kMnSbo, E::kMnLayout)
+                                                      : umma_smem_desc(b_src + k * 32, 16, 1024);
                     if constexpr (E::kTf32) umma_tf32(tmem_d, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
                     else                    umma_bf16(tmem_d, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
                 }
@@ -954,9 +1034,10 @@ static EncodeIm2colFn get_encode_im2col_fn() {
 
 // im2col tensor map over an NHWC activation [N, H, W, C] (channel pitch ld): boxes of `pixels` output pixels x kBK channels (128 B).
 // Bounding box per spatial dim: [low, dim - 1 + up]; the instruction adds the filter-tap offset to every pixel.
+// small_c: one 16-byte channel granule per pixel and tap, written UNSWIZZLED (core-matrix layout of the small-channel operand forms).
 template <typename E>
 static int make_tmap_im2col(CUtensorMap* map, const void* base, int C, int W, int H, int N, int ld, int low_w, int low_h, int up_w, int up_h,
-                            int sw, int sh, int pixels, bool mn_major) {
+                            int sw, int sh, int pixels, bool mn_major, bool small_c = false) {
     EncodeIm2colFn fn = get_encode_im2col_fn();
     DMLB_REQUIRE(fn != nullptr, "cuTensorMapEncodeIm2col entry point not available");
     DMLB_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0 && (ld * E::kBytes) % 16 == 0, "im2col TMA needs a 16-byte aligned NHWC tensor");
@@ -966,9 +1047,10 @@ static int make_tmap_im2col(CUtensorMap* map, const void* base, int C, int W, in
     int lower[2] = {low_w, low_h};
     int upper[2] = {up_w, up_h};
     cuuint32_t trav[4] = {1, (cuuint32_t)sw, (cuuint32_t)sh, 1};
-    CUresult r = fn(map, tma_dtype<E>(), 4, const_cast<void*>(base), dims, strides, lower, upper, E::kBK, (cuuint32_t)pixels, trav,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? E::kTmaMnSwizzle : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    const cuuint32_t box_c = small_c ? (cuuint32_t)(16 / E::kBytes) : (cuuint32_t)E::kBK;
+    const CUtensorMapSwizzle swz = small_c ? CU_TENSOR_MAP_SWIZZLE_NONE : (mn_major ? E::kTmaMnSwizzle : CU_TENSOR_MAP_SWIZZLE_128B);
+    CUresult r = fn(map, tma_dtype<E>(), 4, const_cast<void*>(base), dims, strides, lower, upper, box_c, (cuuint32_t)pixels, trav,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         char buf[256];
         snprintf(buf, sizeof(buf), "cuTensorMapEncodeIm2col failed: CUresult %d (C=%d W=%d H=%d N=%d ld=%d low=%d,%d up=%d,%d stride=%d,%d pixels=%d elem=%dB)",
@@ -1109,7 +1191,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmE
     const int nkb = (K + E::kBK - 1) / E::kBK;
     const int kb_per = (nkb + splits - 1) / splits;
     const long long ctas = 1ll * ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN) * ((nkb + kb_per - 1) / kb_per);
-    if constexpr (!E::kTf32 && BN <= 128 && BMODE == 0) {
+    if constexpr (!E::kTf32 && BN <= 128 && BMODE == 0 && AM != 3) {
         // forward form only (both operands K-major): the backward GEMMs share the GPU with the side-stream wgrad branch and a grid
         // that pins every SM would serialise against it.  Short reductions only: with a long K loop the per-tile set-up is already amortised and the 2-CTA variant rasterises better
         if (splits == 1 && ep.fin_counters == nullptr && nkb <= 24 && ctas >= 3ll * dmlb_sm_count() && dmlb_gemm_persistent_enabled())
@@ -1292,6 +1374,69 @@ static int conv_implicit_impl(const FinishArgs* fin, int kind, const void* act, 
         if (BN == 128) return launch_gemm<E, 128, 2, 3>(ta, tb, ep, cv, (int)Mpix, Cin, Kd, split_k, stream);
     }
     dmlb_set_error("dmlb_conv_implicit: unsupported tile_n for this kind");
+    return -4;
+}
+
+// Implicit-GEMM convolution for SMALL channel counts (the first layer of every model here: Cin = 3).  The activation is channels-last with
+// exactly one 16-byte granule per pixel (4 fp32 / 8 bf16 channels, the unused ones zero); a k-block gathers eight filter taps, so the
+// reduction is kh*kw*granule long instead of kh*kw*64 — see the A = 3 / B = 4 operand forms of the kernel.
+//   kind 0  fprop: out[B*Ho*Wo, Cout] = conv(x, W);   other = W as [Cout, kh*kw*granule] (pad channels zero), K-major
+//                  pool_w > 0 additionally writes maxpool2x2(out) to pooled (fused in the epilogue; needs Wo | 16, Ho even)
+//   kind 1  wgrad: out[Cout, kh*kw*cin] (+)= dY^T * im2col(x);  other = dY [B*Ho*Wo, ld_other]; pad-channel columns are dropped;
+//                  pt_layout = 1 writes PyTorch's [Cout, Cin, kh, kw] order instead of [Cout, kh, kw, Cin]
+// Reference: the first nn.Conv2d of example/models.py:8,29 (3 -> 6 5x5 and 3 -> 64 11x11 stride 4).
+template <typename E>
+static int conv_smallc_impl(int kind, const void* act, int B, int Ha, int Wa, int cin, const void* other, int ld_other, int KH, int KW, int SH,
+                            int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo, const float* bias, int relu, int split_k,
+                            int pt_layout, void* pooled, int ldp, int pool_w, int tile_n, void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    constexpr int BK = E::kBK;
+    constexpr int G = 16 / E::kBytes;            // channels per granule = channel pitch of the activation
+    DMLB_REQUIRE(kind == 0 || kind == 1, "kind must be 0 (fprop) or 1 (wgrad)");
+    DMLB_REQUIRE(cin >= 1 && cin <= G, "small-channel convolution: Cin must fit one 16-byte granule (4 fp32 / 8 bf16 channels)");
+    DMLB_REQUIRE(!E::kTf32 || out_is_f32, "the tf32 convolution writes fp32");
+    const int Ho = (Ha + 2 * PH - KH) / SH + 1, Wo = (Wa + 2 * PW - KW) / SW + 1;
+    DMLB_REQUIRE(Ho > 0 && Wo > 0, "empty conv output");
+    const int ntaps = KH * KW;
+    const int Kg = ntaps * G;                    // GEMM reduction length of fprop = column count of wgrad
+    const long long Mpix = 1ll * B * Ho * Wo;
+    DMLB_REQUIRE(Mpix < (1ll << 31), "too many output pixels");
+    if (split_k < 1) split_k = 1;
+    GemmEpilogue ep = {};
+    ConvK cv = {};
+    cv.C = G; cv.KH = KH; cv.KW = KW; cv.sh = SH; cv.sw = SW; cv.P = Ho; cv.Q = Wo; cv.low_h = -PH; cv.low_w = -PW; cv.flip = 0;
+    CUtensorMap ta, tb;
+    int rc;
+    if (kind == 0) {
+        const int N = n_out;
+        DMLB_REQUIRE(split_k == 1, "small-channel fprop has a short reduction: no split-K");
+        int BN = tile_n ? tile_n : ((N > 64) ? 128 : (N > 32 ? 64 : 32));
+        ep.out = out; ep.bias = bias; ep.ldo = ldo; ep.out_is_f32 = out_is_f32; ep.relu = relu;
+        if (pool_w > 0) {
+            DMLB_REQUIRE(pool_w == Wo && (pool_w & (pool_w - 1)) == 0 && pool_w >= 2 && pool_w <= 16 && Ho % 2 == 0 && pooled != nullptr,
+                         "fused 2x2 pool needs a power-of-two output width <= 16 and an even height");
+            ep.pooled = pooled; ep.ldp = ldp; ep.pool_w = pool_w;
+        }
+        rc = make_tmap_im2col<E>(&ta, act, G, Wa, Ha, B, G, -PW, -PH, PW - (KW - 1), PH - (KH - 1), SW, SH, kBM, false, true);
+        if (rc) return rc;
+        rc = make_tmap_2d<E>(&tb, other, (uint64_t)Kg, (uint64_t)N, (uint64_t)ld_other, BK, (uint32_t)BN, false);
+        if (rc) return rc;
+        if (BN == 32) return launch_gemm<E, 32, 3, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, 1, stream);
+        if (BN == 64) return launch_gemm<E, 64, 3, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, 1, stream);
+        if (BN == 128) return launch_gemm<E, 128, 3, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, 1, stream);
+    } else {
+        const int Cout = n_out;
+        int BN = tile_n ? tile_n : 128;
+        DMLB_REQUIRE(out_is_f32, "weight gradients accumulate in fp32");
+        ep.out = out; ep.ldo = ldo; ep.out_is_f32 = 1; ep.atomic = 1; ep.cpad = G; ep.cin = cin; ep.perm_khw = pt_layout ? ntaps : 0;
+        rc = make_tmap_2d<E>(&ta, other, (uint64_t)Cout, (uint64_t)Mpix, (uint64_t)ld_other, BK, BK, true);   // dY as MN-major A
+        if (rc) return rc;
+        rc = make_tmap_im2col<E>(&tb, act, G, Wa, Ha, B, G, -PW, -PH, PW - (KW - 1), PH - (KH - 1), SW, SH, BK, true, true);
+        if (rc) return rc;
+        if (BN == 64) return launch_gemm<E, 64, 1, 4>(ta, tb, ep, cv, Cout, Kg, (int)Mpix, split_k, stream);
+        if (BN == 128) return launch_gemm<E, 128, 1, 4>(ta, tb, ep, cv, Cout, Kg, (int)Mpix, split_k, stream);
+    }
+    dmlb_set_error("dmlb_conv_smallc: unsupported tile_n for this kind");
     return -4;
 }
 

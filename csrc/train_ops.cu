@@ -132,8 +132,10 @@ __global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ param
 // ---------------------------------------------------------------------------------------------
 struct ShadowEntry {
     long long src_off;   // elements into the fp32 arena
-    long long dst_off;   // elements into the bf16 shadow arena
+    long long dst_off;   // elements into the shadow arena
     int rows, cin, khw, ld;
+    int cpad;            // 0: columns (khw, cin) dense.  > 0: small-channel layout, cpad channels per tap (the extra ones stay zero)
+    int src_gemm_order;  // source is stored [rows, khw, cin] (channels-last arena) instead of PyTorch's [rows, cin, khw]
 };
 
 template <typename T>
@@ -151,7 +153,8 @@ __global__ void __launch_bounds__(256) refresh_shadows_kernel(const float* __res
         const int k = static_cast<int>(i % K);
         const int ci = k % e.cin;
         const int kk = k / e.cin;
-        dst[1ll * r * e.ld + k] = from_f32<T>(__ldg(src + (1ll * r * e.cin + ci) * e.khw + kk));
+        const float v = e.src_gemm_order ? __ldg(src + 1ll * r * K + k) : __ldg(src + (1ll * r * e.cin + ci) * e.khw + kk);
+        dst[1ll * r * e.ld + (e.cpad > 0 ? kk * e.cpad + ci : k)] = from_f32<T>(v);
     }
 }
 
@@ -287,6 +290,23 @@ extern "C" int dmlb_sgd_flat_slot(float* params, float* grads, void* acc_slot, f
 }
 
 namespace dmlb {
+// fp32 NCHW batch -> channels-last activation with ONE 16-byte granule per pixel (C <= 4 fp32 / 8 bf16 channels, the rest zero): the
+// input layout of the small-channel first-layer convolution.  One thread per pixel: C strided reads, one 16-byte store.
+template <typename T>
+__global__ void __launch_bounds__(256) nchw_to_act_kernel(const float* __restrict__ x, T* __restrict__ y, int B, int C, long long plane) {
+    pdl_prologue();
+    constexpr int G = 16 / sizeof(T);
+    const long long total = 1ll * B * plane;
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
+        const long long b = i / plane, p = i - b * plane;
+        const float* src = x + b * C * plane + p;
+        float f[G];
+#pragma unroll
+        for (int c = 0; c < G; ++c) f[c] = c < C ? __ldg(src + c * plane) : 0.f;
+        Vec16<T>::store(y + i * G, f);
+    }
+}
+
 __global__ void store_u64_kernel(unsigned long long* slot, unsigned long long value) { *slot = value; }
 
 // params = pulled + unpushed;  shadow = bf16(params)   (n4 float4 groups; unpushed / shadow may be null)
@@ -311,6 +331,21 @@ __global__ void __launch_bounds__(256) apply_pull_kernel(float* __restrict__ par
 }
 }  // namespace dmlb
 
+extern "C" int dmlb_nchw_to_act_bf16(const float* x, void* y, int B, int C, int H, int W, void* stream) {
+    DMLB_REQUIRE(C >= 1 && C <= 8, "one 16-byte granule holds at most 8 bf16 channels");
+    DMLB_CHECK_CUDA(launch_k(nchw_to_act_kernel<__nv_bfloat16>, flat_grid(1ll * B * H * W), 256, 0, static_cast<cudaStream_t>(stream), x,
+                             static_cast<__nv_bfloat16*>(y), B, C, 1ll * H * W));
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+extern "C" int dmlb_nchw_to_act_f32(const float* x, void* y, int B, int C, int H, int W, void* stream) {
+    DMLB_REQUIRE(C >= 1 && C <= 4, "one 16-byte granule holds at most 4 fp32 channels");
+    DMLB_CHECK_CUDA(launch_k(nchw_to_act_kernel<float>, flat_grid(1ll * B * H * W), 256, 0, static_cast<cudaStream_t>(stream), x,
+                             static_cast<float*>(y), B, C, 1ll * H * W));
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
 // *slot = value on the stream (8 bytes of device memory): how the host retargets dmlb_sgd_flat_slot / dmlb_apply_pull between replays.
 extern "C" int dmlb_store_u64(void* slot, unsigned long long value, void* stream) {
     DMLB_REQUIRE(slot != nullptr && (reinterpret_cast<uintptr_t>(slot) & 7) == 0, "slot must be an 8-byte aligned device address");
@@ -329,7 +364,7 @@ extern "C" int dmlb_apply_pull(float* params, const float* pulled, void* unpushe
     return 0;
 }
 
-// table: device array of n_entries ShadowEntry {int64 src_off, int64 dst_off, int32 rows, cin, khw, ld}.
+// table: device array of n_entries ShadowEntry {int64 src_off, int64 dst_off, int32 rows, cin, khw, ld, cpad, src_gemm_order}.
 extern "C" int dmlb_refresh_shadows(const float* params, void* shadow, const void* table, int n_entries, void* stream) {
     if (n_entries <= 0) return 0;
     dim3 grid(96, n_entries);

@@ -61,6 +61,20 @@ class TrainStep:
         self.batch_size = batch_size
         self.loss_fn = loss_fn or OF.cross_entropy
         self.static_x = torch.zeros((batch_size, *input_shape), dtype=torch.float32, device=self.device)
+        # A model whose first layer is a small-channel convolution (RGB input) reads a channels-last, one-16-byte-granule-per-pixel
+        # activation: keep the static input in that layout, so the per-step device copy of the batch IS the layout change (one kernel,
+        # outside the graph, in place of a memcpy) and the captured step starts directly with the implicit-GEMM convolution.
+        self._smallc_in = False
+        if self.device.type == "cuda":
+            from . import nn as dnn
+            from .ops import kernels as K
+            first = next((m for m in model.modules() if isinstance(m, dnn.Conv2d)), None)
+            if first is not None and first._smallc() and first.in_channels == input_shape[0]:
+                g = K.granule(first.compute_dtype)
+                buf = torch.zeros((batch_size, input_shape[1], input_shape[2], g), dtype=first.compute_dtype, device=self.device)
+                self.static_x = buf[..., :input_shape[0]].permute(0, 3, 1, 2)
+                self.static_x._dmlb_padzero = True
+                self._smallc_in = True
         self.static_y = torch.zeros((batch_size,), dtype=torch.int64, device=self.device)
         self.metrics = torch.zeros(2, dtype=torch.float32, device=self.device)
         self._pinned = None
@@ -173,7 +187,13 @@ class TrainStep:
                 x.record_stream(self.stream)
                 y.record_stream(self.stream)
         with torch.cuda.stream(self.stream):
-            self.static_x.copy_(x, non_blocking=True)
+            if self._smallc_in:
+                from .ops import kernels as K
+                if x.dtype != torch.float32 or not x.is_contiguous():
+                    x = x.float().contiguous()
+                K.nchw_to_act(x, self.static_x)
+            else:
+                self.static_x.copy_(x, non_blocking=True)
             self.static_y.copy_(y, non_blocking=True)
             if self._staging is not None and x is self._staging[slot][0]:
                 self._consumed[slot].record(self.stream)

@@ -103,12 +103,26 @@ class _ShadowedModule(nn.Module):
             return False
         return not _gemm_order(self.weight)
 
+    def _smallc(self) -> bool:
+        """Small-channel layout (first layers, <= 4 input channels): the shadow holds one 16-byte granule per filter tap."""
+        return False
+
+    def _shadow_ld(self) -> int:
+        rows, cin, khw = self._shadow_dims()
+        if self._smallc():
+            return khw * K.granule(self.compute_dtype)
+        return K.pad_for(self.compute_dtype, cin * khw)
+
     def _shadow_entry(self) -> bytes:
         rows, cin, khw = self._shadow_dims()
-        ld = K.pad_for(self.compute_dtype, cin * khw)
+        ld = self._shadow_ld()
+        dst = self._shadow.data_ptr() // self._shadow.element_size()
+        if self._smallc():
+            in_gemm_order = _gemm_order(self.weight) or cin == 1
+            return struct.pack("<qqiiiiii", self.weight.data_ptr() // 4, dst, rows, cin, khw, ld, K.granule(self.compute_dtype), int(in_gemm_order))
         if not self._needs_permute():
             cin, khw = cin * khw, 1       # source already in GEMM order: plain cast with a row pitch
-        return struct.pack("<qqiiii", self.weight.data_ptr() // 4, self._shadow.data_ptr() // self._shadow.element_size(), rows, cin, khw, ld)
+        return struct.pack("<qqiiiiii", self.weight.data_ptr() // 4, dst, rows, cin, khw, ld, 0, 0)
 
     def _ensure_shadow_storage(self) -> None:
         rows, cin, khw = self._shadow_dims()
@@ -116,6 +130,15 @@ class _ShadowedModule(nn.Module):
         w = self.weight
         slot = self._arena_slot
         flat_ok = False
+        if self._smallc():
+            ld = self._shadow_ld()
+            if self._flat or self._shadow is None or self._shadow.device != w.device or tuple(self._shadow.shape) != (rows, ld) \
+                    or self._shadow.dtype != self.compute_dtype:
+                self._shadow = torch.zeros((rows, ld), dtype=self.compute_dtype, device=w.device)     # pad channels stay zero for ever
+                self._flat, self._shadow_key = False, None
+                if self._shadow_set is not None:
+                    self._shadow_set.invalidate_table()
+            return
         if self.compute_dtype == torch.float32:
             # tf32: fp32 storage already in GEMM order with 16-byte rows is read by TMA as it is
             if w.dim() == 4:
@@ -212,7 +235,7 @@ class ShadowSet:
         self._has_flat = any(m._flat for m in self.modules)
         self._n_table = len(tabled)
         dev = self.modules[0].weight.device
-        raw = b"".join(m._shadow_entry() for m in tabled) or b"\0" * 32
+        raw = b"".join(m._shadow_entry() for m in tabled) or b"\0" * 40
         self._table = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(dev)
         self._ptrs = self._signature()
 
@@ -277,12 +300,16 @@ class Conv2d(_ShadowedModule):
     def _shadow_dims(self):
         return self.out_channels, self.in_channels, self.kernel_size[0] * self.kernel_size[1]
 
+    def _smallc(self) -> bool:
+        # RGB / grey-scale first layers: <= 4 channels fit one 16-byte granule in either compute dtype
+        return self.in_channels <= 4 and self.kernel_size[0] * self.kernel_size[1] > 1 and OF.smallc_enabled()
+
     def forward(self, x):
         relu = self.activation == "relu"
         if not x.is_cuda:
             return OF.conv_block(x, self.weight, self.bias, self.stride, self.padding, relu, self.pool)
         return OF.conv_block(x, self.weight, self.bias, self.stride, self.padding, relu, self.pool, shadow=self.shadow(),
-                             wsink=self._wsink, bsink=self._bsink, sole_consumer=self.sole_consumer_is_conv)
+                             wsink=self._wsink, bsink=self._bsink, sole_consumer=self.sole_consumer_is_conv, smallc=self._smallc())
 
     def extra_repr(self):
         return (f"{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, stride={self.stride}, padding={self.padding}, "

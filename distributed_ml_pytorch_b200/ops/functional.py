@@ -239,7 +239,24 @@ def _sink_ok(param: torch.Tensor, sink: Optional[torch.Tensor]) -> bool:
 # ------------------------------------------------------------------------------------------------
 # conv (+bias +ReLU +max-pool) block
 # ------------------------------------------------------------------------------------------------
-_conv_opts = SimpleNamespace(implicit=True)
+_conv_opts = SimpleNamespace(implicit=True, smallc=os.environ.get("DMLB_SMALLC", "1") == "1")
+
+
+def smallc_enabled() -> bool:
+    """Small-channel first layers (Cin <= 4) run as implicit GEMMs gathering eight filter taps per k-block (no column matrix)."""
+    return _conv_opts.smallc
+
+
+def to_smallc_act(x: torch.Tensor, dt) -> torch.Tensor:
+    """fp32 NCHW batch with C <= 4 -> the channels-last, one-granule-per-pixel activation the small-channel convolution reads
+    (pad channels zero).  :class:`~distributed_ml_pytorch_b200.engine.TrainStep` keeps its static input in this layout."""
+    B, C, H, W = x.shape
+    g = K.granule(dt)
+    buf = torch.empty((B, H, W, g), dtype=dt, device=x.device)
+    K.nchw_to_act(x, buf)
+    out = buf[..., :C].permute(0, 3, 1, 2)
+    out._dmlb_padzero = True
+    return out
 
 
 def set_implicit_conv(flag: bool) -> bool:
@@ -286,6 +303,8 @@ class _ConvBlockFn(torch.autograd.Function):
         bk = K.kblock(dt)
         Kpad = pad_for(dt, Kd)
         dev = x.device
+        if cfg.smallc:
+            return _ConvBlockFn._forward_smallc(ctx, x, weight, bias, cfg, (B, H, W, Cin, Cout, KH, KW, SH, SW, PH, PW, Ho, Wo))
         from_nchw_f32 = act4_pitch(x, dt) is None and x.dtype == torch.float32 and x.is_contiguous()
         direct = (not from_nchw_f32) and KH == 1 and KW == 1 and SH == 1 and SW == 1 and PH == 0 and PW == 0 and Cin % _vec(dt) == 0
         implicit = _conv_opts.implicit and (not from_nchw_f32) and (not direct) and Cin % bk == 0
@@ -363,6 +382,52 @@ class _ConvBlockFn(torch.autograd.Function):
         return out
 
     @staticmethod
+    def _forward_smallc(ctx, x, weight, bias, cfg, geom):
+        """First layers (Cin <= 4): the input is one 16-byte granule per pixel; eight filter taps form one k-block of the implicit GEMM."""
+        (B, H, W, Cin, Cout, KH, KW, SH, SW, PH, PW, Ho, Wo) = geom
+        dt, dev = cfg.dt, x.device
+        g = K.granule(dt)
+        if act4_pitch(x, dt) == g and getattr(x, "_dmlb_padzero", False):
+            xa = x                                               # already in the layout (TrainStep's static input)
+        elif x.dtype == torch.float32 and x.is_contiguous():
+            xa = to_smallc_act(x, dt)                            # the user's NCHW batch (reference main.py:64-70): one small kernel
+        else:
+            _warn_once("smallc_in", "a small-channel convolution received an activation whose pad channels are not known to be zero; "
+                                    "re-laying it out with ATen copies")
+            buf = torch.zeros((B, H, W, g), dtype=dt, device=dev)
+            xa = buf[..., :Cin].permute(0, 3, 1, 2)
+            xa.copy_(x)
+        Kg = KH * KW * g
+        M = B * Ho * Wo
+        y = new_act4(B, Cout, Ho, Wo, dev, dt)
+        ldy = pad_for(dt, Cout)
+        out = y
+        pool_w = 0
+        if cfg.pool == (2, 2, 0) and Ho % 2 == 0 and Wo in (2, 4, 8, 16):
+            out = new_act4(B, Cout, Ho // 2, Wo // 2, dev, dt)   # 2x2 pool by warp shuffles in the GEMM epilogue
+            pool_w = Wo
+        K.conv_smallc(0, xa.data_ptr(), B, H, W, Cin, cfg.shadow.data_ptr(), Kg, KH, KW, SH, SW, PH, PW, Cout, y, ldy, bias=bias, relu=cfg.relu,
+                      pooled_ptr=out.data_ptr() if pool_w else 0, ldp=ldy, pool_w=pool_w, dt=dt)
+        if cfg.pool is not None and not pool_w:
+            k, s, p = cfg.pool
+            Hp, Wp = (Ho + 2 * p - k) // s + 1, (Wo + 2 * p - k) // s + 1
+            out = new_act4(B, Cout, Hp, Wp, dev, dt)
+            K.maxpool_fwd(y.data_ptr(), out.data_ptr(), B, Ho, Wo, Cout, ldy, ldy, k, s, p, dt=dt)
+        ctx.cfg = cfg
+        cfg.fwd = None
+        if cfg.sole_consumer and _fuse.enabled:
+            pool2 = cfg.pool == (2, 2, 0)
+            if (cfg.pool is None or (pool2 and Ho % 2 == 0 and Wo % 2 == 0)) and Cout % 4 == 0:
+                cfg.fwd = SimpleNamespace(y=y, B=B, Ho=Ho, Wo=Wo, C=Cout, ldy=ldy, dt=dt, pool2=pool2, relu=cfg.relu, out_ptr=out.data_ptr(),
+                                          bias=bias, bsink=cfg.bsink if (bias is not None and _sink_ok(bias, cfg.bsink)) else None,
+                                          needs_bias_grad=bias is not None and bias.requires_grad)
+        ctx.x_ptr = xa.data_ptr()
+        ctx.geom = (B, H, W, Cin, Cout, KH, KW, SH, SW, PH, PW, Ho, Wo, Cin * KH * KW, Kg, g, 0, False, False, False)
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(xa, y if (cfg.relu or cfg.pool is not None) else None, weight, bias)
+        return out
+
+    @staticmethod
     def backward(ctx, dout):
         cfg = ctx.cfg
         a_t, y, weight, bias = ctx.saved_tensors
@@ -416,7 +481,11 @@ class _ConvBlockFn(torch.autograd.Function):
                 target = gw
                 gemm_order = KH * KW == 1 or Cin == 1 or target.permute(0, 2, 3, 1).is_contiguous()
             with _WgradFork(dev, dy, a_t, gw) as fork:
-                if implicit and gemm_order:
+                if cfg.smallc:
+                    # columns of the GEMM are (tap, padded channel); the epilogue drops the pad channels and writes either order
+                    K.conv_smallc(1, a_t.data_ptr(), B, H, W, Cin, dy.data_ptr(), lddy, KH, KW, SH, SW, PH, PW, Cout, target, Kd,
+                                  split_k=split, pt_layout=not gemm_order, dt=dt)
+                elif implicit and gemm_order:
                     K.conv_implicit(1, a_t.data_ptr(), ldx, B, H, W, Cin, dy.data_ptr(), lddy, KH, KW, SH, SW, PH, PW, Cout, target, Kd,
                                     split_k=split, atomic=True, dt=dt)
                 else:
@@ -440,7 +509,13 @@ class _ConvBlockFn(torch.autograd.Function):
                 raise RuntimeError("gradient w.r.t. an fp32 NCHW network input is not implemented on the CUDA path")
             dx = new_act4(B, Cin, H, W, dev, dt)
             ldxo = pad_for(dt, Cin)
-            if direct:
+            if cfg.smallc:
+                # rare (a small-channel layer that is not the first): explicit transposed conv over the tap-padded weights
+                g = K.granule(dt)
+                dcol = torch.empty((M, Kpad), dtype=dt, device=dev)
+                K.gemm(dy, lddy, False, cfg.shadow, Kpad, True, M, Kpad, Cout, dcol, Kpad)
+                K.col2im_nhwc(dcol, dx.data_ptr(), B, H, W, g, ldxo, KH, KW, SH, SW, PH, PW, Kpad)
+            elif direct:
                 K.gemm(dy, lddy, False, cfg.shadow, Kpad, True, M, Kd, Cout, dx, ldxo)
             elif implicit and SH == 1 and SW == 1 and Cout % bk == 0 and Cin % _vec(dt) == 0 and Kpad == Kd:
                 # transposed convolution as an implicit GEMM over dY: no dcol matrix, no col2im
@@ -485,7 +560,7 @@ class _ConvBlockFn(torch.autograd.Function):
 
 
 def conv_block(x, weight, bias=None, stride=(1, 1), padding=(0, 0), relu=False, pool=None, shadow=None, wsink=None, bsink=None,
-               sole_consumer=False):
+               sole_consumer=False, smallc=False):
     """``max_pool(relu(conv2d(x, weight, bias)))`` with the optional parts fused (CUDA) or composed (CPU).
 
     ``sole_consumer=True`` promises that the result is read by exactly one op and that op is another ``conv_block``: its backward may
@@ -505,7 +580,8 @@ def conv_block(x, weight, bias=None, stride=(1, 1), padding=(0, 0), relu=False, 
     if shadow is None:
         raise RuntimeError("conv_block on CUDA needs the GEMM-layout weight shadow (use nn.Conv2d from this package)")
     cfg = SimpleNamespace(stride=tuple(stride), padding=tuple(padding), relu=bool(relu), pool=pool, shadow=shadow, wsink=wsink, bsink=bsink,
-                          dt=shadow.dtype, sole_consumer=bool(sole_consumer), prod=getattr(x, "_dmlb_prod", None), fwd=None)
+                          dt=shadow.dtype, sole_consumer=bool(sole_consumer), prod=getattr(x, "_dmlb_prod", None), fwd=None,
+                          smallc=bool(smallc))
     out = _ConvBlockFn.apply(x, weight, bias, cfg)
     if cfg.fwd is not None:
         out._dmlb_prod = cfg          # "this activation's only reader is a conv block": lets that block fuse our activation backward

@@ -75,6 +75,26 @@ def conv_implicit(kind: int, act_ptr: int, ld_act: int, B, Ha, Wa, Ca, other_ptr
           stream_ptr())
 
 
+def granule(dt) -> int:
+    """Channels in one 16-byte granule: the channel pitch of a small-channel (first-layer) activation."""
+    return 4 if dt == torch.float32 else 8
+
+
+def conv_smallc(kind: int, act_ptr: int, B, Ha, Wa, cin, other_ptr: int, ld_other: int, KH, KW, SH, SW, PH, PW, n_out: int, out: torch.Tensor,
+                ldo: int, bias=None, relu: bool = False, split_k: int = 1, pt_layout: bool = False, pooled_ptr: int = 0, ldp: int = 0,
+                pool_w: int = 0, tile_n: int = 0, dt=torch.bfloat16) -> None:
+    """Small-channel first-layer convolution (``dmlb_conv_smallc_*``): kind 0 fprop (optional fused 2x2 pool), 1 wgrad."""
+    _call("dmlb_conv_smallc_tf32" if dt == torch.float32 else "dmlb_conv_smallc_bf16", kind, act_ptr, B, Ha, Wa, cin, other_ptr, ld_other, KH, KW,
+          SH, SW, PH, PW, n_out, out.data_ptr(), int(out.dtype == torch.float32), ldo, bias.data_ptr() if bias is not None else None, int(relu),
+          split_k, int(pt_layout), pooled_ptr or None, ldp, pool_w, tile_n, stream_ptr())
+
+
+def nchw_to_act(x: torch.Tensor, y: torch.Tensor) -> None:
+    """fp32 NCHW batch -> channels-last activation ``y`` with one zero-padded 16-byte granule per pixel (``dmlb_nchw_to_act_*``)."""
+    B, C, H, W = x.shape
+    _call("dmlb_nchw_to_act_" + _sfx(y.dtype), x.data_ptr(), y.data_ptr(), B, C, H, W, stream_ptr())
+
+
 def pick_split_k(tiles: int, k_total: int, sms: int = 148, min_kblocks: int = 2, bk: int = 64) -> int:
     """Split-K factor that fills the SMs when the output has few tiles (weight gradients, tiny-M fprop)."""
     nkb = (k_total + bk - 1) // bk

@@ -60,6 +60,18 @@ int dmlb_conv_implicit_tf32(int kind, const void* act, int ld_act, int B, int Ha
                             int SH, int SW, int PH, int PW, int n_out, void* out, int ldo, const float* bias, int relu, int split_k,
                             int atomic, int tile_n, void* stream);
 
+/* Small-channel first-layer convolution as an implicit GEMM (reference: the first nn.Conv2d of example/models.py:8,29 — 3 input channels).
+ * act is channels-last with ONE 16-byte granule per pixel (bf16: 8 channels, fp32/tf32: 4; unused channels zero; see dmlb_nchw_to_act_*);
+ * a 128-byte k-block gathers eight filter taps by TMA im2col, so the reduction is kh*kw*granule long.
+ * kind 0 fprop: other = weights [n_out, kh*kw*granule] (pad channels zero); optional fused 2x2 max-pool into pooled (pool_w = output width).
+ * kind 1 wgrad: other = dY [pixels, ld_other]; out fp32 [n_out, kh*kw*cin] (+)=, PyTorch's [Cout,Cin,kh,kw] order when pt_layout = 1. */
+int dmlb_conv_smallc_bf16(int kind, const void* act, int B, int Ha, int Wa, int cin, const void* other, int ld_other, int KH, int KW, int SH,
+                          int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo, const float* bias, int relu, int split_k,
+                          int pt_layout, void* pooled, int ldp, int pool_w, int tile_n, void* stream);
+int dmlb_conv_smallc_tf32(int kind, const void* act, int B, int Ha, int Wa, int cin, const void* other, int ld_other, int KH, int KW, int SH,
+                          int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo, const float* bias, int relu, int split_k,
+                          int pt_layout, void* pooled, int ldp, int pool_w, int tile_n, void* stream);
+
 /* Implicit-GEMM convolution: the activation operand is gathered by TMA in im2col mode, no column matrix exists in memory.
  * kind 0 fprop (act = x, other = W shadow [n_out=Cout, kh*kw*Cin]), 1 wgrad (act = x, other = dY, out [n_out=Cout, kh*kw*Cin], fp32 accumulate),
  * 2 dgrad (act = dY with Ca = Cout, other = W shadow, n_out = Cin, stride 1 only).  The gathered tensor needs Ca % 64 == 0.
@@ -147,7 +159,11 @@ int dmlb_sgd_flat_slot(float* params, float* grads, void* acc_slot, float* mom, 
 int dmlb_store_u64(void* slot, unsigned long long value, void* stream);   /* *slot = value, stream ordered */
 /* Landing of an overlapped pull (Asynchronous.py:17-18): params = pulled (+ *unpushed_slot), bf16 mirror refreshed in the same pass. */
 int dmlb_apply_pull(float* params, const float* pulled, void* unpushed_slot, void* shadow_bf16, long long n, void* stream);
-/* table: device array of { int64 src_off, int64 dst_off, int32 rows, cin, khw, ld } — see csrc/train_ops.cu. */
+/* fp32 NCHW batch (the reference's input, example/main.py:64-70) -> channels-last activation with one 16-byte granule per pixel
+ * (C <= 8 bf16 / 4 fp32 channels, the rest zero): the input layout of dmlb_conv_smallc_*. */
+int dmlb_nchw_to_act_bf16(const float* x, void* y, int B, int C, int H, int W, void* stream);
+int dmlb_nchw_to_act_f32(const float* x, void* y, int B, int C, int H, int W, void* stream);
+/* table: device array of { int64 src_off, int64 dst_off, int32 rows, cin, khw, ld, cpad, src_gemm_order } — see csrc/train_ops.cu. */
 int dmlb_refresh_shadows(const float* params, void* shadow, const void* table, int n_entries, void* stream);
 int dmlb_refresh_shadows_f32(const float* params, void* shadow, const void* table, int n_entries, void* stream);   /* fp32 copies (tf32 path) */
 int dmlb_cast_f32_bf16(const float* x, void* y, long long rows, int C, long long ldx, int ldy, void* stream);
