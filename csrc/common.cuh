@@ -167,6 +167,12 @@ __device__ __forceinline__ void tma_load_im2col_4d(uint32_t dst_smem, const CUte
         "h"(static_cast<unsigned short>(off_w)), "h"(static_cast<unsigned short>(off_h))
         : "memory");
 }
+__device__ __forceinline__ void tma_load_4d(uint32_t dst_smem, const CUtensorMap* m, int c0, int c1, int c2, int c3, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];" ::"r"(dst_smem),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(bar)
+        : "memory");
+}
 __device__ __forceinline__ void tma_load_3d(uint32_t dst_smem, const CUtensorMap* m, int c0, int c1, int c2, uint32_t bar) {
     asm volatile(
         "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst_smem),

@@ -43,7 +43,7 @@ extern "C" int dmlb_conv_implicit_fin(int kind, const void* act, int ld_act, int
 // Small-channel first-layer convolution (Cin <= 8): see conv_smallc_impl in gemm_tcgen05.cuh and include/dmlb.h.
 extern "C" int dmlb_conv_smallc_bf16(int kind, const void* act, int B, int Ha, int Wa, int cin, const void* other, int ld_other, int KH, int KW,
                                      int SH, int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo, const float* bias, int relu,
-                                     int split_k, int pt_layout, void* pooled, int ldp, int pool_w, int tile_n, void* stream) {
+                                     int split_k, int pt_layout, void* pooled, int ldp, int pool_w, int tile_n, int hp, int wp, void* stream) {
     return conv_smallc_impl<ElemBF16>(kind, act, B, Ha, Wa, cin, other, ld_other, KH, KW, SH, SW, PH, PW, n_out, out, out_is_f32, ldo, bias, relu,
-                                 split_k, pt_layout, pooled, ldp, pool_w, tile_n, stream);
+                                 split_k, pt_layout, pooled, ldp, pool_w, tile_n, hp, wp, stream);
 }

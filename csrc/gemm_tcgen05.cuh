@@ -71,6 +71,7 @@ struct GemmEpilogue {
     // `cin` are real.  cpad > 0 (accumulating epilogue only): column c = tap * cpad + ch is dropped when ch >= cin, else lands at
     // tap * cin + ch (GEMM order) or, with perm_khw > 0, at ch * perm_khw + tap (PyTorch's [Cout, Cin, kh, kw]).
     int cpad, cin;
+    int kw, kwpad;        // kwpad > 0: taps are (kh, kw padded to kwpad); columns with kw >= the real width are dropped too
     // 2x2 / stride-2 max-pool of the stored activation computed in the same epilogue (warp shuffles across the rows = pixels of the
     // tile): pool_w = W of the [B, H, W] map the rows enumerate (power of two <= 16, H even), 0 = off; pooled is [M/4, ldp].
     void* pooled;
@@ -95,6 +96,11 @@ struct GemmEpilogue {
 // EIGHT filter taps per 128-byte k-block, each tap one TMA im2col box of 128 pixels x 16 bytes written unswizzled (the K-major
 // no-swizzle core-matrix layout: 8 pixels x 16 B = 128 B, next 8 pixels +128 B, next tap +2048 B); B = 4 is the same gather as the
 // MN-major operand of wgrad (one box of kBK pixels x 16 B per tap).  K order = (tap, padded channel).
+// Row-window forms (A = 4, B = 5), for the same layers when the input sits in a zero-PADDED granule buffer [B, Hp, Wp, granule] and
+// the output extents are powers of two: eight horizontally adjacent taps of one output pixel are 128 CONTIGUOUS bytes of that
+// buffer, and neighbouring output pixels start stride granules further — an overlapping-window tensor map (dims: bytes inside an image,
+// wo, ho, n) turns a whole k-block (128 or kBK pixels x 128 B) into ONE ordinary tiled TMA load with the 128-byte swizzle.  No
+// im2col mode, no padding logic (the zeros are in the buffer), fully coalesced; K order = (kh, kw padded to 8, padded channel).
 struct ConvK {
     int C;            // channels of the gathered activation (Cin for fprop / wgrad, Cout for dgrad)
     int KH, KW;
@@ -102,6 +108,7 @@ struct ConvK {
     int sh, sw;       // traversal stride
     int low_h, low_w; // bounding-box lower corner (= -padding for fprop/wgrad, -(k-1-padding) for dgrad)
     int flip;         // dgrad: weight tap = kh*kw-1 - gather tap
+    int wp, kwb;      // row-window forms (A = 4 / B = 5): row pitch of the zero-padded input in pixels, k-blocks per filter row
 };
 
 template <int BN, bool kDual>
@@ -180,8 +187,15 @@ __device__ __forceinline__ void gemm_epilogue_tile(uint32_t tmem_d, int q, int l
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                     const int c = col0 + j;
-                    const int tap = c / ep.cpad, ch = c - tap * ep.cpad;
-                    if (j < ncols && ch < ep.cin) red_add_f32(o + (ep.perm_khw > 0 ? ch * ep.perm_khw + tap : tap * ep.cin + ch), f[j]);
+                    int tap = c / ep.cpad;
+                    const int ch = c - tap * ep.cpad;
+                    bool ok = j < ncols && ch < ep.cin;
+                    if (ep.kwpad > 0) {
+                        const int kh = tap / ep.kwpad, kwp = tap - kh * ep.kwpad;
+                        ok = ok && kwp < ep.kw;
+                        tap = kh * ep.kw + kwp;
+                    }
+                    if (ok) red_add_f32(o + (ep.perm_khw > 0 ? ch * ep.perm_khw + tap : tap * ep.cin + ch), f[j]);
                 }
             } else if (ep.perm_cin > 0) {
 #pragma unroll
@@ -413,6 +427,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
                     const int tap = k0 / cv.C;
                     const int r = tap / cv.KW;
                     tma_load_im2col_4d(a_dst, &tma_a, k0 - tap * cv.C, a_w, a_h, a_n, tap - r * cv.KW, r, full_bar(s));
+                } else if constexpr (AM == 4) {
+                    // row-window: k-block (kh, kwb) = 8 taps of filter row kh starting at kw = 8*kwb, for 128 consecutive output pixels
+                    const int kb = kb_begin + it;
+                    const int kh = kb / cv.kwb;
+                    const int pq = cv.P * cv.Q;
+                    const int n_ = m0 / pq, rem = m0 - n_ * pq;
+                    const int ho = rem / cv.Q;
+                    tma_load_4d(a_dst, &tma_a, (kh * cv.wp + (kb - kh * cv.kwb) * 8) * (16 / E::kBytes), rem - ho * cv.Q, ho, n_, full_bar(s));
                 } else {
                     // small-channel conv: k-block = 8 taps x one 16-byte channel granule; taps past the filter repeat the last one
                     // (their weights are zero-filled by B's map, the products vanish, the byte count stays that of a full stage)
@@ -455,6 +477,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
                         int cin0 = n0 + kBK * j;
                         if (cin0 >= N) cin0 = 0;
                         tma_load_3d(b_dst + j * E::kBoxBytes, &tma_b, cin0, wtap, k0 - tap * cv.C, full_bar(s));
+                    }
+                } else if constexpr (BMODE == 5) {
+                    // row-window wgrad: reduction rows = kBK output pixels starting at k0; every kBK columns are one (kh, kwb) block
+                    const int pq = cv.P * cv.Q;
+                    const int n_ = k0 / pq, rem = k0 - n_ * pq;
+                    const int ho = rem / cv.Q;
+                    const int wo = rem - ho * cv.Q;
+#pragma unroll
+                    for (int j = 0; j < BN / kBK; ++j) {
+                        int cb = n0 / kBK + j;
+                        if (cb >= cv.KH * cv.kwb) cb = 0;          // tile overhang: any legal block, the epilogue masks those columns
+                        const int kh = cb / cv.kwb;
+                        tma_load_4d(b_dst + j * E::kBoxBytes, &tma_b, (kh * cv.wp + (cb - kh * cv.kwb) * 8) * (16 / E::kBytes), wo, ho, n_,
+                                    full_bar(s));
                     }
                 } else {
                     // small-channel wgrad: reduction rows = kBK output pixels starting at k0, columns = (tap, padded channel):
@@ -1377,6 +1413,51 @@ static int conv_implicit_impl(const FinishArgs* fin, int kind, const void* act, 
     return -4;
 }
 
+// R consecutive output pixels (in (n, ho, wo) order, starting at a multiple of R) as a box {qb, pb, nb} of the (wo, ho, n) index space.
+static bool pixel_box(int R, int Q, int P, int* qb, int* pb, int* nb) {
+    if (Q >= R) {
+        if (Q % R) return false;
+        *qb = R; *pb = 1; *nb = 1;
+        return true;
+    }
+    if (R % Q) return false;
+    const int a = R / Q;
+    if (a <= P) {
+        if (P % a) return false;
+        *qb = Q; *pb = a; *nb = 1;
+        return true;
+    }
+    if (a % P) return false;
+    *qb = Q; *pb = P; *nb = a / P;
+    return *nb <= 256;
+}
+
+// Overlapping-window tensor map over a zero-padded granule buffer [B, Hp, Wp, granule]: dim 0 walks the bytes of one image (so a
+// coordinate (kh*Wp + kw0)*granule selects the filter tap), dims 1-3 are wo / ho / n with strides of `sw` pixels / `sh` rows / one image.
+template <typename E>
+static int make_tmap_rowwin(CUtensorMap* map, const void* base, int B, int Hp, int Wp, int P, int Q, int sh, int sw, int R, bool mn_major) {
+    EncodeTiledFn fn = get_encode_fn();
+    DMLB_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point not available");
+    DMLB_REQUIRE((reinterpret_cast<uintptr_t>(base) & 127) == 0, "the padded input buffer must be 128-byte aligned");
+    constexpr int G = 16 / E::kBytes;
+    int qb, pb, nb;
+    DMLB_REQUIRE(pixel_box(R, Q, P, &qb, &pb, &nb), "output extents do not tile into boxes of consecutive pixels");
+    cuuint64_t dims[4] = {(cuuint64_t)Hp * Wp * G, (cuuint64_t)Q, (cuuint64_t)P, (cuuint64_t)B};
+    cuuint64_t strides[3] = {(cuuint64_t)sw * 16, (cuuint64_t)sh * Wp * 16, (cuuint64_t)Hp * Wp * 16};
+    cuuint32_t box[4] = {(cuuint32_t)(8 * G), (cuuint32_t)qb, (cuuint32_t)pb, (cuuint32_t)nb};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = fn(map, tma_dtype<E>(), 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    mn_major ? E::kTmaMnSwizzle : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char buf[256];
+        snprintf(buf, sizeof(buf), "cuTensorMapEncodeTiled (row-window map) failed: CUresult %d (B=%d Hp=%d Wp=%d P=%d Q=%d stride=%d,%d box=%d,%d,%d)",
+                 (int)r, B, Hp, Wp, P, Q, sh, sw, qb, pb, nb);
+        dmlb_set_error(buf);
+        return -3;
+    }
+    return 0;
+}
+
 // Implicit-GEMM convolution for SMALL channel counts (the first layer of every model here: Cin = 3).  The activation is channels-last with
 // exactly one 16-byte granule per pixel (4 fp32 / 8 bf16 channels, the unused ones zero); a k-block gathers eight filter taps, so the
 // reduction is kh*kw*granule long instead of kh*kw*64 — see the A = 3 / B = 4 operand forms of the kernel.
@@ -1385,10 +1466,12 @@ static int conv_implicit_impl(const FinishArgs* fin, int kind, const void* act, 
 //   kind 1  wgrad: out[Cout, kh*kw*cin] (+)= dY^T * im2col(x);  other = dY [B*Ho*Wo, ld_other]; pad-channel columns are dropped;
 //                  pt_layout = 1 writes PyTorch's [Cout, Cin, kh, kw] order instead of [Cout, kh, kw, Cin]
 // Reference: the first nn.Conv2d of example/models.py:8,29 (3 -> 6 5x5 and 3 -> 64 11x11 stride 4).
+// Row-window variant (hp > 0): act is the zero-PADDED buffer [B, hp, wp, granule] (image at rows PH.., columns PW..), the filter width is
+// padded to kwpad = 8 * ceil(KW / 8) in the weight layout [n_out, KH * kwpad * granule], and one tiled TMA load fetches a whole k-block.
 template <typename E>
 static int conv_smallc_impl(int kind, const void* act, int B, int Ha, int Wa, int cin, const void* other, int ld_other, int KH, int KW, int SH,
                             int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo, const float* bias, int relu, int split_k,
-                            int pt_layout, void* pooled, int ldp, int pool_w, int tile_n, void* stream_) {
+                            int pt_layout, void* pooled, int ldp, int pool_w, int tile_n, int hp, int wp, void* stream_) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     constexpr int BK = E::kBK;
     constexpr int G = 16 / E::kBytes;            // channels per granule = channel pitch of the activation
@@ -1397,14 +1480,21 @@ static int conv_smallc_impl(int kind, const void* act, int B, int Ha, int Wa, in
     DMLB_REQUIRE(!E::kTf32 || out_is_f32, "the tf32 convolution writes fp32");
     const int Ho = (Ha + 2 * PH - KH) / SH + 1, Wo = (Wa + 2 * PW - KW) / SW + 1;
     DMLB_REQUIRE(Ho > 0 && Wo > 0, "empty conv output");
-    const int ntaps = KH * KW;
+    const bool rowwin = hp > 0;
+    const int kwb = (KW + 7) / 8;                // k-blocks per filter row of the row-window form
+    const int ntaps = rowwin ? KH * kwb * 8 : KH * KW;
     const int Kg = ntaps * G;                    // GEMM reduction length of fprop = column count of wgrad
+    if (rowwin) {
+        DMLB_REQUIRE(hp >= (Ho - 1) * SH + KH && wp >= (Wo - 1) * SW + kwb * 8 && hp >= Ha + 2 * PH && wp >= Wa + 2 * PW,
+                     "padded input buffer too small for the row windows");
+    }
     const long long Mpix = 1ll * B * Ho * Wo;
     DMLB_REQUIRE(Mpix < (1ll << 31), "too many output pixels");
     if (split_k < 1) split_k = 1;
     GemmEpilogue ep = {};
     ConvK cv = {};
     cv.C = G; cv.KH = KH; cv.KW = KW; cv.sh = SH; cv.sw = SW; cv.P = Ho; cv.Q = Wo; cv.low_h = -PH; cv.low_w = -PW; cv.flip = 0;
+    cv.wp = wp; cv.kwb = kwb;
     CUtensorMap ta, tb;
     int rc;
     if (kind == 0) {
@@ -1417,9 +1507,18 @@ static int conv_smallc_impl(int kind, const void* act, int B, int Ha, int Wa, in
                          "fused 2x2 pool needs a power-of-two output width <= 16 and an even height");
             ep.pooled = pooled; ep.ldp = ldp; ep.pool_w = pool_w;
         }
-        rc = make_tmap_im2col<E>(&ta, act, G, Wa, Ha, B, G, -PW, -PH, PW - (KW - 1), PH - (KH - 1), SW, SH, kBM, false, true);
-        if (rc) return rc;
         rc = make_tmap_2d<E>(&tb, other, (uint64_t)Kg, (uint64_t)N, (uint64_t)ld_other, BK, (uint32_t)BN, false);
+        if (rc) return rc;
+        if (rowwin) {
+            rc = make_tmap_rowwin<E>(&ta, act, B, hp, wp, Ho, Wo, SH, SW, kBM, false);
+            if (rc) return rc;
+            if (BN == 32) return launch_gemm<E, 32, 4, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, 1, stream);
+            if (BN == 64) return launch_gemm<E, 64, 4, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, 1, stream);
+            if (BN == 128) return launch_gemm<E, 128, 4, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, 1, stream);
+            dmlb_set_error("dmlb_conv_smallc: unsupported tile_n");
+            return -4;
+        }
+        rc = make_tmap_im2col<E>(&ta, act, G, Wa, Ha, B, G, -PW, -PH, PW - (KW - 1), PH - (KH - 1), SW, SH, kBM, false, true);
         if (rc) return rc;
         if (BN == 32) return launch_gemm<E, 32, 3, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, 1, stream);
         if (BN == 64) return launch_gemm<E, 64, 3, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, 1, stream);
@@ -1428,9 +1527,20 @@ static int conv_smallc_impl(int kind, const void* act, int B, int Ha, int Wa, in
         const int Cout = n_out;
         int BN = tile_n ? tile_n : 128;
         DMLB_REQUIRE(out_is_f32, "weight gradients accumulate in fp32");
-        ep.out = out; ep.ldo = ldo; ep.out_is_f32 = 1; ep.atomic = 1; ep.cpad = G; ep.cin = cin; ep.perm_khw = pt_layout ? ntaps : 0;
+        ep.out = out; ep.ldo = ldo; ep.out_is_f32 = 1; ep.atomic = 1; ep.cpad = G; ep.cin = cin; ep.perm_khw = pt_layout ? KH * KW : 0;
         rc = make_tmap_2d<E>(&ta, other, (uint64_t)Cout, (uint64_t)Mpix, (uint64_t)ld_other, BK, BK, true);   // dY as MN-major A
         if (rc) return rc;
+        if (rowwin) {
+            ep.kw = KW; ep.kwpad = kwb * 8;
+            rc = make_tmap_rowwin<E>(&tb, act, B, hp, wp, Ho, Wo, SH, SW, BK, true);
+            if (rc) return rc;
+            if (BN == 64) return launch_gemm<E, 64, 1, 5>(ta, tb, ep, cv, Cout, Kg, (int)Mpix, split_k, stream);
+            if (BN == 128) return launch_gemm<E, 128, 1, 5>(ta, tb, ep, cv, Cout, Kg, (int)Mpix, split_k, stream);
+            dmlb_set_error("dmlb_conv_smallc: unsupported tile_n");
+            return -4;
+        }
+        DMLB_REQUIRE(!E::kTf32, "the granule form has no tf32 weight-gradient kernel (32-bit MN-major operands exist only in the 32-byte-granule "
+                                "swizzle): use the row-window form or the explicit column matrix");
         rc = make_tmap_im2col<E>(&tb, act, G, Wa, Ha, B, G, -PW, -PH, PW - (KW - 1), PH - (KH - 1), SW, SH, BK, true, true);
         if (rc) return rc;
         if (BN == 64) return launch_gemm<E, 64, 1, 4>(ta, tb, ep, cv, Cout, Kg, (int)Mpix, split_k, stream);

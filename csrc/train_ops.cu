@@ -136,6 +136,7 @@ struct ShadowEntry {
     int rows, cin, khw, ld;
     int cpad;            // 0: columns (khw, cin) dense.  > 0: small-channel layout, cpad channels per tap (the extra ones stay zero)
     int src_gemm_order;  // source is stored [rows, khw, cin] (channels-last arena) instead of PyTorch's [rows, cin, khw]
+    int kw, kwpad;       // kwpad > 0 (with cpad): taps are laid out (kh, kw padded to kwpad) — the row-window convolution's weight order
 };
 
 template <typename T>
@@ -154,7 +155,9 @@ __global__ void __launch_bounds__(256) refresh_shadows_kernel(const float* __res
         const int ci = k % e.cin;
         const int kk = k / e.cin;
         const float v = e.src_gemm_order ? __ldg(src + 1ll * r * K + k) : __ldg(src + (1ll * r * e.cin + ci) * e.khw + kk);
-        dst[1ll * r * e.ld + (e.cpad > 0 ? kk * e.cpad + ci : k)] = from_f32<T>(v);
+        int tap = kk;
+        if (e.kwpad > 0) tap = (kk / e.kw) * e.kwpad + kk % e.kw;
+        dst[1ll * r * e.ld + (e.cpad > 0 ? tap * e.cpad + ci : k)] = from_f32<T>(v);
     }
 }
 
@@ -292,18 +295,22 @@ extern "C" int dmlb_sgd_flat_slot(float* params, float* grads, void* acc_slot, f
 namespace dmlb {
 // fp32 NCHW batch -> channels-last activation with ONE 16-byte granule per pixel (C <= 4 fp32 / 8 bf16 channels, the rest zero): the
 // input layout of the small-channel first-layer convolution.  One thread per pixel: C strided reads, one 16-byte store.
+// The destination may be a zero-padded buffer [B, Hp, Wp, G] (image at rows ph.., columns pw..; the border is zeroed once, by its owner).
 template <typename T>
-__global__ void __launch_bounds__(256) nchw_to_act_kernel(const float* __restrict__ x, T* __restrict__ y, int B, int C, long long plane) {
+__global__ void __launch_bounds__(256) nchw_to_act_kernel(const float* __restrict__ x, T* __restrict__ y, int B, int C, int H, int W, int Hp, int Wp,
+                                                          int ph, int pw) {
     pdl_prologue();
     constexpr int G = 16 / sizeof(T);
+    const long long plane = 1ll * H * W;
     const long long total = 1ll * B * plane;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total; i += 1ll * gridDim.x * blockDim.x) {
         const long long b = i / plane, p = i - b * plane;
+        const int h = static_cast<int>(p / W), w = static_cast<int>(p - 1ll * h * W);
         const float* src = x + b * C * plane + p;
         float f[G];
 #pragma unroll
         for (int c = 0; c < G; ++c) f[c] = c < C ? __ldg(src + c * plane) : 0.f;
-        Vec16<T>::store(y + i * G, f);
+        Vec16<T>::store(y + ((b * Hp + h + ph) * Wp + w + pw) * G, f);
     }
 }
 
@@ -331,19 +338,21 @@ __global__ void __launch_bounds__(256) apply_pull_kernel(float* __restrict__ par
 }
 }  // namespace dmlb
 
-extern "C" int dmlb_nchw_to_act_bf16(const float* x, void* y, int B, int C, int H, int W, void* stream) {
-    DMLB_REQUIRE(C >= 1 && C <= 8, "one 16-byte granule holds at most 8 bf16 channels");
-    DMLB_CHECK_CUDA(launch_k(nchw_to_act_kernel<__nv_bfloat16>, flat_grid(1ll * B * H * W), 256, 0, static_cast<cudaStream_t>(stream), x,
-                             static_cast<__nv_bfloat16*>(y), B, C, 1ll * H * W));
+template <typename T>
+static int nchw_to_act_t(const float* x, void* y, int B, int C, int H, int W, int hp, int wp, int ph, int pw, void* stream) {
+    DMLB_REQUIRE(C >= 1 && C <= static_cast<int>(16 / sizeof(T)), "one 16-byte granule holds at most 8 bf16 / 4 fp32 channels");
+    if (hp <= 0) { hp = H; wp = W; ph = 0; pw = 0; }
+    DMLB_REQUIRE(hp >= H + ph && wp >= W + pw && ph >= 0 && pw >= 0, "the image does not fit the padded buffer");
+    DMLB_CHECK_CUDA(launch_k(nchw_to_act_kernel<T>, flat_grid(1ll * B * H * W), 256, 0, static_cast<cudaStream_t>(stream), x, static_cast<T*>(y), B, C,
+                             H, W, hp, wp, ph, pw));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
-extern "C" int dmlb_nchw_to_act_f32(const float* x, void* y, int B, int C, int H, int W, void* stream) {
-    DMLB_REQUIRE(C >= 1 && C <= 4, "one 16-byte granule holds at most 4 fp32 channels");
-    DMLB_CHECK_CUDA(launch_k(nchw_to_act_kernel<float>, flat_grid(1ll * B * H * W), 256, 0, static_cast<cudaStream_t>(stream), x,
-                             static_cast<float*>(y), B, C, 1ll * H * W));
-    DMLB_LAUNCH_CHECK();
-    return 0;
+extern "C" int dmlb_nchw_to_act_bf16(const float* x, void* y, int B, int C, int H, int W, int hp, int wp, int ph, int pw, void* stream) {
+    return nchw_to_act_t<__nv_bfloat16>(x, y, B, C, H, W, hp, wp, ph, pw, stream);
+}
+extern "C" int dmlb_nchw_to_act_f32(const float* x, void* y, int B, int C, int H, int W, int hp, int wp, int ph, int pw, void* stream) {
+    return nchw_to_act_t<float>(x, y, B, C, H, W, hp, wp, ph, pw, stream);
 }
 
 // *slot = value on the stream (8 bytes of device memory): how the host retargets dmlb_sgd_flat_slot / dmlb_apply_pull between replays.

@@ -67,12 +67,14 @@ _SIGNATURES = {
     "dmlb_avgpool_bwd_bf16": [c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_vp],
     # (kind, act, B, Ha, Wa, cin, other, ld_other, KH, KW, SH, SW, PH, PW, n_out, out, out_is_f32, ldo, bias, relu, split_k, pt_layout, pooled, ldp,
     #  pool_w, tile_n, stream)
+    #  pool_w, tile_n, hp, wp, stream)
     "dmlb_conv_smallc_bf16": [c_int, c_vp, c_int, c_int, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_vp, c_int,
-                              c_int, c_vp, c_int, c_int, c_int, c_vp, c_int, c_int, c_int, c_vp],
+                              c_int, c_vp, c_int, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp],
     "dmlb_conv_smallc_tf32": [c_int, c_vp, c_int, c_int, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_vp, c_int,
-                              c_int, c_vp, c_int, c_int, c_int, c_vp, c_int, c_int, c_int, c_vp],
-    "dmlb_nchw_to_act_bf16": [c_vp, c_vp, c_int, c_int, c_int, c_int, c_vp],
-    "dmlb_nchw_to_act_f32": [c_vp, c_vp, c_int, c_int, c_int, c_int, c_vp],
+                              c_int, c_vp, c_int, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp],
+    # (x, y, B, C, H, W, hp, wp, ph, pw, stream)
+    "dmlb_nchw_to_act_bf16": [c_vp, c_vp] + [c_int] * 8 + [c_vp],
+    "dmlb_nchw_to_act_f32": [c_vp, c_vp] + [c_int] * 8 + [c_vp],
     # (ws, ldw, y, dy, ldy, dbias, B, Hx, Wx, C, pool2, relu, is_f32, stream)
     "dmlb_splitk_finish_actbwd": [c_vp, c_int, c_vp, c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_vp],
     "dmlb_sgd_flat_slot": [c_vp, c_vp, c_vp, c_vp, c_vp, c_ll, c_vp, c_float, c_float, c_int, c_vp],

@@ -70,10 +70,9 @@ class TrainStep:
             from .ops import kernels as K
             first = next((m for m in model.modules() if isinstance(m, dnn.Conv2d)), None)
             if first is not None and first._smallc() and first.in_channels == input_shape[0]:
-                g = K.granule(first.compute_dtype)
-                buf = torch.zeros((batch_size, input_shape[1], input_shape[2], g), dtype=first.compute_dtype, device=self.device)
-                self.static_x = buf[..., :input_shape[0]].permute(0, 3, 1, 2)
-                self.static_x._dmlb_padzero = True
+                C, H, W = input_shape
+                rw = K.rowwin_geometry(H, W, *first.kernel_size, *first.stride, *first.padding, first.compute_dtype)
+                self.static_x = OF.smallc_input(batch_size, C, H, W, first.compute_dtype, self.device, rw, first.padding)
                 self._smallc_in = True
         self.static_y = torch.zeros((batch_size,), dtype=torch.int64, device=self.device)
         self.metrics = torch.zeros(2, dtype=torch.float32, device=self.device)
@@ -188,10 +187,7 @@ class TrainStep:
                 y.record_stream(self.stream)
         with torch.cuda.stream(self.stream):
             if self._smallc_in:
-                from .ops import kernels as K
-                if x.dtype != torch.float32 or not x.is_contiguous():
-                    x = x.float().contiguous()
-                K.nchw_to_act(x, self.static_x)
+                OF.fill_smallc_input(self.static_x, x)
             else:
                 self.static_x.copy_(x, non_blocking=True)
             self.static_y.copy_(y, non_blocking=True)

@@ -107,10 +107,16 @@ class _ShadowedModule(nn.Module):
         """Small-channel layout (first layers, <= 4 input channels): the shadow holds one 16-byte granule per filter tap."""
         return False
 
+    def _kw_pad(self):
+        """(kw, kwpad) of the row-window weight layout, or (0, 0): taps in plain (kh, kw) order."""
+        return 0, 0
+
     def _shadow_ld(self) -> int:
         rows, cin, khw = self._shadow_dims()
         if self._smallc():
-            return khw * K.granule(self.compute_dtype)
+            kw, kwpad = self._kw_pad()
+            taps = khw // kw * kwpad if kwpad else khw
+            return taps * K.granule(self.compute_dtype)
         return K.pad_for(self.compute_dtype, cin * khw)
 
     def _shadow_entry(self) -> bytes:
@@ -119,10 +125,12 @@ class _ShadowedModule(nn.Module):
         dst = self._shadow.data_ptr() // self._shadow.element_size()
         if self._smallc():
             in_gemm_order = _gemm_order(self.weight) or cin == 1
-            return struct.pack("<qqiiiiii", self.weight.data_ptr() // 4, dst, rows, cin, khw, ld, K.granule(self.compute_dtype), int(in_gemm_order))
+            kw, kwpad = self._kw_pad()
+            return struct.pack("<qqiiiiiiii", self.weight.data_ptr() // 4, dst, rows, cin, khw, ld, K.granule(self.compute_dtype), int(in_gemm_order),
+                               kw, kwpad)
         if not self._needs_permute():
             cin, khw = cin * khw, 1       # source already in GEMM order: plain cast with a row pitch
-        return struct.pack("<qqiiiiii", self.weight.data_ptr() // 4, dst, rows, cin, khw, ld, 0, 0)
+        return struct.pack("<qqiiiiiiii", self.weight.data_ptr() // 4, dst, rows, cin, khw, ld, 0, 0, 0, 0)
 
     def _ensure_shadow_storage(self) -> None:
         rows, cin, khw = self._shadow_dims()
@@ -235,7 +243,7 @@ class ShadowSet:
         self._has_flat = any(m._flat for m in self.modules)
         self._n_table = len(tabled)
         dev = self.modules[0].weight.device
-        raw = b"".join(m._shadow_entry() for m in tabled) or b"\0" * 40
+        raw = b"".join(m._shadow_entry() for m in tabled) or b"\0" * 48
         self._table = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(dev)
         self._ptrs = self._signature()
 
@@ -281,6 +289,7 @@ class Conv2d(_ShadowedModule):
         # the model author's promise that this layer's output is read by exactly one op, another Conv2d of this package: that layer's
         # backward may then run this layer's pool / ReLU backward inside its own split-K dgrad finish (ops/functional.py, K8)
         self.sole_consumer_is_conv = bool(sole_consumer_is_conv)
+        self._rowwin = None               # (Hp, Wp) of the padded input buffer when the row-window first-layer form is in use
         self.in_channels, self.out_channels = in_channels, out_channels
         self.kernel_size, self.stride, self.padding = _pair(kernel_size), _pair(stride), _pair(padding)
         self.activation = activation
@@ -304,12 +313,25 @@ class Conv2d(_ShadowedModule):
         # RGB / grey-scale first layers: <= 4 channels fit one 16-byte granule in either compute dtype
         return self.in_channels <= 4 and self.kernel_size[0] * self.kernel_size[1] > 1 and OF.smallc_enabled()
 
+    def _kw_pad(self):
+        return (self.kernel_size[1], (self.kernel_size[1] + 7) // 8 * 8) if self._rowwin is not None else (0, 0)
+
     def forward(self, x):
         relu = self.activation == "relu"
         if not x.is_cuda:
             return OF.conv_block(x, self.weight, self.bias, self.stride, self.padding, relu, self.pool)
+        smallc = self._smallc()
+        if smallc:
+            # the weight layout depends on the variant the input geometry allows: row windows (power-of-two outputs) or flat taps
+            rw = K.rowwin_geometry(x.shape[2], x.shape[3], *self.kernel_size, *self.stride, *self.padding, self.compute_dtype)
+            if rw != self._rowwin:
+                self._rowwin = rw
+                self._shadow, self._shadow_key, self._flat = None, None, False
+                if self._shadow_set is not None:
+                    self._shadow_set.invalidate_table()
         return OF.conv_block(x, self.weight, self.bias, self.stride, self.padding, relu, self.pool, shadow=self.shadow(),
-                             wsink=self._wsink, bsink=self._bsink, sole_consumer=self.sole_consumer_is_conv, smallc=self._smallc())
+                             wsink=self._wsink, bsink=self._bsink, sole_consumer=self.sole_consumer_is_conv, smallc=smallc,
+                             rowwin=self._rowwin if smallc else None)
 
     def extra_repr(self):
         return (f"{self.in_channels}, {self.out_channels}, kernel_size={self.kernel_size}, stride={self.stride}, padding={self.padding}, "

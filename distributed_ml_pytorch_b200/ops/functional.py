@@ -247,16 +247,35 @@ def smallc_enabled() -> bool:
     return _conv_opts.smallc
 
 
-def to_smallc_act(x: torch.Tensor, dt) -> torch.Tensor:
-    """fp32 NCHW batch with C <= 4 -> the channels-last, one-granule-per-pixel activation the small-channel convolution reads
-    (pad channels zero).  :class:`~distributed_ml_pytorch_b200.engine.TrainStep` keeps its static input in this layout."""
-    B, C, H, W = x.shape
+def smallc_input(B: int, C: int, H: int, W: int, dt, device, rowwin=None, padding=(0, 0)) -> torch.Tensor:
+    """Empty first-layer input in the layout the small-channel convolution reads: logical ``[B, C, H, W]`` view of a channels-last
+    buffer with one zero-padded 16-byte granule per pixel — for the row-window form (``rowwin=(Hp, Wp)``) the buffer additionally has
+    a zero border of the convolution's padding.  Fill it with :func:`fill_smallc_input`.
+    :class:`~distributed_ml_pytorch_b200.engine.TrainStep` keeps its static input this way."""
     g = K.granule(dt)
-    buf = torch.empty((B, H, W, g), dtype=dt, device=x.device)
-    K.nchw_to_act(x, buf)
-    out = buf[..., :C].permute(0, 3, 1, 2)
-    out._dmlb_padzero = True
+    if rowwin is not None:
+        Hp, Wp = rowwin
+        ph, pw = padding
+        buf = torch.zeros((B, Hp, Wp, g), dtype=dt, device=device)
+        out = buf[:, ph:ph + H, pw:pw + W, :C].permute(0, 3, 1, 2)
+        out._dmlb_rowwin = SimpleNamespace(buf=buf, Hp=Hp, Wp=Wp, ph=ph, pw=pw)
+    else:
+        buf = torch.zeros((B, H, W, g), dtype=dt, device=device)
+        out = buf[..., :C].permute(0, 3, 1, 2)
+        out._dmlb_padzero = True
+        out._dmlb_buf = buf
     return out
+
+
+def fill_smallc_input(dst: torch.Tensor, x: torch.Tensor) -> None:
+    """``dst`` (from :func:`smallc_input`) <- the fp32 NCHW batch ``x``: one kernel, layout change (and bf16 cast) included."""
+    if x.dtype != torch.float32 or not x.is_contiguous():
+        x = x.float().contiguous()
+    rw = getattr(dst, "_dmlb_rowwin", None)
+    if rw is not None:
+        K.nchw_to_act(x, rw.buf, rw.Hp, rw.Wp, rw.ph, rw.pw)
+    else:
+        K.nchw_to_act(x, dst._dmlb_buf)
 
 
 def set_implicit_conv(flag: bool) -> bool:
@@ -387,17 +406,23 @@ class _ConvBlockFn(torch.autograd.Function):
         (B, H, W, Cin, Cout, KH, KW, SH, SW, PH, PW, Ho, Wo) = geom
         dt, dev = cfg.dt, x.device
         g = K.granule(dt)
-        if act4_pitch(x, dt) == g and getattr(x, "_dmlb_padzero", False):
-            xa = x                                               # already in the layout (TrainStep's static input)
-        elif x.dtype == torch.float32 and x.is_contiguous():
-            xa = to_smallc_act(x, dt)                            # the user's NCHW batch (reference main.py:64-70): one small kernel
+        rw = cfg.rowwin
+        tag = getattr(x, "_dmlb_rowwin", None)
+        if rw is not None and tag is not None and (tag.Hp, tag.Wp, tag.ph, tag.pw) == (rw[0], rw[1], PH, PW) and tag.buf.dtype == dt:
+            xa = x                                               # already in the padded layout (TrainStep's static input)
+        elif rw is None and act4_pitch(x, dt) == g and getattr(x, "_dmlb_padzero", False):
+            xa = x
         else:
-            _warn_once("smallc_in", "a small-channel convolution received an activation whose pad channels are not known to be zero; "
-                                    "re-laying it out with ATen copies")
-            buf = torch.zeros((B, H, W, g), dtype=dt, device=dev)
-            xa = buf[..., :Cin].permute(0, 3, 1, 2)
-            xa.copy_(x)
-        Kg = KH * KW * g
+            xa = smallc_input(B, Cin, H, W, dt, dev, rw, (PH, PW))
+            if x.dtype == torch.float32 and x.is_contiguous():
+                fill_smallc_input(xa, x)                         # the user's NCHW batch (reference main.py:64-70): one small kernel
+            else:
+                _warn_once("smallc_in", "a small-channel convolution received an activation that is not an fp32 NCHW batch; re-laying it out "
+                                        "with an ATen copy")
+                xa.copy_(x)
+        xbuf = xa._dmlb_rowwin.buf if rw is not None else xa
+        hp, wp = (rw if rw is not None else (0, 0))
+        Kg = cfg.shadow.shape[1]                                 # taps (kw padded to 8 in the row-window form) x granule
         M = B * Ho * Wo
         y = new_act4(B, Cout, Ho, Wo, dev, dt)
         ldy = pad_for(dt, Cout)
@@ -406,8 +431,8 @@ class _ConvBlockFn(torch.autograd.Function):
         if cfg.pool == (2, 2, 0) and Ho % 2 == 0 and Wo in (2, 4, 8, 16):
             out = new_act4(B, Cout, Ho // 2, Wo // 2, dev, dt)   # 2x2 pool by warp shuffles in the GEMM epilogue
             pool_w = Wo
-        K.conv_smallc(0, xa.data_ptr(), B, H, W, Cin, cfg.shadow.data_ptr(), Kg, KH, KW, SH, SW, PH, PW, Cout, y, ldy, bias=bias, relu=cfg.relu,
-                      pooled_ptr=out.data_ptr() if pool_w else 0, ldp=ldy, pool_w=pool_w, dt=dt)
+        K.conv_smallc(0, xbuf.data_ptr(), B, H, W, Cin, cfg.shadow.data_ptr(), Kg, KH, KW, SH, SW, PH, PW, Cout, y, ldy, bias=bias, relu=cfg.relu,
+                      pooled_ptr=out.data_ptr() if pool_w else 0, ldp=ldy, pool_w=pool_w, dt=dt, hp=hp, wp=wp)
         if cfg.pool is not None and not pool_w:
             k, s, p = cfg.pool
             Hp, Wp = (Ho + 2 * p - k) // s + 1, (Wo + 2 * p - k) // s + 1
@@ -424,7 +449,8 @@ class _ConvBlockFn(torch.autograd.Function):
         ctx.x_ptr = xa.data_ptr()
         ctx.geom = (B, H, W, Cin, Cout, KH, KW, SH, SW, PH, PW, Ho, Wo, Cin * KH * KW, Kg, g, 0, False, False, False)
         ctx.has_bias = bias is not None
-        ctx.save_for_backward(xa, y if (cfg.relu or cfg.pool is not None) else None, weight, bias)
+        ctx.xa_view = xa if rw is None else None                 # granule activation (logical view) for the explicit tf32 wgrad
+        ctx.save_for_backward(xbuf, y if (cfg.relu or cfg.pool is not None) else None, weight, bias)
         return out
 
     @staticmethod
@@ -481,10 +507,19 @@ class _ConvBlockFn(torch.autograd.Function):
                 target = gw
                 gemm_order = KH * KW == 1 or Cin == 1 or target.permute(0, 2, 3, 1).is_contiguous()
             with _WgradFork(dev, dy, a_t, gw) as fork:
-                if cfg.smallc:
+                if cfg.smallc and (cfg.rowwin is not None or dt == BF16):
                     # columns of the GEMM are (tap, padded channel); the epilogue drops the pad channels and writes either order
+                    hp, wp = cfg.rowwin if cfg.rowwin is not None else (0, 0)
                     K.conv_smallc(1, a_t.data_ptr(), B, H, W, Cin, dy.data_ptr(), lddy, KH, KW, SH, SW, PH, PW, Cout, target, Kd,
-                                  split_k=split, pt_layout=not gemm_order, dt=dt)
+                                  split_k=split, pt_layout=not gemm_order, dt=dt, hp=hp, wp=wp)
+                elif cfg.smallc:
+                    # tf32 with flat taps: a 32-bit MN-major operand exists only in the 32-byte-granule swizzle, which granule boxes cannot
+                    # produce -> column matrix of the real channels (on this side stream, off the critical path) + the ordinary GEMM
+                    kp = pad_for(dt, Kd)
+                    col = torch.empty((M, kp), dtype=dt, device=dev)
+                    K.im2col_nhwc(a_t.data_ptr(), col, B, H, W, Cin, K.granule(dt), KH, KW, SH, SW, PH, PW, kp)
+                    K.gemm(dy, lddy, True, col, kp, True, Cout, Kd, M, target, Kd, split_k=split, atomic=True,
+                           perm_cin=0 if gemm_order else Cin, perm_khw=KH * KW)
                 elif implicit and gemm_order:
                     K.conv_implicit(1, a_t.data_ptr(), ldx, B, H, W, Cin, dy.data_ptr(), lddy, KH, KW, SH, SW, PH, PW, Cout, target, Kd,
                                     split_k=split, atomic=True, dt=dt)
@@ -560,7 +595,7 @@ class _ConvBlockFn(torch.autograd.Function):
 
 
 def conv_block(x, weight, bias=None, stride=(1, 1), padding=(0, 0), relu=False, pool=None, shadow=None, wsink=None, bsink=None,
-               sole_consumer=False, smallc=False):
+               sole_consumer=False, smallc=False, rowwin=None):
     """``max_pool(relu(conv2d(x, weight, bias)))`` with the optional parts fused (CUDA) or composed (CPU).
 
     ``sole_consumer=True`` promises that the result is read by exactly one op and that op is another ``conv_block``: its backward may
@@ -581,7 +616,7 @@ def conv_block(x, weight, bias=None, stride=(1, 1), padding=(0, 0), relu=False, 
         raise RuntimeError("conv_block on CUDA needs the GEMM-layout weight shadow (use nn.Conv2d from this package)")
     cfg = SimpleNamespace(stride=tuple(stride), padding=tuple(padding), relu=bool(relu), pool=pool, shadow=shadow, wsink=wsink, bsink=bsink,
                           dt=shadow.dtype, sole_consumer=bool(sole_consumer), prod=getattr(x, "_dmlb_prod", None), fwd=None,
-                          smallc=bool(smallc))
+                          smallc=bool(smallc), rowwin=rowwin)
     out = _ConvBlockFn.apply(x, weight, bias, cfg)
     if cfg.fwd is not None:
         out._dmlb_prod = cfg          # "this activation's only reader is a conv block": lets that block fuse our activation backward

@@ -82,17 +82,40 @@ def granule(dt) -> int:
 
 def conv_smallc(kind: int, act_ptr: int, B, Ha, Wa, cin, other_ptr: int, ld_other: int, KH, KW, SH, SW, PH, PW, n_out: int, out: torch.Tensor,
                 ldo: int, bias=None, relu: bool = False, split_k: int = 1, pt_layout: bool = False, pooled_ptr: int = 0, ldp: int = 0,
-                pool_w: int = 0, tile_n: int = 0, dt=torch.bfloat16) -> None:
-    """Small-channel first-layer convolution (``dmlb_conv_smallc_*``): kind 0 fprop (optional fused 2x2 pool), 1 wgrad."""
+                pool_w: int = 0, tile_n: int = 0, dt=torch.bfloat16, hp: int = 0, wp: int = 0) -> None:
+    """Small-channel first-layer convolution (``dmlb_conv_smallc_*``): kind 0 fprop (optional fused 2x2 pool), 1 wgrad.
+    ``hp, wp`` > 0 selects the row-window form: ``act_ptr`` is the zero-padded buffer ``[B, hp, wp, granule]``."""
     _call("dmlb_conv_smallc_tf32" if dt == torch.float32 else "dmlb_conv_smallc_bf16", kind, act_ptr, B, Ha, Wa, cin, other_ptr, ld_other, KH, KW,
           SH, SW, PH, PW, n_out, out.data_ptr(), int(out.dtype == torch.float32), ldo, bias.data_ptr() if bias is not None else None, int(relu),
-          split_k, int(pt_layout), pooled_ptr or None, ldp, pool_w, tile_n, stream_ptr())
+          split_k, int(pt_layout), pooled_ptr or None, ldp, pool_w, tile_n, hp, wp, stream_ptr())
 
 
-def nchw_to_act(x: torch.Tensor, y: torch.Tensor) -> None:
-    """fp32 NCHW batch -> channels-last activation ``y`` with one zero-padded 16-byte granule per pixel (``dmlb_nchw_to_act_*``)."""
+def nchw_to_act(x: torch.Tensor, buf: torch.Tensor, hp: int = 0, wp: int = 0, ph: int = 0, pw: int = 0) -> None:
+    """fp32 NCHW batch -> channels-last granule buffer (``dmlb_nchw_to_act_*``): ``buf`` is ``[B, H, W, g]``, or the zero-bordered
+    ``[B, hp, wp, g]`` of the row-window convolution with the image at rows ``ph..``, columns ``pw..``."""
     B, C, H, W = x.shape
-    _call("dmlb_nchw_to_act_" + _sfx(y.dtype), x.data_ptr(), y.data_ptr(), B, C, H, W, stream_ptr())
+    _call("dmlb_nchw_to_act_" + _sfx(buf.dtype), x.data_ptr(), buf.data_ptr(), B, C, H, W, hp, wp, ph, pw, stream_ptr())
+
+
+def _pixel_box(R: int, Q: int, P: int) -> bool:
+    """Do R consecutive output pixels (aligned to R) form a box of the (wo, ho, n) index space?  (csrc/gemm_tcgen05.cuh pixel_box)"""
+    if Q >= R:
+        return Q % R == 0
+    if R % Q:
+        return False
+    a = R // Q
+    if a <= P:
+        return P % a == 0
+    return a % P == 0 and a // P <= 256
+
+
+def rowwin_geometry(H, W, KH, KW, SH, SW, PH, PW, dt):
+    """``(Hp, Wp)`` of the zero-padded input buffer when the row-window convolution applies to this geometry, else ``None``."""
+    Ho, Wo = (H + 2 * PH - KH) // SH + 1, (W + 2 * PW - KW) // SW + 1
+    if Ho <= 0 or Wo <= 0 or not (_pixel_box(128, Wo, Ho) and _pixel_box(kblock(dt), Wo, Ho)):
+        return None
+    kwb = (KW + 7) // 8
+    return max(H + 2 * PH, (Ho - 1) * SH + KH), max(W + 2 * PW, (Wo - 1) * SW + 8 * kwb)
 
 
 def pick_split_k(tiles: int, k_total: int, sms: int = 148, min_kblocks: int = 2, bk: int = 64) -> int:

@@ -64,13 +64,17 @@ int dmlb_conv_implicit_tf32(int kind, const void* act, int ld_act, int B, int Ha
  * act is channels-last with ONE 16-byte granule per pixel (bf16: 8 channels, fp32/tf32: 4; unused channels zero; see dmlb_nchw_to_act_*);
  * a 128-byte k-block gathers eight filter taps by TMA im2col, so the reduction is kh*kw*granule long.
  * kind 0 fprop: other = weights [n_out, kh*kw*granule] (pad channels zero); optional fused 2x2 max-pool into pooled (pool_w = output width).
- * kind 1 wgrad: other = dY [pixels, ld_other]; out fp32 [n_out, kh*kw*cin] (+)=, PyTorch's [Cout,Cin,kh,kw] order when pt_layout = 1. */
+ * kind 1 wgrad: other = dY [pixels, ld_other]; out fp32 [n_out, kh*kw*cin] (+)=, PyTorch's [Cout,Cin,kh,kw] order when pt_layout = 1
+ *   (bf16 only in this form).
+ * Row-window form (hp > 0, both dtypes, output extents powers of two): act is the zero-padded buffer [B, hp, wp, granule] written by
+ *   dmlb_nchw_to_act_* with padding, the weights are [n_out, kh * kwpad * granule] with kwpad = 8*ceil(kw/8), and a whole k-block
+ *   (128 pixels x 8 taps) is ONE tiled TMA load through an overlapping-window tensor map. */
 int dmlb_conv_smallc_bf16(int kind, const void* act, int B, int Ha, int Wa, int cin, const void* other, int ld_other, int KH, int KW, int SH,
                           int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo, const float* bias, int relu, int split_k,
-                          int pt_layout, void* pooled, int ldp, int pool_w, int tile_n, void* stream);
+                          int pt_layout, void* pooled, int ldp, int pool_w, int tile_n, int hp, int wp, void* stream);
 int dmlb_conv_smallc_tf32(int kind, const void* act, int B, int Ha, int Wa, int cin, const void* other, int ld_other, int KH, int KW, int SH,
                           int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo, const float* bias, int relu, int split_k,
-                          int pt_layout, void* pooled, int ldp, int pool_w, int tile_n, void* stream);
+                          int pt_layout, void* pooled, int ldp, int pool_w, int tile_n, int hp, int wp, void* stream);
 
 /* Implicit-GEMM convolution: the activation operand is gathered by TMA in im2col mode, no column matrix exists in memory.
  * kind 0 fprop (act = x, other = W shadow [n_out=Cout, kh*kw*Cin]), 1 wgrad (act = x, other = dY, out [n_out=Cout, kh*kw*Cin], fp32 accumulate),
@@ -161,9 +165,10 @@ int dmlb_store_u64(void* slot, unsigned long long value, void* stream);   /* *sl
 int dmlb_apply_pull(float* params, const float* pulled, void* unpushed_slot, void* shadow_bf16, long long n, void* stream);
 /* fp32 NCHW batch (the reference's input, example/main.py:64-70) -> channels-last activation with one 16-byte granule per pixel
  * (C <= 8 bf16 / 4 fp32 channels, the rest zero): the input layout of dmlb_conv_smallc_*. */
-int dmlb_nchw_to_act_bf16(const float* x, void* y, int B, int C, int H, int W, void* stream);
-int dmlb_nchw_to_act_f32(const float* x, void* y, int B, int C, int H, int W, void* stream);
-/* table: device array of { int64 src_off, int64 dst_off, int32 rows, cin, khw, ld, cpad, src_gemm_order } — see csrc/train_ops.cu. */
+int dmlb_nchw_to_act_bf16(const float* x, void* y, int B, int C, int H, int W, int hp, int wp, int ph, int pw, void* stream);
+int dmlb_nchw_to_act_f32(const float* x, void* y, int B, int C, int H, int W, int hp, int wp, int ph, int pw, void* stream);
+/* (hp > 0: y is a zero-bordered buffer [B, hp, wp, granule] and the image lands at rows ph.., columns pw.. — the row-window form) */
+/* table: device array of { int64 src_off, int64 dst_off, int32 rows, cin, khw, ld, cpad, src_gemm_order, kw, kwpad } — see csrc/train_ops.cu. */
 int dmlb_refresh_shadows(const float* params, void* shadow, const void* table, int n_entries, void* stream);
 int dmlb_refresh_shadows_f32(const float* params, void* shadow, const void* table, int n_entries, void* stream);   /* fp32 copies (tf32 path) */
 int dmlb_cast_f32_bf16(const float* x, void* y, long long rows, int C, long long ldx, int ldy, void* stream);

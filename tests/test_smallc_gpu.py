@@ -31,7 +31,8 @@ CASES = [
     (3, 6, 5, 1, 0, 32, (2, 2, 0)),        # LeNet conv1: 28x28 output, pool as its own kernel
     (1, 6, 5, 1, 0, 28, (2, 2, 0)),        # LeNet on the MNIST shape
     (3, 64, 7, 2, 3, 64, None),            # ResNet stem
-    (3, 64, 3, 1, 1, 16, None),            # ResNet CIFAR stem (pooled width would qualify, no pool here)
+    (3, 64, 3, 1, 1, 16, None),            # ResNet CIFAR stem: 16x16 outputs -> row windows
+    (3, 64, 3, 1, 1, 32, (2, 2, 0)),       # 32x32 outputs: row windows, pool as its own kernel (width 32 > 16)
     (4, 32, 3, 2, 1, 17, None),            # full granule (fp32), odd extent
 ]
 
@@ -100,7 +101,8 @@ def test_train_step_static_input_is_smallc_layout():
     net = build_model("alexnet").cuda()
     opt = FusedSGD(net.parameters(), lr=0.01, model=net)
     ts = TrainStep(net, opt, 16, (3, 32, 32))
-    assert ts._smallc_in and OF.act4_pitch(ts.static_x, torch.float32) == 4
+    assert ts._smallc_in and getattr(ts.static_x, "_dmlb_rowwin", None) is not None      # 8x8 outputs: the row-window form
+    assert ts.static_x._dmlb_rowwin.buf.shape == (16, 42, 44, 4)
     x = torch.randn(16, 3, 32, 32, device="cuda")
     y = torch.randint(0, 10, (16,), device="cuda")
     r = ts(x, y, sync=True)

@@ -20,13 +20,13 @@ zk = convnp(x).contiguous()                      # kernel's post-relu activation
 with torch.backends.cudnn.flags(allow_tf32=False):
     zr = F.relu(F.conv2d(x32, conv.weight, conv.bias, stride=s, padding=p))
 g = tf32_round(torch.randn(8, cout, 4, 4, device=dev))
-zr1 = zr.clone().requires_grad_(True); F.max_pool2d(zr1, *pool).backward(g)
-zk1 = zk.clone().requires_grad_(True); F.max_pool2d(zk1, *pool).backward(g)
+zr1 = zr.detach().clone().requires_grad_(True); F.max_pool2d(zr1, *pool).backward(g)
+zk1 = zk.detach().clone().requires_grad_(True); F.max_pool2d(zk1, *pool).backward(g)
 print('max |zk-zr|', (zk-zr).abs().max().item())
 d = (zr1.grad != zk1.grad)
 print('ATen pool-bwd routing differs between kernel activation and reference activation at', int(d.sum()), 'elements')
 # our kernel's pool backward on the kernel activation
-zin = act4(zk).requires_grad_(True)
+zin = act4(zk.detach()).requires_grad_(True)
 yo = OF.max_pool2d(zin, 3, 2, 1); yo.backward(act4(g))
 d2 = (zin.grad.contiguous() != zk1.grad)
 print('our pool-bwd vs ATen pool-bwd on the SAME activation differ at', int(d2.sum()), 'elements')
