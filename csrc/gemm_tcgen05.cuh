@@ -1499,9 +1499,13 @@ static int conv_smallc_impl(int kind, const void* act, int B, int Ha, int Wa, in
     int rc;
     if (kind == 0) {
         const int N = n_out;
-        DMLB_REQUIRE(split_k == 1, "small-channel fprop has a short reduction: no split-K");
         int BN = tile_n ? tile_n : ((N > 64) ? 128 : (N > 32 ? 64 : 32));
         ep.out = out; ep.bias = bias; ep.ldo = ldo; ep.out_is_f32 = out_is_f32; ep.relu = relu;
+        if (split_k > 1) {
+            // few row tiles and a long reduction (AlexNet conv1: 32 tiles x 22 k-blocks): spread K over the SMs into an fp32 workspace
+            DMLB_REQUIRE(out_is_f32 && bias == nullptr && !relu && pool_w == 0, "split-K small-channel fprop accumulates raw sums into an fp32 workspace");
+            ep.atomic = 1;
+        }
         if (pool_w > 0) {
             DMLB_REQUIRE(pool_w == Wo && (pool_w & (pool_w - 1)) == 0 && pool_w >= 2 && pool_w <= 16 && Ho % 2 == 0 && pooled != nullptr,
                          "fused 2x2 pool needs a power-of-two output width <= 16 and an even height");
@@ -1512,17 +1516,17 @@ static int conv_smallc_impl(int kind, const void* act, int B, int Ha, int Wa, in
         if (rowwin) {
             rc = make_tmap_rowwin<E>(&ta, act, B, hp, wp, Ho, Wo, SH, SW, kBM, false);
             if (rc) return rc;
-            if (BN == 32) return launch_gemm<E, 32, 4, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, 1, stream);
-            if (BN == 64) return launch_gemm<E, 64, 4, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, 1, stream);
-            if (BN == 128) return launch_gemm<E, 128, 4, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, 1, stream);
+            if (BN == 32) return launch_gemm<E, 32, 4, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, split_k, stream);
+            if (BN == 64) return launch_gemm<E, 64, 4, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, split_k, stream);
+            if (BN == 128) return launch_gemm<E, 128, 4, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, split_k, stream);
             dmlb_set_error("dmlb_conv_smallc: unsupported tile_n");
             return -4;
         }
         rc = make_tmap_im2col<E>(&ta, act, G, Wa, Ha, B, G, -PW, -PH, PW - (KW - 1), PH - (KH - 1), SW, SH, kBM, false, true);
         if (rc) return rc;
-        if (BN == 32) return launch_gemm<E, 32, 3, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, 1, stream);
-        if (BN == 64) return launch_gemm<E, 64, 3, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, 1, stream);
-        if (BN == 128) return launch_gemm<E, 128, 3, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, 1, stream);
+        if (BN == 32) return launch_gemm<E, 32, 3, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, split_k, stream);
+        if (BN == 64) return launch_gemm<E, 64, 3, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, split_k, stream);
+        if (BN == 128) return launch_gemm<E, 128, 3, 0>(ta, tb, ep, cv, (int)Mpix, N, Kg, split_k, stream);
     } else {
         const int Cout = n_out;
         int BN = tile_n ? tile_n : 128;

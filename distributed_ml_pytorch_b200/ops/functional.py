@@ -428,15 +428,32 @@ class _ConvBlockFn(torch.autograd.Function):
         ldy = pad_for(dt, Cout)
         out = y
         pool_w = 0
-        if cfg.pool == (2, 2, 0) and Ho % 2 == 0 and Wo in (2, 4, 8, 16):
-            out = new_act4(B, Cout, Ho // 2, Wo // 2, dev, dt)   # 2x2 pool by warp shuffles in the GEMM epilogue
-            pool_w = Wo
-        K.conv_smallc(0, xbuf.data_ptr(), B, H, W, Cin, cfg.shadow.data_ptr(), Kg, KH, KW, SH, SW, PH, PW, Cout, y, ldy, bias=bias, relu=cfg.relu,
-                      pooled_ptr=out.data_ptr() if pool_w else 0, ldp=ldy, pool_w=pool_w, dt=dt, hp=hp, wp=wp)
-        if cfg.pool is not None and not pool_w:
+        want_pool2 = cfg.pool == (2, 2, 0) and Ho % 2 == 0 and Wo % 2 == 0
+        split = K.fprop_split(M, Cout, Kg, bk=K.kblock(dt))
+        done_pool = False
+        if split > 1:
+            # few row tiles, long reduction (AlexNet conv1: 32 tiles x 22 k-blocks): K over the SMs, then one finish (+ 2x2 pool) kernel
+            ldw = (Cout + 3) // 4 * 4
+            ws = K.splitk_workspace(dev, M * ldw)
+            K.conv_smallc(0, xbuf.data_ptr(), B, H, W, Cin, cfg.shadow.data_ptr(), Kg, KH, KW, SH, SW, PH, PW, Cout, ws, ldw, split_k=split, dt=dt,
+                          hp=hp, wp=wp)
+            if want_pool2:
+                out = new_act4(B, Cout, Ho // 2, Wo // 2, dev, dt)
+                K.splitk_finish(ws, ldw, bias, cfg.relu, y.data_ptr(), ldy, M, Cout, pool2=(B, Ho, Wo), pooled_ptr=out.data_ptr(), ldp=ldy, dt=dt)
+                done_pool = True
+            else:
+                K.splitk_finish(ws, ldw, bias, cfg.relu, y.data_ptr(), ldy, M, Cout, dt=dt)
+        else:
+            if want_pool2 and Wo in (2, 4, 8, 16):
+                out = new_act4(B, Cout, Ho // 2, Wo // 2, dev, dt)   # 2x2 pool by warp shuffles in the GEMM epilogue
+                pool_w = Wo
+                done_pool = True
+            K.conv_smallc(0, xbuf.data_ptr(), B, H, W, Cin, cfg.shadow.data_ptr(), Kg, KH, KW, SH, SW, PH, PW, Cout, y, ldy, bias=bias,
+                          relu=cfg.relu, pooled_ptr=out.data_ptr() if pool_w else 0, ldp=ldy, pool_w=pool_w, dt=dt, hp=hp, wp=wp)
+        if cfg.pool is not None and not done_pool:
             k, s, p = cfg.pool
-            Hp, Wp = (Ho + 2 * p - k) // s + 1, (Wo + 2 * p - k) // s + 1
-            out = new_act4(B, Cout, Hp, Wp, dev, dt)
+            Hp_, Wp_ = (Ho + 2 * p - k) // s + 1, (Wo + 2 * p - k) // s + 1
+            out = new_act4(B, Cout, Hp_, Wp_, dev, dt)
             K.maxpool_fwd(y.data_ptr(), out.data_ptr(), B, Ho, Wo, Cout, ldy, ldy, k, s, p, dt=dt)
         ctx.cfg = cfg
         cfg.fwd = None
@@ -510,6 +527,7 @@ class _ConvBlockFn(torch.autograd.Function):
                 if cfg.smallc and (cfg.rowwin is not None or dt == BF16):
                     # columns of the GEMM are (tap, padded channel); the epilogue drops the pad channels and writes either order
                     hp, wp = cfg.rowwin if cfg.rowwin is not None else (0, 0)
+                    split = K.pick_split_k(((Cout + 127) // 128) * ((Kpad + 127) // 128), M, bk=bk)     # tiles of the PADDED column space
                     K.conv_smallc(1, a_t.data_ptr(), B, H, W, Cin, dy.data_ptr(), lddy, KH, KW, SH, SW, PH, PW, Cout, target, Kd,
                                   split_k=split, pt_layout=not gemm_order, dt=dt, hp=hp, wp=wp)
                 elif cfg.smallc:

@@ -40,7 +40,7 @@ def _grads(dtype, fused, seed=0):
 def test_fused_dgrad_finish_matches_two_kernel_form(dtype):
     g0, l0, n0 = _grads(dtype, fused=False)
     g1, l1, n1 = _grads(dtype, fused=True)
-    assert l0 == l1
+    assert abs(l0 - l1) < 1e-5 * max(1.0, abs(l0))      # (split-K partial sums arrive in a different order from run to run)
     assert n1 == n0 - 4, (n0, n1)                  # four layer boundaries of AlexNet: (finish + act_bwd) -> one kernel each
     err = ((g0 - g1).norm() / g0.norm()).item()
     # identical products; only the bias gradients' summation differs (fp32 values before vs after the bf16 rounding of dy)
