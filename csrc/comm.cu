@@ -322,9 +322,15 @@ __global__ void __launch_bounds__(512) sync_nvls_kernel(const float* __restrict_
     }
 }
 
+// Grid cap of the push / pull movers (0 = two CTAs per SM).  An optimizer that overlaps them with training sets a small cap: the transfer
+// then trickles in the background of the next steps instead of taking every SM away from them for a few microseconds.
+static int g_comm_max_blocks = 0;
+extern "C" void dmlb_set_comm_max_blocks(int n) { g_comm_max_blocks = n > 0 ? n : 0; }
+
 static inline int comm_grid(long long work_items, int threads) {
     long long blocks = (work_items + threads - 1) / threads;
-    const long long cap = dmlb_sm_count() * 2ll;
+    long long cap = dmlb_sm_count() * 2ll;
+    if (g_comm_max_blocks > 0 && g_comm_max_blocks < cap) cap = g_comm_max_blocks;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     return static_cast<int>(blocks);

@@ -78,7 +78,8 @@ class Asynchronous(ArenaOptimizer):
     def __init__(self, params, lr, n_push: int, n_pull: int, model: torch.nn.Module, momentum: float = 0.0,
                  staleness: Optional[str] = None, staleness_param: float = 0.9, transport: str = "auto", group=None,
                  init_rank: Optional[int] = None, torn_pulls: bool = False, server_rank: int = msg.SERVER_RANK,
-                 blocking_pull: bool = False, pull_timeout_s: float = 60.0, server_ranks=None, overlap: bool = True, pull_lag: int = 1):
+                 blocking_pull: bool = False, pull_timeout_s: float = 60.0, server_ranks=None, overlap: bool = True, pull_lag: int = 1,
+                 comm_blocks: int = 24):
         if lr < 0.0:
             raise ValueError("Invalid learning rate: {}".format(lr))
         if n_push < 1 or n_pull < 1:
@@ -117,6 +118,7 @@ class Asynchronous(ArenaOptimizer):
         self.pushes = self.pulls = 0
         self.overlap = bool(overlap) and transport == "peer"
         self.pull_lag = max(0, int(pull_lag))
+        self.comm_blocks = int(comm_blocks)    # CTAs of an overlapped push / pull kernel (a background trickle next to the training step)
 
         arena = None
         if transport == "peer":
@@ -253,6 +255,7 @@ class Asynchronous(ArenaOptimizer):
         ready = torch.cuda.Event()
         ready.record(cur)
         self.comm_stream.wait_event(ready)
+        peer.set_comm_max_blocks(self.comm_blocks)       # background transfer: leave the SMs to the training step
         with torch.cuda.stream(self.comm_stream):
             if push_now:
                 self._push(self._acc[retired])
@@ -267,6 +270,7 @@ class Asynchronous(ArenaOptimizer):
                 fetched.record(self.comm_stream)
                 self._pending_pull = (self.idx, fetched)
                 self.pulls += 1
+        peer.set_comm_max_blocks(0)
         if pull_now and self.pull_lag == 0:
             self._land_pull(force=True)
 

@@ -150,6 +150,14 @@ def flag_words() -> int:
     return int(_native.lib().dmlb_comm_flag_words())
 
 
+_native.register("dmlb_set_comm_max_blocks", [c_int], restype=None)
+
+
+def set_comm_max_blocks(n: int) -> None:
+    """Grid cap of the push / pull kernels launched next (0 = default, two CTAs per SM)."""
+    _native.lib().dmlb_set_comm_max_blocks(int(n))
+
+
 def push_add(acc: torch.Tensor, master_table, world: int, shard_size: int, n: int) -> None:
     _native.call("dmlb_push_add", acc.data_ptr(), master_table, world, shard_size, n, _stream())
 

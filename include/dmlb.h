@@ -225,6 +225,7 @@ int dmlb_enable_peer_access(int peer_dev);
 
 /* ---- fused communication + update kernels (csrc/comm.cu).  Pointer tables are HOST arrays of `world` device
  * pointers, index = rank; the flat vector is cut into `world` shards of shard_size elements, GPU g owns shard g. ---- */
+void dmlb_set_comm_max_blocks(int n);                      /* grid cap of dmlb_push_add / dmlb_pull (0 = default): small when overlapped with training */
 int dmlb_comm_chunk_elems(void);                          /* mailbox chunk (shard sizes must be multiples of it) */
 int dmlb_comm_flag_words(void);                           /* uint32 words of the per-GPU flag block of the sync kernel */
 /* K1 (Asynchronous.py:55,58-60 + server add): master[owner][i] += acc[i]; acc[i] = 0 — vector red.add over NVLink. */
