@@ -19,7 +19,8 @@ namespace dmlb {
 template <typename T>
 __global__ void __launch_bounds__(1024) softmax_xent_kernel(const T* __restrict__ logits, const long long* __restrict__ labels,
                                                             float* __restrict__ metrics, T* __restrict__ dlogits, int B, int C,
-                                                            int ldl, int ldd) {
+                                                            int ldl, int ldd, volatile float* host_ring, unsigned long long* ring_ctr,
+                                                            int ring_slots) {
     pdl_prologue();
     __shared__ float s_loss[32];
     __shared__ float s_hit[32];
@@ -64,7 +65,21 @@ __global__ void __launch_bounds__(1024) softmax_xent_kernel(const T* __restrict_
         float h = lane < nwarps ? s_hit[lane] : 0.f;
         l = warp_sum(l);
         h = warp_sum(h);
-        if (lane == 0) { metrics[0] = l * inv_b; metrics[1] = h; }
+        if (lane == 0) {
+            metrics[0] = l * inv_b;
+            metrics[1] = h;
+            if (host_ring != nullptr) {
+                // result mailbox in pinned host memory: slot = launch number mod ring_slots, {loss, hits, launch number + 1}; the sequence
+                // word is written last, so a host that sees it sees the values (no D2H copy, no event on the step stream)
+                const unsigned long long n = *ring_ctr;
+                volatile float* slot = host_ring + 4 * (n % static_cast<unsigned long long>(ring_slots));
+                slot[0] = l * inv_b;
+                slot[1] = h;
+                __threadfence_system();
+                slot[2] = static_cast<float>((n + 1ull) & 0xFFFFFFull);
+                *ring_ctr = n + 1ull;
+            }
+        }
     }
 }
 
@@ -244,17 +259,35 @@ static inline int flat_grid(long long total, int threads = 256) {
 
 using namespace dmlb;
 
+static int softmax_xent_impl(const void* logits, int logits_is_bf16, const long long* labels, float* metrics, void* dlogits, int B, int C, int ldl,
+                             int ldd, float* host_ring, void* ring_ctr, int ring_slots, void* stream);
+
 extern "C" int dmlb_softmax_xent(const void* logits, int logits_is_bf16, const long long* labels, float* metrics, void* dlogits, int B, int C,
                                  int ldl, int ldd, void* stream) {
+    return softmax_xent_impl(logits, logits_is_bf16, labels, metrics, dlogits, B, C, ldl, ldd, nullptr, nullptr, 0, stream);
+}
+
+// The same kernel additionally posts {loss, hits, sequence number} into a ring of `ring_slots` 16-byte slots in pinned (device-visible)
+// host memory; ring_ctr is a device counter of launches.  Replaces the reference's blocking loss.item() (example/main.py:79) without
+// putting a D2H copy or an event between two replays of the training step.
+extern "C" int dmlb_softmax_xent_ring(const void* logits, int logits_is_bf16, const long long* labels, float* metrics, void* dlogits, int B, int C,
+                                      int ldl, int ldd, float* host_ring, void* ring_ctr, int ring_slots, void* stream) {
+    DMLB_REQUIRE(host_ring != nullptr && ring_ctr != nullptr && ring_slots > 0, "ring buffer arguments");
+    return softmax_xent_impl(logits, logits_is_bf16, labels, metrics, dlogits, B, C, ldl, ldd, host_ring, ring_ctr, ring_slots, stream);
+}
+
+static int softmax_xent_impl(const void* logits, int logits_is_bf16, const long long* labels, float* metrics, void* dlogits, int B, int C, int ldl,
+                             int ldd, float* host_ring, void* ring_ctr, int ring_slots, void* stream) {
     DMLB_REQUIRE(B > 0 && C > 0, "empty logits");
     int threads = 32 * ((B < 32) ? B : 32);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (logits_is_bf16)
         DMLB_CHECK_CUDA(launch_k(softmax_xent_kernel<__nv_bfloat16>, 1, threads, 0, st, static_cast<const __nv_bfloat16*>(logits), labels, metrics,
-                                                                  static_cast<__nv_bfloat16*>(dlogits), B, C, ldl, ldd));
+                                                                  static_cast<__nv_bfloat16*>(dlogits), B, C, ldl, ldd, static_cast<volatile float*>(host_ring),
+                                                                  static_cast<unsigned long long*>(ring_ctr), ring_slots));
     else
         DMLB_CHECK_CUDA(launch_k(softmax_xent_kernel<float>, 1, threads, 0, st, static_cast<const float*>(logits), labels, metrics, static_cast<float*>(dlogits), B, C,
-                                                          ldl, ldd));
+                                                          ldl, ldd, static_cast<volatile float*>(host_ring), static_cast<unsigned long long*>(ring_ctr), ring_slots));
     DMLB_LAUNCH_CHECK();
     return 0;
 }

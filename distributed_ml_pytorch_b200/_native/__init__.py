@@ -51,6 +51,7 @@ _SIGNATURES = {
     "dmlb_relu_fwd_bf16": [c_vp, c_vp, c_ll, c_int, c_int, c_int, c_vp],
     "dmlb_relu_bwd_bf16": [c_vp, c_vp, c_vp, c_ll, c_int, c_int, c_int, c_int, c_vp],
     "dmlb_softmax_xent": [c_vp, c_int, c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_vp],
+    "dmlb_softmax_xent_ring": [c_vp, c_int, c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_vp, c_vp, c_int, c_vp],
     "dmlb_scale_rows_bf16": [c_vp, c_vp, c_ll, c_int, c_int, c_vp],
     "dmlb_sgd_flat": [c_vp, c_vp, c_vp, c_vp, c_vp, c_ll, c_vp, c_float, c_float, c_int, c_vp],
     "dmlb_refresh_shadows": [c_vp, c_vp, c_vp, c_int, c_vp],

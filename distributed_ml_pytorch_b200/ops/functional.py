@@ -1062,7 +1062,7 @@ def global_avg_pool(x):
 # ------------------------------------------------------------------------------------------------
 class _XentFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, logits, labels, metrics):
+    def forward(ctx, logits, labels, metrics, ring=None):
         B, C = logits.shape
         if logits.dtype == torch.bfloat16:
             logits, ldl = as_act2(logits)
@@ -1074,7 +1074,7 @@ class _XentFn(torch.autograd.Function):
             dlogits = new_act2(B, C, logits.device, F32)       # padded rows: the gradient is a legal GEMM operand of the tf32 path as is
             ldd = pad_for(F32, C)
         need_grad = ctx.needs_input_grad[0]
-        K.softmax_xent(logits, labels, metrics, dlogits if need_grad else None, B, C, ldl, ldd)
+        K.softmax_xent(logits, labels, metrics, dlogits if need_grad else None, B, C, ldl, ldd, ring=ring)
         ctx.save_for_backward(dlogits if need_grad else None)
         ctx.dims = (B, C, ldd)
         return metrics[0]
@@ -1085,18 +1085,19 @@ class _XentFn(torch.autograd.Function):
         B, C, ldd = ctx.dims
         if not _state.unit_loss_grad:
             K.scale_rows(dlogits, g.reshape(1).float(), B, C, ldd)
-        return dlogits, None, None
+        return dlogits, None, None, None
 
 
-def cross_entropy(logits, labels, metrics: Optional[torch.Tensor] = None):
+def cross_entropy(logits, labels, metrics: Optional[torch.Tensor] = None, ring=None):
     """Mean softmax cross-entropy (reference main.py:71).  On CUDA the kernel also writes
     ``metrics[1]`` = number of correct arg-max predictions (the reference recomputes it with
-    ``torch.max(outputs, 1)``, main.py:75) and the returned loss is a view of ``metrics[0]``."""
+    ``torch.max(outputs, 1)``, main.py:75) and the returned loss is a view of ``metrics[0]``.  ``ring = (pinned float32 [slots, 4],
+    device int64 counter)`` makes the kernel post ``{loss, hits, launch number + 1}`` to host memory as well (see ``engine.TrainStep``)."""
     if not logits.is_cuda:
         return F.cross_entropy(logits.float(), labels)
     if metrics is None:
         metrics = torch.empty(2, dtype=torch.float32, device=logits.device)
     if labels.dtype != torch.int64:
         labels = labels.long()
-    loss = _XentFn.apply(logits, labels, metrics)
+    loss = _XentFn.apply(logits, labels, metrics, ring)
     return loss

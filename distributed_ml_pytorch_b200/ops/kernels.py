@@ -260,7 +260,13 @@ def relu_bwd(y_ptr, dy_ptr, dx_ptr, rows, C, ldy, lddy, lddx, dt=torch.bfloat16)
     _call("dmlb_relu_bwd_" + _sfx(dt), y_ptr, dy_ptr, dx_ptr, rows, C, ldy, lddy, lddx, stream_ptr())
 
 
-def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, metrics: torch.Tensor, dlogits, B, C, ldl, ldd) -> None:
+def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, metrics: torch.Tensor, dlogits, B, C, ldl, ldd, ring=None) -> None:
+    """``ring = (pinned host float32 tensor [slots, 4], device int64 launch counter)``: also post the result to host memory."""
+    if ring is not None:
+        _call("dmlb_softmax_xent_ring", logits.data_ptr(), int(logits.dtype == torch.bfloat16), labels.data_ptr(), metrics.data_ptr(),
+              dlogits.data_ptr() if dlogits is not None else None, B, C, ldl, ldd, ring[0].data_ptr(), ring[1].data_ptr(), ring[0].shape[0],
+              stream_ptr())
+        return
     _call("dmlb_softmax_xent", logits.data_ptr(), int(logits.dtype == torch.bfloat16), labels.data_ptr(), metrics.data_ptr(),
           dlogits.data_ptr() if dlogits is not None else None, B, C, ldl, ldd, stream_ptr())
 

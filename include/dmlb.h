@@ -149,6 +149,11 @@ int dmlb_relu_bwd_f32(const void* y, const void* dy, void* dx, long long rows, i
 /* metrics[0] = mean loss, metrics[1] = #rows with argmax == label; dlogits (dtype of logits, [B,ldd], may be NULL) = (softmax-onehot)/B. */
 int dmlb_softmax_xent(const void* logits, int logits_is_bf16, const long long* labels, float* metrics, void* dlogits, int B, int C,
                       int ldl, int ldd, void* stream);
+/* Same, and the kernel also posts {loss, hits, launch number + 1 (mod 2^24)} into slot (launch number mod ring_slots) of a ring of 16-byte
+ * slots in pinned, device-visible host memory (sequence word last): the host reads a step's result from memory, with no D2H copy and no
+ * event between two replays of the training step (the reference blocks on loss.item() every step, example/main.py:79). */
+int dmlb_softmax_xent_ring(const void* logits, int logits_is_bf16, const long long* labels, float* metrics, void* dlogits, int B, int C,
+                           int ldl, int ldd, float* host_ring, void* ring_ctr, int ring_slots, void* stream);
 int dmlb_scale_rows_bf16(void* x, const float* scale, long long rows, int C, int ld, void* stream);
 int dmlb_scale_rows_f32(void* x, const float* scale, long long rows, int C, int ld, void* stream);
 /* theta -= lr*g over the flat arena (n % 4 == 0); optional Downpour accumulator acc -= lr*g, momentum buffer,
