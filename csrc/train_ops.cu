@@ -103,13 +103,50 @@ __global__ void __launch_bounds__(256) scale_rows_kernel(T* __restrict__ x, cons
 // lr is read from device memory so a captured CUDA graph follows LR-scheduler changes.
 // n must be a multiple of 4 (the arena pads to that).
 // ---------------------------------------------------------------------------------------------
+struct ShadowEntry {
+    long long src_off;   // elements into the fp32 arena
+    long long dst_off;   // elements into the shadow arena
+    int rows, cin, khw, ld;
+    int cpad;            // 0: columns (khw, cin) dense.  > 0: small-channel layout, cpad channels per tap (the extra ones stay zero)
+    int src_gemm_order;  // source is stored [rows, khw, cin] (channels-last arena) instead of PyTorch's [rows, cin, khw]
+    int kw, kwpad;       // kwpad > 0 (with cpad): taps are laid out (kh, kw padded to kwpad) — the row-window convolution's weight order
+};
+
+// Destination column of element k = (kk, ci) of a GEMM-layout shadow row (see ShadowEntry).
+__device__ __forceinline__ int shadow_col(const ShadowEntry& e, int kk, int ci, int k) {
+    if (e.cpad <= 0) return k;
+    int tap = kk;
+    if (e.kwpad > 0) tap = (kk / e.kw) * e.kwpad + kk % e.kw;
+    return tap * e.cpad + ci;
+}
+
+// One updated master value -> the table-backed shadow it belongs to, if any (weights whose GEMM-layout copy is not a plain cast of the
+// arena: padded rows, PyTorch (cin,kh,kw) order, first-layer tap padding).  Folding this scatter into the optimizer kernel removes the
+// separate refresh_shadows launch from the end of every training step.
+template <typename T>
+__device__ __forceinline__ void scatter_to_shadows(const ShadowEntry* __restrict__ table, int n_entries, long long elem, float v) {
+    for (int t = 0; t < n_entries; ++t) {
+        const ShadowEntry e = table[t];
+        const int K = e.cin * e.khw;
+        const long long local = elem - e.src_off;
+        if (local < 0 || local >= 1ll * e.rows * K) continue;
+        const int r = static_cast<int>(local / K), rem = static_cast<int>(local - 1ll * r * K);
+        int kk, ci;
+        if (e.src_gemm_order) { kk = rem / e.cin; ci = rem - kk * e.cin; }
+        else                  { ci = rem / e.khw; kk = rem - ci * e.khw; }
+        reinterpret_cast<T*>(0)[e.dst_off + 1ll * r * e.ld + shadow_col(e, kk, ci, kk * e.cin + ci)] = from_f32<T>(v);
+        return;
+    }
+}
+
 // acc_slot (may be null): device location holding the address of the CURRENT accumulator.  The asynchronous optimizer double-buffers
 // its accumulator so a gradient push can drain the retired buffer on a communication stream while the next steps already
 // accumulate into the other one; reading the address from memory lets a captured CUDA graph follow the swap.
 __global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ params, float* __restrict__ grads, float* __restrict__ acc_direct,
                                                        float* const* __restrict__ acc_slot, float* __restrict__ mom,
                                                        __nv_bfloat16* __restrict__ shadow, long long n4, const float* __restrict__ lr_ptr,
-                                                       float mu, float wd, int zero_grads) {
+                                                       float mu, float wd, int zero_grads, const ShadowEntry* __restrict__ table, int n_entries,
+                                                       int table_f32, long long table_lo, long long table_hi) {
     pdl_prologue();
     const float lr = *lr_ptr;
     float* __restrict__ acc = acc_slot != nullptr ? *acc_slot : acc_direct;
@@ -137,6 +174,16 @@ __global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ param
             a.x -= lr * g.x; a.y -= lr * g.y; a.z -= lr * g.z; a.w -= lr * g.w;
             reinterpret_cast<float4*>(acc)[i] = a;
         }
+        if (n_entries > 0 && 4 * i + 3 >= table_lo && 4 * i < table_hi) {      // [table_lo, table_hi): hull of the table-backed weights
+            const float pv[4] = {p.x, p.y, p.z, p.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                // table offsets are absolute (address / element size): rebase the arena index
+                const long long abs_elem = (reinterpret_cast<long long>(params) >> 2) + 4 * i + j;
+                if (table_f32) scatter_to_shadows<float>(table, n_entries, abs_elem, pv[j]);
+                else           scatter_to_shadows<__nv_bfloat16>(table, n_entries, abs_elem, pv[j]);
+            }
+        }
     }
 }
 
@@ -145,14 +192,7 @@ __global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ param
 // Each table entry describes one weight tensor [rows, cin, khw] (PyTorch layout, khw = kh*kw, 1 for
 // Linear) and where its GEMM-layout copy [rows, ld] with columns ordered (khw, cin) lives.
 // ---------------------------------------------------------------------------------------------
-struct ShadowEntry {
-    long long src_off;   // elements into the fp32 arena
-    long long dst_off;   // elements into the shadow arena
-    int rows, cin, khw, ld;
-    int cpad;            // 0: columns (khw, cin) dense.  > 0: small-channel layout, cpad channels per tap (the extra ones stay zero)
-    int src_gemm_order;  // source is stored [rows, khw, cin] (channels-last arena) instead of PyTorch's [rows, cin, khw]
-    int kw, kwpad;       // kwpad > 0 (with cpad): taps are laid out (kh, kw padded to kwpad) — the row-window convolution's weight order
-};
+
 
 template <typename T>
 __global__ void __launch_bounds__(256) refresh_shadows_kernel(const float* __restrict__ params, T* __restrict__ shadow,
@@ -170,9 +210,7 @@ __global__ void __launch_bounds__(256) refresh_shadows_kernel(const float* __res
         const int ci = k % e.cin;
         const int kk = k / e.cin;
         const float v = e.src_gemm_order ? __ldg(src + 1ll * r * K + k) : __ldg(src + (1ll * r * e.cin + ci) * e.khw + kk);
-        int tap = kk;
-        if (e.kwpad > 0) tap = (kk / e.kw) * e.kwpad + kk % e.kw;
-        dst[1ll * r * e.ld + (e.cpad > 0 ? tap * e.cpad + ci : k)] = from_f32<T>(v);
+        dst[1ll * r * e.ld + shadow_col(e, kk, ci, k)] = from_f32<T>(v);
     }
 }
 
@@ -303,26 +341,31 @@ extern "C" int dmlb_scale_rows_f32(void* x, const float* scale, long long rows, 
     return 0;
 }
 
-extern "C" int dmlb_sgd_flat(float* params, float* grads, float* acc, float* mom, void* shadow, long long n, const float* lr_ptr, float mu,
-                             float wd, int zero_grads, void* stream) {
+// Everything dmlb_sgd_flat / dmlb_sgd_flat_slot do, plus the table-backed weight shadows (dmlb_refresh_shadows' table with ABSOLUTE addresses:
+// src_off / dst_off = address / element size) refreshed by the same launch.  [table_lo, table_hi) is the element range of the arena
+// (relative to params) that holds those weights.
+extern "C" int dmlb_sgd_flat_ex(float* params, float* grads, float* acc, void* acc_slot, float* mom, void* shadow, long long n, const float* lr_ptr,
+                                float mu, float wd, int zero_grads, const void* table, int n_entries, int table_is_f32, long long table_lo,
+                                long long table_hi, void* stream) {
     DMLB_REQUIRE(n % 4 == 0, "flat SGD length must be a multiple of 4 (arena padding)");
     DMLB_REQUIRE(((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads)) & 15) == 0, "arena must be 16-byte aligned");
     DMLB_CHECK_CUDA(launch_k(sgd_flat_kernel, flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream), params, grads, acc,
-                             static_cast<float* const*>(nullptr), mom, static_cast<__nv_bfloat16*>(shadow), n / 4, lr_ptr, mu, wd, zero_grads));
+                             static_cast<float* const*>(acc_slot), mom, static_cast<__nv_bfloat16*>(shadow), n / 4, lr_ptr, mu, wd, zero_grads,
+                             static_cast<const ShadowEntry*>(table), table != nullptr ? n_entries : 0, table_is_f32, table_lo, table_hi));
     DMLB_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int dmlb_sgd_flat(float* params, float* grads, float* acc, float* mom, void* shadow, long long n, const float* lr_ptr, float mu,
+                             float wd, int zero_grads, void* stream) {
+    return dmlb_sgd_flat_ex(params, grads, acc, nullptr, mom, shadow, n, lr_ptr, mu, wd, zero_grads, nullptr, 0, 0, 0, 0, stream);
 }
 
 // dmlb_sgd_flat with the accumulator named indirectly: *acc_slot (device memory) is the buffer to accumulate -lr*g into.
 extern "C" int dmlb_sgd_flat_slot(float* params, float* grads, void* acc_slot, float* mom, void* shadow, long long n, const float* lr_ptr, float mu,
                                   float wd, int zero_grads, void* stream) {
-    DMLB_REQUIRE(n % 4 == 0, "flat SGD length must be a multiple of 4 (arena padding)");
-    DMLB_REQUIRE(((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads)) & 15) == 0, "arena must be 16-byte aligned");
     DMLB_REQUIRE(acc_slot != nullptr, "acc_slot is required (use dmlb_sgd_flat for a direct accumulator)");
-    DMLB_CHECK_CUDA(launch_k(sgd_flat_kernel, flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream), params, grads, static_cast<float*>(nullptr),
-                             static_cast<float* const*>(acc_slot), mom, static_cast<__nv_bfloat16*>(shadow), n / 4, lr_ptr, mu, wd, zero_grads));
-    DMLB_LAUNCH_CHECK();
-    return 0;
+    return dmlb_sgd_flat_ex(params, grads, nullptr, acc_slot, mom, shadow, n, lr_ptr, mu, wd, zero_grads, nullptr, 0, 0, 0, 0, stream);
 }
 
 namespace dmlb {

@@ -247,7 +247,27 @@ class ShadowSet:
         self._table = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(dev)
         self._ptrs = self._signature()
 
-    def refresh(self, flat_done: bool = False) -> None:
+    def fused_table(self, arena):
+        """``(table, n_entries, shadow dtype, lo, hi)`` for an optimizer kernel that refreshes the table-backed shadows itself
+        (``K.sgd_flat_ex``), or ``None`` when there is nothing to refresh or a table-backed weight lives outside ``arena``."""
+        if not self.modules or not self.modules[0].weight.is_cuda:
+            return None
+        if self._table is None or self._ptrs != self._signature():
+            self._build_table()
+        if not self._n_table:
+            return None
+        base, n = arena.params.data_ptr(), arena.padded
+        lo, hi = n, 0
+        for m in self.modules:
+            if m._flat:
+                continue
+            off = (m.weight.data_ptr() - base) // 4
+            if off < 0 or off + m.weight.numel() > n:
+                return None
+            lo, hi = min(lo, off), max(hi, off + m.weight.numel())
+        return self._table, self._n_table, self.modules[0].compute_dtype, lo, hi
+
+    def refresh(self, flat_done: bool = False, table_done: bool = False) -> None:
         if not self.modules or not self.modules[0].weight.is_cuda:
             return
         if self._table is None or self._ptrs != self._signature():
@@ -257,7 +277,7 @@ class ShadowSet:
         if self._has_flat and not flat_done and dt == torch.bfloat16:
             arena = getattr(self.model, "_dmlb_arena", None)
             K.cast_f32_bf16(arena.params, arena.shadow.data_ptr(), 1, arena.padded, arena.padded, arena.padded)
-        if self._n_table:
+        if self._n_table and not table_done:
             K.refresh_shadows(self._table, self._n_table, dt=dt)
         for m in self.modules:
             m._mark_shadow_fresh()

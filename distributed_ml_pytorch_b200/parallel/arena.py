@@ -146,12 +146,19 @@ class FlatArena:
     def zero_grads(self) -> None:
         self.grads.zero_()
 
-    def mark_params_changed(self, flat_done: bool = False) -> None:
-        """Call after writing ``params`` through raw pointers: refreshes the bf16 weight shadows
-        (``flat_done``: the writing kernel already updated the flat bf16 mirror ``self.shadow``)."""
+    def mark_params_changed(self, flat_done: bool = False, table_done: bool = False) -> None:
+        """Call after writing ``params`` through raw pointers: refreshes the weight shadows (``flat_done``: the writing kernel
+        already updated the flat bf16 mirror ``self.shadow``; ``table_done``: it also refreshed the table-backed shadows)."""
         shadows = getattr(self.model, "_dmlb_shadows", None)
         if shadows is not None and self.params.is_cuda:
-            shadows.refresh(flat_done=flat_done)
+            shadows.refresh(flat_done=flat_done, table_done=table_done)
+
+    def fused_shadow_table(self):
+        """Argument for ``K.sgd_flat_ex(table=...)``: the model's table-backed shadows, refreshed inside the optimizer kernel."""
+        shadows = getattr(self.model, "_dmlb_shadows", None)
+        if shadows is None or not self.params.is_cuda:
+            return None
+        return shadows.fused_table(self)
 
     def flat_params(self) -> torch.Tensor:
         return self.params[: self.numel]

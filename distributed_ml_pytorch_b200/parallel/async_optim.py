@@ -298,13 +298,10 @@ class Asynchronous(ArenaOptimizer):
         self._sync_lr()
         if a.params.is_cuda:
             from ..ops import kernels as K
-            if self.overlap:
-                K.sgd_flat_slot(a.params, a.grads, self._acc_slot, None, a.padded, self.lr_dev, 0.0, 0.0, shadow=a.shadow,
-                                zero_grads=self.fused_zero_grad)
-            else:
-                K.sgd_flat(a.params, a.grads, self.accumulated_gradients, None, a.padded, self.lr_dev, 0.0, 0.0, shadow=a.shadow,
-                           zero_grads=self.fused_zero_grad)
-            a.mark_params_changed(flat_done=a.shadow is not None)
+            table = a.fused_shadow_table()
+            K.sgd_flat_ex(a.params, a.grads, None if self.overlap else self.accumulated_gradients, self._acc_slot if self.overlap else None, None,
+                          a.padded, self.lr_dev, 0.0, 0.0, shadow=a.shadow, zero_grads=self.fused_zero_grad, table=table)
+            a.mark_params_changed(flat_done=a.shadow is not None, table_done=table is not None)
         else:
             lr = self.lr
             self.accumulated_gradients.add_(a.grads, alpha=-lr)

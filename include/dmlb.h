@@ -165,6 +165,11 @@ int dmlb_sgd_flat(float* params, float* grads, float* acc, float* mom, void* sha
  * optimizer swaps two accumulators so a push can drain one on a communication stream while training fills the other. */
 int dmlb_sgd_flat_slot(float* params, float* grads, void* acc_slot, float* mom, void* shadow_bf16, long long n, const float* lr_ptr, float mu,
                        float wd, int zero_grads, void* stream);
+/* Superset of the two: direct or indirect accumulator, and the table-backed weight shadows (absolute-address table of
+ * dmlb_refresh_shadows) refreshed by the same launch; [table_lo, table_hi) = element range of params that holds those weights. */
+int dmlb_sgd_flat_ex(float* params, float* grads, float* acc, void* acc_slot, float* mom, void* shadow_bf16, long long n, const float* lr_ptr,
+                     float mu, float wd, int zero_grads, const void* table, int n_entries, int table_is_f32, long long table_lo,
+                     long long table_hi, void* stream);
 int dmlb_store_u64(void* slot, unsigned long long value, void* stream);   /* *slot = value, stream ordered */
 /* Landing of an overlapped pull (Asynchronous.py:17-18): params = pulled (+ *unpushed_slot), bf16 mirror refreshed in the same pass. */
 int dmlb_apply_pull(float* params, const float* pulled, void* unpushed_slot, void* shadow_bf16, long long n, void* stream);
