@@ -134,7 +134,9 @@ __device__ __forceinline__ void scatter_to_shadows(const ShadowEntry* __restrict
         int kk, ci;
         if (e.src_gemm_order) { kk = rem / e.cin; ci = rem - kk * e.cin; }
         else                  { ci = rem / e.khw; kk = rem - ci * e.khw; }
-        reinterpret_cast<T*>(0)[e.dst_off + 1ll * r * e.ld + shadow_col(e, kk, ci, kk * e.cin + ci)] = from_f32<T>(v);
+        // dst_off is an absolute address in units of T (not an offset from a null base: that would be undefined behaviour)
+        T* dst = reinterpret_cast<T*>(static_cast<uintptr_t>(e.dst_off) * sizeof(T));
+        dst[1ll * r * e.ld + shadow_col(e, kk, ci, kk * e.cin + ci)] = from_f32<T>(v);
         return;
     }
 }

@@ -46,3 +46,32 @@ def test_fused_dgrad_finish_matches_two_kernel_form(dtype):
     # identical products; only the bias gradients' summation differs (fp32 values before vs after the bf16 rounding of dy)
     assert err < 2e-2, err        # run-to-run split-K summation order already moves a few ReLU decisions
     assert torch.isfinite(g1).all() and g1.abs().sum() > 0
+
+
+@pytest.mark.parametrize("model", ["lenet", "alexnet"])
+@pytest.mark.parametrize("dtype", ["tf32", "bf16"])
+def test_optimizer_kernel_refreshes_table_shadows(model, dtype):
+    """The SGD kernel scatters every updated master value into the table-backed weight shadows (padded rows, permuted fc1, tap-padded
+    conv1): after two steps they must equal what the stand-alone refresh kernel builds from the masters."""
+    from distributed_ml_pytorch_b200.ops import kernels as K
+    torch.manual_seed(0)
+    net = build_model(model, dtype=dtype).cuda()
+    opt = FusedSGD(net.parameters(), lr=0.05, model=net)
+    x = torch.randn(16, 3, 32, 32, device="cuda")
+    y = torch.randint(0, 10, (16,), device="cuda")
+    n0 = None
+    for _ in range(2):
+        opt.zero_grad()
+        OF.cross_entropy(net(x), y).backward()
+        n0 = _native.launch_count()
+        opt.step()
+        assert _native.launch_count() - n0 == 1            # one kernel: update + accumulate + shadows (no refresh launch)
+    torch.cuda.synchronize()
+    ss = net._dmlb_shadows
+    mods = [m for m in ss.modules if not m._flat]
+    assert mods
+    got = [m._shadow.clone() for m in mods]
+    K.refresh_shadows(ss._table, ss._n_table, dt=mods[0].compute_dtype)
+    torch.cuda.synchronize()
+    for m, g in zip(mods, got):
+        assert torch.equal(m._shadow, g), (type(m).__name__, tuple(m.weight.shape))
