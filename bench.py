@@ -210,7 +210,7 @@ def run_ours(args) -> dict:
                                  "(the reference: fp32 tensors, cuDNN TF32 convolutions)" if dtype == "tf32" else
                                  "fp32 master parameters and gradients, bf16 GEMM operands and activations, fp32 accumulation"),
                    "l2_policy": f"inputs rotate through a pool of {m['pool']} distinct batches ({m['pool'] * m['bytes_per_batch'] >> 20} MiB > 126 MiB L2)",
-                   "cuda_graph": m["cuda_graph"], "loss_readback": "every step, read one step late (pinned double buffer)"},
+                   "cuda_graph": m["cuda_graph"], "loss_readback": "every step, read one step late from a pinned ring the loss kernel writes (no D2H copy on the step stream)"},
         "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"), "reasons": clocks.get("reasons", [])},
         "e2e": {"value": round(e2e, 1), "unit": "images/sec", "h2d_bytes_per_step": m["bytes_per_batch"], "d2h_bytes_per_step": 8,
                 "ms_per_step": round(e2e_ms / K_, 5), "mean_loss": m["mean_loss"]},
