@@ -227,6 +227,27 @@ __device__ __forceinline__ uint32_t cluster_ctarank() {
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
+// ---- distributed shared memory (thread-block clusters) ----
+__device__ __forceinline__ uint32_t cluster_nctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+    return r;
+}
+// shared::cluster address of `local_smem_addr` in the CTA with cluster rank `rank`
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t local_smem_addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void st_cluster_f32x4(uint32_t cluster_addr, float a, float b, float c, float d) {
+    asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(cluster_addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ float4 ld_shared_f32x4(uint32_t smem_addr) {
+    float4 r;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(smem_addr) : "memory");
+    return r;
+}
+
 template <int kCols>
 __device__ __forceinline__ void tmem_alloc_2cta(uint32_t holder_smem) {  // the same warp of both CTAs
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(holder_smem), "n"(kCols) : "memory");
@@ -397,6 +418,28 @@ inline cudaError_t launch_k(void (*kern)(P...), dim3 grid, dim3 block, size_t sm
     attr[0].val.programmaticStreamSerializationAllowed = dmlb_pdl_enabled();
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<P>(args)...);
+}
+}  // namespace dmlb
+
+namespace dmlb {
+// launch_k with a runtime cluster shape (1, 1, cluster_z): the z-slices of one output tile form a thread-block cluster.
+template <typename... P, typename... A>
+inline cudaError_t launch_k_cluster(void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, unsigned cluster_z, A... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = dmlb_pdl_enabled();
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = 1;
+    attr[1].val.clusterDim.y = 1;
+    attr[1].val.clusterDim.z = cluster_z;
+    cfg.attrs = attr;
+    cfg.numAttrs = 2;
     return cudaLaunchKernelEx(&cfg, kern, static_cast<P>(args)...);
 }
 }  // namespace dmlb

@@ -76,6 +76,14 @@ struct GemmEpilogue {
     // tile): pool_w = W of the [B, H, W] map the rows enumerate (power of two <= 16, H even), 0 = off; pooled is [M/4, ldp].
     void* pooled;
     int ldp, pool_w;
+    // Cluster split-K epilogue only: activation backward of the block that produced this dgrad's input (see dmlb_splitk_finish_actbwd):
+    // rows are pixels of that block's OUTPUT [B, act_hx, act_wx]; act_y / act_dy are its activation / pre-activation gradient
+    // [B, H, W, act_ldy] with (H, W) = (act_hx, act_wx) or twice that when act_pool2; act_dbias (fp32 [N], may be null) += column sums.
+    const void* act_y;
+    void* act_dy;
+    float* act_dbias;
+    int act_ldy, act_pool2, act_relu, act_hx, act_wx;
+    int cluster_s;        // host side only: > 1 = launch the cluster split-K form with this many K-slices per tile
     // Split-K with the finishing pass folded in ("last CTA of a tile finishes"): every z-slice red.adds its partial tile into the
     // fp32 workspace `out`, then bumps the tile's arrival counter; the slice that arrives last reads the summed tile back from L2,
     // applies bias / ReLU, rounds to bf16 into fin_y (optionally also the 2x2/2 max-pool into fin_pooled), and writes zeros back,
@@ -345,7 +353,102 @@ __device__ __forceinline__ void splitk_finish_tile(const GemmEpilogue& ep, int e
     }
 }
 
-template <typename E, int BN, int AM, int BMODE, bool kDual, bool kFin = false>
+// Final stage of the cluster split-K kernel: one thread = one output row, `ncols` (<= 32, multiple of 4 except at the right edge) summed
+// columns starting at col0.  Forward: bias / ReLU / store (+ 2x2 pool by shuffles).  Backward: either a plain store of dx, or the
+// producer block's pool / ReLU backward and bias gradient (ep.act_y != nullptr) — what dmlb_splitk_finish_actbwd does as a kernel.
+template <typename T>
+__device__ __forceinline__ void actbwd_rows(const GemmEpilogue& ep, int row, bool row_ok, int lane, int col0, int ncols, const float (&g)[32]) {
+    const T* __restrict__ y = static_cast<const T*>(ep.act_y);
+    T* __restrict__ dy = static_cast<T*>(ep.act_dy);
+    const int Hx = ep.act_hx, Wx = ep.act_wx;
+    const int b = row / (Hx * Wx), rem = row - b * (Hx * Wx);
+    const int hx = rem / Wx, wx = rem - hx * Wx;
+    float sum[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) sum[j] = 0.f;
+    if (row_ok) {
+        if (!ep.act_pool2) {
+            const size_t yi = (static_cast<size_t>(b * Hx + hx) * Wx + wx) * ep.act_ldy + col0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                if (j < ncols) {
+                    const float yv = to_f32<T>(y[yi + j]);
+                    const float o = (ep.act_relu && !(yv > 0.f)) ? 0.f : g[j];
+                    dy[yi + j] = from_f32<T>(o);
+                    sum[j] = o;
+                }
+            }
+        } else {
+            const int H = 2 * Hx, W = 2 * Wx;
+            size_t yi[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) yi[q] = (static_cast<size_t>(b * H + 2 * hx + (q >> 1)) * W + 2 * wx + (q & 1)) * ep.act_ldy + col0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                if (j < ncols) {
+                    float yv[4];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) yv[q] = to_f32<T>(y[yi[q] + j]);
+                    int best = 0;
+#pragma unroll
+                    for (int q = 1; q < 4; ++q)
+                        if (yv[q] > yv[best]) best = q;                   // strict: the first maximum wins (PyTorch's rule)
+                    const float o = (ep.act_relu && !(yv[best] > 0.f)) ? 0.f : g[j];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) dy[yi[q] + j] = from_f32<T>(q == best ? o : 0.f);
+                    sum[j] = o;
+                }
+            }
+        }
+    }
+    if (ep.act_dbias != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            if (j < ncols) {                                                  // warp-uniform
+                const float t = warp_sum(sum[j]);
+                if (lane == 0 && t != 0.f) red_add_f32(ep.act_dbias + col0 + j, t);
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ void cluster_final_rows(const GemmEpilogue& ep, int row, bool row_ok, int lane, int col0, int ncols, float (&f)[32],
+                                                   bool add_bias) {
+    if (ep.act_y != nullptr) {
+        if (ep.out_is_f32) actbwd_rows<float>(ep, row, row_ok, lane, col0, ncols, f);
+        else               actbwd_rows<__nv_bfloat16>(ep, row, row_ok, lane, col0, ncols, f);
+        return;
+    }
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        float x = f[j];
+        if (add_bias && j < ncols) x += __ldg(ep.bias + col0 + j);
+        if (ep.relu) x = fmaxf(x, 0.f);
+        if (!ep.out_is_f32) x = __bfloat162float(__float2bfloat16_rn(x));
+        f[j] = x;
+    }
+    if (row_ok) store_row32(ep.out, ep.out_is_f32, static_cast<size_t>(row), ep.ldo, col0, ncols, f);
+    if (ep.pool_w > 0) {
+        const int W = ep.pool_w;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            float m = fmaxf(f[j], __shfl_xor_sync(0xffffffffu, f[j], 1));
+            f[j] = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, W));
+        }
+        if (row_ok && (lane & 1) == 0 && (lane & W) == 0) {
+            const int irow = row / W;
+            const size_t mp = static_cast<size_t>(irow >> 1) * (W >> 1) + ((row - irow * W) >> 1);
+            store_row32(ep.pooled, ep.out_is_f32, mp, ep.ldp, col0, ncols, f);
+        }
+    }
+}
+
+// kCluster: the gridDim.z K-slices of one output tile form a thread-block cluster (launch attribute, size <= 8).  Instead of red.adding
+// partial tiles into an fp32 workspace that a second kernel finishes, the slices reduce through DISTRIBUTED SHARED MEMORY: after its
+// main loop every CTA scatters its TMEM accumulator — column slice d to CTA d (st.shared::cluster into the operand stages, which are
+// free by then) — and, after a cluster barrier, CTA r sums the S partial copies of its BN/S columns and runs the fused epilogue on them.
+// No workspace, no atomics, no finishing launch.
+template <typename E, int BN, int AM, int BMODE, bool kDual, bool kFin = false, bool kCluster = false>
 __global__ void __launch_bounds__(kGemmThreads, ((kDual && BN <= 128) ? 2 : 1))
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                          GemmEpilogue ep, ConvK cv, int M, int N, int K, int kb_per_split) {
@@ -373,8 +476,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     const int m0 = blockIdx.x * kBM;
     const int n0 = blockIdx.y * BN;
     const int nkb_total = (K + kBK - 1) / kBK;
-    const int kb_begin = blockIdx.z * kb_per_split;
-    const int kb_end = min(nkb_total, kb_begin + kb_per_split);
+    // cluster form: an even partition (every slice non-empty because the host keeps gridDim.z <= nkb_total)
+    const int kb_begin = kCluster ? static_cast<int>(1ll * blockIdx.z * nkb_total / gridDim.z) : blockIdx.z * kb_per_split;
+    const int kb_end = kCluster ? static_cast<int>(1ll * (blockIdx.z + 1) * nkb_total / gridDim.z) : min(nkb_total, kb_begin + kb_per_split);
     const int nkb = kb_end - kb_begin;  // host guarantees >= 1
 
     if (warp == 0 && lane == 0) {
@@ -548,7 +652,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
         const int q = warp & 3;                 // TMEM lane quadrant this warp may access
         mbar_wait(tmem_full_bar, 0);
         tcgen05_fence_after();
-        gemm_epilogue_tile<BN>(tmem_d, q, lane, m0, n0, M, N, ep, ep.bias != nullptr && (!ep.atomic || blockIdx.z == 0));
+        if constexpr (!kCluster)
+            gemm_epilogue_tile<BN>(tmem_d, q, lane, m0, n0, M, N, ep, ep.bias != nullptr && (!ep.atomic || blockIdx.z == 0));
         if constexpr (kFin) {     // separate instantiation: the finishing code costs ~100 registers the plain kernels should not carry
             // release: this thread's red.adds are ordered before the counter bump; acquire on the other side before reading back
             __threadfence();
@@ -564,6 +669,53 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
                 __threadfence();
                 splitk_finish_tile<BN>(ep, warp - 2, lane, m0, n0, M, N);
             }
+        }
+    }
+
+    if constexpr (kCluster) {
+        const uint32_t S = gridDim.z, rank = blockIdx.z;        // cluster = (1, 1, S): the rank is the K-slice index
+        const uint32_t cs = BN / S;                              // columns this CTA finalises (host: multiple of 4, <= 32)
+        // #1: every CTA of the cluster has retired its MMAs, i.e. nobody reads its operand stages any more: they become the exchange area
+        //     [source slice][128 rows][cs columns] fp32 (S * 128 * cs * 4 = 128 * BN * 4 bytes <= the stage ring)
+        cluster_sync_all();
+        if (warp >= 2) {
+            const int q = warp & 3;
+            const uint32_t row = q * 32 + lane;
+#pragma unroll 1
+            for (int c0 = 0; c0 < BN; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld_32x32(tmem_d + (static_cast<uint32_t>(q * 32) << 16) + c0, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int g = 0; g < 8; ++g) {
+                    const uint32_t col = c0 + 4 * g;
+                    const uint32_t d = col / cs, off = col - d * cs;
+                    const uint32_t laddr = smem_base + ((rank * 128u + row) * cs + off) * 4u;
+                    st_cluster_f32x4(mapa_shared(laddr, d), __uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]), __uint_as_float(v[4 * g + 2]),
+                                     __uint_as_float(v[4 * g + 3]));
+                }
+            }
+        }
+        cluster_sync_all();                                      // #2: all partial slices have landed (release / acquire at cluster scope)
+        if (warp >= 2) {
+            const int q = warp & 3;
+            const uint32_t row = q * 32 + lane;
+            float f[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = 0.f;
+            for (uint32_t src = 0; src < S; ++src) {
+#pragma unroll
+                for (int g = 0; g < 8; ++g) {
+                    if (4u * g < cs) {
+                        const float4 t = ld_shared_f32x4(smem_base + ((src * 128u + row) * cs + 4u * g) * 4u);
+                        f[4 * g] += t.x; f[4 * g + 1] += t.y; f[4 * g + 2] += t.z; f[4 * g + 3] += t.w;
+                    }
+                }
+            }
+            const int col0 = n0 + static_cast<int>(rank * cs);
+            const int grow = m0 + static_cast<int>(row);
+            if (col0 < N)       // warp-uniform
+                cluster_final_rows(ep, grow, grow < M, lane, col0, min(static_cast<int>(cs), N - col0), f, ep.bias != nullptr);
         }
     }
 
@@ -1220,10 +1372,48 @@ static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb_half, c
     return 0;
 }
 
+// Cluster split-K: grid (tiles_m, tiles_n, S), the S K-slices of a tile form a cluster and reduce through distributed shared memory.
+template <typename E, int BN, int AM, int BMODE>
+static int launch_gemm_cluster(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpilogue& ep, const ConvK& cv, int M, int N, int K, int S,
+                               cudaStream_t stream) {
+    if constexpr (BN > 128) {
+        dmlb_set_error("cluster split-K is instantiated for tiles up to 128 columns");
+        return -4;
+    } else {
+        using Sm = GemmSmem<BN, false>;
+        auto kern = gemm_tcgen05_kernel<E, BN, AM, BMODE, false, false, true>;
+        const int nkb = (K + E::kBK - 1) / E::kBK;
+        DMLB_REQUIRE(S == 2 || S == 4 || S == 8, "cluster split-K: 2, 4 or 8 K-slices per tile");
+        DMLB_REQUIRE(S <= nkb, "cluster split-K: more slices than k-blocks");
+        DMLB_REQUIRE(BN % S == 0 && (BN / S) % 4 == 0 && BN / S <= 32, "cluster split-K: each slice finalises 4..32 columns (tile_n / slices)");
+        DMLB_REQUIRE(!ep.atomic && ep.perm_cin == 0 && ep.cpad == 0, "cluster split-K writes final values (no accumulating epilogue)");
+        DMLB_REQUIRE(128 * BN * 4 <= Sm::kStages * Sm::kStageBytes, "exchange area does not fit the operand stages");
+        static bool attr_set[64] = {};
+        int dev = 0;
+        DMLB_CHECK_CUDA(cudaGetDevice(&dev));
+        if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+            DMLB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Sm::kTotal));
+            if (dev >= 0 && dev < 64) attr_set[dev] = true;
+        }
+        dim3 grid((M + kBM - 1) / kBM, (N + BN - 1) / BN, S);
+        DMLB_CHECK_CUDA(launch_k_cluster(kern, grid, kGemmThreads, Sm::kTotal, stream, (unsigned)S, ta, tb, ep, cv, M, N, K, 0));
+        DMLB_LAUNCH_CHECK();
+        return 0;
+    }
+}
+
 // Several waves of tiles and no split-K -> the persistent kernel (bf16); more than one wave -> two CTAs per SM; otherwise the deep ring.
 template <typename E, int BN, int AM, int BMODE>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmEpilogue& ep, const ConvK& cv, int M, int N, int K, int splits,
                        cudaStream_t stream) {
+    if constexpr ((AM == 0 || AM == 2 || AM == 4) && (BMODE == 0 || BMODE == 3)) {
+        if (ep.cluster_s > 1) return launch_gemm_cluster<E, BN, AM, BMODE>(ta, tb, ep, cv, M, N, K, ep.cluster_s, stream);
+    } else {
+        if (ep.cluster_s > 1) {
+            dmlb_set_error("cluster split-K is instantiated for the forward / data-gradient operand forms");
+            return -4;
+        }
+    }
     const int nkb = (K + E::kBK - 1) / E::kBK;
     const int kb_per = (nkb + splits - 1) / splits;
     const long long ctas = 1ll * ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN) * ((nkb + kb_per - 1) / kb_per);
@@ -1339,10 +1529,11 @@ static int gemm_impl(const FinishArgs* fin, const void* A, int lda, int a_mn_maj
 //                   n_out = Cin;  (Ha, Wa) are the conv OUTPUT extents, the result has the conv INPUT extents.
 // Needs Ca % kBK == 0 (a 128-byte k-block must stay inside one filter tap: 64 bf16 / 32 fp32 channels); dgrad also needs 16-byte taps.
 // Epilogue arguments as in dmlb_gemm_*.  Reference: nn.Conv2d forward/backward in example/models.py:29-39 (cuDNN there).
+// `extra` (may be null): cluster_s / pooled / pool_w / act_* fields to copy into the epilogue (cluster split-K form).
 template <typename E>
 static int conv_implicit_impl(const FinishArgs* fin, int kind, const void* act, int ld_act, int B, int Ha, int Wa, int Ca, const void* other, int ld_other,
                               int KH, int KW, int SH, int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo,
-                              const float* bias, int relu, int split_k, int atomic, int tile_n, void* stream_) {
+                              const float* bias, int relu, int split_k, int atomic, int tile_n, void* stream_, const GemmEpilogue* extra = nullptr) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     constexpr int BK = E::kBK;
     DMLB_REQUIRE(kind >= 0 && kind <= 2, "kind must be 0 (fprop), 1 (wgrad) or 2 (dgrad)");
@@ -1354,6 +1545,15 @@ static int conv_implicit_impl(const FinishArgs* fin, int kind, const void* act, 
     DMLB_REQUIRE(!E::kTf32 || out_is_f32, "the tf32 convolution writes fp32");
     GemmEpilogue ep = {};
     ep.out = out; ep.bias = bias; ep.ldo = ldo; ep.out_is_f32 = out_is_f32; ep.relu = relu; ep.atomic = atomic; ep.perm_cin = 0; ep.perm_khw = 0;
+    if (extra != nullptr) {
+        DMLB_REQUIRE(kind != 1 && !atomic && split_k == 1, "the cluster form replaces split-K for fprop / dgrad");
+        ep.cluster_s = extra->cluster_s; ep.pooled = extra->pooled; ep.ldp = extra->ldp; ep.pool_w = extra->pool_w;
+        ep.act_y = extra->act_y; ep.act_dy = extra->act_dy; ep.act_dbias = extra->act_dbias; ep.act_ldy = extra->act_ldy;
+        ep.act_pool2 = extra->act_pool2; ep.act_relu = extra->act_relu; ep.act_hx = extra->act_hx; ep.act_wx = extra->act_wx;
+        if (ep.pool_w > 0)
+            DMLB_REQUIRE((ep.pool_w & (ep.pool_w - 1)) == 0 && ep.pool_w >= 2 && ep.pool_w <= 16 && ep.pooled != nullptr,
+                         "fused 2x2 pool needs a power-of-two map width <= 16");
+    }
     ConvK cv = {};
     cv.C = Ca; cv.KH = KH; cv.KW = KW; cv.sh = SH; cv.sw = SW;
     CUtensorMap ta, tb;

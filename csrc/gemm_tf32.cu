@@ -27,3 +27,18 @@ extern "C" int dmlb_conv_smallc_tf32(int kind, const void* act, int B, int Ha, i
     return conv_smallc_impl<ElemTF32>(kind, act, B, Ha, Wa, cin, other, ld_other, KH, KW, SH, SW, PH, PW, n_out, out, out_is_f32, ldo, bias, relu,
                                  split_k, pt_layout, pooled, ldp, pool_w, tile_n, hp, wp, stream);
 }
+
+// Implicit convolution, cluster split-K form (kind 0 fprop / 2 dgrad): the K-slices of a tile reduce through distributed shared memory and
+// the fused epilogue runs on the sum — see gemm_tcgen05.cuh (kCluster) and include/dmlb.h.
+extern "C" int dmlb_conv_implicit_cluster_tf32(int kind, const void* act, int ld_act, int B, int Ha, int Wa, int Ca, const void* other, int ld_other,
+                                               int KH, int KW, int SH, int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo,
+                                               const float* bias, int relu, int cluster_s, int tile_n, void* pooled, int ldp, int pool_w,
+                                               const void* act_y, void* act_dy, int act_ldy, float* act_dbias, int act_pool2, int act_relu,
+                                               int act_hx, int act_wx, void* stream) {
+    GemmEpilogue x = {};
+    x.cluster_s = cluster_s; x.pooled = pooled; x.ldp = ldp; x.pool_w = pool_w;
+    x.act_y = act_y; x.act_dy = act_dy; x.act_ldy = act_ldy; x.act_dbias = act_dbias; x.act_pool2 = act_pool2; x.act_relu = act_relu;
+    x.act_hx = act_hx; x.act_wx = act_wx;
+    return conv_implicit_impl<ElemTF32>(nullptr, kind, act, ld_act, B, Ha, Wa, Ca, other, ld_other, KH, KW, SH, SW, PH, PW, n_out, out, out_is_f32, ldo,
+                                   bias, relu, 1, 0, tile_n, stream, &x);
+}

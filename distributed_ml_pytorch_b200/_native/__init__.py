@@ -76,6 +76,14 @@ _SIGNATURES = {
     # (x, y, B, C, H, W, hp, wp, ph, pw, stream)
     "dmlb_nchw_to_act_bf16": [c_vp, c_vp] + [c_int] * 8 + [c_vp],
     "dmlb_nchw_to_act_f32": [c_vp, c_vp] + [c_int] * 8 + [c_vp],
+    # (kind, act, ld_act, B, Ha, Wa, Ca, other, ld_other, KH, KW, SH, SW, PH, PW, n_out, out, out_is_f32, ldo, bias, relu, cluster_s, tile_n,
+    #  pooled, ldp, pool_w, act_y, act_dy, act_ldy, act_dbias, act_pool2, act_relu, act_hx, act_wx, stream)
+    "dmlb_conv_implicit_cluster_bf16": [c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                        c_vp, c_int, c_int, c_vp, c_int, c_int, c_int, c_vp, c_int, c_int, c_vp, c_vp, c_int, c_vp, c_int, c_int,
+                                        c_int, c_int, c_vp],
+    "dmlb_conv_implicit_cluster_tf32": [c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                        c_vp, c_int, c_int, c_vp, c_int, c_int, c_int, c_vp, c_int, c_int, c_vp, c_vp, c_int, c_vp, c_int, c_int,
+                                        c_int, c_int, c_vp],
     # (ws, ldw, y, dy, ldy, dbias, B, Hx, Wx, C, pool2, relu, is_f32, stream)
     "dmlb_splitk_finish_actbwd": [c_vp, c_int, c_vp, c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_vp],
     "dmlb_sgd_flat_slot": [c_vp, c_vp, c_vp, c_vp, c_vp, c_ll, c_vp, c_float, c_float, c_int, c_vp],

@@ -354,7 +354,18 @@ class _ConvBlockFn(torch.autograd.Function):
         split = K.fprop_split(M, Cout, Kd, bk=bk)
         out = y
         fused_pool = False
-        if split > 1:
+        plan = K.cluster_plan(M, Cout, Kd, bk) if (split > 1 and implicit) else None
+        if plan is not None:
+            # tiny-M / long-K layer, cluster form: the K-slices of a tile reduce through distributed shared memory and the epilogue
+            # (bias, ReLU, 2x2 pool) runs on the sum — no workspace, no atomics, no finishing kernel
+            pool_w = 0
+            if cfg.pool == (2, 2, 0) and Ho % 2 == 0 and Wo in (2, 4, 8, 16):
+                out = new_act4(B, Cout, Ho // 2, Wo // 2, dev, dt)
+                pool_w, fused_pool = Wo, True
+            K.conv_implicit_cluster(0, x.data_ptr(), ldx, B, H, W, Cin, cfg.shadow.data_ptr(), Kpad, KH, KW, SH, SW, PH, PW, Cout, y.data_ptr(), ldy,
+                                    plan[1], plan[0], bias=bias, relu=cfg.relu, pooled_ptr=out.data_ptr() if pool_w else 0, ldp=ldy, pool_w=pool_w,
+                                    dt=dt)
+        elif split > 1:
             # tiny-M / long-K layer: spread K over the SMs, reduce in an fp32 workspace, finish (bias, ReLU, bf16, 2x2 pool) in one
             # more kernel — or, opt-in (K.set_fused_finish(True); measured slower), in the GEMM's last-arriving CTA per tile
             ldw = (Cout + 3) // 4 * 4
@@ -574,7 +585,31 @@ class _ConvBlockFn(torch.autograd.Function):
                 # transposed convolution as an implicit GEMM over dY: no dcol matrix, no col2im
                 Min, Kdg = B * H * W, KH * KW * Cout
                 dsplit = K.fprop_split(Min, Cin, Kdg, bk=bk)
-                if dsplit > 1:
+                dplan = K.cluster_plan(Min, Cin, Kdg, bk, bns=(128, 64)) if dsplit > 1 else None
+                pf = cfg.prod.fwd if (cfg.prod is not None and _fuse.enabled) else None
+                if pf is not None and not (pf.out_ptr == ctx.x_ptr and pf.dt == dt and pf.C == Cin and pf.B == B and
+                                           (pf.Ho, pf.Wo) == ((2 * H, 2 * W) if pf.pool2 else (H, W))):
+                    pf = None
+                if dplan is not None:
+                    # cluster split-K dgrad; when the producer block allows it its pool / ReLU backward + bias gradient run in the epilogue
+                    if pf is not None:
+                        dyp = new_act4(B, Cin, pf.Ho, pf.Wo, dev, dt)
+                        pgb = torch.zeros(Cin, dtype=torch.float32, device=dev) if (pf.bsink is None and pf.needs_bias_grad) else None
+                        K.conv_implicit_cluster(2, dy.data_ptr(), lddy, B, Ho, Wo, Cout, cfg.shadow.data_ptr(), Kpad, KH, KW, 1, 1, PH, PW, Cin,
+                                                dyp.data_ptr(), pf.ldy, dplan[1], dplan[0],
+                                                act=(pf.y.data_ptr(), dyp.data_ptr(), pf.ldy, pf.bsink if pf.bsink is not None else pgb, pf.pool2,
+                                                     pf.relu, H, W), dt=dt)
+                        if pf.bsink is not None:
+                            _notify_grad_ready(pf.bias, dev)
+                        token = torch.empty(1, dtype=dt, device=dev)
+                        if len(_fuse.pending) > 256:
+                            _fuse.pending.clear()
+                        _fuse.pending[token.data_ptr()] = SimpleNamespace(dy=dyp, gb=pgb, token=token)
+                        dx = token.expand(B, Cin, H, W)
+                    else:
+                        K.conv_implicit_cluster(2, dy.data_ptr(), lddy, B, Ho, Wo, Cout, cfg.shadow.data_ptr(), Kpad, KH, KW, 1, 1, PH, PW, Cin,
+                                                dx.data_ptr(), ldxo, dplan[1], dplan[0], dt=dt)
+                elif dsplit > 1:
                     ldw = (Cin + 3) // 4 * 4
                     ws = K.splitk_workspace(dev, Min * ldw)
                     if dt == BF16 and K.fused_finish():

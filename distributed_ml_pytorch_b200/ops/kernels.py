@@ -118,6 +118,52 @@ def rowwin_geometry(H, W, KH, KW, SH, SW, PH, PW, dt):
     return max(H + 2 * PH, (Ho - 1) * SH + KH), max(W + 2 * PW, (Wo - 1) * SW + 8 * kwb)
 
 
+_cluster = [os.environ.get("DMLB_CLUSTER_SPLITK", "1") == "1"]
+
+
+def set_cluster_splitk(on: bool) -> bool:
+    """Cluster split-K (K-slices of a tile reduce through distributed shared memory, fused epilogue on the sum) instead of an fp32
+    workspace + finishing kernel; returns the old setting."""
+    old, _cluster[0] = _cluster[0], bool(on)
+    return old
+
+
+def cluster_plan(M: int, N: int, Kd: int, bk: int, bns=(128, 64, 32), sms: int = 148):
+    """``(tile_n, slices)`` of the cluster split-K form for a tiny-M / long-K GEMM, or ``None``: every tile's K is cut into 2, 4 or 8
+    slices (one cluster), each CTA finalises ``tile_n / slices`` (4..32) columns; pick what fits the SMs with the fewest bytes per CTA."""
+    if not _cluster[0]:
+        return None
+    nkb = (Kd + bk - 1) // bk
+    tiles_m = (M + 127) // 128
+    best = None
+    for bn in bns:
+        if bn > 32 and bn // 2 >= N:          # tile much wider than the matrix
+            continue
+        tiles = tiles_m * ((N + bn - 1) // bn)
+        for s in (8, 4, 2):
+            cs = bn // s
+            if s > nkb or cs > 32 or cs % 4:
+                continue
+            if tiles * s > sms:
+                continue
+            per = -(-nkb // s) * (16384 + bn * 128)
+            if best is None or per < best[0]:
+                best = (per, bn, s)
+    return (best[1], best[2]) if best else None
+
+
+def conv_implicit_cluster(kind: int, act_ptr: int, ld_act: int, B, Ha, Wa, Ca, other_ptr: int, ld_other: int, KH, KW, SH, SW, PH, PW, n_out: int,
+                          out_ptr: int, ldo: int, cluster_s: int, tile_n: int, bias=None, relu: bool = False, pooled_ptr: int = 0, ldp: int = 0,
+                          pool_w: int = 0, act=None, dt=torch.bfloat16) -> None:
+    """Implicit convolution, cluster split-K form (``dmlb_conv_implicit_cluster_*``): kind 0 fprop (bias / ReLU / optional 2x2 pool),
+    kind 2 dgrad (``act = (y_ptr, dy_ptr, ldy, dbias tensor or None, pool2, relu, Hx, Wx)``: producer block's activation backward fused)."""
+    ay, ady, aldy, adb, ap2, arelu, ahx, awx = act if act is not None else (0, 0, 0, None, False, False, 0, 0)
+    _call("dmlb_conv_implicit_cluster_tf32" if dt == torch.float32 else "dmlb_conv_implicit_cluster_bf16", kind, act_ptr, ld_act, B, Ha, Wa, Ca,
+          other_ptr, ld_other, KH, KW, SH, SW, PH, PW, n_out, out_ptr or None, int(dt == torch.float32), ldo,
+          bias.data_ptr() if bias is not None else None, int(relu), cluster_s, tile_n, pooled_ptr or None, ldp, pool_w, ay or None, ady or None, aldy,
+          adb.data_ptr() if adb is not None else None, int(ap2), int(arelu), ahx, awx, stream_ptr())
+
+
 def pick_split_k(tiles: int, k_total: int, sms: int = 148, min_kblocks: int = 2, bk: int = 64) -> int:
     """Split-K factor that fills the SMs when the output has few tiles (weight gradients, tiny-M fprop)."""
     nkb = (k_total + bk - 1) // bk

@@ -84,6 +84,21 @@ int dmlb_conv_implicit_bf16(int kind, const void* act, int ld_act, int B, int Ha
                             int SH, int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo, const float* bias, int relu,
                             int split_k, int atomic, int tile_n, void* stream);
 
+/* dmlb_conv_implicit_* with the K reduction split over a thread-block CLUSTER (cluster_s = 2, 4 or 8 CTAs per output tile) instead of an
+ * fp32 workspace + finishing kernel: every CTA scatters its TMEM accumulator through distributed shared memory, CTA r sums and finalises
+ * tile_n / cluster_s columns (4..32).  kind 0 fprop: bias, ReLU, optional 2x2 max-pool into pooled (pool_w = map width, power of two <= 16).
+ * kind 2 dgrad: plain store of dx, or (act_y != NULL) the producer block's pool / ReLU backward + bias gradient as in
+ * dmlb_splitk_finish_actbwd: out is then unused, act_dy receives the producer's pre-activation gradient.
+ * Reference: nn.Conv2d forward / backward of example/models.py:32-41 at batch 64 (tiny M, long K). */
+int dmlb_conv_implicit_cluster_bf16(int kind, const void* act, int ld_act, int B, int Ha, int Wa, int Ca, const void* other, int ld_other, int KH,
+                                    int KW, int SH, int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo, const float* bias,
+                                    int relu, int cluster_s, int tile_n, void* pooled, int ldp, int pool_w, const void* act_y, void* act_dy,
+                                    int act_ldy, float* act_dbias, int act_pool2, int act_relu, int act_hx, int act_wx, void* stream);
+int dmlb_conv_implicit_cluster_tf32(int kind, const void* act, int ld_act, int B, int Ha, int Wa, int Ca, const void* other, int ld_other, int KH,
+                                    int KW, int SH, int SW, int PH, int PW, int n_out, void* out, int out_is_f32, int ldo, const float* bias,
+                                    int relu, int cluster_s, int tile_n, void* pooled, int ldp, int pool_w, const void* act_y, void* act_dy,
+                                    int act_ldy, float* act_dbias, int act_pool2, int act_relu, int act_hx, int act_wx, void* stream);
+
 /* Split-K forward (csrc/splitk.cu): for tiny-M, long-K layers (AlexNet conv3-5 at the reference's batch 64,
  * example/main.py:142).  ws is fp32 scratch [M, round_up(N,4)], all zeros on entry and zeroed again by the finish. */
 int dmlb_splitk_finish(float* ws, int ldw, const float* bias, int relu, void* y, int ldy, long long M, int N, int pool2, int B, int H, int W,
