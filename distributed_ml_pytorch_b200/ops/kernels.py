@@ -134,6 +134,10 @@ def cluster_plan(M: int, N: int, Kd: int, bk: int, bns=(128, 64, 32), sms: int =
     if not _cluster[0]:
         return None
     nkb = (Kd + bk - 1) // bk
+    # Measured on B200 (AlexNet, batch 64): a CTA of these kernels streams ~0.4-0.5 us per 128-byte k-block however few bytes it is, so
+    # what counts is the serial loop length.  A cluster caps the K-split at 8, the workspace form does not: the cluster form only wins
+    # while each slice keeps a short loop (DMLB_CLUSTER_MAXKB k-blocks, default 4); longer reductions stay on split-K + finish.
+    max_kb = int(os.environ.get("DMLB_CLUSTER_MAXKB", "4"))
     tiles_m = (M + 127) // 128
     best = None
     for bn in bns:
@@ -144,7 +148,7 @@ def cluster_plan(M: int, N: int, Kd: int, bk: int, bns=(128, 64, 32), sms: int =
             cs = bn // s
             if s > nkb or cs > 32 or cs % 4:
                 continue
-            if tiles * s > sms:
+            if tiles * s > sms or -(-nkb // s) > max_kb:
                 continue
             per = -(-nkb // s) * (16384 + bn * 128)
             if best is None or per < best[0]:

@@ -84,11 +84,14 @@ def test_cluster_splitk_matches_workspace_form(dtype):
     from distributed_ml_pytorch_b200.ops import kernels as K
 
     def run(cluster):
+        import os
         old = K.set_cluster_splitk(cluster)
+        os.environ["DMLB_CLUSTER_MAXKB"] = "1000"           # force the cluster form on every split layer, whatever its loop length
         try:
             return _grads(dtype, fused=True)
         finally:
             K.set_cluster_splitk(old)
+            os.environ.pop("DMLB_CLUSTER_MAXKB", None)
 
     g0, l0, n0 = run(False)
     g1, l1, n1 = run(True)
