@@ -76,25 +76,34 @@ struct GemmEpilogue {
     // tile): pool_w = W of the [B, H, W] map the rows enumerate (power of two <= 16, H even), 0 = off; pooled is [M/4, ldp].
     void* pooled;
     int ldp, pool_w;
-    // Cluster split-K epilogue only: activation backward of the block that produced this dgrad's input (see dmlb_splitk_finish_actbwd):
-    // rows are pixels of that block's OUTPUT [B, act_hx, act_wx]; act_y / act_dy are its activation / pre-activation gradient
-    // [B, H, W, act_ldy] with (H, W) = (act_hx, act_wx) or twice that when act_pool2; act_dbias (fp32 [N], may be null) += column sums.
-    const void* act_y;
-    void* act_dy;
-    float* act_dbias;
-    int act_ldy, act_pool2, act_relu, act_hx, act_wx;
+    int use_fin;          // the fin_* member of the union below is live (folded split-K finish, kFin kernels)
     int cluster_s;        // host side only: > 1 = launch the cluster split-K form with this many K-slices per tile
-    // Split-K with the finishing pass folded in ("last CTA of a tile finishes"): every z-slice red.adds its partial tile into the
-    // fp32 workspace `out`, then bumps the tile's arrival counter; the slice that arrives last reads the summed tile back from L2,
-    // applies bias / ReLU, rounds to bf16 into fin_y (optionally also the 2x2/2 max-pool into fin_pooled), and writes zeros back,
-    // so workspace and counters are clean for the next layer and no separate finishing launch is needed.
-    int* fin_counters;    // nullptr = off; [tiles_n * tiles_m] ints, all zero on entry and on exit
-    void* fin_y;          // bf16 [M, fin_ldy]
-    const float* fin_bias;
-    void* fin_pooled;     // bf16 [M/4, fin_ldp] when fin_pool_w > 0
-    int fin_ldy, fin_ldp, fin_relu;
-    int fin_pool_w;       // W of the [B,H,W] map the rows enumerate (H, W even, 128 % (2W) == 0); 0 = no pooling
+    // The two rarely used argument groups share storage (kernel parameters are copied at every launch, and this step is launch-bound).
+    union {
+        // Split-K with the finishing pass folded in ("last CTA of a tile finishes"): every z-slice red.adds its partial tile into the
+        // fp32 workspace `out`, then bumps the tile's arrival counter; the slice that arrives last reads the summed tile back from L2,
+        // applies bias / ReLU, rounds to bf16 into fin_y (optionally also the 2x2/2 max-pool into fin_pooled), and writes zeros back,
+        // so workspace and counters are clean for the next layer and no separate finishing launch is needed.
+        struct {
+            int* fin_counters;    // [tiles_n * tiles_m] ints, all zero on entry and on exit
+            void* fin_y;          // bf16 [M, fin_ldy]
+            const float* fin_bias;
+            void* fin_pooled;     // bf16 [M/4, fin_ldp] when fin_pool_w > 0
+            int fin_ldy, fin_ldp, fin_relu;
+            int fin_pool_w;       // W of the [B,H,W] map the rows enumerate (H, W even, 128 % (2W) == 0); 0 = no pooling
+        };
+        // Cluster split-K epilogue only: activation backward of the block that produced this dgrad's input (see dmlb_splitk_finish_actbwd):
+        // rows are pixels of that block's OUTPUT [B, act_hx, act_wx]; act_y / act_dy are its activation / pre-activation gradient
+        // [B, H, W, act_ldy] with (H, W) = (act_hx, act_wx) or twice that when act_pool2; act_dbias (fp32 [N], may be null) += column sums.
+        struct {
+            const void* act_y;
+            void* act_dy;
+            float* act_dbias;
+            int act_ldy, act_pool2, act_relu, act_hx, act_wx;
+        };
+    };
 };
+static_assert(sizeof(GemmEpilogue) == 128, "keep the epilogue arguments compact");
 
 // Operand sources.  A: 0 = K-major matrix (2-D TMA), 1 = MN-major matrix, 2 = im2col gather of an NHWC activation
 // (implicit-GEMM convolution: fprop reads x, dgrad reads dY).  B: 0 = K-major matrix, 1 = MN-major matrix,
@@ -414,7 +423,7 @@ __device__ __forceinline__ void actbwd_rows(const GemmEpilogue& ep, int row, boo
 
 __device__ __forceinline__ void cluster_final_rows(const GemmEpilogue& ep, int row, bool row_ok, int lane, int col0, int ncols, float (&f)[32],
                                                    bool add_bias) {
-    if (ep.act_y != nullptr) {
+    if (!ep.use_fin && ep.act_y != nullptr) {
         if (ep.out_is_f32) actbwd_rows<float>(ep, row, row_ok, lane, col0, ncols, f);
         else               actbwd_rows<__nv_bfloat16>(ep, row, row_ok, lane, col0, ncols, f);
         return;
@@ -1420,10 +1429,10 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmE
     if constexpr (!E::kTf32 && BN <= 128 && BMODE == 0 && AM != 3) {
         // forward form only (both operands K-major): the backward GEMMs share the GPU with the side-stream wgrad branch and a grid
         // that pins every SM would serialise against it.  Short reductions only: with a long K loop the per-tile set-up is already amortised and the 2-CTA variant rasterises better
-        if (splits == 1 && ep.fin_counters == nullptr && nkb <= 24 && ctas >= 3ll * dmlb_sm_count() && dmlb_gemm_persistent_enabled())
+        if (splits == 1 && !ep.use_fin && nkb <= 24 && ctas >= 3ll * dmlb_sm_count() && dmlb_gemm_persistent_enabled())
             return launch_gemm_persistent<BN, AM, BMODE>(ta, tb, ep, cv, M, N, K, stream);
     }
-    if (ep.fin_counters != nullptr) {
+    if (ep.use_fin) {
         // folded split-K finish: forward / dgrad operand forms only, small grids by construction -> deep-ring variant (bf16 outputs)
         if constexpr (!E::kTf32 && (AM == 0 || AM == 2) && (BMODE == 0 || BMODE == 3) && BN <= 128)
             return launch_gemm_v<E, BN, AM, BMODE, false, true>(ta, tb, ep, cv, M, N, K, splits, stream);
@@ -1453,6 +1462,7 @@ static int apply_finish(GemmEpilogue& ep, const FinishArgs& f, int M, int N, int
     DMLB_REQUIRE(f.counters != nullptr && f.y != nullptr && f.ldy % 4 == 0 && (reinterpret_cast<uintptr_t>(f.y) & 7) == 0, "fused finish: bad output");
     const long long tiles = 1ll * ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN);
     DMLB_REQUIRE(tiles <= f.n_counters, "fused finish: more output tiles than arrival counters");
+    ep.use_fin = 1;
     ep.fin_counters = f.counters; ep.fin_y = f.y; ep.fin_bias = f.bias; ep.fin_ldy = f.ldy; ep.fin_relu = f.relu;
     ep.fin_pooled = nullptr; ep.fin_ldp = 0; ep.fin_pool_w = 0;
     if (f.pool_w > 0) {
