@@ -118,7 +118,11 @@ def rowwin_geometry(H, W, KH, KW, SH, SW, PH, PW, dt):
     return max(H + 2 * PH, (Ho - 1) * SH + KH), max(W + 2 * PW, (Wo - 1) * SW + 8 * kwb)
 
 
-_cluster = [os.environ.get("DMLB_CLUSTER_SPLITK", "1") == "1"]
+# Measured on B200 (AlexNet, batch 64, 1 GPU): correct, 8 launches fewer per step, and SLOWER — 0.263 ms/step (tf32, every split layer) vs
+# 0.198 with the workspace form; restricted to slices of <= 4 k-blocks (bf16 conv2 / conv3) still 0.205 vs 0.188.  A CTA of these kernels
+# streams ~0.4-0.5 us per k-block whatever its size, so the serial loop length decides; a cluster caps the split at 8 where the workspace
+# form cuts K 13-32 ways, and gang-scheduling 8 CTAs of 165 KB shared memory each delays the start.  Hence opt-in (DMLB_CLUSTER_SPLITK=1).
+_cluster = [os.environ.get("DMLB_CLUSTER_SPLITK", "0") == "1"]
 
 
 def set_cluster_splitk(on: bool) -> bool:
