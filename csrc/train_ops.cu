@@ -148,10 +148,16 @@ __global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ param
                                                        float* const* __restrict__ acc_slot, float* __restrict__ mom,
                                                        __nv_bfloat16* __restrict__ shadow, long long n4, const float* __restrict__ lr_ptr,
                                                        float mu, float wd, int zero_grads, const ShadowEntry* __restrict__ table, int n_entries,
-                                                       int table_f32, long long table_lo, long long table_hi) {
+                                                       int table_f32, long long table_lo, long long table_hi,
+                                                       const float* __restrict__ pulled, const unsigned* __restrict__ pull_flag) {
     pdl_prologue();
     const float lr = *lr_ptr;
     float* __restrict__ acc = acc_slot != nullptr ? *acc_slot : acc_direct;
+    // Landing of an overlapped parameter pull (asynchronous optimizer): while *pull_flag is set, `pulled` holds the server's parameters as
+    // fetched after this worker's last push, and the replica is re-based on them: theta = pulled + (updates not pushed yet) — the
+    // accumulator, which already includes this step.  The flag is raised by the communication stream after the fetch and cleared by the
+    // step stream at the next push; an element sees either value and is correct both ways (it lands now or at the next step).
+    const bool land = pull_flag != nullptr && *reinterpret_cast<const volatile unsigned*>(pull_flag) != 0u;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
         float4 p = reinterpret_cast<float4*>(params)[i];
         float4 g = ld_stream_f32x4(grads + 4 * i);
@@ -163,7 +169,13 @@ __global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ param
             reinterpret_cast<float4*>(mom)[i] = v;
             g = v;
         }
-        p.x -= lr * g.x; p.y -= lr * g.y; p.z -= lr * g.z; p.w -= lr * g.w;
+        if (land && acc != nullptr) {
+            const float4 a = reinterpret_cast<const float4*>(acc)[i];
+            const float4 s = ld_stream_f32x4(pulled + 4 * i);
+            p.x = s.x + (a.x - lr * g.x); p.y = s.y + (a.y - lr * g.y); p.z = s.z + (a.z - lr * g.z); p.w = s.w + (a.w - lr * g.w);
+        } else {
+            p.x -= lr * g.x; p.y -= lr * g.y; p.z -= lr * g.z; p.w -= lr * g.w;
+        }
         reinterpret_cast<float4*>(params)[i] = p;
         if (shadow != nullptr) {  // bf16 mirror for the tensor cores, same flat offsets
             uint2 h;
@@ -348,26 +360,27 @@ extern "C" int dmlb_scale_rows_f32(void* x, const float* scale, long long rows, 
 // (relative to params) that holds those weights.
 extern "C" int dmlb_sgd_flat_ex(float* params, float* grads, float* acc, void* acc_slot, float* mom, void* shadow, long long n, const float* lr_ptr,
                                 float mu, float wd, int zero_grads, const void* table, int n_entries, int table_is_f32, long long table_lo,
-                                long long table_hi, void* stream) {
+                                long long table_hi, const float* pulled, const void* pull_flag, void* stream) {
     DMLB_REQUIRE(n % 4 == 0, "flat SGD length must be a multiple of 4 (arena padding)");
     DMLB_REQUIRE(((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads)) & 15) == 0, "arena must be 16-byte aligned");
     DMLB_CHECK_CUDA(launch_k(sgd_flat_kernel, flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream), params, grads, acc,
                              static_cast<float* const*>(acc_slot), mom, static_cast<__nv_bfloat16*>(shadow), n / 4, lr_ptr, mu, wd, zero_grads,
-                             static_cast<const ShadowEntry*>(table), table != nullptr ? n_entries : 0, table_is_f32, table_lo, table_hi));
+                             static_cast<const ShadowEntry*>(table), table != nullptr ? n_entries : 0, table_is_f32, table_lo, table_hi, pulled,
+                             static_cast<const unsigned*>(pull_flag)));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
 
 extern "C" int dmlb_sgd_flat(float* params, float* grads, float* acc, float* mom, void* shadow, long long n, const float* lr_ptr, float mu,
                              float wd, int zero_grads, void* stream) {
-    return dmlb_sgd_flat_ex(params, grads, acc, nullptr, mom, shadow, n, lr_ptr, mu, wd, zero_grads, nullptr, 0, 0, 0, 0, stream);
+    return dmlb_sgd_flat_ex(params, grads, acc, nullptr, mom, shadow, n, lr_ptr, mu, wd, zero_grads, nullptr, 0, 0, 0, 0, nullptr, nullptr, stream);
 }
 
 // dmlb_sgd_flat with the accumulator named indirectly: *acc_slot (device memory) is the buffer to accumulate -lr*g into.
 extern "C" int dmlb_sgd_flat_slot(float* params, float* grads, void* acc_slot, float* mom, void* shadow, long long n, const float* lr_ptr, float mu,
                                   float wd, int zero_grads, void* stream) {
     DMLB_REQUIRE(acc_slot != nullptr, "acc_slot is required (use dmlb_sgd_flat for a direct accumulator)");
-    return dmlb_sgd_flat_ex(params, grads, nullptr, acc_slot, mom, shadow, n, lr_ptr, mu, wd, zero_grads, nullptr, 0, 0, 0, 0, stream);
+    return dmlb_sgd_flat_ex(params, grads, nullptr, acc_slot, mom, shadow, n, lr_ptr, mu, wd, zero_grads, nullptr, 0, 0, 0, 0, nullptr, nullptr, stream);
 }
 
 namespace dmlb {
@@ -393,6 +406,10 @@ __global__ void __launch_bounds__(256) nchw_to_act_kernel(const float* __restric
 }
 
 __global__ void store_u64_kernel(unsigned long long* slot, unsigned long long value) { *slot = value; }
+__global__ void store_u64_u32_kernel(unsigned long long* slot, unsigned long long value, unsigned* flag, unsigned fvalue) {
+    *slot = value;
+    *flag = fvalue;
+}
 
 // params = pulled + unpushed;  shadow = bf16(params)   (n4 float4 groups; unpushed / shadow may be null)
 __global__ void __launch_bounds__(256) apply_pull_kernel(float* __restrict__ params, const float* __restrict__ pulled,
@@ -437,6 +454,15 @@ extern "C" int dmlb_nchw_to_act_f32(const float* x, void* y, int B, int C, int H
 extern "C" int dmlb_store_u64(void* slot, unsigned long long value, void* stream) {
     DMLB_REQUIRE(slot != nullptr && (reinterpret_cast<uintptr_t>(slot) & 7) == 0, "slot must be an 8-byte aligned device address");
     DMLB_CHECK_CUDA(launch_k(store_u64_kernel, 1, 1, 0, static_cast<cudaStream_t>(stream), static_cast<unsigned long long*>(slot), value));
+    DMLB_LAUNCH_CHECK();
+    return 0;
+}
+
+// *slot = value and *flag = fvalue in one launch (accumulator switch + "no pull to land" at a push).
+extern "C" int dmlb_store_u64_u32(void* slot, unsigned long long value, void* flag, unsigned fvalue, void* stream) {
+    DMLB_REQUIRE(slot != nullptr && flag != nullptr, "null destination");
+    DMLB_CHECK_CUDA(launch_k(store_u64_u32_kernel, 1, 1, 0, static_cast<cudaStream_t>(stream), static_cast<unsigned long long*>(slot), value,
+                             static_cast<unsigned*>(flag), fvalue));
     DMLB_LAUNCH_CHECK();
     return 0;
 }

@@ -26,9 +26,10 @@ uploads the initial parameters.
 Overlap on the peer transport (``overlap=True``, the default): pushes, owner-side applies and pulls run on a communication stream
 while the worker keeps training.  The accumulator is double-buffered — at a push the training step switches to the other buffer (its
 address is read from device memory, so a captured CUDA graph follows the switch) and the push drains the retired one over NVLink — and a
-pull is fetched into a staging buffer that *lands* one step later, at a step boundary, as ``params = pulled + unpushed local updates``
-(one local pass over HBM).  The step stream therefore never waits for NVLink: per communication round it runs one 8-byte store and
-one landing kernel.
+pull is fetched into a staging buffer and raises a device flag when it is complete; while the flag is up the (captured) optimizer
+kernel re-bases the replica on it, ``params = pulled + unpushed local updates``, instead of ``params -= lr * grad`` — the pull *lands*
+at a step boundary inside a kernel that runs anyway.  The step stream never waits for NVLink: per communication round it runs one
+12-byte store (accumulator switch + flag reset).
 """
 from __future__ import annotations
 
@@ -188,9 +189,9 @@ class Asynchronous(ArenaOptimizer):
             self._acc_cur = 0
             self._acc_slot = torch.tensor([self._acc[0].data_ptr()], dtype=torch.int64, device=dev)
             self._pulled = torch.empty_like(a.params)
+            self._pull_flag = torch.zeros(1, dtype=torch.int64, device=dev)     # != 0: `_pulled` is complete and not yet superseded
             self.comm_stream = torch.cuda.Stream(device=dev)
             self._push_done = [None, None]
-            self._pending_pull = None        # (step index it was issued at, completion event)
         pg.barrier()
         self._pull()                                           # every replica starts from the server's parameters
         torch.cuda.synchronize(a.params.device)
@@ -220,36 +221,24 @@ class Asynchronous(ArenaOptimizer):
         a.mark_params_changed(flat_done=a.shadow is not None)
         self.pulls += 1
 
-    def _land_pull(self, force: bool = False) -> None:
-        """Overlap mode: make a fetched pull the model's parameters (on the current stream, at a step boundary)."""
-        pp = self._pending_pull
-        if pp is None or (not force and self.idx - pp[0] < self.pull_lag):
-            return
-        from ..ops import kernels as K
-        a = self.arena
-        cur = torch.cuda.current_stream(a.params.device)
-        cur.wait_event(pp[1])
-        # pulled + the local updates the server has not seen yet (they sit in the current accumulator): exactly what a pull that
-        # had landed the moment it was issued, followed by the local steps since, would have produced
-        K.apply_pull(a.params, self._pulled, self._acc_slot, a.shadow, a.padded)
-        a.mark_params_changed(flat_done=a.shadow is not None)
-        self._pending_pull = None
-
     def _communicate_overlapped(self, push_now: bool, pull_now: bool) -> None:
         from . import peer
         from ..ops import kernels as K
         pg, a = self.peer, self.arena
         dev = a.params.device
         cur = torch.cuda.current_stream(dev)
-        self._land_pull()
         if not (push_now or pull_now or self._use_mailbox):
             return
         retired = None
-        if push_now:
-            retired, nxt = self._acc_cur, self._acc_cur ^ 1
-            if self._push_done[nxt] is not None:
-                cur.wait_event(self._push_done[nxt])       # drained n_push steps ago: no wait in practice
-            K.store_u64(self._acc_slot, self._acc[nxt].data_ptr())
+        if push_now or pull_now:
+            nxt = self._acc_cur
+            if push_now:
+                retired, nxt = self._acc_cur, self._acc_cur ^ 1
+                if self._push_done[nxt] is not None:
+                    cur.wait_event(self._push_done[nxt])       # drained n_push steps ago: no wait in practice
+            # one tiny kernel on the step stream: switch the accumulator (push) and take the landing flag down — the staging buffer
+            # is about to be overwritten (pull) and / or its contents are about to be superseded by this push
+            K.store_u64_u32(self._acc_slot, self._acc[nxt].data_ptr(), self._pull_flag, 0)
             self._acc_cur = nxt
             self.accumulated_gradients = self._acc[nxt]
         ready = torch.cuda.Event()
@@ -266,13 +255,9 @@ class Asynchronous(ArenaOptimizer):
                 self._owner_apply()
             if pull_now:
                 peer.pull(self._pulled, self.master_sym.table, pg.world, a.shards.shard_size, a.padded, self.version_sym.table, self.pulled_ver)
-                fetched = torch.cuda.Event()
-                fetched.record(self.comm_stream)
-                self._pending_pull = (self.idx, fetched)
+                K.store_u64(self._pull_flag, 1)            # from the next optimizer kernel on, the replica is re-based on `_pulled`
                 self.pulls += 1
         peer.set_comm_max_blocks(0)
-        if pull_now and self.pull_lag == 0:
-            self._land_pull(force=True)
 
     # ------------------------------------------------------------------------------------------
     # the optimizer step
@@ -285,11 +270,11 @@ class Asynchronous(ArenaOptimizer):
         self.idx = st[1]
 
     def drain(self) -> None:
-        """Overlap mode: wait (stream-wise) for outstanding pushes and land a fetched pull, e.g. before evaluating or checkpointing."""
+        """Overlap mode: order the current stream behind outstanding pushes / fetches, e.g. before evaluating or checkpointing (a fetched
+        pull lands inside the next optimizer kernel)."""
         if not self.overlap:
             return
         torch.cuda.current_stream(self.arena.params.device).wait_stream(self.comm_stream)
-        self._land_pull(force=True)
 
     @torch.no_grad()
     def step_local(self) -> None:
@@ -300,7 +285,8 @@ class Asynchronous(ArenaOptimizer):
             from ..ops import kernels as K
             table = a.fused_shadow_table()
             K.sgd_flat_ex(a.params, a.grads, None if self.overlap else self.accumulated_gradients, self._acc_slot if self.overlap else None, None,
-                          a.padded, self.lr_dev, 0.0, 0.0, shadow=a.shadow, zero_grads=self.fused_zero_grad, table=table)
+                          a.padded, self.lr_dev, 0.0, 0.0, shadow=a.shadow, zero_grads=self.fused_zero_grad, table=table,
+                          pulled=self._pulled if self.overlap else None, pull_flag=self._pull_flag if self.overlap else None)
             a.mark_params_changed(flat_done=a.shadow is not None, table_done=table is not None)
         else:
             lr = self.lr

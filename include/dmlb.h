@@ -184,7 +184,10 @@ int dmlb_sgd_flat_slot(float* params, float* grads, void* acc_slot, float* mom, 
  * dmlb_refresh_shadows) refreshed by the same launch; [table_lo, table_hi) = element range of params that holds those weights. */
 int dmlb_sgd_flat_ex(float* params, float* grads, float* acc, void* acc_slot, float* mom, void* shadow_bf16, long long n, const float* lr_ptr,
                      float mu, float wd, int zero_grads, const void* table, int n_entries, int table_is_f32, long long table_lo,
-                     long long table_hi, void* stream);
+                     long long table_hi, const float* pulled, const void* pull_flag, void* stream);
+/* (pulled, pull_flag: while the device word *pull_flag is non-zero the replica is re-based on the fetched server parameters,
+ *  theta = pulled + accumulator — the landing of an overlapped pull, Asynchronous.py:17-18 — instead of theta -= lr * g.) */
+int dmlb_store_u64_u32(void* slot, unsigned long long value, void* flag, unsigned fvalue, void* stream);
 int dmlb_store_u64(void* slot, unsigned long long value, void* stream);   /* *slot = value, stream ordered */
 /* Landing of an overlapped pull (Asynchronous.py:17-18): params = pulled (+ *unpushed_slot), bf16 mirror refreshed in the same pass. */
 int dmlb_apply_pull(float* params, const float* pulled, void* unpushed_slot, void* shadow_bf16, long long n, void* stream);
