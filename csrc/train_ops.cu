@@ -157,9 +157,10 @@ __global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ param
     // fetched after this worker's last push, and the replica is re-based on them: theta = pulled + (updates not pushed yet) — the
     // accumulator, which already includes this step.  The flag is raised by the communication stream after the fetch and cleared by the
     // step stream at the next push; an element sees either value and is correct both ways (it lands now or at the next step).
-    const bool land = pull_flag != nullptr && *reinterpret_cast<const volatile unsigned*>(pull_flag) != 0u;
+    const bool land = pull_flag != nullptr && acc != nullptr && *reinterpret_cast<const volatile unsigned*>(pull_flag) != 0u;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
-        float4 p = reinterpret_cast<float4*>(params)[i];
+        // landing: the base is the fetched server value instead of the replica's (same traffic either way)
+        float4 p = land ? ld_stream_f32x4(pulled + 4 * i) : reinterpret_cast<float4*>(params)[i];
         float4 g = ld_stream_f32x4(grads + 4 * i);
         if (zero_grads) reinterpret_cast<float4*>(grads)[i] = make_float4(0.f, 0.f, 0.f, 0.f);  // next step starts clean: no memset node
         if (wd != 0.f) { g.x += wd * p.x; g.y += wd * p.y; g.z += wd * p.z; g.w += wd * p.w; }
@@ -169,24 +170,20 @@ __global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ param
             reinterpret_cast<float4*>(mom)[i] = v;
             g = v;
         }
-        if (land && acc != nullptr) {
-            const float4 a = reinterpret_cast<const float4*>(acc)[i];
-            const float4 s = ld_stream_f32x4(pulled + 4 * i);
-            p.x = s.x + (a.x - lr * g.x); p.y = s.y + (a.y - lr * g.y); p.z = s.z + (a.z - lr * g.z); p.w = s.w + (a.w - lr * g.w);
-        } else {
-            p.x -= lr * g.x; p.y -= lr * g.y; p.z -= lr * g.z; p.w -= lr * g.w;
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (acc != nullptr) {
+            a = reinterpret_cast<float4*>(acc)[i];
+            a.x -= lr * g.x; a.y -= lr * g.y; a.z -= lr * g.z; a.w -= lr * g.w;
+            reinterpret_cast<float4*>(acc)[i] = a;
         }
+        if (land) { p.x += a.x; p.y += a.y; p.z += a.z; p.w += a.w; }                 // server value + every update it has not seen
+        else      { p.x -= lr * g.x; p.y -= lr * g.y; p.z -= lr * g.z; p.w -= lr * g.w; }
         reinterpret_cast<float4*>(params)[i] = p;
         if (shadow != nullptr) {  // bf16 mirror for the tensor cores, same flat offsets
             uint2 h;
             h.x = pack_bf16x2(p.x, p.y);
             h.y = pack_bf16x2(p.z, p.w);
             reinterpret_cast<uint2*>(shadow)[i] = h;
-        }
-        if (acc != nullptr) {
-            float4 a = reinterpret_cast<float4*>(acc)[i];
-            a.x -= lr * g.x; a.y -= lr * g.y; a.z -= lr * g.z; a.w -= lr * g.w;
-            reinterpret_cast<float4*>(acc)[i] = a;
         }
         if (n_entries > 0 && 4 * i + 3 >= table_lo && 4 * i < table_hi) {      // [table_lo, table_hi): hull of the table-backed weights
             const float pv[4] = {p.x, p.y, p.z, p.w};

@@ -173,13 +173,12 @@ def _mgpu_async(rank, size, out_dir, steps, momentum):
     theta0 = opt.server_parameters().cpu().clone()
     local_sum = torch.zeros_like(opt.arena.flat_params())
     for i in range(steps):
-        before = opt.arena.flat_params().clone()
         x, y = _batch(100 * rank + i, dev=dev)
         opt.zero_grad()
         OF.cross_entropy(net(x), y).backward()
         opt._apply_pending()
-        opt.step_local()
-        local_sum += opt.arena.flat_params() - before      # this worker's -lr*g contribution
+        local_sum += opt.arena.flat_grads() * (-0.02)      # this worker's -lr*g contribution (the replica itself also moves when a
+        opt.step_local()                                   # fetched pull lands inside the optimizer kernel)
         opt.communicate()
     opt.finish()
     final = opt.server_parameters().cpu()
