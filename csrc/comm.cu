@@ -25,14 +25,24 @@ struct PeerTable {
 // Vector fp32 reductions (red.global.add.v4.f32, .sys scope) travel over NVLink and are applied by the
 // owner's L2; the worker never waits for an acknowledgement.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) push_add_kernel(float* __restrict__ acc, PeerTable masters, long long shard_size, long long n4) {
+// Delta form (live != nullptr): no accumulator is kept at all.  `acc` is then a SNAPSHOT of the replica as of the last push, the update to
+// send is live - snapshot (exact: both are the same fp32 variable at two times), and the snapshot is advanced to the value just read.
+// It is safe to run while training keeps writing `live`: each element is read once, so every local update is sent exactly once.
+__global__ void __launch_bounds__(256) push_add_kernel(float* __restrict__ acc, const float* __restrict__ live, PeerTable masters,
+                                                       long long shard_size, long long n4) {
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
         const long long e = i * 4;
         const int owner = static_cast<int>(e / shard_size);
         float* dst = static_cast<float*>(masters.ptr[owner]) + (e - owner * shard_size);
-        const float4 a = reinterpret_cast<float4*>(acc)[i];
+        float4 a = reinterpret_cast<float4*>(acc)[i];
+        if (live != nullptr) {
+            const float4 p = ld_volatile_f32x4(live + e);
+            reinterpret_cast<float4*>(acc)[i] = p;
+            a.x = p.x - a.x; a.y = p.y - a.y; a.z = p.z - a.z; a.w = p.w - a.w;
+        } else {
+            reinterpret_cast<float4*>(acc)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
         if (a.x != 0.f || a.y != 0.f || a.z != 0.f || a.w != 0.f) red_add_f32x4_sys(dst, a.x, a.y, a.z, a.w);
-        reinterpret_cast<float4*>(acc)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
 }
 
@@ -89,7 +99,7 @@ __global__ void __launch_bounds__(256) pull_kernel(float* __restrict__ params, _
 //   full   : owner's uint32 [world][cps]      (set remotely here, cleared by the owner)
 //   mailbox: owner's float  [world][shard_size]
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) push_mailbox_kernel(float* __restrict__ acc, uint32_t* __restrict__ busy,
+__global__ void __launch_bounds__(256) push_mailbox_kernel(float* __restrict__ acc, const float* __restrict__ live, uint32_t* __restrict__ busy,
                                                            const uint32_t* __restrict__ pulled_ver, PeerTable mailboxes, PeerTable fulls,
                                                            int rank, int world, long long shard_size, int cps) {
     __shared__ uint32_t s_busy;
@@ -103,9 +113,17 @@ __global__ void __launch_bounds__(256) push_mailbox_kernel(float* __restrict__ a
         const int owner = c / cps, lc = c % cps;
         float* src = acc + static_cast<long long>(owner) * shard_size + static_cast<long long>(lc) * kChunk;
         float* dst = static_cast<float*>(mailboxes.ptr[owner]) + static_cast<long long>(rank) * shard_size + static_cast<long long>(lc) * kChunk;
+        const float* lsrc = live != nullptr ? live + static_cast<long long>(owner) * shard_size + static_cast<long long>(lc) * kChunk : nullptr;
         for (int j = threadIdx.x; j < kChunk / 4; j += blockDim.x) {
-            reinterpret_cast<float4*>(dst)[j] = reinterpret_cast<float4*>(src)[j];
-            reinterpret_cast<float4*>(src)[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            float4 a = reinterpret_cast<float4*>(src)[j];
+            if (lsrc != nullptr) {            // delta form: send live - snapshot, advance the snapshot (see push_add_kernel)
+                const float4 p = ld_volatile_f32x4(lsrc + 4 * j);
+                reinterpret_cast<float4*>(src)[j] = p;
+                a.x = p.x - a.x; a.y = p.y - a.y; a.z = p.z - a.z; a.w = p.w - a.w;
+            } else {
+                reinterpret_cast<float4*>(src)[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            reinterpret_cast<float4*>(dst)[j] = a;
         }
         __syncthreads();
         if (threadIdx.x == 0) {
@@ -363,13 +381,25 @@ using namespace dmlb;
 extern "C" int dmlb_comm_chunk_elems() { return kChunk; }
 extern "C" int dmlb_comm_flag_words() { return 2 * kMaxPeers + 2; }
 
-extern "C" int dmlb_push_add(float* acc, void* const* master_ptrs, int world, long long shard_size, long long n, void* stream) {
+static int push_add_impl(float* acc, const float* live, void* const* master_ptrs, int world, long long shard_size, long long n, void* stream) {
     DMLB_REQUIRE(n % 4 == 0 && shard_size % 4 == 0, "lengths must be multiples of 4");
     PeerTable t;
     if (fill_table(&t, master_ptrs, world)) return -2;
-    push_add_kernel<<<comm_grid(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(acc, t, shard_size, n / 4);
+    push_add_kernel<<<comm_grid(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(acc, live, t, shard_size, n / 4);
     DMLB_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int dmlb_push_add(float* acc, void* const* master_ptrs, int world, long long shard_size, long long n, void* stream) {
+    return push_add_impl(acc, nullptr, master_ptrs, world, shard_size, n, stream);
+}
+
+// Delta push: master[owner][i] += live[i] - snapshot[i]; snapshot[i] = live[i].  The worker keeps no accumulator: what it has not pushed yet
+// is the difference between its replica and the snapshot (reference: accumulated_gradients, Asynchronous.py:27,55,58-60).
+extern "C" int dmlb_push_delta(const float* live, float* snapshot, void* const* master_ptrs, int world, long long shard_size, long long n,
+                               void* stream) {
+    DMLB_REQUIRE(live != nullptr && snapshot != nullptr, "live and snapshot are required");
+    return push_add_impl(snapshot, live, master_ptrs, world, shard_size, n, stream);
 }
 
 extern "C" int dmlb_pull(float* params, void* shadow_bf16, void* const* master_ptrs, void* const* version_ptrs, void* pulled_ver, int world,
@@ -390,8 +420,23 @@ extern "C" int dmlb_pull(float* params, void* shadow_bf16, void* const* master_p
     return 0;
 }
 
+static int push_mailbox_impl(float* acc, const float* live, void* busy, const void* pulled_ver, void* const* mailbox_ptrs, void* const* full_ptrs,
+                             int rank, int world, long long shard_size, void* stream);
+
 extern "C" int dmlb_push_mailbox(float* acc, void* busy, const void* pulled_ver, void* const* mailbox_ptrs, void* const* full_ptrs, int rank,
                                  int world, long long shard_size, void* stream) {
+    return push_mailbox_impl(acc, nullptr, busy, pulled_ver, mailbox_ptrs, full_ptrs, rank, world, shard_size, stream);
+}
+
+// Mailbox push in delta form (see dmlb_push_delta): chunks whose slot at the owner is busy are skipped and simply keep growing.
+extern "C" int dmlb_push_mailbox_delta(const float* live, float* snapshot, void* busy, const void* pulled_ver, void* const* mailbox_ptrs,
+                                       void* const* full_ptrs, int rank, int world, long long shard_size, void* stream) {
+    DMLB_REQUIRE(live != nullptr && snapshot != nullptr, "live and snapshot are required");
+    return push_mailbox_impl(snapshot, live, busy, pulled_ver, mailbox_ptrs, full_ptrs, rank, world, shard_size, stream);
+}
+
+static int push_mailbox_impl(float* acc, const float* live, void* busy, const void* pulled_ver, void* const* mailbox_ptrs, void* const* full_ptrs,
+                             int rank, int world, long long shard_size, void* stream) {
     DMLB_REQUIRE(shard_size % kChunk == 0, "shard size must be a multiple of the chunk size");
     PeerTable m, f;
     if (fill_table(&m, mailbox_ptrs, world) || fill_table(&f, full_ptrs, world)) return -2;
@@ -399,7 +444,7 @@ extern "C" int dmlb_push_mailbox(float* acc, void* busy, const void* pulled_ver,
     int blocks = world * cps;
     const int cap = dmlb_sm_count() * 4;
     if (blocks > cap) blocks = cap;
-    push_mailbox_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(acc, static_cast<uint32_t*>(busy),
+    push_mailbox_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(acc, live, static_cast<uint32_t*>(busy),
                                                                               static_cast<const uint32_t*>(pulled_ver), m, f, rank, world,
                                                                               shard_size, cps);
     DMLB_LAUNCH_CHECK();

@@ -141,26 +141,15 @@ __device__ __forceinline__ void scatter_to_shadows(const ShadowEntry* __restrict
     }
 }
 
-// acc_slot (may be null): device location holding the address of the CURRENT accumulator.  The asynchronous optimizer double-buffers
-// its accumulator so a gradient push can drain the retired buffer on a communication stream while the next steps already
-// accumulate into the other one; reading the address from memory lets a captured CUDA graph follow the swap.
-__global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ params, float* __restrict__ grads, float* __restrict__ acc_direct,
-                                                       float* const* __restrict__ acc_slot, float* __restrict__ mom,
-                                                       __nv_bfloat16* __restrict__ shadow, long long n4, const float* __restrict__ lr_ptr,
-                                                       float mu, float wd, int zero_grads, const ShadowEntry* __restrict__ table, int n_entries,
-                                                       int table_f32, long long table_lo, long long table_hi,
-                                                       const float* __restrict__ pulled, const unsigned* __restrict__ pull_flag) {
+__global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ params, float* __restrict__ grads, float* __restrict__ acc,
+                                                       float* __restrict__ mom, __nv_bfloat16* __restrict__ shadow, long long n4,
+                                                       const float* __restrict__ lr_ptr, float mu, float wd, int zero_grads,
+                                                       const ShadowEntry* __restrict__ table, int n_entries, int table_f32, long long table_lo,
+                                                       long long table_hi) {
     pdl_prologue();
     const float lr = *lr_ptr;
-    float* __restrict__ acc = acc_slot != nullptr ? *acc_slot : acc_direct;
-    // Landing of an overlapped parameter pull (asynchronous optimizer): while *pull_flag is set, `pulled` holds the server's parameters as
-    // fetched after this worker's last push, and the replica is re-based on them: theta = pulled + (updates not pushed yet) — the
-    // accumulator, which already includes this step.  The flag is raised by the communication stream after the fetch and cleared by the
-    // step stream at the next push; an element sees either value and is correct both ways (it lands now or at the next step).
-    const bool land = pull_flag != nullptr && acc != nullptr && *reinterpret_cast<const volatile unsigned*>(pull_flag) != 0u;
     for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
-        // landing: the base is the fetched server value instead of the replica's (same traffic either way)
-        float4 p = land ? ld_stream_f32x4(pulled + 4 * i) : reinterpret_cast<float4*>(params)[i];
+        float4 p = reinterpret_cast<float4*>(params)[i];
         float4 g = ld_stream_f32x4(grads + 4 * i);
         if (zero_grads) reinterpret_cast<float4*>(grads)[i] = make_float4(0.f, 0.f, 0.f, 0.f);  // next step starts clean: no memset node
         if (wd != 0.f) { g.x += wd * p.x; g.y += wd * p.y; g.z += wd * p.z; g.w += wd * p.w; }
@@ -170,14 +159,12 @@ __global__ void __launch_bounds__(256) sgd_flat_kernel(float* __restrict__ param
             reinterpret_cast<float4*>(mom)[i] = v;
             g = v;
         }
-        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
         if (acc != nullptr) {
-            a = reinterpret_cast<float4*>(acc)[i];
+            float4 a = reinterpret_cast<float4*>(acc)[i];
             a.x -= lr * g.x; a.y -= lr * g.y; a.z -= lr * g.z; a.w -= lr * g.w;
             reinterpret_cast<float4*>(acc)[i] = a;
         }
-        if (land) { p.x += a.x; p.y += a.y; p.z += a.z; p.w += a.w; }                 // server value + every update it has not seen
-        else      { p.x -= lr * g.x; p.y -= lr * g.y; p.z -= lr * g.z; p.w -= lr * g.w; }
+        p.x -= lr * g.x; p.y -= lr * g.y; p.z -= lr * g.z; p.w -= lr * g.w;
         reinterpret_cast<float4*>(params)[i] = p;
         if (shadow != nullptr) {  // bf16 mirror for the tensor cores, same flat offsets
             uint2 h;
@@ -352,32 +339,24 @@ extern "C" int dmlb_scale_rows_f32(void* x, const float* scale, long long rows, 
     return 0;
 }
 
-// Everything dmlb_sgd_flat / dmlb_sgd_flat_slot do, plus the table-backed weight shadows (dmlb_refresh_shadows' table with ABSOLUTE addresses:
-// src_off / dst_off = address / element size) refreshed by the same launch.  [table_lo, table_hi) is the element range of the arena
-// (relative to params) that holds those weights.
-extern "C" int dmlb_sgd_flat_ex(float* params, float* grads, float* acc, void* acc_slot, float* mom, void* shadow, long long n, const float* lr_ptr,
-                                float mu, float wd, int zero_grads, const void* table, int n_entries, int table_is_f32, long long table_lo,
-                                long long table_hi, const float* pulled, const void* pull_flag, void* stream) {
+// dmlb_sgd_flat plus the table-backed weight shadows (dmlb_refresh_shadows' table with ABSOLUTE addresses: src_off / dst_off = address /
+// element size) refreshed by the same launch.  [table_lo, table_hi) is the element range of the arena (relative to params) that holds
+// those weights.
+extern "C" int dmlb_sgd_flat_ex(float* params, float* grads, float* acc, float* mom, void* shadow, long long n, const float* lr_ptr, float mu,
+                                float wd, int zero_grads, const void* table, int n_entries, int table_is_f32, long long table_lo,
+                                long long table_hi, void* stream) {
     DMLB_REQUIRE(n % 4 == 0, "flat SGD length must be a multiple of 4 (arena padding)");
     DMLB_REQUIRE(((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads)) & 15) == 0, "arena must be 16-byte aligned");
-    DMLB_CHECK_CUDA(launch_k(sgd_flat_kernel, flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream), params, grads, acc,
-                             static_cast<float* const*>(acc_slot), mom, static_cast<__nv_bfloat16*>(shadow), n / 4, lr_ptr, mu, wd, zero_grads,
-                             static_cast<const ShadowEntry*>(table), table != nullptr ? n_entries : 0, table_is_f32, table_lo, table_hi, pulled,
-                             static_cast<const unsigned*>(pull_flag)));
+    DMLB_CHECK_CUDA(launch_k(sgd_flat_kernel, flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream), params, grads, acc, mom,
+                             static_cast<__nv_bfloat16*>(shadow), n / 4, lr_ptr, mu, wd, zero_grads, static_cast<const ShadowEntry*>(table),
+                             table != nullptr ? n_entries : 0, table_is_f32, table_lo, table_hi));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
 
 extern "C" int dmlb_sgd_flat(float* params, float* grads, float* acc, float* mom, void* shadow, long long n, const float* lr_ptr, float mu,
                              float wd, int zero_grads, void* stream) {
-    return dmlb_sgd_flat_ex(params, grads, acc, nullptr, mom, shadow, n, lr_ptr, mu, wd, zero_grads, nullptr, 0, 0, 0, 0, nullptr, nullptr, stream);
-}
-
-// dmlb_sgd_flat with the accumulator named indirectly: *acc_slot (device memory) is the buffer to accumulate -lr*g into.
-extern "C" int dmlb_sgd_flat_slot(float* params, float* grads, void* acc_slot, float* mom, void* shadow, long long n, const float* lr_ptr, float mu,
-                                  float wd, int zero_grads, void* stream) {
-    DMLB_REQUIRE(acc_slot != nullptr, "acc_slot is required (use dmlb_sgd_flat for a direct accumulator)");
-    return dmlb_sgd_flat_ex(params, grads, nullptr, acc_slot, mom, shadow, n, lr_ptr, mu, wd, zero_grads, nullptr, 0, 0, 0, 0, nullptr, nullptr, stream);
+    return dmlb_sgd_flat_ex(params, grads, acc, mom, shadow, n, lr_ptr, mu, wd, zero_grads, nullptr, 0, 0, 0, 0, stream);
 }
 
 namespace dmlb {
@@ -402,32 +381,6 @@ __global__ void __launch_bounds__(256) nchw_to_act_kernel(const float* __restric
     }
 }
 
-__global__ void store_u64_kernel(unsigned long long* slot, unsigned long long value) { *slot = value; }
-__global__ void store_u64_u32_kernel(unsigned long long* slot, unsigned long long value, unsigned* flag, unsigned fvalue) {
-    *slot = value;
-    *flag = fvalue;
-}
-
-// params = pulled + unpushed;  shadow = bf16(params)   (n4 float4 groups; unpushed / shadow may be null)
-__global__ void __launch_bounds__(256) apply_pull_kernel(float* __restrict__ params, const float* __restrict__ pulled,
-                                                         float* const* __restrict__ unpushed_slot, __nv_bfloat16* __restrict__ shadow, long long n4) {
-    pdl_prologue();
-    const float* __restrict__ unpushed = unpushed_slot != nullptr ? *unpushed_slot : nullptr;
-    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
-        float4 p = ld_stream_f32x4(pulled + 4 * i);
-        if (unpushed != nullptr) {
-            const float4 a = reinterpret_cast<const float4*>(unpushed)[i];
-            p.x += a.x; p.y += a.y; p.z += a.z; p.w += a.w;
-        }
-        reinterpret_cast<float4*>(params)[i] = p;
-        if (shadow != nullptr) {
-            uint2 h;
-            h.x = pack_bf16x2(p.x, p.y);
-            h.y = pack_bf16x2(p.z, p.w);
-            reinterpret_cast<uint2*>(shadow)[i] = h;
-        }
-    }
-}
 }  // namespace dmlb
 
 template <typename T>
@@ -447,32 +400,39 @@ extern "C" int dmlb_nchw_to_act_f32(const float* x, void* y, int B, int C, int H
     return nchw_to_act_t<float>(x, y, B, C, H, W, hp, wp, ph, pw, stream);
 }
 
-// *slot = value on the stream (8 bytes of device memory): how the host retargets dmlb_sgd_flat_slot / dmlb_apply_pull between replays.
-extern "C" int dmlb_store_u64(void* slot, unsigned long long value, void* stream) {
-    DMLB_REQUIRE(slot != nullptr && (reinterpret_cast<uintptr_t>(slot) & 7) == 0, "slot must be an 8-byte aligned device address");
-    DMLB_CHECK_CUDA(launch_k(store_u64_kernel, 1, 1, 0, static_cast<cudaStream_t>(stream), static_cast<unsigned long long*>(slot), value));
+namespace dmlb {
+// params = pulled + (params - snapshot);  snapshot = pulled;  shadow = bf16(params)
+__global__ void __launch_bounds__(256) land_pull_kernel(float* __restrict__ params, const float* __restrict__ pulled, float* __restrict__ snapshot,
+                                                        __nv_bfloat16* __restrict__ shadow, long long n4) {
+    pdl_prologue();
+    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
+        const float4 s = ld_stream_f32x4(pulled + 4 * i);
+        const float4 q = reinterpret_cast<const float4*>(snapshot)[i];
+        float4 p = reinterpret_cast<const float4*>(params)[i];
+        p.x = s.x + (p.x - q.x); p.y = s.y + (p.y - q.y); p.z = s.z + (p.z - q.z); p.w = s.w + (p.w - q.w);
+        reinterpret_cast<float4*>(params)[i] = p;
+        reinterpret_cast<float4*>(snapshot)[i] = s;
+        if (shadow != nullptr) {
+            uint2 h;
+            h.x = pack_bf16x2(p.x, p.y);
+            h.y = pack_bf16x2(p.z, p.w);
+            reinterpret_cast<uint2*>(shadow)[i] = h;
+        }
+    }
+}
+}  // namespace dmlb
+
+// Landing of a fetched pull in the delta scheme (see dmlb_push_delta): the replica is re-based on the server's parameters while keeping
+// exactly the local updates the server has not seen, params = pulled + (params - snapshot), and the snapshot becomes the server value.
+// Reference: the listener overwrites the model with the server's reply (Asynchronous.py:17-18) and thereby drops those updates from the replica.
+extern "C" int dmlb_land_pull(float* params, const float* pulled, float* snapshot, void* shadow_bf16, long long n, void* stream) {
+    DMLB_REQUIRE(n % 4 == 0 && params != nullptr && pulled != nullptr && snapshot != nullptr, "bad arguments");
+    DMLB_CHECK_CUDA(launch_k(land_pull_kernel, flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream), params, pulled, snapshot,
+                             static_cast<__nv_bfloat16*>(shadow_bf16), n / 4));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
 
-// *slot = value and *flag = fvalue in one launch (accumulator switch + "no pull to land" at a push).
-extern "C" int dmlb_store_u64_u32(void* slot, unsigned long long value, void* flag, unsigned fvalue, void* stream) {
-    DMLB_REQUIRE(slot != nullptr && flag != nullptr, "null destination");
-    DMLB_CHECK_CUDA(launch_k(store_u64_u32_kernel, 1, 1, 0, static_cast<cudaStream_t>(stream), static_cast<unsigned long long*>(slot), value,
-                             static_cast<unsigned*>(flag), fvalue));
-    DMLB_LAUNCH_CHECK();
-    return 0;
-}
-
-// Landing of an overlapped parameter pull (reference Asynchronous.py:17-18: the listener overwrites the model with the server's reply):
-// params = pulled (+ *unpushed_slot, the worker's updates the server has not seen yet), fused with the cast into the bf16 mirror.
-extern "C" int dmlb_apply_pull(float* params, const float* pulled, void* unpushed_slot, void* shadow_bf16, long long n, void* stream) {
-    DMLB_REQUIRE(n % 4 == 0, "length must be a multiple of 4");
-    DMLB_CHECK_CUDA(launch_k(apply_pull_kernel, flat_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream), params, pulled,
-                             static_cast<float* const*>(unpushed_slot), static_cast<__nv_bfloat16*>(shadow_bf16), n / 4));
-    DMLB_LAUNCH_CHECK();
-    return 0;
-}
 
 // table: device array of n_entries ShadowEntry {int64 src_off, int64 dst_off, int32 rows, cin, khw, ld, cpad, src_gemm_order}.
 extern "C" int dmlb_refresh_shadows(const float* params, void* shadow, const void* table, int n_entries, void* stream) {

@@ -86,11 +86,8 @@ _SIGNATURES = {
                                         c_int, c_int, c_vp],
     # (ws, ldw, y, dy, ldy, dbias, B, Hx, Wx, C, pool2, relu, is_f32, stream)
     "dmlb_splitk_finish_actbwd": [c_vp, c_int, c_vp, c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_vp],
-    "dmlb_sgd_flat_slot": [c_vp, c_vp, c_vp, c_vp, c_vp, c_ll, c_vp, c_float, c_float, c_int, c_vp],
-    "dmlb_sgd_flat_ex": [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_ll, c_vp, c_float, c_float, c_int, c_vp, c_int, c_int, c_ll, c_ll, c_vp, c_vp, c_vp],
-    "dmlb_store_u64_u32": [c_vp, c_ull, c_vp, ctypes.c_uint, c_vp],
-    "dmlb_store_u64": [c_vp, c_ull, c_vp],
-    "dmlb_apply_pull": [c_vp, c_vp, c_vp, c_vp, c_ll, c_vp],
+    "dmlb_sgd_flat_ex": [c_vp, c_vp, c_vp, c_vp, c_vp, c_ll, c_vp, c_float, c_float, c_int, c_vp, c_int, c_int, c_ll, c_ll, c_vp],
+    "dmlb_land_pull": [c_vp, c_vp, c_vp, c_vp, c_ll, c_vp],
     # ---- tf32 path: fp32 tensors, tcgen05 kind::tf32 ----
     # (A, lda, a_mn, B, ldb, b_mn, M, N, K, out, ldo, bias, relu, split_k, atomic, perm_cin, perm_khw, tile_n, stream)
     "dmlb_gemm_tf32": [c_vp, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int,

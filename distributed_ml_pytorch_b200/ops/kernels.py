@@ -336,36 +336,20 @@ def sgd_flat(params: torch.Tensor, grads: torch.Tensor, acc, mom, n: int, lr_dev
           float(wd), int(zero_grads), stream_ptr())
 
 
-def sgd_flat_slot(params: torch.Tensor, grads: torch.Tensor, acc_slot: torch.Tensor, mom, n: int, lr_dev: torch.Tensor, mu: float = 0.0,
-                  wd: float = 0.0, shadow=None, zero_grads: bool = False) -> None:
-    """:func:`sgd_flat` accumulating into the buffer whose address is stored in ``acc_slot`` (int64 device tensor)."""
-    _call("dmlb_sgd_flat_slot", params.data_ptr(), grads.data_ptr(), acc_slot.data_ptr(), mom.data_ptr() if mom is not None else None,
-          shadow.data_ptr() if shadow is not None else None, n, lr_dev.data_ptr(), float(mu), float(wd), int(zero_grads), stream_ptr())
-
-
-def sgd_flat_ex(params: torch.Tensor, grads: torch.Tensor, acc, acc_slot, mom, n: int, lr_dev: torch.Tensor, mu: float = 0.0, wd: float = 0.0,
-                shadow=None, zero_grads: bool = False, table=None, pulled=None, pull_flag=None) -> None:
-    """:func:`sgd_flat` / :func:`sgd_flat_slot` in one entry point, optionally refreshing the table-backed weight shadows in the same
-    launch: ``table = (device uint8 table, n_entries, dtype of the shadows, lo, hi)`` from ``ShadowSet.fused_table()``."""
+def sgd_flat_ex(params: torch.Tensor, grads: torch.Tensor, acc, mom, n: int, lr_dev: torch.Tensor, mu: float = 0.0, wd: float = 0.0,
+                shadow=None, zero_grads: bool = False, table=None) -> None:
+    """:func:`sgd_flat`, optionally refreshing the table-backed weight shadows in the same launch:
+    ``table = (device uint8 table, n_entries, dtype of the shadows, lo, hi)`` from ``ShadowSet.fused_table()``."""
     tptr, tn, tf32, lo, hi = (table[0].data_ptr(), table[1], int(table[2] == torch.float32), table[3], table[4]) if table else (None, 0, 0, 0, 0)
     _call("dmlb_sgd_flat_ex", params.data_ptr(), grads.data_ptr(), acc.data_ptr() if acc is not None else None,
-          acc_slot.data_ptr() if acc_slot is not None else None, mom.data_ptr() if mom is not None else None,
-          shadow.data_ptr() if shadow is not None else None, n, lr_dev.data_ptr(), float(mu), float(wd), int(zero_grads), tptr, tn, tf32, lo, hi,
-          pulled.data_ptr() if pulled is not None else None, pull_flag.data_ptr() if pull_flag is not None else None, stream_ptr())
+          mom.data_ptr() if mom is not None else None, shadow.data_ptr() if shadow is not None else None, n, lr_dev.data_ptr(), float(mu),
+          float(wd), int(zero_grads), tptr, tn, tf32, lo, hi, stream_ptr())
 
 
-def store_u64_u32(slot: torch.Tensor, value: int, flag: torch.Tensor, fvalue: int) -> None:
-    _call("dmlb_store_u64_u32", slot.data_ptr(), int(value), flag.data_ptr(), int(fvalue), stream_ptr())
-
-
-def store_u64(slot: torch.Tensor, value: int) -> None:
-    _call("dmlb_store_u64", slot.data_ptr(), int(value), stream_ptr())
-
-
-def apply_pull(params: torch.Tensor, pulled: torch.Tensor, unpushed_slot, shadow, n: int) -> None:
-    """``params = pulled (+ *unpushed_slot)``, bf16 mirror refreshed in the same pass (``dmlb_apply_pull``)."""
-    _call("dmlb_apply_pull", params.data_ptr(), pulled.data_ptr(), unpushed_slot.data_ptr() if unpushed_slot is not None else None,
-          shadow.data_ptr() if shadow is not None else None, n, stream_ptr())
+def land_pull(params: torch.Tensor, pulled: torch.Tensor, snapshot: torch.Tensor, shadow, n: int) -> None:
+    """``params = pulled + (params - snapshot); snapshot = pulled``, bf16 mirror refreshed in the same pass (``dmlb_land_pull``)."""
+    _call("dmlb_land_pull", params.data_ptr(), pulled.data_ptr(), snapshot.data_ptr(), shadow.data_ptr() if shadow is not None else None, n,
+          stream_ptr())
 
 
 def refresh_shadows(table: torch.Tensor, n_entries: int, dt=torch.bfloat16) -> None:

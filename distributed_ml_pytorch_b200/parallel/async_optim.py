@@ -24,12 +24,14 @@ the reference's behaviour on the gloo transport); a pull request carries no payl
 uploads the initial parameters.
 
 Overlap on the peer transport (``overlap=True``, the default): pushes, owner-side applies and pulls run on a communication stream
-while the worker keeps training.  The accumulator is double-buffered — at a push the training step switches to the other buffer (its
-address is read from device memory, so a captured CUDA graph follows the switch) and the push drains the retired one over NVLink — and a
-pull is fetched into a staging buffer and raises a device flag when it is complete; while the flag is up the (captured) optimizer
-kernel re-bases the replica on it, ``params = pulled + unpushed local updates``, instead of ``params -= lr * grad`` — the pull *lands*
-at a step boundary inside a kernel that runs anyway.  The step stream never waits for NVLink: per communication round it runs one
-12-byte store (accumulator switch + flag reset).
+while the worker keeps training, and the worker keeps NO accumulator.  What a worker has not pushed yet is, by definition, the
+difference between its replica and the replica as of its last push, so the worker keeps a *snapshot* instead: a push sends
+``params - snapshot`` (exact in fp32: the same variable at two times) and advances the snapshot to the value it read — element by
+element, so it may run while training keeps writing ``params`` and every local update is still sent exactly once.  The training step
+is then the plain fused SGD kernel (no accumulator read + write: 2 x 4 bytes per parameter per step saved, and nothing to switch inside
+a captured CUDA graph).  A pull is fetched into a staging buffer; ``pull_lag`` steps later one kernel on the step stream lands it,
+``params = pulled + (params - snapshot); snapshot = pulled`` — the server's parameters plus exactly the local updates the server has
+not seen.  ``accumulated_gradients`` (the reference's attribute) is computed on demand in this mode.
 """
 from __future__ import annotations
 
@@ -129,7 +131,8 @@ class Asynchronous(ArenaOptimizer):
             arena = FlatArena(model, n_shards=self.peer.world, align=self._chunk)   # shards are whole mailbox chunks
         super().__init__(params, dict(lr=lr), model, arena=arena)
         a = self.arena
-        self.accumulated_gradients = torch.zeros(a.padded, dtype=torch.float32, device=a.params.device)
+        self._snapshot = None
+        self._acc_buf = None if self.overlap else torch.zeros(a.padded, dtype=torch.float32, device=a.params.device)
 
         if transport == "peer":
             self._init_peer()
@@ -185,26 +188,39 @@ class Asynchronous(ArenaOptimizer):
             self.master_mom = torch.zeros(S, dtype=torch.float32, device=a.params.device) if self.server_momentum else None
         if self.overlap:
             dev = a.params.device
-            self._acc = [self.accumulated_gradients, torch.zeros_like(self.accumulated_gradients)]
-            self._acc_cur = 0
-            self._acc_slot = torch.tensor([self._acc[0].data_ptr()], dtype=torch.int64, device=dev)
             self._pulled = torch.empty_like(a.params)
-            self._pull_flag = torch.zeros(1, dtype=torch.int64, device=dev)     # != 0: `_pulled` is complete and not yet superseded
+            self._pending_pull = None
             self.comm_stream = torch.cuda.Stream(device=dev)
-            self._push_done = [None, None]
         pg.barrier()
         self._pull()                                           # every replica starts from the server's parameters
+        if self.overlap:
+            self._snapshot = a.params.clone()                  # nothing unpushed yet
         torch.cuda.synchronize(a.params.device)
         pg.barrier()
 
-    def _push(self, acc: Optional[torch.Tensor] = None) -> None:
+    @property
+    def accumulated_gradients(self) -> torch.Tensor:
+        """The update this worker has not pushed yet, ``sum(-lr * grad)`` since the last push (reference Asynchronous.py:27,55).  In
+        overlap mode it is not stored: it is the replica minus its snapshot (a fresh tensor, ordered behind outstanding pushes)."""
+        if self._snapshot is None:
+            return self._acc_buf
+        a = self.arena
+        torch.cuda.current_stream(a.params.device).wait_stream(self.comm_stream)
+        return a.params - self._snapshot
+
+    def _push(self) -> None:
         from . import peer
         pg, a = self.peer, self.arena
-        acc = acc if acc is not None else self.accumulated_gradients
-        if self._use_mailbox:
-            peer.push_mailbox(acc, self.busy, self.pulled_ver, self.mailbox_sym.table, self.full_sym.table, pg.rank, pg.world, a.shards.shard_size)
+        S = a.shards.shard_size
+        if self.overlap and self._use_mailbox:
+            peer.push_mailbox_delta(a.params, self._snapshot, self.busy, self.pulled_ver, self.mailbox_sym.table, self.full_sym.table, pg.rank,
+                                    pg.world, S)
+        elif self.overlap:
+            peer.push_delta(a.params, self._snapshot, self.master_sym.table, pg.world, S, a.padded)
+        elif self._use_mailbox:
+            peer.push_mailbox(self._acc_buf, self.busy, self.pulled_ver, self.mailbox_sym.table, self.full_sym.table, pg.rank, pg.world, S)
         else:
-            peer.push_add(acc, self.master_sym.table, pg.world, a.shards.shard_size, a.padded)
+            peer.push_add(self._acc_buf, self.master_sym.table, pg.world, S, a.padded)
         self.pushes += 1
 
     def _owner_apply(self) -> None:
@@ -216,65 +232,87 @@ class Asynchronous(ArenaOptimizer):
     def _pull(self) -> None:
         from . import peer
         pg, a = self.peer, self.arena
-        peer.pull(a.params, self.master_sym.table, pg.world, a.shards.shard_size, a.padded, self.version_sym.table, self.pulled_ver,
-                  shadow=a.shadow)
+        if self._snapshot is not None:      # delta scheme: fetch, then re-base the replica (keeps what has not been pushed)
+            from ..ops import kernels as K
+            peer.pull(self._pulled, self.master_sym.table, pg.world, a.shards.shard_size, a.padded, self.version_sym.table, self.pulled_ver)
+            K.land_pull(a.params, self._pulled, self._snapshot, a.shadow, a.padded)
+        else:
+            peer.pull(a.params, self.master_sym.table, pg.world, a.shards.shard_size, a.padded, self.version_sym.table, self.pulled_ver,
+                      shadow=a.shadow)
         a.mark_params_changed(flat_done=a.shadow is not None)
         self.pulls += 1
 
+    def set_unpushed(self, update: torch.Tensor) -> None:
+        """Restore the not-yet-pushed update (``accumulated_gradients``), e.g. from a checkpoint."""
+        if self._snapshot is None:
+            if update is not self._acc_buf:
+                self._acc_buf.copy_(update)
+        else:
+            a = self.arena
+            torch.cuda.current_stream(a.params.device).wait_stream(self.comm_stream)
+            torch.sub(a.params, update, out=self._snapshot)
+
+    def _land_pull(self, force: bool = False) -> None:
+        """Overlap mode: make a fetched pull the model's parameters (on the current stream, at a step boundary)."""
+        pp = self._pending_pull
+        if pp is None or (not force and self.idx - pp[0] < self.pull_lag):
+            return
+        from ..ops import kernels as K
+        a = self.arena
+        cur = torch.cuda.current_stream(a.params.device)
+        cur.wait_event(pp[1])                                  # fetched `pull_lag` steps ago: no wait in practice
+        # the server's parameters + the local updates it has not seen (replica - snapshot): what a pull that had landed the moment it
+        # was issued, followed by the local steps since, would have produced
+        K.land_pull(a.params, self._pulled, self._snapshot, a.shadow, a.padded)
+        a.mark_params_changed(flat_done=a.shadow is not None)
+        self._pending_pull = None
+
     def _communicate_overlapped(self, push_now: bool, pull_now: bool) -> None:
         from . import peer
-        from ..ops import kernels as K
         pg, a = self.peer, self.arena
-        dev = a.params.device
-        cur = torch.cuda.current_stream(dev)
+        cur = torch.cuda.current_stream(a.params.device)
+        self._land_pull()
         if not (push_now or pull_now or self._use_mailbox):
             return
-        retired = None
-        if push_now or pull_now:
-            nxt = self._acc_cur
-            if push_now:
-                retired, nxt = self._acc_cur, self._acc_cur ^ 1
-                if self._push_done[nxt] is not None:
-                    cur.wait_event(self._push_done[nxt])       # drained n_push steps ago: no wait in practice
-            # one tiny kernel on the step stream: switch the accumulator (push) and take the landing flag down — the staging buffer
-            # is about to be overwritten (pull) and / or its contents are about to be superseded by this push
-            K.store_u64_u32(self._acc_slot, self._acc[nxt].data_ptr(), self._pull_flag, 0)
-            self._acc_cur = nxt
-            self.accumulated_gradients = self._acc[nxt]
+        if pull_now:
+            self._land_pull(force=True)                        # the staging buffer is about to be overwritten
         ready = torch.cuda.Event()
         ready.record(cur)
-        self.comm_stream.wait_event(ready)
-        peer.set_comm_max_blocks(self.comm_blocks)       # background transfer: leave the SMs to the training step
+        self.comm_stream.wait_event(ready)                     # behind this step's update and behind a landing (both touch the snapshot)
+        peer.set_comm_max_blocks(self.comm_blocks)             # background transfer: leave the SMs to the training step
         with torch.cuda.stream(self.comm_stream):
             if push_now:
-                self._push(self._acc[retired])
-                done = torch.cuda.Event()
-                done.record(self.comm_stream)
-                self._push_done[retired] = done
+                self._push()
             if self._use_mailbox:
                 self._owner_apply()
             if pull_now:
                 peer.pull(self._pulled, self.master_sym.table, pg.world, a.shards.shard_size, a.padded, self.version_sym.table, self.pulled_ver)
-                K.store_u64(self._pull_flag, 1)            # from the next optimizer kernel on, the replica is re-based on `_pulled`
+                fetched = torch.cuda.Event()
+                fetched.record(self.comm_stream)
+                self._pending_pull = (self.idx, fetched)
                 self.pulls += 1
         peer.set_comm_max_blocks(0)
+        if pull_now and self.pull_lag == 0:
+            self._land_pull(force=True)
 
     # ------------------------------------------------------------------------------------------
     # the optimizer step
     # ------------------------------------------------------------------------------------------
     def capture_state(self):
-        return (self.accumulated_gradients.clone(), self.idx)
+        """State a dry run of ``step_local`` changes besides the parameters (``engine.TrainStep`` warms up and captures with it)."""
+        return (self._acc_buf.clone() if self._acc_buf is not None else None, self.idx)
 
     def restore_state(self, st) -> None:
-        self.accumulated_gradients.copy_(st[0])
+        if st[0] is not None:
+            self._acc_buf.copy_(st[0])        # overlap mode: the unpushed update is params - snapshot; restoring params restores it
         self.idx = st[1]
 
     def drain(self) -> None:
-        """Overlap mode: order the current stream behind outstanding pushes / fetches, e.g. before evaluating or checkpointing (a fetched
-        pull lands inside the next optimizer kernel)."""
+        """Overlap mode: wait (stream-wise) for outstanding pushes and land a fetched pull, e.g. before evaluating or checkpointing."""
         if not self.overlap:
             return
         torch.cuda.current_stream(self.arena.params.device).wait_stream(self.comm_stream)
+        self._land_pull(force=True)
 
     @torch.no_grad()
     def step_local(self) -> None:
@@ -284,13 +322,12 @@ class Asynchronous(ArenaOptimizer):
         if a.params.is_cuda:
             from ..ops import kernels as K
             table = a.fused_shadow_table()
-            K.sgd_flat_ex(a.params, a.grads, None if self.overlap else self.accumulated_gradients, self._acc_slot if self.overlap else None, None,
-                          a.padded, self.lr_dev, 0.0, 0.0, shadow=a.shadow, zero_grads=self.fused_zero_grad, table=table,
-                          pulled=self._pulled if self.overlap else None, pull_flag=self._pull_flag if self.overlap else None)
+            K.sgd_flat_ex(a.params, a.grads, self._acc_buf, None, a.padded, self.lr_dev, 0.0, 0.0, shadow=a.shadow,
+                          zero_grads=self.fused_zero_grad, table=table)
             a.mark_params_changed(flat_done=a.shadow is not None, table_done=table is not None)
         else:
             lr = self.lr
-            self.accumulated_gradients.add_(a.grads, alpha=-lr)
+            self._acc_buf.add_(a.grads, alpha=-lr)
             a.params.add_(a.grads, alpha=-lr)
 
     @torch.no_grad()
@@ -312,8 +349,8 @@ class Asynchronous(ArenaOptimizer):
                 with trace.span("push", "comm", step=self.idx, floats=self.arena.numel):
                     for k, r in enumerate(self.server_ranks):
                         b, e = self._srv_shards.valid_bounds(k)
-                        send_message(MessageCode.GradientUpdate, self.accumulated_gradients[b:e], dst=r)
-                    self.accumulated_gradients.zero_()
+                        send_message(MessageCode.GradientUpdate, self._acc_buf[b:e], dst=r)
+                    self._acc_buf.zero_()
                 self.pushes += 1
             if pull_now:
                 with trace.span("pull request", "comm", step=self.idx, blocking=self.blocking_pull):
@@ -329,8 +366,8 @@ class Asynchronous(ArenaOptimizer):
                         self._apply_pending()
         else:
             if push_now:
-                self._local_server_apply(self.accumulated_gradients)
-                self.accumulated_gradients.zero_()
+                self._local_server_apply(self._acc_buf)
+                self._acc_buf.zero_()
                 self.pushes += 1
             if pull_now:
                 self.arena.params.copy_(self._master)

@@ -90,7 +90,7 @@ class FusedSGD(ArenaOptimizer):
         if a.params.is_cuda:
             from ..ops import kernels as K
             table = a.fused_shadow_table()
-            K.sgd_flat_ex(a.params, a.grads, None, None, self.momentum_buf, a.padded, self.lr_dev, g["momentum"], g["weight_decay"],
+            K.sgd_flat_ex(a.params, a.grads, None, self.momentum_buf, a.padded, self.lr_dev, g["momentum"], g["weight_decay"],
                           shadow=a.shadow, zero_grads=self.fused_zero_grad, table=table)
             a.mark_params_changed(flat_done=a.shadow is not None, table_done=table is not None)
         else:

@@ -31,6 +31,8 @@ _native.register("dmlb_comm_chunk_elems", [])
 _native.register("dmlb_comm_flag_words", [])
 _native.register("dmlb_push_add", [c_vp, _PP, c_int, c_ll, c_ll, c_vp])
 _native.register("dmlb_pull", [c_vp, c_vp, _PP, _PP, c_vp, c_int, c_ll, c_ll, c_vp])
+_native.register("dmlb_push_delta", [c_vp, c_vp, _PP, c_int, c_ll, c_ll, c_vp])
+_native.register("dmlb_push_mailbox_delta", [c_vp, c_vp, c_vp, c_vp, _PP, _PP, c_int, c_int, c_ll, c_vp])
 _native.register("dmlb_push_mailbox", [c_vp, c_vp, c_vp, _PP, _PP, c_int, c_int, c_ll, c_vp])
 _native.register("dmlb_owner_apply", [c_vp, c_vp, c_vp, c_vp, c_vp, _PP, c_vp, c_int, c_int, c_ll, c_float, c_int, c_float, c_vp])
 _native.register("dmlb_sync_rs_update_ag", [_PP, _PP, _PP, c_vp, c_int, c_int, c_ll, c_vp, c_float, c_float, c_float, c_vp])
@@ -166,6 +168,16 @@ def pull(params: torch.Tensor, master_table, world: int, shard_size: int, n: int
          shadow: Optional[torch.Tensor] = None) -> None:
     _native.call("dmlb_pull", params.data_ptr(), shadow.data_ptr() if shadow is not None else None, master_table, version_table, pulled_ver.data_ptr() if pulled_ver is not None else None, world,
                  shard_size, n, _stream())
+
+
+def push_delta(live: torch.Tensor, snapshot: torch.Tensor, master_table, world: int, shard_size: int, n: int) -> None:
+    """``master[owner] += live - snapshot; snapshot = live`` (``dmlb_push_delta``): the accumulator-free push."""
+    _native.call("dmlb_push_delta", live.data_ptr(), snapshot.data_ptr(), master_table, world, shard_size, n, _stream())
+
+
+def push_mailbox_delta(live, snapshot, busy, pulled_ver, mailbox_table, full_table, rank, world, shard_size) -> None:
+    _native.call("dmlb_push_mailbox_delta", live.data_ptr(), snapshot.data_ptr(), busy.data_ptr(), pulled_ver.data_ptr(), mailbox_table,
+                 full_table, rank, world, shard_size, _stream())
 
 
 def push_mailbox(acc, busy, pulled_ver, mailbox_table, full_table, rank, world, shard_size) -> None:

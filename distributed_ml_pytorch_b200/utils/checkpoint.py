@@ -127,6 +127,8 @@ def load_optimizer_state(optimizer, ost) -> None:
                 raise ValueError(f"checkpoint {key} was written in a device-specific arena layout (format v1); it cannot be restored "
                                  "into this arena — re-save it with this version or drop the optimizer state")
             buf[: vec.numel()].copy_(vec)
+        if key == "accumulated_gradients" and hasattr(optimizer, "set_unpushed"):
+            optimizer.set_unpushed(buf)       # overlap mode keeps no accumulator: the snapshot is rewound instead
 
 
 def load_checkpoint(path: str, model: torch.nn.Module, optimizer=None, map_location="cpu") -> Dict[str, Any]:

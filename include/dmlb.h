@@ -176,21 +176,11 @@ int dmlb_scale_rows_f32(void* x, const float* scale, long long rows, int C, int 
  * gradients as they are consumed (replaces the next step's zero_grad memset). */
 int dmlb_sgd_flat(float* params, float* grads, float* acc, float* mom, void* shadow_bf16, long long n, const float* lr_ptr, float mu,
                   float wd, int zero_grads, void* stream);
-/* dmlb_sgd_flat whose accumulator is named indirectly (*acc_slot, a device location holding the buffer's address): the asynchronous
- * optimizer swaps two accumulators so a push can drain one on a communication stream while training fills the other. */
-int dmlb_sgd_flat_slot(float* params, float* grads, void* acc_slot, float* mom, void* shadow_bf16, long long n, const float* lr_ptr, float mu,
-                       float wd, int zero_grads, void* stream);
-/* Superset of the two: direct or indirect accumulator, and the table-backed weight shadows (absolute-address table of
- * dmlb_refresh_shadows) refreshed by the same launch; [table_lo, table_hi) = element range of params that holds those weights. */
-int dmlb_sgd_flat_ex(float* params, float* grads, float* acc, void* acc_slot, float* mom, void* shadow_bf16, long long n, const float* lr_ptr,
-                     float mu, float wd, int zero_grads, const void* table, int n_entries, int table_is_f32, long long table_lo,
-                     long long table_hi, const float* pulled, const void* pull_flag, void* stream);
-/* (pulled, pull_flag: while the device word *pull_flag is non-zero the replica is re-based on the fetched server parameters,
- *  theta = pulled + accumulator — the landing of an overlapped pull, Asynchronous.py:17-18 — instead of theta -= lr * g.) */
-int dmlb_store_u64_u32(void* slot, unsigned long long value, void* flag, unsigned fvalue, void* stream);
-int dmlb_store_u64(void* slot, unsigned long long value, void* stream);   /* *slot = value, stream ordered */
-/* Landing of an overlapped pull (Asynchronous.py:17-18): params = pulled (+ *unpushed_slot), bf16 mirror refreshed in the same pass. */
-int dmlb_apply_pull(float* params, const float* pulled, void* unpushed_slot, void* shadow_bf16, long long n, void* stream);
+/* dmlb_sgd_flat plus the table-backed weight shadows (absolute-address table of dmlb_refresh_shadows) refreshed by the same launch;
+ * [table_lo, table_hi) = element range of params that holds those weights. */
+int dmlb_sgd_flat_ex(float* params, float* grads, float* acc, float* mom, void* shadow_bf16, long long n, const float* lr_ptr, float mu,
+                     float wd, int zero_grads, const void* table, int n_entries, int table_is_f32, long long table_lo, long long table_hi,
+                     void* stream);
 /* fp32 NCHW batch (the reference's input, example/main.py:64-70) -> channels-last activation with one 16-byte granule per pixel
  * (C <= 8 bf16 / 4 fp32 channels, the rest zero): the input layout of dmlb_conv_smallc_*. */
 int dmlb_nchw_to_act_bf16(const float* x, void* y, int B, int C, int H, int W, int hp, int wp, int ph, int pw, void* stream);
@@ -258,6 +248,13 @@ int dmlb_comm_chunk_elems(void);                          /* mailbox chunk (shar
 int dmlb_comm_flag_words(void);                           /* uint32 words of the per-GPU flag block of the sync kernel */
 /* K1 (Asynchronous.py:55,58-60 + server add): master[owner][i] += acc[i]; acc[i] = 0 — vector red.add over NVLink. */
 int dmlb_push_add(float* acc, void* const* master_ptrs, int world, long long shard_size, long long n, void* stream);
+/* Delta forms of K1 / K2: the worker keeps a SNAPSHOT of its replica as of the last push instead of an accumulator; the update sent is
+ * live - snapshot (exact), the snapshot advances to the value read.  Saves the accumulator's read + write in every training step and may
+ * run concurrently with training.  dmlb_land_pull applies a fetched pull: params = pulled + (params - snapshot), snapshot = pulled. */
+int dmlb_push_delta(const float* live, float* snapshot, void* const* master_ptrs, int world, long long shard_size, long long n, void* stream);
+int dmlb_push_mailbox_delta(const float* live, float* snapshot, void* busy, const void* pulled_ver, void* const* mailbox_ptrs,
+                            void* const* full_ptrs, int rank, int world, long long shard_size, void* stream);
+int dmlb_land_pull(float* params, const float* pulled, float* snapshot, void* shadow_bf16, long long n, void* stream);
 /* K3 (Asynchronous.py:17-18,48-49): params[i] = master[owner][i] by peer loads, fused with the cast into the worker's flat bf16
  * weight mirror (shadow_bf16, may be NULL); optional per-chunk version snapshot. */
 int dmlb_pull(float* params, void* shadow_bf16, void* const* master_ptrs, void* const* version_ptrs, void* pulled_ver, int world,
