@@ -30,19 +30,35 @@ struct PeerTable {
 // It is safe to run while training keeps writing `live`: each element is read once, so every local update is sent exactly once.
 __global__ void __launch_bounds__(256) push_add_kernel(float* __restrict__ acc, const float* __restrict__ live, PeerTable masters,
                                                        long long shard_size, long long n4) {
-    for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < n4; i += 1ll * gridDim.x * blockDim.x) {
-        const long long e = i * 4;
-        const int owner = static_cast<int>(e / shard_size);
-        float* dst = static_cast<float*>(masters.ptr[owner]) + (e - owner * shard_size);
-        float4 a = reinterpret_cast<float4*>(acc)[i];
-        if (live != nullptr) {
-            const float4 p = ld_volatile_f32x4(live + e);
-            reinterpret_cast<float4*>(acc)[i] = p;
-            a.x = p.x - a.x; a.y = p.y - a.y; a.z = p.z - a.z; a.w = p.w - a.w;
-        } else {
-            reinterpret_cast<float4*>(acc)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    // Runs with a small grid next to the training step: keep kUnroll independent 16-byte loads (x2 in the delta form) in flight per thread.
+    constexpr int kUnroll = 4;
+    const long long stride = 1ll * gridDim.x * blockDim.x;
+    for (long long i0 = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i0 < n4; i0 += stride * kUnroll) {
+        float4 a[kUnroll], p[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const long long i = i0 + u * stride;
+            if (i < n4) {
+                a[u] = reinterpret_cast<float4*>(acc)[i];
+                if (live != nullptr) p[u] = ld_volatile_f32x4(live + 4 * i);
+            }
         }
-        if (a.x != 0.f || a.y != 0.f || a.z != 0.f || a.w != 0.f) red_add_f32x4_sys(dst, a.x, a.y, a.z, a.w);
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const long long i = i0 + u * stride;
+            if (i >= n4) continue;
+            const long long e = i * 4;
+            const int owner = static_cast<int>(e / shard_size);
+            float* dst = static_cast<float*>(masters.ptr[owner]) + (e - owner * shard_size);
+            float4 d = a[u];
+            if (live != nullptr) {
+                reinterpret_cast<float4*>(acc)[i] = p[u];
+                d.x = p[u].x - d.x; d.y = p[u].y - d.y; d.z = p[u].z - d.z; d.w = p[u].w - d.w;
+            } else {
+                reinterpret_cast<float4*>(acc)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            if (d.x != 0.f || d.y != 0.f || d.z != 0.f || d.w != 0.f) red_add_f32x4_sys(dst, d.x, d.y, d.z, d.w);
+        }
     }
 }
 

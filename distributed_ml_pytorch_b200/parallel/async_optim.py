@@ -81,7 +81,7 @@ class Asynchronous(ArenaOptimizer):
     def __init__(self, params, lr, n_push: int, n_pull: int, model: torch.nn.Module, momentum: float = 0.0,
                  staleness: Optional[str] = None, staleness_param: float = 0.9, transport: str = "auto", group=None,
                  init_rank: Optional[int] = None, torn_pulls: bool = False, server_rank: int = msg.SERVER_RANK,
-                 blocking_pull: bool = False, pull_timeout_s: float = 60.0, server_ranks=None, overlap: bool = True, pull_lag: int = 1,
+                 blocking_pull: bool = False, pull_timeout_s: float = 60.0, server_ranks=None, overlap: bool = True, pull_lag: int = 2,
                  comm_blocks: int = 24):
         if lr < 0.0:
             raise ValueError("Invalid learning rate: {}".format(lr))

@@ -68,12 +68,10 @@ def test_mailbox_momentum_and_staleness_world1():
     opt = Asynchronous(net.parameters(), lr=0.05, n_push=1, n_pull=1000, model=net, momentum=0.5, staleness="inverse")
     theta = opt.server_parameters().clone()
     v = torch.zeros_like(theta)
-    prev = opt.arena.flat_params().clone()     # arena order == server order
     for i in range(4):
         _steps(net, opt, 1, seed0=i)
-        cur = opt.arena.flat_params().clone()
-        delta = cur - prev                   # = -lr * g of this step (pull is far away, replica only does local SGD)
-        prev = cur
+        delta = opt.arena.flat_grads() * (-0.05)   # this step's update, arena order == server order (the replica itself also moves
+                                                   # when the step-0 pull lands, so it is not measured on the replica)
         tau = max(0, i - 1)                  # step 0 pushes then pulls (version 1); afterwards the snapshot ages by one per push
         v = 0.5 * v + delta / (1.0 + tau)
         theta = theta + v
@@ -178,7 +176,7 @@ def _mgpu_async(rank, size, out_dir, steps, momentum):
         OF.cross_entropy(net(x), y).backward()
         opt._apply_pending()
         local_sum += opt.arena.flat_grads() * (-0.02)      # this worker's -lr*g contribution (the replica itself also moves when a
-        opt.step_local()                                   # fetched pull lands inside the optimizer kernel)
+        opt.step_local()                                   # fetched pull lands)
         opt.communicate()
     opt.finish()
     final = opt.server_parameters().cpu()
