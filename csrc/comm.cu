@@ -356,6 +356,167 @@ __global__ void __launch_bounds__(512) sync_nvls_kernel(const float* __restrict_
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// TMA bulk forms of K1 / K3 (1-D `cp.async.bulk`, no tensor map): one thread per CTA moves 16 KiB tiles through a shared-memory ring.
+//   pull: peer master --cp.async.bulk--> smem --cp.async.bulk--> local params (+ bf16 mirror written by the CTA's threads)
+//   push: local accumulator (or replica + snapshot) --cp.async.bulk--> smem --cp.reduce.async.bulk.add.f32--> peer master
+// A tile is one mailbox chunk, so it never straddles two owners.  Each CTA walks a CONTIGUOUS run of tiles: at any moment the grid
+// touches ~one 2 MiB page per CTA on the remote side instead of thousands (the per-thread grid-stride movers above spread every warp
+// over the whole vector, which is what made them fall off above ~256 MB).  None of these loads uses multicast.
+// ---------------------------------------------------------------------------------------------
+constexpr int kBulkStages = 4;                  // pull, push: 4 x 16 KiB tiles in flight per CTA
+constexpr int kBulkStagesDelta = 2;             // delta push: 2 x (snapshot tile + replica tile)
+constexpr uint32_t kTileBytes = kChunk * 4;
+
+__device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_smem), "l"(src), "r"(bytes),
+                 "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst, uint32_t src_smem, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src_smem), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_red_add_f32(void* dst, uint32_t src_smem, uint32_t bytes) {
+    asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(dst), "r"(src_smem), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory"); }
+
+__device__ __forceinline__ void tile_run(long long n_tiles, long long* t0, long long* t1) {
+    const long long per = (n_tiles + gridDim.x - 1) / gridDim.x;
+    *t0 = blockIdx.x * per;
+    *t1 = *t0 + per < n_tiles ? *t0 + per : n_tiles;
+}
+
+__global__ void __launch_bounds__(128) pull_bulk_kernel(float* __restrict__ params, __nv_bfloat16* __restrict__ shadow, PeerTable masters,
+                                                        PeerTable versions, uint32_t* __restrict__ pulled_ver, long long shard_size,
+                                                        long long n_tiles, int chunks_per_shard) {
+    extern __shared__ __align__(128) uint8_t bulk_smem[];
+    __shared__ __align__(8) uint64_t full[kBulkStages];
+    long long t0, t1;
+    tile_run(n_tiles, &t0, &t1);
+    if (t0 >= t1) return;
+    const int tid = threadIdx.x;
+    const uint32_t tiles = smem_u32(bulk_smem);
+    if (tid == 0) {
+        for (int s = 0; s < kBulkStages; ++s) mbar_init(smem_u32(&full[s]), 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+    auto issue = [&](long long t) {
+        const int stage = static_cast<int>((t - t0) % kBulkStages);
+        const long long e = t * kChunk;
+        const int owner = static_cast<int>(e / shard_size);
+        const float* src = static_cast<const float*>(masters.ptr[owner]) + (e - owner * shard_size);
+        mbar_arrive_expect_tx(smem_u32(&full[stage]), kTileBytes);
+        bulk_g2s(tiles + stage * kTileBytes, src, kTileBytes, smem_u32(&full[stage]));
+    };
+    if (tid == 0)
+        for (int k = 0; k < kBulkStages && t0 + k < t1; ++k) issue(t0 + k);
+    const bool all_threads = shadow != nullptr;
+    if (!all_threads && tid != 0) return;
+    for (long long t = t0; t < t1; ++t) {
+        const long long it = t - t0;
+        const int stage = static_cast<int>(it % kBulkStages);
+        mbar_wait(smem_u32(&full[stage]), static_cast<uint32_t>((it / kBulkStages) & 1));
+        const long long e = t * kChunk;
+        if (all_threads) {   // bf16 mirror for the tensor cores, same flat offsets
+            const float4* src = reinterpret_cast<const float4*>(bulk_smem + stage * kTileBytes);
+            for (int j = tid; j < kChunk / 4; j += blockDim.x) {
+                const float4 v = src[j];
+                uint2 h;
+                h.x = pack_bf16x2(v.x, v.y);
+                h.y = pack_bf16x2(v.z, v.w);
+                reinterpret_cast<uint2*>(shadow + e)[j] = h;
+            }
+        }
+        if (tid == 0) {
+            bulk_s2g(params + e, tiles + stage * kTileBytes, kTileBytes);
+            bulk_commit();
+            if (pulled_ver != nullptr) {
+                const int owner = static_cast<int>(e / shard_size);
+                const int lc = static_cast<int>((e - owner * shard_size) / kChunk);
+                pulled_ver[owner * chunks_per_shard + lc] = ld_relaxed_sys_u32(static_cast<const uint32_t*>(versions.ptr[owner]) + lc);
+            }
+        }
+        if (all_threads) __syncthreads();            // everybody is done reading the PREVIOUS stage as well
+        if (tid == 0 && it >= 1 && t - 1 + kBulkStages < t1) {
+            bulk_wait_read<1>();                      // all stores but the newest have read their tile: the previous stage is free
+            issue(t - 1 + kBulkStages);
+        }
+    }
+    if (tid == 0) bulk_wait<0>();
+}
+
+// kDelta = false: master += acc, acc = 0.   kDelta = true: master += live - snapshot, snapshot = live (acc is the snapshot).
+template <bool kDelta>
+__global__ void __launch_bounds__(128) push_bulk_kernel(float* __restrict__ acc, const float* __restrict__ live, PeerTable masters,
+                                                        long long shard_size, long long n_tiles) {
+    extern __shared__ __align__(128) uint8_t bulk_smem[];
+    constexpr int kStages = kDelta ? kBulkStagesDelta : kBulkStages;
+    __shared__ __align__(8) uint64_t full[kStages];
+    constexpr uint32_t kStageBytes = kDelta ? 2 * kTileBytes : kTileBytes;
+    long long t0, t1;
+    tile_run(n_tiles, &t0, &t1);
+    if (t0 >= t1) return;
+    const int tid = threadIdx.x;
+    const uint32_t tiles = smem_u32(bulk_smem);
+    uint8_t* zero_tile = bulk_smem + kStages * kStageBytes;     // kDelta = false only: source of "acc = 0"
+    if (!kDelta) {
+        for (int j = tid; j < kChunk / 4; j += blockDim.x) reinterpret_cast<float4*>(zero_tile)[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        fence_proxy_async_smem();
+    }
+    if (tid == 0) {
+        for (int s = 0; s < kStages; ++s) mbar_init(smem_u32(&full[s]), 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+    auto issue = [&](long long t) {
+        const int stage = static_cast<int>((t - t0) % kStages);
+        const long long e = t * kChunk;
+        mbar_arrive_expect_tx(smem_u32(&full[stage]), kStageBytes);
+        bulk_g2s(tiles + stage * kStageBytes, acc + e, kTileBytes, smem_u32(&full[stage]));
+        if (kDelta) bulk_g2s(tiles + stage * kStageBytes + kTileBytes, live + e, kTileBytes, smem_u32(&full[stage]));
+    };
+    if (tid == 0)
+        for (int k = 0; k < kStages && t0 + k < t1; ++k) issue(t0 + k);
+    if (!kDelta && tid != 0) return;
+    for (long long t = t0; t < t1; ++t) {
+        const long long it = t - t0;
+        const int stage = static_cast<int>(it % kStages);
+        mbar_wait(smem_u32(&full[stage]), static_cast<uint32_t>((it / kStages) & 1));
+        const long long e = t * kChunk;
+        const int owner = static_cast<int>(e / shard_size);
+        float* dst = static_cast<float*>(masters.ptr[owner]) + (e - owner * shard_size);
+        if (kDelta) {
+            float4* snap = reinterpret_cast<float4*>(bulk_smem + stage * kStageBytes);
+            const float4* cur = reinterpret_cast<const float4*>(bulk_smem + stage * kStageBytes + kTileBytes);
+            for (int j = tid; j < kChunk / 4; j += blockDim.x) {
+                const float4 p = cur[j];
+                float4 q = snap[j];
+                q.x = p.x - q.x; q.y = p.y - q.y; q.z = p.z - q.z; q.w = p.w - q.w;
+                snap[j] = q;
+            }
+            fence_proxy_async_smem();                 // the difference was written by threads, the reduction reads it through the async proxy
+            __syncthreads();
+        }
+        if (tid == 0) {
+            bulk_red_add_f32(dst, tiles + stage * kStageBytes, kTileBytes);
+            if (kDelta) bulk_s2g(acc + e, tiles + stage * kStageBytes + kTileBytes, kTileBytes);       // snapshot = the value just sent
+            else        bulk_s2g(acc + e, smem_u32(zero_tile), kTileBytes);
+            bulk_commit();
+            if (it >= 1 && t - 1 + kStages < t1) {
+                bulk_wait_read<1>();
+                issue(t - 1 + kStages);
+            }
+        }
+    }
+    if (tid == 0) bulk_wait<0>();
+}
+
 // Grid cap of the push / pull movers (0 = two CTAs per SM).  An optimizer that overlaps them with training sets a small cap: the transfer
 // then trickles in the background of the next steps instead of taking every SM away from them for a few microseconds.
 static int g_comm_max_blocks = 0;
@@ -397,10 +558,54 @@ using namespace dmlb;
 extern "C" int dmlb_comm_chunk_elems() { return kChunk; }
 extern "C" int dmlb_comm_flag_words() { return 2 * kMaxPeers + 2; }
 
+// Which mover dmlb_push_add / dmlb_push_delta / dmlb_pull use: 0 = by size (bulk from DMLB_BULK_MIN_BYTES, default 8 MiB, when the grid
+// is not capped), 1 = per-thread ld / red, 2 = TMA bulk.
+static int g_comm_mover = 0;
+extern "C" void dmlb_set_comm_mover(int m) { g_comm_mover = (m >= 0 && m <= 2) ? m : 0; }
+
+static bool use_bulk(long long n, long long shard_size) {
+    if (shard_size % kChunk != 0 || n % kChunk != 0) return false;
+    if (g_comm_mover != 0) return g_comm_mover == 2;
+    static long long min_bytes = -1;
+    if (min_bytes < 0) {
+        const char* e = getenv("DMLB_BULK_MIN_BYTES");
+        min_bytes = (e != nullptr && atoll(e) >= 0) ? atoll(e) : (8ll << 20);
+    }
+    return g_comm_max_blocks == 0 && n * 4 >= min_bytes;
+}
+
+// One CTA per SM: 64 KiB in flight per SM is several times what the link needs (770 GB/s x ~3 us / 148 SMs = 16 KiB); three CTAs per SM
+// measured the same below 64 MB and 5-10 % slower above (2 GPUs).
+static int bulk_grid(long long n_tiles) {
+    long long cap = dmlb_sm_count();
+    if (g_comm_max_blocks > 0 && g_comm_max_blocks < cap) cap = g_comm_max_blocks;
+    return static_cast<int>(n_tiles < cap ? n_tiles : cap);
+}
+
+template <typename Kern>
+static int bulk_smem_attr(Kern kern, int bytes) {
+    DMLB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    return 0;
+}
+
 static int push_add_impl(float* acc, const float* live, void* const* master_ptrs, int world, long long shard_size, long long n, void* stream) {
     DMLB_REQUIRE(n % 4 == 0 && shard_size % 4 == 0, "lengths must be multiples of 4");
     PeerTable t;
     if (fill_table(&t, master_ptrs, world)) return -2;
+    if (use_bulk(n, shard_size)) {
+        const long long n_tiles = n / kChunk;
+        if (live != nullptr) {
+            const int smem = kBulkStagesDelta * 2 * kTileBytes;
+            if (bulk_smem_attr(push_bulk_kernel<true>, smem)) return -1;
+            push_bulk_kernel<true><<<bulk_grid(n_tiles), 128, smem, static_cast<cudaStream_t>(stream)>>>(acc, live, t, shard_size, n_tiles);
+        } else {
+            const int smem = (kBulkStages + 1) * kTileBytes;
+            if (bulk_smem_attr(push_bulk_kernel<false>, smem)) return -1;
+            push_bulk_kernel<false><<<bulk_grid(n_tiles), 128, smem, static_cast<cudaStream_t>(stream)>>>(acc, live, t, shard_size, n_tiles);
+        }
+        DMLB_LAUNCH_CHECK();
+        return 0;
+    }
     push_add_kernel<<<comm_grid(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(acc, live, t, shard_size, n / 4);
     DMLB_LAUNCH_CHECK();
     return 0;
@@ -428,6 +633,16 @@ extern "C" int dmlb_pull(float* params, void* shadow_bf16, void* const* master_p
     } else {
         for (int i = 0; i < kMaxPeers; ++i) v.ptr[i] = nullptr;
         pulled_ver = nullptr;
+    }
+    if (use_bulk(n, shard_size)) {
+        const long long n_tiles = n / kChunk;
+        const int smem = kBulkStages * kTileBytes;
+        if (bulk_smem_attr(pull_bulk_kernel, smem)) return -1;
+        pull_bulk_kernel<<<bulk_grid(n_tiles), 128, smem, static_cast<cudaStream_t>(stream)>>>(
+            params, static_cast<__nv_bfloat16*>(shadow_bf16), t, v, static_cast<uint32_t*>(pulled_ver), shard_size, n_tiles,
+            static_cast<int>(shard_size / kChunk));
+        DMLB_LAUNCH_CHECK();
+        return 0;
     }
     pull_kernel<<<comm_grid(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(params, static_cast<__nv_bfloat16*>(shadow_bf16), t, v,
                                                                                      static_cast<uint32_t*>(pulled_ver), shard_size,

@@ -160,6 +160,12 @@ def set_comm_max_blocks(n: int) -> None:
     _native.lib().dmlb_set_comm_max_blocks(int(n))
 
 
+def set_comm_mover(mover: int) -> None:
+    """Mover of the push / pull kernels launched next: 0 = chosen by size, 1 = per-thread ``ld`` / ``red.add``, 2 = TMA bulk copies
+    (``cp.async.bulk`` through shared memory, ``cp.reduce.async.bulk.add.f32`` into the owner)."""
+    _native.lib().dmlb_set_comm_mover(int(mover))
+
+
 def push_add(acc: torch.Tensor, master_table, world: int, shard_size: int, n: int) -> None:
     _native.call("dmlb_push_add", acc.data_ptr(), master_table, world, shard_size, n, _stream())
 

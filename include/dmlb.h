@@ -251,6 +251,9 @@ int dmlb_push_add(float* acc, void* const* master_ptrs, int world, long long sha
 /* Delta forms of K1 / K2: the worker keeps a SNAPSHOT of its replica as of the last push instead of an accumulator; the update sent is
  * live - snapshot (exact), the snapshot advances to the value read.  Saves the accumulator's read + write in every training step and may
  * run concurrently with training.  dmlb_land_pull applies a fetched pull: params = pulled + (params - snapshot), snapshot = pulled. */
+/* Mover used by dmlb_push_add / dmlb_push_delta / dmlb_pull: 0 = by size, 1 = per-thread ld / red.add, 2 = TMA bulk
+ * (cp.async.bulk through a shared-memory ring, cp.reduce.async.bulk.add.f32 into the owner). */
+void dmlb_set_comm_mover(int mover);
 int dmlb_push_delta(const float* live, float* snapshot, void* const* master_ptrs, int world, long long shard_size, long long n, void* stream);
 int dmlb_push_mailbox_delta(const float* live, float* snapshot, void* busy, const void* pulled_ver, void* const* mailbox_ptrs,
                             void* const* full_ptrs, int rank, int world, long long shard_size, void* stream);

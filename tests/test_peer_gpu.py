@@ -300,3 +300,69 @@ def test_train_step_graph_with_dropout_and_lr_schedule():
         g["lr"] = 0.0                       # a scheduler would do this between steps
     ts(x, y, sync=True)
     assert torch.equal(opt.arena.flat_params(), before)
+
+
+def _bulk_vs_thread(dev, pg, world, rank, tiles_per_shard=5):
+    """TMA bulk movers against the per-thread movers on the same inputs: push_add, push_delta, pull (+ bf16 mirror, version snapshot)."""
+    from distributed_ml_pytorch_b200.parallel import peer
+    chunk = peer.chunk_elems()
+    shard = tiles_per_shard * chunk
+    n = shard * world
+    g = torch.Generator(device=dev).manual_seed(7 + rank)
+    out = {}
+    for name, mv in (("thread", 1), ("bulk", 2)):
+        peer.set_comm_mover(mv)
+        master = pg.symmetric(shard * 4)
+        version = pg.symmetric(tiles_per_shard * 4)
+        master.view(torch.float32, shard).copy_(torch.arange(shard, device=dev, dtype=torch.float32) * 1e-3 + rank)
+        version.view(torch.int32, tiles_per_shard).copy_(torch.arange(tiles_per_shard, device=dev, dtype=torch.int32) + 10 * rank)
+        g.manual_seed(7 + rank)
+        acc = torch.randn(n, device=dev, generator=g)
+        live = torch.randn(n, device=dev, generator=g)
+        snap = live + torch.randn(n, device=dev, generator=g) * 1e-2
+        live0 = live.clone()
+        pg.barrier()
+        peer.push_add(acc, master.table, world, shard, n)
+        peer.push_delta(live, snap, master.table, world, shard, n)
+        torch.cuda.synchronize(dev)
+        pg.barrier()
+        params = torch.empty(n, device=dev)
+        shadow = torch.empty(n, device=dev, dtype=torch.bfloat16)
+        pv = torch.zeros(world * tiles_per_shard, dtype=torch.int32, device=dev)
+        peer.pull(params, master.table, world, shard, n, version.table, pv, shadow=shadow)
+        torch.cuda.synchronize(dev)
+        pg.barrier()
+        assert acc.abs().sum().item() == 0.0 and torch.equal(snap, live) and torch.equal(live, live0)
+        assert torch.equal(shadow.float(), params.to(torch.bfloat16).float())
+        out[name] = (params.cpu(), pv.cpu())
+        del master, version
+    peer.set_comm_mover(0)
+    torch.testing.assert_close(out["bulk"][0], out["thread"][0], rtol=1e-5, atol=1e-5)   # fp32 adds from several GPUs land in any order
+    assert torch.equal(out["bulk"][1], out["thread"][1])
+    expect_ver = torch.cat([torch.arange(tiles_per_shard, dtype=torch.int32) + 10 * r for r in range(world)])
+    assert torch.equal(out["bulk"][1], expect_ver)
+
+
+def test_bulk_movers_match_thread_movers_world1():
+    from distributed_ml_pytorch_b200.parallel import peer
+    dev = torch.device("cuda", 0)
+    pg = peer.PeerGroup(device=dev)
+    _bulk_vs_thread(dev, pg, 1, 0, tiles_per_shard=331)       # more tiles than CTAs, uneven runs, several ring wraps
+    _bulk_vs_thread(dev, pg, 1, 0, tiles_per_shard=3)
+    pg.close()
+
+
+def _mgpu_bulk(rank, size, out_dir):
+    from distributed_ml_pytorch_b200.parallel import peer
+    dev = torch.device("cuda", rank)
+    pg = peer.PeerGroup(device=dev)
+    _bulk_vs_thread(dev, pg, size, rank, tiles_per_shard=37)
+    pg.close()
+    torch.save({"ok": True}, os.path.join(out_dir, f"bulk{rank}.pt"))
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_bulk_movers_match_thread_movers_multi_gpu(tmp_path, world):
+    _need(world)
+    spawn(_mgpu_bulk, world, backend="nccl", args=(str(tmp_path),))
+    assert all(os.path.exists(tmp_path / f"bulk{r}.pt") for r in range(world))

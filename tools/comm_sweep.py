@@ -60,6 +60,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--max-mb", type=int, default=1024)
     ap.add_argument("--out", default=None)
+    ap.add_argument("--min-kb", type=int, default=1)
+    ap.add_argument("--movers-only", action="store_true", help="only the push / pull movers (per-thread and TMA bulk forms), no sync / NCCL columns")
     a = ap.parse_args()
     rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(local)
@@ -69,7 +71,7 @@ def main():
     chunk = peer.chunk_elems()
     lr = torch.tensor([0.01], device=dev)
     rows = []
-    nbytes = 1 << 10
+    nbytes = a.min_kb << 10
     while nbytes <= a.max_mb << 20:
         n = max(nbytes // 4, 4)
         shard = ((n + world - 1) // world + chunk - 1) // chunk * chunk
@@ -93,6 +95,39 @@ def main():
             peer.sync_rs_update_ag(grads_s.table, params_s.table, flags.table, None, rank, world, shard, lr, 0.0, 0.0, 1.0 / world)
             dist.all_reduce(nccl_buf)
         pg.barrier()
+        movers = {}
+        snap = torch.zeros(padded, device=dev)
+        wire = n * 4 * (world - 1) / world if world > 1 else n * 4
+        for name, mv in (("thread", 1), ("bulk", 2)):
+            peer.set_comm_mover(mv)
+            for _ in range(2):
+                peer.push_add(acc, master.table, world, shard, padded)
+                peer.push_delta(params, snap, master.table, world, shard, padded)
+                peer.pull(params, master.table, world, shard, padded)
+            pg.barrier()
+            tp = max_ranks(timed(lambda: peer.push_add(acc, master.table, world, shard, padded), iters, pre=lambda: acc.fill_(1.0)), dev)
+            pg.barrier()
+            td = max_ranks(timed(lambda: peer.push_delta(params, snap, master.table, world, shard, padded), iters,
+                                 pre=lambda: params.add_(1.0)), dev)      # a delta of zero is not sent by the per-thread form
+            pg.barrier()
+            tl = max_ranks(timed(lambda: peer.pull(params, master.table, world, shard, padded), iters), dev)
+            pg.barrier()
+            movers[name] = {"push_us": tp * 1e3, "push_delta_us": td * 1e3, "pull_us": tl * 1e3, "push_gbs": wire / (tp * 1e-3) / 1e9,
+                            "push_delta_gbs": wire / (td * 1e-3) / 1e9, "pull_gbs": wire / (tl * 1e-3) / 1e9}
+        peer.set_comm_mover(0)
+        del snap
+        if a.movers_only:
+            row = {"bytes": n * 4, "world": world, "movers": movers,
+                   "best_push_frac_of_link": max(m["push_gbs"] for m in movers.values()) / LINK_GBS if world > 1 else None,
+                   "best_pull_frac_of_link": max(m["pull_gbs"] for m in movers.values()) / LINK_GBS if world > 1 else None}
+            rows.append(row)
+            if rank == 0:
+                print(json.dumps(row), flush=True)
+            del acc, params, grads, nccl_buf, nccl_p
+            pg.close()
+            pg = peer.PeerGroup(device=dev)
+            nbytes *= 4
+            continue
         t_push = max_ranks(timed(lambda: peer.push_add(acc, master.table, world, shard, padded), iters, pre=lambda: acc.fill_(1.0)), dev)
         pg.barrier()
         t_pull = max_ranks(timed(lambda: peer.pull(params, master.table, world, shard, padded), iters), dev)
@@ -138,7 +173,7 @@ def main():
                 ms = 0.0
             t_p2p = max_ranks(ms, dev)
         wire = n * 4 * (world - 1) / world
-        row = {"bytes": n * 4, "world": world,
+        row = {"bytes": n * 4, "world": world, "movers": movers,
                "push_us": t_push * 1e3, "pull_us": t_pull * 1e3, "sync_us": t_sync * 1e3, "sync_nvls_us": (t_nvls * 1e3 if t_nvls else None),
                "nccl_allreduce_sgd_us": t_nccl * 1e3,
                "p2p_us": (t_p2p * 1e3 if t_p2p is not None else None),
