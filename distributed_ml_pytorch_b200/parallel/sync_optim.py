@@ -13,7 +13,7 @@ travels over NVLink while the earlier layers are still differentiating.  Inside 
 All of this is capturable: in :class:`~distributed_ml_pytorch_b200.engine.TrainStep` the bucket kernels are parallel
 branches of the step's CUDA graph.
 
-NVLS: when the arenas can be mapped behind an NVSwitch multicast address (``nvls=None`` = use it when available), the
+NVLS: when the arenas can be mapped behind an NVSwitch multicast address (``nvls=None`` = use it where it was measured faster: :func:`nvls_pays`), the
 reduce-scatter is one ``multimem.ld_reduce`` per 16 bytes (summed inside the switch) and the all-gather one ``multimem.st``.
 
 On CPU tensors (gloo) the same optimizer falls back to ``dist.all_reduce`` + an in-place update.
@@ -63,6 +63,8 @@ class Synchronous(ArenaOptimizer):
             # the all-gather run inside the switch (multimem.ld_reduce / multimem.st).  Otherwise: CUDA-IPC buffers, peer loads/stores.
             self.nvls = False
             self.params_sym = self.grads_sym = self.flags_sym = None
+            if nvls is None and not nvls_pays(world, padded * 4):
+                nvls = False                     # measured: the peer-load form is faster here (see nvls_pays)
             if world > 1 and nvls is not False:
                 try:
                     self.params_sym = peer.SymmMemBuffer(padded * 4, device, group)
@@ -247,3 +249,11 @@ class Synchronous(ArenaOptimizer):
         self.params_sym = self.grads_sym = self.flags_sym = None
         self.peer.close()
         self.peer = None
+
+
+def nvls_pays(world: int, nbytes: int) -> bool:
+    """Should the synchronous step reduce / broadcast inside the NVSwitch (``multimem``) or with peer loads / stores?  From the measured
+    sweeps (profiles/comm_sweep_2gpu_nvls.json, comm_sweep_8gpu_v3_nvls.json): at 2 GPUs the peer form is never slower and wins from
+    4 MB up (64 MB: 120 vs 182 us); at 8 GPUs the switch wins from 1 KB (18 vs 23 us) to 256 MB (604 vs 776 us) and loses at 1 GB
+    (3.43 vs 3.08 ms).  ``Synchronous(nvls=True / False)`` overrides."""
+    return world >= 4 and nbytes <= (512 << 20)
