@@ -6,6 +6,7 @@ rank 1, both print it), spawned as two local processes on 127.0.0.1:29500.
     python pytorch_p2p_ex.py --backend nccl     # 2 GPUs: ncclSend/ncclRecv over NVLink, issued on a side stream and
                                                 # overlapped with compute on the main stream
     python pytorch_p2p_ex.py --backend nccl --sweep    # bandwidth sweep 1 KB - 1 GB (BASELINE.json config 5)
+    python pytorch_p2p_ex.py --backend nccl --overlap  # send || tcgen05 GEMM vs send + GEMM, 1 MB - 1 GB
 
 Point-to-point stays on NCCL by design (BASELINE.json north star); everything bulk goes through the fused
 peer-memory kernels in distributed_ml_pytorch_b200.parallel instead.
@@ -56,6 +57,21 @@ def sweep(rank, size, backend="nccl"):
             print("{bytes:>12d} B  {ms:10.4f} ms  {gbs:8.2f} GB/s".format(**r))
 
 
+def overlap(rank, size, backend="nccl"):
+    """How much of a 1 MB .. 1 GB send hides behind the package's own tensor-core GEMM on the main stream."""
+    from distributed_ml_pytorch_b200.parallel.p2p import p2p_overlap_sweep
+    rows = p2p_overlap_sweep(rank, size)
+    if rank == 0:
+        import json
+        for r in rows:
+            print("{bytes:>12d} B  send {send_ms:8.4f} ms ({send_gbs:6.1f} GB/s)  {gemms:3d} GEMM {gemm_ms:8.4f} ms ({gemm_tflops:6.1f} TFLOP/s)  "
+                  "together {both_ms:8.4f} ms  hidden {hidden:5.2f}".format(**r))
+        out = os.environ.get("P2P_OVERLAP_OUT")
+        if out:
+            with open(out, "w") as f:
+                json.dump(rows, f, indent=1)
+
+
 def init_process(rank, size, fn, backend="gloo"):
     """Initialize the distributed environment."""
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -73,12 +89,13 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--backend", default="gloo", choices=["gloo", "nccl"])
     ap.add_argument("--sweep", action="store_true")
+    ap.add_argument("--overlap", action="store_true", help="nccl: measure how much of a send hides behind the tcgen05 GEMM (1 MB - 1 GB)")
     a = ap.parse_args()
     size = 2
     processes = []
     mp.set_start_method("spawn")
     for rank in range(size):
-        p = mp.Process(target=init_process, args=(rank, size, sweep if a.sweep else run, a.backend))
+        p = mp.Process(target=init_process, args=(rank, size, overlap if a.overlap else sweep if a.sweep else run, a.backend))
         p.start()
         processes.append(p)
     for p in processes:
