@@ -12,7 +12,7 @@
 //     are rejected with an error, never truncated.  Every GPU that loads the library carries these 4 MiB until
 //     the process exits, whether or not this entry point is ever called.
 //   * The first call on each device looks up the array's device address (cudaGetSymbolAddress with that device
-//     current).  Make that first call before you start any stream capture on that device.
+//     current).  Make that first call during start-up.
 //   * This function calls no cudaMalloc, cudaFree or any allocating library routine (torch's included).
 //   * All calls on a device share the one array, and it keeps whatever the previous call left in it.  Each call
 //     therefore clears the part it is about to use (on `stream`) before accumulating into it.  Two calls whose

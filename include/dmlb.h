@@ -119,7 +119,7 @@ int dmlb_gemm_bias_act_splitk(const void* A, int lda, const void* Wt, int ldb, i
  * The fp32 workspace is a fixed array inside the library: M * round_up(N,4) must not exceed
  * dmlb_noalloc_scratch_capacity() floats (1 Mi floats = 4 MiB per GPU, held until process exit); larger problems are
  * rejected with an error.  Calls no cudaMalloc/cudaFree or other allocating routine.  The first call on a device
- * resolves the array's address — issue it before any stream capture on that device.  All calls on a device share
+ * resolves the array's address (make it during start-up).  All calls on a device share
  * the array (each call clears the region it uses first), so calls whose GPU work overlaps race: keep them on one
  * stream or order them yourself.  See csrc/splitk_static.cu. */
 long long dmlb_noalloc_scratch_capacity(void);

@@ -66,6 +66,34 @@ def test_noalloc_matches_workspace_entry_point_twice(M, N, K, split):
         assert _rel_err(y_new[:, :N], fp32) < 1e-2
 
 
+def test_noalloc_leaves_free_device_memory_unchanged():
+    """``cudaMemGetInfo`` before and after: the call must not take (or return) a single byte of device memory — not on the first
+    call on the device, which looks the array's address up, and not on later ones."""
+    lib = _lib()
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+
+    def free_bytes():
+        return torch.cuda.mem_get_info(dev)[0]          # cudaMemGetInfo: free bytes of the whole device, all allocators included
+
+    M, N, K, split = 256, 384, 1728, 13
+    ldy = (N + 7) // 8 * 8
+    a = torch.randn(M, K, device=dev).to(torch.bfloat16).contiguous()
+    w = (torch.randn(N, K, device=dev) * 0.05).to(torch.bfloat16).contiguous()
+    bias = torch.randn(N, device=dev)
+    y = torch.zeros(M, ldy, device=dev, dtype=torch.bfloat16)
+    stream = torch.cuda.current_stream().cuda_stream
+    torch.cuda.synchronize()
+    for _ in range(3):
+        before = free_bytes()
+        rc = lib.dmlb_gemm_bias_act_splitk_noalloc(a.data_ptr(), K, w.data_ptr(), K, M, N, K, bias.data_ptr(), 1, y.data_ptr(), ldy, split, stream)
+        assert rc == 0, lib.dmlb_last_error()
+        during = free_bytes()
+        torch.cuda.synchronize()
+        after = free_bytes()
+        assert before == during == after, (before, during, after)
+
+
 def test_noalloc_rejects_oversized_problem():
     lib = _lib()
     dev = torch.device("cuda", 0)
