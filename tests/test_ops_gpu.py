@@ -193,6 +193,41 @@ def test_dropout_statistics_and_backward():
     assert torch.all(per_plane.min(-1).values == per_plane.max(-1).values)
 
 
+def test_dropout_masks_are_independent_across_elements_and_calls():
+    """The mask generator is a counter hash (splitmix of seed, call counter, element index), not Philox: check what training relies on.
+    (a) keep-rate per call is binomial around 1-p (chi-square over 64 calls); (b) no correlation between neighbouring elements
+    (lags 1, 2, 8, row pitch) inside a call; (c) no correlation between the masks of consecutive calls, element by element;
+    (d) the 4-bit patterns of 4 consecutive elements are uniform (chi-square, 15 dof)."""
+    dev = "cuda"
+    rows, cols, p = 512, 256, 0.5
+    n = rows * cols
+    x, _ = OF.as_act2(torch.ones(rows, cols, device=dev, dtype=torch.bfloat16))
+    calls = 64
+    masks = torch.stack([(OF.dropout(x, p, True).float()[:, :cols] != 0).float() for _ in range(calls)])       # [calls, rows, cols]
+    # (a) each call keeps Binomial(n, 1-p): z-scores of the per-call keep counts ~ N(0,1) -> sum of squares ~ chi2(calls)
+    z = (masks.sum((1, 2)) - n * (1 - p)) / (n * p * (1 - p)) ** 0.5
+    chi2 = float((z ** 2).sum())
+    assert 30.0 < chi2 < 115.0, chi2                      # chi2(64): 0.01 % tails at ~29 / ~116
+    assert float(z.abs().max()) < 4.5
+    # (b) lag correlations inside a call: each estimate has sigma = 1/sqrt(n * calls) ~ 3.5e-4
+    m = masks - masks.mean()
+    flat = m.reshape(calls, -1)
+    var = float((flat ** 2).mean())
+    for lag in (1, 2, 8, cols):
+        c = float((flat[:, :-lag] * flat[:, lag:]).mean()) / var
+        assert abs(c) < 2.5e-3, (lag, c)
+    # (c) consecutive calls, same element
+    c = float((m[:-1] * m[1:]).mean()) / var
+    assert abs(c) < 2.5e-3, c
+    # (d) 4-element patterns
+    bits = masks.reshape(calls, -1, 4)
+    code = (bits * torch.tensor([1.0, 2.0, 4.0, 8.0], device=dev)).sum(-1).long().flatten()
+    counts = torch.bincount(code, minlength=16).float()
+    expect = code.numel() / 16.0
+    chi2p = float(((counts - expect) ** 2 / expect).sum())
+    assert chi2p < 50.0, chi2p                            # chi2(15): 1e-5 tail at ~48
+
+
 def test_sgd_flat_and_shadow_refresh():
     torch.manual_seed(6)
     dev = "cuda"
