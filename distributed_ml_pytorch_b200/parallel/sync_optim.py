@@ -253,7 +253,10 @@ class Synchronous(ArenaOptimizer):
 
 def nvls_pays(world: int, nbytes: int) -> bool:
     """Should the synchronous step reduce / broadcast inside the NVSwitch (``multimem``) or with peer loads / stores?  From the measured
-    sweeps (profiles/comm_sweep_2gpu_nvls.json, comm_sweep_8gpu_v3_nvls.json): at 2 GPUs the peer form is never slower and wins from
-    4 MB up (64 MB: 120 vs 182 us); at 8 GPUs the switch wins from 1 KB (18 vs 23 us) to 256 MB (604 vs 776 us) and loses at 1 GB
-    (3.43 vs 3.08 ms).  ``Synchronous(nvls=True / False)`` overrides."""
-    return world >= 4 and nbytes <= (512 << 20)
+    sweeps (profiles/comm_sweep_2gpu_nvls.json, r2_comm_sweep_4gpu.json, comm_sweep_8gpu_v3_nvls.json): at 2 GPUs the peer form is never
+    slower and wins from 4 MB up (64 MB: 120 vs 182 us); at 4 GPUs the switch is 5-10 % ahead up to 4 MB and behind at 16-64 MB
+    (56 vs 65 us); at 8 GPUs it wins from 1 KB (18 vs 23 us) to 256 MB (604 vs 776 us) and loses at 1 GB (3.43 vs 3.08 ms).
+    ``Synchronous(nvls=True / False)`` overrides."""
+    if world >= 8:
+        return nbytes <= (512 << 20)
+    return world >= 4 and nbytes <= (8 << 20)
