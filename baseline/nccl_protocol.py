@@ -14,7 +14,9 @@ CUDA tensor [sender, code, payload(N)] — with dist.isend / dist.irecv on the N
     ParameterUpdate                       server -> worker reply; the worker overwrites its model when the reply has arrived
 
 NCCL has no receive-from-anyone and is not thread safe per communicator, so the reference's listener THREAD becomes a posted
-irecv that is polled between steps (worker) and one posted irecv per worker that the serve loop polls (server).  Everything
+irecv that is polled between steps (worker) and one posted irecv per worker that the serve loop polls (server).  Each
+server <-> worker pair talks over its own two-rank communicator: point-to-point operations of ONE communicator execute in
+issue order, so with a single communicator a reply to worker 2 would sit behind the posted receive from worker 1.  Everything
 else — message sizes, cadence, per-tensor SGD launches, ravel / unravel copies — is the reference's.
 Prints one JSON line: images/sec = batch * workers * steps / max-over-ranks device time (CUDA events).
 """
@@ -46,10 +48,10 @@ def unravel(model, flat):
         o += n
 
 
-def serve(n, world, dev):
+def serve(n, world, dev, pairs):
     theta = torch.zeros(n, device=dev)
     bufs = [torch.zeros(n + 2, device=dev) for _ in range(world)]
-    works = [None] + [dist.irecv(bufs[w], src=w) for w in range(1, world)]
+    works = [None] + [dist.irecv(bufs[w], src=w, group=pairs[w]) for w in range(1, world)]
     sends = []
     alive = world - 1
     have_init = False
@@ -74,14 +76,14 @@ def serve(n, world, dev):
                 m = torch.empty(n + 2, device=dev)
                 m[0], m[1] = 0.0, UPD
                 m[2:].copy_(theta)
-                sends.append((dist.isend(m, dst=w), m))
+                sends.append((dist.isend(m, dst=w, group=pairs[w]), m))
                 sends = [(s, t) for (s, t) in sends if not s.is_completed()]
-            works[w] = dist.irecv(bufs[w], src=w)
+            works[w] = dist.irecv(bufs[w], src=w, group=pairs[w])
     for s, _ in sends:
         s.wait()
 
 
-def work(args, rank, world, dev):
+def work(args, rank, world, dev, pair):
     from models import AlexNet                                     # the reference's model, unmodified
     torch.manual_seed(1234)
     net = AlexNet().to(dev)
@@ -95,7 +97,7 @@ def work(args, rank, world, dev):
         m = torch.empty(n + 2, device=dev)
         m[0], m[1] = float(rank), code
         m[2:].copy_(payload)
-        pending_sends.append((dist.isend(m, dst=0), m))
+        pending_sends.append((dist.isend(m, dst=0, group=pair), m))
         while len(pending_sends) > 8:
             pending_sends.pop(0)[0].wait()
 
@@ -125,7 +127,7 @@ def work(args, rank, world, dev):
         if idx % n_pull == 0:
             send(REQ, acc)                                          # dummy payload, like the reference
             if reply_work is None:
-                reply_work = dist.irecv(reply, src=0)
+                reply_work = dist.irecv(reply, src=0, group=pair)
         acc.add_(ravel(net, grads=True), alpha=-lr)
         if idx % n_push == 0:
             send(GRAD, acc)
@@ -161,12 +163,13 @@ def main():
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     from models import AlexNet
     n = sum(p.numel() for p in AlexNet().parameters())
+    pairs = [None] + [dist.new_group(ranks=[0, w], backend="nccl") for w in range(1, world)]   # collective: every rank creates all
     t0 = time.time()
     ms = 0.0
     if rank == 0:
-        serve(n, world, dev)
+        serve(n, world, dev, pairs)
     else:
-        ms = work(args, rank, world, dev)
+        ms = work(args, rank, world, dev, pairs[rank])
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     if rank == 0:
