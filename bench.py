@@ -50,6 +50,7 @@ def parse():
     ap.add_argument("--classes", type=int, default=10)
     ap.add_argument("--momentum", type=float, default=0.0)
     ap.add_argument("--staleness", default=None)
+    ap.add_argument("--server-gain", default="auto", help="async + --momentum: auto = (1 - mu) / workers, none = 1, or a number")
     ap.add_argument("--pull-lag", type=int, default=None, help="async mode: steps between issuing a pull and landing it (default: the optimizer's)")
     ap.add_argument("--dtype", choices=["tf32", "bf16"], default=None,
                     help="CUDA compute dtype (default: tf32 for the reference's LeNet / AlexNet = the reference's own precision, bf16 for the ResNets)")
@@ -252,6 +253,7 @@ def make_optimizer(args, model, rank, world, device):
         how = "NVLS multimem.ld_reduce/multimem.st" if getattr(opt, "nvls", False) else "NVLink peer loads/stores"
         return opt, f"sync-dp{world} fused reduce-scatter+update+all-gather ({how}), 4 buckets overlapped with backward"
     opt = Asynchronous(model.parameters(), lr=LR, n_push=N_PUSH, n_pull=N_PULL, model=model, momentum=args.momentum, staleness=args.staleness,
+                       server_gain=(None if args.server_gain == "none" else args.server_gain if args.server_gain == "auto" else float(args.server_gain)),
                        **({} if args.pull_lag is None else {"pull_lag": args.pull_lag}))
     return opt, f"async-ps dp{world}, parameter server sharded over {world} GPU(s), fused NVLink push/pull"
 

@@ -165,7 +165,7 @@ __device__ __forceinline__ float staleness_scale(int mode, float param, uint32_t
 __global__ void __launch_bounds__(256) owner_apply_kernel(float* __restrict__ master, float* __restrict__ mom, uint32_t* __restrict__ version,
                                                           uint32_t* __restrict__ full, const float* __restrict__ mailbox, PeerTable busys,
                                                           uint32_t* __restrict__ stats, int rank, int world, long long shard_size, int cps,
-                                                          float mu, int stale_mode, float stale_param) {
+                                                          float mu, int stale_mode, float stale_param, float gain) {
     __shared__ uint32_t s_flag;
     for (int lc = blockIdx.x; lc < cps; lc += gridDim.x) {
         for (int w = 0; w < world; ++w) {
@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(256) owner_apply_kernel(float* __restrict__ ma
             if (flag == 0) continue;
             const uint32_t ver = version[lc];
             const uint32_t tau = ver - (flag - 1u);
-            const float s = staleness_scale(stale_mode, stale_param, tau);
+            const float s = gain * staleness_scale(stale_mode, stale_param, tau);
             const float* src = mailbox + static_cast<long long>(w) * shard_size + static_cast<long long>(lc) * kChunk;
             float* th = master + static_cast<long long>(lc) * kChunk;
             for (int j = threadIdx.x; j < kChunk / 4; j += blockDim.x) {
@@ -683,7 +683,8 @@ static int push_mailbox_impl(float* acc, const float* live, void* busy, const vo
 }
 
 extern "C" int dmlb_owner_apply(float* master, float* mom, void* version, void* full, const float* mailbox, void* const* busy_ptrs, void* stats,
-                                int rank, int world, long long shard_size, float mu, int stale_mode, float stale_param, void* stream) {
+                                int rank, int world, long long shard_size, float mu, int stale_mode, float stale_param, float gain,
+                                void* stream) {
     DMLB_REQUIRE(shard_size % kChunk == 0, "shard size must be a multiple of the chunk size");
     PeerTable b;
     if (fill_table(&b, busy_ptrs, world)) return -2;
@@ -694,7 +695,7 @@ extern "C" int dmlb_owner_apply(float* master, float* mom, void* version, void* 
     owner_apply_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(master, mom, static_cast<uint32_t*>(version),
                                                                              static_cast<uint32_t*>(full), mailbox, b,
                                                                              static_cast<uint32_t*>(stats), rank, world, shard_size, cps, mu,
-                                                                             stale_mode, stale_param);
+                                                                             stale_mode, stale_param, gain);
     DMLB_LAUNCH_CHECK();
     return 0;
 }

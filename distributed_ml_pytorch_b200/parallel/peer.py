@@ -34,7 +34,7 @@ _native.register("dmlb_pull", [c_vp, c_vp, _PP, _PP, c_vp, c_int, c_ll, c_ll, c_
 _native.register("dmlb_push_delta", [c_vp, c_vp, _PP, c_int, c_ll, c_ll, c_vp])
 _native.register("dmlb_push_mailbox_delta", [c_vp, c_vp, c_vp, c_vp, _PP, _PP, c_int, c_int, c_ll, c_vp])
 _native.register("dmlb_push_mailbox", [c_vp, c_vp, c_vp, _PP, _PP, c_int, c_int, c_ll, c_vp])
-_native.register("dmlb_owner_apply", [c_vp, c_vp, c_vp, c_vp, c_vp, _PP, c_vp, c_int, c_int, c_ll, c_float, c_int, c_float, c_vp])
+_native.register("dmlb_owner_apply", [c_vp, c_vp, c_vp, c_vp, c_vp, _PP, c_vp, c_int, c_int, c_ll, c_float, c_int, c_float, c_float, c_vp])
 _native.register("dmlb_sync_rs_update_ag", [_PP, _PP, _PP, c_vp, c_int, c_int, c_ll, c_vp, c_float, c_float, c_float, c_vp])
 _native.register("dmlb_sync_nvls_range", [c_vp, c_vp, c_vp, _PP, c_vp, c_int, c_int, c_ll, c_ll, c_vp, c_float, c_float, c_float, c_int, c_vp])
 _native.register("dmlb_sync_rs_update_ag_range", [_PP, _PP, _PP, c_vp, c_int, c_int, c_ll, c_ll, c_vp, c_float, c_float, c_float, c_int, c_vp])
@@ -191,10 +191,10 @@ def push_mailbox(acc, busy, pulled_ver, mailbox_table, full_table, rank, world, 
                  _stream())
 
 
-def owner_apply(master, mom, version, full, mailbox, busy_table, stats, rank, world, shard_size, mu, stale_mode, stale_param) -> None:
+def owner_apply(master, mom, version, full, mailbox, busy_table, stats, rank, world, shard_size, mu, stale_mode, stale_param, gain=1.0) -> None:
     _native.call("dmlb_owner_apply", master.data_ptr(), mom.data_ptr() if mom is not None else None, version.data_ptr(), full.data_ptr(),
                  mailbox.data_ptr(), busy_table, stats.data_ptr() if stats is not None else None, rank, world, shard_size, float(mu),
-                 int(stale_mode), float(stale_param), _stream())
+                 int(stale_mode), float(stale_param), float(gain), _stream())
 
 
 def sync_rs_update_ag(grad_table, param_table, flag_table, mom, rank, world, shard_size, lr_dev, mu, wd, grad_scale) -> None:

@@ -38,7 +38,8 @@ class WorkerLost(RuntimeError):
 
 class ParameterServer:
     def __init__(self, model: torch.nn.Module, n_workers: Optional[int] = None, momentum: float = 0.0, staleness: Optional[str] = None,
-                 staleness_param: float = 0.9, group=None, shard_index: int = 0, n_shards: int = 1, idle_timeout_s: Optional[float] = None):
+                 staleness_param: float = 0.9, group=None, shard_index: int = 0, n_shards: int = 1, idle_timeout_s: Optional[float] = None,
+                 gain=None):
         """``n_shards > 1``: the flat parameter vector is cut into ``n_shards`` contiguous pieces (``ShardMap``, the same cut the
         workers use) and this server owns piece ``shard_index``; every message payload is then that slice (NORTH-STAR sharded
         server, SURVEY.md §2.4 — the reference has exactly one server rank)."""
@@ -58,6 +59,8 @@ class ParameterServer:
         if n_workers is None and dist.is_available() and dist.is_initialized():
             n_workers = dist.get_world_size(group) - self.n_shards
         self.n_workers = n_workers
+        from .async_optim import resolve_server_gain
+        self.gain = resolve_server_gain(gain, self.momentum, n_workers or 1)     # "auto": (1 - mu) / workers, see resolve_server_gain
         self.done_workers = set()
         self.running = False
         self.counters = {"ParameterUpdate": 0, "GradientUpdate": 0, "ParameterRequest": 0}
@@ -72,7 +75,7 @@ class ParameterServer:
         elif message_code == MessageCode.GradientUpdate:
             tau = self.version - self.pulled_version.get(sender, self.version)
             self.staleness_hist[tau] = self.staleness_hist.get(tau, 0) + 1
-            s = staleness_scale(self.staleness, self.staleness_param, tau)
+            s = self.gain * staleness_scale(self.staleness, self.staleness_param, tau)
             delta = parameter[: self.parameter_shard.numel()]
             if self.velocity is not None:
                 self.velocity.mul_(self.momentum).add_(delta, alpha=s)
@@ -149,14 +152,15 @@ class ParameterServer:
     # ------------------------------------------------------------------------------------------
     @staticmethod
     def run_peer(model: torch.nn.Module, lr: float = 0.0, momentum: float = 0.0, staleness: Optional[str] = None, group=None,
-                 poll_s: float = 0.0005):
+                 poll_s: float = 0.0005, gain=None):
         """``--server`` rank on the NVLink transport: join the peer group as a shard owner that does not train.
 
         The rank allocates the same symmetric buffers as the workers (collective), then — for the mailbox protocol —
         keeps applying incoming updates to its shard until every worker has reached ``finish()``.
         """
         from .async_optim import Asynchronous
-        opt = Asynchronous(model.parameters(), lr=lr, n_push=1, n_pull=1, model=model, momentum=momentum, staleness=staleness, group=group)
+        opt = Asynchronous(model.parameters(), lr=lr, n_push=1, n_pull=1, model=model, momentum=momentum, staleness=staleness, group=group,
+                           server_gain=gain)
         dev = opt.arena.params.device
         work = dist.barrier(group=group, async_op=True) if opt.peer.world > 1 else None
         while work is not None and not work.is_completed():

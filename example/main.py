@@ -91,6 +91,11 @@ def get_dataset(args, transform=None):
     return train, test
 
 
+def _gain(args):
+    g = getattr(args, "server_gain", "auto")
+    return None if g in (None, "none") else g if g == "auto" else float(g)
+
+
 def make_optimizer(args, net):
     if args.no_distributed:
         if args.cuda:
@@ -100,7 +105,7 @@ def make_optimizer(args, net):
         return Synchronous(net.parameters(), lr=args.lr, model=net, momentum=args.momentum)
     servers = list(range(args.num_servers)) if (args.num_servers > 1 and not args.cuda) else None
     return Asynchronous(net.parameters(), lr=args.lr, n_push=args.num_push, n_pull=args.num_pull, model=net, momentum=args.momentum,
-                        staleness=args.staleness, server_ranks=servers)
+                        staleness=args.staleness, server_ranks=servers, server_gain=_gain(args))
 
 
 def main(args):
@@ -260,9 +265,9 @@ def init_server(args):
         device = torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0)))
         torch.cuda.set_device(device)
         torch.manual_seed(args.seed)
-        ParameterServer.run_peer(model.to(device), momentum=args.momentum, staleness=args.staleness)
+        ParameterServer.run_peer(model.to(device), momentum=args.momentum, staleness=args.staleness, gain=_gain(args))
         return
-    server = ParameterServer(model=model, momentum=args.momentum, staleness=args.staleness, shard_index=args.rank if args.num_servers > 1 else 0,
+    server = ParameterServer(model=model, momentum=args.momentum, staleness=args.staleness, gain=_gain(args), shard_index=args.rank if args.num_servers > 1 else 0,
                              n_shards=args.num_servers, idle_timeout_s=args.server_idle_timeout_s)
     server.run()
     if args.trace:
@@ -296,6 +301,8 @@ def build_parser():
                         "lenet / alexnet); bf16 = bf16 operands and activations over fp32 masters (default for the resnets)")
     parser.add_argument("--momentum", type=float, default=0.0)
     parser.add_argument("--staleness", default=None, choices=[None, "none", "inverse", "exp"])
+    parser.add_argument("--server-gain", default="auto", help="gain of the server's momentum update: auto = (1 - momentum) / workers (the "
+                        "step size of plain SGD whatever the worker count), none = 1 (classic), or a number; no effect without --momentum")
     parser.add_argument("--backend", default=None, help="torch.distributed backend (default: nccl with --cuda, gloo otherwise)")
     parser.add_argument("--trace", default=None, help="write a Chrome / Perfetto trace of this process (steps, push / pull, server "
                         "messages) to this path; distributed runs add .rank<N>")

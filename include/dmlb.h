@@ -265,8 +265,10 @@ int dmlb_pull(float* params, void* shadow_bf16, void* const* master_ptrs, void* 
 /* K2 (NORTH-STAR momentum / staleness): chunked mailbox push and owner-side apply. */
 int dmlb_push_mailbox(float* acc, void* busy, const void* pulled_ver, void* const* mailbox_ptrs, void* const* full_ptrs, int rank, int world,
                       long long shard_size, void* stream);
+/* owner: v = mu * v + gain * s(tau) * delta; theta += v   (gain = 1: the classic update; (1 - mu) / workers keeps the step size of
+ * plain SGD when several workers feed one momentum buffer) */
 int dmlb_owner_apply(float* master, float* mom, void* version, void* full, const float* mailbox, void* const* busy_ptrs, void* stats, int rank,
-                     int world, long long shard_size, float mu, int stale_mode, float stale_param, void* stream);
+                     int world, long long shard_size, float mu, int stale_mode, float stale_param, float gain, void* stream);
 /* K4 (NORTH-STAR synchronous mode): barrier + reduce-scatter + SGD/momentum + all-gather + barrier in one kernel. */
 int dmlb_sync_rs_update_ag(void* const* grad_ptrs, void* const* param_ptrs, void* const* flag_ptrs, float* mom, int rank, int world,
                            long long shard_size, const float* lr_ptr, float mu, float wd, float grad_scale, void* stream);

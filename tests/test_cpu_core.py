@@ -200,3 +200,32 @@ def test_parameter_server_message_semantics_without_a_network(monkeypatch):
     assert ps2.staleness_hist == {0: 2, 2: 1}
     snap = ps2.snapshot()
     assert set(snap.keys()) == set(LeNet().state_dict().keys())
+
+
+def test_server_gain_keeps_momentum_server_stable_with_many_workers():
+    """Round 1's ResNet-50 run with server momentum 0.9 and 8 workers climbed to loss 10: W workers feeding one momentum buffer step
+    W * lr / (1 - mu) per unit of gradient.  On f = |theta|^2 / 2 with lr = 0.1 that is 8 (diverges); gain='auto' brings it back to 0.1."""
+    from distributed_ml_pytorch_b200.parallel.async_optim import resolve_server_gain
+    from distributed_ml_pytorch_b200.parallel.server import ParameterServer
+    from distributed_ml_pytorch_b200.utils.messaging import MessageCode
+    assert resolve_server_gain(None, 0.9, 8) == 1.0
+    assert resolve_server_gain("auto", 0.9, 8) == pytest.approx(0.0125)
+    assert resolve_server_gain("auto", 0.0, 8) == 1.0          # no momentum: the reference's plain sum of updates
+    assert resolve_server_gain(0.5, 0.9, 8) == 0.5
+
+    def run(gain):
+        net = torch.nn.Linear(4, 1, bias=False)
+        with torch.no_grad():
+            net.weight.fill_(1.0)
+        ps = ParameterServer(net, n_workers=8, momentum=0.9, gain=gain)
+        for w in range(1, 9):
+            ps.pulled_version[w] = 0
+        for _ in range(60):
+            theta = ps.parameter_shard.clone()
+            for w in range(1, 9):
+                ps.receive(w, MessageCode.GradientUpdate, -0.1 * theta)        # every worker's gradient of |theta|^2 / 2 at the pulled point
+                ps.pulled_version[w] = ps.version
+        return float(ps.parameter_shard.norm())
+
+    assert run("auto") < 0.05                # converging: 2.0 -> ~1e-3 in 60 rounds
+    assert not run(None) < 1e3               # the classic update with 8 workers blows up
