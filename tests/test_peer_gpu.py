@@ -366,3 +366,38 @@ def test_bulk_movers_match_thread_movers_multi_gpu(tmp_path, world):
     _need(world)
     spawn(_mgpu_bulk, world, backend="nccl", args=(str(tmp_path),))
     assert all(os.path.exists(tmp_path / f"bulk{r}.pt") for r in range(world))
+
+
+def _mgpu_momentum_converges(rank, size, out_dir, steps):
+    """BASELINE config 4 in small: ResNet-18, asynchronous, server momentum 0.9 + inverse-staleness scaling, server_gain='auto'."""
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(0)
+    net = build_model("resnet18").to(dev).train()
+    opt = Asynchronous(net.parameters(), lr=0.05, n_push=2, n_pull=2, model=net, momentum=0.9, staleness="inverse", server_gain="auto")
+    g = torch.Generator().manual_seed(50 + rank)
+    x = torch.randn(32, 3, 32, 32, generator=g).to(dev)          # one fixed batch per worker: the run has to memorise it
+    y = torch.randint(0, 10, (32,), generator=g).to(dev)
+    losses = []
+    for _ in range(steps):
+        opt.zero_grad()
+        loss = OF.cross_entropy(net(x), y)
+        loss.backward()
+        opt.step()
+        losses.append(loss.item())
+    opt.finish()
+    torch.save({"losses": losses, "stats": opt.staleness_stats(), "gain": opt.server_gain}, os.path.join(out_dir, f"conv{rank}.pt"))
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_async_momentum_staleness_trains_multi_gpu(tmp_path, world):
+    """Round 1: this configuration (several workers feeding one server momentum buffer) climbed to loss 10.  With the gain
+    (1 - mu) / workers the loss has to fall on every worker."""
+    _need(world)
+    spawn(_mgpu_momentum_converges, world, backend="nccl", args=(str(tmp_path), 80))
+    for r in range(world):
+        o = torch.load(tmp_path / f"conv{r}.pt", weights_only=False)
+        first, last = sum(o["losses"][:5]) / 5, sum(o["losses"][-5:]) / 5
+        print(f"rank {r}: loss {first:.3f} -> {last:.3f}, gain {o['gain']:.4f}, staleness {o['stats']}")
+        assert o["gain"] == pytest.approx(0.1 / world)
+        assert all(l == l and l < 20 for l in o["losses"])
+        assert last < 0.7 * first, (first, last)
