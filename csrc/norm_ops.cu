@@ -45,14 +45,17 @@ __device__ __forceinline__ RowTiling row_tiling(int C) {
 // sums[0..C) += sum over rows of a, sums[C..2C) += sum over rows of a*b'   (generic two-moment reduction)
 //   mode 0 (forward stats):  a = x,  second = x * x
 //   mode 1 (backward):       a = g = dy * mask,  second = g * xhat;  optionally stores g
+// The block's partial sums go through shared memory WITHOUT atomics: every thread parks its 16 register sums in its own slot, then each
+// of the slab's 2 x 8 x c8n columns is summed over the row lanes by one thread and leaves the block as one red.add.  (The first version
+// used shared-memory atomics: 4096 per block with up to 32 threads on one address, which cost more than streaming the block's rows.)
+constexpr int kBnPartFloats = 256 * 16;
+template <int mode, int kU>
 __global__ void __launch_bounds__(256) bn_reduce_kernel(const __nv_bfloat16* __restrict__ x, int ldx, const __nv_bfloat16* __restrict__ dy, int lddy,
                                                         const __nv_bfloat16* __restrict__ yact, int ldya, __nv_bfloat16* __restrict__ gout, int ldg,
-                                                        const float* __restrict__ mean_rstd, float* __restrict__ sums, long long M, int C, int mode,
+                                                        const float* __restrict__ mean_rstd, float* __restrict__ sums, long long M, int C,
                                                         int relu) {
     pdl_prologue();
-    extern __shared__ float ssum[];  // [2 * 256]: this block's channel slab
-    for (int i = threadIdx.x; i < 512; i += blockDim.x) ssum[i] = 0.f;
-    __syncthreads();
+    extern __shared__ __align__(16) float part[];  // [256 threads][16]: s1[8], s2[8] of each thread
     const RowTiling t = row_tiling(C);
     const int per = (C >> 3) < 32 ? (C >> 3) : 32;
     const int txl = threadIdx.x % per, ty = threadIdx.x / per;
@@ -66,7 +69,6 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const __nv_bfloat16* __r
     }
     if (live) {
         // kU rows per trip, every load issued before the first use: the kernel is a pure stream and lives on loads in flight
-        constexpr int kU = 4;
         const long long rstride = 1ll * gridDim.x * t.lanes;
         for (long long r0 = blockIdx.x * 1ll * t.lanes + ty; r0 < M; r0 += rstride * kU) {
             uint4 rx[kU], rd[kU], ry[kU];
@@ -106,16 +108,18 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const __nv_bfloat16* __r
                 }
             }
         }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            atomicAdd(&ssum[txl * 8 + j], s1[j]);
-            atomicAdd(&ssum[256 + txl * 8 + j], s2[j]);
-        }
+        float4* slot = reinterpret_cast<float4*>(part + (ty * per + txl) * 16);
+        slot[0] = make_float4(s1[0], s1[1], s1[2], s1[3]);
+        slot[1] = make_float4(s1[4], s1[5], s1[6], s1[7]);
+        slot[2] = make_float4(s2[0], s2[1], s2[2], s2[3]);
+        slot[3] = make_float4(s2[4], s2[5], s2[6], s2[7]);
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < t.c8n * 8; i += blockDim.x) {
-        red_add_f32(sums + t.c8_0 * 8 + i, ssum[i]);
-        red_add_f32(sums + C + t.c8_0 * 8 + i, ssum[256 + i]);
+    for (int col = threadIdx.x; col < t.c8n * 16; col += blockDim.x) {
+        float acc = 0.f;
+        for (int l = 0; l < t.lanes; ++l) acc += part[l * per * 16 + col];
+        const int g8 = col >> 4, k = col & 15;
+        red_add_f32(sums + (k < 8 ? 0 : C) + (t.c8_0 + g8) * 8 + (k & 7), acc);
     }
 }
 
@@ -134,6 +138,23 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
     const int txl = threadIdx.x % per, ty = threadIdx.x / per;
     if (ty >= t.lanes || txl >= t.c8n) return;
     const int tx = t.c8_0 + txl;
+    // The first trip's rows are requested BEFORE the per-channel constants are loaded and combined (~30 dependent scalar loads per thread):
+    // with 16 rows per thread that prologue would otherwise be a quarter of the kernel.
+    constexpr int kU = 8;
+    const long long rstride = 1ll * gridDim.x * t.lanes;
+    long long r0 = blockIdx.x * 1ll * t.lanes + ty;
+    uint4 rx[kU], rr[kU];
+    auto request = [&](long long base) {
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            const long long r = base + u * rstride;
+            if (r < M) {
+                rx[u] = __ldg(reinterpret_cast<const uint4*>(x + r * ldx + tx * 8));
+                if (res != nullptr) rr[u] = __ldg(reinterpret_cast<const uint4*>(res + r * ldr + tx * 8));
+            }
+        }
+    };
+    if (r0 < M) request(r0);
     float sc[8], sh[8];
     const float inv_m = 1.f / static_cast<float>(M);
 #pragma unroll
@@ -162,18 +183,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
         sc[j] = g * rstd;
         sh[j] = (beta != nullptr ? beta[c] : 0.f) - mean * g * rstd;
     }
-    constexpr int kU = 4;
-    const long long rstride = 1ll * gridDim.x * t.lanes;
-    for (long long r0 = blockIdx.x * 1ll * t.lanes + ty; r0 < M; r0 += rstride * kU) {
-        uint4 rx[kU], rr[kU];
-#pragma unroll
-        for (int u = 0; u < kU; ++u) {
-            const long long r = r0 + u * rstride;
-            if (r < M) {
-                rx[u] = __ldg(reinterpret_cast<const uint4*>(x + r * ldx + tx * 8));
-                if (res != nullptr) rr[u] = __ldg(reinterpret_cast<const uint4*>(res + r * ldr + tx * 8));
-            }
-        }
+    while (r0 < M) {
 #pragma unroll
         for (int u = 0; u < kU; ++u) {
             const long long r = r0 + u * rstride;
@@ -194,6 +204,8 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
             }
             *reinterpret_cast<uint4*>(y + r * ldy + tx * 8) = pack8f(v);
         }
+        r0 += rstride * kU;
+        if (r0 < M) request(r0);
     }
 }
 
@@ -208,6 +220,21 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
     const int txl = threadIdx.x % per, ty = threadIdx.x / per;
     if (ty >= t.lanes || txl >= t.c8n) return;
     const int tx = t.c8_0 + txl;
+    constexpr int kU = 4;
+    const long long rstride = 1ll * gridDim.x * t.lanes;
+    long long r0 = blockIdx.x * 1ll * t.lanes + ty;
+    uint4 rx[kU], rg[kU];
+    auto request = [&](long long base) {       // see bn_apply_kernel: rows first, constants second
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            const long long r = base + u * rstride;
+            if (r < M) {
+                rx[u] = __ldg(reinterpret_cast<const uint4*>(x + r * ldx + tx * 8));
+                rg[u] = __ldg(reinterpret_cast<const uint4*>(g + r * ldg + tx * 8));
+            }
+        }
+    };
+    if (r0 < M) request(r0);
     float mu[8], rs[8], k0[8], k1[8], k2[8];
     const float inv_m = 1.f / static_cast<float>(M);
 #pragma unroll
@@ -225,18 +252,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
             if (dbeta != nullptr) dbeta[c] += dsum[c];
         }
     }
-    constexpr int kU = 4;
-    const long long rstride = 1ll * gridDim.x * t.lanes;
-    for (long long r0 = blockIdx.x * 1ll * t.lanes + ty; r0 < M; r0 += rstride * kU) {
-        uint4 rx[kU], rg[kU];
-#pragma unroll
-        for (int u = 0; u < kU; ++u) {
-            const long long r = r0 + u * rstride;
-            if (r < M) {
-                rx[u] = __ldg(reinterpret_cast<const uint4*>(x + r * ldx + tx * 8));
-                rg[u] = __ldg(reinterpret_cast<const uint4*>(g + r * ldg + tx * 8));
-            }
-        }
+    while (r0 < M) {
 #pragma unroll
         for (int u = 0; u < kU; ++u) {
             const long long r = r0 + u * rstride;
@@ -248,6 +264,8 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const __nv_bfloat16* 
             for (int j = 0; j < 8; ++j) gv[j] = k0[j] * (gv[j] - k1[j] - (xv[j] - mu[j]) * rs[j] * k2[j]);
             *reinterpret_cast<uint4*>(dx + r * lddx + tx * 8) = pack8f(gv);
         }
+        r0 += rstride * kU;
+        if (r0 < M) request(r0);
     }
 }
 
@@ -311,10 +329,10 @@ using namespace dmlb;
 // sums: fp32 [2C], zero on entry.
 extern "C" int dmlb_bn_stats(const void* x, int ldx, float* sums, long long M, int C, void* stream) {
     DMLB_REQUIRE(BN_SHAPE_OK(C) && ldx % 8 == 0, "batch-norm kernels need C % 8 == 0, C <= 2048 and 16-byte rows");
-    DMLB_CHECK_CUDA(launch_k(bn_reduce_kernel, rows_grid(M, C), 256, 512 * sizeof(float), static_cast<cudaStream_t>(stream),
+    DMLB_CHECK_CUDA(launch_k(bn_reduce_kernel<0, 8>, rows_grid(M, C), 256, kBnPartFloats * sizeof(float), static_cast<cudaStream_t>(stream),
                              static_cast<const __nv_bfloat16*>(x), ldx, static_cast<const __nv_bfloat16*>(nullptr), 0,
                              static_cast<const __nv_bfloat16*>(nullptr), 0, static_cast<__nv_bfloat16*>(nullptr), 0,
-                             static_cast<const float*>(nullptr), sums, M, C, 0, 0));
+                             static_cast<const float*>(nullptr), sums, M, C, 0));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
@@ -335,9 +353,9 @@ extern "C" int dmlb_bn_apply(const void* x, int ldx, void* y, int ldy, const voi
 extern "C" int dmlb_bn_bwd_reduce(const void* x, int ldx, const void* dy, int lddy, const void* yact, int ldya, void* g_out, int ldg,
                                   const float* mean_rstd, float* dsum, long long M, int C, int relu, void* stream) {
     DMLB_REQUIRE(BN_SHAPE_OK(C) && ldx % 8 == 0 && lddy % 8 == 0, "batch-norm kernels need C % 8 == 0, C <= 2048 and 16-byte rows");
-    DMLB_CHECK_CUDA(launch_k(bn_reduce_kernel, rows_grid(M, C), 256, 512 * sizeof(float), static_cast<cudaStream_t>(stream),
+    DMLB_CHECK_CUDA(launch_k(bn_reduce_kernel<1, 4>, rows_grid(M, C), 256, kBnPartFloats * sizeof(float), static_cast<cudaStream_t>(stream),
                              static_cast<const __nv_bfloat16*>(x), ldx, static_cast<const __nv_bfloat16*>(dy), lddy,
-                             static_cast<const __nv_bfloat16*>(yact), ldya, static_cast<__nv_bfloat16*>(g_out), ldg, mean_rstd, dsum, M, C, 1, relu));
+                             static_cast<const __nv_bfloat16*>(yact), ldya, static_cast<__nv_bfloat16*>(g_out), ldg, mean_rstd, dsum, M, C, relu));
     DMLB_LAUNCH_CHECK();
     return 0;
 }
