@@ -100,7 +100,7 @@ def dump_sass() -> None:
     import re
     out = ROOT / "artifacts" / "sass"
     out.mkdir(parents=True, exist_ok=True)
-    keys = ("UTCHMMA", "UTCHMMA.2CTA", "UTCBAR", "UTCBAR.2CTA.MULTICAST", "LDTM", "UTMALDG.2D", "UTMALDG.2D.2CTA", "UCGABAR_ARV", "UTMALDG.3D", "UTMALDG.4D.IM2COL", "SYNCS", "REDG", "LDGMC", "STG.E.128", "LDGSTS")
+    keys = ("UTCHMMA", "UTCHMMA.2CTA", "UTCBAR", "UTCBAR.2CTA.MULTICAST", "LDTM", "UTMALDG.2D", "UTMALDG.2D.2CTA", "UCGABAR_ARV", "UTMALDG.3D", "UTMALDG.4D.IM2COL", "UBLKCP.S.G", "UBLKCP.G.S", "UBLKRED.G.S.ADD.F32", "SYNCS", "REDG", "LDGMC", "STG.E.128", "LDGSTS")
     census, per_fn = [], []
     cap = 1_200_000
     for obj in sorted(BUILD_DIR.glob("*.o")):
