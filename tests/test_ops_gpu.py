@@ -330,6 +330,38 @@ def test_resident_loader_kernel_matches_totensor_normalize():
 
 
 @pytest.mark.gpu
+def test_train_step_orders_its_copy_behind_the_producer_of_a_device_batch():
+    """GpuResidentLoader batches are produced on the caller's stream; TrainStep copies them into its staging slot on another stream.
+    Put a long-running kernel in front of the gather: without the stream ordering the copy would read the batch before it is written."""
+    from distributed_ml_pytorch_b200.engine import TrainStep
+    from distributed_ml_pytorch_b200.models import build_model
+    from distributed_ml_pytorch_b200.parallel import FusedSGD
+    from distributed_ml_pytorch_b200.utils.data import GpuResidentLoader
+    g = torch.Generator().manual_seed(1)
+    imgs = torch.randint(0, 256, (256, 32, 32, 3), generator=g, dtype=torch.uint8)
+    labels = torch.randint(0, 10, (256,), generator=g)
+    ld = GpuResidentLoader(imgs, labels, batch_size=64, device="cuda", shuffle=False)
+    net = build_model("lenet").cuda().train()
+    ts = TrainStep(net, FusedSGD(net.parameters(), lr=0.01, model=net), 64, (3, 32, 32), device=torch.device("cuda", 0))
+    big = torch.randn(8192, 8192, device="cuda")
+    for step in range(4):
+        idx = torch.arange(step * 64, step * 64 + 64, device="cuda")
+        for _ in range(3):
+            big = torch.tanh(big @ big * 1e-4)                       # ~ms of work queued on the current stream, ahead of the gather
+        x, y = ld.gather(idx)
+        slot = ts.step_count & 1
+        ts(x, y)
+        del x, y                                                    # the allocator may hand the blocks out again right away
+        junk = torch.full((64, 3, 32, 32), 7.0, device="cuda")      # ... to this
+        ts.flush()
+        sx, sy = ts._staging[slot]
+        ref = (imgs[step * 64:step * 64 + 64].permute(0, 3, 1, 2).float() / 255 - 0.5) / 0.5
+        assert torch.allclose(sx.float().cpu(), ref, atol=1e-6), step
+        assert torch.equal(sy.cpu(), labels[step * 64:step * 64 + 64]), step
+        del junk
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("name", ["alexnet", "lenet"])
 def test_eval_forward_at_reference_test_batch_size(name):
     """The reference evaluates with one 10000-image batch (main.py:143 --test-batch-size 10000)."""
