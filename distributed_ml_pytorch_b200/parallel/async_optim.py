@@ -264,7 +264,9 @@ class Asynchronous(ArenaOptimizer):
         from ..ops import kernels as K
         a = self.arena
         cur = torch.cuda.current_stream(a.params.device)
-        cur.wait_event(pp[1])                                  # fetched `pull_lag` steps ago: no wait in practice
+        # behind the fetch AND behind every push issued since (with n_push < pull_lag one may still be advancing the snapshot this kernel
+        # rewrites); both were queued steps ago, so in practice nothing waits
+        cur.wait_stream(self.comm_stream)
         # the server's parameters + the local updates it has not seen (replica - snapshot): what a pull that had landed the moment it
         # was issued, followed by the local steps since, would have produced
         K.land_pull(a.params, self._pulled, self._snapshot, a.shadow, a.padded)
