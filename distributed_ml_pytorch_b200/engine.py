@@ -74,8 +74,10 @@ class TrainStep:
                           torch.zeros((batch_size,), dtype=torch.int64, device=self.device)) for _ in range(n_slots)]
         self.static_x, self.static_y = self._staging[0]
         # A model whose first layer is a small-channel convolution (RGB input) reads a channels-last, one-16-byte-granule-per-pixel
-        # activation (zero-bordered for the row-window form): the step's first kernel lays the staged batch out that way.
+        # activation (zero-bordered for the row-window form).  The layout kernel runs on the COPY stream right behind the staging copy,
+        # one buffer per slot: it overlaps the previous step instead of being the first link of this step's kernel chain.
         self._smallc_in = False
+        self._smallc_x = None
         if cuda:
             from . import nn as dnn
             from .ops import kernels as K
@@ -83,7 +85,8 @@ class TrainStep:
             if first is not None and first._smallc() and first.in_channels == input_shape[0]:
                 C, H, W = input_shape
                 rw = K.rowwin_geometry(H, W, *first.kernel_size, *first.stride, *first.padding, first.compute_dtype)
-                self.static_x = OF.smallc_input(batch_size, C, H, W, first.compute_dtype, self.device, rw, first.padding)
+                self._smallc_x = [OF.smallc_input(batch_size, C, H, W, first.compute_dtype, self.device, rw, first.padding) for _ in range(2)]
+                self.static_x = self._smallc_x[0]
                 self._smallc_in = True
         self.metrics = torch.zeros(2, dtype=torch.float32, device=self.device)
         self.graphs = []
@@ -125,8 +128,7 @@ class TrainStep:
         sx, sy = self._staging[slot]
         self.optimizer.zero_grad()
         if self._smallc_in:
-            OF.fill_smallc_input(self.static_x, sx)          # layout (and bf16 cast) of the staged batch: the step's first kernel
-            out = self.model(self.static_x)
+            out = self.model(self._smallc_x[slot])           # laid out (and cast) by __call__ on the copy stream
         else:
             out = self.model(sx)
         if self._own_loss:
@@ -229,6 +231,8 @@ class TrainStep:
         with torch.cuda.stream(self._copy_stream):
             sx.copy_(x, non_blocking=True)
             sy.copy_(y, non_blocking=True)
+            if self._smallc_in:
+                OF.fill_smallc_input(self._smallc_x[slot], sx)
             self._staged[slot].record(self._copy_stream)
         self.stream.wait_event(self._staged[slot])
         with torch.cuda.stream(self.stream):
