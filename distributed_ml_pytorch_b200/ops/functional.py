@@ -286,6 +286,7 @@ def set_implicit_conv(flag: bool) -> bool:
 
 
 _PAIR_CONV = os.environ.get("DMLB_PAIR_CONV", "0") == "1"
+_SMALLC_WGRAD_SPLIT = int(os.environ.get("DMLB_SMALLC_WGRAD_SPLIT", "0"))     # tuning knob: K-split of the first layer's weight gradient
 
 # Backward fusion across two conv blocks (K8).  When block P declares that its output feeds exactly one consumer and that consumer is a
 # conv block C (``conv_block(..., sole_consumer=True)``; the model author's promise), C's backward finishes its split-K data-gradient
@@ -539,6 +540,8 @@ class _ConvBlockFn(torch.autograd.Function):
                     # columns of the GEMM are (tap, padded channel); the epilogue drops the pad channels and writes either order
                     hp, wp = cfg.rowwin if cfg.rowwin is not None else (0, 0)
                     split = K.pick_split_k(((Cout + 127) // 128) * ((Kpad + 127) // 128), M, bk=bk)     # tiles of the PADDED column space
+                    if _SMALLC_WGRAD_SPLIT > 0:
+                        split = _SMALLC_WGRAD_SPLIT
                     K.conv_smallc(1, a_t.data_ptr(), B, H, W, Cin, dy.data_ptr(), lddy, KH, KW, SH, SW, PH, PW, Cout, target, Kd,
                                   split_k=split, pt_layout=not gemm_order, dt=dt, hp=hp, wp=wp)
                 elif cfg.smallc:
