@@ -252,9 +252,13 @@ class Asynchronous(ArenaOptimizer):
             if update is not self._acc_buf:
                 self._acc_buf.copy_(update)
         else:
+            # the model was just loaded with the SERVER's parameters (that is what a checkpoint of this transport holds): the replica
+            # the run was stopped with is that plus the update it had not pushed yet
             a = self.arena
             torch.cuda.current_stream(a.params.device).wait_stream(self.comm_stream)
-            torch.sub(a.params, update, out=self._snapshot)
+            self._snapshot.copy_(a.params)
+            a.params.add_(update)
+            a.mark_params_changed()
 
     def _land_pull(self, force: bool = False) -> None:
         """Overlap mode: make a fetched pull the model's parameters (on the current stream, at a step boundary)."""

@@ -82,3 +82,50 @@ def test_main_py_trains_from_gpu_resident_cifar(tmp_path):
     from distributed_ml_pytorch_b200.utils.csvlog import read_csv
     rows = read_csv(os.path.join(tmp_path, "log", "gpu.csv"))
     assert len(rows) == 5 * 512 // 64                     # every sample once per epoch, fixed batch shape
+
+
+def test_async_overlap_checkpoint_restores_the_unpushed_update(tmp_path):
+    """Overlap mode keeps no accumulator (the unpushed update is replica - snapshot): a checkpoint still carries it, in logical order,
+    and a fresh optimizer resumes with exactly that much left to push."""
+    from distributed_ml_pytorch_b200.models import build_model
+    from distributed_ml_pytorch_b200.ops import functional as OF
+    from distributed_ml_pytorch_b200.parallel import Asynchronous
+    from distributed_ml_pytorch_b200.utils.checkpoint import load_model_state, load_optimizer_state, read_checkpoint, save_checkpoint
+
+    def train(net, opt, steps, seed):
+        g = torch.Generator().manual_seed(seed)
+        for _ in range(steps):
+            x = torch.randn(32, 3, 32, 32, generator=g).cuda()
+            y = torch.randint(0, 10, (32,), generator=g).cuda()
+            opt.zero_grad()
+            OF.cross_entropy(net(x), y).backward()
+            opt.step()
+
+    torch.manual_seed(0)
+    net = build_model("lenet").cuda().eval()
+    opt = Asynchronous(net.parameters(), lr=0.05, n_push=1000, n_pull=1000, model=net)       # pushes at step 0 only
+    assert opt.overlap
+    train(net, opt, 4, seed=1)
+    unpushed = opt.accumulated_gradients.clone()
+    assert unpushed.abs().sum().item() > 0
+    server = opt.server_parameters().clone()
+    replica = opt.arena.flat_params().clone()
+    torch.testing.assert_close(server + unpushed[: server.numel()], replica, rtol=1e-5, atol=1e-6)   # replica = server + not yet pushed
+    save_checkpoint(str(tmp_path / "ck.pt"), net, opt, epoch=0)
+    opt.finish()
+    opt.close()
+
+    sd, meta, ost = read_checkpoint(str(tmp_path / "ck.pt"))
+    net2 = build_model("lenet").cuda().eval()
+    load_model_state(net2, sd)                                   # the server's parameters (what a resumed run seeds the server with)
+    opt2 = Asynchronous(net2.parameters(), lr=0.05, n_push=1000, n_pull=1000, model=net2)
+    load_optimizer_state(opt2, ost)
+    assert opt2.idx == 4
+    torch.testing.assert_close(opt2.accumulated_gradients, unpushed, rtol=0, atol=1e-7)
+    torch.testing.assert_close(opt2.server_parameters(), server, rtol=0, atol=0)
+    opt2._push()                                                  # what was left goes to the server exactly once
+    torch.cuda.synchronize()
+    torch.testing.assert_close(opt2.server_parameters(), server + unpushed[: server.numel()], rtol=1e-5, atol=1e-6)
+    assert opt2.accumulated_gradients.abs().sum().item() == 0.0
+    opt2.finish()
+    opt2.close()
