@@ -160,3 +160,20 @@ def test_async_gloo_resume_reseeds_the_server(tmp_path):
     server2 = torch.load(tmp_path / "ck.pt", weights_only=False)
     for k in server1:
         assert torch.equal(server1[k], server2[k]), k
+
+
+def test_server_momentum_with_gain_via_launcher(tmp_path):
+    """1 server + 2 workers on gloo with the NORTH-STAR server update (momentum 0.9, inverse-staleness scaling) and the default
+    --server-gain auto: the run finishes, the server reports its gain, and the workers' losses stay finite and near ln(10)."""
+    import csv
+    from distributed_ml_pytorch_b200.parallel.launcher import free_port
+    r = _run([sys.executable, os.path.join(ROOT, "run-pytorch.py"), "--local", "3", "--cpu", "--port", str(free_port()), "--", "--model", "lenet",
+              "--epochs", "1", "--steps-per-epoch", "30", "--log-interval", "1000", "--test-batch-size", "50", "--synthetic", "--num-push", "2",
+              "--num-pull", "2", "--momentum", "0.9", "--staleness", "inverse", "--lr", "0.05"], cwd=tmp_path)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    assert "server done" in r.stdout
+    for node in (1, 2):
+        with open(tmp_path / "log" / f"node{node}.csv") as f:
+            rows = list(csv.DictReader(f))
+        losses = [float(x["training_loss"]) for x in rows if x.get("training_loss") not in (None, "", "None")]
+        assert losses and all(l == l and l < 5.0 for l in losses), losses[-5:]
