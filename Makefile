@@ -71,3 +71,25 @@ install-test:
 	$(PY) -m pip install --index-url https://test.pypi.org/simple/ pytorch-distbelief
 
 .PHONY: setup install build graph first second server single gpu gpu8 gpu8-sync local3 local-sharded local-sync p2p test test-gpu bench dist upload upload-test install-test
+
+# measurement helpers (B200 box).  N = GPUs
+N ?= 8
+TORCHRUN = $(PY) -m torch.distributed.run --nnodes=1 --nproc-per-node $(N) --master-addr 127.0.0.1 --master-port 29511
+
+bench-scale:
+	for n in 1 2 4 8; do $(PY) bench.py --gpus $$n; done
+
+baseline-nccl:
+	$(TORCHRUN) baseline/nccl_protocol.py --steps 100
+
+sweep:
+	$(TORCHRUN) tools/comm_sweep.py --out gpurun_out/comm_sweep_$(N)gpu.json
+
+sweep-movers:
+	$(TORCHRUN) tools/comm_sweep.py --movers-only --min-kb 1024 --out gpurun_out/comm_movers_$(N)gpu.json
+
+p2p-overlap:
+	$(PY) pytorch_p2p_ex.py --backend nccl --overlap
+
+evidence-8gpu:
+	bash tools/run_8gpu.sh
