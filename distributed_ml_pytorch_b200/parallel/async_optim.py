@@ -83,6 +83,14 @@ class Asynchronous(ArenaOptimizer):
                  init_rank: Optional[int] = None, torn_pulls: bool = False, server_rank: int = msg.SERVER_RANK,
                  blocking_pull: bool = False, pull_timeout_s: float = 60.0, server_ranks=None, overlap: bool = True, pull_lag: int = 2,
                  comm_blocks: int = 24, server_gain=None):
+        """``params, lr, n_push, n_pull, model`` are the reference's arguments (Asynchronous.py:20-31).  Additions:
+
+        ``momentum``, ``staleness`` (``None | "inverse" | "exp"``), ``staleness_param``: server-side update ``v = mu v + gain s(tau) delta``.
+        ``server_gain``: ``None`` (1), ``"auto"`` ((1 - momentum) / workers) or a number — see :func:`resolve_server_gain`.
+        ``transport``: ``"auto" | "peer" | "gloo" | "local"``; ``group``: process group of the workers.
+        ``overlap`` (peer): run pushes / pulls on a communication stream, keep a snapshot instead of an accumulator (default).
+        ``pull_lag`` (peer, overlap): steps between issuing a pull and landing it on the replica; ``comm_blocks``: CTAs of an overlapped
+        push / pull kernel.  ``init_rank``, ``server_rank(s)``, ``torn_pulls``, ``blocking_pull``, ``pull_timeout_s``: gloo transport."""
         if lr < 0.0:
             raise ValueError("Invalid learning rate: {}".format(lr))
         if n_push < 1 or n_pull < 1:
